@@ -1,0 +1,198 @@
+/*
+ * mft_b200.h — C ABI of the B200-native training-step hot path of MobileFineTuner.
+ *
+ * Every entry point is `extern "C"`, takes plain DEVICE pointers and sizes (no C++/torch types),
+ * enqueues work on the given CUDA stream and does not synchronise. Tensors are dense row-major fp32
+ * unless a leading dimension (`ld*`, in elements) is given; token ids / labels are int32.
+ * Return value: 0 = ok, non-zero = error (message via mft_last_error()). There is NO CPU fallback:
+ * the library is sm_100a-only and every call fails loudly when no such device is present.
+ *
+ * Each declaration cites the reference code it replaces (paths relative to the reference's
+ * operators/finetune_ops/ unless stated otherwise). The host-side C++ mirror of the reference's
+ * operator API (ops::Tensor, ops::matmul, LoRALinear, Adam, GPT2Model ...) lives in
+ * mobilefinetuner_b200/csrc/host and calls only these functions.
+ */
+#ifndef MFT_B200_H_
+#define MFT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* mft_stream_t; /* a cudaStream_t (NULL = default stream) */
+
+/* ------------------------------------------------------------------ library / errors */
+int mft_version(void);
+const char* mft_last_error(void);          /* thread-local, valid until the next failing call */
+int mft_device_check(void);                /* 0 iff the current device is sm_100 (B200)        */
+int mft_use_tensor_cores(int enable);      /* 1 (default): tcgen05 TF32 GEMM when eligible; 0: SIMT fp32 GEMM
+                                              everywhere (bit-faithful fp32, used by parity tests). Returns previous. */
+
+/* ------------------------------------------------------------------ GEMM
+ * C[m,n] = alpha * ( opA(A) * opB(B)  +  A2 * B2^T )  (+ bias[n])  (+ beta * C), optional GELU aux.
+ *   trans_a = 0: A stored [m,k] (lda >= k)      trans_a = 1: A stored [k,m] (lda >= m)
+ *   trans_b = 0: B stored [k,n] (ldb >= n)      trans_b = 1: B stored [n,k] (ldb >= k)
+ *   optional second K-segment (LoRA rank-r update fused into the same accumulator):
+ *       A2 stored [m,k2] (lda2), B2 stored [n,k2] (ldb2); k2 = 0 disables it.
+ *   batch > 1: strided batches (element strides), bias/second segment not batched.
+ *   gelu_out != NULL: C receives the pre-activation, gelu_out (ldc) receives gelu_tanh(C).
+ * Tensor-core path (tcgen05.mma kind::tf32, fp32 accumulate in TMEM, TMA-fed) is taken when both
+ * operands are K-major (trans_a = 0, trans_b = 1), 16-byte aligned with ld % 4 == 0; otherwise a
+ * SIMT fp32 kernel runs. Replaces ops::matmul + MatmulBackward's three products
+ * (core/ops.cpp:486-651, core/backward_functions.cpp:94-138; cblas_sgemm call sites
+ * core/ops.cpp:563,613,692,759) and the add/mul nodes of LoRALinear::forward (nn/lora_linear.cpp:47-108).
+ */
+typedef struct mft_gemm_args {
+    int32_t m, n, k;
+    const float* a; int64_t lda; int32_t trans_a;
+    const float* b; int64_t ldb; int32_t trans_b;
+    float* c; int64_t ldc;
+    float alpha, beta;
+    const float* bias;                 /* [n] or NULL */
+    float* gelu_out;                   /* [m,n] (ldc) or NULL */
+    int32_t k2; const float* a2; int64_t lda2; const float* b2; int64_t ldb2;
+    int32_t batch; int64_t stride_a, stride_b, stride_c;
+} mft_gemm_args;
+int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
+/* 1 if mft_gemm would take the tcgen05 path for these arguments (host-side predicate, no launch). */
+int mft_gemm_uses_tensor_cores(const mft_gemm_args* args);
+
+/* Out-of-place 2-D transpose: out[c,r] (ldo) = in[r,c] (ldi). Replaces ops::transpose's per-element
+ * index loop for the 2-D case (core/ops.cpp:844-865) — used to keep K-major shadows of weights. */
+int mft_transpose2d(const float* in, int64_t ldi, float* out, int64_t ldo, int64_t rows, int64_t cols,
+                    int64_t batch, int64_t stride_in, int64_t stride_out, mft_stream_t stream);
+/* out[b,d2,d1,d3] = in[b,d1,d2,d3]  (ops::permute {0,2,1,3}, core/ops.cpp:886-961; its own inverse). */
+int mft_permute0213(const float* in, float* out, int64_t d0, int64_t d1, int64_t d2, int64_t d3, mft_stream_t stream);
+
+/* ------------------------------------------------------------------ elementwise (HBM streaming)
+ * mft_binary: out = a (op) b with numpy broadcasting of b over a described by (outer, mid, inner):
+ *   a, out are [outer, mid, inner]; b_mode 0: b same shape; 1: b is [inner] (bias); 2: b is [mid, inner]
+ *   (mask [S,S] onto [B*H,S,S]); 3: b is [outer_b, 1, inner] with outer index a_outer / b_div
+ *   (padding mask [B,1,1,S]). op: 0 add, 1 sub, 2 mul, 3 div. (core/ops.cpp:166-484) */
+int mft_binary(int op, const float* a, const float* b, float* out, int64_t outer, int64_t mid, int64_t inner,
+               int b_mode, int64_t b_div, mft_stream_t stream);
+/* out = a*alpha + beta   (ops::mul/add/sub/div with a scalar, core/ops.cpp:380-484; ScaleBackward :970-974) */
+int mft_affine(const float* a, float* out, int64_t n, float alpha, float beta, mft_stream_t stream);
+/* acc += g   (Engine::accumulate_grad, core/autograd_engine.cpp:116-140) */
+int mft_accumulate(float* acc, const float* g, int64_t n, mft_stream_t stream);
+int mft_fill(float* out, int64_t n, float value, mft_stream_t stream);
+/* out[n] = sum over rows of g[rows,n] (ldg) — AddBackward's sum_to_shape for a bias
+ * (core/backward_functions.cpp:36-64). workspace: mft_colsum_workspace_bytes(rows,n). */
+size_t mft_colsum_workspace_bytes(int64_t rows, int64_t n);
+int mft_colsum(const float* g, int64_t ldg, float* out, int64_t rows, int64_t n, void* workspace,
+               size_t workspace_bytes, mft_stream_t stream);
+/* unary ops: kind 0 gelu_tanh fwd, 1 relu, 2 sigmoid, 3 silu, 4 tanh, 5 exp, 6 log, 7 sqrt, 8 abs
+ * (core/ops.cpp:1033-1117). */
+int mft_unary(int kind, const float* x, float* y, int64_t n, mft_stream_t stream);
+/* GELU (tanh form, constants 0.7978845608f / 0.044715f): core/ops.cpp:1055-1079, GeluBackward
+ * core/backward_functions.cpp:155-177. */
+int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t stream);
+int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stream_t stream);
+/* MulBackward for same-shape operands: ga = gy*b, gb = gy*a (core/backward_functions.cpp:74-83). */
+int mft_mul_bwd(const float* a, const float* b, const float* gy, float* ga, float* gb, int64_t n, mft_stream_t stream);
+
+/* ------------------------------------------------------------------ normalisation
+ * LayerNorm over the last dim (rows x dim): y = (x-mu)*rstd*gamma + beta, biased variance, fp32
+ * accumulation. Forward: ops::layer_norm core/ops.cpp:1404-1458. Backward recomputes mu/rstd and
+ * always produces dx, dgamma, dbeta: LayerNormBackward core/backward_functions.cpp:425-481.
+ * The backward needs mft_norm_bwd_workspace_bytes(rows, dim) bytes of scratch for the column
+ * reductions (dgamma/dbeta partial sums); dgamma/dbeta are overwritten, not accumulated. */
+int mft_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, int64_t rows,
+                      int64_t dim, float eps, mft_stream_t stream);
+size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim);
+int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
+                      float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                      size_t workspace_bytes, mft_stream_t stream);
+/* RMSNorm with (1+w) scale, double-precision row statistics: y = x * rsqrt(mean(x^2)+eps) * (1+w)
+ * (ops::rms_norm core/ops.cpp:1489-1537, RMSNormBackward core/backward_functions.cpp:483-523).
+ * plus_one = 0 gives rms_norm_affine (y = x_hat * w). */
+int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t rows, int64_t dim, float eps,
+                    int plus_one, mft_stream_t stream);
+int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,
+                    int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
+                    mft_stream_t stream);
+
+/* ------------------------------------------------------------------ softmax / attention / rope
+ * Softmax over the last dim: core/ops.cpp:1119-1175; backward dx = y*(gy - sum(gy*y)) with the row
+ * dot accumulated in double: SoftmaxBackward core/backward_functions.cpp:297-340. */
+int mft_softmax_fwd(const float* x, float* y, int64_t rows, int64_t dim, mft_stream_t stream);
+int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64_t rows, int64_t dim, mft_stream_t stream);
+/* Causal self-attention forward, GPT-2 semantics (scores*scale, j>i masked with -1e10, softmax, P*V;
+ * no gradient): memory_efficient_attention core/memory_efficient_attention.cpp:40-185.
+ * q/k/v are addressed as  base + b*stride_b + s*stride_s + h*stride_h + d  so the kernel reads the
+ * fused [B,S,3C] qkv buffer directly (replacing the zeros+memcpy split and the two permutes of
+ * graph/gpt2_model.cpp:616-664) and writes ctx as [B,S,H*Hd] (replacing :739-740).
+ * window > 0 additionally masks i-j >= window (Gemma sliding layers, graph/gemma_model.cpp:272-285). */
+int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
+                             int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                             int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                             int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                             float scale, int32_t window, mft_stream_t stream);
+/* Interleaved-pair RoPE on [B,H,S,Hd]: pair (2d,2d+1) rotated by pos*theta^(-2d/Hd)
+ * (ops::apply_rope core/ops.cpp:2151-2225). inverse != 0 applies the transpose rotation
+ * (ApplyRoPEBackward core/backward_functions.cpp:718-763). */
+int mft_rope(const float* x, float* y, int64_t BH, int64_t S, int64_t Hd, float theta, int inverse, mft_stream_t stream);
+/* GQA head repeat [B,KV,S,Hd] -> [B,KV*rep,S,Hd] (head h reads kv head h/rep) and its backward (sum over
+ * the repeats): ops::repeat_kv_heads core/ops.cpp:2072-2149, RepeatKVHeadsBackward backward_functions.cpp:683-716. */
+int mft_repeat_kv_fwd(const float* x, float* y, int64_t B, int64_t KV, int64_t rep, int64_t S, int64_t Hd, mft_stream_t stream);
+int mft_repeat_kv_bwd(const float* gy, float* gx, int64_t B, int64_t KV, int64_t rep, int64_t S, int64_t Hd, mft_stream_t stream);
+
+/* ------------------------------------------------------------------ embedding
+ * GPT-2: x[t,:] = wte[ids[t],:] + wpe[t % S,:]  (graph/gpt2_model.cpp:346-381,500-528).
+ * Gemma (wpe = NULL): x[t,:] = embed[ids[t],:] * scale (graph/gemma_model.cpp:222-259).
+ * An out-of-range id sets *status (device int, may be NULL) to 1; the row is zero-filled. */
+int mft_embedding_fwd(const int32_t* ids, const float* wte, const float* wpe, float* x, int64_t tokens,
+                      int64_t S, int64_t C, int64_t vocab, float scale, int32_t* status, mft_stream_t stream);
+
+/* ------------------------------------------------------------------ shifted LM cross-entropy
+ * Row (b,s), s < S-1, is scored against labels[b,s+1]; rows whose label is ignore_index or outside
+ * [0,V) are skipped; logsumexp with a double sum; mean over the valid rows
+ * (ops::lm_cross_entropy core/lm_loss.cpp:106-210). logits has leading dimension ld (>= V).
+ *   fwd: loss_out[0] = reduced loss ("mean": reduction=0, "sum": 1), valid_out[0] = number of valid
+ *        rows (int32), row_lse[B*S] = max+log(sum) per row (saved for the backward).
+ *   bwd: dlogits[r,v] = (exp(x-lse) - [v==y]) * gout[0] / valid  for valid rows, 0 elsewhere
+ *        (LMCrossEntropyBackward core/lm_loss.cpp:19-104). dlogits has leading dimension ldg.
+ * workspace: mft_lm_ce_workspace_bytes(B*S) for the per-row losses reduced in a fixed order. */
+size_t mft_lm_ce_workspace_bytes(int64_t rows);
+int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* labels, int32_t B, int32_t S, int32_t V,
+                  int32_t ignore_index, int32_t reduction, float* loss_out, int32_t* valid_out, float* row_lse,
+                  void* workspace, size_t workspace_bytes, mft_stream_t stream);
+int mft_lm_ce_bwd(const float* logits, int64_t ld, const int32_t* labels, const float* row_lse,
+                  const int32_t* valid, const float* gout, int32_t B, int32_t S, int32_t V, int32_t ignore_index,
+                  int32_t reduction, float* dlogits, int64_t ldg, mft_stream_t stream);
+
+/* ------------------------------------------------------------------ clip + Adam (multi-tensor)
+ * A tensor list is an array of mft_tensor_slot in DEVICE memory (param/grad/m/v pointers + length).
+ * mft_grad_sumsq: out[0] = sum over all slots of grad^2 (double accumulation, fixed reduction order),
+ *   the quantity under the sqrt of the trainers' clip (gpt2_lora_finetune/main.cpp:491-516,
+ *   optim/gemma_trainer.cpp:84-102). workspace: mft_grad_sumsq_workspace_bytes().
+ * mft_clip_scale: scale_out[0] = (max_norm > 0 && norm > max_norm) ? max_norm/(norm+1e-6) : 1, norm_out[0] = norm,
+ *   with norm = sqrt(sumsq[0]) * pre_scale (pre_scale = 1/world_size after a summed allreduce).
+ * mft_scale_grads: grad *= scale[0] * pre_scale in place (host-visible clip semantics).
+ * mft_adam_step: Adam with L2-coupled weight decay exactly as optim/adam.cpp:25-90:
+ *   g' = g*gscale + wd*p; m = b1*m+(1-b1)g'; v = b2*v+(1-b2)g'^2; p -= lr*(m/bc1)/(sqrt(v/bc2)+eps),
+ *   bc = 1-beta^t with std::pow(float) semantics, t = step_per_slot (each slot carries its own step
+ *   count, advanced by the host only for tensors that have a gradient, adam.cpp:35-43).
+ *   gscale = grad_scale[0] (device scalar, NULL = 1) so the clip factor never visits the host. */
+typedef struct mft_tensor_slot {
+    float* param; float* grad; float* m; float* v;
+    int64_t n;
+    float bias_corr1, bias_corr2;     /* 1-beta1^t, 1-beta2^t for this tensor's step count */
+    int32_t pad0, pad1;
+} mft_tensor_slot;
+size_t mft_grad_sumsq_workspace_bytes(void);
+int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, double* out, void* workspace,
+                   size_t workspace_bytes, mft_stream_t stream);
+int mft_clip_scale(const double* sumsq, float max_norm, float pre_scale, float* scale_out, float* norm_out,
+                   mft_stream_t stream);
+int mft_scale_grads(const mft_tensor_slot* slots, int32_t num_slots, const float* scale, mft_stream_t stream);
+int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, float lr, float beta1, float beta2, float eps,
+                  float weight_decay, const float* grad_scale, mft_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MFT_B200_H_ */

@@ -1,0 +1,248 @@
+// Causal self-attention forward (GPT-2 semantics: core/memory_efficient_attention.cpp:40-185).
+//
+// Flash-style: one CTA = 64 query rows of one (batch, head); 4 warps x 16 rows; K/V streamed in
+// 64-key tiles through shared memory with cp.async double buffering; scores and P*V on the tensor
+// pipe (mma.sync m16n8k8 TF32) with the 3xTF32 split (hi/lo) so results stay at fp32 accuracy
+// (the reference is fp32; attention is <5% of the step's FLOPs so the 3x cost is immaterial).
+// No S x S matrix is ever written to HBM. q/k/v are read with arbitrary (batch, seq, head) strides,
+// so the fused [B,S,3C] qkv projection output is consumed in place and ctx is written as [B,S,C].
+#include "common.cuh"
+
+namespace mft {
+
+constexpr int kAttBQ = 64;   // query rows per CTA
+constexpr int kAttBK = 64;   // keys per tile
+constexpr int kAttPad = 4;   // smem row padding (floats): conflict-free B-fragment reads
+
+__device__ __forceinline__ uint32_t f2tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = f2tf32(x);
+    lo = f2tf32(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
+    uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
+    int bytes = pred ? 16 : 0;   // src-size 0 => zero fill
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(s), "l"(gmem), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+template <int HD>
+__global__ void __launch_bounds__(128)
+causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
+                            float* __restrict__ ctx, int H, int S,
+                            int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
+                            int64_t osb, int64_t oss, int64_t osh, float scale, int window) {
+    constexpr int LD = HD + kAttPad;
+    constexpr int KS = HD / 8;    // k-slabs over the head dim (QK^T)
+    constexpr int NT = HD / 8;    // n-tiles over the head dim (PV)
+    extern __shared__ __align__(16) float smem[];
+    float* sK = smem;                          // [2][kAttBK][LD]
+    float* sV = smem + 2 * kAttBK * LD;        // [2][kAttBK][LD]
+
+    const int qt = gridDim.x - 1 - blockIdx.x; // heavy (late) query tiles first
+    const int bh = blockIdx.y;
+    const int b = bh / H, h = bh % H;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int q0 = qt * kAttBQ;
+    const float* qb = q + b * qsb + h * qsh;
+    const float* kb = k + b * ksb + h * ksh;
+    const float* vb = v + b * ksb + h * ksh;
+
+    // Q fragments (A operand, rows g / g+8 of this warp's 16-row slab), pre-scaled, split hi/lo.
+    uint32_t qhi[KS][4], qlo[KS][4];
+    {
+        const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+#pragma unroll
+        for (int s = 0; s < KS; ++s) {
+            float a0 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t] * scale : 0.f;
+            float a1 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t] * scale : 0.f;
+            float a2 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t + 4] * scale : 0.f;
+            float a3 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t + 4] * scale : 0.f;
+            split_tf32(a0, qhi[s][0], qlo[s][0]); split_tf32(a1, qhi[s][1], qlo[s][1]);
+            split_tf32(a2, qhi[s][2], qlo[s][2]); split_tf32(a3, qhi[s][3], qlo[s][3]);
+        }
+    }
+
+    float o[NT][4];
+#pragma unroll
+    for (int n = 0; n < NT; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+    // key-tile range: causal upper bound, optional sliding-window lower bound
+    int kt_hi = qt;                                    // last tile index (inclusive)
+    int kt_lo = 0;
+    if (window > 0) { int lo = q0 - (window - 1); if (lo > 0) kt_lo = lo / kAttBK; }
+
+    auto load_tile = [&](int kt, int buf) {
+        const int key0 = kt * kAttBK;
+        float* dk = sK + buf * kAttBK * LD;
+        float* dv = sV + buf * kAttBK * LD;
+        constexpr int CH = HD / 4;                    // 16-byte chunks per row
+        for (int c = threadIdx.x; c < kAttBK * CH; c += 128) {
+            int r = c / CH, cc = c % CH;
+            bool ok = (key0 + r) < S;
+            int64_t off = int64_t(ok ? key0 + r : 0) * kss + cc * 4;
+            cp_async16(dk + r * LD + cc * 4, kb + off, ok);
+            cp_async16(dv + r * LD + cc * 4, vb + off, ok);
+        }
+        cp_async_commit();
+    };
+
+    load_tile(kt_lo, 0);
+    for (int kt = kt_lo; kt <= kt_hi; ++kt) {
+        const int buf = (kt - kt_lo) & 1;
+        if (kt + 1 <= kt_hi) { load_tile(kt + 1, buf ^ 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+        __syncthreads();
+        const float* tk = sK + buf * kAttBK * LD;
+        const float* tv = sV + buf * kAttBK * LD;
+        const int key0 = kt * kAttBK;
+
+        // ---- S = (Q*scale) K^T  : 16 x 64 per warp
+        float sc[8][4];
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+#pragma unroll
+            for (int s = 0; s < KS; ++s) {
+                float k0 = tk[(n * 8 + g) * LD + s * 8 + t];
+                float k1 = tk[(n * 8 + g) * LD + s * 8 + t + 4];
+                uint32_t bh0, bl0, bh1, bl1;
+                split_tf32(k0, bh0, bl0); split_tf32(k1, bh1, bl1);
+                mma_tf32(sc[n], qlo[s], bh0, bh1);
+                mma_tf32(sc[n], qhi[s], bl0, bl1);
+                mma_tf32(sc[n], qhi[s], bh0, bh1);
+            }
+        }
+        // ---- masks (causal / window / sequence tail) + online softmax
+        const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+        const bool need_mask = (kt == kt_hi) || (window > 0) || (key0 + kAttBK > S);
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            if (need_mask) {
+                int c0 = key0 + n * 8 + 2 * t, c1 = c0 + 1;
+                bool w00 = c0 <= r0 && c0 < S && (window <= 0 || r0 - c0 < window);
+                bool w01 = c1 <= r0 && c1 < S && (window <= 0 || r0 - c1 < window);
+                bool w10 = c0 <= r1 && c0 < S && (window <= 0 || r1 - c0 < window);
+                bool w11 = c1 <= r1 && c1 < S && (window <= 0 || r1 - c1 < window);
+                if (!w00) sc[n][0] = -INFINITY;
+                if (!w01) sc[n][1] = -INFINITY;
+                if (!w10) sc[n][2] = -INFINITY;
+                if (!w11) sc[n][3] = -INFINITY;
+            }
+            mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
+            mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float nm0 = fmaxf(m0, mx0), nm1 = fmaxf(m1, mx1);
+        const float ref0 = (nm0 == -INFINITY) ? 0.f : nm0, ref1 = (nm1 == -INFINITY) ? 0.f : nm1;
+        const float cor0 = expf(m0 - ref0), cor1 = expf(m1 - ref1);   // exp(-inf) = 0 on the first tile
+        m0 = nm0; m1 = nm1;
+        float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+        for (int n = 0; n < 8; ++n) {
+            sc[n][0] = expf(sc[n][0] - ref0); sc[n][1] = expf(sc[n][1] - ref0);
+            sc[n][2] = expf(sc[n][2] - ref1); sc[n][3] = expf(sc[n][3] - ref1);
+            rs0 += sc[n][0] + sc[n][1];
+            rs1 += sc[n][2] + sc[n][3];
+        }
+        l0 = l0 * cor0 + rs0;   // per-thread partial row sums; quad-reduced at the end
+        l1 = l1 * cor1 + rs1;
+#pragma unroll
+        for (int n = 0; n < NT; ++n) { o[n][0] *= cor0; o[n][1] *= cor0; o[n][2] *= cor1; o[n][3] *= cor1; }
+
+        // ---- O += P V. The C-fragment of S holds columns (2t, 2t+1) where an A-fragment wants (t, t+4):
+        // relabel the contraction index (key 2t <-> slot t, key 2t+1 <-> slot t+4) and read V rows to match.
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {           // 8 key-slabs of 8 keys
+            uint32_t phi[4], plo[4];
+            split_tf32(sc[s][0], phi[0], plo[0]);   // (row g,   key 2t)   -> a0
+            split_tf32(sc[s][2], phi[1], plo[1]);   // (row g+8, key 2t)   -> a1
+            split_tf32(sc[s][1], phi[2], plo[2]);   // (row g,   key 2t+1) -> a2
+            split_tf32(sc[s][3], phi[3], plo[3]);   // (row g+8, key 2t+1) -> a3
+#pragma unroll
+            for (int n = 0; n < NT; ++n) {
+                float v0 = tv[(s * 8 + 2 * t) * LD + n * 8 + g];
+                float v1 = tv[(s * 8 + 2 * t + 1) * LD + n * 8 + g];
+                uint32_t bh0, bl0, bh1, bl1;
+                split_tf32(v0, bh0, bl0); split_tf32(v1, bh1, bl1);
+                mma_tf32(o[n], plo, bh0, bh1);
+                mma_tf32(o[n], phi, bl0, bl1);
+                mma_tf32(o[n], phi, bh0, bh1);
+            }
+        }
+        __syncthreads();   // everyone done with this buffer before it is refilled
+    }
+
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float inv0 = l0 > 0.f ? 1.0f / l0 : 0.f, inv1 = l1 > 0.f ? 1.0f / l1 : 0.f;
+    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+    float* ob = ctx + b * osb + h * osh;
+#pragma unroll
+    for (int n = 0; n < NT; ++n) {
+        if (r0 < S) *reinterpret_cast<float2*>(ob + int64_t(r0) * oss + n * 8 + 2 * t) = make_float2(o[n][0] * inv0, o[n][1] * inv0);
+        if (r1 < S) *reinterpret_cast<float2*>(ob + int64_t(r1) * oss + n * 8 + 2 * t) = make_float2(o[n][2] * inv1, o[n][3] * inv1);
+    }
+}
+
+template <int HD>
+static int launch_attention(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
+                            int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
+                            int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
+    constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(causal_attention_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        attr_set = true;
+    }
+    dim3 grid(unsigned(ceil_div(S, kAttBQ)), unsigned(B * H));
+    causal_attention_fwd_kernel<HD><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
+                                                             osh, scale, window);
+    return 0;
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
+                                        int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                        int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                                        int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                                        float scale, int32_t window, mft_stream_t stream) {
+    if (B == 0 || H == 0 || S == 0) return 0;
+    if (!q || !k || !v || !ctx) return set_error(1, "mft_causal_attention_fwd: null pointer");
+    if (int64_t(B) * H > 65535) return set_error(1, "mft_causal_attention_fwd: B*H too large");
+    if (!(aligned16(k) && aligned16(v)) || (kv_stride_b % 4) || (kv_stride_s % 4) || (kv_stride_h % 4))
+        return set_error(1, "mft_causal_attention_fwd: k/v must be 16-byte aligned with strides %% 4 == 0");
+    if ((reinterpret_cast<uintptr_t>(ctx) & 7u) || (o_stride_b % 2) || (o_stride_s % 2) || (o_stride_h % 2))
+        return set_error(1, "mft_causal_attention_fwd: ctx must be 8-byte aligned with even strides");
+    cudaStream_t st = as_stream(stream);
+#define MFT_ATT(HD_) launch_attention<HD_>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
+                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st)
+    switch (Hd) {
+        case 16: MFT_ATT(16); break;
+        case 32: MFT_ATT(32); break;
+        case 64: MFT_ATT(64); break;
+        case 128: MFT_ATT(128); break;
+        default: return set_error(1, "mft_causal_attention_fwd: head_dim %d not supported (16/32/64/128)", Hd);
+    }
+#undef MFT_ATT
+    MFT_CHECK_LAUNCH("mft_causal_attention_fwd");
+    return 0;
+}

@@ -1,0 +1,111 @@
+// Shared device/host helpers for the mft_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "mft_b200.h"
+
+namespace mft {
+
+// Records a message for mft_last_error() and returns `code`.
+int set_error(int code, const char* fmt, ...);
+
+inline cudaStream_t as_stream(mft_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// Post-launch check used by every entry point.
+#define MFT_CHECK_LAUNCH(name)                                                             \
+    do {                                                                                   \
+        cudaError_t _e = cudaGetLastError();                                               \
+        if (_e != cudaSuccess) return ::mft::set_error(2, "%s: %s", name, cudaGetErrorString(_e)); \
+    } while (0)
+
+#define MFT_CUDA_OK(expr, name)                                                            \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) return ::mft::set_error(2, "%s: %s", name, cudaGetErrorString(_e)); \
+    } while (0)
+
+constexpr int kNumSMs = 148;  // B200
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide reductions (blockDim.x multiple of 32, <= 1024). `smem` must hold 32 elements.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* smem) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    T r = (lane < nw) ? smem[lane] : T(0);
+    r = warp_sum(r);
+    return r;  // valid in every thread
+}
+__device__ __forceinline__ float block_max(float v, float* smem) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    float r = (lane < nw) ? smem[lane] : -INFINITY;
+    r = warp_max(r);
+    return r;
+}
+
+// Streaming 128-bit accesses (data touched once: keep it out of L1).
+__device__ __forceinline__ float4 ld_stream(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream(float4* p, const float4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+__device__ __forceinline__ float gelu_tanh_f(float x) {
+    // reference constants: core/ops.cpp:1055-1059
+    const float k0 = 0.7978845608f, k1 = 0.044715f;
+    float inner = k0 * (x + k1 * x * x * x);
+    return 0.5f * x * (1.0f + tanhf(inner));
+}
+__device__ __forceinline__ float gelu_tanh_grad_f(float x) {
+    // core/backward_functions.cpp:155-177
+    const float k0 = 0.7978845608f, k1 = 0.044715f;
+    float x2 = x * x;
+    float inner = k0 * (x + k1 * x * x2);
+    float t = tanhf(inner);
+    float sech2 = 1.0f - t * t;
+    float dinner = k0 * (1.0f + 3.0f * k1 * x2);
+    return 0.5f * (1.0f + t) + 0.5f * x * sech2 * dinner;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Grid size for grid-stride streaming kernels: enough CTAs to fill the chip a few times over,
+// in multiples of the SM count.
+inline int stream_grid(int64_t work_items, int threads, int per_thread = 1) {
+    int64_t blocks = ceil_div(work_items, int64_t(threads) * per_thread);
+    int64_t cap = int64_t(kNumSMs) * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+}  // namespace mft

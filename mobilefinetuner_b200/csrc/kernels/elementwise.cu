@@ -1,0 +1,270 @@
+// HBM-streaming elementwise / layout kernels: 128-bit vectorised, grid-stride, coalesced.
+// Each is bound by HBM bandwidth; algorithmic bytes per element are stated per kernel.
+#include "common.cuh"
+
+namespace mft {
+
+// ---------------------------------------------------------------- binary with broadcast
+template <int OP>
+__device__ __forceinline__ float bin_apply(float a, float b) {
+    if (OP == 0) return a + b;
+    if (OP == 1) return a - b;
+    if (OP == 2) return a * b;
+    return a / b;
+}
+
+// b_mode 0: same shape (12 B/elem); vectorised when n % 4 == 0 and pointers aligned.
+template <int OP>
+__global__ void binary_same_vec4(const float4* __restrict__ a, const float4* __restrict__ b,
+                                 float4* __restrict__ out, int64_t n4) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        float4 x = ld_stream(a + i), y = ld_stream(b + i), r;
+        r.x = bin_apply<OP>(x.x, y.x); r.y = bin_apply<OP>(x.y, y.y);
+        r.z = bin_apply<OP>(x.z, y.z); r.w = bin_apply<OP>(x.w, y.w);
+        st_stream(out + i, r);
+    }
+}
+
+// General broadcast path (scalar): out[o,m,i] = a[o,m,i] op b[f(o,m,i)].
+template <int OP>
+__global__ void binary_bcast(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out,
+                             int64_t outer, int64_t mid, int64_t inner, int b_mode, int64_t b_div) {
+    const int64_t n = outer * mid * inner;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t i = idx % inner;
+        int64_t om = idx / inner;
+        int64_t m = om % mid, o = om / mid;
+        int64_t bi;
+        if (b_mode == 0) bi = idx;
+        else if (b_mode == 1) bi = i;
+        else if (b_mode == 2) bi = m * inner + i;
+        else bi = (o / b_div) * inner + i;
+        out[idx] = bin_apply<OP>(a[idx], __ldg(b + bi));
+    }
+}
+
+// Bias broadcast, vectorised: rows x inner with inner % 4 == 0.
+template <int OP>
+__global__ void binary_bias_vec4(const float4* __restrict__ a, const float4* __restrict__ b,
+                                 float4* __restrict__ out, int64_t n4, int64_t inner4) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        float4 x = ld_stream(a + i), y = __ldg(b + (i % inner4)), r;
+        r.x = bin_apply<OP>(x.x, y.x); r.y = bin_apply<OP>(x.y, y.y);
+        r.z = bin_apply<OP>(x.z, y.z); r.w = bin_apply<OP>(x.w, y.w);
+        st_stream(out + i, r);
+    }
+}
+
+template <int OP>
+static int launch_binary(const float* a, const float* b, float* out, int64_t outer, int64_t mid, int64_t inner,
+                         int b_mode, int64_t b_div, cudaStream_t st) {
+    const int64_t n = outer * mid * inner;
+    if (n == 0) return 0;
+    const bool al = aligned16(a) && aligned16(b) && aligned16(out);
+    if (b_mode == 0 && (n % 4 == 0) && al) {
+        int64_t n4 = n / 4;
+        binary_same_vec4<OP><<<stream_grid(n4, 256), 256, 0, st>>>(
+            reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b), reinterpret_cast<float4*>(out), n4);
+    } else if (b_mode == 1 && (inner % 4 == 0) && al) {
+        int64_t n4 = n / 4;
+        binary_bias_vec4<OP><<<stream_grid(n4, 256), 256, 0, st>>>(
+            reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b), reinterpret_cast<float4*>(out), n4,
+            inner / 4);
+    } else {
+        binary_bcast<OP><<<stream_grid(n, 256), 256, 0, st>>>(a, b, out, outer, mid, inner, b_mode, b_div < 1 ? 1 : b_div);
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------- affine / accumulate / fill
+__global__ void affine_kernel(const float* __restrict__ a, float* __restrict__ out, int64_t n, float alpha, float beta) {
+    const int64_t n4 = n >> 2;
+    const bool vec = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0;
+    int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
+    if (vec) {
+        const float4* a4 = reinterpret_cast<const float4*>(a);
+        float4* o4 = reinterpret_cast<float4*>(out);
+        for (int64_t i = tid; i < n4; i += stride) {
+            float4 x = ld_stream(a4 + i);
+            x.x = x.x * alpha + beta; x.y = x.y * alpha + beta; x.z = x.z * alpha + beta; x.w = x.w * alpha + beta;
+            st_stream(o4 + i, x);
+        }
+        for (int64_t i = n4 * 4 + tid; i < n; i += stride) out[i] = a[i] * alpha + beta;
+    } else {
+        for (int64_t i = tid; i < n; i += stride) out[i] = a[i] * alpha + beta;
+    }
+}
+
+__global__ void accumulate_kernel(float* __restrict__ acc, const float* __restrict__ g, int64_t n) {
+    const int64_t n4 = n >> 2;
+    const bool vec = ((reinterpret_cast<uintptr_t>(acc) | reinterpret_cast<uintptr_t>(g)) & 15u) == 0;
+    int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
+    if (vec) {
+        float4* a4 = reinterpret_cast<float4*>(acc);
+        const float4* g4 = reinterpret_cast<const float4*>(g);
+        for (int64_t i = tid; i < n4; i += stride) {
+            float4 x = a4[i], y = ld_stream(g4 + i);
+            x.x += y.x; x.y += y.y; x.z += y.z; x.w += y.w;
+            a4[i] = x;
+        }
+        for (int64_t i = n4 * 4 + tid; i < n; i += stride) acc[i] += g[i];
+    } else {
+        for (int64_t i = tid; i < n; i += stride) acc[i] += g[i];
+    }
+}
+
+__global__ void fill_kernel(float* __restrict__ out, int64_t n, float v) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = v;
+}
+
+// ---------------------------------------------------------------- unary / gelu / mul backward
+template <int KIND>
+__device__ __forceinline__ float unary_apply(float x) {
+    if (KIND == 0) return gelu_tanh_f(x);
+    if (KIND == 1) return x > 0.f ? x : 0.f;
+    if (KIND == 2) return 1.0f / (1.0f + expf(-x));
+    if (KIND == 3) return x / (1.0f + expf(-x));
+    if (KIND == 4) return tanhf(x);
+    if (KIND == 5) return expf(x);
+    if (KIND == 6) return logf(x);
+    if (KIND == 7) return sqrtf(x);
+    return fabsf(x);
+}
+template <int KIND>
+__global__ void unary_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n) {
+    const int64_t n4 = n >> 2;
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) == 0;
+    int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
+    if (vec) {
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        float4* y4 = reinterpret_cast<float4*>(y);
+        for (int64_t i = tid; i < n4; i += stride) {
+            float4 v = ld_stream(x4 + i);
+            v.x = unary_apply<KIND>(v.x); v.y = unary_apply<KIND>(v.y);
+            v.z = unary_apply<KIND>(v.z); v.w = unary_apply<KIND>(v.w);
+            st_stream(y4 + i, v);
+        }
+        for (int64_t i = n4 * 4 + tid; i < n; i += stride) y[i] = unary_apply<KIND>(x[i]);
+    } else {
+        for (int64_t i = tid; i < n; i += stride) y[i] = unary_apply<KIND>(x[i]);
+    }
+}
+
+// gx = gy * gelu'(x): reads 8 B, writes 4 B per element.
+__global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gy, float* __restrict__ gx, int64_t n) {
+    const int64_t n4 = n >> 2;
+    const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gy) | reinterpret_cast<uintptr_t>(gx)) & 15u) == 0;
+    int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
+    if (vec) {
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const float4* g4 = reinterpret_cast<const float4*>(gy);
+        float4* o4 = reinterpret_cast<float4*>(gx);
+        for (int64_t i = tid; i < n4; i += stride) {
+            float4 v = ld_stream(x4 + i), g = ld_stream(g4 + i), r;
+            r.x = g.x * gelu_tanh_grad_f(v.x); r.y = g.y * gelu_tanh_grad_f(v.y);
+            r.z = g.z * gelu_tanh_grad_f(v.z); r.w = g.w * gelu_tanh_grad_f(v.w);
+            st_stream(o4 + i, r);
+        }
+        for (int64_t i = n4 * 4 + tid; i < n; i += stride) gx[i] = gy[i] * gelu_tanh_grad_f(x[i]);
+    } else {
+        for (int64_t i = tid; i < n; i += stride) gx[i] = gy[i] * gelu_tanh_grad_f(x[i]);
+    }
+}
+
+__global__ void mul_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ gy,
+                               float* __restrict__ ga, float* __restrict__ gb, int64_t n) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        float g = gy[i], x = a[i], y = b[i];
+        if (ga) ga[i] = g * y;
+        if (gb) gb[i] = g * x;
+    }
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" int mft_binary(int op, const float* a, const float* b, float* out, int64_t outer, int64_t mid,
+                          int64_t inner, int b_mode, int64_t b_div, mft_stream_t stream) {
+    if (!a || !b || !out) return set_error(1, "mft_binary: null pointer");
+    if (op < 0 || op > 3 || b_mode < 0 || b_mode > 3) return set_error(1, "mft_binary: bad op/b_mode");
+    cudaStream_t st = as_stream(stream);
+    switch (op) {
+        case 0: launch_binary<0>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 1: launch_binary<1>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 2: launch_binary<2>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        default: launch_binary<3>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+    }
+    MFT_CHECK_LAUNCH("mft_binary");
+    return 0;
+}
+
+extern "C" int mft_affine(const float* a, float* out, int64_t n, float alpha, float beta, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!a || !out) return set_error(1, "mft_affine: null pointer");
+    affine_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(a, out, n, alpha, beta);
+    MFT_CHECK_LAUNCH("mft_affine");
+    return 0;
+}
+
+extern "C" int mft_accumulate(float* acc, const float* g, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!acc || !g) return set_error(1, "mft_accumulate: null pointer");
+    accumulate_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(acc, g, n);
+    MFT_CHECK_LAUNCH("mft_accumulate");
+    return 0;
+}
+
+extern "C" int mft_fill(float* out, int64_t n, float value, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!out) return set_error(1, "mft_fill: null pointer");
+    if (value == 0.0f) {
+        MFT_CUDA_OK(cudaMemsetAsync(out, 0, size_t(n) * 4, as_stream(stream)), "mft_fill");
+        return 0;
+    }
+    fill_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(out, n, value);
+    MFT_CHECK_LAUNCH("mft_fill");
+    return 0;
+}
+
+extern "C" int mft_unary(int kind, const float* x, float* y, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!x || !y) return set_error(1, "mft_unary: null pointer");
+    cudaStream_t st = as_stream(stream);
+    int g = stream_grid(n, 256, 4);
+    switch (kind) {
+        case 0: unary_kernel<0><<<g, 256, 0, st>>>(x, y, n); break;
+        case 1: unary_kernel<1><<<g, 256, 0, st>>>(x, y, n); break;
+        case 2: unary_kernel<2><<<g, 256, 0, st>>>(x, y, n); break;
+        case 3: unary_kernel<3><<<g, 256, 0, st>>>(x, y, n); break;
+        case 4: unary_kernel<4><<<g, 256, 0, st>>>(x, y, n); break;
+        case 5: unary_kernel<5><<<g, 256, 0, st>>>(x, y, n); break;
+        case 6: unary_kernel<6><<<g, 256, 0, st>>>(x, y, n); break;
+        case 7: unary_kernel<7><<<g, 256, 0, st>>>(x, y, n); break;
+        case 8: unary_kernel<8><<<g, 256, 0, st>>>(x, y, n); break;
+        default: return set_error(1, "mft_unary: unknown kind %d", kind);
+    }
+    MFT_CHECK_LAUNCH("mft_unary");
+    return 0;
+}
+
+extern "C" int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t stream) {
+    return mft_unary(0, x, y, n, stream);
+}
+
+extern "C" int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!x || !gy || !gx) return set_error(1, "mft_gelu_bwd: null pointer");
+    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n);
+    MFT_CHECK_LAUNCH("mft_gelu_bwd");
+    return 0;
+}
+
+extern "C" int mft_mul_bwd(const float* a, const float* b, const float* gy, float* ga, float* gb, int64_t n,
+                           mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!a || !b || !gy) return set_error(1, "mft_mul_bwd: null pointer");
+    mul_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(a, b, gy, ga, gb, n);
+    MFT_CHECK_LAUNCH("mft_mul_bwd");
+    return 0;
+}

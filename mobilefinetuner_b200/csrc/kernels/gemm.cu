@@ -1,0 +1,77 @@
+// mft_gemm dispatch + library-level entry points (version, errors, device check).
+#include <cstdarg>
+#include <cstring>
+#include "common.cuh"
+#include "gemm_internal.cuh"
+
+namespace mft {
+
+static thread_local char g_err[512] = "";
+static bool g_use_tc = true;
+
+int set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+static int to_params(const mft_gemm_args* a, GemmParams& p) {
+    if (!a) return set_error(1, "mft_gemm: null args");
+    if (a->m < 0 || a->n < 0 || a->k < 0 || a->k2 < 0) return set_error(1, "mft_gemm: negative dimension");
+    p.m = a->m; p.n = a->n; p.k = a->k;
+    p.a = a->a; p.lda = a->lda; p.trans_a = a->trans_a;
+    p.b = a->b; p.ldb = a->ldb; p.trans_b = a->trans_b;
+    p.c = a->c; p.ldc = a->ldc; p.alpha = a->alpha; p.beta = a->beta;
+    p.bias = a->bias; p.gelu_out = a->gelu_out;
+    p.k2 = a->k2; p.a2 = a->a2; p.lda2 = a->lda2; p.b2 = a->b2; p.ldb2 = a->ldb2;
+    p.batch = a->batch < 1 ? 1 : a->batch;
+    p.stride_a = a->stride_a; p.stride_b = a->stride_b; p.stride_c = a->stride_c;
+    if (p.m == 0 || p.n == 0) return 0;
+    if (!p.c || (p.k > 0 && (!p.a || !p.b))) return set_error(1, "mft_gemm: null operand");
+    if (p.k2 > 0 && (!p.a2 || !p.b2)) return set_error(1, "mft_gemm: null second-segment operand");
+    const int64_t min_lda = p.trans_a ? p.m : p.k, min_ldb = p.trans_b ? p.k : p.n;
+    if (p.lda < min_lda || p.ldb < min_ldb || p.ldc < p.n) return set_error(1, "mft_gemm: leading dimension too small");
+    if (p.k2 > 0 && (p.lda2 < p.k2 || p.ldb2 < p.k2)) return set_error(1, "mft_gemm: second-segment ld too small");
+    return 0;
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" int mft_version(void) { return 100; }
+extern "C" const char* mft_last_error(void) { return g_err; }
+
+extern "C" int mft_device_check(void) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error(4, "mft_device_check: %s", cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, dev);
+    if (e != cudaSuccess) return set_error(4, "mft_device_check: %s", cudaGetErrorString(e));
+    if (prop.major != 10) return set_error(4, "mft_device_check: device is sm_%d%d, this library is sm_100a only", prop.major, prop.minor);
+    return 0;
+}
+
+extern "C" int mft_use_tensor_cores(int enable) {
+    int prev = g_use_tc ? 1 : 0;
+    g_use_tc = enable != 0;
+    return prev;
+}
+
+extern "C" int mft_gemm_uses_tensor_cores(const mft_gemm_args* args) {
+    GemmParams p;
+    if (!args || to_params(args, p) != 0) return 0;
+    return (g_use_tc && gemm_tc_eligible(p)) ? 1 : 0;
+}
+
+extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
+    GemmParams p;
+    int rc = to_params(args, p);
+    if (rc) return rc;
+    if (p.m == 0 || p.n == 0) return 0;
+    if (g_use_tc && gemm_tc_eligible(p)) return launch_gemm_tc(p, as_stream(stream));
+    return launch_gemm_simt(p, as_stream(stream));
+}

@@ -1,0 +1,23 @@
+// Internal GEMM parameter block shared by the SIMT and tcgen05 paths (mirrors mft_gemm_args).
+#pragma once
+#include "common.cuh"
+
+namespace mft {
+
+struct GemmParams {
+    int m, n, k;
+    const float* a; int64_t lda; int trans_a;
+    const float* b; int64_t ldb; int trans_b;
+    float* c; int64_t ldc;
+    float alpha, beta;
+    const float* bias;
+    float* gelu_out;
+    int k2; const float* a2; int64_t lda2; const float* b2; int64_t ldb2;
+    int batch; int64_t stride_a, stride_b, stride_c;
+};
+
+int launch_gemm_simt(const GemmParams& p, cudaStream_t st);
+bool gemm_tc_eligible(const GemmParams& p);
+int launch_gemm_tc(const GemmParams& p, cudaStream_t st);
+
+}  // namespace mft

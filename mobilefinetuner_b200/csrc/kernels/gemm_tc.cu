@@ -1,0 +1,392 @@
+// tcgen05 TF32 GEMM for sm_100a:  C = alpha*(A*B^T [+ A2*B2^T]) (+bias) (+beta*C) [, gelu aux]
+//   A [m,k] and B [n,k] both K-major fp32 in HBM.
+// Persistent, warp-specialised CTA (one per SM):
+//   warp 0    : TMA producer  (cp.async.bulk.tensor 3-D boxes, 128B swizzle, TFLOAT32 rounding in the TMA)
+//   warp 1    : TMEM allocator + single-thread tcgen05.mma issuer (kind::tf32, M=128, N=BN, K=8 per instr)
+//   warps 2-5 : epilogue (tcgen05.ld 32x32b -> registers -> alpha/bias/beta/GELU -> st.global.v4)
+// Pipelines: NS-deep smem ring (full/empty mbarriers) between TMA and MMA; double-buffered TMEM accumulator
+// (tmem_full/tmem_empty) between MMA and epilogue so tile i's epilogue overlaps tile i+1's main loop.
+// The optional second K-segment (A2 [m,k2], B2 [n,k2]) feeds extra k-blocks into the same accumulator:
+// this is how LoRA's rank-r update s*(xA)*B is fused with the base x*W product (nn/lora_linear.cpp:47-108).
+#include <cuda.h>
+#include <mutex>
+#include <unordered_map>
+#include "common.cuh"
+#include "gemm_internal.cuh"
+
+namespace mft {
+
+constexpr int TBM = 128;          // tile rows  (UMMA M)
+constexpr int TBK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
+constexpr int TUK = 8;            // UMMA K for tf32 (32 bytes)
+constexpr int kTcThreads = 192;
+constexpr int kSmemBudget = 200 * 1024;
+
+template <int BN> struct TcCfg {
+    static constexpr int stage_bytes = (TBM + BN) * TBK * 4;
+    static constexpr int stages = (kSmemBudget / stage_bytes) > 8 ? 8 : (kSmemBudget / stage_bytes);
+    static constexpr int tmem_cols = 2 * BN;             // two accumulator buffers
+    static constexpr int smem_bytes = stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra.uni WAIT_DONE;\n\t"
+        "bra.uni WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t}"
+        :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart (SBO), version 1.
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= uint64_t((smem_addr >> 4) & 0x3FFF);          // start address
+    d |= uint64_t(0) << 16;                            // LBO (unused for swizzled K-major)
+    d |= uint64_t((1024 >> 4) & 0x3FFF) << 32;         // SBO
+    d |= uint64_t(1) << 46;                            // descriptor version (sm_100)
+    d |= uint64_t(2) << 61;                            // SWIZZLE_128B
+    return d;
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+struct TcArgs {
+    int m, n, batch;
+    int kb1, kb2;              // k-blocks of segment 1 / segment 2
+    float* c; int64_t ldc, stride_c;
+    float* gelu_out;
+    const float* bias;
+    float alpha, beta;
+    int tiles_m, tiles_n;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2, TcArgs p) {
+    using Cfg = TcCfg<BN>;
+    constexpr int NS = Cfg::stages;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + NS * Cfg::stage_bytes);
+    uint64_t* full = bars;                 // [NS]
+    uint64_t* empty = bars + NS;           // [NS]
+    uint64_t* tmem_full = bars + 2 * NS;   // [2]
+    uint64_t* tmem_empty = bars + 2 * NS + 2;  // [2]
+    uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * NS + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_tiles = p.tiles_m * p.tiles_n * p.batch;
+    const int num_kb = p.kb1 + p.kb2;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(tmem_base_slot)), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int mt = tile % p.tiles_m;
+                const int nt = (tile / p.tiles_m) % p.tiles_n;
+                const int bz = tile / (p.tiles_m * p.tiles_n);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    uint8_t* sa = tiles + stage * Cfg::stage_bytes;
+                    uint8_t* sb = sa + TBM * TBK * 4;
+                    mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes));
+                    if (kb < p.kb1) {
+                        tma_load_3d(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
+                        tma_load_3d(sb, &map_b, &full[stage], kb * TBK, nt * BN, bz);
+                    } else {
+                        tma_load_3d(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
+                        tma_load_3d(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, nt * BN, 0);
+                    }
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (one thread) =====================
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=B=tf32, both K-major, N=BN, M=128
+            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t(TBM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tmem_empty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + uint32_t(as * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(tiles + stage * Cfg::stage_bytes);
+                    const uint32_t sb = sa + TBM * TBK * 4;
+                    const uint64_t adesc = make_kmajor_sw128_desc(sa);
+                    const uint64_t bdesc = make_kmajor_sw128_desc(sb);
+#pragma unroll
+                    for (int k = 0; k < TBK / TUK; ++k) {
+                        // advance 32 bytes (one UMMA K) inside the 128B swizzle span: +2 in 16-byte units
+                        tc_mma_tf32(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    tc_commit(&empty[stage]);            // frees the smem slot when these MMAs retire
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&tmem_full[as]);               // accumulator ready for the epilogue
+            }
+        }
+    } else {
+        // ===================== epilogue warps (TMEM -> regs -> HBM) =====================
+        const int lg = warp & 3;                          // TMEM lane group this warp may touch
+        const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15u) == 0) &&
+                            ((p.stride_c & 3) == 0) &&
+                            (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            const int mt = tile % p.tiles_m;
+            const int nt = (tile / p.tiles_m) % p.tiles_n;
+            const int bz = tile / (p.tiles_m * p.tiles_n);
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(&tmem_full[as], aphase);
+            tc_fence_after();
+            const int row = mt * TBM + lg * 32 + lane;
+            const int n0 = nt * BN;
+            float* crow = p.c + int64_t(bz) * p.stride_c + int64_t(row) * p.ldc;
+            float* grow = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c + int64_t(row) * p.ldc : nullptr;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                if (n0 + c0 >= p.n) break;               // warp-uniform
+                float v[32];
+                tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
+                if (row < p.m) {
+                    const int ncol = n0 + c0;
+                    if (vec_ok && ncol + 32 <= p.n) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 o = make_float4(v[j] * p.alpha, v[j + 1] * p.alpha, v[j + 2] * p.alpha, v[j + 3] * p.alpha);
+                            if (p.bias) {
+                                float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + ncol + j));
+                                o.x += bb.x; o.y += bb.y; o.z += bb.z; o.w += bb.w;
+                            }
+                            if (p.beta != 0.f) {
+                                float4 old = *reinterpret_cast<const float4*>(crow + ncol + j);
+                                o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
+                            }
+                            *reinterpret_cast<float4*>(crow + ncol + j) = o;
+                            if (grow) {
+                                float4 ge = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                                *reinterpret_cast<float4*>(grow + ncol + j) = ge;
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (ncol + j < p.n) {
+                                float o = v[j] * p.alpha;
+                                if (p.bias) o += __ldg(p.bias + ncol + j);
+                                if (p.beta != 0.f) o += p.beta * crow[ncol + j];
+                                crow[ncol + j] = o;
+                                if (grow) grow[ncol + j] = gelu_tanh_f(o);
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[as]);  // 4 arrivals (one per epilogue warp) free the buffer
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+    }
+}
+
+}  // namespace mft
+
+// ---------------------------------------------------------------- host side
+namespace mft {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+struct MapKey {
+    const void* ptr; uint64_t inner, rows, batch, ld, stride; uint32_t box_rows;
+    bool operator==(const MapKey& o) const {
+        return ptr == o.ptr && inner == o.inner && rows == o.rows && batch == o.batch && ld == o.ld &&
+               stride == o.stride && box_rows == o.box_rows;
+    }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        uint64_t h = reinterpret_cast<uint64_t>(k.ptr);
+        auto mix = [&h](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
+        mix(k.inner); mix(k.rows); mix(k.batch); mix(k.ld); mix(k.stride); mix(k.box_rows);
+        return size_t(h);
+    }
+};
+
+// K-major operand [batch][rows][inner] (ld elements between rows): box = {32, box_rows, 1}, 128B swizzle.
+// Encoding costs ~1 us on the host; the step re-uses the same buffers so descriptors are cached.
+static bool make_operand_map(CUtensorMap* out, const float* ptr, uint64_t inner, uint64_t rows, uint64_t batch,
+                             uint64_t ld, uint64_t stride, uint32_t box_rows) {
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    static std::mutex mu;
+    MapKey key{ptr, inner, rows, batch, ld, stride, box_rows};
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) { *out = it->second; return true; }
+    }
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return false;
+    alignas(64) CUtensorMap m;
+    cuuint64_t dims[3] = {inner, rows, batch};
+    if (batch == 1 || stride == 0) stride = rows * ld;
+    cuuint64_t strides[2] = {ld * 4, stride * 4};
+    cuuint32_t box[3] = {uint32_t(TBK), box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 3, const_cast<float*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (cache.size() > 4096) cache.clear();
+        cache.emplace(key, m);
+    }
+    *out = m;
+    return true;
+}
+
+bool gemm_tc_eligible(const GemmParams& p) {
+    if (p.trans_a != 0 || p.trans_b == 0) return false;                 // both operands must be K-major
+    if (p.m < 1 || p.n < 1 || p.k < 1) return false;
+    if ((p.lda & 3) || (p.ldb & 3) || !aligned16(p.a) || !aligned16(p.b)) return false;
+    if (p.batch > 1 && ((p.stride_a & 3) || (p.stride_b & 3))) return false;
+    if (p.k2 > 0 && ((p.lda2 & 3) || (p.ldb2 & 3) || !aligned16(p.a2) || !aligned16(p.b2) || p.batch != 1)) return false;
+    // tiny problems are launch-bound either way; keep them on the SIMT kernel (exact fp32)
+    if (int64_t(p.m) * p.n * p.batch < 64 * 64 || p.k < 32) return false;
+    return true;
+}
+
+template <int BN>
+static int launch_tc(const GemmParams& p, cudaStream_t st) {
+    using Cfg = TcCfg<BN>;
+    CUtensorMap ma, mb, ma2, mb2;
+    if (!make_operand_map(&ma, p.a, p.k, p.m, p.batch, p.lda, p.stride_a, TBM) ||
+        !make_operand_map(&mb, p.b, p.k, p.n, p.batch, p.ldb, p.stride_b, BN))
+        return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed");
+    if (p.k2 > 0) {
+        if (!make_operand_map(&ma2, p.a2, p.k2, p.m, 1, p.lda2, 0, TBM) ||
+            !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, BN))
+            return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (segment 2)");
+    } else { ma2 = ma; mb2 = mb; }
+    TcArgs a;
+    a.m = p.m; a.n = p.n; a.batch = p.batch;
+    a.kb1 = int(ceil_div(p.k, TBK)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, TBK)) : 0;
+    a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;
+    a.alpha = p.alpha; a.beta = p.beta;
+    a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
+        if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
+        attr_set = true;
+    }
+    int64_t tiles = int64_t(a.tiles_m) * a.tiles_n * a.batch;
+    int grid = int(tiles < kNumSMs ? tiles : kNumSMs);
+    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::smem_bytes, st>>>(ma, mb, ma2, mb2, a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): %s", cudaGetErrorString(e));
+    return 0;
+}
+
+int launch_gemm_tc(const GemmParams& p, cudaStream_t st) {
+    // Tile width: widest tile that still gives every SM work; narrow N uses narrow tiles.
+    const int64_t tm = ceil_div(p.m, TBM) * p.batch;
+    if (p.n <= 64 || tm * ceil_div(p.n, 128) < kNumSMs / 2) return launch_tc<64>(p, st);
+    if (p.n <= 128 || tm * ceil_div(p.n, 256) < kNumSMs) return launch_tc<128>(p, st);
+    return launch_tc<256>(p, st);
+}
+
+}  // namespace mft

@@ -1,0 +1,231 @@
+// Layout / gather kernels: transpose, head permute, column sums, embedding gather, RoPE, GQA repeat.
+#include "common.cuh"
+
+namespace mft {
+
+// 32x32 shared-memory tile transpose (coalesced on both sides, padded against bank conflicts).
+__global__ void transpose2d_kernel(const float* __restrict__ in, int64_t ldi, float* __restrict__ out, int64_t ldo,
+                                   int64_t rows, int64_t cols, int64_t stride_in, int64_t stride_out) {
+    __shared__ float tile[32][33];
+    in += blockIdx.z * stride_in;
+    out += blockIdx.z * stride_out;
+    const int64_t c0 = int64_t(blockIdx.x) * 32, r0 = int64_t(blockIdx.y) * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int64_t r = r0 + j, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[j][threadIdx.x] = in[r * ldi + c];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int64_t c = c0 + j, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) out[c * ldo + r] = tile[threadIdx.x][j];
+    }
+}
+
+// out[b, j, i, :] = in[b, i, j, :]  — rows of d3 floats are moved whole (coalesced both sides).
+__global__ void permute0213_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t d0, int64_t d1,
+                                   int64_t d2, int64_t d3) {
+    const int64_t n = d0 * d1 * d2 * d3;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t d = idx % d3;
+        int64_t t = idx / d3;
+        int64_t i = t % d1;  // output layout [d0, d2, d1, d3]
+        t /= d1;
+        int64_t j = t % d2;
+        int64_t b = t / d2;
+        out[idx] = in[((b * d1 + i) * d2 + j) * d3 + d];
+    }
+}
+
+// Column sums, stage 1: each CTA owns a 32-column strip and a slab of rows, 32x8 threads.
+constexpr int kColsumRowsPerCta = 256;
+__global__ void colsum_partial_kernel(const float* __restrict__ g, int64_t ldg, float* __restrict__ partial,
+                                      int64_t rows, int64_t n) {
+    __shared__ float red[8][33];
+    const int64_t c = int64_t(blockIdx.x) * 32 + threadIdx.x;
+    const int64_t r0 = int64_t(blockIdx.y) * kColsumRowsPerCta;
+    int64_t r1 = r0 + kColsumRowsPerCta;
+    if (r1 > rows) r1 = rows;
+    float acc = 0.f;
+    if (c < n)
+        for (int64_t r = r0 + threadIdx.y; r < r1; r += 8) acc += g[r * ldg + c];
+    red[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < n) {
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += red[j][threadIdx.x];
+        partial[int64_t(blockIdx.y) * n + c] = s;
+    }
+}
+// stage 2: fixed-order sum of the slabs (deterministic).
+__global__ void colsum_final_kernel(const float* __restrict__ partial, float* __restrict__ out, int64_t slabs, int64_t n) {
+    int64_t c = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    if (c >= n) return;
+    float s = 0.f;
+    for (int64_t j = 0; j < slabs; ++j) s += partial[j * n + c];
+    out[c] = s;
+}
+
+// Embedding gather: one warp per token row, float4 when C % 4 == 0.
+__global__ void embedding_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wte,
+                                 const float* __restrict__ wpe, float* __restrict__ x, int64_t tokens, int64_t S,
+                                 int64_t C, int64_t vocab, float scale, int32_t* status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps_per_grid = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t t = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; t < tokens; t += warps_per_grid) {
+        int32_t id = ids[t];
+        float* dst = x + t * C;
+        if (id < 0 || id >= vocab) {
+            if (status && lane == 0) *status = 1;
+            for (int64_t i = lane; i < C; i += 32) dst[i] = 0.f;
+            continue;
+        }
+        const float* src = wte + int64_t(id) * C;
+        const float* pos = wpe ? wpe + (t % S) * C : nullptr;
+        if ((C & 3) == 0) {
+            const float4* s4 = reinterpret_cast<const float4*>(src);
+            const float4* p4 = reinterpret_cast<const float4*>(pos);
+            float4* d4 = reinterpret_cast<float4*>(dst);
+            for (int64_t i = lane; i < (C >> 2); i += 32) {
+                float4 v = __ldg(s4 + i);
+                if (pos) { float4 p = __ldg(p4 + i); v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w; }
+                else { v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale; }
+                d4[i] = v;
+            }
+        } else {
+            for (int64_t i = lane; i < C; i += 32) dst[i] = pos ? src[i] + pos[i] : src[i] * scale;
+        }
+    }
+}
+
+// RoPE on interleaved pairs. One thread per pair; float2 accesses.
+__global__ void rope_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t BH, int64_t S, int64_t Hd,
+                            float theta, int inverse) {
+    const int64_t half = Hd >> 1;
+    const int64_t n = BH * S * half;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t d = idx % half;
+        int64_t pos = (idx / half) % S;
+        // reference: freq = 1/pow(theta, 2d/Hd); angle = pos*freq (float) — core/ops.cpp:2183-2187
+        float freq = 1.0f / powf(theta, 2.0f * float(d) / float(Hd));
+        float angle = float(pos) * freq;
+        float c = cosf(angle), s = sinf(angle);
+        if (inverse) s = -s;
+        float2 v = reinterpret_cast<const float2*>(x)[idx];
+        float2 r;
+        r.x = v.x * c - v.y * s;
+        r.y = v.x * s + v.y * c;
+        reinterpret_cast<float2*>(y)[idx] = r;
+    }
+}
+
+__global__ void repeat_kv_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t B, int64_t KV,
+                                     int64_t rep, int64_t SHd) {
+    const int64_t n = B * KV * rep * SHd;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t e = idx % SHd;
+        int64_t h = (idx / SHd) % (KV * rep);
+        int64_t b = idx / (SHd * KV * rep);
+        y[idx] = x[(b * KV + h / rep) * SHd + e];
+    }
+}
+__global__ void repeat_kv_bwd_kernel(const float* __restrict__ gy, float* __restrict__ gx, int64_t B, int64_t KV,
+                                     int64_t rep, int64_t SHd) {
+    const int64_t n = B * KV * SHd;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t e = idx % SHd;
+        int64_t kv = (idx / SHd) % KV;
+        int64_t b = idx / (SHd * KV);
+        float s = 0.f;
+        for (int64_t r = 0; r < rep; ++r) s += gy[((b * KV + kv) * rep + r) * SHd + e];
+        gx[idx] = s;
+    }
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" int mft_transpose2d(const float* in, int64_t ldi, float* out, int64_t ldo, int64_t rows, int64_t cols,
+                               int64_t batch, int64_t stride_in, int64_t stride_out, mft_stream_t stream) {
+    if (rows == 0 || cols == 0 || batch == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_transpose2d: null pointer");
+    if (batch > 65535) return set_error(1, "mft_transpose2d: batch %lld too large", (long long)batch);
+    dim3 grid(unsigned(ceil_div(cols, 32)), unsigned(ceil_div(rows, 32)), unsigned(batch));
+    if (grid.y > 65535) return set_error(1, "mft_transpose2d: too many rows");
+    transpose2d_kernel<<<grid, dim3(32, 8), 0, as_stream(stream)>>>(in, ldi, out, ldo, rows, cols, stride_in, stride_out);
+    MFT_CHECK_LAUNCH("mft_transpose2d");
+    return 0;
+}
+
+extern "C" int mft_permute0213(const float* in, float* out, int64_t d0, int64_t d1, int64_t d2, int64_t d3,
+                               mft_stream_t stream) {
+    int64_t n = d0 * d1 * d2 * d3;
+    if (n == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_permute0213: null pointer");
+    permute0213_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(in, out, d0, d1, d2, d3);
+    MFT_CHECK_LAUNCH("mft_permute0213");
+    return 0;
+}
+
+extern "C" size_t mft_colsum_workspace_bytes(int64_t rows, int64_t n) {
+    return size_t(ceil_div(rows, kColsumRowsPerCta)) * size_t(n) * sizeof(float);
+}
+
+extern "C" int mft_colsum(const float* g, int64_t ldg, float* out, int64_t rows, int64_t n, void* workspace,
+                          size_t workspace_bytes, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!g || !out) return set_error(1, "mft_colsum: null pointer");
+    if (rows == 0) return mft_fill(out, n, 0.f, stream);
+    const int64_t slabs = ceil_div(rows, kColsumRowsPerCta);
+    if (workspace_bytes < mft_colsum_workspace_bytes(rows, n) || !workspace)
+        return set_error(1, "mft_colsum: workspace too small (%zu < %zu)", workspace_bytes, mft_colsum_workspace_bytes(rows, n));
+    if (slabs > 65535) return set_error(1, "mft_colsum: too many rows");
+    float* partial = static_cast<float*>(workspace);
+    colsum_partial_kernel<<<dim3(unsigned(ceil_div(n, 32)), unsigned(slabs)), dim3(32, 8), 0, as_stream(stream)>>>(g, ldg, partial, rows, n);
+    colsum_final_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, as_stream(stream)>>>(partial, out, slabs, n);
+    MFT_CHECK_LAUNCH("mft_colsum");
+    return 0;
+}
+
+extern "C" int mft_embedding_fwd(const int32_t* ids, const float* wte, const float* wpe, float* x, int64_t tokens,
+                                 int64_t S, int64_t C, int64_t vocab, float scale, int32_t* status, mft_stream_t stream) {
+    if (tokens == 0 || C == 0) return 0;
+    if (!ids || !wte || !x) return set_error(1, "mft_embedding_fwd: null pointer");
+    if ((C & 3) == 0 && !(aligned16(wte) && aligned16(x) && (!wpe || aligned16(wpe))))
+        return set_error(1, "mft_embedding_fwd: tables must be 16-byte aligned");
+    int blocks = stream_grid(tokens * 32, 256);
+    embedding_kernel<<<blocks, 256, 0, as_stream(stream)>>>(ids, wte, wpe, x, tokens, S, C, vocab, scale, status);
+    MFT_CHECK_LAUNCH("mft_embedding_fwd");
+    return 0;
+}
+
+extern "C" int mft_rope(const float* x, float* y, int64_t BH, int64_t S, int64_t Hd, float theta, int inverse,
+                        mft_stream_t stream) {
+    if (BH * S * Hd == 0) return 0;
+    if (!x || !y) return set_error(1, "mft_rope: null pointer");
+    if (Hd & 1) return set_error(1, "mft_rope: head_dim must be even");
+    rope_kernel<<<stream_grid(BH * S * (Hd / 2), 256), 256, 0, as_stream(stream)>>>(x, y, BH, S, Hd, theta, inverse);
+    MFT_CHECK_LAUNCH("mft_rope");
+    return 0;
+}
+
+extern "C" int mft_repeat_kv_fwd(const float* x, float* y, int64_t B, int64_t KV, int64_t rep, int64_t S, int64_t Hd,
+                                 mft_stream_t stream) {
+    int64_t n = B * KV * rep * S * Hd;
+    if (n == 0) return 0;
+    if (!x || !y) return set_error(1, "mft_repeat_kv_fwd: null pointer");
+    repeat_kv_fwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(x, y, B, KV, rep, S * Hd);
+    MFT_CHECK_LAUNCH("mft_repeat_kv_fwd");
+    return 0;
+}
+
+extern "C" int mft_repeat_kv_bwd(const float* gy, float* gx, int64_t B, int64_t KV, int64_t rep, int64_t S, int64_t Hd,
+                                 mft_stream_t stream) {
+    int64_t n = B * KV * S * Hd;
+    if (n == 0) return 0;
+    if (!gy || !gx) return set_error(1, "mft_repeat_kv_bwd: null pointer");
+    repeat_kv_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(gy, gx, B, KV, rep, S * Hd);
+    MFT_CHECK_LAUNCH("mft_repeat_kv_bwd");
+    return 0;
+}

@@ -1,0 +1,182 @@
+// Shifted language-model cross-entropy over a 50k..262k vocabulary (core/lm_loss.cpp:19-210).
+// HBM-bound: forward reads each valid logits row once from HBM (the second pass hits L2), backward
+// reads it once more and writes dlogits once. Rows whose label is ignored (and every last position)
+// are never read. Per-row losses are reduced in a fixed order (deterministic).
+#include "common.cuh"
+
+namespace mft {
+
+constexpr int kCeThreads = 512;
+
+__device__ __forceinline__ int ce_label(const int32_t* labels, int64_t row, int S, int V, int ignore_index) {
+    // row = b*S + s is scored against labels[b, s+1]; returns -1 when the row is skipped.
+    int s = int(row % S);
+    if (s + 1 >= S) return -1;
+    int y = labels[row + 1];
+    if (y == ignore_index || y < 0 || y >= V) return -1;
+    return y;
+}
+
+__global__ void __launch_bounds__(kCeThreads)
+lm_ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels, int64_t rows, int S,
+                 int V, int ignore_index, float* __restrict__ row_lse, double* __restrict__ row_nll) {
+    __shared__ float sred[32];
+    __shared__ double dred[32];
+    const bool vec = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15u) == 0);
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int y = ce_label(labels, row, S, V, ignore_index);
+        if (y < 0) {
+            if (threadIdx.x == 0) { row_nll[row] = 0.0; row_lse[row] = 0.f; }
+            continue;
+        }
+        const float* x = logits + row * ld;
+        float m = -INFINITY;
+        if (vec) {
+            const float4* x4 = reinterpret_cast<const float4*>(x);
+            const int v4 = V >> 2;
+            for (int i = threadIdx.x; i < v4; i += kCeThreads) {
+                float4 a = x4[i];
+                m = fmaxf(m, fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)));
+            }
+            for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) m = fmaxf(m, x[i]);
+        } else {
+            for (int i = threadIdx.x; i < V; i += kCeThreads) m = fmaxf(m, x[i]);
+        }
+        m = block_max(m, sred);
+        float s = 0.f;
+        if (vec) {
+            const float4* x4 = reinterpret_cast<const float4*>(x);
+            const int v4 = V >> 2;
+            for (int i = threadIdx.x; i < v4; i += kCeThreads) {
+                float4 a = x4[i];
+                s += expf(a.x - m) + expf(a.y - m) + expf(a.z - m) + expf(a.w - m);
+            }
+            for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) s += expf(x[i] - m);
+        } else {
+            for (int i = threadIdx.x; i < V; i += kCeThreads) s += expf(x[i] - m);
+        }
+        const double denom = block_sum<double>(double(s), dred);
+        if (threadIdx.x == 0) {
+            double lse = double(m) + log(denom);
+            row_lse[row] = float(lse);
+            row_nll[row] = lse - double(x[y]);
+        }
+    }
+}
+
+// Single-CTA fixed-order reduction of the per-row losses and of the valid-row count.
+__global__ void __launch_bounds__(1024)
+lm_ce_reduce_kernel(const double* __restrict__ row_nll, const int32_t* __restrict__ labels, int64_t rows, int S, int V,
+                    int ignore_index, int reduction, float* __restrict__ loss_out, int32_t* __restrict__ valid_out) {
+    __shared__ double dred[32];
+    __shared__ double cred[32];
+    double s = 0.0, c = 0.0;
+    for (int64_t r = threadIdx.x; r < rows; r += blockDim.x) {
+        if (ce_label(labels, r, S, V, ignore_index) >= 0) { s += row_nll[r]; c += 1.0; }
+    }
+    s = block_sum<double>(s, dred);
+    c = block_sum<double>(c, cred);
+    if (threadIdx.x == 0) {
+        int64_t cnt = int64_t(c + 0.5);
+        float out;
+        if (reduction == 1) out = float(s);
+        else out = cnt > 0 ? float(s / double(cnt)) : 0.0f;
+        loss_out[0] = out;
+        valid_out[0] = int32_t(cnt);
+    }
+}
+
+__global__ void __launch_bounds__(kCeThreads)
+lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels,
+                 const float* __restrict__ row_lse, const int32_t* __restrict__ valid, const float* __restrict__ gout,
+                 int64_t rows, int S, int V, int ignore_index, int reduction, float* __restrict__ dlogits, int64_t ldg) {
+    const bool vec = ((ld & 3) == 0) && ((ldg & 3) == 0) &&
+                     (((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15u) == 0);
+    const int cnt = valid[0];
+    const float g = gout ? gout[0] : 1.0f;
+    const float scale = (reduction == 1) ? g : (cnt > 0 ? g / float(cnt) : 0.0f);
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int y = ce_label(labels, row, S, V, ignore_index);
+        float* d = dlogits + row * ldg;
+        if (y < 0) {   // skipped rows get an all-zero gradient (core/lm_loss.cpp:45-52)
+            if (vec) {
+                float4* d4 = reinterpret_cast<float4*>(d);
+                const int v4 = V >> 2;
+                for (int i = threadIdx.x; i < v4; i += kCeThreads) st_stream(d4 + i, make_float4(0.f, 0.f, 0.f, 0.f));
+                for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) d[i] = 0.f;
+            } else {
+                for (int i = threadIdx.x; i < V; i += kCeThreads) d[i] = 0.f;
+            }
+            continue;
+        }
+        const float* x = logits + row * ld;
+        const float lse = row_lse[row];
+        if (vec) {
+            const float4* x4 = reinterpret_cast<const float4*>(x);
+            float4* d4 = reinterpret_cast<float4*>(d);
+            const int v4 = V >> 2;
+            for (int i = threadIdx.x; i < v4; i += kCeThreads) {
+                float4 a = ld_stream(x4 + i), r;
+                r.x = expf(a.x - lse) * scale; r.y = expf(a.y - lse) * scale;
+                r.z = expf(a.z - lse) * scale; r.w = expf(a.w - lse) * scale;
+                const int base = i << 2;
+                if (y >= base && y < base + 4) {
+                    if (y == base) r.x -= scale; else if (y == base + 1) r.y -= scale;
+                    else if (y == base + 2) r.z -= scale; else r.w -= scale;
+                }
+                st_stream(d4 + i, r);
+            }
+            for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) {
+                float r = expf(x[i] - lse) * scale;
+                if (i == y) r -= scale;
+                d[i] = r;
+            }
+        } else {
+            for (int i = threadIdx.x; i < V; i += kCeThreads) {
+                float r = expf(x[i] - lse) * scale;
+                if (i == y) r -= scale;
+                d[i] = r;
+            }
+        }
+    }
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" size_t mft_lm_ce_workspace_bytes(int64_t rows) { return size_t(rows) * sizeof(double); }
+
+extern "C" int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* labels, int32_t B, int32_t S, int32_t V,
+                             int32_t ignore_index, int32_t reduction, float* loss_out, int32_t* valid_out,
+                             float* row_lse, void* workspace, size_t workspace_bytes, mft_stream_t stream) {
+    if (!logits || !labels || !loss_out || !valid_out || !row_lse) return set_error(1, "mft_lm_ce_fwd: null pointer");
+    if (ld < V) return set_error(1, "mft_lm_ce_fwd: ld (%lld) < V (%d)", (long long)ld, V);
+    if (reduction != 0 && reduction != 1) return set_error(1, "mft_lm_ce_fwd: reduction must be 0 (mean) or 1 (sum)");
+    const int64_t rows = int64_t(B) * S;
+    if (!workspace || workspace_bytes < mft_lm_ce_workspace_bytes(rows))
+        return set_error(1, "mft_lm_ce_fwd: workspace too small");
+    cudaStream_t st = as_stream(stream);
+    double* row_nll = static_cast<double*>(workspace);
+    if (rows > 0 && V > 0) {
+        int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
+        lm_ce_fwd_kernel<<<grid, kCeThreads, 0, st>>>(logits, ld, labels, rows, S, V, ignore_index, row_lse, row_nll);
+    }
+    lm_ce_reduce_kernel<<<1, 1024, 0, st>>>(row_nll, labels, rows, S, V, ignore_index, reduction, loss_out, valid_out);
+    MFT_CHECK_LAUNCH("mft_lm_ce_fwd");
+    return 0;
+}
+
+extern "C" int mft_lm_ce_bwd(const float* logits, int64_t ld, const int32_t* labels, const float* row_lse,
+                             const int32_t* valid, const float* gout, int32_t B, int32_t S, int32_t V,
+                             int32_t ignore_index, int32_t reduction, float* dlogits, int64_t ldg, mft_stream_t stream) {
+    if (!logits || !labels || !row_lse || !valid || !dlogits) return set_error(1, "mft_lm_ce_bwd: null pointer");
+    if (ld < V || ldg < V) return set_error(1, "mft_lm_ce_bwd: leading dimension < V");
+    const int64_t rows = int64_t(B) * S;
+    if (rows == 0 || V == 0) return 0;
+    int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
+    lm_ce_bwd_kernel<<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V,
+                                                                ignore_index, reduction, dlogits, ldg);
+    MFT_CHECK_LAUNCH("mft_lm_ce_bwd");
+    return 0;
+}

@@ -1,0 +1,464 @@
+// LayerNorm / RMSNorm(1+w) / softmax: one warp per row, row cached in registers (one HBM read),
+// warp-shuffle reductions, 128-bit accesses. Weight-gradient column sums go through per-CTA partials
+// in caller-provided scratch and a fixed-order second stage (deterministic, no atomics).
+#include "common.cuh"
+
+namespace mft {
+
+constexpr int kNormWarps = 8;               // warps (rows in flight) per CTA
+constexpr int kNormMaxCtas = kNumSMs * 2;   // persistent-style grid for the backward kernels
+
+// ---------------------------------------------------------------- LayerNorm forward
+// NV = float4 per lane (dim <= 128*NV). Algorithmic bytes: 8*rows*dim.
+template <int NV>
+__global__ void __launch_bounds__(kNormWarps * 32)
+layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                     float* __restrict__ y, int64_t rows, int dim, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int dim4 = dim >> 2;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float4* xr = reinterpret_cast<const float4*>(x + r * dim);
+        float4 v[NV];
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            v[j] = (c < dim4) ? ld_stream(xr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            s += v[j].x + v[j].y + v[j].z + v[j].w;
+        }
+        const float mean = warp_sum(s) / float(dim);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            if (c < dim4) {
+                float a = v[j].x - mean, b = v[j].y - mean, cc = v[j].z - mean, d = v[j].w - mean;
+                q += a * a + b * b + cc * cc + d * d;
+            }
+        }
+        const float rstd = 1.0f / sqrtf(warp_sum(q) / float(dim) + eps);
+        float4* yr = reinterpret_cast<float4*>(y + r * dim);
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            if (c < dim4) {
+                float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + c);
+                float4 b = __ldg(reinterpret_cast<const float4*>(beta) + c);
+                float4 o;
+                o.x = (v[j].x - mean) * rstd * g.x + b.x;
+                o.y = (v[j].y - mean) * rstd * g.y + b.y;
+                o.z = (v[j].z - mean) * rstd * g.z + b.z;
+                o.w = (v[j].w - mean) * rstd * g.w + b.w;
+                st_stream(yr + c, o);
+            }
+        }
+    }
+}
+
+// Generic fallback (any dim / alignment): one warp per row, three passes through L1/L2.
+__global__ void layernorm_fwd_generic(const float* __restrict__ x, const float* __restrict__ gamma,
+                                      const float* __restrict__ beta, float* __restrict__ y, int64_t rows, int dim, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float* xr = x + r * dim;
+        float s = 0.f;
+        for (int i = lane; i < dim; i += 32) s += xr[i];
+        const float mean = warp_sum(s) / float(dim);
+        float q = 0.f;
+        for (int i = lane; i < dim; i += 32) { float d = xr[i] - mean; q += d * d; }
+        const float rstd = 1.0f / sqrtf(warp_sum(q) / float(dim) + eps);
+        for (int i = lane; i < dim; i += 32) y[r * dim + i] = (xr[i] - mean) * rstd * gamma[i] + beta[i];
+    }
+}
+
+// ---------------------------------------------------------------- LayerNorm backward
+// dx per row; per-CTA partial dgamma/dbeta -> partial[cta][2][dim]. Algorithmic bytes: 12*rows*dim.
+template <int NV>
+__global__ void __launch_bounds__(kNormWarps * 32)
+layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ gy,
+                     float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps) {
+    extern __shared__ float smem[];  // [kNormWarps][2][dim]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int dim4 = dim >> 2;
+    const int64_t warps = int64_t(gridDim.x) * kNormWarps;
+    float4 dg[NV], db[NV], gam[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        dg[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        db[j] = dg[j];
+        int c = lane + 32 * j;
+        gam[j] = (c < dim4) ? __ldg(reinterpret_cast<const float4*>(gamma) + c) : dg[j];
+    }
+    for (int64_t r = int64_t(blockIdx.x) * kNormWarps + warp; r < rows; r += warps) {
+        const float4* xr = reinterpret_cast<const float4*>(x + r * dim);
+        const float4* gr = reinterpret_cast<const float4*>(gy + r * dim);
+        float4 v[NV], g[NV];
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            v[j] = (c < dim4) ? ld_stream(xr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            g[j] = (c < dim4) ? ld_stream(gr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            s += v[j].x + v[j].y + v[j].z + v[j].w;
+        }
+        const float mean = warp_sum(s) / float(dim);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            if (c < dim4) {
+                float a = v[j].x - mean, b = v[j].y - mean, cc = v[j].z - mean, d = v[j].w - mean;
+                q += a * a + b * b + cc * cc + d * d;
+            }
+        }
+        const float rstd = 1.0f / sqrtf(warp_sum(q) / float(dim) + eps);
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {   // v becomes x_hat, g stays gy
+            v[j].x = (v[j].x - mean) * rstd; v[j].y = (v[j].y - mean) * rstd;
+            v[j].z = (v[j].z - mean) * rstd; v[j].w = (v[j].w - mean) * rstd;
+            int c = lane + 32 * j;
+            if (c < dim4) {
+                float a = g[j].x * gam[j].x, b = g[j].y * gam[j].y, cc = g[j].z * gam[j].z, d = g[j].w * gam[j].w;
+                s1 += a + b + cc + d;
+                s2 += a * v[j].x + b * v[j].y + cc * v[j].z + d * v[j].w;
+                dg[j].x += g[j].x * v[j].x; dg[j].y += g[j].y * v[j].y; dg[j].z += g[j].z * v[j].z; dg[j].w += g[j].w * v[j].w;
+                db[j].x += g[j].x; db[j].y += g[j].y; db[j].z += g[j].z; db[j].w += g[j].w;
+            }
+        }
+        s1 = warp_sum(s1);
+        s2 = warp_sum(s2);
+        const float k = rstd / float(dim), D = float(dim);
+        float4* or_ = reinterpret_cast<float4*>(gx + r * dim);
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            int c = lane + 32 * j;
+            if (c < dim4) {
+                float4 o;
+                o.x = k * (D * (g[j].x * gam[j].x) - s1 - v[j].x * s2);
+                o.y = k * (D * (g[j].y * gam[j].y) - s1 - v[j].y * s2);
+                o.z = k * (D * (g[j].z * gam[j].z) - s1 - v[j].z * s2);
+                o.w = k * (D * (g[j].w * gam[j].w) - s1 - v[j].w * s2);
+                st_stream(or_ + c, o);
+            }
+        }
+    }
+    // CTA reduction of the per-warp column partials, then one row of `partial` per CTA.
+    float4* sg = reinterpret_cast<float4*>(smem) + size_t(warp) * 2 * dim4;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        int c = lane + 32 * j;
+        if (c < dim4) { sg[c] = dg[j]; sg[dim4 + c] = db[j]; }
+    }
+    __syncthreads();
+    float* out = partial + size_t(blockIdx.x) * 2 * dim;
+    for (int i = threadIdx.x; i < 2 * dim; i += blockDim.x) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kNormWarps; ++w) s += smem[size_t(w) * 2 * dim + i];
+        out[i] = s;
+    }
+}
+
+__global__ void layernorm_bwd_generic(const float* __restrict__ x, const float* __restrict__ gamma,
+                                      const float* __restrict__ gy, float* __restrict__ gx, int64_t rows, int dim, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float* xr = x + r * dim;
+        const float* gr = gy + r * dim;
+        float s = 0.f;
+        for (int i = lane; i < dim; i += 32) s += xr[i];
+        const float mean = warp_sum(s) / float(dim);
+        float q = 0.f;
+        for (int i = lane; i < dim; i += 32) { float d = xr[i] - mean; q += d * d; }
+        const float rstd = 1.0f / sqrtf(warp_sum(q) / float(dim) + eps);
+        float s1 = 0.f, s2 = 0.f;
+        for (int i = lane; i < dim; i += 32) {
+            float gh = gr[i] * gamma[i], xh = (xr[i] - mean) * rstd;
+            s1 += gh; s2 += gh * xh;
+        }
+        s1 = warp_sum(s1); s2 = warp_sum(s2);
+        for (int i = lane; i < dim; i += 32) {
+            float gh = gr[i] * gamma[i], xh = (xr[i] - mean) * rstd;
+            gx[r * dim + i] = (rstd / float(dim)) * (float(dim) * gh - s1 - xh * s2);
+        }
+    }
+}
+// generic weight-grad partials: CTA b handles rows [b*chunk, (b+1)*chunk), thread per column.
+__global__ void layernorm_wgrad_generic(const float* __restrict__ x, const float* __restrict__ gy,
+                                        float* __restrict__ partial, int64_t rows, int dim, float eps, int64_t chunk) {
+    extern __shared__ float stats[];  // [chunk][2] mean, rstd
+    const int64_t r0 = int64_t(blockIdx.x) * chunk;
+    int64_t r1 = r0 + chunk; if (r1 > rows) r1 = rows;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int64_t r = r0 + warp; r < r1; r += nw) {
+        const float* xr = x + r * dim;
+        float s = 0.f;
+        for (int i = lane; i < dim; i += 32) s += xr[i];
+        float mean = warp_sum(s) / float(dim);
+        float q = 0.f;
+        for (int i = lane; i < dim; i += 32) { float d = xr[i] - mean; q += d * d; }
+        float rstd = 1.0f / sqrtf(warp_sum(q) / float(dim) + eps);
+        if (lane == 0) { stats[(r - r0) * 2] = mean; stats[(r - r0) * 2 + 1] = rstd; }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < dim; c += blockDim.x) {
+        float a = 0.f, b = 0.f;
+        for (int64_t r = r0; r < r1; ++r) {
+            float g = gy[r * dim + c];
+            a += g * (x[r * dim + c] - stats[(r - r0) * 2]) * stats[(r - r0) * 2 + 1];
+            b += g;
+        }
+        partial[size_t(blockIdx.x) * 2 * dim + c] = a;
+        partial[size_t(blockIdx.x) * 2 * dim + dim + c] = b;
+    }
+}
+
+// Second stage shared by LayerNorm (two outputs) and RMSNorm (one): fixed-order sum over CTAs.
+__global__ void norm_wgrad_final(const float* __restrict__ partial, float* __restrict__ out0, float* __restrict__ out1,
+                                 int parts, int dim, int per_part) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= dim) return;
+    float a = 0.f, b = 0.f;
+    for (int p = 0; p < parts; ++p) {
+        a += partial[size_t(p) * per_part * dim + c];
+        if (out1) b += partial[size_t(p) * per_part * dim + dim + c];
+    }
+    out0[c] = a;
+    if (out1) out1[c] = b;
+}
+
+}  // namespace mft
+
+namespace mft {
+
+// ---------------------------------------------------------------- RMSNorm (1+w), double statistics
+// One warp per row, generic over dim (row re-read hits L1); Gemma dims are 640 (hidden) and 256 (q/k norm).
+__global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, float* __restrict__ y,
+                                   int64_t rows, int dim, float eps, int plus_one) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float* xr = x + r * dim;
+        double sq = 0.0;
+        for (int i = lane; i < dim; i += 32) { double v = xr[i]; sq += v * v; }
+        sq = warp_sum(sq);
+        const float rms = float(sqrt(sq / double(dim) + double(eps)));
+        for (int i = lane; i < dim; i += 32) {
+            float sc = plus_one ? 1.0f + w[i] : w[i];
+            y[r * dim + i] = (xr[i] / rms) * sc;
+        }
+    }
+}
+
+// dx per row (double math as the reference) + per-CTA partial dw -> partial[cta][dim].
+__global__ void __launch_bounds__(kNormWarps * 32)
+rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ gy,
+                   float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps, int plus_one) {
+    extern __shared__ float smem[];  // [kNormWarps][dim]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* my = smem + size_t(warp) * dim;
+    for (int i = lane; i < dim; i += 32) my[i] = 0.f;
+    const int64_t warps = int64_t(gridDim.x) * kNormWarps;
+    for (int64_t r = int64_t(blockIdx.x) * kNormWarps + warp; r < rows; r += warps) {
+        const float* xr = x + r * dim;
+        const float* gr = gy + r * dim;
+        double sq = 0.0, dot = 0.0;
+        for (int i = lane; i < dim; i += 32) {
+            double v = xr[i];
+            double we = plus_one ? 1.0 + double(w[i]) : double(w[i]);
+            sq += v * v;
+            dot += double(gr[i]) * we * v;
+        }
+        sq = warp_sum(sq);
+        dot = warp_sum(dot);
+        const double inv = 1.0 / sqrt(sq / double(dim) + double(eps));
+        const double coeff = inv * inv * inv / double(dim);
+        for (int i = lane; i < dim; i += 32) {
+            double we = plus_one ? 1.0 + double(w[i]) : double(w[i]);
+            double g = gr[i], v = xr[i];
+            gx[r * dim + i] = float(g * we * inv - v * coeff * dot);
+            my[i] += float(g * v * inv);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) {
+        float s = 0.f;
+#pragma unroll
+        for (int q = 0; q < kNormWarps; ++q) s += smem[size_t(q) * dim + i];
+        partial[size_t(blockIdx.x) * dim + i] = s;
+    }
+}
+
+// ---------------------------------------------------------------- softmax over the last dim
+__global__ void softmax_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t rows, int dim) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float* xr = x + r * dim;
+        float m = -INFINITY;
+        for (int i = lane; i < dim; i += 32) m = fmaxf(m, xr[i]);
+        m = warp_max(m);
+        float s = 0.f;
+        for (int i = lane; i < dim; i += 32) s += expf(xr[i] - m);
+        s = warp_sum(s);
+        for (int i = lane; i < dim; i += 32) y[r * dim + i] = expf(xr[i] - m) / s;
+    }
+}
+__global__ void softmax_bwd_kernel(const float* __restrict__ y, const float* __restrict__ gy, float* __restrict__ gx,
+                                   int64_t rows, int dim) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+    for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
+        const float* yr = y + r * dim;
+        const float* gr = gy + r * dim;
+        double dot = 0.0;
+        for (int i = lane; i < dim; i += 32) dot += double(gr[i]) * double(yr[i]);
+        const float d = float(warp_sum(dot));
+        for (int i = lane; i < dim; i += 32) gx[r * dim + i] = yr[i] * (gr[i] - d);
+    }
+}
+
+static int norm_bwd_ctas(int64_t rows) {
+    int64_t c = ceil_div(rows, kNormWarps);
+    if (c > kNormMaxCtas) c = kNormMaxCtas;
+    if (c < 1) c = 1;
+    return int(c);
+}
+
+template <int NV>
+static int launch_ln_fwd(const float* x, const float* g, const float* b, float* y, int64_t rows, int dim, float eps, cudaStream_t st) {
+    int blocks = int(ceil_div(rows, kNormWarps));
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    layernorm_fwd_kernel<NV><<<blocks, kNormWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps);
+    return 0;
+}
+template <int NV>
+static int launch_ln_bwd(const float* x, const float* g, const float* gy, float* gx, float* partial, int64_t rows,
+                         int dim, float eps, int ctas, cudaStream_t st) {
+    size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(layernorm_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    layernorm_bwd_kernel<NV><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps);
+    return 0;
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+extern "C" int mft_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, int64_t rows,
+                                 int64_t dim, float eps, mft_stream_t stream) {
+    if (rows == 0 || dim == 0) return 0;
+    if (!x || !gamma || !beta || !y) return set_error(1, "mft_layernorm_fwd: null pointer");
+    cudaStream_t st = as_stream(stream);
+    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta);
+    if (vec) {
+        int nv = int(ceil_div(dim, 128));
+        if (nv <= 1) launch_ln_fwd<1>(x, gamma, beta, y, rows, int(dim), eps, st);
+        else if (nv <= 2) launch_ln_fwd<2>(x, gamma, beta, y, rows, int(dim), eps, st);
+        else if (nv <= 4) launch_ln_fwd<4>(x, gamma, beta, y, rows, int(dim), eps, st);
+        else if (nv <= 6) launch_ln_fwd<6>(x, gamma, beta, y, rows, int(dim), eps, st);
+        else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st);
+        else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st);
+    } else {
+        layernorm_fwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, beta, y, rows, int(dim), eps);
+    }
+    MFT_CHECK_LAUNCH("mft_layernorm_fwd");
+    return 0;
+}
+
+extern "C" size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim) {
+    // room for either path: vectorised (ctas x 2 x dim) or generic (chunks of 64 rows x 2 x dim)
+    int64_t parts = norm_bwd_ctas(rows);
+    int64_t chunks = ceil_div(rows, 64);
+    if (chunks > parts) parts = chunks;
+    return size_t(parts) * 2 * size_t(dim) * sizeof(float);
+}
+
+extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
+                                 float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                                 size_t workspace_bytes, mft_stream_t stream) {
+    if (dim == 0) return 0;
+    if (!x || !gamma || !gy || !gx || !dgamma || !dbeta) return set_error(1, "mft_layernorm_bwd: null pointer");
+    if (rows == 0) { mft_fill(dgamma, dim, 0.f, stream); return mft_fill(dbeta, dim, 0.f, stream); }
+    if (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim))
+        return set_error(1, "mft_layernorm_bwd: workspace too small (%zu < %zu)", workspace_bytes,
+                         mft_norm_bwd_workspace_bytes(rows, dim));
+    cudaStream_t st = as_stream(stream);
+    float* partial = static_cast<float*>(workspace);
+    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(gy) && aligned16(gx) && aligned16(gamma);
+    int parts;
+    if (vec) {
+        parts = norm_bwd_ctas(rows);
+        int nv = int(ceil_div(dim, 128));
+        if (nv <= 1) launch_ln_bwd<1>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        else if (nv <= 2) launch_ln_bwd<2>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        else if (nv <= 4) launch_ln_bwd<4>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        else if (nv <= 6) launch_ln_bwd<6>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+    } else {
+        layernorm_bwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, gy, gx, rows, int(dim), eps);
+        parts = int(ceil_div(rows, 64));
+        layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
+    }
+    norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dgamma, dbeta, parts, int(dim), 2);
+    MFT_CHECK_LAUNCH("mft_layernorm_bwd");
+    return 0;
+}
+
+extern "C" int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t rows, int64_t dim, float eps,
+                               int plus_one, mft_stream_t stream) {
+    if (rows == 0 || dim == 0) return 0;
+    if (!x || !w || !y) return set_error(1, "mft_rmsnorm_fwd: null pointer");
+    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one);
+    MFT_CHECK_LAUNCH("mft_rmsnorm_fwd");
+    return 0;
+}
+
+extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,
+                               int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
+                               mft_stream_t stream) {
+    if (dim == 0) return 0;
+    if (!x || !w || !gy || !gx || !dw) return set_error(1, "mft_rmsnorm_bwd: null pointer");
+    if (rows == 0) return mft_fill(dw, dim, 0.f, stream);
+    if (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim))
+        return set_error(1, "mft_rmsnorm_bwd: workspace too small");
+    if (size_t(kNormWarps) * dim * sizeof(float) > 200 * 1024) return set_error(1, "mft_rmsnorm_bwd: dim %lld too large", (long long)dim);
+    cudaStream_t st = as_stream(stream);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(rmsnorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    int parts = norm_bwd_ctas(rows);
+    float* partial = static_cast<float*>(workspace);
+    rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
+        x, w, gy, gx, partial, rows, int(dim), eps, plus_one);
+    norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
+    MFT_CHECK_LAUNCH("mft_rmsnorm_bwd");
+    return 0;
+}
+
+extern "C" int mft_softmax_fwd(const float* x, float* y, int64_t rows, int64_t dim, mft_stream_t stream) {
+    if (rows == 0 || dim == 0) return 0;
+    if (!x || !y) return set_error(1, "mft_softmax_fwd: null pointer");
+    softmax_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, y, rows, int(dim));
+    MFT_CHECK_LAUNCH("mft_softmax_fwd");
+    return 0;
+}
+
+extern "C" int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64_t rows, int64_t dim, mft_stream_t stream) {
+    if (rows == 0 || dim == 0) return 0;
+    if (!y || !gy || !gx) return set_error(1, "mft_softmax_bwd: null pointer");
+    softmax_bwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(y, gy, gx, rows, int(dim));
+    MFT_CHECK_LAUNCH("mft_softmax_bwd");
+    return 0;
+}
