@@ -186,8 +186,9 @@ using namespace mft;
 
 extern "C" int mft_binary(int op, const float* a, const float* b, float* out, int64_t outer, int64_t mid,
                           int64_t inner, int b_mode, int64_t b_div, mft_stream_t stream) {
-    if (!a || !b || !out) return set_error(1, "mft_binary: null pointer");
     if (op < 0 || op > 3 || b_mode < 0 || b_mode > 3) return set_error(1, "mft_binary: bad op/b_mode");
+    if (outer * mid * inner == 0) return 0;
+    if (!a || !b || !out) return set_error(1, "mft_binary: null pointer");
     cudaStream_t st = as_stream(stream);
     switch (op) {
         case 0: launch_binary<0>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;

@@ -1,0 +1,196 @@
+"""GPU parity tests: every CUDA entry point of include/mft_b200.h, called through the C ABI (ctypes),
+against the oracle (numpy restatement pinned to the reference) and against tensors produced by the
+reference itself (tests/golden/ops). Tolerances (relative to max|ref|):
+  * fp32 elementwise / norm / softmax / CE / Adam / SIMT GEMM / attention (3xTF32): 1e-5
+  * tcgen05 TF32 GEMM (tf32 inputs rounded in the TMA, fp32 accumulate):           2e-3   
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import mft_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+from conftest import FP32_TOL, TF32_TOL, dev, rel, ws  # noqa: E402
+
+
+# ----------------------------------------------------------------------------- elementwise
+def test_binary_and_bias_golden(capi, golden_ops):
+    L = golden_ops
+    x, b = dev(L("bias_x")), dev(L("bias_b"))
+    out = torch.empty_like(x)
+    rows, n = x.numel() // b.numel(), b.numel()
+    capi.call("mft_binary", 0, x, b, out, 1, rows, n, 1, 1, None)
+    assert rel(out, L("bias_y")) == 0
+    gy = dev(L("bias_gy"))
+    gb = torch.empty(n, device="cuda")
+    w = ws(capi.lib.mft_colsum_workspace_bytes(rows, n))
+    capi.call("mft_colsum", gy, n, gb, rows, n, w, w.numel(), None)
+    assert rel(gb, L("bias_gb")) < FP32_TOL
+    a, bb = dev(L("mul_a")), dev(L("mul_b"))
+    capi.call("mft_binary", 2, a, bb, out, 1, 1, a.numel(), 0, 1, None)
+    assert rel(out, L("mul_y")) == 0
+    ga, gb2 = torch.empty_like(a), torch.empty_like(a)
+    capi.call("mft_mul_bwd", a, bb, dev(L("mul_gy")), ga, gb2, a.numel(), None)
+    assert rel(ga, L("mul_ga")) == 0 and rel(gb2, L("mul_gb")) == 0
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 1024, 4099, 1 << 20])
+def test_elementwise_sizes(capi, n):
+    rng = np.random.default_rng(n)
+    a, b = rng.standard_normal(n).astype(np.float32), rng.standard_normal(n).astype(np.float32) + 3
+    da, db = dev(a), dev(b)
+    out = torch.empty_like(da)
+    for op, f in enumerate([np.add, np.subtract, np.multiply, np.divide]):
+        capi.call("mft_binary", op, da, db, out, 1, 1, n, 0, 1, None)
+        assert rel(out, f(a, b)) < 1e-6
+    capi.call("mft_affine", da, out, n, 0.5, -2.0, None)
+    assert rel(out, a * np.float32(0.5) - 2) < 1e-6
+    acc = da.clone()
+    capi.call("mft_accumulate", acc, db, n, None)
+    assert rel(acc, a + b) == 0
+    capi.call("mft_fill", out, n, 1.25, None)
+    assert rel(out, np.full(n, 1.25, np.float32)) == 0
+    capi.call("mft_gelu_fwd", da, out, n, None)
+    assert rel(out, O.gelu_fwd(a)) < FP32_TOL
+    capi.call("mft_gelu_bwd", da, db, out, n, None)
+    assert rel(out, O.gelu_bwd(a, b)) < FP32_TOL
+
+
+def test_broadcast_modes(capi):
+    rng = np.random.default_rng(0)
+    a = rng.standard_normal((6, 5, 7)).astype(np.float32)     # [B*H, S, S]-like
+    mask = rng.standard_normal((5, 7)).astype(np.float32)
+    out = torch.empty(6, 5, 7, device="cuda")
+    capi.call("mft_binary", 0, dev(a), dev(mask), out, 6, 5, 7, 2, 1, None)
+    assert rel(out, a + mask) == 0
+    pad = rng.standard_normal((2, 1, 7)).astype(np.float32)   # [B,1,1,S] with H=3
+    capi.call("mft_binary", 0, dev(a), dev(pad), out, 6, 5, 7, 3, 3, None)
+    assert rel(out, a + np.repeat(pad, 3, axis=0)) == 0
+
+
+def test_gelu_golden(capi, golden_ops):
+    L = golden_ops
+    x = dev(L("gelu_x"))
+    y = torch.empty_like(x)
+    capi.call("mft_gelu_fwd", x, y, x.numel(), None)
+    assert rel(y, L("gelu_y")) < FP32_TOL
+    capi.call("mft_gelu_bwd", x, dev(L("gelu_gy")), y, x.numel(), None)
+    assert rel(y, L("gelu_gx")) < FP32_TOL
+
+
+# ----------------------------------------------------------------------------- layout
+def test_transpose_permute_golden(capi, golden_ops):
+    L = golden_ops
+    x = dev(L("perm_x"))
+    y = torch.empty(L("perm_y").shape, device="cuda")
+    capi.call("mft_permute0213", x, y, *L("perm_x").shape, None)
+    assert rel(y, L("perm_y")) == 0
+    x2 = dev(L("tr_x"))
+    b, h, r, c = L("tr_x").shape
+    y2 = torch.empty(b, h, c, r, device="cuda")
+    capi.call("mft_transpose2d", x2, c, y2, r, r, c, b * h, r * c, r * c, None)
+    assert rel(y2, L("tr_y")) == 0
+    big = torch.randn(300, 517, device="cuda")
+    out = torch.empty(517, 300, device="cuda")
+    capi.call("mft_transpose2d", big, 517, out, 300, 300, 517, 1, 0, 0, None)
+    assert torch.equal(out, big.t().contiguous())
+
+
+def test_embedding_rope_repeat(capi, golden_ops):
+    L = golden_ops
+    rng = np.random.default_rng(1)
+    V, C_, S, B = 97, 24, 6, 3
+    wte, wpe = rng.standard_normal((V, C_)).astype(np.float32), rng.standard_normal((16, C_)).astype(np.float32)
+    ids = rng.integers(0, V, (B, S)).astype(np.int32)
+    x = torch.empty(B, S, C_, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    capi.call("mft_embedding_fwd", dev(ids, torch.int32), dev(wte), dev(wpe), x, B * S, S, C_, V, 1.0, status, None)
+    assert rel(x, O.embedding_gpt2(ids, wte, wpe)) == 0 and status.item() == 0
+    capi.call("mft_embedding_fwd", dev(ids, torch.int32), dev(wte), None, x, B * S, S, C_, V, 4.0, status, None)
+    assert rel(x, wte[ids] * np.float32(4.0)) == 0
+    bad = ids.copy(); bad[0, 0] = V
+    capi.call("mft_embedding_fwd", dev(bad, torch.int32), dev(wte), None, x, B * S, S, C_, V, 1.0, status, None)
+    assert status.item() == 1
+    xr = dev(L("rope_x"))
+    yr = torch.empty_like(xr)
+    b, h, s, hd = L("rope_x").shape
+    capi.call("mft_rope", xr, yr, b * h, s, hd, 10000.0, 0, None)
+    assert rel(yr, L("rope_y")) < FP32_TOL
+    capi.call("mft_rope", dev(L("rope_gy")), yr, b * h, s, hd, 10000.0, 1, None)
+    assert rel(yr, L("rope_gx")) < FP32_TOL
+    xk = dev(L("repkv_x"))
+    b, kv, s, hd = L("repkv_x").shape
+    yk = torch.empty(L("repkv_y").shape, device="cuda")
+    capi.call("mft_repeat_kv_fwd", xk, yk, b, kv, 3, s, hd, None)
+    assert rel(yk, L("repkv_y")) == 0
+    gk = torch.empty_like(xk)
+    capi.call("mft_repeat_kv_bwd", dev(L("repkv_gy")), gk, b, kv, 3, s, hd, None)
+    assert rel(gk, L("repkv_gx")) < FP32_TOL
+
+
+# ----------------------------------------------------------------------------- norms / softmax
+def run_layernorm(capi, x, w, b, gy):
+    rows, dim = x.size // x.shape[-1], x.shape[-1]
+    dx_, dw_, db_ = dev(x), dev(w), dev(b)
+    y = torch.empty_like(dx_)
+    capi.call("mft_layernorm_fwd", dx_, dw_, db_, y, rows, dim, 1e-5, None)
+    gx, dg, dbeta = torch.empty_like(dx_), torch.empty(dim, device="cuda"), torch.empty(dim, device="cuda")
+    w_ = ws(capi.lib.mft_norm_bwd_workspace_bytes(rows, dim))
+    capi.call("mft_layernorm_bwd", dx_, dw_, dev(gy), gx, dg, dbeta, rows, dim, 1e-5, w_, w_.numel(), None)
+    return y, gx, dg, dbeta
+
+
+def test_layernorm_golden(capi, golden_ops):
+    L = golden_ops
+    y, gx, dg, db = run_layernorm(capi, L("ln_x"), L("ln_w"), L("ln_b"), L("ln_gy"))
+    assert rel(y, L("ln_y")) < FP32_TOL and rel(gx, L("ln_gx")) < FP32_TOL
+    assert rel(dg, L("ln_gw")) < FP32_TOL and rel(db, L("ln_gb")) < FP32_TOL
+
+
+@pytest.mark.parametrize("rows,dim", [(1, 768), (37, 768), (512, 1024), (300, 640), (64, 100), (5, 2048), (9, 3000)])
+def test_layernorm_shapes(capi, rows, dim):
+    rng = np.random.default_rng(rows * dim)
+    x = (rng.standard_normal((rows, dim)) * 1.5 + 0.3).astype(np.float32)
+    w, b = rng.standard_normal(dim).astype(np.float32), rng.standard_normal(dim).astype(np.float32)
+    gy = rng.standard_normal((rows, dim)).astype(np.float32)
+    y, gx, dg, db = run_layernorm(capi, x, w, b, gy)
+    ey = O.layer_norm_fwd(x, w, b)
+    ex, eg, eb = O.layer_norm_bwd(x, w, gy)
+    assert rel(y, ey) < FP32_TOL and rel(gx, ex) < 2e-5 and rel(dg, eg) < FP32_TOL and rel(db, eb) < FP32_TOL
+
+
+def test_rmsnorm_golden_and_shapes(capi, golden_ops):
+    L = golden_ops
+    cases = [(L("rms_x"), L("rms_w"), L("rms_gy"), L("rms_y"), L("rms_gx"), L("rms_gw"))]
+    rng = np.random.default_rng(3)
+    for rows, dim in [(1024, 640), (100, 256), (3, 50)]:
+        x = rng.standard_normal((rows, dim)).astype(np.float32)
+        w = (rng.standard_normal(dim) * 0.3).astype(np.float32)
+        gy = rng.standard_normal((rows, dim)).astype(np.float32)
+        ex, ew = O.rms_norm_bwd(x, w, gy)
+        cases.append((x, w, gy, O.rms_norm_fwd(x, w), ex, ew))
+    for x, w, gy, ey, ex, ew in cases:
+        rows, dim = x.size // x.shape[-1], x.shape[-1]
+        dx_, dw_ = dev(x), dev(w)
+        y = torch.empty_like(dx_)
+        capi.call("mft_rmsnorm_fwd", dx_, dw_, y, rows, dim, 1e-6, 1, None)
+        gx, gw = torch.empty_like(dx_), torch.empty(dim, device="cuda")
+        w_ = ws(capi.lib.mft_norm_bwd_workspace_bytes(rows, dim))
+        capi.call("mft_rmsnorm_bwd", dx_, dw_, dev(gy), gx, gw, rows, dim, 1e-6, 1, w_, w_.numel(), None)
+        assert rel(y, ey) < FP32_TOL and rel(gx, ex) < FP32_TOL and rel(gw, ew) < FP32_TOL
+
+
+def test_softmax_golden(capi, golden_ops):
+    L = golden_ops
+    x = dev(L("softmax_x"))
+    rows, dim = x.numel() // x.shape[-1], x.shape[-1]
+    y = torch.empty_like(x)
+    capi.call("mft_softmax_fwd", x, y, rows, dim, None)
+    assert rel(y, L("softmax_y")) < FP32_TOL
+    gx = torch.empty_like(x)
+    capi.call("mft_softmax_bwd", y, dev(L("softmax_gy")), gx, rows, dim, None)
+    assert rel(gx, L("softmax_gx")) < FP32_TOL
