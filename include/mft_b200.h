@@ -71,7 +71,8 @@ int mft_permute0213(const float* in, float* out, int64_t d0, int64_t d1, int64_t
  * mft_binary: out = a (op) b with numpy broadcasting of b over a described by (outer, mid, inner):
  *   a, out are [outer, mid, inner]; b_mode 0: b same shape; 1: b is [inner] (bias); 2: b is [mid, inner]
  *   (mask [S,S] onto [B*H,S,S]); 3: b is [outer_b, 1, inner] with outer index a_outer / b_div
- *   (padding mask [B,1,1,S]). op: 0 add, 1 sub, 2 mul, 3 div. (core/ops.cpp:166-484) */
+ *   (padding mask [B,1,1,S]). op: 0 add, 1 sub, 2 mul, 3 div (core/ops.cpp:166-484); 4 eq, 5 ne, 6 gt, 7 lt,
+ *   8 ge, 9 le with 1.0/0.0 results (core/ops.cpp:1941-1992). */
 int mft_binary(int op, const float* a, const float* b, float* out, int64_t outer, int64_t mid, int64_t inner,
                int b_mode, int64_t b_div, mft_stream_t stream);
 /* out = a*alpha + beta   (ops::mul/add/sub/div with a scalar, core/ops.cpp:380-484; ScaleBackward :970-974) */
@@ -87,6 +88,8 @@ int mft_colsum(const float* g, int64_t ldg, float* out, int64_t rows, int64_t n,
 /* unary ops: kind 0 gelu_tanh fwd, 1 relu, 2 sigmoid, 3 silu, 4 tanh, 5 exp, 6 log, 7 sqrt, 8 abs
  * (core/ops.cpp:1033-1117). */
 int mft_unary(int kind, const float* x, float* y, int64_t n, mft_stream_t stream);
+/* parameterised unary ops: kind 0 pow(x, p0), kind 1 clamp(x, p0, p1) (ops::pow / ops::clamp, core/ops.cpp). */
+int mft_unary_param(int kind, const float* x, float* y, int64_t n, float p0, float p1, mft_stream_t stream);
 /* GELU (tanh form, constants 0.7978845608f / 0.044715f): core/ops.cpp:1055-1079, GeluBackward
  * core/backward_functions.cpp:155-177. */
 int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t stream);
@@ -171,7 +174,8 @@ int mft_lm_ce_bwd(const float* logits, int64_t ld, const int32_t* labels, const 
  *   optim/gemma_trainer.cpp:84-102). workspace: mft_grad_sumsq_workspace_bytes().
  * mft_clip_scale: scale_out[0] = (max_norm > 0 && norm > max_norm) ? max_norm/(norm+1e-6) : 1, norm_out[0] = norm,
  *   with norm = sqrt(sumsq[0]) * pre_scale (pre_scale = 1/world_size after a summed allreduce).
- * mft_scale_grads: grad *= scale[0] * pre_scale in place (host-visible clip semantics).
+ *   scale_out already includes pre_scale, so it can be handed to mft_adam_step / mft_scale_grads as is.
+ * mft_scale_grads: grad *= scale[0] in place (host-visible clip semantics).
  * mft_adam_step: Adam with L2-coupled weight decay exactly as optim/adam.cpp:25-90:
  *   g' = g*gscale + wd*p; m = b1*m+(1-b1)g'; v = b2*v+(1-b2)g'^2; p -= lr*(m/bc1)/(sqrt(v/bc2)+eps),
  *   bc = 1-beta^t with std::pow(float) semantics, t = step_per_slot (each slot carries its own step

@@ -57,6 +57,7 @@ SIGNATURES = {
     "mft_colsum_workspace_bytes": (sz, [i64, i64]),
     "mft_colsum": (C.c_int, [vp, i64, vp, i64, i64, vp, sz, vp]),
     "mft_unary": (C.c_int, [C.c_int, vp, vp, i64, vp]),
+    "mft_unary_param": (C.c_int, [C.c_int, vp, vp, i64, f32, f32, vp]),
     "mft_gelu_fwd": (C.c_int, [vp, vp, i64, vp]),
     "mft_gelu_bwd": (C.c_int, [vp, vp, vp, i64, vp]),
     "mft_mul_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, vp]),

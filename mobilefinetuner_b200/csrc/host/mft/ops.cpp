@@ -1,0 +1,282 @@
+// ops:: implementations: shape logic on the host, arithmetic in CUDA kernels behind the C ABI.
+// Reference semantics are cited per function (paths relative to operators/finetune_ops/).
+#include "ops.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <random>
+#include <stdexcept>
+
+#include "autograd_engine.h"
+#include "mft_b200.h"
+#include "ops_internal.h"
+#include "runtime.h"
+
+namespace ops {
+
+using autograd::Engine;
+using internal::GemmCall;
+
+namespace internal {
+
+bool wants_grad(const TensorPtr& t) { return t && t->requires_grad(); }
+
+void track(const TensorPtr& out, const std::vector<TensorPtr>& inputs, BackwardFunctionPtr fn) {
+    if (!Engine::instance().is_enabled()) return;
+    bool any = false;
+    for (const auto& t : inputs) any = any || wants_grad(t);
+    if (!any) return;
+    out->set_requires_grad(true);
+    Engine::instance().register_node(out, inputs, std::move(fn));
+}
+
+TensorPtr new_like(const TensorPtr& t) { return Tensor::make(t->shape(), t->dtype()); }
+
+void require_f32(const TensorPtr& t, const char* op) {
+    if (!t) throw TensorError(std::string(op) + ": null tensor");
+    if (t->dtype() != kFloat32) throw TensorError(std::string(op) + ": float32 tensor expected");
+}
+
+// Chooses the execution form of one GEMM. Large products whose operands are not K-major are brought into
+// K-major form by a transpose pass (cached on 2-D weights) so they run on the tcgen05 kernel; everything
+// else goes to mft_gemm as is (SIMT kernel handles any layout).
+void run_gemm(GemmCall g) {
+    if (g.m == 0 || g.n == 0) return;
+    const int64_t work = int64_t(g.m) * g.n * std::max<int64_t>(g.k, 1) * std::max(g.batch, 1);
+    const bool big = work >= (int64_t(1) << 24) && g.m >= 64 && g.n >= 16 && g.k >= 32;
+    TensorPtr tmp_a, tmp_b;   // keep K-major temporaries alive until the launch is enqueued
+    if (big && g.batch <= 1) {
+        if (g.trans_a) {       // stored [k,m] -> [m,k]
+            const int64_t ld = (g.k + 3) / 4 * 4;
+            tmp_a = Tensor::make({g.m, g.k}, kFloat32, false, ld);
+            mft_rt::check(mft_transpose2d(g.a, g.lda, tmp_a->dev_f32_out(), ld, g.k, g.m, 1, 0, 0, mft_rt::stream()), "mft_transpose2d");
+            g.a = tmp_a->dev_f32(); g.lda = ld; g.trans_a = 0;
+        }
+        if (!g.trans_b) {      // stored [k,n] -> [n,k]
+            if (g.b_weight && g.b_weight->ndim() == 2 && g.b_weight->dev_f32() == g.b) {
+                tmp_b = g.b_weight->transposed_shadow();
+            } else {
+                const int64_t ld = (g.k + 3) / 4 * 4;
+                tmp_b = Tensor::make({g.n, g.k}, kFloat32, false, ld);
+                mft_rt::check(mft_transpose2d(g.b, g.ldb, tmp_b->dev_f32_out(), ld, g.k, g.n, 1, 0, 0, mft_rt::stream()), "mft_transpose2d");
+            }
+            g.b = tmp_b->dev_f32(); g.ldb = tmp_b->ld(); g.trans_b = 1;
+        }
+    }
+    mft_gemm_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.m = int32_t(g.m); a.n = int32_t(g.n); a.k = int32_t(g.k);
+    a.a = g.a; a.lda = g.lda; a.trans_a = g.trans_a;
+    a.b = g.b; a.ldb = g.ldb; a.trans_b = g.trans_b;
+    a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
+    a.k2 = int32_t(g.k2); a.a2 = g.a2; a.lda2 = g.lda2; a.b2 = g.b2; a.ldb2 = g.ldb2;
+    a.batch = std::max(g.batch, 1); a.stride_a = g.stride_a; a.stride_b = g.stride_b; a.stride_c = g.stride_c;
+    mft_rt::check(mft_gemm(&a, mft_rt::stream()), "mft_gemm");
+}
+
+// Output leading dimension for a [.., n] GEMM result: rows are padded to 32 floats when n is large and not a
+// multiple of 4 (a 50257-wide logits row could not be addressed by TMA otherwise).
+int64_t out_ld(int64_t n) { return (n >= 1024 && (n % 4) != 0) ? (n + 31) / 32 * 32 : n; }
+
+}  // namespace internal
+
+using namespace internal;
+
+TensorPtr contiguous(const TensorPtr& t) {
+    if (!t) throw TensorError("contiguous: null tensor");
+    if (t->is_dense()) return t;
+    auto out = Tensor::make(t->shape(), t->dtype());
+    const size_t es = DTypeUtils::size_of(t->dtype());
+    const int64_t w = t->shape().back();
+    mft_rt::d2d_2d(out->dev_out(), size_t(w) * es, t->dev(), size_t(t->ld()) * es, size_t(w) * es, size_t(t->rows()));
+    return out;
+}
+
+// ============================================================================ broadcasting helpers
+bool same_shape(const TensorPtr& a, const TensorPtr& b) { return a && b && a->shape() == b->shape(); }
+
+std::vector<int64_t> infer_broadcast_shape(const TensorPtr& a, const TensorPtr& b) {
+    const auto& sa = a->shape();
+    const auto& sb = b->shape();
+    const size_t n = std::max(sa.size(), sb.size());
+    std::vector<int64_t> out(n);
+    for (size_t i = 0; i < n; ++i) {
+        int64_t da = i < n - sa.size() ? 1 : sa[i - (n - sa.size())];
+        int64_t db = i < n - sb.size() ? 1 : sb[i - (n - sb.size())];
+        if (da != db && da != 1 && db != 1) throw TensorError("Tensors are not broadcastable");
+        out[i] = std::max(da, db);
+    }
+    return out;
+}
+std::vector<int64_t> broadcast_shape(const TensorPtr& a, const TensorPtr& b) { return infer_broadcast_shape(a, b); }
+bool broadcastable(const TensorPtr& a, const TensorPtr& b) {
+    try { infer_broadcast_shape(a, b); return true; } catch (const TensorError&) { return false; }
+}
+
+namespace {
+
+// Describes how `small` broadcasts over `big` (big has the output shape): one of the four modes of mft_binary.
+struct Bcast { int mode; int64_t outer, mid, inner, div; };
+
+bool plan_broadcast(const std::vector<int64_t>& big, const std::vector<int64_t>& small, Bcast& p) {
+    int64_t nb = 1, ns = 1;
+    for (auto d : big) nb *= d;
+    for (auto d : small) ns *= d;
+    if (big == small) { p = {0, 1, 1, nb, 1}; return true; }
+    if (ns == 1) return false;  // scalar tensors are handled by the caller
+    // strip leading 1s of small
+    std::vector<int64_t> s = small;
+    while (!s.empty() && s.front() == 1 && s.size() > 1) s.erase(s.begin());
+    // suffix match: small == trailing dims of big  -> mode 1 (1 dim) / mode 2 (>= 2 dims)
+    if (s.size() <= big.size() && std::equal(s.begin(), s.end(), big.end() - s.size())) {
+        if (s.size() == 1) { p = {1, 1, nb / s[0], s[0], 1}; return true; }
+        int64_t inner = s.back(), mid = ns / inner;
+        p = {2, nb / ns, mid, inner, 1};
+        return true;
+    }
+    // [B,1,..,1,S] over [B,H,..,S]: same rank, first and last dims equal, the rest 1 -> mode 3
+    if (small.size() == big.size() && small.size() >= 3 && small.front() == big.front() && small.back() == big.back()) {
+        bool mid_ones = true;
+        for (size_t i = 1; i + 1 < small.size(); ++i) mid_ones = mid_ones && small[i] == 1;
+        if (mid_ones) {
+            int64_t inner = big.back();
+            int64_t per_b = nb / big.front() / inner;   // rows per batch entry
+            p = {3, nb / inner, 1, inner, per_b};
+            return true;
+        }
+    }
+    return false;
+}
+
+// Sums `g` (shape gshape) down to `target` shape — AddBackward's sum_to_shape, core/backward_functions.cpp:36-64.
+TensorPtr reduce_to_shape(const TensorPtr& g, const std::vector<int64_t>& target) {
+    if (g->shape() == target) return g;
+    int64_t nt = 1;
+    for (auto d : target) nt *= d;
+    auto gd = contiguous(g);
+    Bcast p;
+    if (nt == 1) {
+        auto out = Tensor::make(target, kFloat32);
+        size_t wsb = mft_colsum_workspace_bytes(gd->numel(), 1);
+        mft_rt::check(mft_colsum(gd->dev_f32(), 1, out->dev_f32_out(), gd->numel(), 1, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_colsum");
+        return out;
+    }
+    if (!plan_broadcast(gd->shape(), target, p)) throw TensorError("sum_to_shape: unsupported broadcast pattern");
+    auto out = Tensor::make(target, kFloat32);
+    if (p.mode == 1 || p.mode == 2) {
+        const int64_t n = (p.mode == 1) ? p.inner : p.mid * p.inner;
+        const int64_t rows = gd->numel() / n;
+        size_t wsb = mft_colsum_workspace_bytes(rows, n);
+        mft_rt::check(mft_colsum(gd->dev_f32(), n, out->dev_f32_out(), rows, n, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_colsum");
+        return out;
+    }
+    // mode 3: [B, per_b, inner] summed over per_b, batched column sums
+    const int64_t B = target.front(), inner = p.inner, per_b = p.div;
+    for (int64_t b = 0; b < B; ++b) {
+        size_t wsb = mft_colsum_workspace_bytes(per_b, inner);
+        mft_rt::check(mft_colsum(gd->dev_f32() + b * per_b * inner, inner, out->dev_f32_out() + b * inner, per_b, inner,
+                                 mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_colsum");
+    }
+    return out;
+}
+
+class BinaryBackward : public BackwardFunction {
+public:
+    BinaryBackward(int op, TensorPtr a, TensorPtr b) : op_(op), a_(std::move(a)), b_(std::move(b)) {}
+    std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
+        TensorPtr gy = contiguous(gy_in);
+        TensorPtr ga, gb;
+        const bool wa = wants_grad(a_), wb = wants_grad(b_);
+        if (op_ == 0 || op_ == 1) {          // add / sub  (core/backward_functions.cpp:36-72)
+            if (wa) ga = reduce_to_shape(gy, a_->shape());
+            if (wb) {
+                TensorPtr g = gy;
+                if (op_ == 1) { g = new_like(gy); mft_rt::check(mft_affine(gy->dev_f32(), g->dev_f32_out(), gy->numel(), -1.f, 0.f, mft_rt::stream()), "mft_affine"); }
+                gb = reduce_to_shape(g, b_->shape());
+            }
+        } else if (op_ == 2) {               // mul (core/backward_functions.cpp:74-83)
+            if (a_->shape() == b_->shape()) {
+                if (wa) ga = new_like(gy);
+                if (wb) gb = new_like(gy);
+                mft_rt::check(mft_mul_bwd(contiguous(a_)->dev_f32(), contiguous(b_)->dev_f32(), gy->dev_f32(),
+                                          ga ? ga->dev_f32_out() : nullptr, gb ? gb->dev_f32_out() : nullptr, gy->numel(), mft_rt::stream()), "mft_mul_bwd");
+            } else {
+                if (wa) ga = reduce_to_shape(mul(gy, b_), a_->shape());
+                if (wb) gb = reduce_to_shape(mul(gy, a_), b_->shape());
+            }
+        } else {                             // div: ga = gy/b ; gb = -gy*a/b^2
+            if (wa) ga = reduce_to_shape(div(gy, b_), a_->shape());
+            if (wb) gb = reduce_to_shape(mul(div(mul(gy, a_), mul(b_, b_)), -1.0f), b_->shape());
+        }
+        return {ga, gb};
+    }
+private:
+    int op_;
+    TensorPtr a_, b_;
+};
+
+TensorPtr binary(int op, const TensorPtr& a_in, const TensorPtr& b_in, const char* name) {
+    require_f32(a_in, name);
+    require_f32(b_in, name);
+    TensorPtr a = contiguous(a_in), b = contiguous(b_in);
+    auto oshape = infer_broadcast_shape(a, b);
+    auto out = Tensor::make(oshape, kFloat32);
+    Bcast p;
+    auto st = mft_rt::stream();
+    if (a->shape() == oshape && plan_broadcast(oshape, b->shape(), p)) {
+        mft_rt::check(mft_binary(op, a->dev_f32(), b->dev_f32(), out->dev_f32_out(), p.outer, p.mid, p.inner, p.mode, p.div, st), name);
+    } else if (b->numel() == 1 && a->shape() == oshape) {
+        // scalar tensor on the right: broadcast as a 1-element bias
+        mft_rt::check(mft_binary(op, a->dev_f32(), b->dev_f32(), out->dev_f32_out(), 1, a->numel(), 1, 1, 1, st), name);
+    } else if (b->shape() == oshape && (op == 0 || op == 2) && (plan_broadcast(oshape, a->shape(), p) || a->numel() == 1)) {
+        // commutative ops with the small operand on the left
+        if (a->numel() == 1) mft_rt::check(mft_binary(op, b->dev_f32(), a->dev_f32(), out->dev_f32_out(), 1, b->numel(), 1, 1, 1, st), name);
+        else mft_rt::check(mft_binary(op, b->dev_f32(), a->dev_f32(), out->dev_f32_out(), p.outer, p.mid, p.inner, p.mode, p.div, st), name);
+    } else {
+        throw TensorError(std::string(name) + ": unsupported broadcast pattern on the device path");
+    }
+    track(out, {a_in, b_in}, std::make_shared<BinaryBackward>(op, a_in, b_in));
+    return out;
+}
+
+class AffineBackward : public BackwardFunction {   // ScaleBackward: core/backward_functions.cpp:970-974
+public:
+    explicit AffineBackward(float s) : s_(s) {}
+    std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
+        if (s_ == 1.0f) return {gy_in};
+        TensorPtr gy = contiguous(gy_in);
+        auto g = new_like(gy);
+        mft_rt::check(mft_affine(gy->dev_f32(), g->dev_f32_out(), gy->numel(), s_, 0.f, mft_rt::stream()), "mft_affine");
+        return {g};
+    }
+private:
+    float s_;
+};
+
+TensorPtr affine(const TensorPtr& t_in, float alpha, float beta, const char* name) {
+    require_f32(t_in, name);
+    TensorPtr t = contiguous(t_in);
+    auto out = new_like(t);
+    mft_rt::check(mft_affine(t->dev_f32(), out->dev_f32_out(), t->numel(), alpha, beta, mft_rt::stream()), name);
+    track(out, {t_in}, std::make_shared<AffineBackward>(alpha));
+    return out;
+}
+
+}  // namespace
+
+// core/ops.cpp:166-484
+TensorPtr add(const TensorPtr& a, const TensorPtr& b) { return binary(0, a, b, "add"); }
+TensorPtr sub(const TensorPtr& a, const TensorPtr& b) { return binary(1, a, b, "sub"); }
+TensorPtr mul(const TensorPtr& a, const TensorPtr& b) { return binary(2, a, b, "mul"); }
+TensorPtr div(const TensorPtr& a, const TensorPtr& b) { return binary(3, a, b, "div"); }
+TensorPtr add(const TensorPtr& t, float s) { return affine(t, 1.f, s, "add(scalar)"); }
+TensorPtr sub(const TensorPtr& t, float s) { return affine(t, 1.f, -s, "sub(scalar)"); }
+TensorPtr mul(const TensorPtr& t, float s) { return affine(t, s, 0.f, "mul(scalar)"); }
+TensorPtr div(const TensorPtr& t, float s) { return affine(t, 1.0f / s, 0.f, "div(scalar)"); }
+TensorPtr add(float s, const TensorPtr& t) { return affine(t, 1.f, s, "add(scalar)"); }
+TensorPtr sub(float s, const TensorPtr& t) { return affine(t, -1.f, s, "sub(scalar)"); }
+TensorPtr mul(float s, const TensorPtr& t) { return affine(t, s, 0.f, "mul(scalar)"); }
+TensorPtr div(float s, const TensorPtr& t) { return mul(pow(t, -1.0f), s); }
+
+}  // namespace ops

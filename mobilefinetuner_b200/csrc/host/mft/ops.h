@@ -1,0 +1,124 @@
+// ops:: free functions — API mirror of the reference's core/ops.h:24-189 (same names, argument meaning and
+// error behaviour: shape errors throw ops::TensorError / std::runtime_error). Every body enqueues hand-written
+// CUDA kernels through the C ABI (include/mft_b200.h); nothing computes on the host.
+#pragma once
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "tensor.h"
+
+namespace ops {
+
+// arithmetic (numpy broadcasting for tensor-tensor forms)
+TensorPtr add(const TensorPtr& a, const TensorPtr& b);
+TensorPtr sub(const TensorPtr& a, const TensorPtr& b);
+TensorPtr mul(const TensorPtr& a, const TensorPtr& b);
+TensorPtr div(const TensorPtr& a, const TensorPtr& b);
+TensorPtr add(const TensorPtr& t, float s);
+TensorPtr sub(const TensorPtr& t, float s);
+TensorPtr mul(const TensorPtr& t, float s);
+TensorPtr div(const TensorPtr& t, float s);
+TensorPtr add(float s, const TensorPtr& t);
+TensorPtr sub(float s, const TensorPtr& t);
+TensorPtr mul(float s, const TensorPtr& t);
+TensorPtr div(float s, const TensorPtr& t);
+
+// linear algebra
+TensorPtr matmul(const TensorPtr& a, const TensorPtr& b);
+TensorPtr matmul_rhs_T(const TensorPtr& a, const TensorPtr& b);   // a @ b^T without materialising b^T
+TensorPtr transpose(const TensorPtr& t, int dim0, int dim1);
+TensorPtr permute(const TensorPtr& t, const std::vector<int>& dims);
+TensorPtr linear(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias = nullptr);
+TensorPtr lora_linear(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& lora_A,
+                      const TensorPtr& lora_B, float alpha = 1.0f, const TensorPtr& bias = nullptr);
+
+// activations
+TensorPtr relu(const TensorPtr& x);
+TensorPtr gelu(const TensorPtr& x);
+TensorPtr silu(const TensorPtr& x);
+TensorPtr sigmoid(const TensorPtr& x);
+TensorPtr tanh_op(const TensorPtr& x);
+inline TensorPtr tanh(const TensorPtr& x) { return tanh_op(x); }
+TensorPtr softmax(const TensorPtr& x, int dim = -1);
+TensorPtr log_softmax(const TensorPtr& x, int dim = -1);
+
+// losses
+TensorPtr mse_loss(const TensorPtr& input, const TensorPtr& target, const std::string& reduction = "mean");
+TensorPtr cross_entropy_loss(const TensorPtr& input, const TensorPtr& target, const std::string& reduction = "mean");
+TensorPtr nll_loss(const TensorPtr& input, const TensorPtr& target, const std::string& reduction = "mean");
+
+// normalisation
+TensorPtr layer_norm(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias, float eps = 1e-5f);
+TensorPtr rms_norm(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);         // scale (1 + w)
+TensorPtr rms_norm_affine(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);  // scale w
+TensorPtr batch_norm(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias,
+                     const TensorPtr& running_mean = nullptr, const TensorPtr& running_var = nullptr,
+                     bool training = true, float momentum = 0.1f, float eps = 1e-5f);
+
+// shape
+TensorPtr reshape(const TensorPtr& t, const std::vector<int64_t>& shape);
+TensorPtr view(const TensorPtr& t, const std::vector<int64_t>& shape);
+TensorPtr flatten(const TensorPtr& t, int start_dim = 0, int end_dim = -1);
+TensorPtr squeeze(const TensorPtr& t, int dim = -1);
+TensorPtr unsqueeze(const TensorPtr& t, int dim);
+
+// dtype
+TensorPtr cast(const TensorPtr& t, DType target_dtype);
+inline TensorPtr to_fp16(const TensorPtr& t) { return cast(t, DType::kFloat16); }
+inline TensorPtr to_fp32(const TensorPtr& t) { return cast(t, DType::kFloat32); }
+
+// reductions: dim == -1 means "all elements" (reference quirk)
+TensorPtr sum(const TensorPtr& t, int dim = -1, bool keepdim = false);
+TensorPtr mean(const TensorPtr& t, int dim = -1, bool keepdim = false);
+
+// comparisons (1.0 / 0.0 results)
+TensorPtr eq(const TensorPtr& a, const TensorPtr& b);
+TensorPtr ne(const TensorPtr& a, const TensorPtr& b);
+TensorPtr gt(const TensorPtr& a, const TensorPtr& b);
+TensorPtr lt(const TensorPtr& a, const TensorPtr& b);
+TensorPtr ge(const TensorPtr& a, const TensorPtr& b);
+TensorPtr le(const TensorPtr& a, const TensorPtr& b);
+
+TensorPtr dropout(const TensorPtr& t, float p = 0.5f, bool training = true);
+TensorPtr uniform(const std::vector<int64_t>& shape, float low = 0.0f, float high = 1.0f, DType dtype = kFloat32,
+                  Device device = kCPU);
+inline TensorPtr unifor(const std::vector<int64_t>& shape, float low = 0.0f, float high = 1.0f, DType dtype = kFloat32,
+                        Device device = kCPU) { return uniform(shape, low, high, dtype, device); }
+
+TensorPtr abs(const TensorPtr& t);
+TensorPtr sqrt(const TensorPtr& t);
+TensorPtr exp(const TensorPtr& t);
+TensorPtr log(const TensorPtr& t);
+TensorPtr pow(const TensorPtr& t, float exponent);
+TensorPtr clamp(const TensorPtr& t, float min_val, float max_val);
+
+// attention helpers
+TensorPtr create_causal_mask(int seq_len, DType dtype = kFloat32, Device device = kCPU);
+TensorPtr apply_mask(const TensorPtr& input, const TensorPtr& mask, float mask_value = -1e9f);
+TensorPtr repeat_kv_heads(const TensorPtr& kv, int repeat_factor);
+TensorPtr apply_rope(const TensorPtr& x, int seq_len, int head_dim, float rope_theta = 10000.0f);
+TensorPtr swiglu(const TensorPtr& gate, const TensorPtr& up);
+
+bool same_shape(const TensorPtr& a, const TensorPtr& b);
+bool broadcastable(const TensorPtr& a, const TensorPtr& b);
+std::vector<int64_t> broadcast_shape(const TensorPtr& a, const TensorPtr& b);
+std::vector<int64_t> infer_broadcast_shape(const TensorPtr& a, const TensorPtr& b);
+
+// ---- B200 extensions used by the model graphs (no counterpart in the reference API) ----
+// Dense copy of a pitched tensor (identity for dense ones).
+TensorPtr contiguous(const TensorPtr& t);
+// One autograd node for y = x W (+b) + sum_i s_i (x A_i) B_i  — replaces the six-node chain LoRALinear::forward
+// builds in the reference (nn/lora_linear.cpp:47-108). A/B accept both [in,r]/[r,out] and PEFT [r,in]/[out,r].
+struct LoraTerm { TensorPtr A, B; float scale; };
+TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms);
+// logits = x @ E^T for an embedding table E [V,C] (tied lm_head) without materialising E^T
+// (graph/gpt2_model.cpp:425-439 transposes wte on every forward).
+TensorPtr lm_head_tied(const TensorPtr& x, const TensorPtr& table);
+// GPT-2 attention over the fused qkv projection [B,S,3C] -> ctx [B,S,C]; forward only, result carries no
+// autograd history exactly like the reference's zeros+memcpy split (graph/gpt2_model.cpp:616-676).
+TensorPtr gpt2_causal_attention(const TensorPtr& qkv, int n_head);
+// x[b,s,:] = wte[ids[b,s],:] + wpe[s,:]   (wpe == nullptr: Gemma, times `scale`)
+TensorPtr embedding_lookup(const TensorPtr& ids, const TensorPtr& wte, const TensorPtr& wpe, float scale = 1.0f);
+
+}  // namespace ops

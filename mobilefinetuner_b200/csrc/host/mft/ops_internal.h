@@ -1,0 +1,35 @@
+// Helpers shared by the op translation units (not part of the mirrored API).
+#pragma once
+#include <vector>
+
+#include "autograd_engine.h"
+#include "tensor.h"
+
+namespace ops {
+namespace internal {
+
+bool wants_grad(const TensorPtr& t);
+// Registers `fn` as the producer of `out` when the engine is enabled and any input requires grad
+// (the reference's `if (a->requires_grad() || ...) { set_requires_grad(true); register_backward(...) }`).
+void track(const TensorPtr& out, const std::vector<TensorPtr>& inputs, BackwardFunctionPtr fn);
+TensorPtr new_like(const TensorPtr& t);
+void require_f32(const TensorPtr& t, const char* op);
+int64_t out_ld(int64_t n);
+
+// One GEMM in mft_gemm terms with device pointers; `b_weight` lets run_gemm reuse a cached K-major shadow.
+struct GemmCall {
+    int64_t m = 0, n = 0, k = 0;
+    const float* a = nullptr; int64_t lda = 0; int trans_a = 0;
+    const float* b = nullptr; int64_t ldb = 0; int trans_b = 0;
+    float* c = nullptr; int64_t ldc = 0;
+    float alpha = 1.0f, beta = 0.0f;
+    const float* bias = nullptr;
+    float* gelu_out = nullptr;
+    int64_t k2 = 0; const float* a2 = nullptr; int64_t lda2 = 0; const float* b2 = nullptr; int64_t ldb2 = 0;
+    int batch = 1; int64_t stride_a = 0, stride_b = 0, stride_c = 0;
+    TensorPtr b_weight;
+};
+void run_gemm(GemmCall g);
+
+}  // namespace internal
+}  // namespace ops

@@ -10,7 +10,13 @@ __device__ __forceinline__ float bin_apply(float a, float b) {
     if (OP == 0) return a + b;
     if (OP == 1) return a - b;
     if (OP == 2) return a * b;
-    return a / b;
+    if (OP == 3) return a / b;
+    if (OP == 4) return a == b ? 1.f : 0.f;
+    if (OP == 5) return a != b ? 1.f : 0.f;
+    if (OP == 6) return a > b ? 1.f : 0.f;
+    if (OP == 7) return a < b ? 1.f : 0.f;
+    if (OP == 8) return a >= b ? 1.f : 0.f;
+    return a <= b ? 1.f : 0.f;
 }
 
 // b_mode 0: same shape (12 B/elem); vectorised when n % 4 == 0 and pointers aligned.
@@ -171,6 +177,14 @@ __global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __rest
     }
 }
 
+// y = pow(x, p0) (kind 0) or clamp(x, p0, p1) (kind 1)
+__global__ void unary_param_kernel(int kind, const float* __restrict__ x, float* __restrict__ y, int64_t n, float p0, float p1) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        float v = x[i];
+        y[i] = kind == 0 ? powf(v, p0) : fminf(fmaxf(v, p0), p1);
+    }
+}
+
 __global__ void mul_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ gy,
                                float* __restrict__ ga, float* __restrict__ gb, int64_t n) {
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
@@ -186,7 +200,7 @@ using namespace mft;
 
 extern "C" int mft_binary(int op, const float* a, const float* b, float* out, int64_t outer, int64_t mid,
                           int64_t inner, int b_mode, int64_t b_div, mft_stream_t stream) {
-    if (op < 0 || op > 3 || b_mode < 0 || b_mode > 3) return set_error(1, "mft_binary: bad op/b_mode");
+    if (op < 0 || op > 9 || b_mode < 0 || b_mode > 3) return set_error(1, "mft_binary: bad op/b_mode");
     if (outer * mid * inner == 0) return 0;
     if (!a || !b || !out) return set_error(1, "mft_binary: null pointer");
     cudaStream_t st = as_stream(stream);
@@ -194,7 +208,13 @@ extern "C" int mft_binary(int op, const float* a, const float* b, float* out, in
         case 0: launch_binary<0>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
         case 1: launch_binary<1>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
         case 2: launch_binary<2>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
-        default: launch_binary<3>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 3: launch_binary<3>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 4: launch_binary<4>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 5: launch_binary<5>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 6: launch_binary<6>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 7: launch_binary<7>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        case 8: launch_binary<8>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
+        default: launch_binary<9>(a, b, out, outer, mid, inner, b_mode, b_div, st); break;
     }
     MFT_CHECK_LAUNCH("mft_binary");
     return 0;
@@ -267,5 +287,14 @@ extern "C" int mft_mul_bwd(const float* a, const float* b, const float* gy, floa
     if (!a || !b || !gy) return set_error(1, "mft_mul_bwd: null pointer");
     mul_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(a, b, gy, ga, gb, n);
     MFT_CHECK_LAUNCH("mft_mul_bwd");
+    return 0;
+}
+
+extern "C" int mft_unary_param(int kind, const float* x, float* y, int64_t n, float p0, float p1, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!x || !y) return set_error(1, "mft_unary_param: null pointer");
+    if (kind < 0 || kind > 1) return set_error(1, "mft_unary_param: unknown kind %d", kind);
+    unary_param_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(kind, x, y, n, p0, p1);
+    MFT_CHECK_LAUNCH("mft_unary_param");
     return 0;
 }
