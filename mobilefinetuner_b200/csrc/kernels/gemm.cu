@@ -1,5 +1,6 @@
 // mft_gemm dispatch + library-level entry points (version, errors, device check).
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include "common.cuh"
 #include "gemm_internal.cuh"
@@ -7,7 +8,12 @@
 namespace mft {
 
 static thread_local char g_err[512] = "";
-static bool g_use_tc = true;
+// MFT_USE_TENSOR_CORES=0 in the environment starts the library on the exact fp32 SIMT GEMM (parity debugging).
+static bool env_use_tc() {
+    const char* e = getenv("MFT_USE_TENSOR_CORES");
+    return !(e && e[0] == '0');
+}
+static bool g_use_tc = env_use_tc();
 
 int set_error(int code, const char* fmt, ...) {
     va_list ap;

@@ -22,9 +22,10 @@ pytestmark = pytest.mark.gpu
 HARNESS = os.path.join(ROOT, "mobilefinetuner_b200", "mft_harness")
 
 
-def run_harness(args, timeout=600):
+def run_harness(args, timeout=600, tensor_cores=True):
     assert os.path.exists(HARNESS), "build the host library first (make -C mobilefinetuner_b200/csrc)"
-    r = subprocess.run([HARNESS] + args, capture_output=True, text=True, timeout=timeout)
+    env = dict(os.environ, MFT_USE_TENSOR_CORES="1" if tensor_cores else "0")
+    r = subprocess.run([HARNESS] + args, capture_output=True, text=True, timeout=timeout, env=env)
     assert r.returncode == 0, f"harness failed:\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}"
     assert "impl mft_b200" in r.stdout
     return r.stdout
@@ -91,10 +92,18 @@ def test_gpt2_full_finetune_tiny_50_steps():
     assert check_traj(out, "gpt2_full_tiny.txt") < 1e-4
 
 
-def test_gpt2_lora_all_targets_seq64_high_lr():
+@pytest.mark.parametrize("tensor_cores", [False, True])
+def test_gpt2_lora_all_targets_seq64_high_lr(tensor_cores):
+    """lr = 1e-2 makes the adapters move: with the exact fp32 GEMM the trajectory matches tightly; with TF32
+    tensor-core GEMMs (the lm_head product is large enough to take that path) the loss still matches to 1e-3
+    and the gradient norm to the TF32 tolerance."""
     out = run_harness(["gpt2", "--steps", "10", "--layers", "2", "--embd", "128", "--heads", "4", "--vocab", "1000",
-                       "--batch", "2", "--seq", "64", "--rank", "8", "--lora_mlp", "1", "--lr", "1e-2", "--quiet", "1"])
-    check_traj(out, "gpt2_lora_mlp_s64.txt")
+                       "--batch", "2", "--seq", "64", "--rank", "8", "--lora_mlp", "1", "--lr", "1e-2", "--quiet", "1"],
+                      tensor_cores=tensor_cores)
+    if tensor_cores:
+        check_traj(out, "gpt2_lora_mlp_s64.txt", loss_tol=1e-3, gnorm_tol=2e-2, sumabs_tol=5e-3)
+    else:
+        check_traj(out, "gpt2_lora_mlp_s64.txt", loss_tol=1e-4, gnorm_tol=1e-3)
 
 
 def test_gemma_lora_tiny_50_steps():
