@@ -26,6 +26,7 @@ typedef void* mft_stream_t; /* a cudaStream_t (NULL = default stream) */
 
 /* ------------------------------------------------------------------ library / errors */
 int mft_version(void);
+int64_t mft_launch_count(void);            /* kernels enqueued by this library so far (process-wide) */
 const char* mft_last_error(void);          /* thread-local, valid until the next failing call */
 int mft_device_check(void);                /* 0 iff the current device is sm_100 (B200)        */
 int mft_use_tensor_cores(int enable);      /* 1 (default): tcgen05 TF32 GEMM when eligible; 0: SIMT fp32 GEMM
@@ -59,6 +60,10 @@ typedef struct mft_gemm_args {
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
 /* 1 if mft_gemm would take the tcgen05 path for these arguments (host-side predicate, no launch). */
 int mft_gemm_uses_tensor_cores(const mft_gemm_args* args);
+/* Measurement aid (no reference counterpart): while enabled, every tensor-core GEMM launch is bracketed by CUDA events on
+ * its stream; read returns the summed algorithmic FLOPs (2*m*n*(k+k2)*batch), summed launch milliseconds and launch count. */
+int mft_gemm_profile(int enable);
+int mft_gemm_profile_read(double* flops, double* ms, int64_t* launches);
 
 /* Out-of-place 2-D transpose: out[c,r] (ldo) = in[r,c] (ldi). Replaces ops::transpose's per-element
  * index loop for the 2-D case (core/ops.cpp:844-865) — used to keep K-major shadows of weights. */
@@ -185,8 +190,11 @@ typedef struct mft_tensor_slot {
     float* param; float* grad; float* m; float* v;
     int64_t n;
     float bias_corr1, bias_corr2;     /* 1-beta1^t, 1-beta2^t for this tensor's step count */
-    int32_t pad0, pad1;
+    int64_t bucket_offset;            /* element offset of this tensor in a flat gradient bucket (mft_pack_grads) */
 } mft_tensor_slot;
+/* Data-parallel exchange: pack every gradient (zeros where grad == NULL) into one flat fp32 bucket that a single
+ * all-reduce can sum; no counterpart in the reference (it has no distributed code). */
+int mft_pack_grads(const mft_tensor_slot* slots, int32_t num_slots, float* bucket, mft_stream_t stream);
 size_t mft_grad_sumsq_workspace_bytes(void);
 int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, double* out, void* workspace,
                    size_t workspace_bytes, mft_stream_t stream);

@@ -37,17 +37,20 @@ class GemmArgs(C.Structure):
 
 class TensorSlot(C.Structure):
     _fields_ = [("param", vp), ("grad", vp), ("m", vp), ("v", vp), ("n", i64),
-                ("bias_corr1", f32), ("bias_corr2", f32), ("pad0", i32), ("pad1", i32)]
+                ("bias_corr1", f32), ("bias_corr2", f32), ("bucket_offset", i64)]
 
 
 # name -> (restype, argtypes); must list every symbol declared in include/mft_b200.h
 SIGNATURES = {
     "mft_version": (C.c_int, []),
+    "mft_launch_count": (i64, []),
     "mft_last_error": (C.c_char_p, []),
     "mft_device_check": (C.c_int, []),
     "mft_use_tensor_cores": (C.c_int, [C.c_int]),
     "mft_gemm": (C.c_int, [C.POINTER(GemmArgs), vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),
+    "mft_gemm_profile": (C.c_int, [C.c_int]),
+    "mft_gemm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]),
     "mft_transpose2d": (C.c_int, [vp, i64, vp, i64, i64, i64, i64, i64, i64, vp]),
     "mft_permute0213": (C.c_int, [vp, vp, i64, i64, i64, i64, vp]),
     "mft_binary": (C.c_int, [C.c_int, vp, vp, vp, i64, i64, i64, C.c_int, i64, vp]),
@@ -77,6 +80,7 @@ SIGNATURES = {
     "mft_lm_ce_workspace_bytes": (sz, [i64]),
     "mft_lm_ce_fwd": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, sz, vp]),
     "mft_lm_ce_bwd": (C.c_int, [vp, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i64, vp]),
+    "mft_pack_grads": (C.c_int, [vp, i32, vp, vp]),
     "mft_grad_sumsq_workspace_bytes": (sz, []),
     "mft_grad_sumsq": (C.c_int, [vp, i32, vp, vp, sz, vp]),
     "mft_clip_scale": (C.c_int, [vp, f32, f32, vp, vp, vp]),

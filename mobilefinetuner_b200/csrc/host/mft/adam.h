@@ -35,6 +35,8 @@ public:
 
     // B200 extension: the same update with the clip factor read from a device scalar (never visits the host).
     void step_scaled(const std::vector<TensorPtr>& parameters, const std::vector<TensorPtr>& gradients, const float* dev_grad_scale);
+    // ... and with raw device gradient pointers (nullptr = no gradient), e.g. slices of an all-reduced bucket.
+    void step_device(const std::vector<TensorPtr>& parameters, const std::vector<float*>& grad_ptrs, const float* dev_grad_scale);
 
 protected:
     void update_param(TensorPtr param, const TensorPtr& grad, OptimizerState& state) override;
@@ -53,7 +55,7 @@ private:
 namespace optim_detail {
 struct SlotTable { void* dev = nullptr; int count = 0; };
 // Builds (and uploads) a table with one slot per parameter; grads[i] == nullptr marks "no gradient".
-SlotTable upload_slots(const std::vector<TensorPtr>& params, const std::vector<TensorPtr>& grads,
+SlotTable upload_slots(const std::vector<TensorPtr>& params, const std::vector<float*>& grads,
                        const std::vector<TensorPtr>* m, const std::vector<TensorPtr>* v,
                        const std::vector<float>* bc1, const std::vector<float>* bc2, void** dev_buf, size_t* dev_bytes);
 // sumsq of all non-null grads into a persistent device double; returns its device address.

@@ -12,22 +12,20 @@ namespace ops {
 
 namespace optim_detail {
 
-SlotTable upload_slots(const std::vector<TensorPtr>& params, const std::vector<TensorPtr>& grads,
+SlotTable upload_slots(const std::vector<TensorPtr>& params, const std::vector<float*>& grads,
                        const std::vector<TensorPtr>* m, const std::vector<TensorPtr>* v,
                        const std::vector<float>* bc1, const std::vector<float>* bc2, void** dev_buf, size_t* dev_bytes) {
     std::vector<mft_tensor_slot> host(params.size());
     for (size_t i = 0; i < params.size(); ++i) {
         mft_tensor_slot& s = host[i];
         std::memset(&s, 0, sizeof(s));
-        const TensorPtr& g = i < grads.size() ? grads[i] : nullptr;
         s.n = params[i]->numel();
         s.param = m ? params[i]->dev_f32_mut() : const_cast<float*>(params[i]->dev_f32());
-        s.grad = g ? g->dev_f32_mut() : nullptr;
+        s.grad = i < grads.size() ? grads[i] : nullptr;
         s.m = (m && (*m)[i]) ? (*m)[i]->dev_f32_mut() : nullptr;
         s.v = (v && (*v)[i]) ? (*v)[i]->dev_f32_mut() : nullptr;
         s.bias_corr1 = bc1 ? (*bc1)[i] : 1.0f;
         s.bias_corr2 = bc2 ? (*bc2)[i] : 1.0f;
-        if (g && g->numel() != s.n) throw std::runtime_error("optimizer: gradient size mismatch");
     }
     const size_t bytes = host.size() * sizeof(mft_tensor_slot);
     if (bytes > *dev_bytes) {
@@ -56,9 +54,10 @@ using optim_detail::SlotTable;
 namespace {
 void* g_clip_slots = nullptr;
 size_t g_clip_slots_bytes = 0;
-std::vector<TensorPtr> grads_of(const std::vector<TensorPtr>& params) {
-    std::vector<TensorPtr> g(params.size());
-    for (size_t i = 0; i < params.size(); ++i) g[i] = params[i] ? params[i]->grad() : nullptr;
+std::vector<float*> grads_of(const std::vector<TensorPtr>& params) {
+    std::vector<float*> g(params.size(), nullptr);
+    for (size_t i = 0; i < params.size(); ++i)
+        if (params[i] && params[i]->grad()) g[i] = params[i]->grad()->dev_f32_mut();
     return g;
 }
 }  // namespace
@@ -107,8 +106,19 @@ void Adam::step(const std::vector<TensorPtr>& parameters, const std::vector<Tens
     step_scaled(parameters, gradients, nullptr);
 }
 
-// optim/adam.cpp:25-90
 void Adam::step_scaled(const std::vector<TensorPtr>& parameters, const std::vector<TensorPtr>& gradients, const float* dev_grad_scale) {
+    if (parameters.size() != gradients.size()) throw std::runtime_error("Parameters and gradients size mismatch");
+    std::vector<float*> ptrs(gradients.size(), nullptr);
+    for (size_t i = 0; i < gradients.size(); ++i) {
+        if (!gradients[i]) continue;
+        if (gradients[i]->numel() != parameters[i]->numel()) throw std::runtime_error("optimizer: gradient size mismatch");
+        ptrs[i] = gradients[i]->dev_f32_mut();
+    }
+    step_device(parameters, ptrs, dev_grad_scale);
+}
+
+// optim/adam.cpp:25-90
+void Adam::step_device(const std::vector<TensorPtr>& parameters, const std::vector<float*>& gradients, const float* dev_grad_scale) {
     if (parameters.size() != gradients.size()) throw std::runtime_error("Parameters and gradients size mismatch");
     if (adam_config_.amsgrad) throw std::runtime_error("Adam: amsgrad is not implemented on the B200 path");
     std::vector<TensorPtr> m(parameters.size()), v(parameters.size());

@@ -1,0 +1,352 @@
+// mft_trainer_* — the training step of the reference's trainers behind a C ABI (include/mft_trainer.h).
+// Loop body mirrored: gpt2_lora_finetune/main.cpp:561-601 (forward, lm_cross_entropy, backward, global clip with
+// scale = max/(norm+1e-6), Adam, drop grads); Gemma: optim/gemma_trainer.cpp:104-149.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "adam.h"
+#include "autograd_engine.h"
+#include "gemma_lora_injector.h"
+#include "gemma_model.h"
+#include "gpt2_model.h"
+#include "lm_loss.h"
+#include "lora_injector.h"
+#include "mft_b200.h"
+#include "mft_trainer.h"
+#include "ops.h"
+#include "runtime.h"
+
+using namespace ops;
+
+namespace {
+thread_local char g_terr[1024] = "";
+int fail(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_terr, sizeof(g_terr), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+}  // namespace
+
+struct mft_trainer {
+    mft_trainer_config cfg;
+    std::unique_ptr<GPT2Model> gpt2;
+    std::unique_ptr<GemmaModel> gemma;
+    LoraInjector gpt2_inj;
+    GemmaLoraInjector gemma_inj;
+    std::vector<TensorPtr> trainable;
+    std::unique_ptr<Adam> opt;
+    std::mt19937 gen;
+    TensorPtr ids;                 // persistent [B,S] int32 device buffer (labels = ids)
+    float* loss_dev = nullptr;     // persistent scalars
+    float* norm_dev = nullptr;
+    float* scale_dev = nullptr;
+    void* slots_dev = nullptr;
+    size_t slots_bytes = 0;
+    float* bucket = nullptr;
+    int64_t bucket_elems = 0, grad_elems = 0;
+    std::vector<int64_t> offsets;
+    std::vector<TensorPtr> grads;  // of the last backward (arena memory, valid until the next step)
+    int with_grad = 0;
+    int64_t launches = 0;
+    bool arena_on = false;
+    // CUDA graph of one whole step (forward .. Adam), captured after warm-up
+    cudaGraphExec_t graph_exec = nullptr;
+    int eager_steps = 0;
+};
+
+namespace {
+
+void fill_normal(const TensorPtr& t, std::mt19937& g, float stdv) {
+    std::normal_distribution<float> d(0.0f, stdv);
+    float* p = t->data<float>();
+    for (int64_t i = 0; i < t->numel(); ++i) p[i] = d(g);
+    (void)t->dev();   // upload now (persistent scope still active)
+}
+void fill_const(const TensorPtr& t, float v) {
+    float* p = t->data<float>();
+    for (int64_t i = 0; i < t->numel(); ++i) p[i] = v;
+    (void)t->dev();
+}
+
+void build(mft_trainer* t) {
+    const mft_trainer_config& c = t->cfg;
+    mft_rt::PersistentScope keep;   // everything created here outlives the step arena
+    t->gen.seed(c.seed);
+    if (c.model == 0) {
+        GPT2Config g;
+        g.n_layer = c.n_layer; g.n_embd = c.n_embd; g.n_head = c.n_head; g.vocab_size = c.vocab_size; g.n_positions = c.n_positions;
+        t->gpt2 = std::make_unique<GPT2Model>(g);
+        t->gpt2->tie_weights();
+        auto ps = t->gpt2->parameters();
+        for (size_t i = 0; i < ps.size(); ++i) {   // same protocol as oracle/harness/train_synth.cpp
+            bool gamma = false;
+            if (i >= 2 && i < ps.size() - 2) { size_t k = (i - 2) % 12; gamma = (k == 0 || k == 6); }
+            if (i == ps.size() - 2) gamma = true;
+            if (gamma) fill_const(ps[i], 1.0f); else fill_normal(ps[i], t->gen, 0.02f);
+        }
+        t->gpt2->init_lora_modules();
+        if (!c.full_finetune) {
+            LoraSpec s;
+            s.rank = c.lora_rank; s.alpha = c.lora_alpha; s.dropout = 0.0f; s.split_qkv = false;
+            s.targets = {LoraTarget::AttnQKV, LoraTarget::AttnProj};
+            if (c.lora_mlp) s.targets = {LoraTarget::AttnQKV, LoraTarget::AttnProj, LoraTarget::MlpFcIn, LoraTarget::MlpFcOut};
+            t->gpt2_inj.inject(*t->gpt2, s);
+            t->trainable = t->gpt2->get_lora_parameters();
+            for (auto& p : t->gpt2->parameters()) p->set_requires_grad(false);
+            for (auto& p : t->trainable) { p->set_requires_grad(true); (void)p->dev(); }
+        } else {
+            t->trainable = t->gpt2->parameters();
+            for (auto& p : t->trainable) p->set_requires_grad(true);
+        }
+    } else {
+        GemmaTextConfig g;
+        g.num_hidden_layers = c.n_layer; g.hidden_size = c.n_embd; g.intermediate_size = c.intermediate;
+        g.num_attention_heads = c.n_head; g.num_key_value_heads = c.kv_heads; g.head_dim = c.head_dim;
+        g.vocab_size = c.vocab_size; g.sliding_window = c.sliding_window > 0 ? c.sliding_window : 512;
+        g.layer_types.clear();
+        for (int i = 0; i < g.num_hidden_layers; ++i) g.layer_types.push_back(((i + 1) % 6 == 0) ? "full_attention" : "sliding_attention");
+        t->gemma = std::make_unique<GemmaModel>(g);
+        auto mk = [&](std::vector<int64_t> shape) {
+            auto w = std::make_shared<Tensor>(shape, kFloat32, kCPU);
+            fill_normal(w, t->gen, 0.02f);
+            return w;
+        };
+        const int64_t C = g.hidden_size, I = g.intermediate_size, Hd = g.head_dim;
+        const int64_t QD = g.num_attention_heads * Hd, KD = g.num_key_value_heads * Hd;
+        t->gemma->assign_weight("embed_tokens.weight", mk({g.vocab_size, C}));
+        t->gemma->assign_weight("norm.weight", mk({C}));
+        for (int l = 0; l < g.num_hidden_layers; ++l) {
+            const std::string p = "layers." + std::to_string(l) + ".";
+            t->gemma->assign_weight(p + "input_layernorm.weight", mk({C}));
+            t->gemma->assign_weight(p + "post_attention_layernorm.weight", mk({C}));
+            t->gemma->assign_weight(p + "pre_feedforward_layernorm.weight", mk({C}));
+            t->gemma->assign_weight(p + "post_feedforward_layernorm.weight", mk({C}));
+            t->gemma->assign_weight(p + "self_attn.q_proj.weight", mk({C, QD}));
+            t->gemma->assign_weight(p + "self_attn.k_proj.weight", mk({C, KD}));
+            t->gemma->assign_weight(p + "self_attn.v_proj.weight", mk({C, KD}));
+            t->gemma->assign_weight(p + "self_attn.o_proj.weight", mk({QD, C}));
+            t->gemma->assign_weight(p + "self_attn.q_norm.weight", mk({Hd}));
+            t->gemma->assign_weight(p + "self_attn.k_norm.weight", mk({Hd}));
+            t->gemma->assign_weight(p + "mlp.gate_proj.weight", mk({C, I}));
+            t->gemma->assign_weight(p + "mlp.up_proj.weight", mk({C, I}));
+            t->gemma->assign_weight(p + "mlp.down_proj.weight", mk({I, C}));
+        }
+        t->gemma->init_lora_modules();
+        GemmaLoraSpec s = GemmaLoraSpec::full_attn_mlp();
+        s.rank = c.lora_rank; s.alpha = c.lora_alpha; s.dropout = 0.0f;
+        t->gemma_inj.inject(*t->gemma, s);
+        t->trainable = t->gemma_inj.get_trainable_params();
+        for (auto& p : t->trainable) (void)p->dev();
+    }
+    AdamConfig oc(c.lr, c.beta1, c.beta2, c.eps, c.weight_decay, c.clip_norm, false);
+    t->opt = std::make_unique<Adam>(oc);
+    t->ids = std::make_shared<Tensor>(std::vector<int64_t>{c.batch, c.seq_len}, kInt32, kCPU);
+    float* scalars = static_cast<float*>(mft_rt::dev_alloc(64));
+    mft_rt::memset0(scalars, 64);
+    t->loss_dev = scalars; t->norm_dev = scalars + 1; t->scale_dev = scalars + 2;
+    t->offsets.resize(t->trainable.size());
+    int64_t off = 0;
+    for (size_t i = 0; i < t->trainable.size(); ++i) { t->offsets[i] = off; off += (t->trainable[i]->numel() + 3) / 4 * 4; }
+    t->grad_elems = off;
+}
+
+void forward_backward(mft_trainer* t) {
+    if (t->arena_on) mft_rt::arena_reset();
+    TensorPtr logits = t->cfg.model == 0 ? t->gpt2->forward(t->ids, nullptr) : t->gemma->forward(t->ids, nullptr);
+    TensorPtr loss = lm_cross_entropy(logits, t->ids, -100, "mean");
+    mft_rt::d2d(t->loss_dev, loss->dev(), sizeof(float));
+    loss->backward();
+    t->grads.assign(t->trainable.size(), nullptr);
+    t->with_grad = 0;
+    for (size_t i = 0; i < t->trainable.size(); ++i) {
+        t->grads[i] = t->trainable[i]->grad();
+        if (t->grads[i]) ++t->with_grad;
+    }
+}
+
+// Slot table for clip + Adam; when a bucket is set the gradients are first packed into it (and read from it).
+void update(mft_trainer* t, bool pack_only, bool packed) {
+    const size_t n = t->trainable.size();
+    std::vector<mft_tensor_slot> host(n);
+    // Adam bookkeeping goes through the optimizer so per-tensor step counts behave like optim/adam.cpp:35-43
+    if (pack_only) {
+        for (size_t i = 0; i < n; ++i) {
+            std::memset(&host[i], 0, sizeof(mft_tensor_slot));
+            host[i].n = t->trainable[i]->numel();
+            host[i].grad = t->grads[i] ? t->grads[i]->dev_f32_mut() : nullptr;
+            host[i].bucket_offset = t->offsets[i];
+        }
+        const size_t bytes = n * sizeof(mft_tensor_slot);
+        if (bytes > t->slots_bytes) {
+            mft_rt::PersistentScope keep;
+            if (t->slots_dev) mft_rt::dev_free(t->slots_dev, t->slots_bytes);
+            t->slots_bytes = bytes * 2;
+            t->slots_dev = mft_rt::dev_alloc(t->slots_bytes);
+        }
+        mft_rt::h2d(t->slots_dev, host.data(), bytes);
+        mft_rt::check(mft_pack_grads(static_cast<const mft_tensor_slot*>(t->slots_dev), int32_t(n), t->bucket, mft_rt::stream()), "mft_pack_grads");
+        return;
+    }
+    // global norm over the tensors that have gradients, on the device
+    std::vector<TensorPtr> params = t->trainable;
+    for (size_t i = 0; i < n; ++i) {
+        std::memset(&host[i], 0, sizeof(mft_tensor_slot));
+        host[i].n = params[i]->numel();
+        if (t->grads[i]) host[i].grad = packed ? t->bucket + t->offsets[i] : t->grads[i]->dev_f32_mut();
+    }
+    const size_t bytes = n * sizeof(mft_tensor_slot);
+    if (bytes > t->slots_bytes) {
+        mft_rt::PersistentScope keep;
+        if (t->slots_dev) mft_rt::dev_free(t->slots_dev, t->slots_bytes);
+        t->slots_bytes = bytes * 2;
+        t->slots_dev = mft_rt::dev_alloc(t->slots_bytes);
+    }
+    mft_rt::h2d(t->slots_dev, host.data(), bytes);
+    static double* sumsq = nullptr;
+    if (!sumsq) { mft_rt::PersistentScope keep; sumsq = static_cast<double*>(mft_rt::dev_alloc(64)); }
+    const size_t wsb = mft_grad_sumsq_workspace_bytes();
+    mft_rt::check(mft_grad_sumsq(static_cast<const mft_tensor_slot*>(t->slots_dev), int32_t(n), sumsq, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_grad_sumsq");
+    const float pre = packed && t->cfg.world_size > 1 ? 1.0f / float(t->cfg.world_size) : 1.0f;
+    mft_rt::check(mft_clip_scale(sumsq, t->cfg.clip_norm, pre, t->scale_dev, t->norm_dev, mft_rt::stream()), "mft_clip_scale");
+    // Adam with the clip factor read on the device (per-tensor step counts advance only for tensors with a gradient)
+    std::vector<float*> gp(n, nullptr);
+    for (size_t i = 0; i < n; ++i) gp[i] = host[i].grad;
+    t->opt->step_device(params, gp, t->scale_dev);
+    for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
+}
+
+}  // namespace
+
+extern "C" const char* mft_trainer_last_error(void) { return g_terr; }
+
+extern "C" int mft_trainer_create(const mft_trainer_config* cfg, mft_trainer** out) {
+    if (!cfg || !out) return fail("mft_trainer_create: null argument");
+    if (cfg->batch <= 0 || cfg->seq_len <= 0 || cfg->n_layer <= 0) return fail("mft_trainer_create: bad shape");
+    try {
+        auto t = std::make_unique<mft_trainer>();
+        t->cfg = *cfg;
+        if (t->cfg.world_size < 1) t->cfg.world_size = 1;
+        (void)mft_rt::stream();
+        build(t.get());
+        const size_t mb = cfg->arena_mb > 0 ? size_t(cfg->arena_mb) : size_t(24) * 1024;
+        mft_rt::arena_enable(mb << 20);
+        t->arena_on = true;
+        mft_rt::sync();
+        *out = t.release();
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_create: %s", e.what()); }
+}
+
+extern "C" void mft_trainer_destroy(mft_trainer* t) {
+    if (!t) return;
+    try { mft_rt::sync(); } catch (...) {}
+    if (t->graph_exec) cudaGraphExecDestroy(t->graph_exec);
+    delete t;
+}
+
+extern "C" int mft_trainer_next_synthetic_batch(mft_trainer* t, int32_t* host_ids) {
+    if (!t || !host_ids) return fail("mft_trainer_next_synthetic_batch: null argument");
+    std::uniform_int_distribution<int> d(0, t->cfg.vocab_size - 1);
+    const int64_t n = int64_t(t->cfg.batch) * t->cfg.seq_len;
+    for (int64_t i = 0; i < n; ++i) host_ids[i] = d(t->gen);
+    return 0;
+}
+
+static int run_step(mft_trainer* t) {
+    const int64_t before = mft_launch_count();
+    forward_backward(t);
+    update(t, false, false);
+    t->launches = mft_launch_count() - before;
+    ++t->eager_steps;
+    return 0;
+}
+
+extern "C" int mft_trainer_step_device(mft_trainer* t, const int32_t* dev_ids) {
+    if (!t || !dev_ids) return fail("mft_trainer_step_device: null argument");
+    try {
+        const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
+        mft_rt::d2d(t->ids->dev_out(), dev_ids, bytes);
+        return run_step(t);
+    } catch (const std::exception& e) { return fail("mft_trainer_step_device: %s", e.what()); }
+}
+
+extern "C" int mft_trainer_step(mft_trainer* t, const int32_t* host_ids, float* host_loss) {
+    if (!t || !host_ids || !host_loss) return fail("mft_trainer_step: null argument");
+    try {
+        const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
+        mft_rt::h2d(t->ids->dev_out(), host_ids, bytes);
+        run_step(t);
+        mft_rt::d2h(host_loss, t->loss_dev, sizeof(float));   // synchronises
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_step: %s", e.what()); }
+}
+
+extern "C" int64_t mft_trainer_grad_elems(mft_trainer* t) { return t ? t->grad_elems : 0; }
+
+extern "C" int mft_trainer_set_grad_bucket(mft_trainer* t, float* dev_bucket, int64_t elems) {
+    if (!t || !dev_bucket) return fail("mft_trainer_set_grad_bucket: null argument");
+    if (elems < t->grad_elems) return fail("mft_trainer_set_grad_bucket: bucket too small (%lld < %lld)", (long long)elems, (long long)t->grad_elems);
+    t->bucket = dev_bucket;
+    t->bucket_elems = elems;
+    return 0;
+}
+
+extern "C" int mft_trainer_forward_backward(mft_trainer* t, const int32_t* dev_ids) {
+    if (!t || !dev_ids) return fail("mft_trainer_forward_backward: null argument");
+    if (!t->bucket) return fail("mft_trainer_forward_backward: set a gradient bucket first");
+    try {
+        const int64_t before = mft_launch_count();
+        const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
+        mft_rt::d2d(t->ids->dev_out(), dev_ids, bytes);
+        forward_backward(t);
+        update(t, true, false);
+        t->launches = mft_launch_count() - before;
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_forward_backward: %s", e.what()); }
+}
+
+extern "C" int mft_trainer_update(mft_trainer* t) {
+    if (!t) return fail("mft_trainer_update: null argument");
+    try {
+        const int64_t before = mft_launch_count();
+        update(t, false, true);
+        t->launches += mft_launch_count() - before;
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_update: %s", e.what()); }
+}
+
+extern "C" const float* mft_trainer_loss_ptr(mft_trainer* t) { return t ? t->loss_dev : nullptr; }
+extern "C" const float* mft_trainer_grad_norm_ptr(mft_trainer* t) { return t ? t->norm_dev : nullptr; }
+extern "C" void* mft_trainer_stream(mft_trainer*) { return mft_rt::stream(); }
+extern "C" int mft_trainer_sync(mft_trainer*) {
+    try { mft_rt::sync(); return 0; } catch (const std::exception& e) { return fail("mft_trainer_sync: %s", e.what()); }
+}
+extern "C" void mft_trainer_set_lr(mft_trainer* t, float lr) { if (t && t->opt) t->opt->set_learning_rate(lr); }
+extern "C" int32_t mft_trainer_num_trainable(mft_trainer* t) { return t ? int32_t(t->trainable.size()) : 0; }
+extern "C" int32_t mft_trainer_num_with_grad(mft_trainer* t) { return t ? t->with_grad : 0; }
+extern "C" int64_t mft_trainer_kernel_launches(mft_trainer* t) { return t ? t->launches : 0; }
+extern "C" size_t mft_trainer_arena_high_water(mft_trainer*) { return mft_rt::arena_high_water(); }
+
+extern "C" int mft_trainer_param_checksum(mft_trainer* t, int32_t index, double* sum, double* sumabs, int64_t* n) {
+    if (!t || index < 0 || index >= int32_t(t->trainable.size())) return fail("mft_trainer_param_checksum: bad index");
+    try {
+        const TensorPtr& p = t->trainable[index];
+        const float* d = static_cast<const Tensor&>(*p).data<float>();
+        double s = 0, sa = 0;
+        for (int64_t i = 0; i < p->numel(); ++i) { s += d[i]; sa += std::fabs(d[i]); }
+        if (sum) *sum = s;
+        if (sumabs) *sumabs = sa;
+        if (n) *n = p->numel();
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_param_checksum: %s", e.what()); }
+}

@@ -12,9 +12,13 @@ int set_error(int code, const char* fmt, ...);
 
 inline cudaStream_t as_stream(mft_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
-// Post-launch check used by every entry point.
+// Kernel-launch accounting (mft_launch_count): every entry point reports how many kernels it enqueued.
+void add_launches(int n);
+
+// Post-launch check used by every entry point (counts one kernel; multi-kernel entry points add the rest).
 #define MFT_CHECK_LAUNCH(name)                                                             \
     do {                                                                                   \
+        ::mft::add_launches(1);                                                            \
         cudaError_t _e = cudaGetLastError();                                               \
         if (_e != cudaSuccess) return ::mft::set_error(2, "%s: %s", name, cudaGetErrorString(_e)); \
     } while (0)

@@ -8,6 +8,8 @@
 namespace mft {
 
 static thread_local char g_err[512] = "";
+static long long g_launches = 0;
+void add_launches(int n) { g_launches += n; }
 // MFT_USE_TENSOR_CORES=0 in the environment starts the library on the exact fp32 SIMT GEMM (parity debugging).
 static bool env_use_tc() {
     const char* e = getenv("MFT_USE_TENSOR_CORES");
@@ -48,6 +50,7 @@ static int to_params(const mft_gemm_args* a, GemmParams& p) {
 using namespace mft;
 
 extern "C" int mft_version(void) { return 100; }
+extern "C" int64_t mft_launch_count(void) { return g_launches; }
 extern "C" const char* mft_last_error(void) { return g_err; }
 
 extern "C" int mft_device_check(void) {
@@ -80,4 +83,12 @@ extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
     if (p.m == 0 || p.n == 0) return 0;
     if (g_use_tc && gemm_tc_eligible(p)) return launch_gemm_tc(p, as_stream(stream));
     return launch_gemm_simt(p, as_stream(stream));
+}
+
+extern "C" int mft_gemm_profile(int enable) { gemm_tc_profile_enable(enable != 0); return 0; }
+extern "C" int mft_gemm_profile_read(double* flops, double* ms, int64_t* launches) {
+    long long n = 0;
+    gemm_tc_profile_read(flops, ms, &n);
+    if (launches) *launches = n;
+    return 0;
 }

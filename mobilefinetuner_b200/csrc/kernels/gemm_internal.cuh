@@ -19,5 +19,7 @@ struct GemmParams {
 int launch_gemm_simt(const GemmParams& p, cudaStream_t st);
 bool gemm_tc_eligible(const GemmParams& p);
 int launch_gemm_tc(const GemmParams& p, cudaStream_t st);
+void gemm_tc_profile_enable(bool on);
+void gemm_tc_profile_read(double* flops, double* ms, long long* launches);
 
 }  // namespace mft

@@ -88,6 +88,7 @@ int launch_gemm_simt(const GemmParams& p, cudaStream_t st) {
     dim3 grid(unsigned(ceil_div(p.n, SBN)), unsigned(ceil_div(p.m, SBM)), unsigned(p.batch));
     if (grid.y > 65535 || grid.z > 65535) return set_error(1, "mft_gemm(simt): grid too large");
     gemm_simt_kernel<<<grid, 256, 0, st>>>(p);
+    add_launches(1);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(2, "mft_gemm(simt): %s", cudaGetErrorString(e));
     return 0;

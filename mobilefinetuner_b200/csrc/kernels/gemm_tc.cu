@@ -11,6 +11,7 @@
 #include <cuda.h>
 #include <mutex>
 #include <unordered_map>
+#include <vector>
 #include "common.cuh"
 #include "gemm_internal.cuh"
 
@@ -349,6 +350,43 @@ bool gemm_tc_eligible(const GemmParams& p) {
     return true;
 }
 
+// Optional in-library timing of every tcgen05 GEMM launch (CUDA events on the launching stream): feeds the
+// roofline figure bench.py reports (sum of algorithmic FLOPs / sum of launch durations over profiled steps).
+namespace {
+struct TcProfile {
+    bool on = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pool;
+    std::vector<double> flops;
+    size_t used = 0;
+    double total_flops = 0, total_ms = 0;
+    long long launches = 0;
+} g_prof;
+void prof_drain() {
+    for (size_t i = 0; i < g_prof.used; ++i) {
+        cudaEventSynchronize(g_prof.pool[i].second);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_prof.pool[i].first, g_prof.pool[i].second) == cudaSuccess) {
+            g_prof.total_ms += ms;
+            g_prof.total_flops += g_prof.flops[i];
+            ++g_prof.launches;
+        }
+    }
+    g_prof.used = 0;
+}
+}  // namespace
+
+void gemm_tc_profile_enable(bool on) {
+    if (!on && g_prof.on) prof_drain();
+    if (on) { g_prof.total_flops = g_prof.total_ms = 0; g_prof.launches = 0; g_prof.used = 0; }
+    g_prof.on = on;
+}
+void gemm_tc_profile_read(double* flops, double* ms, long long* launches) {
+    prof_drain();
+    if (flops) *flops = g_prof.total_flops;
+    if (ms) *ms = g_prof.total_ms;
+    if (launches) *launches = g_prof.launches;
+}
+
 template <int BN>
 static int launch_tc(const GemmParams& p, cudaStream_t st) {
     using Cfg = TcCfg<BN>;
@@ -375,7 +413,24 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     }
     int64_t tiles = int64_t(a.tiles_m) * a.tiles_n * a.batch;
     int grid = int(tiles < kNumSMs ? tiles : kNumSMs);
+    size_t slot = 0;
+    if (g_prof.on) {
+        if (g_prof.used == g_prof.pool.size()) {
+            if (g_prof.pool.size() >= 8192) prof_drain();
+            else {
+                cudaEvent_t e0, e1;
+                cudaEventCreate(&e0); cudaEventCreate(&e1);
+                g_prof.pool.emplace_back(e0, e1);
+                g_prof.flops.push_back(0.0);
+            }
+        }
+        slot = g_prof.used++;
+        g_prof.flops[slot] = 2.0 * double(p.m) * double(p.n) * double(p.k + p.k2) * double(p.batch);
+        cudaEventRecord(g_prof.pool[slot].first, st);
+    }
     gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::smem_bytes, st>>>(ma, mb, ma2, mb2, a);
+    if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
+    add_launches(1);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): %s", cudaGetErrorString(e));
     return 0;

@@ -184,6 +184,7 @@ extern "C" int mft_colsum(const float* g, int64_t ldg, float* out, int64_t rows,
     float* partial = static_cast<float*>(workspace);
     colsum_partial_kernel<<<dim3(unsigned(ceil_div(n, 32)), unsigned(slabs)), dim3(32, 8), 0, as_stream(stream)>>>(g, ldg, partial, rows, n);
     colsum_final_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, as_stream(stream)>>>(partial, out, slabs, n);
+    add_launches(1);
     MFT_CHECK_LAUNCH("mft_colsum");
     return 0;
 }

@@ -163,6 +163,7 @@ extern "C" int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* lab
         lm_ce_fwd_kernel<<<grid, kCeThreads, 0, st>>>(logits, ld, labels, rows, S, V, ignore_index, row_lse, row_nll);
     }
     lm_ce_reduce_kernel<<<1, 1024, 0, st>>>(row_nll, labels, rows, S, V, ignore_index, reduction, loss_out, valid_out);
+    add_launches(1);
     MFT_CHECK_LAUNCH("mft_lm_ce_fwd");
     return 0;
 }

@@ -410,6 +410,7 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
         layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
     }
     norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dgamma, dbeta, parts, int(dim), 2);
+    add_launches(1);
     MFT_CHECK_LAUNCH("mft_layernorm_bwd");
     return 0;
 }
@@ -443,6 +444,7 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
     rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
         x, w, gy, gx, partial, rows, int(dim), eps, plus_one);
     norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
+    add_launches(1);
     MFT_CHECK_LAUNCH("mft_rmsnorm_bwd");
     return 0;
 }

@@ -117,6 +117,29 @@ adam_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float lr, 
 
 using namespace mft;
 
+namespace mft {
+// bucket[offset + i] = grad[i] (0 where a tensor has no gradient): one launch packs every gradient for the all-reduce
+__global__ void __launch_bounds__(kOptThreads)
+pack_grads_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float* __restrict__ bucket) {
+    const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
+    const int64_t stride = int64_t(gridDim.x) * kOptThreads;
+    for (int s = 0; s < num_slots; ++s) {
+        const float* g = slots[s].grad;
+        float* dst = bucket + slots[s].bucket_offset;
+        const int64_t n = slots[s].n;
+        for (int64_t i = tid; i < n; i += stride) dst[i] = g ? g[i] : 0.f;
+    }
+}
+}  // namespace mft
+
+extern "C" int mft_pack_grads(const mft_tensor_slot* slots, int32_t num_slots, float* bucket, mft_stream_t stream) {
+    if (num_slots == 0) return 0;
+    if (!slots || !bucket) return mft::set_error(1, "mft_pack_grads: null pointer");
+    mft::pack_grads_kernel<<<mft::kOptCtas, mft::kOptThreads, 0, mft::as_stream(stream)>>>(slots, num_slots, bucket);
+    MFT_CHECK_LAUNCH("mft_pack_grads");
+    return 0;
+}
+
 extern "C" size_t mft_grad_sumsq_workspace_bytes(void) { return size_t(kOptCtas) * sizeof(double); }
 
 extern "C" int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, double* out, void* workspace,
@@ -129,6 +152,7 @@ extern "C" int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, d
     double* partial = static_cast<double*>(workspace);
     grad_sumsq_kernel<<<kOptCtas, kOptThreads, 0, st>>>(slots, num_slots, partial);
     sumsq_final_kernel<<<1, 1024, 0, st>>>(partial, kOptCtas, out);
+    add_launches(1);
     MFT_CHECK_LAUNCH("mft_grad_sumsq");
     return 0;
 }
