@@ -114,6 +114,20 @@ size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim);
 int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
                       float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
                       size_t workspace_bytes, mft_stream_t stream);
+/* LayerNorm backward for callers that cannot allocate device memory. It has no counterpart in the reference.
+ * Who needs it: a front end over this ABI (cgo, JNI, ctypes) that merely forwards tensors owned by its host
+ * application has no device allocator to take workspace from, and a steady-state loop may ban cudaMalloc because
+ * it stalls the whole device. Same arguments and results as mft_layernorm_bwd minus the workspace: the partial
+ * sums go to an array built into the library (MFT_LN_BWD_STATIC_SCRATCH_BYTES, resident on every GPU that loads the
+ * library until the process exits). Limit: mft_norm_bwd_workspace_bytes(rows, dim) must not exceed that size
+ * (e.g. dim <= 2048 with rows <= 18944, dim <= 1024 with rows <= 37888); larger problems are rejected with an error
+ * and must use mft_layernorm_bwd. Nothing is allocated or freed by this call. The first call on each device also
+ * looks up the array's device address, so make that first call before starting any stream capture. All calls share
+ * the one array (its previous contents are simply overwritten, nothing needs clearing), so two calls that may run at
+ * the same time on the GPU - different streams, or different host threads - race on it: serialise them. */
+#define MFT_LN_BWD_STATIC_SCRATCH_BYTES 4849664
+int mft_layernorm_bwd_static(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
+                             float* dbeta, int64_t rows, int64_t dim, float eps, mft_stream_t stream);
 /* RMSNorm with (1+w) scale, double-precision row statistics: y = x * rsqrt(mean(x^2)+eps) * (1+w)
  * (ops::rms_norm core/ops.cpp:1489-1537, RMSNormBackward core/backward_functions.cpp:483-523).
  * plus_one = 0 gives rms_norm_affine (y = x_hat * w). */

@@ -464,3 +464,39 @@ extern "C" int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64
     MFT_CHECK_LAUNCH("mft_softmax_bwd");
     return 0;
 }
+
+// ---------------------------------------------------------------- LayerNorm backward without caller scratch
+// Some users of this library cannot hand us workspace: a cgo/JNI/ctypes front end that only forwards the tensors
+// its host application gave it owns no device allocator, and a steady-state training loop may forbid cudaMalloc
+// because it synchronises the whole device. For them the column-reduction partials live in this fixed array, which
+// every GPU that loads the library keeps resident until the process exits.
+#define MFT_LN_BWD_STATIC_FLOATS (size_t(mft::kNormMaxCtas) * 2 * 2048)      /* 1,212,416 floats = 4,849,664 bytes */
+static __device__ __align__(256) float g_ln_bwd_static_scratch[MFT_LN_BWD_STATIC_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_ln_bwd_static_ptr[kMaxDevices] = {nullptr};   // device address of the array, resolved once per device
+}  // namespace
+
+extern "C" int mft_layernorm_bwd_static(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
+                                        float* dbeta, int64_t rows, int64_t dim, float eps, mft_stream_t stream) {
+    const size_t need = mft_norm_bwd_workspace_bytes(rows, dim);
+    const size_t have = MFT_LN_BWD_STATIC_FLOATS * sizeof(float);
+    if (need > have)
+        return set_error(1, "mft_layernorm_bwd_static: rows=%lld dim=%lld needs %zu bytes of scratch, the built-in array holds %zu; "
+                            "use mft_layernorm_bwd with caller-provided workspace", (long long)rows, (long long)dim, need, have);
+    int dev = 0;
+    MFT_CUDA_OK(cudaGetDevice(&dev), "mft_layernorm_bwd_static");
+    if (dev < 0 || dev >= kMaxDevices) return set_error(1, "mft_layernorm_bwd_static: device index %d out of range", dev);
+    if (!g_ln_bwd_static_ptr[dev]) {
+        // In host code the array's name is only a handle; the address kernels can dereference comes from the runtime,
+        // separately on each device (done here on first use with that device current).
+        float* p = nullptr;
+        MFT_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_ln_bwd_static_scratch), "mft_layernorm_bwd_static(cudaGetSymbolAddress)");
+        if (!p) return set_error(2, "mft_layernorm_bwd_static: cudaGetSymbolAddress returned a null address");
+        g_ln_bwd_static_ptr[dev] = p;
+    }
+    // The partial sums are fully rewritten by the first stage on every call, so stale contents from earlier calls are
+    // harmless and nothing has to be cleared.
+    return mft_layernorm_bwd(x, gamma, gy, gx, dgamma, dbeta, rows, dim, eps, g_ln_bwd_static_ptr[dev], have, stream);
+}
