@@ -58,6 +58,12 @@ typedef struct mft_gemm_args {
     int32_t batch; int64_t stride_a, stride_b, stride_c;
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
+/* Split-K form for products with a tiny output and a long contraction (LoRA's dA = x^T d(xA) and dB = (xA)^T dY, where the
+ * contraction runs over all tokens): the fp32 SIMT kernel computes `splits` partial products over disjoint K ranges into
+ * `workspace` (mft_gemm_splitk_workspace_bytes) and a second kernel sums them in a fixed order and applies alpha/bias/beta
+ * (deterministic). Same operation as mft_gemm otherwise; k2 must be 0 when splits > 1. */
+size_t mft_gemm_splitk_workspace_bytes(int32_t m, int32_t n, int32_t batch, int32_t splits);
+int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* workspace, size_t workspace_bytes, mft_stream_t stream);
 /* 1 if mft_gemm would take the tcgen05 path for these arguments (host-side predicate, no launch). */
 int mft_gemm_uses_tensor_cores(const mft_gemm_args* args);
 /* Measurement aid (no reference counterpart): while enabled, every tensor-core GEMM launch is bracketed by CUDA events on
@@ -107,7 +113,8 @@ int mft_mul_bwd(const float* a, const float* b, const float* gy, float* ga, floa
  * accumulation. Forward: ops::layer_norm core/ops.cpp:1404-1458. Backward recomputes mu/rstd and
  * always produces dx, dgamma, dbeta: LayerNormBackward core/backward_functions.cpp:425-481.
  * The backward needs mft_norm_bwd_workspace_bytes(rows, dim) bytes of scratch for the column
- * reductions (dgamma/dbeta partial sums); dgamma/dbeta are overwritten, not accumulated. */
+ * reductions (dgamma/dbeta partial sums); dgamma/dbeta are overwritten, not accumulated. dgamma and dbeta may both be
+ * NULL (frozen LayerNorm parameters, LoRA runs): only dx is produced and no workspace is needed. */
 int mft_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, int64_t rows,
                       int64_t dim, float eps, mft_stream_t stream);
 size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim);
@@ -148,6 +155,10 @@ int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64_t rows, in
  * fused [B,S,3C] qkv buffer directly (replacing the zeros+memcpy split and the two permutes of
  * graph/gpt2_model.cpp:616-664) and writes ctx as [B,S,H*Hd] (replacing :739-740).
  * window > 0 additionally masks i-j >= window (Gemma sliding layers, graph/gemma_model.cpp:272-285). */
+/* Precision of both attention products: 0 (default) = TF32 operands like the tcgen05 GEMMs (relative error ~1e-3);
+ * 1 = 3xTF32 split, fp32-accurate (used by the exact-mode parity tests; also selected by MFT_USE_TENSOR_CORES=0).
+ * Returns the previous setting. */
+int mft_attention_precise(int enable);
 int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
                              int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
                              int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,

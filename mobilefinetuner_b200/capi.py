@@ -48,6 +48,8 @@ SIGNATURES = {
     "mft_device_check": (C.c_int, []),
     "mft_use_tensor_cores": (C.c_int, [C.c_int]),
     "mft_gemm": (C.c_int, [C.POINTER(GemmArgs), vp]),
+    "mft_gemm_splitk_workspace_bytes": (sz, [i32, i32, i32, i32]),
+    "mft_gemm_splitk": (C.c_int, [C.POINTER(GemmArgs), i32, vp, sz, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),
     "mft_gemm_profile": (C.c_int, [C.c_int]),
     "mft_gemm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]),
@@ -72,6 +74,7 @@ SIGNATURES = {
     "mft_rmsnorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, C.c_int, vp, sz, vp]),
     "mft_softmax_fwd": (C.c_int, [vp, vp, i64, i64, vp]),
     "mft_softmax_bwd": (C.c_int, [vp, vp, vp, i64, i64, vp]),
+    "mft_attention_precise": (C.c_int, [C.c_int]),
     "mft_causal_attention_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
                                            i64, i64, i64, f32, i32, vp]),
     "mft_rope": (C.c_int, [vp, vp, i64, i64, i64, f32, C.c_int, vp]),

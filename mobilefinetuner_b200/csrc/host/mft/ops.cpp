@@ -44,7 +44,10 @@ void require_f32(const TensorPtr& t, const char* op) {
 void run_gemm(GemmCall g) {
     if (g.m == 0 || g.n == 0) return;
     const int64_t work = int64_t(g.m) * g.n * std::max<int64_t>(g.k, 1) * std::max(g.batch, 1);
-    const bool big = work >= (int64_t(1) << 24) && g.m >= 64 && g.n >= 16 && g.k >= 32;
+    // A skinny output whose large operand would have to be transposed (contraction over the token index: LoRA dA/dB) is
+    // cheaper as a split-K SIMT product reading that operand once than as transpose + tensor-core GEMM.
+    const bool skinny_tn = g.trans_a && std::min(g.m, g.n) < 64;
+    const bool big = !skinny_tn && work >= (int64_t(1) << 24) && g.m >= 64 && g.n >= 16 && g.k >= 32;
     TensorPtr tmp_a, tmp_b;   // keep K-major temporaries alive until the launch is enqueued
     if (big && g.batch <= 1) {
         if (g.trans_a) {       // stored [k,m] -> [m,k]
@@ -72,6 +75,18 @@ void run_gemm(GemmCall g) {
     a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
     a.k2 = int32_t(g.k2); a.a2 = g.a2; a.lda2 = g.lda2; a.b2 = g.b2; a.ldb2 = g.ldb2;
     a.batch = std::max(g.batch, 1); a.stride_a = g.stride_a; a.stride_b = g.stride_b; a.stride_c = g.stride_c;
+    // few output tiles + long contraction on the SIMT path: split K so the whole chip works on it
+    if (!big && g.k2 == 0 && g.k >= 1024) {
+        const int64_t tiles = ((g.m + 63) / 64) * ((g.n + 63) / 64) * a.batch;
+        if (tiles < 74) {
+            int splits = int(std::min<int64_t>(std::min<int64_t>(296 / tiles, g.k / 256), 65535 / a.batch));
+            if (splits > 1) {
+                const size_t wsb = mft_gemm_splitk_workspace_bytes(a.m, a.n, a.batch, splits);
+                mft_rt::check(mft_gemm_splitk(&a, splits, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_gemm_splitk");
+                return;
+            }
+        }
+    }
     mft_rt::check(mft_gemm(&a, mft_rt::stream()), "mft_gemm");
 }
 

@@ -88,19 +88,24 @@ TensorPtr swiglu(const TensorPtr& gate, const TensorPtr& up) { return mul(silu(g
 namespace {
 class LayerNormBackward : public BackwardFunction {  // core/backward_functions.cpp:425-481
 public:
-    LayerNormBackward(TensorPtr x, TensorPtr w, float eps) : x_(std::move(x)), w_(std::move(w)), eps_(eps) {}
+    LayerNormBackward(TensorPtr x, TensorPtr w, TensorPtr b, float eps) : x_(std::move(x)), w_(std::move(w)), b_(std::move(b)), eps_(eps) {}
     std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
         TensorPtr gy = contiguous(gy_in);
         const int64_t dim = x_->shape().back(), rows = x_->numel() / dim;
         auto gx = new_like(x_);
-        auto gw = Tensor::make(w_->shape(), kFloat32), gb = Tensor::make(w_->shape(), kFloat32);
-        size_t wsb = mft_norm_bwd_workspace_bytes(rows, dim);
-        mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), gw->dev_f32_out(),
-                                        gb->dev_f32_out(), rows, dim, eps_, mft_rt::workspace(wsb), wsb, st()), "mft_layernorm_bwd");
+        // the reference always computes dgamma/dbeta (core/backward_functions.cpp:443-470); nobody reads them when both
+        // parameters are frozen (LoRA), so the column reductions are skipped then
+        const bool wg = wants_grad(w_) || wants_grad(b_);
+        TensorPtr gw, gb;
+        if (wg) { gw = Tensor::make(w_->shape(), kFloat32); gb = Tensor::make(w_->shape(), kFloat32); }
+        size_t wsb = wg ? mft_norm_bwd_workspace_bytes(rows, dim) : 0;
+        mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr,
+                                        wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()),
+                      "mft_layernorm_bwd");
         return {gx, gw, gb};
     }
 private:
-    TensorPtr x_, w_;
+    TensorPtr x_, w_, b_;
     float eps_;
 };
 class RmsNormBackward : public BackwardFunction {    // core/backward_functions.cpp:483-523
@@ -132,7 +137,7 @@ TensorPtr layer_norm(const TensorPtr& x_in, const TensorPtr& weight, const Tenso
     if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
     auto y = new_like(x);
     mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), y->dev_f32_out(), rows, dim, eps, st()), "mft_layernorm_fwd");
-    track(y, {x_in, weight, bias}, std::make_shared<LayerNormBackward>(x, weight, eps));
+    track(y, {x_in, weight, bias}, std::make_shared<LayerNormBackward>(x, weight, bias, eps));
     return y;
 }
 

@@ -6,6 +6,7 @@
 // (the reference is fp32; attention is <5% of the step's FLOPs so the 3x cost is immaterial).
 // No S x S matrix is ever written to HBM. q/k/v are read with arbitrary (batch, seq, head) strides,
 // so the fused [B,S,3C] qkv projection output is consumed in place and ctx is written as [B,S,C].
+#include <cstdlib>
 #include "common.cuh"
 
 namespace mft {
@@ -38,7 +39,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
-template <int HD>
+// PRECISE = true : 3xTF32 split (hi/lo) on both products, fp32-accurate (exact mode / parity tests).
+// PRECISE = false: plain TF32 operands (same input precision as the tcgen05 GEMMs), 3x fewer MMAs.
+template <int HD, bool PRECISE>
 __global__ void __launch_bounds__(128)
 causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                             float* __restrict__ ctx, int H, int S,
@@ -62,7 +65,7 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
     const float* vb = v + b * ksb + h * ksh;
 
     // Q fragments (A operand, rows g / g+8 of this warp's 16-row slab), pre-scaled, split hi/lo.
-    uint32_t qhi[KS][4], qlo[KS][4];
+    uint32_t qhi[KS][4], qlo[PRECISE ? KS : 1][4];
     {
         const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
 #pragma unroll
@@ -71,8 +74,12 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
             float a1 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t] * scale : 0.f;
             float a2 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t + 4] * scale : 0.f;
             float a3 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t + 4] * scale : 0.f;
-            split_tf32(a0, qhi[s][0], qlo[s][0]); split_tf32(a1, qhi[s][1], qlo[s][1]);
-            split_tf32(a2, qhi[s][2], qlo[s][2]); split_tf32(a3, qhi[s][3], qlo[s][3]);
+            if (PRECISE) {
+                split_tf32(a0, qhi[s][0], qlo[s][0]); split_tf32(a1, qhi[s][1], qlo[s][1]);
+                split_tf32(a2, qhi[s][2], qlo[s][2]); split_tf32(a3, qhi[s][3], qlo[s][3]);
+            } else {
+                qhi[s][0] = f2tf32(a0); qhi[s][1] = f2tf32(a1); qhi[s][2] = f2tf32(a2); qhi[s][3] = f2tf32(a3);
+            }
         }
     }
 
@@ -119,11 +126,15 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
             for (int s = 0; s < KS; ++s) {
                 float k0 = tk[(n * 8 + g) * LD + s * 8 + t];
                 float k1 = tk[(n * 8 + g) * LD + s * 8 + t + 4];
-                uint32_t bh0, bl0, bh1, bl1;
-                split_tf32(k0, bh0, bl0); split_tf32(k1, bh1, bl1);
-                mma_tf32(sc[n], qlo[s], bh0, bh1);
-                mma_tf32(sc[n], qhi[s], bl0, bl1);
-                mma_tf32(sc[n], qhi[s], bh0, bh1);
+                if (PRECISE) {
+                    uint32_t bh0, bl0, bh1, bl1;
+                    split_tf32(k0, bh0, bl0); split_tf32(k1, bh1, bl1);
+                    mma_tf32(sc[n], qlo[s], bh0, bh1);
+                    mma_tf32(sc[n], qhi[s], bl0, bl1);
+                    mma_tf32(sc[n], qhi[s], bh0, bh1);
+                } else {
+                    mma_tf32(sc[n], qhi[s], f2tf32(k0), f2tf32(k1));
+                }
             }
         }
         // ---- masks (causal / window / sequence tail) + online softmax
@@ -170,19 +181,27 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
 #pragma unroll
         for (int s = 0; s < 8; ++s) {           // 8 key-slabs of 8 keys
             uint32_t phi[4], plo[4];
-            split_tf32(sc[s][0], phi[0], plo[0]);   // (row g,   key 2t)   -> a0
-            split_tf32(sc[s][2], phi[1], plo[1]);   // (row g+8, key 2t)   -> a1
-            split_tf32(sc[s][1], phi[2], plo[2]);   // (row g,   key 2t+1) -> a2
-            split_tf32(sc[s][3], phi[3], plo[3]);   // (row g+8, key 2t+1) -> a3
+            if (PRECISE) {
+                split_tf32(sc[s][0], phi[0], plo[0]);   // (row g,   key 2t)   -> a0
+                split_tf32(sc[s][2], phi[1], plo[1]);   // (row g+8, key 2t)   -> a1
+                split_tf32(sc[s][1], phi[2], plo[2]);   // (row g,   key 2t+1) -> a2
+                split_tf32(sc[s][3], phi[3], plo[3]);   // (row g+8, key 2t+1) -> a3
+            } else {
+                phi[0] = f2tf32(sc[s][0]); phi[1] = f2tf32(sc[s][2]); phi[2] = f2tf32(sc[s][1]); phi[3] = f2tf32(sc[s][3]);
+            }
 #pragma unroll
             for (int n = 0; n < NT; ++n) {
                 float v0 = tv[(s * 8 + 2 * t) * LD + n * 8 + g];
                 float v1 = tv[(s * 8 + 2 * t + 1) * LD + n * 8 + g];
-                uint32_t bh0, bl0, bh1, bl1;
-                split_tf32(v0, bh0, bl0); split_tf32(v1, bh1, bl1);
-                mma_tf32(o[n], plo, bh0, bh1);
-                mma_tf32(o[n], phi, bl0, bl1);
-                mma_tf32(o[n], phi, bh0, bh1);
+                if (PRECISE) {
+                    uint32_t bh0, bl0, bh1, bl1;
+                    split_tf32(v0, bh0, bl0); split_tf32(v1, bh1, bl1);
+                    mma_tf32(o[n], plo, bh0, bh1);
+                    mma_tf32(o[n], phi, bl0, bl1);
+                    mma_tf32(o[n], phi, bh0, bh1);
+                } else {
+                    mma_tf32(o[n], phi, f2tf32(v0), f2tf32(v1));
+                }
             }
         }
         __syncthreads();   // everyone done with this buffer before it is refilled
@@ -200,25 +219,37 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
     }
 }
 
-template <int HD>
+template <int HD, bool PRECISE>
 static int launch_attention(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
                             int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                             int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
     constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(causal_attention_fwd_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        cudaFuncSetAttribute(causal_attention_fwd_kernel<HD, PRECISE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         attr_set = true;
     }
     dim3 grid(unsigned(ceil_div(S, kAttBQ)), unsigned(B * H));
-    causal_attention_fwd_kernel<HD><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
+    causal_attention_fwd_kernel<HD, PRECISE><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
                                                              osh, scale, window);
     return 0;
 }
 
+static bool env_attention_precise() {
+    const char* e = getenv("MFT_USE_TENSOR_CORES");
+    return e && e[0] == '0';        // exact mode: everything at fp32 accuracy
+}
+static bool g_attention_precise = env_attention_precise();
+
 }  // namespace mft
 
 using namespace mft;
+
+extern "C" int mft_attention_precise(int enable) {
+    int prev = g_attention_precise ? 1 : 0;
+    g_attention_precise = enable != 0;
+    return prev;
+}
 
 extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
                                         int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
@@ -233,8 +264,10 @@ extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const fl
     if ((reinterpret_cast<uintptr_t>(ctx) & 7u) || (o_stride_b % 2) || (o_stride_s % 2) || (o_stride_h % 2))
         return set_error(1, "mft_causal_attention_fwd: ctx must be 8-byte aligned with even strides");
     cudaStream_t st = as_stream(stream);
-#define MFT_ATT(HD_) launch_attention<HD_>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
-                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st)
+#define MFT_ATT(HD_) (g_attention_precise ? launch_attention<HD_, true>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
+                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st) \
+                                          : launch_attention<HD_, false>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
+                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st))
     switch (Hd) {
         case 16: MFT_ATT(16); break;
         case 32: MFT_ATT(32); break;

@@ -76,6 +76,28 @@ extern "C" int mft_gemm_uses_tensor_cores(const mft_gemm_args* args) {
     return (g_use_tc && gemm_tc_eligible(p)) ? 1 : 0;
 }
 
+extern "C" size_t mft_gemm_splitk_workspace_bytes(int32_t m, int32_t n, int32_t batch, int32_t splits) {
+    if (splits <= 1) return 0;
+    return size_t(m) * size_t(n) * size_t(batch < 1 ? 1 : batch) * size_t(splits) * sizeof(float);
+}
+
+extern "C" int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* workspace, size_t workspace_bytes, mft_stream_t stream) {
+    GemmParams p;
+    int rc = to_params(args, p);
+    if (rc) return rc;
+    if (p.m == 0 || p.n == 0) return 0;
+    if (splits < 1) return set_error(1, "mft_gemm_splitk: splits must be >= 1");
+    if (splits > 1) {
+        if (p.k2 > 0) return set_error(1, "mft_gemm_splitk: a second K segment cannot be split");
+        const size_t need = mft_gemm_splitk_workspace_bytes(p.m, p.n, p.batch, splits);
+        if (!workspace || workspace_bytes < need) return set_error(1, "mft_gemm_splitk: workspace too small (%zu < %zu)", workspace_bytes, need);
+        if (int64_t(p.batch) * splits > 65535) return set_error(1, "mft_gemm_splitk: batch*splits too large");
+        p.ksplit = splits;
+        p.partial = static_cast<float*>(workspace);
+    }
+    return launch_gemm_simt(p, as_stream(stream));
+}
+
 extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
     GemmParams p;
     int rc = to_params(args, p);

@@ -14,6 +14,8 @@ struct GemmParams {
     float* gelu_out;
     int k2; const float* a2; int64_t lda2; const float* b2; int64_t ldb2;
     int batch; int64_t stride_a, stride_b, stride_c;
+    int ksplit = 1;            // SIMT split-K: number of K slices (partials reduced in a fixed order)
+    float* partial = nullptr;  // [batch][ksplit][m][n] scratch when ksplit > 1
 };
 
 int launch_gemm_simt(const GemmParams& p, cudaStream_t st);

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(256)
 gemm_simt_kernel(GemmParams p) {
     __shared__ float As[SBK][SBM + 4];
     __shared__ float Bs[SBK][SBN + 4];
-    const int bz = blockIdx.z;
+    const int bz = blockIdx.z / p.ksplit, ks = blockIdx.z % p.ksplit;
     const float* A = p.a + bz * p.stride_a;
     const float* B = p.b + bz * p.stride_b;
     float* C = p.c + bz * p.stride_c;
@@ -49,7 +49,14 @@ gemm_simt_kernel(GemmParams p) {
         const int64_t lda = seg == 0 ? p.lda : p.lda2, ldb = seg == 0 ? p.ldb : p.ldb2;
         const bool a_ck = seg == 0 ? (p.trans_a == 0) : true;
         const bool b_ck = seg == 0 ? (p.trans_b != 0) : true;
-        for (int k0 = 0; k0 < K; k0 += SBK) {
+        // split-K: this CTA owns k-blocks [kb0, kb1) of segment 1 (segment 2 is never split)
+        int k_begin = 0, k_end = K;
+        if (p.ksplit > 1) {
+            const int kblocks = (K + SBK - 1) / SBK, per = (kblocks + p.ksplit - 1) / p.ksplit;
+            k_begin = ks * per * SBK;
+            k_end = min(K, (ks + 1) * per * SBK);
+        }
+        for (int k0 = k_begin; k0 < k_end; k0 += SBK) {
             load_tile(As, a, lda, a_ck, m0, k0, p.m, K);
             load_tile(Bs, b, ldb, b_ck, n0, k0, p.n, K);
             __syncthreads();
@@ -65,6 +72,20 @@ gemm_simt_kernel(GemmParams p) {
             }
             __syncthreads();
         }
+    }
+    if (p.ksplit > 1) {   // raw partial sums; alpha/bias/beta are applied by the reduction kernel
+        float* P = p.partial + (size_t(bz) * p.ksplit + ks) * size_t(p.m) * p.n;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int gm = m0 + ty * 4 + i;
+            if (gm >= p.m) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                int gn = n0 + tx * 4 + j;
+                if (gn < p.n) P[size_t(gm) * p.n + gn] = acc[i][j];
+            }
+        }
+        return;
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -84,11 +105,35 @@ gemm_simt_kernel(GemmParams p) {
     }
 }
 
+// Fixed-order reduction of the split-K partials + epilogue (deterministic, unlike atomics).
+__global__ void gemm_splitk_reduce_kernel(GemmParams p) {
+    const int64_t total = int64_t(p.batch) * p.m * p.n;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total; idx += int64_t(gridDim.x) * blockDim.x) {
+        const int gn = int(idx % p.n);
+        const int64_t t = idx / p.n;
+        const int gm = int(t % p.m);
+        const int bz = int(t / p.m);
+        const float* P = p.partial + size_t(bz) * p.ksplit * size_t(p.m) * p.n + size_t(gm) * p.n + gn;
+        float s = 0.f;
+        for (int k = 0; k < p.ksplit; ++k) s += P[size_t(k) * p.m * p.n];
+        float v = s * p.alpha;
+        if (p.bias) v += p.bias[gn];
+        const int64_t off = bz * p.stride_c + int64_t(gm) * p.ldc + gn;
+        if (p.beta != 0.f) v += p.beta * p.c[off];
+        p.c[off] = v;
+        if (p.gelu_out) p.gelu_out[off] = gelu_tanh_f(v);
+    }
+}
+
 int launch_gemm_simt(const GemmParams& p, cudaStream_t st) {
-    dim3 grid(unsigned(ceil_div(p.n, SBN)), unsigned(ceil_div(p.m, SBM)), unsigned(p.batch));
+    dim3 grid(unsigned(ceil_div(p.n, SBN)), unsigned(ceil_div(p.m, SBM)), unsigned(p.batch * p.ksplit));
     if (grid.y > 65535 || grid.z > 65535) return set_error(1, "mft_gemm(simt): grid too large");
     gemm_simt_kernel<<<grid, 256, 0, st>>>(p);
     add_launches(1);
+    if (p.ksplit > 1) {
+        gemm_splitk_reduce_kernel<<<stream_grid(int64_t(p.batch) * p.m * p.n, 256), 256, 0, st>>>(p);
+        add_launches(1);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(2, "mft_gemm(simt): %s", cudaGetErrorString(e));
     return 0;

@@ -22,12 +22,14 @@ constexpr int TBK = 32;           // fp32 elements per k-block = one 128-byte sw
 constexpr int TUK = 8;            // UMMA K for tf32 (32 bytes)
 constexpr int kTcThreads = 192;
 constexpr int kSmemBudget = 200 * 1024;
+constexpr int kEpiPitch = 36;     // floats per staged row: 16-byte aligned and conflict-free for both access patterns
 
 template <int BN> struct TcCfg {
     static constexpr int stage_bytes = (TBM + BN) * TBK * 4;
     static constexpr int stages = (kSmemBudget / stage_bytes) > 8 ? 8 : (kSmemBudget / stage_bytes);
     static constexpr int tmem_cols = 2 * BN;             // two accumulator buffers
-    static constexpr int smem_bytes = stages * stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int epi_bytes = 4 * 32 * kEpiPitch * 4;  // per-warp 32x32 transpose buffers (coalesced stores)
+    static constexpr int smem_bytes = stages * stage_bytes + epi_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -113,7 +115,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     constexpr int NS = Cfg::stages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + NS * Cfg::stage_bytes);
+    float* epi_stage = reinterpret_cast<float*>(tiles + NS * Cfg::stage_bytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + NS * Cfg::stage_bytes + Cfg::epi_bytes);
     uint64_t* full = bars;                 // [NS]
     uint64_t* empty = bars + NS;           // [NS]
     uint64_t* tmem_full = bars + 2 * NS;   // [2]
@@ -197,11 +200,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
         }
     } else {
-        // ===================== epilogue warps (TMEM -> regs -> HBM) =====================
+        // ===================== epilogue warps (TMEM -> regs -> smem transpose -> HBM) =====================
+        // tcgen05.ld hands each thread one accumulator ROW; storing that directly would hit 32 different 128-byte lines
+        // per warp instruction. Each 32x32 chunk is therefore bounced through a per-warp smem buffer so that a warp
+        // instruction writes 4 full 128-byte row segments (8 lanes x float4 per row).
         const int lg = warp & 3;                          // TMEM lane group this warp may touch
+        float* stg = epi_stage + lg * 32 * kEpiPitch;
+        const int r4 = lane >> 3, c4 = lane & 7;          // read-back role: row within a group of 4, float4 column
         const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15u) == 0) &&
                             ((p.stride_c & 3) == 0) &&
-                            (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0);
+                            (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0) &&
+                            (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int mt = tile % p.tiles_m;
@@ -211,48 +220,60 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const uint32_t aphase = (it >> 1) & 1;
             mbar_wait(&tmem_full[as], aphase);
             tc_fence_after();
-            const int row = mt * TBM + lg * 32 + lane;
+            const int row_base = mt * TBM + lg * 32;
             const int n0 = nt * BN;
-            float* crow = p.c + int64_t(bz) * p.stride_c + int64_t(row) * p.ldc;
-            float* grow = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c + int64_t(row) * p.ldc : nullptr;
+            float* cbase = p.c + int64_t(bz) * p.stride_c;
+            float* gbase = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c : nullptr;
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.n) break;               // warp-uniform
                 float v[32];
                 tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
-                if (row < p.m) {
-                    const int ncol = n0 + c0;
-                    if (vec_ok && ncol + 32 <= p.n) {
+                float4* srow = reinterpret_cast<float4*>(stg + lane * kEpiPitch);
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            float4 o = make_float4(v[j] * p.alpha, v[j + 1] * p.alpha, v[j + 2] * p.alpha, v[j + 3] * p.alpha);
-                            if (p.bias) {
-                                float4 bb = __ldg(reinterpret_cast<const float4*>(p.bias + ncol + j));
-                                o.x += bb.x; o.y += bb.y; o.z += bb.z; o.w += bb.w;
-                            }
+                for (int j = 0; j < 8; ++j) srow[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                __syncwarp();
+                const int col = n0 + c0 + c4 * 4;
+                if (vec_ok && col + 4 <= p.n) {
+                    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (p.bias) bb = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const int r = q * 4 + r4;
+                        const int grow = row_base + r;
+                        if (grow < p.m) {
+                            float4 a = *reinterpret_cast<const float4*>(stg + r * kEpiPitch + c4 * 4);
+                            float4 o = make_float4(a.x * p.alpha + bb.x, a.y * p.alpha + bb.y, a.z * p.alpha + bb.z, a.w * p.alpha + bb.w);
+                            float* dst = cbase + int64_t(grow) * p.ldc + col;
                             if (p.beta != 0.f) {
-                                float4 old = *reinterpret_cast<const float4*>(crow + ncol + j);
+                                float4 old = *reinterpret_cast<const float4*>(dst);
                                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
                             }
-                            *reinterpret_cast<float4*>(crow + ncol + j) = o;
-                            if (grow) {
-                                float4 ge = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
-                                *reinterpret_cast<float4*>(grow + ncol + j) = ge;
-                            }
+                            *reinterpret_cast<float4*>(dst) = o;
+                            if (gbase)
+                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) =
+                                    make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
                         }
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            if (ncol + j < p.n) {
-                                float o = v[j] * p.alpha;
-                                if (p.bias) o += __ldg(p.bias + ncol + j);
-                                if (p.beta != 0.f) o += p.beta * crow[ncol + j];
-                                crow[ncol + j] = o;
-                                if (grow) grow[ncol + j] = gelu_tanh_f(o);
-                            }
+                    }
+                } else {
+#pragma unroll 1
+                    for (int q = 0; q < 8; ++q) {
+                        const int r = q * 4 + r4;
+                        const int grow = row_base + r;
+                        if (grow >= p.m) continue;
+                        for (int e = 0; e < 4; ++e) {
+                            const int cc = col + e;
+                            if (cc >= p.n) break;
+                            float o = stg[r * kEpiPitch + c4 * 4 + e] * p.alpha;
+                            if (p.bias) o += __ldg(p.bias + cc);
+                            float* dst = cbase + int64_t(grow) * p.ldc + cc;
+                            if (p.beta != 0.f) o += p.beta * *dst;
+                            *dst = o;
+                            if (gbase) gbase[int64_t(grow) * p.ldc + cc] = gelu_tanh_f(o);
                         }
                     }
                 }
+                __syncwarp();                             // buffer is rewritten by the next chunk
             }
             tc_fence_before();
             __syncwarp();

@@ -75,7 +75,7 @@ __global__ void layernorm_fwd_generic(const float* __restrict__ x, const float* 
 
 // ---------------------------------------------------------------- LayerNorm backward
 // dx per row; per-CTA partial dgamma/dbeta -> partial[cta][2][dim]. Algorithmic bytes: 12*rows*dim.
-template <int NV>
+template <int NV, bool WG>
 __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ gy,
                      float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps) {
@@ -124,8 +124,10 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                 float a = g[j].x * gam[j].x, b = g[j].y * gam[j].y, cc = g[j].z * gam[j].z, d = g[j].w * gam[j].w;
                 s1 += a + b + cc + d;
                 s2 += a * v[j].x + b * v[j].y + cc * v[j].z + d * v[j].w;
-                dg[j].x += g[j].x * v[j].x; dg[j].y += g[j].y * v[j].y; dg[j].z += g[j].z * v[j].z; dg[j].w += g[j].w * v[j].w;
-                db[j].x += g[j].x; db[j].y += g[j].y; db[j].z += g[j].z; db[j].w += g[j].w;
+                if (WG) {
+                    dg[j].x += g[j].x * v[j].x; dg[j].y += g[j].y * v[j].y; dg[j].z += g[j].z * v[j].z; dg[j].w += g[j].w * v[j].w;
+                    db[j].x += g[j].x; db[j].y += g[j].y; db[j].z += g[j].z; db[j].w += g[j].w;
+                }
             }
         }
         s1 = warp_sum(s1);
@@ -145,6 +147,7 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
             }
         }
     }
+    if (!WG) return;   // frozen gamma/beta: only dx was wanted
     // CTA reduction of the per-warp column partials, then one row of `partial` per CTA.
     float4* sg = reinterpret_cast<float4*>(smem) + size_t(warp) * 2 * dim4;
 #pragma unroll
@@ -217,18 +220,29 @@ __global__ void layernorm_wgrad_generic(const float* __restrict__ x, const float
     }
 }
 
-// Second stage shared by LayerNorm (two outputs) and RMSNorm (one): fixed-order sum over CTAs.
-__global__ void norm_wgrad_final(const float* __restrict__ partial, float* __restrict__ out0, float* __restrict__ out1,
-                                 int parts, int dim, int per_part) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= dim) return;
+// Second stage shared by LayerNorm (two outputs) and RMSNorm (one): 32 columns x 8 row-groups per CTA, each thread sums
+// every 8th partial row, then the 8 groups are added in a fixed order (deterministic).
+__global__ void __launch_bounds__(256)
+norm_wgrad_final(const float* __restrict__ partial, float* __restrict__ out0, float* __restrict__ out1,
+                 int parts, int dim, int per_part) {
+    __shared__ float ra[8][33], rb[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
     float a = 0.f, b = 0.f;
-    for (int p = 0; p < parts; ++p) {
-        a += partial[size_t(p) * per_part * dim + c];
-        if (out1) b += partial[size_t(p) * per_part * dim + dim + c];
+    if (c < dim)
+        for (int p = ty; p < parts; p += 8) {
+            a += partial[size_t(p) * per_part * dim + c];
+            if (out1) b += partial[size_t(p) * per_part * dim + dim + c];
+        }
+    ra[ty][tx] = a; rb[ty][tx] = b;
+    __syncthreads();
+    if (ty == 0 && c < dim) {
+        float sa = 0.f, sb = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { sa += ra[j][tx]; sb += rb[j][tx]; }
+        out0[c] = sa;
+        if (out1) out1[c] = sb;
     }
-    out0[c] = a;
-    if (out1) out1[c] = b;
 }
 
 }  // namespace mft
@@ -339,13 +353,19 @@ static int launch_ln_fwd(const float* x, const float* g, const float* b, float* 
 template <int NV>
 static int launch_ln_bwd(const float* x, const float* g, const float* gy, float* gx, float* partial, int64_t rows,
                          int dim, float eps, int ctas, cudaStream_t st) {
+    if (!partial) {   // dx only
+        int blocks = int(ceil_div(rows, kNormWarps));
+        if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+        layernorm_bwd_kernel<NV, false><<<blocks, kNormWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps);
+        return 0;
+    }
     size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(layernorm_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
-    layernorm_bwd_kernel<NV><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps);
+    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps);
     return 0;
 }
 
@@ -386,13 +406,15 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
                                  float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
                                  size_t workspace_bytes, mft_stream_t stream) {
     if (dim == 0) return 0;
-    if (!x || !gamma || !gy || !gx || !dgamma || !dbeta) return set_error(1, "mft_layernorm_bwd: null pointer");
-    if (rows == 0) { mft_fill(dgamma, dim, 0.f, stream); return mft_fill(dbeta, dim, 0.f, stream); }
-    if (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim))
+    if (!x || !gamma || !gy || !gx) return set_error(1, "mft_layernorm_bwd: null pointer");
+    if ((dgamma == nullptr) != (dbeta == nullptr)) return set_error(1, "mft_layernorm_bwd: dgamma and dbeta must both be given or both be NULL");
+    const bool want_wgrad = dgamma != nullptr;
+    if (rows == 0) { if (want_wgrad) { mft_fill(dgamma, dim, 0.f, stream); return mft_fill(dbeta, dim, 0.f, stream); } return 0; }
+    if (want_wgrad && (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim)))
         return set_error(1, "mft_layernorm_bwd: workspace too small (%zu < %zu)", workspace_bytes,
                          mft_norm_bwd_workspace_bytes(rows, dim));
     cudaStream_t st = as_stream(stream);
-    float* partial = static_cast<float*>(workspace);
+    float* partial = want_wgrad ? static_cast<float*>(workspace) : nullptr;
     const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(gy) && aligned16(gx) && aligned16(gamma);
     int parts;
     if (vec) {
@@ -407,10 +429,12 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
     } else {
         layernorm_bwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, gy, gx, rows, int(dim), eps);
         parts = int(ceil_div(rows, 64));
-        layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
+        if (want_wgrad) layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
     }
-    norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dgamma, dbeta, parts, int(dim), 2);
-    add_launches(1);
+    if (want_wgrad) {
+        norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dgamma, dbeta, parts, int(dim), 2);
+        add_launches(1);
+    }
     MFT_CHECK_LAUNCH("mft_layernorm_bwd");
     return 0;
 }
@@ -443,7 +467,7 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
     float* partial = static_cast<float*>(workspace);
     rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
         x, w, gy, gx, partial, rows, int(dim), eps, plus_one);
-    norm_wgrad_final<<<unsigned(ceil_div(dim, 256)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
+    norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
     add_launches(1);
     MFT_CHECK_LAUNCH("mft_rmsnorm_bwd");
     return 0;

@@ -92,6 +92,29 @@ def test_gemm_golden_matmul_and_bmm(capi, golden_ops):
     assert rel(gb, L("bmm_gb").reshape(gb.shape)) < FP32_TOL
 
 
+@pytest.mark.parametrize("m,n,k,ta,splits", [(16, 1024, 4096, 1, 16), (1024, 16, 4096, 1, 16), (8, 768, 512, 1, 2),
+                                             (130, 70, 1000, 0, 7), (16, 1024, 4096, 1, 1)])
+def test_gemm_splitk_matches_reference(capi, m, n, k, ta, splits):
+    """Split-K SIMT product (LoRA dA / dB shapes: tiny output, contraction over all tokens); deterministic."""
+    rng = np.random.default_rng(m + n + k)
+    a = rng.standard_normal((k, m) if ta else (m, k)).astype(np.float32)
+    b = rng.standard_normal((k, n)).astype(np.float32)
+    bias = rng.standard_normal(n).astype(np.float32)
+    c0 = rng.standard_normal((m, n)).astype(np.float32)
+    da, db, dbias = dev(a), dev(b), dev(bias)
+    outs = []
+    for _ in range(2):
+        c = dev(c0)
+        args = capi.GemmArgs(m, n, k, da.data_ptr(), a.shape[1], ta, db.data_ptr(), n, 0, c.data_ptr(), n, 0.5, 2.0, dbias.data_ptr(),
+                             None, 0, None, 0, None, 0, 1, 0, 0, 0)
+        w = ws(capi.lib.mft_gemm_splitk_workspace_bytes(m, n, 1, splits))
+        capi.check(capi.lib.mft_gemm_splitk(C.byref(args), splits, w.data_ptr(), w.numel(), None), "mft_gemm_splitk")
+        torch.cuda.synchronize()
+        outs.append(c.clone())
+    assert torch.equal(outs[0], outs[1])                      # fixed-order reduction
+    assert rel(outs[0], ref_gemm(a, b, ta, 0, 0.5, 2.0, bias, c0)) < FP32_TOL
+
+
 # ----------------------------------------------------------------------------- tcgen05 TF32 path
 @pytest.mark.parametrize("m,n,k", [(128, 256, 32), (128, 64, 64), (512, 768, 768), (512, 2304, 768), (300, 200, 100),
                                    (2048, 3072, 768), (129, 257, 36), (4096, 1024, 4096), (64, 64, 4096)])
@@ -169,16 +192,38 @@ def run_attention(capi, q, k, v, scale, window=0):
     return ctx.cpu().numpy().reshape(B, S, H, Hd).transpose(0, 2, 1, 3)
 
 
-def test_attention_golden(capi, golden_ops):
+@pytest.fixture
+def precise_attention(capi):
+    prev = capi.lib.mft_attention_precise(1)
+    yield
+    capi.lib.mft_attention_precise(prev)
+
+
+def test_attention_golden(capi, golden_ops, precise_attention):
     L = golden_ops
     y = run_attention(capi, L("attn_q"), L("attn_k"), L("attn_v"), 0.25)
     assert rel(y, L("attn_y")) < FP32_TOL
 
 
+def test_attention_tf32_mode(capi, golden_ops):
+    """Default mode: TF32 operands (same input precision as the tensor-core GEMMs)."""
+    L = golden_ops
+    prev = capi.lib.mft_attention_precise(0)
+    try:
+        y = run_attention(capi, L("attn_q"), L("attn_k"), L("attn_v"), 0.25)
+        assert rel(y, L("attn_y")) < TF32_TOL
+        rng = np.random.default_rng(9)
+        q, k, v = (rng.standard_normal((2, 16, 512, 64)).astype(np.float32) for _ in range(3))
+        y = run_attention(capi, q, k, v, 0.125)
+        assert rel(y, O.causal_attention_fwd(q, k, v, 0.125)) < TF32_TOL
+    finally:
+        capi.lib.mft_attention_precise(prev)
+
+
 @pytest.mark.parametrize("B,H,S,Hd,window", [(4, 12, 128, 64, 0), (1, 2, 1, 64, 0), (2, 3, 200, 64, 0),
                                              (1, 4, 512, 64, 0), (2, 2, 130, 32, 0), (1, 2, 300, 64, 128),
                                              (1, 1, 96, 128, 0)])
-def test_attention_shapes(capi, B, H, S, Hd, window):
+def test_attention_shapes(capi, precise_attention, B, H, S, Hd, window):
     rng = np.random.default_rng(S + Hd)
     q, k, v = (rng.standard_normal((B, H, S, Hd)).astype(np.float32) for _ in range(3))
     y = run_attention(capi, q, k, v, 1.0 / np.sqrt(Hd), window)

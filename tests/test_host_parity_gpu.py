@@ -62,7 +62,7 @@ def check_traj(out, golden_file, loss_tol=1e-3, gnorm_tol=1e-3, sumabs_tol=1e-3)
 
 
 def test_per_op_forward_and_gradients_match_reference(tmp_path):
-    run_harness(["ops", "--dump", str(tmp_path), "--seed", "7"])
+    run_harness(["ops", "--dump", str(tmp_path), "--seed", "7"], tensor_cores=False)   # exact mode: fp32-accurate attention too
     ref_dir = os.path.join(GOLDEN, "ops")
     names = sorted(f for f in os.listdir(ref_dir) if f.endswith(".npy"))
     assert len(names) >= 90
@@ -80,16 +80,24 @@ def test_per_op_forward_and_gradients_match_reference(tmp_path):
     assert not bad, f"tensors outside 1e-5: {bad}"
 
 
-def test_gpt2_lora_tiny_50_steps():
+@pytest.mark.parametrize("tensor_cores", [False, True])
+def test_gpt2_lora_tiny_50_steps(tensor_cores):
     out = run_harness(["gpt2", "--steps", "50", "--layers", "2", "--embd", "64", "--heads", "4", "--vocab", "503",
-                       "--batch", "2", "--seq", "16", "--rank", "8", "--quiet", "1"])
-    assert check_traj(out, "gpt2_lora_tiny.txt") < 1e-4
+                       "--batch", "2", "--seq", "16", "--rank", "8", "--quiet", "1"], tensor_cores=tensor_cores)
+    if tensor_cores:   # TF32 attention operands (GEMMs this small stay on the fp32 kernel)
+        assert check_traj(out, "gpt2_lora_tiny.txt", loss_tol=1e-3, gnorm_tol=2e-2, sumabs_tol=5e-3) < 1e-3
+    else:
+        assert check_traj(out, "gpt2_lora_tiny.txt") < 1e-4
 
 
-def test_gpt2_full_finetune_tiny_50_steps():
+@pytest.mark.parametrize("tensor_cores", [False, True])
+def test_gpt2_full_finetune_tiny_50_steps(tensor_cores):
     out = run_harness(["gpt2", "--steps", "50", "--layers", "2", "--embd", "64", "--heads", "4", "--vocab", "503",
-                       "--batch", "2", "--seq", "16", "--mode", "full", "--quiet", "1"])
-    assert check_traj(out, "gpt2_full_tiny.txt") < 1e-4
+                       "--batch", "2", "--seq", "16", "--mode", "full", "--quiet", "1"], tensor_cores=tensor_cores)
+    if tensor_cores:
+        assert check_traj(out, "gpt2_full_tiny.txt", loss_tol=1e-3, gnorm_tol=2e-2, sumabs_tol=5e-3) < 1e-3
+    else:
+        assert check_traj(out, "gpt2_full_tiny.txt") < 1e-4
 
 
 @pytest.mark.parametrize("tensor_cores", [False, True])

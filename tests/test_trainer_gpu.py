@@ -17,6 +17,19 @@ TINY_GEMMA = dict(model=1, n_layer=6, n_embd=64, n_head=4, vocab_size=1009, n_po
                   head_dim=32, sliding_window=512)
 
 
+@pytest.fixture(autouse=True)
+def exact_mode(request):
+    """Tight comparisons run in exact mode (fp32 SIMT GEMM, 3xTF32 attention); tests marked tf32 use the default path."""
+    from mobilefinetuner_b200 import capi
+    if "tf32" in request.keywords:
+        yield
+        return
+    prev_tc, prev_at = capi.lib.mft_use_tensor_cores(0), capi.lib.mft_attention_precise(1)
+    yield
+    capi.lib.mft_use_tensor_cores(prev_tc)
+    capi.lib.mft_attention_precise(prev_at)
+
+
 def golden(name):
     text = open(os.path.join(GOLDEN, "traj", name)).read()
     steps = [(float(m[1]), float(m[2]), int(m[3]), int(m[4])) for m in
@@ -78,3 +91,17 @@ def test_split_step_with_bucket_equals_fused_step():
     for i in range(a.num_trainable):
         assert a.param_checksum(i) == b.param_checksum(i)
     a.close(); b.close()
+
+
+@pytest.mark.tf32
+def test_trainer_default_tf32_path_stays_within_loss_tolerance():
+    """Default execution mode (TF32 tensor-core GEMMs where eligible, TF32 attention operands): loss within 1e-3."""
+    from mobilefinetuner_b200.trainer import Trainer
+    tr = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, lora_alpha=16.0, arena_mb=256)
+    steps, _ = golden("gpt2_lora_tiny.txt")
+    for i, (ref_loss, ref_gnorm, with_grad, total) in enumerate(steps[:20]):
+        loss = tr.step_numpy(tr.next_synthetic_batch())
+        assert abs(loss - ref_loss) / ref_loss < 1e-3, (i, loss, ref_loss)
+        assert abs(tr.grad_norm() - ref_gnorm) <= 2e-2 * ref_gnorm
+        assert (tr.num_with_grad, tr.num_trainable) == (with_grad, total)
+    tr.close()
