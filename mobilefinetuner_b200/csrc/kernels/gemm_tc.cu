@@ -9,6 +9,8 @@
 // The optional second K-segment (A2 [m,k2], B2 [n,k2]) feeds extra k-blocks into the same accumulator:
 // this is how LoRA's rank-r update s*(xA)*B is fused with the base x*W product (nn/lora_linear.cpp:47-108).
 #include <cuda.h>
+#include <cstdlib>
+#include <cstring>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -24,8 +26,13 @@ constexpr int kTcThreads = 192;
 constexpr int kSmemBudget = 200 * 1024;
 constexpr int kEpiPitch = 36;     // floats per staged row: 16-byte aligned and conflict-free for both access patterns
 
-template <int BN> struct TcCfg {
-    static constexpr int stage_bytes = (TBM + BN) * TBK * 4;
+// CG = CTAs cooperating on one UMMA (cta_group). CG = 2: a cluster of two CTAs computes a 256 x BN tile pair — each CTA
+// stages its own 128 rows of A and HALF of the B tile, the leader issues tcgen05.mma.cta_group::2 (M = 256) which reads
+// both halves, and each CTA keeps its 128 x BN accumulator in its own TMEM. Halving the B traffic per SM is what lets
+// the tensor pipe run above ~50 % (single-CTA UMMA is bounded by shared-memory bandwidth).
+template <int BN, int CG = 1> struct TcCfg {
+    static constexpr int b_rows = BN / CG;                 // B rows staged by one CTA
+    static constexpr int stage_bytes = (TBM + b_rows) * TBK * 4;
     static constexpr int stages = (kSmemBudget / stage_bytes) > 8 ? 8 : (kSmemBudget / stage_bytes);
     static constexpr int tmem_cols = 2 * BN;             // two accumulator buffers
     static constexpr int epi_bytes = 4 * 32 * kEpiPitch * 4;  // per-warp 32x32 transpose buffers (coalesced stores)
@@ -59,6 +66,40 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+    // executed by both CTAs of the pair; the barrier address has the peer bit cleared so the bytes are credited to the
+    // leader CTA's barrier
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+    asm volatile(
+        "{\n\t.reg .b32 ra;\n\t"
+        "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}"
+        :: "r"(smem_u32(bar)), "r"(cta) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void tc_commit_2sm(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(smem_u32(bar)), "h"(uint16_t(3)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -107,11 +148,15 @@ struct TcArgs {
     int tiles_m, tiles_n;
 };
 
-template <int BN>
+template <int BN, int CG>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2, TcArgs p) {
-    using Cfg = TcCfg<BN>;
+    using Cfg = TcCfg<BN, CG>;
+    const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
+    const int unit = CG == 2 ? int(blockIdx.x >> 1) : int(blockIdx.x);        // CTA (or CTA pair) index
+    const int num_units = CG == 2 ? int(gridDim.x >> 1) : int(gridDim.x);
+    if (CG == 2) cluster_sync_all();                               // both CTAs alive before the paired TMEM allocation
     constexpr int NS = Cfg::stages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -124,23 +169,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(bars + 2 * NS + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_tiles = p.tiles_m * p.tiles_n * p.batch;
+    // tiles are counted in units of CG m-tiles: with CG = 2 a "tile" is a pair of adjacent 128-row tiles
+    const int tiles_mu = (p.tiles_m + CG - 1) / CG;
+    const int num_tiles = tiles_mu * p.tiles_n * p.batch;
     const int num_kb = p.kb1 + p.kb2;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
-        for (int i = 0; i < NS; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+        for (int i = 0; i < NS; ++i) { mbar_init(&full[i], CG); mbar_init(&empty[i], 1); }      // full: one arrival per CTA, at the leader
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4 * CG); }   // tmem_empty: leader only
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
-                     :: "r"(smem_u32(tmem_base_slot)), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (CG == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;"
+                         :: "r"(smem_u32(tmem_base_slot)), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                         :: "r"(smem_u32(tmem_base_slot)), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
 
@@ -148,21 +201,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         // ===================== TMA producer =====================
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int mt = tile % p.tiles_m;
-                const int nt = (tile / p.tiles_m) % p.tiles_n;
-                const int bz = tile / (p.tiles_m * p.tiles_n);
+            for (int tile = unit; tile < num_tiles; tile += num_units) {
+                const int mt = (tile % tiles_mu) * CG + int(cta_rank);          // this CTA's own 128-row tile
+                const int nt = (tile / tiles_mu) % p.tiles_n;
+                const int bz = tile / (tiles_mu * p.tiles_n);
+                const int brow = nt * BN + int(cta_rank) * Cfg::b_rows;         // this CTA's share of the B tile
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     uint8_t* sa = tiles + stage * Cfg::stage_bytes;
                     uint8_t* sb = sa + TBM * TBK * 4;
-                    mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes));
-                    if (kb < p.kb1) {
-                        tma_load_3d(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
-                        tma_load_3d(sb, &map_b, &full[stage], kb * TBK, nt * BN, bz);
+                    if (CG == 1) {
+                        mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes));
+                        if (kb < p.kb1) {
+                            tma_load_3d(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
+                            tma_load_3d(sb, &map_b, &full[stage], kb * TBK, brow, bz);
+                        } else {
+                            tma_load_3d(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
+                            tma_load_3d(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, brow, 0);
+                        }
                     } else {
-                        tma_load_3d(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
-                        tma_load_3d(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, nt * BN, 0);
+                        if (kb < p.kb1) {
+                            tma_load_3d_2sm(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
+                            tma_load_3d_2sm(sb, &map_b, &full[stage], kb * TBK, brow, bz);
+                        } else {
+                            tma_load_3d_2sm(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
+                            tma_load_3d_2sm(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, brow, 0);
+                        }
+                        // the leader's barrier collects both CTAs' bytes: it expects 2 x stage_bytes and one arrival per CTA
+                        if (cta_rank == 0) mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes) * 2u);
+                        else mbar_arrive_remote(&full[stage], 0);
                     }
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
@@ -170,12 +237,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
-            // instruction descriptor: D=f32, A=B=tf32, both K-major, N=BN, M=128
-            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t(TBM >> 4) << 24);
+        if (lane == 0 && cta_rank == 0) {
+            // instruction descriptor: D=f32, A=B=tf32, both K-major, N=BN, M=128 per CTA (256 across the pair)
+            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t((TBM * CG) >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             int it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(&tmem_empty[as], aphase ^ 1);
@@ -191,12 +258,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                     for (int k = 0; k < TBK / TUK; ++k) {
                         // advance 32 bytes (one UMMA K) inside the 128B swizzle span: +2 in 16-byte units
-                        tc_mma_tf32(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (CG == 2) tc_mma_tf32_2sm(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+                        else tc_mma_tf32(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    tc_commit(&empty[stage]);            // frees the smem slot when these MMAs retire
+                    // frees the smem slot (in both CTAs when paired) once these MMAs retire
+                    if (CG == 2) tc_commit_2sm(&empty[stage]); else tc_commit(&empty[stage]);
                     if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
-                tc_commit(&tmem_full[as]);               // accumulator ready for the epilogue
+                if (CG == 2) tc_commit_2sm(&tmem_full[as]); else tc_commit(&tmem_full[as]);   // accumulator(s) ready
+            }
+            if (CG == 2 && it > 0) {   // do not run ahead of the peer's last epilogue arrivals
+                const int last = it - 1;
+                mbar_wait(&tmem_empty[last & 1], (last >> 1) & 1);
             }
         }
     } else {
@@ -212,10 +285,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0) &&
                             (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
         int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int mt = tile % p.tiles_m;
-            const int nt = (tile / p.tiles_m) % p.tiles_n;
-            const int bz = tile / (p.tiles_m * p.tiles_n);
+        for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
+            const int mt = (tile % tiles_mu) * CG + int(cta_rank);
+            const int nt = (tile / tiles_mu) % p.tiles_n;
+            const int bz = tile / (tiles_mu * p.tiles_n);
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
             mbar_wait(&tmem_full[as], aphase);
@@ -277,15 +350,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty[as]);  // 4 arrivals (one per epilogue warp) free the buffer
+            if (lane == 0) {                              // one arrival per epilogue warp (of both CTAs when paired), at the leader
+                if (CG == 2) mbar_arrive_remote(&tmem_empty[as], 0); else mbar_arrive(&tmem_empty[as]);
+            }
         }
     }
 
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+        if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(Cfg::tmem_cols)) : "memory");
     }
 }
 
@@ -408,16 +484,16 @@ void gemm_tc_profile_read(double* flops, double* ms, long long* launches) {
     if (launches) *launches = g_prof.launches;
 }
 
-template <int BN>
+template <int BN, int CG>
 static int launch_tc(const GemmParams& p, cudaStream_t st) {
-    using Cfg = TcCfg<BN>;
+    using Cfg = TcCfg<BN, CG>;
     CUtensorMap ma, mb, ma2, mb2;
     if (!make_operand_map(&ma, p.a, p.k, p.m, p.batch, p.lda, p.stride_a, TBM) ||
-        !make_operand_map(&mb, p.b, p.k, p.n, p.batch, p.ldb, p.stride_b, BN))
+        !make_operand_map(&mb, p.b, p.k, p.n, p.batch, p.ldb, p.stride_b, Cfg::b_rows))
         return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed");
     if (p.k2 > 0) {
         if (!make_operand_map(&ma2, p.a2, p.k2, p.m, 1, p.lda2, 0, TBM) ||
-            !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, BN))
+            !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, Cfg::b_rows))
             return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (segment 2)");
     } else { ma2 = ma; mb2 = mb; }
     TcArgs a;
@@ -428,12 +504,13 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
         if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
-    int64_t tiles = int64_t(a.tiles_m) * a.tiles_n * a.batch;
-    int grid = int(tiles < kNumSMs ? tiles : kNumSMs);
+    const int64_t units = ceil_div(a.tiles_m, CG) * a.tiles_n * a.batch;    // CTAs, or CTA pairs
+    const int max_units = kNumSMs / CG;
+    const int grid = int(units < max_units ? units : max_units) * CG;
     size_t slot = 0;
     if (g_prof.on) {
         if (g_prof.used == g_prof.pool.size()) {
@@ -449,20 +526,44 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
         g_prof.flops[slot] = 2.0 * double(p.m) * double(p.n) * double(p.k + p.k2) * double(p.batch);
         cudaEventRecord(g_prof.pool[slot].first, st);
     }
-    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::smem_bytes, st>>>(ma, mb, ma2, mb2, a);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(unsigned(grid));
+    cfg.blockDim = dim3(kTcThreads);
+    cfg.dynamicSmemBytes = Cfg::smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG>, ma, mb, ma2, mb2, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);
-    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): %s", cudaGetErrorString(e));
     return 0;
 }
 
+static bool env_two_cta() {
+    const char* e = getenv("MFT_GEMM_2CTA");
+    return !(e && e[0] == '0');
+}
+
 int launch_gemm_tc(const GemmParams& p, cudaStream_t st) {
-    // Tile width: widest tile that still gives every SM work; narrow N uses narrow tiles.
-    const int64_t tm = ceil_div(p.m, TBM) * p.batch;
-    if (p.n <= 64 || tm * ceil_div(p.n, 128) < kNumSMs / 2) return launch_tc<64>(p, st);
-    if (p.n <= 128 || tm * ceil_div(p.n, 256) < kNumSMs) return launch_tc<128>(p, st);
-    return launch_tc<256>(p, st);
+    static const bool two_cta = env_two_cta();
+    const int64_t tiles_m = ceil_div(p.m, TBM);
+    const int64_t tm = tiles_m * p.batch;
+    // Paired CTAs (cta_group::2) whenever there are at least two row tiles to pair and the output is wide enough.
+    if (two_cta && tiles_m >= 2 && p.n > 64) {
+        const int64_t pairs = ceil_div(tiles_m, 2) * p.batch;
+        if (p.n <= 128 || pairs * ceil_div(p.n, 256) < kNumSMs / 4) return launch_tc<128, 2>(p, st);
+        return launch_tc<256, 2>(p, st);
+    }
+    // Single-CTA tiles: widest tile that still gives every SM work; narrow N uses narrow tiles.
+    if (p.n <= 64 || tm * ceil_div(p.n, 128) < kNumSMs / 2) return launch_tc<64, 1>(p, st);
+    if (p.n <= 128 || tm * ceil_div(p.n, 256) < kNumSMs) return launch_tc<128, 1>(p, st);
+    return launch_tc<256, 1>(p, st);
 }
 
 }  // namespace mft
