@@ -146,6 +146,8 @@ def main():
     ap.add_argument("--impl", default="mft", choices=["mft", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
+    ap.add_argument("--precision", default=os.environ.get("MFT_GEMM_PRECISION", "tf32"), choices=["tf32", "bf16"],
+                    help="operand precision of the large tensor-core GEMMs (fp32 accumulate either way)")
     a = ap.parse_args()
     if a.impl == "reference":
         return reference_arm(a)
@@ -165,7 +167,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     from mobilefinetuner_b200 import capi
-    from mobilefinetuner_b200.trainer import Trainer
+    from mobilefinetuner_b200.trainer import Trainer, hostlib
+    hostlib.mft_host_set_gemm_precision(1 if a.precision == "bf16" else 0)
 
     shape, batch, seq, full_ft, r, alpha, desc = CONFIGS[a.config]
     tr = Trainer(batch, seq, shape=shape, full_finetune=full_ft, lora_rank=r, lora_alpha=alpha, world_size=world, rank=rank,
@@ -259,12 +262,13 @@ def main():
     value = tokens_step * a.steps / (ms_total / 1e3)
     e2e_val = tokens_step * a.steps / (ms_e2e / 1e3)
     achieved_tf = (fl.value / 1e12) / (ms.value / 1e3) if ms.value > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05.mma kind::tf32, TMA-fed, fp32 accumulate in TMEM)",
+    kind = "kind::f16 bf16 operands" if a.precision == "bf16" else "kind::tf32"
+    roofline = {"bound": "tensor", "kernel": f"gemm_tc_kernel (tcgen05.mma cta_group::2 {kind}, TMA-fed, fp32 accumulate in TMEM)",
                 "achieved": round(achieved_tf, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": round(achieved_tf / peaks["tf_sustained"], 4), "traffic": None,
                 "launches_per_step": nl.value // max(a.profile_steps, 1), "gemm_ms_per_step": round(ms.value / max(a.profile_steps, 1), 3),
                 "step_ms_while_profiled": round(t_prof / max(a.profile_steps, 1), 3),
-                "peak_source": peaks["source"] + ", dense bf16 sustained; the kernel computes in TF32 whose hardware peak is half of bf16"}
+                "peak_source": peaks["source"] + ", dense bf16 sustained" + ("" if a.precision == "bf16" else "; the kernel computes in TF32 whose hardware peak is half of bf16")}
     cpu_baseline = None
     if not a.no_cpu_baseline and os.path.exists(REF_HARNESS):
         cores = os.cpu_count() or 1
@@ -278,7 +282,9 @@ def main():
             cpu_baseline = {"value": None, "unit": "tokens/s", "cores": cores, "kind": "reference", "sample": f"failed: {e}"}
     line = {"metric": "train_tokens_per_sec", "value": round(value, 1), "unit": "tokens/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": round(ms_total / a.steps, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32 (fp32 storage/accumulate; GEMM inputs rounded to TF32 in the TMA; norms/softmax/CE/Adam fp32)",
+            "vs_baseline": None,
+            "dtype": ("bf16 GEMM operands (fp32 master tensors and accumulate; attention TF32; norms/softmax/CE/Adam fp32)" if a.precision == "bf16" else
+                      "tf32 (fp32 storage/accumulate; GEMM inputs rounded to TF32 in the TMA; norms/softmax/CE/Adam fp32)"),
             "data": "synthetic",
             "config": {"workload": desc, "config_id": a.config, "tokens_per_step_per_gpu": tokens_rank, "global_tokens_per_step": tokens_step,
                        "parallelism": f"dp{world}", "timing": "inputs larger than L2: per-step activations+logits "

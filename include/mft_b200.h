@@ -58,6 +58,14 @@ typedef struct mft_gemm_args {
     int32_t batch; int64_t stride_a, stride_b, stride_c;
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
+/* bf16-operand form of mft_gemm: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements, multiples of 8),
+ * both operands K-major (trans_a = 0, trans_b = 1); accumulation and C stay fp32 (tcgen05.mma kind::f16). Twice the
+ * tensor throughput of the TF32 form for the same bytes staged; inputs are rounded to bf16 by mft_cast_bf16 /
+ * mft_transpose_cast_bf16 (weights: once, cached by the host layer). No SIMT fallback: ineligible arguments are an error. */
+int mft_gemm_bf16(const mft_gemm_args* args, mft_stream_t stream);
+/* out (bf16, ldo) = in (fp32, ldi), rows x cols, round-to-nearest-even; and the same with a transpose: out[c,r] = in[r,c]. */
+int mft_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream);
+int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream);
 /* Split-K form for products with a tiny output and a long contraction (LoRA's dA = x^T d(xA) and dB = (xA)^T dY, where the
  * contraction runs over all tokens): the fp32 SIMT kernel computes `splits` partial products over disjoint K ranges into
  * `workspace` (mft_gemm_splitk_workspace_bytes) and a second kernel sums them in a fixed order and applies alpha/bias/beta

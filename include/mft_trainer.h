@@ -65,6 +65,11 @@ void* mft_trainer_stream(mft_trainer* t);                /* the cudaStream_t the
 int mft_trainer_sync(mft_trainer* t);
 void mft_trainer_set_lr(mft_trainer* t, float lr);
 
+/* Operand precision of the large tensor-core GEMMs in the host layer (process-wide): 0 = TF32 (default), 1 = bf16
+ * (fp32 accumulate either way). Also settable with MFT_GEMM_PRECISION=bf16|tf32 in the environment. */
+void mft_host_set_gemm_precision(int bf16);
+int mft_host_gemm_precision(void);
+
 /* Introspection for tests / reports. */
 int32_t mft_trainer_num_trainable(mft_trainer* t);
 int32_t mft_trainer_num_with_grad(mft_trainer* t);       /* tensors that received a gradient in the last step */

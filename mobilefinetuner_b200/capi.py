@@ -48,6 +48,9 @@ SIGNATURES = {
     "mft_device_check": (C.c_int, []),
     "mft_use_tensor_cores": (C.c_int, [C.c_int]),
     "mft_gemm": (C.c_int, [C.POINTER(GemmArgs), vp]),
+    "mft_gemm_bf16": (C.c_int, [C.POINTER(GemmArgs), vp]),
+    "mft_cast_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
+    "mft_transpose_cast_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
     "mft_gemm_splitk_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "mft_gemm_splitk": (C.c_int, [C.POINTER(GemmArgs), i32, vp, sz, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),

@@ -193,8 +193,9 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x, int i) {
     auto a = run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias);
     auto x2 = add(x, a);
     auto x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
-    auto h = run_linear(x3, w.fc_in_lin, w.lora_initialized, w.mlp_fc_in_weight, w.mlp_fc_in_bias);
-    h = gelu(h);
+    TensorPtr h;   // fc_in + tanh-GELU: the activation is written by the GEMM epilogue (graph/gpt2_model.cpp:794-802)
+    if (w.lora_initialized && w.fc_in_lin) h = w.fc_in_lin->forward_gelu(x3);
+    else fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, &h);
     auto m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);
     return add(x2, m);
 }

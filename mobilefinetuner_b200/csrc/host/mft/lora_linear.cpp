@@ -28,8 +28,15 @@ void LoRALinear::attach_lora(const TensorPtr& A, const TensorPtr& B, float scale
 }
 void LoRALinear::clear_lora() { slices_.clear(); merged_ = false; }
 
+TensorPtr LoRALinear::forward(const TensorPtr& x) const { return forward_impl(x, nullptr); }
+TensorPtr LoRALinear::forward_gelu(const TensorPtr& x) const {
+    TensorPtr act;
+    forward_impl(x, &act);
+    return act;
+}
+
 // nn/lora_linear.cpp:47-108
-TensorPtr LoRALinear::forward(const TensorPtr& x) const {
+TensorPtr LoRALinear::forward_impl(const TensorPtr& x, TensorPtr* gelu_act) const {
     const TensorPtr& W = base_W();
     if (!W) throw std::runtime_error("LoRALinear::forward: base weight is null (sharded and not loaded?)");
     const TensorPtr& bias = base_b();
@@ -44,7 +51,7 @@ TensorPtr LoRALinear::forward(const TensorPtr& x) const {
             else partial.push_back(&s);
         }
     }
-    TensorPtr y = fused_lora_linear(x, W, bias, full);
+    TensorPtr y = fused_lora_linear(x, W, bias, full, partial.empty() ? gelu_act : nullptr);
     if (!partial.empty()) {
         TensorPtr xc = contiguous(x);
         const int64_t in = W->shape()[0], T = xc->numel() / in;
@@ -66,6 +73,7 @@ TensorPtr LoRALinear::forward(const TensorPtr& x) const {
             h.c = y->dev_f32_mut() + s->col0; h.ldc = y->ld();
             internal::run_gemm(h);
         }
+        if (gelu_act) *gelu_act = gelu(y);
     }
     return y;
 }

@@ -30,6 +30,9 @@ public:
     void merge_to_base();
     void unmerge_from_base();
     TensorPtr forward(const TensorPtr& x) const;
+    // B200 extension: gelu(forward(x)) with the activation produced by the GEMM epilogue (returns the activation;
+    // the pre-activation stays in the graph for GeluBackward).
+    TensorPtr forward_gelu(const TensorPtr& x) const;
 
     void set_debug_name(const std::string& name) { debug_name_ = name; }
     std::vector<std::pair<std::string, TensorPtr>> debug_params() const;
@@ -49,6 +52,7 @@ private:
     const TensorPtr& base_W() const;
     const TensorPtr& base_b() const;
     void add_delta_to_base(float sign);
+    TensorPtr forward_impl(const TensorPtr& x, TensorPtr* gelu_act) const;
 };
 
 }  // namespace ops

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <stdexcept>
@@ -38,6 +39,29 @@ void require_f32(const TensorPtr& t, const char* op) {
     if (t->dtype() != kFloat32) throw TensorError(std::string(op) + ": float32 tensor expected");
 }
 
+namespace {
+int env_precision() {
+    const char* e = std::getenv("MFT_GEMM_PRECISION");
+    return (e && (e[0] == 'b' || e[0] == 'B')) ? 1 : 0;
+}
+int g_precision = env_precision();
+
+// bf16 K-major copy of a small/temporary fp32 matrix stored [rows, cols] (ld) -> [rows, cols] or its transpose
+struct TempBf16 { std::shared_ptr<Tensor> keep; const void* ptr; int64_t ld; };
+TempBf16 temp_bf16(const float* src, int64_t ld_src, int64_t rows, int64_t cols, bool transpose) {
+    const int64_t orows = transpose ? cols : rows, ocols = transpose ? rows : cols;
+    const int64_t ld = (ocols + 7) / 8 * 8;
+    auto buf = Tensor::make({orows, ld / 2}, kFloat32);     // raw bytes: orows * ld bf16
+    void* dst = buf->dev_out();
+    if (transpose) mft_rt::check(mft_transpose_cast_bf16(src, ld_src, dst, ld, rows, cols, mft_rt::stream()), "mft_transpose_cast_bf16");
+    else mft_rt::check(mft_cast_bf16(src, ld_src, dst, ld, rows, cols, mft_rt::stream()), "mft_cast_bf16");
+    return {buf, dst, ld};
+}
+}  // namespace
+
+int gemm_precision() { return g_precision; }
+void set_gemm_precision(int bf16) { g_precision = bf16 ? 1 : 0; }
+
 // Chooses the execution form of one GEMM. Large products whose operands are not K-major are brought into
 // K-major form by a transpose pass (cached on 2-D weights) so they run on the tcgen05 kernel; everything
 // else goes to mft_gemm as is (SIMT kernel handles any layout).
@@ -47,8 +71,41 @@ void run_gemm(GemmCall g) {
     // A skinny output whose large operand would have to be transposed (contraction over the token index: LoRA dA/dB) is
     // cheaper as a split-K SIMT product reading that operand once than as transpose + tensor-core GEMM.
     const bool skinny_tn = g.trans_a && std::min(g.m, g.n) < 64;
-    const bool big = !skinny_tn && work >= (int64_t(1) << 24) && g.m >= 64 && g.n >= 16 && g.k >= 32;
+    // Products with a narrow output (rank-r LoRA factors: x A, dY B^T) only light up m/128 SMs on the tensor-core kernel
+    // and are bandwidth-bound anyway: they go to the split-K SIMT kernel too (exact fp32 as a bonus).
+    const bool big = !skinny_tn && work >= (int64_t(1) << 24) && g.m >= 64 && g.n >= 64 && g.k >= 32;
     TensorPtr tmp_a, tmp_b;   // keep K-major temporaries alive until the launch is enqueued
+    static const bool tc_off = [] { const char* e = std::getenv("MFT_USE_TENSOR_CORES"); return e && e[0] == '0'; }();
+    if (big && g.batch <= 1 && g_precision == 1 && !tc_off) {
+        // ---- bf16 tensor-core form: every operand becomes a K-major bf16 array (cached on the owning tensor when known)
+        std::vector<TempBf16> keep;
+        mft_gemm_args a;
+        std::memset(&a, 0, sizeof(a));
+        a.m = int32_t(g.m); a.n = int32_t(g.n); a.k = int32_t(g.k);
+        a.trans_a = 0; a.trans_b = 1;
+        if (!g.trans_a) {
+            if (g.a_tensor && g.a_tensor->dev_f32() == g.a && g.a_tensor->shape().back() == g.k && g.a_tensor->ld() == g.lda) {
+                auto v = g.a_tensor->bf16_view(); a.a = static_cast<const float*>(v.ptr); a.lda = v.ld;
+            } else { keep.push_back(temp_bf16(g.a, g.lda, g.m, g.k, false)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld; }
+        } else { keep.push_back(temp_bf16(g.a, g.lda, g.k, g.m, true)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld; }
+        const bool b_known = g.b_weight && g.b_weight->ndim() == 2 && g.b_weight->dev_f32() == g.b;
+        if (g.trans_b) {
+            if (b_known) { auto v = g.b_weight->bf16_view(); a.b = static_cast<const float*>(v.ptr); a.ldb = v.ld; }
+            else { keep.push_back(temp_bf16(g.b, g.ldb, g.n, g.k, false)); a.b = static_cast<const float*>(keep.back().ptr); a.ldb = keep.back().ld; }
+        } else {
+            if (b_known) { auto v = g.b_weight->bf16_transposed_view(); a.b = static_cast<const float*>(v.ptr); a.ldb = v.ld; }
+            else { keep.push_back(temp_bf16(g.b, g.ldb, g.k, g.n, true)); a.b = static_cast<const float*>(keep.back().ptr); a.ldb = keep.back().ld; }
+        }
+        if (g.k2 > 0) {
+            keep.push_back(temp_bf16(g.a2, g.lda2, g.m, g.k2, false)); a.a2 = static_cast<const float*>(keep.back().ptr); a.lda2 = keep.back().ld;
+            keep.push_back(temp_bf16(g.b2, g.ldb2, g.n, g.k2, false)); a.b2 = static_cast<const float*>(keep.back().ptr); a.ldb2 = keep.back().ld;
+            a.k2 = int32_t(g.k2);
+        }
+        a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
+        a.batch = 1;
+        mft_rt::check(mft_gemm_bf16(&a, mft_rt::stream()), "mft_gemm_bf16");
+        return;
+    }
     if (big && g.batch <= 1) {
         if (g.trans_a) {       // stored [k,m] -> [m,k]
             const int64_t ld = (g.k + 3) / 4 * 4;
@@ -76,10 +133,11 @@ void run_gemm(GemmCall g) {
     a.k2 = int32_t(g.k2); a.a2 = g.a2; a.lda2 = g.lda2; a.b2 = g.b2; a.ldb2 = g.ldb2;
     a.batch = std::max(g.batch, 1); a.stride_a = g.stride_a; a.stride_b = g.stride_b; a.stride_c = g.stride_c;
     // few output tiles + long contraction on the SIMT path: split K so the whole chip works on it
-    if (!big && g.k2 == 0 && g.k >= 1024) {
-        const int64_t tiles = ((g.m + 63) / 64) * ((g.n + 63) / 64) * a.batch;
-        if (tiles < 74) {
-            int splits = int(std::min<int64_t>(std::min<int64_t>(296 / tiles, g.k / 256), 65535 / a.batch));
+    if (!big && g.k2 == 0 && g.k >= 512) {
+        const int64_t bm = g.m <= 16 ? 16 : 64, bn = g.n <= 16 ? 16 : 64;     // tile shapes of the SIMT kernel
+        const int64_t tiles = ((g.m + bm - 1) / bm) * ((g.n + bn - 1) / bn) * a.batch;
+        if (tiles < 148) {
+            int splits = int(std::min<int64_t>(std::min<int64_t>(592 / tiles, g.k / 128), 65535 / a.batch));
             if (splits > 1) {
                 const size_t wsb = mft_gemm_splitk_workspace_bytes(a.m, a.n, a.batch, splits);
                 mft_rt::check(mft_gemm_splitk(&a, splits, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_gemm_splitk");

@@ -111,7 +111,10 @@ TensorPtr contiguous(const TensorPtr& t);
 // One autograd node for y = x W (+b) + sum_i s_i (x A_i) B_i  — replaces the six-node chain LoRALinear::forward
 // builds in the reference (nn/lora_linear.cpp:47-108). A/B accept both [in,r]/[r,out] and PEFT [r,in]/[out,r].
 struct LoraTerm { TensorPtr A, B; float scale; };
-TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms);
+// When `gelu_act` is given, the GEMM epilogue also writes gelu_tanh(y) there (its own autograd node, GeluBackward), which
+// replaces the separate ops::gelu pass of the MLP (graph/gpt2_model.cpp:794-802).
+TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
+                            TensorPtr* gelu_act = nullptr);
 // logits = x @ E^T for an embedding table E [V,C] (tied lm_head) without materialising E^T
 // (graph/gpt2_model.cpp:425-439 transposes wte on every forward).
 TensorPtr lm_head_tied(const TensorPtr& x, const TensorPtr& table);

@@ -27,9 +27,17 @@ struct GemmCall {
     float* gelu_out = nullptr;
     int64_t k2 = 0; const float* a2 = nullptr; int64_t lda2 = 0; const float* b2 = nullptr; int64_t ldb2 = 0;
     int batch = 1; int64_t stride_a = 0, stride_b = 0, stride_c = 0;
-    TensorPtr b_weight;
+    TensorPtr b_weight;   // tensor behind `b` (lets run_gemm reuse its cached K-major / bf16 shadows)
+    TensorPtr a_tensor;   // tensor behind `a`, dense view [m or k rows] (bf16 shadow reuse); optional
 };
 void run_gemm(GemmCall g);
+
+// Backward node of y = gelu(x) (used by the fused linear+GELU op as well as ops::gelu).
+BackwardFunctionPtr make_gelu_backward(const TensorPtr& x);
+
+// Operand precision of the large (tensor-core) GEMMs: 0 = TF32 (default), 1 = bf16. MFT_GEMM_PRECISION=bf16|tf32.
+int gemm_precision();
+void set_gemm_precision(int bf16);
 
 }  // namespace internal
 }  // namespace ops

@@ -287,8 +287,8 @@ public:
             auto gx = Tensor::make(x_->shape(), kFloat32);
             GemmCall g;
             g.m = T; g.n = in; g.k = out;
-            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0;
-            g.b = W_->dev_f32(); g.ldb = W_->ld(); g.trans_b = 1;    // W stored [in,out]: K-major for this product
+            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
+            g.b = W_->dev_f32(); g.ldb = W_->ld(); g.trans_b = 1; g.b_weight = W_;   // W stored [in,out]: K-major for this product
             g.c = gx->dev_f32_out(); g.ldc = in;
             std::vector<TensorPtr> keep;
             for (size_t i = 0; i < terms_.size(); ++i) {
@@ -334,7 +334,8 @@ private:
 
 }  // namespace
 
-TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms) {
+TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
+                            TensorPtr* gelu_act) {
     require_f32(x_in, "lora_linear");
     require_f32(W, "lora_linear");
     if (W->ndim() != 2) throw TensorError("lora_linear: weight must be [in, out]");
@@ -360,10 +361,13 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     }
     GemmCall g;
     g.m = T; g.n = out; g.k = in;
-    g.a = x->dev_f32(); g.lda = in; g.trans_a = 0;
+    g.a = x->dev_f32(); g.lda = in; g.trans_a = 0; g.a_tensor = x;
     g.b = W->dev_f32(); g.ldb = W->ld(); g.trans_b = 0; g.b_weight = W;
     g.c = y->dev_f32_out(); g.ldc = y->ld();
     g.bias = bias ? bias->dev_f32() : nullptr;
+    TensorPtr act;
+    const bool fuse_gelu = gelu_act != nullptr && terms.size() <= 1;   // later slices accumulate after the epilogue ran
+    if (fuse_gelu) { act = Tensor::make(so, kFloat32, false, y->ld()); g.gelu_out = act->dev_f32_out(); }
     if (!terms.empty()) { g.k2 = xa[0]->shape()[1]; g.a2 = xa[0]->dev_f32(); g.lda2 = g.k2; g.b2 = bt[0]->dev_f32(); g.ldb2 = bt[0]->ld(); }
     run_gemm(g);
     for (size_t i = 1; i < terms.size(); ++i) {
@@ -377,6 +381,10 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     std::vector<TensorPtr> inputs{x_in, W, bias};
     for (const auto& t : terms) { inputs.push_back(t.A); inputs.push_back(t.B); }
     track(y, inputs, std::make_shared<LoraLinearBackward>(x, W, bias, terms, xa));
+    if (gelu_act) {
+        if (fuse_gelu) { track(act, {y}, make_gelu_backward(y)); *gelu_act = act; }
+        else *gelu_act = gelu(y);
+    }
     return y;
 }
 
@@ -405,7 +413,7 @@ public:
             gx = Tensor::make(x_->shape(), kFloat32);
             GemmCall g;
             g.m = T; g.n = C; g.k = V;
-            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0;
+            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
             g.b = e_->dev_f32(); g.ldb = e_->ld(); g.trans_b = 0; g.b_weight = e_;   // E stored [k=V, n=C]
             g.c = gx->dev_f32_out(); g.ldc = C;
             run_gemm(g);
@@ -437,8 +445,8 @@ TensorPtr lm_head_tied(const TensorPtr& x_in, const TensorPtr& table) {
     auto y = Tensor::make(so, kFloat32, false, out_ld(V));
     GemmCall g;
     g.m = T; g.n = V; g.k = C;
-    g.a = x->dev_f32(); g.lda = C; g.trans_a = 0;
-    g.b = table->dev_f32(); g.ldb = table->ld(); g.trans_b = 1;      // E [V,C] is K-major for x E^T
+    g.a = x->dev_f32(); g.lda = C; g.trans_a = 0; g.a_tensor = x;
+    g.b = table->dev_f32(); g.ldb = table->ld(); g.trans_b = 1; g.b_weight = table;     // E [V,C] is K-major for x E^T
     g.c = y->dev_f32_out(); g.ldc = y->ld();
     run_gemm(g);
     track(y, {x_in, table}, std::make_shared<LmHeadBackward>(x, table));

@@ -72,6 +72,10 @@ TensorPtr unary(int kind, const TensorPtr& x_in, const char* name) {
 
 }  // namespace
 
+namespace internal {
+BackwardFunctionPtr make_gelu_backward(const TensorPtr& x) { return std::make_shared<GeluBackward>(x); }
+}  // namespace internal
+
 // core/ops.cpp:1033-1117
 TensorPtr gelu(const TensorPtr& x) { return unary(0, x, "gelu"); }
 TensorPtr relu(const TensorPtr& x) { return unary(1, x, "relu"); }

@@ -39,6 +39,7 @@ void Tensor::allocate(bool zero) {
     st_ = std::make_shared<detail::Storage>();
     const size_t es = DTypeUtils::size_of(dtype_);
     st_->dev_bytes = static_cast<size_t>(rows()) * static_cast<size_t>(ld_) * es;
+    st_->in_arena = mft_rt::arena_active();
     st_->dev = mft_rt::dev_alloc(st_->dev_bytes);
     st_->dev_valid = true;
     if (zero) mft_rt::memset0(st_->dev, st_->dev_bytes);
@@ -166,6 +167,43 @@ TensorPtr Tensor::transposed_shadow() const {
         shadow_version_ = version();
     }
     return shadow_t_;
+}
+
+namespace {
+std::shared_ptr<detail::Storage> raw_buffer(size_t bytes, bool persistent) {
+    auto s = std::make_shared<detail::Storage>();
+    s->dev_bytes = bytes;
+    if (persistent) { mft_rt::PersistentScope keep; s->dev = mft_rt::dev_alloc(bytes); }
+    else s->dev = mft_rt::dev_alloc(bytes);
+    s->dev_valid = true;
+    return s;
+}
+}  // namespace
+
+Tensor::Bf16View Tensor::bf16_view() const {
+    if (dtype_ != kFloat32) throw TensorError("bf16_view: float32 tensors only");
+    const int64_t cols = shape_.empty() ? 1 : shape_.back(), r = rows();
+    const int64_t ld = (cols + 7) / 8 * 8;
+    if (!bf16_ || bf16_version_ != version()) {
+        if (!bf16_) bf16_ = raw_buffer(size_t(r) * ld * 2, !st_->in_arena);
+        mft_rt::check(mft_cast_bf16(dev_f32(), ld_, bf16_->dev, ld, r, cols, mft_rt::stream()), "mft_cast_bf16");
+        bf16_version_ = version();
+        bf16_ld_ = ld;
+    }
+    return {bf16_->dev, bf16_ld_};
+}
+
+Tensor::Bf16View Tensor::bf16_transposed_view() const {
+    if (dtype_ != kFloat32 || shape_.size() != 2) throw TensorError("bf16_transposed_view: 2-D float32 tensors only");
+    const int64_t r = shape_[0], c = shape_[1];
+    const int64_t ld = (r + 7) / 8 * 8;
+    if (!bf16_t_ || bf16_t_version_ != version()) {
+        if (!bf16_t_) bf16_t_ = raw_buffer(size_t(c) * ld * 2, !st_->in_arena);
+        mft_rt::check(mft_transpose_cast_bf16(dev_f32(), ld_, bf16_t_->dev, ld, r, c, mft_rt::stream()), "mft_transpose_cast_bf16");
+        bf16_t_version_ = version();
+        bf16_t_ld_ = ld;
+    }
+    return {bf16_t_->dev, bf16_t_ld_};
 }
 
 // ---------------------------------------------------------------- shape ops

@@ -43,7 +43,7 @@ struct Storage {
     size_t dev_bytes = 0;
     bool dev_valid = false, host_valid = false;
     bool host_external = false;      // wrap mode: the caller owns `host`
-    bool host_dirty_possible = false;
+    bool in_arena = false;           // allocated from the per-step arena (dies at the next arena_reset)
     uint64_t version = 0;            // bumped on every write access (device or host)
     ~Storage();
 };
@@ -131,6 +131,11 @@ public:
     static TensorPtr make(const std::vector<int64_t>& shape, DType dtype = kFloat32, bool zero = false, int64_t ld = 0);
     // Cached K-major shadow of a 2-D weight (its transpose), rebuilt when version() changes.
     TensorPtr transposed_shadow() const;
+    // Cached bf16 copies for the bf16 tensor-core GEMM (device pointer + leading dimension in elements): same layout
+    // viewed as [rows(), shape.back()], or the transpose of a 2-D tensor. Rebuilt when version() changes.
+    struct Bf16View { const void* ptr; int64_t ld; };
+    Bf16View bf16_view() const;
+    Bf16View bf16_transposed_view() const;
 
 private:
     std::vector<int64_t> shape_;
@@ -147,6 +152,9 @@ private:
 
     mutable TensorPtr shadow_t_;
     mutable uint64_t shadow_version_ = ~0ull;
+    mutable std::shared_ptr<detail::Storage> bf16_, bf16_t_;
+    mutable uint64_t bf16_version_ = ~0ull, bf16_t_version_ = ~0ull;
+    mutable int64_t bf16_ld_ = 0, bf16_t_ld_ = 0;
 
     void allocate(bool zero);
     void* host_rw();

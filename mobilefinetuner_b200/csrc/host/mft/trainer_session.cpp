@@ -22,6 +22,7 @@
 #include "mft_b200.h"
 #include "mft_trainer.h"
 #include "ops.h"
+#include "ops_internal.h"
 #include "runtime.h"
 
 using namespace ops;
@@ -331,6 +332,8 @@ extern "C" void* mft_trainer_stream(mft_trainer*) { return mft_rt::stream(); }
 extern "C" int mft_trainer_sync(mft_trainer*) {
     try { mft_rt::sync(); return 0; } catch (const std::exception& e) { return fail("mft_trainer_sync: %s", e.what()); }
 }
+extern "C" void mft_host_set_gemm_precision(int bf16) { ops::internal::set_gemm_precision(bf16); }
+extern "C" int mft_host_gemm_precision(void) { return ops::internal::gemm_precision(); }
 extern "C" void mft_trainer_set_lr(mft_trainer* t, float lr) { if (t && t->opt) t->opt->set_learning_rate(lr); }
 extern "C" int32_t mft_trainer_num_trainable(mft_trainer* t) { return t ? int32_t(t->trainable.size()) : 0; }
 extern "C" int32_t mft_trainer_num_with_grad(mft_trainer* t) { return t ? t->with_grad : 0; }

@@ -114,3 +114,15 @@ extern "C" int mft_gemm_profile_read(double* flops, double* ms, int64_t* launche
     if (launches) *launches = n;
     return 0;
 }
+
+// bf16-operand form: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements); C stays fp32.
+extern "C" int mft_gemm_bf16(const mft_gemm_args* args, mft_stream_t stream) {
+    GemmParams p;
+    int rc = to_params(args, p);
+    if (rc) return rc;
+    if (p.m == 0 || p.n == 0) return 0;
+    p.bf16 = true;
+    if (!gemm_tc_eligible(p))
+        return set_error(1, "mft_gemm_bf16: operands must be K-major (trans_a=0, trans_b=1), 16-byte aligned, with leading dimensions that are multiples of 8");
+    return launch_gemm_tc(p, as_stream(stream));
+}

@@ -6,14 +6,15 @@ namespace mft {
 
 struct GemmParams {
     int m, n, k;
-    const float* a; int64_t lda; int trans_a;
-    const float* b; int64_t ldb; int trans_b;
+    const void* a; int64_t lda; int trans_a;     // fp32, or bf16 when `bf16` is set (tensor-core path only)
+    const void* b; int64_t ldb; int trans_b;
     float* c; int64_t ldc;
     float alpha, beta;
     const float* bias;
     float* gelu_out;
-    int k2; const float* a2; int64_t lda2; const float* b2; int64_t ldb2;
+    int k2; const void* a2; int64_t lda2; const void* b2; int64_t ldb2;
     int batch; int64_t stride_a, stride_b, stride_c;
+    bool bf16 = false;         // operands are bf16 arrays
     int ksplit = 1;            // SIMT split-K: number of K slices (partials reduced in a fixed order)
     float* partial = nullptr;  // [batch][ksplit][m][n] scratch when ksplit > 1
 };

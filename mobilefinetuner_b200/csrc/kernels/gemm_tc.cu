@@ -101,6 +101,20 @@ __device__ __forceinline__ void tc_mma_tf32_2sm(uint32_t tmem_d, uint64_t adesc,
         "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
@@ -146,13 +160,18 @@ struct TcArgs {
     const float* bias;
     float alpha, beta;
     int tiles_m, tiles_n;
+    int debug;                 // MFT_GEMM_DEBUG bits (kernel experiments): 1 = no global stores, 2 = no smem staging either, 4 = no TMEM loads
 };
 
-template <int BN, int CG>
+// BF16 = false: fp32 operands in HBM, TF32 MMA (32 elements per 128-byte k-block, K = 8 per instruction).
+// BF16 = true : bf16 operands in HBM, kind::f16 MMA (64 elements per k-block, K = 16 per instruction): same bytes per
+//               k-block, twice the FLOPs per byte staged.
+template <int BN, int CG, bool BF16>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2, TcArgs p) {
     using Cfg = TcCfg<BN, CG>;
+    constexpr int KE = BF16 ? 64 : 32;                     // elements per k-block (one 128-byte swizzle span)
     const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
     const int unit = CG == 2 ? int(blockIdx.x >> 1) : int(blockIdx.x);        // CTA (or CTA pair) index
     const int num_units = CG == 2 ? int(gridDim.x >> 1) : int(gridDim.x);
@@ -213,19 +232,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     if (CG == 1) {
                         mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes));
                         if (kb < p.kb1) {
-                            tma_load_3d(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
-                            tma_load_3d(sb, &map_b, &full[stage], kb * TBK, brow, bz);
+                            tma_load_3d(sa, &map_a, &full[stage], kb * KE, mt * TBM, bz);
+                            tma_load_3d(sb, &map_b, &full[stage], kb * KE, brow, bz);
                         } else {
-                            tma_load_3d(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
-                            tma_load_3d(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, brow, 0);
+                            tma_load_3d(sa, &map_a2, &full[stage], (kb - p.kb1) * KE, mt * TBM, 0);
+                            tma_load_3d(sb, &map_b2, &full[stage], (kb - p.kb1) * KE, brow, 0);
                         }
                     } else {
                         if (kb < p.kb1) {
-                            tma_load_3d_2sm(sa, &map_a, &full[stage], kb * TBK, mt * TBM, bz);
-                            tma_load_3d_2sm(sb, &map_b, &full[stage], kb * TBK, brow, bz);
+                            tma_load_3d_2sm(sa, &map_a, &full[stage], kb * KE, mt * TBM, bz);
+                            tma_load_3d_2sm(sb, &map_b, &full[stage], kb * KE, brow, bz);
                         } else {
-                            tma_load_3d_2sm(sa, &map_a2, &full[stage], (kb - p.kb1) * TBK, mt * TBM, 0);
-                            tma_load_3d_2sm(sb, &map_b2, &full[stage], (kb - p.kb1) * TBK, brow, 0);
+                            tma_load_3d_2sm(sa, &map_a2, &full[stage], (kb - p.kb1) * KE, mt * TBM, 0);
+                            tma_load_3d_2sm(sb, &map_b2, &full[stage], (kb - p.kb1) * KE, brow, 0);
                         }
                         // the leader's barrier collects both CTAs' bytes: it expects 2 x stage_bytes and one arrival per CTA
                         if (cta_rank == 0) mbar_arrive_expect_tx(&full[stage], uint32_t(Cfg::stage_bytes) * 2u);
@@ -239,7 +258,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         // ===================== MMA issuer (one thread) =====================
         if (lane == 0 && cta_rank == 0) {
             // instruction descriptor: D=f32, A=B=tf32, both K-major, N=BN, M=128 per CTA (256 across the pair)
-            constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t((TBM * CG) >> 4) << 24);
+            constexpr uint32_t fmt = BF16 ? 1u : 2u;       // a/b format: 1 = BF16, 2 = TF32
+            constexpr uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t((TBM * CG) >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             int it = 0;
             for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
@@ -258,8 +278,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                     for (int k = 0; k < TBK / TUK; ++k) {
                         // advance 32 bytes (one UMMA K) inside the 128B swizzle span: +2 in 16-byte units
-                        if (CG == 2) tc_mma_tf32_2sm(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
-                        else tc_mma_tf32(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+                        const uint32_t acc = (kb | k) != 0 ? 1u : 0u;
+                        if (BF16) {
+                            if (CG == 2) tc_mma_bf16_2sm(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, acc);
+                            else tc_mma_bf16(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, acc);
+                        } else {
+                            if (CG == 2) tc_mma_tf32_2sm(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, acc);
+                            else tc_mma_tf32(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, acc);
+                        }
                     }
                     // frees the smem slot (in both CTAs when paired) once these MMAs retire
                     if (CG == 2) tc_commit_2sm(&empty[stage]); else tc_commit(&empty[stage]);
@@ -301,12 +327,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.n) break;               // warp-uniform
                 float v[32];
-                tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
+                if (p.debug & 4) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = 0.f;
+                } else tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
+                if (p.debug & 2) continue;
                 float4* srow = reinterpret_cast<float4*>(stg + lane * kEpiPitch);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) srow[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 __syncwarp();
                 const int col = n0 + c0 + c4 * 4;
+                if (p.debug & 1) { __syncwarp(); continue; }
                 if (vec_ok && col + 4 <= p.n) {
                     float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (p.bias) bb = __ldg(reinterpret_cast<const float4*>(p.bias + col));
@@ -388,28 +419,28 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 struct MapKey {
-    const void* ptr; uint64_t inner, rows, batch, ld, stride; uint32_t box_rows;
+    const void* ptr; uint64_t inner, rows, batch, ld, stride; uint32_t box_rows; uint32_t bf16;
     bool operator==(const MapKey& o) const {
         return ptr == o.ptr && inner == o.inner && rows == o.rows && batch == o.batch && ld == o.ld &&
-               stride == o.stride && box_rows == o.box_rows;
+               stride == o.stride && box_rows == o.box_rows && bf16 == o.bf16;
     }
 };
 struct MapKeyHash {
     size_t operator()(const MapKey& k) const {
         uint64_t h = reinterpret_cast<uint64_t>(k.ptr);
         auto mix = [&h](uint64_t v) { h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); };
-        mix(k.inner); mix(k.rows); mix(k.batch); mix(k.ld); mix(k.stride); mix(k.box_rows);
+        mix(k.inner); mix(k.rows); mix(k.batch); mix(k.ld); mix(k.stride); mix(k.box_rows); mix(k.bf16);
         return size_t(h);
     }
 };
 
 // K-major operand [batch][rows][inner] (ld elements between rows): box = {32, box_rows, 1}, 128B swizzle.
 // Encoding costs ~1 us on the host; the step re-uses the same buffers so descriptors are cached.
-static bool make_operand_map(CUtensorMap* out, const float* ptr, uint64_t inner, uint64_t rows, uint64_t batch,
-                             uint64_t ld, uint64_t stride, uint32_t box_rows) {
+static bool make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, uint64_t rows, uint64_t batch,
+                             uint64_t ld, uint64_t stride, uint32_t box_rows, bool bf16) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
     static std::mutex mu;
-    MapKey key{ptr, inner, rows, batch, ld, stride, box_rows};
+    MapKey key{ptr, inner, rows, batch, ld, stride, box_rows, bf16 ? 1u : 0u};
     {
         std::lock_guard<std::mutex> lk(mu);
         auto it = cache.find(key);
@@ -420,10 +451,11 @@ static bool make_operand_map(CUtensorMap* out, const float* ptr, uint64_t inner,
     alignas(64) CUtensorMap m;
     cuuint64_t dims[3] = {inner, rows, batch};
     if (batch == 1 || stride == 0) stride = rows * ld;
-    cuuint64_t strides[2] = {ld * 4, stride * 4};
-    cuuint32_t box[3] = {uint32_t(TBK), box_rows, 1};
+    const uint64_t es = bf16 ? 2 : 4;
+    cuuint64_t strides[2] = {ld * es, stride * es};
+    cuuint32_t box[3] = {uint32_t(bf16 ? 64 : 32), box_rows, 1};     // 128 bytes of K per row
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 3, const_cast<float*>(ptr), dims, strides, box, estr,
+    CUresult r = enc(&m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 3, const_cast<void*>(ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return false;
@@ -439,9 +471,11 @@ static bool make_operand_map(CUtensorMap* out, const float* ptr, uint64_t inner,
 bool gemm_tc_eligible(const GemmParams& p) {
     if (p.trans_a != 0 || p.trans_b == 0) return false;                 // both operands must be K-major
     if (p.m < 1 || p.n < 1 || p.k < 1) return false;
-    if ((p.lda & 3) || (p.ldb & 3) || !aligned16(p.a) || !aligned16(p.b)) return false;
-    if (p.batch > 1 && ((p.stride_a & 3) || (p.stride_b & 3))) return false;
-    if (p.k2 > 0 && ((p.lda2 & 3) || (p.ldb2 & 3) || !aligned16(p.a2) || !aligned16(p.b2) || p.batch != 1)) return false;
+    const int64_t am = p.bf16 ? 7 : 3;                                  // row pitch must be a multiple of 16 bytes
+    if ((p.lda & am) || (p.ldb & am) || !aligned16(p.a) || !aligned16(p.b)) return false;
+    if (p.batch > 1 && ((p.stride_a & am) || (p.stride_b & am))) return false;
+    if (p.k2 > 0 && ((p.lda2 & am) || (p.ldb2 & am) || !aligned16(p.a2) || !aligned16(p.b2) || p.batch != 1)) return false;
+    if (p.bf16) return true;
     // tiny problems are launch-bound either way; keep them on the SIMT kernel (exact fp32)
     if (int64_t(p.m) * p.n * p.batch < 64 * 64 || p.k < 32) return false;
     return true;
@@ -484,27 +518,30 @@ void gemm_tc_profile_read(double* flops, double* ms, long long* launches) {
     if (launches) *launches = g_prof.launches;
 }
 
-template <int BN, int CG>
+template <int BN, int CG, bool BF16>
 static int launch_tc(const GemmParams& p, cudaStream_t st) {
     using Cfg = TcCfg<BN, CG>;
+    constexpr int KE = BF16 ? 64 : 32;
     CUtensorMap ma, mb, ma2, mb2;
-    if (!make_operand_map(&ma, p.a, p.k, p.m, p.batch, p.lda, p.stride_a, TBM) ||
-        !make_operand_map(&mb, p.b, p.k, p.n, p.batch, p.ldb, p.stride_b, Cfg::b_rows))
+    if (!make_operand_map(&ma, p.a, p.k, p.m, p.batch, p.lda, p.stride_a, TBM, BF16) ||
+        !make_operand_map(&mb, p.b, p.k, p.n, p.batch, p.ldb, p.stride_b, Cfg::b_rows, BF16))
         return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed");
     if (p.k2 > 0) {
-        if (!make_operand_map(&ma2, p.a2, p.k2, p.m, 1, p.lda2, 0, TBM) ||
-            !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, Cfg::b_rows))
+        if (!make_operand_map(&ma2, p.a2, p.k2, p.m, 1, p.lda2, 0, TBM, BF16) ||
+            !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, Cfg::b_rows, BF16))
             return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (segment 2)");
     } else { ma2 = ma; mb2 = mb; }
     TcArgs a;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
-    a.kb1 = int(ceil_div(p.k, TBK)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, TBK)) : 0;
+    a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;
     a.alpha = p.alpha; a.beta = p.beta;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
+    static const int dbg = [] { const char* e = getenv("MFT_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
+    a.debug = dbg;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
         if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
@@ -537,7 +574,7 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG>, ma, mb, ma2, mb2, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16>, ma, mb, ma2, mb2, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);
     if (e == cudaSuccess) e = cudaGetLastError();
@@ -550,20 +587,25 @@ static bool env_two_cta() {
     return !(e && e[0] == '0');
 }
 
-int launch_gemm_tc(const GemmParams& p, cudaStream_t st) {
+template <bool BF16>
+static int dispatch_tc(const GemmParams& p, cudaStream_t st) {
     static const bool two_cta = env_two_cta();
     const int64_t tiles_m = ceil_div(p.m, TBM);
     const int64_t tm = tiles_m * p.batch;
     // Paired CTAs (cta_group::2) whenever there are at least two row tiles to pair and the output is wide enough.
     if (two_cta && tiles_m >= 2 && p.n > 64) {
         const int64_t pairs = ceil_div(tiles_m, 2) * p.batch;
-        if (p.n <= 128 || pairs * ceil_div(p.n, 256) < kNumSMs / 4) return launch_tc<128, 2>(p, st);
-        return launch_tc<256, 2>(p, st);
+        if (p.n <= 128 || pairs * ceil_div(p.n, 256) < kNumSMs / 4) return launch_tc<128, 2, BF16>(p, st);
+        return launch_tc<256, 2, BF16>(p, st);
     }
     // Single-CTA tiles: widest tile that still gives every SM work; narrow N uses narrow tiles.
-    if (p.n <= 64 || tm * ceil_div(p.n, 128) < kNumSMs / 2) return launch_tc<64, 1>(p, st);
-    if (p.n <= 128 || tm * ceil_div(p.n, 256) < kNumSMs) return launch_tc<128, 1>(p, st);
-    return launch_tc<256, 1>(p, st);
+    if (p.n <= 64 || tm * ceil_div(p.n, 128) < kNumSMs / 2) return launch_tc<64, 1, BF16>(p, st);
+    if (p.n <= 128 || tm * ceil_div(p.n, 256) < kNumSMs) return launch_tc<128, 1, BF16>(p, st);
+    return launch_tc<256, 1, BF16>(p, st);
+}
+
+int launch_gemm_tc(const GemmParams& p, cudaStream_t st) {
+    return p.bf16 ? dispatch_tc<true>(p, st) : dispatch_tc<false>(p, st);
 }
 
 }  // namespace mft

@@ -1,4 +1,5 @@
 // Layout / gather kernels: transpose, head permute, column sums, embedding gather, RoPE, GQA repeat.
+#include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace mft {
@@ -18,6 +19,46 @@ __global__ void transpose2d_kernel(const float* __restrict__ in, int64_t ldi, fl
     for (int j = threadIdx.y; j < 32; j += blockDim.y) {
         int64_t c = c0 + j, r = r0 + threadIdx.x;
         if (r < rows && c < cols) out[c * ldo + r] = tile[threadIdx.x][j];
+    }
+}
+
+// fp32 -> bf16 (round to nearest even), row pitches in elements; 4 elements per thread
+__global__ void cast_bf16_kernel(const float* __restrict__ in, int64_t ldi, __nv_bfloat16* __restrict__ out, int64_t ldo,
+                                 int64_t rows, int64_t cols) {
+    const int64_t c4 = (cols + 3) >> 2;
+    const int64_t n = rows * c4;
+    const bool vec = ((ldi & 3) == 0) && ((ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(out) & 7u) == 0);
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = idx / c4, c = (idx % c4) << 2;
+        const float* src = in + r * ldi + c;
+        __nv_bfloat16* dst = out + r * ldo + c;
+        if (vec && c + 4 <= cols) {
+            float4 v = ld_stream(reinterpret_cast<const float4*>(src));
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(dst) = pk;
+        } else {
+            for (int e = 0; e < 4 && c + e < cols; ++e) dst[e] = __float2bfloat16_rn(src[e]);
+        }
+    }
+}
+
+// out[c, r] (bf16, ldo) = in[r, c] (fp32, ldi): K-major bf16 shadow of a weight in one pass
+__global__ void transpose_cast_bf16_kernel(const float* __restrict__ in, int64_t ldi, __nv_bfloat16* __restrict__ out, int64_t ldo,
+                                           int64_t rows, int64_t cols) {
+    __shared__ float tile[32][33];
+    const int64_t c0 = int64_t(blockIdx.x) * 32, r0 = int64_t(blockIdx.y) * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int64_t r = r0 + j, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[j][threadIdx.x] = in[r * ldi + c];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int64_t c = c0 + j, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) out[c * ldo + r] = __float2bfloat16_rn(tile[threadIdx.x][j]);
     }
 }
 
@@ -228,5 +269,23 @@ extern "C" int mft_repeat_kv_bwd(const float* gy, float* gx, int64_t B, int64_t 
     if (!gy || !gx) return set_error(1, "mft_repeat_kv_bwd: null pointer");
     repeat_kv_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(gy, gx, B, KV, rep, S * Hd);
     MFT_CHECK_LAUNCH("mft_repeat_kv_bwd");
+    return 0;
+}
+
+extern "C" int mft_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream) {
+    if (rows == 0 || cols == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_cast_bf16: null pointer");
+    cast_bf16_kernel<<<stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream)>>>(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
+    MFT_CHECK_LAUNCH("mft_cast_bf16");
+    return 0;
+}
+
+extern "C" int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream) {
+    if (rows == 0 || cols == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_transpose_cast_bf16: null pointer");
+    dim3 grid(unsigned(ceil_div(cols, 32)), unsigned(ceil_div(rows, 32)));
+    if (grid.y > 65535) return set_error(1, "mft_transpose_cast_bf16: too many rows");
+    transpose_cast_bf16_kernel<<<grid, dim3(32, 8), 0, as_stream(stream)>>>(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
+    MFT_CHECK_LAUNCH("mft_transpose_cast_bf16");
     return 0;
 }

@@ -42,6 +42,8 @@ TRAINER_SIGNATURES = {
     "mft_trainer_stream": (vp, [vp]),
     "mft_trainer_sync": (C.c_int, [vp]),
     "mft_trainer_set_lr": (None, [vp, f32]),
+    "mft_host_set_gemm_precision": (None, [C.c_int]),
+    "mft_host_gemm_precision": (C.c_int, []),
     "mft_trainer_num_trainable": (i32, [vp]),
     "mft_trainer_num_with_grad": (i32, [vp]),
     "mft_trainer_kernel_launches": (i64, [vp]),

@@ -165,6 +165,45 @@ def test_gemm_tc_batched_and_pitched(capi):
     assert rel(cc, a_full[:, :k].astype(np.float64) @ bmat.astype(np.float64).T) < TF32_TOL
 
 
+BF16_TOL = 1e-2   # bf16 inputs (8-bit mantissa), fp32 accumulate
+
+
+@pytest.mark.parametrize("m,n,k,r", [(512, 768, 768, 0), (4096, 1024, 1024, 16), (300, 200, 104, 8), (256, 50257, 768, 0),
+                                     (2048, 3072, 768, 0)])
+def test_gemm_bf16_tensor_core_path(capi, m, n, k, r):
+    """mft_cast_bf16 / mft_transpose_cast_bf16 + mft_gemm_bf16 (kind::f16 tcgen05) against the fp64 product."""
+    rng = np.random.default_rng(m + n + k)
+    a = rng.standard_normal((m, k)).astype(np.float32)
+    w = (rng.standard_normal((k, n)) * 0.05).astype(np.float32)      # weight stored [in,out] like the reference
+    bias = rng.standard_normal(n).astype(np.float32)
+    da, dw, dbias = dev(a), dev(w), dev(bias)
+    ldk = (k + 7) // 8 * 8
+    a16 = torch.zeros(m, ldk, dtype=torch.bfloat16, device="cuda")
+    w16 = torch.zeros(n, ldk, dtype=torch.bfloat16, device="cuda")
+    capi.call("mft_cast_bf16", da, k, a16, ldk, m, k, None)
+    capi.call("mft_transpose_cast_bf16", dw, n, w16, ldk, k, n, None)
+    assert torch.equal(a16[:, :k], da.to(torch.bfloat16))                    # round-to-nearest-even, like torch
+    assert torch.equal(w16[:, :k], dw.t().contiguous().to(torch.bfloat16))
+    kw = {}
+    seg2 = None
+    if r:
+        xa = rng.standard_normal((m, r)).astype(np.float32)
+        bt = rng.standard_normal((n, r)).astype(np.float32)
+        ldr = (r + 7) // 8 * 8
+        xa16 = torch.zeros(m, ldr, dtype=torch.bfloat16, device="cuda"); xa16[:, :r] = dev(xa).to(torch.bfloat16)
+        bt16 = torch.zeros(n, ldr, dtype=torch.bfloat16, device="cuda"); bt16[:, :r] = dev(bt).to(torch.bfloat16)
+        kw = dict(k2=r, a2=xa16.data_ptr(), lda2=ldr, b2=bt16.data_ptr(), ldb2=ldr)
+        seg2 = (xa, bt)
+    ldc = (n + 31) // 32 * 32
+    c = torch.full((m, ldc), float("nan"), device="cuda")
+    args = capi.GemmArgs(m, n, k, a16.data_ptr(), ldk, 0, w16.data_ptr(), ldk, 1, c.data_ptr(), ldc, 1.0, 0.0, dbias.data_ptr(), None,
+                         kw.get("k2", 0), kw.get("a2"), kw.get("lda2", 0), kw.get("b2"), kw.get("ldb2", 0), 1, 0, 0, 0)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    torch.cuda.synchronize()
+    e = ref_gemm(a, np.ascontiguousarray(w.T), 0, 1, 1.0, 0.0, bias, None, seg2)
+    assert rel(c[:, :n], e) < BF16_TOL
+
+
 def test_lora_linear_fused_forward_golden(capi, golden_ops):
     """y = x W + b + s (xA) B as ONE mft_gemm call with the rank-r update as second K segment, against the
     reference's LoRALinear::forward output (tests/golden/ops/lora0_*)."""

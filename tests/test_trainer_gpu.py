@@ -105,3 +105,22 @@ def test_trainer_default_tf32_path_stays_within_loss_tolerance():
         assert abs(tr.grad_norm() - ref_gnorm) <= 2e-2 * ref_gnorm
         assert (tr.num_with_grad, tr.num_trainable) == (with_grad, total)
     tr.close()
+
+
+@pytest.mark.tf32
+def test_trainer_bf16_gemm_mode_c1_first_steps():
+    """Config c1 (GPT-2 small LoRA r8, B4 S128) with bf16 tensor-core GEMM operands: loss within 1e-3 of the fp32 reference
+    run, same set of tensors receiving gradients."""
+    from mobilefinetuner_b200.trainer import Trainer, hostlib
+    hostlib.mft_host_set_gemm_precision(1)
+    try:
+        tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096)
+        steps, _ = golden("gpt2_small_lora_c1.txt")
+        for i, (ref_loss, ref_gnorm, with_grad, total) in enumerate(steps):
+            loss = tr.step_numpy(tr.next_synthetic_batch())
+            assert abs(loss - ref_loss) / ref_loss < 1e-3, (i, loss, ref_loss)
+            assert abs(tr.grad_norm() - ref_gnorm) <= 5e-2 * ref_gnorm, (i, tr.grad_norm(), ref_gnorm)
+            assert (tr.num_with_grad, tr.num_trainable) == (with_grad, total)
+        tr.close()
+    finally:
+        hostlib.mft_host_set_gemm_precision(0)

@@ -1,0 +1,82 @@
+#!/usr/bin/env python
+"""Times the tensor-core GEMM (C ABI) on the shapes of the benchmark workload: CUDA events, L2 flushed between launches."""
+import ctypes as C
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from mobilefinetuner_b200 import capi  # noqa: E402
+
+SHAPES = [("qkv", 4096, 3072, 1024), ("proj", 4096, 1024, 1024), ("fc_in", 4096, 4096, 1024), ("fc_out", 4096, 1024, 4096),
+          ("lm_head", 4096, 50257, 1024), ("lm_head_dx", 4096, 1024, 50264), ("c1_qkv", 512, 2304, 768), ("big", 8192, 8192, 8192)]
+
+
+def bench(name, m, n, k, bf16, iters=20):
+    dt = torch.bfloat16 if bf16 else torch.float32
+    a = torch.randn(m, k, device="cuda").to(dt)
+    b = (torch.randn(n, k, device="cuda") * 0.05).to(dt)
+    ldc = (n + 31) // 32 * 32
+    c = torch.empty(m, ldc, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c.data_ptr(), ldc, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0)
+    fn = capi.lib.mft_gemm_bf16 if bf16 else capi.lib.mft_gemm
+    for _ in range(3):
+        capi.check(fn(C.byref(args), None), "gemm")
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(C.byref(args), None)
+        e1.record()
+        e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    us = tot / iters * 1e3
+    tf = 2.0 * m * n * k / (us * 1e-6) / 1e12
+    print(f"{name:12s} {'bf16' if bf16 else 'tf32'} m={m} n={n} k={k}: {us:8.1f} us  {tf:7.1f} TFLOP/s", flush=True)
+
+
+SKINNY = [("xa   x*A", 4096, 16, 1024, 0, 0), ("dxa gy*B^T", 4096, 16, 1024, 0, 1), ("dB xa^T*gy", 16, 1024, 4096, 1, 0),
+          ("dA x^T*dxa", 1024, 16, 4096, 1, 0), ("xa r=8", 4096, 8, 1024, 0, 0), ("dB r=64", 64, 1024, 4096, 1, 0)]
+
+
+def bench_skinny(name, m, n, k, ta, tb, iters=20):
+    a = torch.randn((k, m) if ta else (m, k), device="cuda")
+    b = torch.randn((n, k) if tb else (k, n), device="cuda")
+    c = torch.empty(m, n, device="cuda")
+    bm, bn = (16 if m <= 16 else 64), (16 if n <= 16 else 64)
+    tiles = -(-m // bm) * -(-n // bn)
+    splits = max(1, min(592 // tiles, k // 128)) if tiles < 148 else 1
+    ws = torch.empty(max(capi.lib.mft_gemm_splitk_workspace_bytes(m, n, 1, splits), 16), dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), a.shape[1], ta, b.data_ptr(), b.shape[1], tb, c.data_ptr(), n, 1.0, 0.0, None, None,
+                         0, None, 0, None, 0, 1, 0, 0, 0)
+    for _ in range(3):
+        capi.check(capi.lib.mft_gemm_splitk(C.byref(args), splits, ws.data_ptr(), ws.numel(), None), "splitk")
+    torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        capi.lib.mft_gemm_splitk(C.byref(args), splits, ws.data_ptr(), ws.numel(), None)
+        e1.record()
+        e1.synchronize()
+        tot += e0.elapsed_time(e1)
+    us = tot / iters * 1e3
+    mb = (a.numel() + b.numel() + c.numel()) * 4 / 1e6
+    print(f"{name:12s} m={m} n={n} k={k} splits={splits}: {us:7.1f} us  ({mb / us * 1e6 / 1e3:7.1f} GB/s algorithmic)", flush=True)
+
+
+if __name__ == "__main__":
+    if sys.argv[1:] == ["skinny"]:
+        for sh in SKINNY:
+            bench_skinny(*sh)
+        sys.exit(0)
+    which = sys.argv[1:] or ["tf32", "bf16"]
+    for mode in which:
+        for s in SHAPES:
+            bench(*s, bf16=(mode == "bf16"))
