@@ -146,6 +146,7 @@ def main():
     ap.add_argument("--impl", default="mft", choices=["mft", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying the captured CUDA graph")
     ap.add_argument("--precision", default=os.environ.get("MFT_GEMM_PRECISION", "tf32"), choices=["tf32", "bf16"],
                     help="operand precision of the large tensor-core GEMMs (fp32 accumulate either way)")
     a = ap.parse_args()
@@ -168,11 +169,12 @@ def main():
 
     from mobilefinetuner_b200 import capi
     from mobilefinetuner_b200.trainer import Trainer, hostlib
+    from mobilefinetuner_b200.data_parallel import DataParallelTrainer
     hostlib.mft_host_set_gemm_precision(1 if a.precision == "bf16" else 0)
 
     shape, batch, seq, full_ft, r, alpha, desc = CONFIGS[a.config]
     tr = Trainer(batch, seq, shape=shape, full_finetune=full_ft, lora_rank=r, lora_alpha=alpha, world_size=world, rank=rank,
-                 seed=1234)
+                 seed=1234, cuda_graph=not a.no_graph)
     ext = torch.cuda.ExternalStream(tr.stream)
     tokens_rank = batch * seq
     rng = np.random.default_rng(1000 + rank)
@@ -181,7 +183,7 @@ def main():
     host_ids = torch.from_numpy(rng.integers(0, vocab, (nbatches, batch, seq)).astype(np.int32)).pin_memory()
     dev_ids = host_ids.cuda()
     host_loss = torch.zeros(1, dtype=torch.float32).pin_memory()
-    bucket = tr.make_grad_bucket() if world > 1 else None
+    dpt = DataParallelTrainer(tr) if world > 1 else None     # forward/backward -> all-reduce(bucket) -> update
     rt = C.CDLL("libcudart.so.12")
 
     def step_resident(i):
@@ -189,10 +191,7 @@ def main():
         if world == 1:
             tr.step_device(ptr)
         else:
-            tr.forward_backward(ptr)
-            with torch.cuda.stream(ext):
-                dist.all_reduce(bucket)
-            tr.update()
+            dpt.step_device(ptr)
 
     staging = torch.empty(batch, seq, dtype=torch.int32, device="cuda")
 
@@ -203,10 +202,7 @@ def main():
         else:
             with torch.cuda.stream(ext):
                 staging.copy_(src, non_blocking=True)
-            tr.forward_backward(staging.data_ptr())
-            with torch.cuda.stream(ext):
-                dist.all_reduce(bucket)
-            tr.update()
+            dpt.step_device(staging.data_ptr())
             rt.cudaMemcpyAsync(C.c_void_p(host_loss.data_ptr()), C.c_void_p(tr.loss_ptr), 4, 2, C.c_void_p(tr.stream))
             tr.sync()
 
@@ -236,9 +232,8 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = capi.lib.mft_launch_count()
     ms_total = timed(step_resident, a.steps)
-    launches = capi.lib.mft_launch_count() - launches0
+    launches = tr.kernel_launches * a.steps      # kernels per step (counted when the step was captured / last ran eagerly)
     clocks = sampler.stop() if rank == 0 else None
     loss_now = tr.loss()
     for i in range(2):
@@ -246,6 +241,9 @@ def main():
     ms_e2e = timed(step_e2e, a.steps)
 
     # ---- roofline of the dominant kernel (tcgen05 GEMM): events around every launch, inside extra steps
+    tr.enable_graph(False)                       # per-kernel events need eager launches
+    if a.profile_steps > 0:
+        step_resident(0)
     capi.lib.mft_gemm_profile(1)
     t_prof = timed(step_resident, a.profile_steps)
     fl, ms, nl = C.c_double(), C.c_double(), C.c_int64()
@@ -287,7 +285,7 @@ def main():
                       "tf32 (fp32 storage/accumulate; GEMM inputs rounded to TF32 in the TMA; norms/softmax/CE/Adam fp32)"),
             "data": "synthetic",
             "config": {"workload": desc, "config_id": a.config, "tokens_per_step_per_gpu": tokens_rank, "global_tokens_per_step": tokens_step,
-                       "parallelism": f"dp{world}", "timing": "inputs larger than L2: per-step activations+logits "
+                       "parallelism": f"dp{world}", "launch": "eager" if a.no_graph else "cuda graph replay of the captured step", "timing": "inputs larger than L2: per-step activations+logits "
                        f"{tr.arena_high_water / 2**30:.1f} GiB >> 126 MB L2; CUDA events on the compute stream, max over ranks",
                        "loss_last_timed_step": round(loss_now, 5)},
             "e2e": {"value": round(e2e_val, 1), "unit": "tokens/s", "h2d_bytes_per_step": tokens_rank * 4 * world,

@@ -72,6 +72,18 @@ int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo
  * (deterministic). Same operation as mft_gemm otherwise; k2 must be 0 when splits > 1. */
 size_t mft_gemm_splitk_workspace_bytes(int32_t m, int32_t n, int32_t batch, int32_t splits);
 int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* workspace, size_t workspace_bytes, mft_stream_t stream);
+/* Rank-r LoRA factor products (r <= 64), streaming kernels bound by HBM bandwidth; they replace the matmul / MatmulBackward
+ * calls LoRALinear::forward issues for slice.A / slice.B (nn/lora_linear.cpp:66-72, core/backward_functions.cpp:94-138).
+ *   mft_lora_down: y[T,r] (ldy) = alpha * x[T,K] (ldx) * A, with A stored [K,r] (a_is_kr = 1) or [r,K] (a_is_kr = 0).
+ *                  Used for x*A (forward) and dY*B^T (backward). x must be 16-byte aligned, K % 4 == 0, ldx % 4 == 0.
+ *   mft_lora_tn  : out = alpha * S^T * W with S[T,r] (lds), W[T,q] (ldw); out is [r,q] (out_is_rq = 1) or [q,r] (0), row pitch
+ *                  ldo. Used for dB = (xA)^T dY and dA = x^T d(xA). Partial sums over 64-token slabs go to `workspace`
+ *                  (mft_lora_tn_workspace_bytes) and are reduced in a fixed order (deterministic). */
+int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
+                  int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
+size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r);
+int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t ldw, float* out, int64_t ldo, int out_is_rq,
+                int64_t T, int64_t q, int32_t r, float alpha, void* workspace, size_t workspace_bytes, mft_stream_t stream);
 /* 1 if mft_gemm would take the tcgen05 path for these arguments (host-side predicate, no launch). */
 int mft_gemm_uses_tensor_cores(const mft_gemm_args* args);
 /* Measurement aid (no reference counterpart): while enabled, every tensor-core GEMM launch is bracketed by CUDA events on
@@ -236,6 +248,12 @@ int mft_clip_scale(const double* sumsq, float max_norm, float pre_scale, float* 
 int mft_scale_grads(const mft_tensor_slot* slots, int32_t num_slots, const float* scale, mft_stream_t stream);
 int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, float lr, float beta1, float beta2, float eps,
                   float weight_decay, const float* grad_scale, mft_stream_t stream);
+/* Same update with the per-tensor step counters kept in device memory (`steps`, one int32 per slot, zero-initialised by the
+ * caller): they are advanced for every slot that has a gradient and the bias corrections 1-beta^t are evaluated on the
+ * device, so a step needs no per-step host data (lets the whole step be replayed as a CUDA graph). `lr` is one float in
+ * device memory for the same reason: a schedule rewrites it between steps without touching the captured launch. */
+int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots, const float* lr, float beta1, float beta2, float eps,
+                      float weight_decay, const float* grad_scale, int32_t* steps, mft_stream_t stream);
 
 #ifdef __cplusplus
 }

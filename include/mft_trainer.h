@@ -63,7 +63,10 @@ const float* mft_trainer_loss_ptr(mft_trainer* t);       /* device scalar: loss 
 const float* mft_trainer_grad_norm_ptr(mft_trainer* t);  /* device scalar: pre-clip global gradient norm */
 void* mft_trainer_stream(mft_trainer* t);                /* the cudaStream_t the step runs on */
 int mft_trainer_sync(mft_trainer* t);
-void mft_trainer_set_lr(mft_trainer* t, float lr);
+void mft_trainer_set_lr(mft_trainer* t, float lr);          /* written to a device word the update reads: also takes effect under graph replay */
+/* With cfg.use_cuda_graph, each phase is captured after two eager runs and then replayed. This switch turns replay off/on
+ * at run time (e.g. to time individual kernels with events); graphs already captured are kept. */
+void mft_trainer_enable_graph(mft_trainer* t, int enable);
 
 /* Operand precision of the large tensor-core GEMMs in the host layer (process-wide): 0 = TF32 (default), 1 = bf16
  * (fp32 accumulate either way). Also settable with MFT_GEMM_PRECISION=bf16|tf32 in the environment. */
@@ -73,7 +76,7 @@ int mft_host_gemm_precision(void);
 /* Introspection for tests / reports. */
 int32_t mft_trainer_num_trainable(mft_trainer* t);
 int32_t mft_trainer_num_with_grad(mft_trainer* t);       /* tensors that received a gradient in the last step */
-int64_t mft_trainer_kernel_launches(mft_trainer* t);     /* kernels enqueued by the last eager (non-graph) step */
+int64_t mft_trainer_kernel_launches(mft_trainer* t);     /* kernels per step (counted when the step last ran eagerly / was captured) */
 int mft_trainer_param_checksum(mft_trainer* t, int32_t index, double* sum, double* sumabs, int64_t* n);
 size_t mft_trainer_arena_high_water(mft_trainer* t);
 

@@ -53,6 +53,9 @@ SIGNATURES = {
     "mft_transpose_cast_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
     "mft_gemm_splitk_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "mft_gemm_splitk": (C.c_int, [C.POINTER(GemmArgs), i32, vp, sz, vp]),
+    "mft_lora_down": (C.c_int, [vp, i64, vp, i64, C.c_int, vp, i64, i64, i64, i32, f32, vp]),
+    "mft_lora_tn_workspace_bytes": (sz, [i64, i64, i32]),
+    "mft_lora_tn": (C.c_int, [vp, i64, vp, i64, vp, i64, C.c_int, i64, i64, i32, f32, vp, sz, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),
     "mft_gemm_profile": (C.c_int, [C.c_int]),
     "mft_gemm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]),
@@ -93,6 +96,7 @@ SIGNATURES = {
     "mft_clip_scale": (C.c_int, [vp, f32, f32, vp, vp, vp]),
     "mft_scale_grads": (C.c_int, [vp, i32, vp, vp]),
     "mft_adam_step": (C.c_int, [vp, i32, f32, f32, f32, f32, f32, vp, vp]),
+    "mft_adam_step_dev": (C.c_int, [vp, i32, vp, f32, f32, f32, f32, vp, vp, vp]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -27,8 +27,12 @@ bool lookup(GemmaBlockWeights& b, const std::string& name, Target& t) {
 
 // graph/gemma_lora_injector.cpp:30-46 — the generator is shared by every call (static), so the init depends on
 // injection order: layer-major, module order as listed in the spec.
-std::pair<TensorPtr, TensorPtr> make_adapter(int64_t in_dim, int64_t out_dim, int rank) {
+std::mt19937& init_rng() {
     static std::mt19937 rng(42);
+    return rng;
+}
+std::pair<TensorPtr, TensorPtr> make_adapter(int64_t in_dim, int64_t out_dim, int rank) {
+    std::mt19937& rng = init_rng();
     mft_rt::PersistentScope keep;
     const float bound = 1.0f / std::sqrt(static_cast<float>(in_dim));
     std::uniform_real_distribution<float> dist(-bound, bound);
@@ -39,6 +43,8 @@ std::pair<TensorPtr, TensorPtr> make_adapter(int64_t in_dim, int64_t out_dim, in
     return {A, B};
 }
 }  // namespace
+
+void GemmaLoraInjector::reseed_init(unsigned seed) { init_rng().seed(seed); }
 
 // graph/gemma_lora_injector.cpp:50-109
 void GemmaLoraInjector::inject(GemmaModel& model, const GemmaLoraSpec& spec) {

@@ -24,6 +24,9 @@ public:
     GemmaLoraInjector() = default;
     ~GemmaLoraInjector() = default;
     void inject(GemmaModel& model, const GemmaLoraSpec& spec);
+    // Extension: the reference's adapter init draws from one process-wide generator seeded with 42, so a second model built
+    // in the same process starts from different factors. Reseeding restores the first-model state (used by the trainer C ABI).
+    static void reseed_init(unsigned seed = 42);
     std::vector<TensorPtr> get_trainable_params() const;
     void print_info() const;
     void save_lora_safetensors(const std::string& path) const;

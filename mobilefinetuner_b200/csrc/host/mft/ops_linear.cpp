@@ -1,4 +1,5 @@
 // matmul / transpose / permute / fused LoRA linear / tied lm_head — the tensor-core side of the op library.
+#include <cstdlib>
 #include <algorithm>
 #include <cstring>
 #include <stdexcept>
@@ -236,6 +237,42 @@ TensorPtr small_transpose(const TensorPtr& t) {
     return o;
 }
 
+// MFT_LORA_SKINNY: bit 0 routes x*A / dY*B^T through mft_lora_down, bit 1 routes dA / dB through mft_lora_tn; the rest goes
+// through the general GEMM dispatch (SIMT split-K for these shapes).
+int skinny_mask() {
+    static const int m = [] { const char* e = std::getenv("MFT_LORA_SKINNY"); return e ? std::atoi(e) : 2; }();
+    return m;
+}
+// y[T,r] = alpha * x[T,K] * A   (A [K,r] when a_is_kr, else [r,K])
+void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, bool a_is_kr, int64_t r, float alpha, const TensorPtr& y) {
+    if ((skinny_mask() & 1) && r >= 1 && r <= 64) {
+        mft_rt::check(mft_lora_down(x->dev_f32(), x->ld(), A->dev_f32(), A->ld(), a_is_kr ? 1 : 0, y->dev_f32_out(), r, T, K, int32_t(r), alpha,
+                                    mft_rt::stream()), "mft_lora_down");
+        return;
+    }
+    GemmCall g;
+    g.m = T; g.n = r; g.k = K; g.alpha = alpha;
+    g.a = x->dev_f32(); g.lda = x->ld(); g.trans_a = 0;
+    g.b = A->dev_f32(); g.ldb = A->ld(); g.trans_b = a_is_kr ? 0 : 1;
+    g.c = y->dev_f32_out(); g.ldc = r;
+    run_gemm(g);
+}
+// out = S[T,r]^T W[T,q], written as [r,q] (out_is_rq) or [q,r]
+void lora_tn(const TensorPtr& S, const TensorPtr& W, int64_t T, int64_t q, int64_t r, bool out_is_rq, const TensorPtr& out) {
+    if ((skinny_mask() & 2) && r >= 1 && r <= 64) {
+        const size_t wsb = mft_lora_tn_workspace_bytes(T, q, int32_t(r));
+        mft_rt::check(mft_lora_tn(S->dev_f32(), S->ld(), W->dev_f32(), W->ld(), out->dev_f32_out(), out->ld(), out_is_rq ? 1 : 0, T, q, int32_t(r),
+                                  1.0f, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_lora_tn");
+        return;
+    }
+    GemmCall g;
+    g.trans_a = 1; g.trans_b = 0; g.k = T;
+    if (out_is_rq) { g.m = r; g.n = q; g.a = S->dev_f32(); g.lda = S->ld(); g.b = W->dev_f32(); g.ldb = W->ld(); }
+    else { g.m = q; g.n = r; g.a = W->dev_f32(); g.lda = W->ld(); g.b = S->dev_f32(); g.ldb = S->ld(); }
+    g.c = out->dev_f32_out(); g.ldc = out->ld();
+    run_gemm(g);
+}
+
 // One node for  y = x W (+b) + sum_i s_i (x A_i) B_i.
 // Backward (per term, s folded into xa / dxa):   dB = xa^T gy ;  dxa = s gy B^T ;  dA = x^T dxa ;
 // dx = gy W^T + sum dxa A^T (rank-r update fused as second K segment) ; dW = x^T gy ; db = colsum(gy).
@@ -255,31 +292,16 @@ public:
             const bool wa = wants_grad(t.A), wb = wants_grad(t.B);
             if (wb) {                                        // dB = (s x A)^T gy, written in B's own layout
                 auto gB = Tensor::make(t.B->shape(), kFloat32);
-                GemmCall g;
-                g.trans_a = 1; g.trans_b = 0; g.k = T;
-                if (l.b_r_out) { g.m = l.r; g.n = out; g.a = xa_[i]->dev_f32(); g.lda = xa_[i]->ld(); g.b = gy->dev_f32(); g.ldb = gy->ld(); }
-                else { g.m = out; g.n = l.r; g.a = gy->dev_f32(); g.lda = gy->ld(); g.b = xa_[i]->dev_f32(); g.ldb = xa_[i]->ld(); }
-                g.c = gB->dev_f32_out(); g.ldc = t.B->shape()[1];
-                run_gemm(g);
+                lora_tn(xa_[i], gy, T, out, l.r, l.b_r_out, gB);
                 grads[3 + 2 * i + 1] = gB;
             }
             if (wa || need_dx) {                             // dxa = s gy B^T   [T, r]
                 dxa[i] = Tensor::make({T, l.r}, kFloat32);
-                GemmCall g;
-                g.m = T; g.n = l.r; g.k = out; g.alpha = t.scale;
-                g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0;
-                g.b = t.B->dev_f32(); g.ldb = t.B->ld(); g.trans_b = l.b_r_out ? 1 : 0;
-                g.c = dxa[i]->dev_f32_out(); g.ldc = l.r;
-                run_gemm(g);
+                lora_down(gy, T, out, t.B, /*a_is_kr=*/!l.b_r_out, l.r, t.scale, dxa[i]);   // contraction over `out`
             }
             if (wa) {                                        // dA = x^T dxa, in A's own layout
                 auto gA = Tensor::make(t.A->shape(), kFloat32);
-                GemmCall g;
-                g.trans_a = 1; g.trans_b = 0; g.k = T;
-                if (l.a_in_r) { g.m = in; g.n = l.r; g.a = x_->dev_f32(); g.lda = x_->ld(); g.b = dxa[i]->dev_f32(); g.ldb = l.r; }
-                else { g.m = l.r; g.n = in; g.a = dxa[i]->dev_f32(); g.lda = l.r; g.b = x_->dev_f32(); g.ldb = x_->ld(); }
-                g.c = gA->dev_f32_out(); g.ldc = t.A->shape()[1];
-                run_gemm(g);
+                lora_tn(dxa[i], x_, T, in, l.r, /*out_is_rq=*/!l.a_in_r, gA);
                 grads[3 + 2 * i] = gA;
             }
         }
@@ -351,12 +373,7 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     for (size_t i = 0; i < terms.size(); ++i) {
         TermLayout l = classify(terms[i], in, out);
         xa[i] = Tensor::make({T, l.r}, kFloat32);            // s * x A   (kept for dB)
-        GemmCall g;
-        g.m = T; g.n = l.r; g.k = in; g.alpha = terms[i].scale;
-        g.a = x->dev_f32(); g.lda = in; g.trans_a = 0;
-        g.b = terms[i].A->dev_f32(); g.ldb = terms[i].A->ld(); g.trans_b = l.a_in_r ? 0 : 1;
-        g.c = xa[i]->dev_f32_out(); g.ldc = l.r;
-        run_gemm(g);
+        lora_down(x, T, in, terms[i].A, l.a_in_r, l.r, terms[i].scale, xa[i]);
         bt[i] = l.b_r_out ? small_transpose(terms[i].B) : terms[i].B;   // [out, r] K-major
     }
     GemmCall g;

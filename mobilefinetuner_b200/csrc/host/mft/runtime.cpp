@@ -171,6 +171,13 @@ void memset0(void* dst, size_t bytes) {
     cuda_ok(cudaMemsetAsync(dst, 0, bytes, static_cast<cudaStream_t>(stream())), "memset");
 }
 
+void* pinned_alloc(size_t bytes) {
+    void* p = nullptr;
+    cuda_ok(cudaMallocHost(&p, bytes ? bytes : 16), "cudaMallocHost");
+    return p;
+}
+void pinned_free(void* p) { if (p) cudaFreeHost(p); }
+
 void* workspace(size_t bytes) {
     if (bytes <= g_ws_bytes) return g_ws;
     // Grown rarely (first steps only). Older scratch may still be in flight: retire it to the pool, which is

@@ -21,6 +21,8 @@ void d2h_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t wid
 void d2d(void* dst, const void* src, size_t bytes);
 void d2d_2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t rows);
 void memset0(void* dst, size_t bytes);
+void* pinned_alloc(size_t bytes);               // page-locked host memory (persistent staging buffers)
+void pinned_free(void* p);
 
 // Step arena: between arena_begin() and arena_end() every dev_alloc is a bump allocation from one slab that
 // arena_reset() rewinds; persistent allocations (parameters, optimizer state, cached weight shadows) are made

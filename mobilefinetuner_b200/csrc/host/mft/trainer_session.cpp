@@ -51,8 +51,13 @@ struct mft_trainer {
     float* loss_dev = nullptr;     // persistent scalars
     float* norm_dev = nullptr;
     float* scale_dev = nullptr;
-    void* slots_dev = nullptr;
-    size_t slots_bytes = 0;
+    float* lr_dev = nullptr;       // learning rate lives on the device so a schedule never invalidates the captured step
+    float* lr_host = nullptr;      // pinned staging word for it
+    void* slots_dev[2] = {nullptr, nullptr};     // device slot table (param/grad/m/v per trainable tensor)
+    mft_tensor_slot* slots_host[2] = {nullptr, nullptr};   // pinned staging copies; [1] = gradients read from the all-reduced bucket
+    std::vector<TensorPtr> m, v;   // Adam moments, owned by the trainer; step counters live on the device
+    int32_t* steps_dev = nullptr;
+    double* sumsq_dev = nullptr;
     float* bucket = nullptr;
     int64_t bucket_elems = 0, grad_elems = 0;
     std::vector<int64_t> offsets;
@@ -60,8 +65,11 @@ struct mft_trainer {
     int with_grad = 0;
     int64_t launches = 0;
     bool arena_on = false;
-    // CUDA graph of one whole step (forward .. Adam), captured after warm-up
-    cudaGraphExec_t graph_exec = nullptr;
+    // CUDA graphs (captured after two eager runs of the same phase): 0 = whole step, 1 = forward/backward(+pack), 2 = update
+    cudaGraphExec_t graph_exec[3] = {nullptr, nullptr, nullptr};
+    int eager_runs[3] = {0, 0, 0};
+    int64_t phase_launches[3] = {0, 0, 0};
+    bool graph_enabled = true;     // runtime switch (mft_trainer_enable_graph); only effective when cfg.use_cuda_graph
     int eager_steps = 0;
 };
 
@@ -145,6 +153,7 @@ void build(mft_trainer* t) {
         t->gemma->init_lora_modules();
         GemmaLoraSpec s = GemmaLoraSpec::full_attn_mlp();
         s.rank = c.lora_rank; s.alpha = c.lora_alpha; s.dropout = 0.0f;
+        GemmaLoraInjector::reseed_init();       // same adapter init for every trainer of a process
         t->gemma_inj.inject(*t->gemma, s);
         t->trainable = t->gemma_inj.get_trainable_params();
         for (auto& p : t->trainable) (void)p->dev();
@@ -154,7 +163,23 @@ void build(mft_trainer* t) {
     t->ids = std::make_shared<Tensor>(std::vector<int64_t>{c.batch, c.seq_len}, kInt32, kCPU);
     float* scalars = static_cast<float*>(mft_rt::dev_alloc(64));
     mft_rt::memset0(scalars, 64);
-    t->loss_dev = scalars; t->norm_dev = scalars + 1; t->scale_dev = scalars + 2;
+    t->loss_dev = scalars; t->norm_dev = scalars + 1; t->scale_dev = scalars + 2; t->lr_dev = scalars + 3;
+    t->lr_host = static_cast<float*>(mft_rt::pinned_alloc(sizeof(float)));
+    *t->lr_host = c.lr;
+    mft_rt::h2d(t->lr_dev, t->lr_host, sizeof(float));
+    const size_t nt = t->trainable.size();
+    t->m.resize(nt); t->v.resize(nt);
+    for (size_t i = 0; i < nt; ++i) {   // zero-filled; tensors that never receive a gradient simply keep them untouched
+        t->m[i] = zeros(t->trainable[i]->shape(), kFloat32, kCPU);
+        t->v[i] = zeros(t->trainable[i]->shape(), kFloat32, kCPU);
+    }
+    t->steps_dev = static_cast<int32_t*>(mft_rt::dev_alloc(nt * sizeof(int32_t) + 16));
+    mft_rt::memset0(t->steps_dev, nt * sizeof(int32_t) + 16);
+    for (int k = 0; k < 2; ++k) {
+        t->slots_dev[k] = mft_rt::dev_alloc(nt * sizeof(mft_tensor_slot) + 16);
+        t->slots_host[k] = static_cast<mft_tensor_slot*>(mft_rt::pinned_alloc(nt * sizeof(mft_tensor_slot) + 16));
+    }
+    t->sumsq_dev = static_cast<double*>(mft_rt::dev_alloc(64));
     t->offsets.resize(t->trainable.size());
     int64_t off = 0;
     for (size_t i = 0; i < t->trainable.size(); ++i) { t->offsets[i] = off; off += (t->trainable[i]->numel() + 3) / 4 * 4; }
@@ -175,55 +200,74 @@ void forward_backward(mft_trainer* t) {
     }
 }
 
-// Slot table for clip + Adam; when a bucket is set the gradients are first packed into it (and read from it).
-void update(mft_trainer* t, bool pack_only, bool packed) {
+// Slot table for pack / clip / Adam. All state is on the device (moments, step counters, clip factor), so the phase needs no
+// per-step host data and can be replayed from a CUDA graph. `packed`: gradients are read from the all-reduced bucket.
+const mft_tensor_slot* upload_slots(mft_trainer* t, bool packed) {
     const size_t n = t->trainable.size();
-    std::vector<mft_tensor_slot> host(n);
-    // Adam bookkeeping goes through the optimizer so per-tensor step counts behave like optim/adam.cpp:35-43
-    if (pack_only) {
-        for (size_t i = 0; i < n; ++i) {
-            std::memset(&host[i], 0, sizeof(mft_tensor_slot));
-            host[i].n = t->trainable[i]->numel();
-            host[i].grad = t->grads[i] ? t->grads[i]->dev_f32_mut() : nullptr;
-            host[i].bucket_offset = t->offsets[i];
-        }
-        const size_t bytes = n * sizeof(mft_tensor_slot);
-        if (bytes > t->slots_bytes) {
-            mft_rt::PersistentScope keep;
-            if (t->slots_dev) mft_rt::dev_free(t->slots_dev, t->slots_bytes);
-            t->slots_bytes = bytes * 2;
-            t->slots_dev = mft_rt::dev_alloc(t->slots_bytes);
-        }
-        mft_rt::h2d(t->slots_dev, host.data(), bytes);
-        mft_rt::check(mft_pack_grads(static_cast<const mft_tensor_slot*>(t->slots_dev), int32_t(n), t->bucket, mft_rt::stream()), "mft_pack_grads");
+    for (size_t i = 0; i < n; ++i) {
+        mft_tensor_slot& s = t->slots_host[packed][i];
+        std::memset(&s, 0, sizeof(s));
+        s.n = t->trainable[i]->numel();
+        s.param = t->trainable[i]->dev_f32_mut();          // bumps the version: cached K-major / bf16 shadows get rebuilt
+        s.m = t->m[i]->dev_f32_mut();
+        s.v = t->v[i]->dev_f32_mut();
+        s.bucket_offset = t->offsets[i];
+        if (t->grads[i]) s.grad = packed ? t->bucket + t->offsets[i] : t->grads[i]->dev_f32_mut();
+    }
+    // one pinned table per variant: the async upload (or its graph memcpy node) reads the host copy when it executes
+    mft_rt::h2d(t->slots_dev[packed], t->slots_host[packed], n * sizeof(mft_tensor_slot));
+    return static_cast<const mft_tensor_slot*>(t->slots_dev[packed]);
+}
+
+void pack_phase(mft_trainer* t) {
+    const mft_tensor_slot* slots = upload_slots(t, false);
+    mft_rt::check(mft_pack_grads(slots, int32_t(t->trainable.size()), t->bucket, mft_rt::stream()), "mft_pack_grads");
+}
+
+void update_phase(mft_trainer* t, bool packed) {
+    const int32_t n = int32_t(t->trainable.size());
+    const mft_tensor_slot* slots = upload_slots(t, packed);
+    const size_t wsb = mft_grad_sumsq_workspace_bytes();
+    mft_rt::check(mft_grad_sumsq(slots, n, t->sumsq_dev, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_grad_sumsq");
+    const float pre = packed && t->cfg.world_size > 1 ? 1.0f / float(t->cfg.world_size) : 1.0f;
+    mft_rt::check(mft_clip_scale(t->sumsq_dev, t->cfg.clip_norm, pre, t->scale_dev, t->norm_dev, mft_rt::stream()), "mft_clip_scale");
+    mft_rt::check(mft_adam_step_dev(slots, n, t->lr_dev, t->cfg.beta1, t->cfg.beta2, t->cfg.eps, t->cfg.weight_decay,
+                                    t->scale_dev, t->steps_dev, mft_rt::stream()), "mft_adam_step_dev");
+    for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
+}
+
+// Runs one phase eagerly, or (cfg.use_cuda_graph) captures it into a CUDA graph after two eager runs and replays it.
+// The step arena makes every intermediate address identical from step to step, which is what makes replay valid.
+template <typename Body>
+void run_phase(mft_trainer* t, int phase, Body body) {
+    cudaStream_t st = static_cast<cudaStream_t>(mft_rt::stream());
+    const bool want_graph = t->cfg.use_cuda_graph && t->graph_enabled;
+    if (want_graph && t->graph_exec[phase]) {
+        if (cudaGraphLaunch(t->graph_exec[phase], st) != cudaSuccess) mft_rt::fail("cudaGraphLaunch failed");
         return;
     }
-    // global norm over the tensors that have gradients, on the device
-    std::vector<TensorPtr> params = t->trainable;
-    for (size_t i = 0; i < n; ++i) {
-        std::memset(&host[i], 0, sizeof(mft_tensor_slot));
-        host[i].n = params[i]->numel();
-        if (t->grads[i]) host[i].grad = packed ? t->bucket + t->offsets[i] : t->grads[i]->dev_f32_mut();
+    const int64_t before = mft_launch_count();
+    if (want_graph && t->eager_runs[phase] >= 2) {
+        cudaGraph_t graph = nullptr;
+        if (cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) != cudaSuccess) mft_rt::fail("cudaStreamBeginCapture failed");
+        try { body(); } catch (...) {
+            cudaStreamEndCapture(st, &graph);
+            if (graph) cudaGraphDestroy(graph);
+            throw;
+        }
+        if (cudaStreamEndCapture(st, &graph) != cudaSuccess || !graph) mft_rt::fail("cudaStreamEndCapture failed (an operation in the step is not capturable)");
+        cudaGraphExec_t exec = nullptr;
+        cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) mft_rt::fail(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        t->graph_exec[phase] = exec;
+        t->phase_launches[phase] = mft_launch_count() - before;
+        if (cudaGraphLaunch(exec, st) != cudaSuccess) mft_rt::fail("cudaGraphLaunch failed");
+        return;
     }
-    const size_t bytes = n * sizeof(mft_tensor_slot);
-    if (bytes > t->slots_bytes) {
-        mft_rt::PersistentScope keep;
-        if (t->slots_dev) mft_rt::dev_free(t->slots_dev, t->slots_bytes);
-        t->slots_bytes = bytes * 2;
-        t->slots_dev = mft_rt::dev_alloc(t->slots_bytes);
-    }
-    mft_rt::h2d(t->slots_dev, host.data(), bytes);
-    static double* sumsq = nullptr;
-    if (!sumsq) { mft_rt::PersistentScope keep; sumsq = static_cast<double*>(mft_rt::dev_alloc(64)); }
-    const size_t wsb = mft_grad_sumsq_workspace_bytes();
-    mft_rt::check(mft_grad_sumsq(static_cast<const mft_tensor_slot*>(t->slots_dev), int32_t(n), sumsq, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_grad_sumsq");
-    const float pre = packed && t->cfg.world_size > 1 ? 1.0f / float(t->cfg.world_size) : 1.0f;
-    mft_rt::check(mft_clip_scale(sumsq, t->cfg.clip_norm, pre, t->scale_dev, t->norm_dev, mft_rt::stream()), "mft_clip_scale");
-    // Adam with the clip factor read on the device (per-tensor step counts advance only for tensors with a gradient)
-    std::vector<float*> gp(n, nullptr);
-    for (size_t i = 0; i < n; ++i) gp[i] = host[i].grad;
-    t->opt->step_device(params, gp, t->scale_dev);
-    for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
+    body();
+    ++t->eager_runs[phase];
+    t->phase_launches[phase] = mft_launch_count() - before;
 }
 
 }  // namespace
@@ -251,7 +295,9 @@ extern "C" int mft_trainer_create(const mft_trainer_config* cfg, mft_trainer** o
 extern "C" void mft_trainer_destroy(mft_trainer* t) {
     if (!t) return;
     try { mft_rt::sync(); } catch (...) {}
-    if (t->graph_exec) cudaGraphExecDestroy(t->graph_exec);
+    for (auto& g : t->graph_exec) if (g) cudaGraphExecDestroy(g);
+    for (int k = 0; k < 2; ++k) mft_rt::pinned_free(t->slots_host[k]);
+    mft_rt::pinned_free(t->lr_host);
     delete t;
 }
 
@@ -264,10 +310,8 @@ extern "C" int mft_trainer_next_synthetic_batch(mft_trainer* t, int32_t* host_id
 }
 
 static int run_step(mft_trainer* t) {
-    const int64_t before = mft_launch_count();
-    forward_backward(t);
-    update(t, false, false);
-    t->launches = mft_launch_count() - before;
+    run_phase(t, 0, [t] { forward_backward(t); update_phase(t, false); });
+    t->launches = t->phase_launches[0];
     ++t->eager_steps;
     return 0;
 }
@@ -306,12 +350,10 @@ extern "C" int mft_trainer_forward_backward(mft_trainer* t, const int32_t* dev_i
     if (!t || !dev_ids) return fail("mft_trainer_forward_backward: null argument");
     if (!t->bucket) return fail("mft_trainer_forward_backward: set a gradient bucket first");
     try {
-        const int64_t before = mft_launch_count();
         const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
         mft_rt::d2d(t->ids->dev_out(), dev_ids, bytes);
-        forward_backward(t);
-        update(t, true, false);
-        t->launches = mft_launch_count() - before;
+        run_phase(t, 1, [t] { forward_backward(t); pack_phase(t); });
+        t->launches = t->phase_launches[1];
         return 0;
     } catch (const std::exception& e) { return fail("mft_trainer_forward_backward: %s", e.what()); }
 }
@@ -319,9 +361,8 @@ extern "C" int mft_trainer_forward_backward(mft_trainer* t, const int32_t* dev_i
 extern "C" int mft_trainer_update(mft_trainer* t) {
     if (!t) return fail("mft_trainer_update: null argument");
     try {
-        const int64_t before = mft_launch_count();
-        update(t, false, true);
-        t->launches += mft_launch_count() - before;
+        run_phase(t, 2, [t] { update_phase(t, true); });
+        t->launches = t->phase_launches[1] + t->phase_launches[2];
         return 0;
     } catch (const std::exception& e) { return fail("mft_trainer_update: %s", e.what()); }
 }
@@ -332,9 +373,28 @@ extern "C" void* mft_trainer_stream(mft_trainer*) { return mft_rt::stream(); }
 extern "C" int mft_trainer_sync(mft_trainer*) {
     try { mft_rt::sync(); return 0; } catch (const std::exception& e) { return fail("mft_trainer_sync: %s", e.what()); }
 }
+extern "C" void mft_trainer_enable_graph(mft_trainer* t, int enable) {
+    if (!t) return;
+    const bool on = enable != 0;
+    if (on && !t->graph_enabled) {   // eager steps in between may have moved cached buffers: capture again
+        for (int p = 0; p < 3; ++p) {
+            if (t->graph_exec[p]) { cudaGraphExecDestroy(t->graph_exec[p]); t->graph_exec[p] = nullptr; }
+            t->eager_runs[p] = 0;
+        }
+    }
+    t->graph_enabled = on;
+}
 extern "C" void mft_host_set_gemm_precision(int bf16) { ops::internal::set_gemm_precision(bf16); }
 extern "C" int mft_host_gemm_precision(void) { return ops::internal::gemm_precision(); }
-extern "C" void mft_trainer_set_lr(mft_trainer* t, float lr) { if (t && t->opt) t->opt->set_learning_rate(lr); }
+extern "C" void mft_trainer_set_lr(mft_trainer* t, float lr) {
+    if (!t || !t->opt) return;
+    t->opt->set_learning_rate(lr);
+    try {
+        mft_rt::sync();              // the staging word may still be in flight from the previous update
+        *t->lr_host = lr;
+        mft_rt::h2d(t->lr_dev, t->lr_host, sizeof(float));
+    } catch (...) {}
+}
 extern "C" int32_t mft_trainer_num_trainable(mft_trainer* t) { return t ? int32_t(t->trainable.size()) : 0; }
 extern "C" int32_t mft_trainer_num_with_grad(mft_trainer* t) { return t ? t->with_grad : 0; }
 extern "C" int64_t mft_trainer_kernel_launches(mft_trainer* t) { return t ? t->launches : 0; }

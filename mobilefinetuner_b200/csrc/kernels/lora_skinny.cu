@@ -1,0 +1,231 @@
+// Rank-r LoRA factor products. These are bandwidth-bound (one streaming read of a [tokens, width] activation against a
+// matrix with r <= 64 columns) and far too narrow for a 128-row tensor-core tile or a 64x64 SIMT tile, so they get two
+// dedicated streaming kernels with enough independent 128-bit loads in flight per SM to approach HBM bandwidth:
+//   lora_down : y[T,r]  = alpha * x[T,K] * A            (x*A in the forward pass, dY*B^T in the backward pass)
+//   lora_tn   : out     = alpha * S[T,r]^T * W[T,q]      (dB = (xA)^T dY and dA = x^T d(xA): contraction over all tokens)
+// Reference: the matmul/MatmulBackward calls LoRALinear::forward generates for slice.A / slice.B
+// (nn/lora_linear.cpp:66-72, core/backward_functions.cpp:94-138). Algorithmic bytes: 4*T*K (+4*T*r) and 4*T*q (+4*T*r).
+#include "common.cuh"
+
+namespace mft {
+
+// lora_down: one warp owns RPW token rows; lane l takes k = l, l+32, ... (coalesced 128-byte row segments), keeps
+// RPW x RMAX dot products in registers and warp-reduces them once per row. The A chunk sits in shared memory as
+// [k][RMAX+4]: a lane reads its k-row with 128-bit loads and the +4 pitch keeps the eight lanes of a quarter-warp on
+// distinct banks. The grid is sized by the launcher (RPW) so that every SM holds several CTAs: one CTA's staging of A
+// overlaps another's streaming.
+template <int RPW, int RMAX, int KC>
+__global__ void __launch_bounds__(256)
+lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
+                 float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha) {
+    constexpr int PITCH = RMAX + 4;
+    extern __shared__ __align__(16) float At[];     // [KC][PITCH]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t row0 = (int64_t(blockIdx.x) * 8 + warp) * RPW;
+    const float* xr[RPW];
+    bool live[RPW];
+#pragma unroll
+    for (int i = 0; i < RPW; ++i) { live[i] = row0 + i < T; xr[i] = x + (live[i] ? row0 + i : 0) * ldx; }
+    float acc[RPW][RMAX];
+#pragma unroll
+    for (int i = 0; i < RPW; ++i)
+#pragma unroll
+        for (int c = 0; c < RMAX; ++c) acc[i][c] = 0.f;
+
+    for (int k0 = 0; k0 < K; k0 += KC) {
+        const int kc = min(KC, K - k0);
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < KC * RMAX; idx += 256) {
+            int kk, c;
+            if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
+            float v = 0.f;
+            if (kk < kc && c < r) v = a_is_kr ? __ldg(a + int64_t(k0 + kk) * lda + c) : __ldg(a + int64_t(c) * lda + k0 + kk);
+            At[kk * PITCH + c] = v;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < KC / 32; ++j) {
+            const int kk = j * 32 + lane;
+            float xv[RPW];
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) xv[i] = (live[i] && kk < kc) ? ld_stream(xr[i] + k0 + kk) : 0.f;
+            const float4* arow = reinterpret_cast<const float4*>(At + kk * PITCH);
+#pragma unroll
+            for (int c4 = 0; c4 < RMAX / 4; ++c4) {
+                const float4 av = arow[c4];
+#pragma unroll
+                for (int i = 0; i < RPW; ++i) {
+                    acc[i][c4 * 4 + 0] = fmaf(xv[i], av.x, acc[i][c4 * 4 + 0]);
+                    acc[i][c4 * 4 + 1] = fmaf(xv[i], av.y, acc[i][c4 * 4 + 1]);
+                    acc[i][c4 * 4 + 2] = fmaf(xv[i], av.z, acc[i][c4 * 4 + 2]);
+                    acc[i][c4 * 4 + 3] = fmaf(xv[i], av.w, acc[i][c4 * 4 + 3]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < RPW; ++i) {
+#pragma unroll
+        for (int c = 0; c < RMAX; ++c) {
+            const float v = warp_sum(acc[i][c]);
+            if (lane == (c & 31) && c < r && live[i]) y[(row0 + i) * ldy + c] = v * alpha;
+        }
+    }
+}
+
+// lora_tn: CTA = kTnRG row-groups x kTnCT column-threads over kTnRows token rows; a thread owns CPT adjacent columns of
+// W and RMAX accumulators per column. Row-groups are summed through shared memory in a fixed order, so one partial
+// [r, cols] tile leaves the CTA; the partials over the token splits are summed (fixed order again) by the reduce kernel.
+constexpr int kTnRows = 128, kTnRG = 4, kTnCT = 64;
+
+template <int CPT, int RMAX>
+__global__ void __launch_bounds__(kTnRG * kTnCT)
+lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
+               float* __restrict__ partial, int64_t T, int q, int r) {
+    extern __shared__ __align__(16) float sm[];
+    float* Ss = sm;                                  // [kTnRows][RMAX]
+    float* red = sm + kTnRows * RMAX;                // [RMAX][kTnCT * CPT]
+    const int ct = threadIdx.x % kTnCT, rg = threadIdx.x / kTnCT;
+    const int col = (blockIdx.x * kTnCT + ct) * CPT;
+    const int64_t t0 = int64_t(blockIdx.y) * kTnRows;
+    for (int idx = threadIdx.x; idx < kTnRows * RMAX; idx += kTnRG * kTnCT) {
+        const int tt = idx / RMAX, c = idx % RMAX;
+        Ss[idx] = (t0 + tt < T && c < r) ? __ldg(s + (t0 + tt) * lds + c) : 0.f;
+    }
+    __syncthreads();
+    float acc[CPT][RMAX];
+#pragma unroll
+    for (int e = 0; e < CPT; ++e)
+#pragma unroll
+        for (int c = 0; c < RMAX; ++c) acc[e][c] = 0.f;
+    constexpr int RPG = kTnRows / kTnRG;             // rows per row-group (32)
+    constexpr int U = 8;
+    const bool colok = col < q;                      // q % CPT == 0 is guaranteed by the launcher
+#pragma unroll 1
+    for (int u0 = 0; u0 < RPG; u0 += U) {
+        float wv[U][CPT];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t row = t0 + rg * RPG + u0 + u;
+            const bool ok = colok && row < T;
+            if (CPT == 2) {
+                const float2 v = ok ? ld_stream(reinterpret_cast<const float2*>(w + row * ldw + col)) : make_float2(0.f, 0.f);
+                wv[u][0] = v.x; wv[u][CPT - 1] = v.y;
+            } else {
+                wv[u][0] = ok ? ld_stream(w + row * ldw + col) : 0.f;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const float4* srow = reinterpret_cast<const float4*>(Ss + (rg * RPG + u0 + u) * RMAX);
+#pragma unroll
+            for (int c4 = 0; c4 < RMAX / 4; ++c4) {
+                const float4 sv = srow[c4];          // same address for the whole warp: broadcast
+#pragma unroll
+                for (int e = 0; e < CPT; ++e) {
+                    acc[e][c4 * 4 + 0] = fmaf(wv[u][e], sv.x, acc[e][c4 * 4 + 0]);
+                    acc[e][c4 * 4 + 1] = fmaf(wv[u][e], sv.y, acc[e][c4 * 4 + 1]);
+                    acc[e][c4 * 4 + 2] = fmaf(wv[u][e], sv.z, acc[e][c4 * 4 + 2]);
+                    acc[e][c4 * 4 + 3] = fmaf(wv[u][e], sv.w, acc[e][c4 * 4 + 3]);
+                }
+            }
+        }
+    }
+    // fixed-order reduction over the row-groups
+    for (int g = 0; g < kTnRG; ++g) {
+        if (rg == g) {
+#pragma unroll
+            for (int c = 0; c < RMAX; ++c)
+#pragma unroll
+                for (int e = 0; e < CPT; ++e) {
+                    float* dst = red + c * (kTnCT * CPT) + ct * CPT + e;
+                    *dst = (g == 0) ? acc[e][c] : *dst + acc[e][c];
+                }
+        }
+        __syncthreads();
+    }
+    float* P = partial + size_t(blockIdx.y) * size_t(r) * q;
+    for (int idx = threadIdx.x; idx < r * kTnCT * CPT; idx += kTnRG * kTnCT) {
+        const int c = idx / (kTnCT * CPT), cc = idx % (kTnCT * CPT);
+        const int gcol = blockIdx.x * kTnCT * CPT + cc;
+        if (gcol < q) P[size_t(c) * q + gcol] = red[c * (kTnCT * CPT) + cc];
+    }
+}
+
+// out[c][col] (out_is_rq) or out[col][c] = alpha * sum over splits, fixed order
+__global__ void lora_tn_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int64_t ldo, int out_is_rq,
+                                      int splits, int q, int r, float alpha) {
+    const int64_t n = int64_t(r) * q;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        const int c = int(idx / q), col = int(idx % q);
+        float v = 0.f;
+        for (int sp = 0; sp < splits; ++sp) v += partial[size_t(sp) * n + idx];
+        v *= alpha;
+        if (out_is_rq) out[int64_t(c) * ldo + col] = v; else out[int64_t(col) * ldo + c] = v;
+    }
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+template <int RPW, int RMAX, int KC>
+static void launch_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, int64_t T, int K,
+                        int r, float alpha, cudaStream_t st) {
+    constexpr size_t smem = size_t(KC) * (RMAX + 4) * sizeof(float);
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(lora_down_kernel<RPW, RMAX, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); attr = true; }
+    lora_down_kernel<RPW, RMAX, KC><<<unsigned(ceil_div(T, int64_t(8 * RPW))), 256, smem, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha);
+}
+
+extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
+                             int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
+    if (T == 0 || r == 0) return 0;
+    if (!x || !a || !y) return set_error(1, "mft_lora_down: null pointer");
+    if (r < 1 || r > 64) return set_error(1, "mft_lora_down: rank %d outside 1..64", r);
+    if (K < 1 || K > (int64_t(1) << 30)) return set_error(1, "mft_lora_down: K out of range");
+    if (ceil_div(T, int64_t(8)) > 0x7fffffff) return set_error(1, "mft_lora_down: too many rows");
+    cudaStream_t st = as_stream(stream);
+    const int k = int(K);
+    if (r <= 16) {
+        // rows per warp: as many as still leave >= 2 CTAs per SM
+        if (T >= int64_t(32) * 2 * kNumSMs) launch_down<4, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+        else if (T >= int64_t(16) * kNumSMs) launch_down<2, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+        else launch_down<1, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+    } else {
+        launch_down<1, 64, 128>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+    }
+    MFT_CHECK_LAUNCH("mft_lora_down");
+    return 0;
+}
+
+extern "C" size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r) {
+    return size_t(ceil_div(T, kTnRows)) * size_t(r) * size_t(q) * sizeof(float);
+}
+
+extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t ldw, float* out, int64_t ldo, int out_is_rq,
+                           int64_t T, int64_t q, int32_t r, float alpha, void* workspace, size_t workspace_bytes, mft_stream_t stream) {
+    if (q == 0 || r == 0) return 0;
+    if (!s || !w || !out) return set_error(1, "mft_lora_tn: null pointer");
+    if (r < 1 || r > 64) return set_error(1, "mft_lora_tn: rank %d outside 1..64", r);
+    if (T == 0) return set_error(1, "mft_lora_tn: empty contraction");
+    if (!workspace || workspace_bytes < mft_lora_tn_workspace_bytes(T, q, r)) return set_error(1, "mft_lora_tn: workspace too small");
+    const int64_t splits = ceil_div(T, kTnRows);
+    if (splits > 65535) return set_error(1, "mft_lora_tn: too many tokens");
+    cudaStream_t st = as_stream(stream);
+    float* partial = static_cast<float*>(workspace);
+    const bool vec = r <= 16 && (q & 1) == 0 && (ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(w) & 7) == 0;
+    if (vec) {
+        const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
+        lora_tn_kernel<2, 16><<<dim3(unsigned(ceil_div(q, kTnCT * 2)), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r);
+    } else {
+        const size_t smem = (size_t(kTnRows) * 64 + size_t(64) * kTnCT) * sizeof(float);
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(lora_tn_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); attr = true; }
+        lora_tn_kernel<1, 64><<<dim3(unsigned(ceil_div(q, kTnCT)), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r);
+    }
+    add_launches(1);
+    lora_tn_reduce_kernel<<<stream_grid(int64_t(r) * q, 256), 256, 0, st>>>(partial, out, ldo, out_is_rq, int(splits), int(q), r, alpha);
+    MFT_CHECK_LAUNCH("mft_lora_tn");
+    return 0;
+}

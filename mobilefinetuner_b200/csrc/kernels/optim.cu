@@ -78,16 +78,27 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
     p = __fsub_rn(p, __fdiv_rn(__fmul_rn(lr, mc), __fadd_rn(__fsqrt_rn(vc), eps)));
 }
 
+// steps[s] += 1 for every slot that has a gradient (optim/adam.cpp:35-43: the per-tensor step only advances then)
+__global__ void adam_advance_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, int32_t* __restrict__ steps) {
+    for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < num_slots; s += gridDim.x * blockDim.x)
+        if (slots[s].grad) steps[s] += 1;
+}
+
 __global__ void __launch_bounds__(kOptThreads)
-adam_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float lr, float b1, float b2, float eps, float wd,
-            const float* __restrict__ grad_scale) {
+adam_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float lr, const float* __restrict__ lr_dev, float b1, float b2,
+            float eps, float wd, const float* __restrict__ grad_scale, const int32_t* __restrict__ steps) {
     const float gs = grad_scale ? grad_scale[0] : 1.0f;
+    if (lr_dev) lr = lr_dev[0];
     const float omb1 = 1.0f - b1, omb2 = 1.0f - b2;
     const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
     const int64_t stride = int64_t(gridDim.x) * kOptThreads;
     for (int s = 0; s < num_slots; ++s) {
-        const mft_tensor_slot sl = slots[s];
+        mft_tensor_slot sl = slots[s];
         if (!sl.grad) continue;
+        if (steps) {   // device-resident step counters: bias corrections computed here (optim/adam.cpp:222-228)
+            sl.bias_corr1 = 1.0f - powf(b1, float(steps[s]));
+            sl.bias_corr2 = 1.0f - powf(b2, float(steps[s]));
+        }
         const bool vec = ((reinterpret_cast<uintptr_t>(sl.param) | reinterpret_cast<uintptr_t>(sl.grad) |
                            reinterpret_cast<uintptr_t>(sl.m) | reinterpret_cast<uintptr_t>(sl.v)) & 15u) == 0;
         if (vec) {
@@ -177,7 +188,18 @@ extern "C" int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, fl
                              float eps, float weight_decay, const float* grad_scale, mft_stream_t stream) {
     if (num_slots == 0) return 0;
     if (!slots) return set_error(1, "mft_adam_step: null slot table");
-    adam_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, lr, beta1, beta2, eps, weight_decay, grad_scale);
+    adam_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, lr, nullptr, beta1, beta2, eps, weight_decay, grad_scale, nullptr);
     MFT_CHECK_LAUNCH("mft_adam_step");
+    return 0;
+}
+
+extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots, const float* lr, float beta1, float beta2,
+                                 float eps, float weight_decay, const float* grad_scale, int32_t* steps, mft_stream_t stream) {
+    if (num_slots == 0) return 0;
+    if (!slots || !steps || !lr) return set_error(1, "mft_adam_step_dev: null pointer");
+    adam_advance_kernel<<<unsigned(ceil_div(num_slots, 256)), 256, 0, as_stream(stream)>>>(slots, num_slots, steps);
+    add_launches(1);
+    adam_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
+    MFT_CHECK_LAUNCH("mft_adam_step_dev");
     return 0;
 }

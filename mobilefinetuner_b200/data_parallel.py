@@ -1,0 +1,122 @@
+"""Data-parallel training step: one process per GPU, one all-reduce of a flat fp32 gradient bucket per step.
+
+The reference trains on a single device (gpt2_lora_finetune/main.cpp:462-520: backward, global-norm clip, Adam). The
+path shards over independent sequences, so N ranks each run forward/backward on their rows of the global batch and the
+only exchange is the sum of the trainable gradients:
+
+    forward_backward(local rows)   -> gradients packed into the bucket (mft_pack_grads, fixed layout below)
+    all_reduce(bucket, SUM)        -> NCCL on the trainer's stream (gloo in the CPU tests)
+    update()                       -> norm / clip / Adam read the bucket; the 1/world factor of the mean is folded into
+                                      the clip factor on the device (mft_clip_scale pre_scale), no extra pass
+
+Every rank holds identical parameters and identical optimiser state before and after the step. The helpers here are the
+host-side logic of that scheme (layout, sharding, averaging) and are exercised on CPU with world_size-2 gloo groups in
+tests/test_data_parallel.py; the device pieces are the C ABI calls named above.
+"""
+from __future__ import annotations
+
+BUCKET_ALIGN = 4  # elements; keeps every tensor's slice 16-byte aligned for the vectorised kernels (trainer_session.cpp)
+
+
+def bucket_layout(sizes):
+    """Element offset of each trainable tensor inside the flat gradient bucket, and the bucket length.
+    Mirrors the layout mft_trainer_grad_elems / mft_pack_grads use: tensors in trainable order, each slice padded to a
+    multiple of four elements. Padding words are zero and stay zero under the all-reduce."""
+    offsets, off = [], 0
+    for n in sizes:
+        n = int(n)
+        if n < 0:
+            raise ValueError("negative tensor size")
+        offsets.append(off)
+        off += (n + BUCKET_ALIGN - 1) // BUCKET_ALIGN * BUCKET_ALIGN
+    return offsets, off
+
+
+def shard_rows(n_rows, rank, world):
+    """Rows [lo, hi) of the global batch owned by `rank`. Equal contiguous shards: the mean-reduced loss of the global
+    batch is the mean of the shard losses only when every shard holds the same number of target tokens."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f"bad rank {rank} for world size {world}")
+    if n_rows % world:
+        raise ValueError(f"global batch of {n_rows} rows does not divide over {world} ranks")
+    per = n_rows // world
+    return rank * per, (rank + 1) * per
+
+
+def pack(grads, offsets, total, xp):
+    """Gradients -> flat bucket (host restatement of mft_pack_grads; None = tensor without gradient -> zeros)."""
+    bucket = xp.zeros(total, dtype=xp.float32)
+    for g, off in zip(grads, offsets):
+        if g is not None:
+            flat = g.reshape(-1)
+            bucket[off:off + flat.shape[0]] = flat
+    return bucket
+
+
+def unpack(bucket, sizes, offsets, shapes=None):
+    out = []
+    for i, (n, off) in enumerate(zip(sizes, offsets)):
+        t = bucket[off:off + int(n)]
+        out.append(t.reshape(shapes[i]) if shapes is not None else t)
+    return out
+
+
+def all_reduce_sum(bucket, group=None):
+    """In-place sum over ranks of a torch tensor (cuda -> NCCL, cpu -> gloo). No-op without a process group."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=group)
+    return bucket
+
+
+def with_grad_agrees(flags, group=None):
+    """True when every rank produced gradients for the same set of tensors (the stop-gradient attention of the GPT-2
+    graph leaves 24 of 48 LoRA tensors without one; the set must not depend on the rank)."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([1 if f else 0 for f in flags], dtype=torch.int32)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return True
+    lo, hi = t.clone(), t.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    return bool((lo == hi).all())
+
+
+class DataParallelTrainer:
+    """N-rank wrapper around `Trainer`: same step semantics, gradients averaged over ranks.
+
+    `trainer` must have been created with world_size / rank of the current process group. The all-reduce is issued on
+    the trainer's own stream, so it is ordered after the pack and before the update without host synchronisation."""
+
+    def __init__(self, trainer, group=None):
+        import torch
+        import torch.distributed as dist
+        self.trainer = trainer
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if self.world != trainer.cfg.world_size:
+            raise ValueError(f"trainer was built for world_size {trainer.cfg.world_size}, process group has {self.world}")
+        self.stream = torch.cuda.ExternalStream(trainer.stream)
+        self.bucket = trainer.make_grad_bucket() if self.world > 1 else None
+
+    def step_device(self, dev_ids_ptr):
+        """One optimiser step on this rank's rows (int32 token ids already in HBM)."""
+        import torch
+        tr = self.trainer
+        if self.world == 1:
+            tr.step_device(dev_ids_ptr)
+            return
+        tr.forward_backward(dev_ids_ptr)
+        with torch.cuda.stream(self.stream):
+            all_reduce_sum(self.bucket, self.group)
+        tr.update()
+
+    def loss_mean(self):
+        """Mean of the ranks' losses (what a single process would report on the global batch)."""
+        import torch
+        import torch.distributed as dist
+        v = torch.tensor([self.trainer.loss()], device="cuda")
+        if self.world > 1:
+            dist.all_reduce(v, group=self.group)
+        return float(v.item()) / self.world

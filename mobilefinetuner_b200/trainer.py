@@ -42,6 +42,7 @@ TRAINER_SIGNATURES = {
     "mft_trainer_stream": (vp, [vp]),
     "mft_trainer_sync": (C.c_int, [vp]),
     "mft_trainer_set_lr": (None, [vp, f32]),
+    "mft_trainer_enable_graph": (None, [vp, C.c_int]),
     "mft_host_set_gemm_precision": (None, [C.c_int]),
     "mft_host_gemm_precision": (C.c_int, []),
     "mft_trainer_num_trainable": (i32, [vp]),
@@ -72,7 +73,8 @@ class Trainer:
     """One rank's training step. `step(host_ids)` is the end-to-end call (H2D, step, D2H of the loss)."""
 
     def __init__(self, batch, seq_len, shape="gpt2-small", full_finetune=False, lora_rank=8, lora_alpha=16.0, lora_mlp=False,
-                 lr=2e-4, weight_decay=None, clip_norm=1.0, seed=1234, world_size=1, rank=0, arena_mb=0, **overrides):
+                 lr=2e-4, weight_decay=None, clip_norm=1.0, seed=1234, world_size=1, rank=0, arena_mb=0, cuda_graph=False,
+                 **overrides):
         cfg = TrainerConfig()
         for k, v in dict(MODEL_SHAPES[shape] if isinstance(shape, str) else shape, **overrides).items():
             setattr(cfg, k, v)
@@ -83,6 +85,7 @@ class Trainer:
         cfg.weight_decay = (0.01 if full_finetune else 0.0) if weight_decay is None else weight_decay
         cfg.clip_norm, cfg.seed = clip_norm, seed
         cfg.world_size, cfg.rank, cfg.arena_mb = world_size, rank, arena_mb
+        cfg.use_cuda_graph = int(cuda_graph)
         self.cfg = cfg
         self._h = vp()
         if hostlib.mft_trainer_create(C.byref(cfg), C.byref(self._h)) != 0:
@@ -138,6 +141,12 @@ class Trainer:
         self._bucket = torch.zeros(n, dtype=torch.float32, device="cuda")
         self._ck(hostlib.mft_trainer_set_grad_bucket(self._h, self._bucket.data_ptr(), n))
         return self._bucket
+
+    def set_lr(self, lr):
+        hostlib.mft_trainer_set_lr(self._h, float(lr))
+
+    def enable_graph(self, on):
+        hostlib.mft_trainer_enable_graph(self._h, int(on))
 
     def sync(self):
         self._ck(hostlib.mft_trainer_sync(self._h))

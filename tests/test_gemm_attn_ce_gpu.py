@@ -115,6 +115,36 @@ def test_gemm_splitk_matches_reference(capi, m, n, k, ta, splits):
     assert rel(outs[0], ref_gemm(a, b, ta, 0, 0.5, 2.0, bias, c0)) < FP32_TOL
 
 
+@pytest.mark.parametrize("T,K,r,a_is_kr", [(4096, 1024, 16, 1), (4096, 1024, 16, 0), (100, 768, 8, 1), (33, 64, 4, 0),
+                                            (512, 3072, 64, 1), (257, 2048, 32, 0), (10, 24, 4, 1), (37, 101, 5, 1), (2500, 333, 16, 0)])
+def test_lora_down_streaming_kernel(capi, T, K, r, a_is_kr):
+    rng = np.random.default_rng(T + K + r)
+    x = rng.standard_normal((T, K)).astype(np.float32)
+    A = (rng.standard_normal((K, r) if a_is_kr else (r, K)) * 0.1).astype(np.float32)
+    y = torch.full((T, r), float("nan"), device="cuda")
+    capi.call("mft_lora_down", dev(x), K, dev(A), A.shape[1], a_is_kr, y, r, T, K, r, 2.0, None)
+    e = 2.0 * (x.astype(np.float64) @ (A if a_is_kr else A.T).astype(np.float64))
+    assert rel(y, e) < FP32_TOL
+
+
+@pytest.mark.parametrize("T,q,r,rq", [(4096, 1024, 16, 1), (4096, 1024, 16, 0), (100, 768, 8, 1), (65, 50, 4, 0),
+                                       (512, 1024, 64, 1), (300, 2304, 32, 0), (129, 51, 3, 1), (1000, 77, 16, 0)])
+def test_lora_tn_streaming_kernel(capi, T, q, r, rq):
+    rng = np.random.default_rng(T + q + r)
+    S = rng.standard_normal((T, r)).astype(np.float32)
+    W = rng.standard_normal((T, q)).astype(np.float32)
+    outs = []
+    for _ in range(2):
+        out = torch.full((r, q) if rq else (q, r), float("nan"), device="cuda")
+        w = ws(capi.lib.mft_lora_tn_workspace_bytes(T, q, r))
+        capi.call("mft_lora_tn", dev(S), r, dev(W), q, out, out.shape[1], rq, T, q, r, 0.5, w, w.numel(), None)
+        torch.cuda.synchronize()
+        outs.append(out)
+    e = 0.5 * (S.astype(np.float64).T @ W.astype(np.float64))
+    assert torch.equal(outs[0], outs[1])
+    assert rel(outs[0], e if rq else e.T) < FP32_TOL
+
+
 # ----------------------------------------------------------------------------- tcgen05 TF32 path
 @pytest.mark.parametrize("m,n,k", [(128, 256, 32), (128, 64, 64), (512, 768, 768), (512, 2304, 768), (300, 200, 100),
                                    (2048, 3072, 768), (129, 257, 36), (4096, 1024, 4096), (64, 64, 4096)])

@@ -71,10 +71,33 @@ def bench_skinny(name, m, n, k, ta, tb, iters=20):
     print(f"{name:12s} m={m} n={n} k={k} splits={splits}: {us:7.1f} us  ({mb / us * 1e6 / 1e3:7.1f} GB/s algorithmic)", flush=True)
 
 
+def bench_lora(iters=20):
+    T, K, q, r = 4096, 1024, 1024, 16
+    x = torch.randn(T, K, device="cuda"); A = torch.randn(K, r, device="cuda"); y = torch.empty(T, r, device="cuda")
+    W = torch.randn(T, q, device="cuda"); out = torch.empty(r, q, device="cuda")
+    ws = torch.empty(capi.lib.mft_lora_tn_workspace_bytes(T, q, r), dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    calls = {"lora_down [4096x1024]x[1024x16]": lambda: capi.call("mft_lora_down", x, K, A, r, 1, y, r, T, K, r, 1.0, None),
+             "lora_tn   [4096x16]^T[4096x1024]": lambda: capi.call("mft_lora_tn", y, r, W, q, out, q, 1, T, q, r, 1.0, ws, ws.numel(), None)}
+    for name, fn in calls.items():
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        tot = 0.0
+        for _ in range(iters):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); e1.synchronize()
+            tot += e0.elapsed_time(e1)
+        us = tot / iters * 1e3
+        print(f"{name}: {us:7.1f} us  ({16.8 / us * 1e3:7.1f} GB/s algorithmic)", flush=True)
+
+
 if __name__ == "__main__":
     if sys.argv[1:] == ["skinny"]:
         for sh in SKINNY:
             bench_skinny(*sh)
+        bench_lora()
         sys.exit(0)
     which = sys.argv[1:] or ["tf32", "bf16"]
     for mode in which:
