@@ -40,6 +40,11 @@ int mft_use_tensor_cores(int enable);      /* 1 (default): tcgen05 TF32 GEMM whe
  *       A2 stored [m,k2] (lda2), B2 stored [n,k2] (ldb2); k2 = 0 disables it.
  *   batch > 1: strided batches (element strides), bias/second segment not batched.
  *   gelu_out != NULL: C receives the pre-activation, gelu_out (ldc) receives gelu_tanh(C).
+ *   Epilogue order: v = alpha*acc + bias + beta*C + addend;  v *= gelu_tanh'(gelu_grad_x);  C = v;  gelu_out = gelu_tanh(v).
+ *   addend fuses the residual add that follows a projection (ops::add after LoRALinear::forward, graph/gpt2_model.cpp
+ *   block forward); gelu_grad_x fuses GeluBackward (core/backward_functions.cpp:155-177) into the dX product of the
+ *   layer that consumed the activation. Both are element-wise on the fp32 result, so the fused value equals the
+ *   separate kernels' bit for bit. Not available with split-K.
  * Tensor-core path (tcgen05.mma kind::tf32, fp32 accumulate in TMEM, TMA-fed) is taken when both
  * operands are K-major (trans_a = 0, trans_b = 1), 16-byte aligned with ld % 4 == 0; otherwise a
  * SIMT fp32 kernel runs. Replaces ops::matmul + MatmulBackward's three products
@@ -56,6 +61,8 @@ typedef struct mft_gemm_args {
     float* gelu_out;                   /* [m,n] (ldc) or NULL */
     int32_t k2; const float* a2; int64_t lda2; const float* b2; int64_t ldb2;
     int32_t batch; int64_t stride_a, stride_b, stride_c;
+    const float* addend; int64_t ld_addend;            /* [m,n] added after bias/beta (residual stream), or NULL   */
+    const float* gelu_grad_x; int64_t ld_gelu_grad_x;  /* [m,n]: result *= d gelu_tanh / dx at this tensor, or NULL */
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
 /* bf16-operand form of mft_gemm: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements, multiples of 8),

@@ -1,3 +1,4 @@
+#include <cstdlib>
 #include "gpt2_model.h"
 
 #include <filesystem>
@@ -175,6 +176,12 @@ TensorPtr GPT2Model::run_linear(const TensorPtr& x, const std::unique_ptr<LoRALi
     return linear(x, W, b);            // reference fallback: matmul + add (graph/gpt2_model.cpp:592-600)
 }
 
+TensorPtr GPT2Model::run_linear_fused(const TensorPtr& x, const std::unique_ptr<LoRALinear>& lin, bool lora_ready,
+                                      const TensorPtr& W, const TensorPtr& b, const LinearFusion& fusion) const {
+    if (lora_ready && lin) return lin->forward_fused(x, fusion);
+    return fused_lora_linear(x, W, b, {}, fusion);
+}
+
 // graph/gpt2_model.cpp:530-817. Autograd-visible structure preserved: the attention output carries no history
 // (q/k/v are cut from the graph by the reference's zeros+memcpy split, :616-637), residual adds and
 // LayerNorms are tracked ops.
@@ -190,14 +197,29 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x, int i) {
     auto x1 = layer_norm(x, w.ln_1_weight, w.ln_1_bias, eps);
     auto qkv = run_linear(x1, w.qkv_lin, w.lora_initialized, w.attn_qkv_weight, w.attn_qkv_bias);
     auto ctx = gpt2_causal_attention(qkv, config_.n_head);
-    auto a = run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias);
-    auto x2 = add(x, a);
+    // MFT_FUSE_EPILOGUE bit 0: residual adds ride in the projections' epilogues; bit 1: GeluBackward rides in the epilogue of
+    // fc_out's dX product. Off by default: with four epilogue warps per CTA the extra operand traffic and the tanh cost more
+    // inside the GEMM than the separate streaming kernels do (profiles/README.md).
+    static const int fuse = [] { const char* e = std::getenv("MFT_FUSE_EPILOGUE"); return e ? std::atoi(e) : 0; }();
+    TensorPtr x2;
+    if (fuse & 1) {
+        LinearFusion attn_out;
+        attn_out.residual = x;
+        x2 = run_linear_fused(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias, attn_out);
+    } else {
+        x2 = add(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias));
+    }
     auto x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
-    TensorPtr h;   // fc_in + tanh-GELU: the activation is written by the GEMM epilogue (graph/gpt2_model.cpp:794-802)
-    if (w.lora_initialized && w.fc_in_lin) h = w.fc_in_lin->forward_gelu(x3);
-    else fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, &h);
-    auto m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);
-    return add(x2, m);
+    TensorPtr h, pre;   // fc_in + tanh-GELU: the activation is written by the GEMM epilogue (graph/gpt2_model.cpp:794-802)
+    if (w.lora_initialized && w.fc_in_lin) h = w.fc_in_lin->forward_gelu(x3, &pre);
+    else pre = fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, &h);
+    // x2 + fc_out(gelu(pre)): residual in the forward epilogue, GeluBackward in the epilogue of the backward dX product
+    if (!fuse) return add(x2, run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias));
+    LinearFusion mlp_out;
+    if (fuse & 1) mlp_out.residual = x2;
+    if (fuse & 2) mlp_out.gelu_input_pre = pre;
+    auto m = run_linear_fused(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias, mlp_out);
+    return (fuse & 1) ? m : add(x2, m);
 }
 
 // graph/gpt2_model.cpp:323-442

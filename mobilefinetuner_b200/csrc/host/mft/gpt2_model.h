@@ -84,6 +84,8 @@ private:
     GPT2BlockWeights& checked_block(int i, const char* who);
     TensorPtr run_linear(const TensorPtr& x, const std::unique_ptr<LoRALinear>& lin, bool lora_ready,
                          const TensorPtr& W, const TensorPtr& b) const;
+    TensorPtr run_linear_fused(const TensorPtr& x, const std::unique_ptr<LoRALinear>& lin, bool lora_ready,
+                               const TensorPtr& W, const TensorPtr& b, const LinearFusion& fusion) const;
     TensorPtr forward_block(const TensorPtr& x, int block_idx);
 };
 

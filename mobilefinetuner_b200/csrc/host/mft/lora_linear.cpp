@@ -28,15 +28,20 @@ void LoRALinear::attach_lora(const TensorPtr& A, const TensorPtr& B, float scale
 }
 void LoRALinear::clear_lora() { slices_.clear(); merged_ = false; }
 
-TensorPtr LoRALinear::forward(const TensorPtr& x) const { return forward_impl(x, nullptr); }
-TensorPtr LoRALinear::forward_gelu(const TensorPtr& x) const {
+TensorPtr LoRALinear::forward(const TensorPtr& x) const { return forward_impl(x, LinearFusion{}); }
+TensorPtr LoRALinear::forward_gelu(const TensorPtr& x, TensorPtr* pre) const {
     TensorPtr act;
-    forward_impl(x, &act);
+    LinearFusion f;
+    f.gelu_act = &act;
+    TensorPtr y = forward_impl(x, f);
+    if (pre) *pre = y;
     return act;
 }
+TensorPtr LoRALinear::forward_fused(const TensorPtr& x, const LinearFusion& fusion) const { return forward_impl(x, fusion); }
 
 // nn/lora_linear.cpp:47-108
-TensorPtr LoRALinear::forward_impl(const TensorPtr& x, TensorPtr* gelu_act) const {
+TensorPtr LoRALinear::forward_impl(const TensorPtr& x, const LinearFusion& fusion) const {
+    TensorPtr* gelu_act = fusion.gelu_act;
     const TensorPtr& W = base_W();
     if (!W) throw std::runtime_error("LoRALinear::forward: base weight is null (sharded and not loaded?)");
     const TensorPtr& bias = base_b();
@@ -51,7 +56,9 @@ TensorPtr LoRALinear::forward_impl(const TensorPtr& x, TensorPtr* gelu_act) cons
             else partial.push_back(&s);
         }
     }
-    TensorPtr y = fused_lora_linear(x, W, bias, full, partial.empty() ? gelu_act : nullptr);
+    LinearFusion f = fusion;
+    if (!partial.empty()) f.gelu_act = nullptr;    // the activation is taken after the in-place slice updates below
+    TensorPtr y = fused_lora_linear(x, W, bias, full, f);
     if (!partial.empty()) {
         TensorPtr xc = contiguous(x);
         const int64_t in = W->shape()[0], T = xc->numel() / in;

@@ -12,6 +12,8 @@
 
 namespace ops {
 
+struct LinearFusion;   // ops.h
+
 struct LoRASlice {
     TensorPtr A;   // [in, r]  (or PEFT [r, in])
     TensorPtr B;   // [r, out_slice] (or PEFT [out_slice, r])
@@ -32,7 +34,10 @@ public:
     TensorPtr forward(const TensorPtr& x) const;
     // B200 extension: gelu(forward(x)) with the activation produced by the GEMM epilogue (returns the activation;
     // the pre-activation stays in the graph for GeluBackward).
-    TensorPtr forward_gelu(const TensorPtr& x) const;
+    TensorPtr forward_gelu(const TensorPtr& x, TensorPtr* pre = nullptr) const;
+    // B200 extension: forward with the neighbouring residual add / GELU backward folded into the GEMM epilogues
+    // (see ops::LinearFusion).
+    TensorPtr forward_fused(const TensorPtr& x, const LinearFusion& fusion) const;
 
     void set_debug_name(const std::string& name) { debug_name_ = name; }
     std::vector<std::pair<std::string, TensorPtr>> debug_params() const;
@@ -52,7 +57,7 @@ private:
     const TensorPtr& base_W() const;
     const TensorPtr& base_b() const;
     void add_delta_to_base(float sign);
-    TensorPtr forward_impl(const TensorPtr& x, TensorPtr* gelu_act) const;
+    TensorPtr forward_impl(const TensorPtr& x, const LinearFusion& fusion) const;
 };
 
 }  // namespace ops

@@ -102,6 +102,7 @@ void run_gemm(GemmCall g) {
             a.k2 = int32_t(g.k2);
         }
         a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
+        a.addend = g.addend; a.ld_addend = g.ld_addend; a.gelu_grad_x = g.gelu_grad_x; a.ld_gelu_grad_x = g.ld_gelu_grad_x;
         a.batch = 1;
         mft_rt::check(mft_gemm_bf16(&a, mft_rt::stream()), "mft_gemm_bf16");
         return;
@@ -130,6 +131,7 @@ void run_gemm(GemmCall g) {
     a.a = g.a; a.lda = g.lda; a.trans_a = g.trans_a;
     a.b = g.b; a.ldb = g.ldb; a.trans_b = g.trans_b;
     a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
+        a.addend = g.addend; a.ld_addend = g.ld_addend; a.gelu_grad_x = g.gelu_grad_x; a.ld_gelu_grad_x = g.ld_gelu_grad_x;
     a.k2 = int32_t(g.k2); a.a2 = g.a2; a.lda2 = g.lda2; a.b2 = g.b2; a.ldb2 = g.ldb2;
     a.batch = std::max(g.batch, 1); a.stride_a = g.stride_a; a.stride_b = g.stride_b; a.stride_c = g.stride_c;
     // few output tiles + long contraction on the SIMT path: split K so the whole chip works on it

@@ -115,6 +115,20 @@ struct LoraTerm { TensorPtr A, B; float scale; };
 // replaces the separate ops::gelu pass of the MLP (graph/gpt2_model.cpp:794-802).
 TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
                             TensorPtr* gelu_act = nullptr);
+// Element-wise neighbours of the projection folded into its GEMM epilogues (same fp32 values as the separate ops):
+//   residual       : y = linear(x) + residual — the ops::add that follows attn.proj / mlp.fc_out in the block forward
+//                    (graph/gpt2_model.cpp:760-812); the node passes gy through to `residual` like AddBackward.
+//   gelu_input_pre : x is gelu(pre) produced by a previous fused_lora_linear(..., &gelu_act). The node then takes `pre` as
+//                    its autograd input and its dX product returns d pre = (gy W^T + ...) * gelu'(pre) directly
+//                    (GeluBackward, core/backward_functions.cpp:155-177, applied in the epilogue), so the activation's
+//                    gradient is never written to HBM. Only valid when this op is the activation's single consumer.
+struct LinearFusion {
+    TensorPtr* gelu_act = nullptr;
+    TensorPtr residual;
+    TensorPtr gelu_input_pre;
+};
+TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
+                            const LinearFusion& fusion);
 // logits = x @ E^T for an embedding table E [V,C] (tied lm_head) without materialising E^T
 // (graph/gpt2_model.cpp:425-439 transposes wte on every forward).
 TensorPtr lm_head_tied(const TensorPtr& x, const TensorPtr& table);

@@ -25,6 +25,8 @@ struct GemmCall {
     float alpha = 1.0f, beta = 0.0f;
     const float* bias = nullptr;
     float* gelu_out = nullptr;
+    const float* addend = nullptr; int64_t ld_addend = 0;             // + residual, in the epilogue
+    const float* gelu_grad_x = nullptr; int64_t ld_gelu_grad_x = 0;   // * gelu'(x), in the epilogue
     int64_t k2 = 0; const float* a2 = nullptr; int64_t lda2 = 0; const float* b2 = nullptr; int64_t ldb2 = 0;
     int batch = 1; int64_t stride_a = 0, stride_b = 0, stride_c = 0;
     TensorPtr b_weight;   // tensor behind `b` (lets run_gemm reuse its cached K-major / bf16 shadows)

@@ -240,7 +240,7 @@ TensorPtr small_transpose(const TensorPtr& t) {
 // MFT_LORA_SKINNY: bit 0 routes x*A / dY*B^T through mft_lora_down, bit 1 routes dA / dB through mft_lora_tn; the rest goes
 // through the general GEMM dispatch (SIMT split-K for these shapes).
 int skinny_mask() {
-    static const int m = [] { const char* e = std::getenv("MFT_LORA_SKINNY"); return e ? std::atoi(e) : 2; }();
+    static const int m = [] { const char* e = std::getenv("MFT_LORA_SKINNY"); return e ? std::atoi(e) : 3; }();
     return m;
 }
 // y[T,r] = alpha * x[T,K] * A   (A [K,r] when a_is_kr, else [r,K])
@@ -278,13 +278,16 @@ void lora_tn(const TensorPtr& S, const TensorPtr& W, int64_t T, int64_t q, int64
 // dx = gy W^T + sum dxa A^T (rank-r update fused as second K segment) ; dW = x^T gy ; db = colsum(gy).
 class LoraLinearBackward : public BackwardFunction {
 public:
-    LoraLinearBackward(TensorPtr x, TensorPtr W, TensorPtr bias, std::vector<LoraTerm> terms, std::vector<TensorPtr> xa)
-        : x_(std::move(x)), W_(std::move(W)), bias_(std::move(bias)), terms_(std::move(terms)), xa_(std::move(xa)) {}
+    LoraLinearBackward(TensorPtr x, TensorPtr W, TensorPtr bias, std::vector<LoraTerm> terms, std::vector<TensorPtr> xa,
+                       TensorPtr gelu_pre = nullptr, bool has_residual = false)
+        : x_(std::move(x)), W_(std::move(W)), bias_(std::move(bias)), terms_(std::move(terms)), xa_(std::move(xa)),
+          pre_(std::move(gelu_pre)), has_residual_(has_residual) {}
     std::vector<TensorPtr> apply(const TensorPtr& gy) override {
         const int64_t in = W_->shape()[0], out = W_->shape()[1];
         const int64_t T = x_->numel() / in;
-        std::vector<TensorPtr> grads(3 + 2 * terms_.size());
-        const bool need_dx = autograd::Engine::instance().needs_grad(x_);
+        std::vector<TensorPtr> grads(3 + 2 * terms_.size() + (has_residual_ ? 1 : 0));
+        if (has_residual_) grads.back() = gy;               // y = ... + residual: the gradient passes through unchanged
+        const bool need_dx = autograd::Engine::instance().needs_grad(pre_ ? pre_ : x_);
         std::vector<TensorPtr> dxa(terms_.size());
         for (size_t i = 0; i < terms_.size(); ++i) {
             const LoraTerm& t = terms_[i];
@@ -319,6 +322,8 @@ public:
                 keep.push_back(a_in_r);
                 if (i == 0) { g.k2 = l.r; g.a2 = dxa[i]->dev_f32(); g.lda2 = l.r; g.b2 = a_in_r->dev_f32(); g.ldb2 = a_in_r->ld(); }
             }
+            const bool fuse_gelu_bwd = pre_ && terms_.size() <= 1;   // further slices accumulate after the epilogue ran
+            if (fuse_gelu_bwd) { g.gelu_grad_x = pre_->dev_f32(); g.ld_gelu_grad_x = pre_->ld(); }
             run_gemm(g);
             for (size_t i = 1; i < terms_.size(); ++i) {     // further slices: accumulate
                 TermLayout l = classify(terms_[i], in, out);
@@ -328,6 +333,11 @@ public:
                 h.b = keep[i]->dev_f32(); h.ldb = keep[i]->ld(); h.trans_b = 1;
                 h.c = gx->dev_f32_mut(); h.ldc = in;
                 run_gemm(h);
+            }
+            if (pre_ && !fuse_gelu_bwd) {
+                TensorPtr pc = contiguous(pre_);
+                float* gxp = gx->dev_f32_mut();
+                mft_rt::check(mft_gelu_bwd(pc->dev_f32(), gxp, gxp, T * in, mft_rt::stream()), "mft_gelu_bwd");
             }
             grads[0] = gx;
         }
@@ -352,12 +362,22 @@ private:
     TensorPtr x_, W_, bias_;
     std::vector<LoraTerm> terms_;
     std::vector<TensorPtr> xa_;
+    TensorPtr pre_;            // x_ == gelu(pre_): dx is returned for pre_
+    bool has_residual_;
 };
 
 }  // namespace
 
 TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
                             TensorPtr* gelu_act) {
+    LinearFusion f;
+    f.gelu_act = gelu_act;
+    return fused_lora_linear(x_in, W, bias, terms, f);
+}
+
+TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
+                            const LinearFusion& fusion) {
+    TensorPtr* gelu_act = fusion.gelu_act;
     require_f32(x_in, "lora_linear");
     require_f32(W, "lora_linear");
     if (W->ndim() != 2) throw TensorError("lora_linear: weight must be [in, out]");
@@ -368,6 +388,13 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     const int64_t T = x->numel() / in;
     std::vector<int64_t> so = x->shape();
     so.back() = out;
+    TensorPtr residual = fusion.residual;
+    if (residual) {
+        require_f32(residual, "lora_linear");
+        if (residual->shape() != so) throw TensorError("lora_linear: residual shape " + shape_str(residual->shape()) + " does not match the output " + shape_str(so));
+    }
+    const TensorPtr& pre = fusion.gelu_input_pre;
+    if (pre && pre->shape() != x_in->shape()) throw TensorError("lora_linear: gelu_input_pre must have the input's shape");
     auto y = Tensor::make(so, kFloat32, false, out_ld(out));
     std::vector<TensorPtr> xa(terms.size()), bt(terms.size());
     for (size_t i = 0; i < terms.size(); ++i) {
@@ -386,6 +413,7 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     const bool fuse_gelu = gelu_act != nullptr && terms.size() <= 1;   // later slices accumulate after the epilogue ran
     if (fuse_gelu) { act = Tensor::make(so, kFloat32, false, y->ld()); g.gelu_out = act->dev_f32_out(); }
     if (!terms.empty()) { g.k2 = xa[0]->shape()[1]; g.a2 = xa[0]->dev_f32(); g.lda2 = g.k2; g.b2 = bt[0]->dev_f32(); g.ldb2 = bt[0]->ld(); }
+    if (residual) { g.addend = residual->dev_f32(); g.ld_addend = residual->ld(); }   // (x W + b) + residual, then the slices below
     run_gemm(g);
     for (size_t i = 1; i < terms.size(); ++i) {
         GemmCall h;
@@ -395,9 +423,10 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
         h.c = y->dev_f32_mut(); h.ldc = y->ld();
         run_gemm(h);
     }
-    std::vector<TensorPtr> inputs{x_in, W, bias};
+    std::vector<TensorPtr> inputs{pre ? pre : x_in, W, bias};
     for (const auto& t : terms) { inputs.push_back(t.A); inputs.push_back(t.B); }
-    track(y, inputs, std::make_shared<LoraLinearBackward>(x, W, bias, terms, xa));
+    if (residual) inputs.push_back(residual);
+    track(y, inputs, std::make_shared<LoraLinearBackward>(x, W, bias, terms, xa, pre, residual != nullptr));
     if (gelu_act) {
         if (fuse_gelu) { track(act, {y}, make_gelu_backward(y)); *gelu_act = act; }
         else *gelu_act = gelu(y);

@@ -40,8 +40,11 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
 // PRECISE = true : 3xTF32 split (hi/lo) on both products, fp32-accurate (exact mode / parity tests).
-// PRECISE = false: plain TF32 operands (same input precision as the tcgen05 GEMMs), 3x fewer MMAs.
-template <int HD, bool PRECISE>
+// PRECISE = false: plain TF32 operands (same input precision as the tcgen05 GEMMs), 3x fewer MMAs. K and V go to the tensor
+//                  pipe as raw fp32 bit patterns (the pipe reads the upper 19 bits: truncation instead of a cvt.rna per
+//                  fragment element, which would cost more issue slots than the MMA it feeds); Q and P are rounded.
+// MT = 16-row query slabs per warp: every K/V fragment read from shared memory feeds MT MMAs.
+template <int HD, bool PRECISE, int MT>
 __global__ void __launch_bounds__(128)
 causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                             float* __restrict__ ctx, int H, int S,
@@ -50,6 +53,8 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
     constexpr int LD = HD + kAttPad;
     constexpr int KS = HD / 8;    // k-slabs over the head dim (QK^T)
     constexpr int NT = HD / 8;    // n-tiles over the head dim (PV)
+    constexpr int BQ = 64 * MT;   // query rows per CTA (4 warps x MT slabs x 16 rows)
+    constexpr float kLog2e = 1.4426950408889634f;
     extern __shared__ __align__(16) float smem[];
     float* sK = smem;                          // [2][kAttBK][LD]
     float* sV = smem + 2 * kAttBK * LD;        // [2][kAttBK][LD]
@@ -59,37 +64,47 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
     const int b = bh / H, h = bh % H;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
-    const int q0 = qt * kAttBQ;
+    const int q0 = qt * BQ;
+    const int wrow = q0 + warp * 16 * MT;      // first query row of this warp
     const float* qb = q + b * qsb + h * qsh;
     const float* kb = k + b * ksb + h * ksh;
     const float* vb = v + b * ksb + h * ksh;
+    // fast mode: scores are kept in the log2 domain (scale * log2(e) folded into Q) so the softmax uses ex2 directly
+    const float qscale = PRECISE ? scale : scale * kLog2e;
 
-    // Q fragments (A operand, rows g / g+8 of this warp's 16-row slab), pre-scaled, split hi/lo.
-    uint32_t qhi[KS][4], qlo[PRECISE ? KS : 1][4];
-    {
-        const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+    // Q fragments (A operand, rows g / g+8 of each 16-row slab), pre-scaled, split hi/lo in precise mode.
+    uint32_t qhi[MT][KS][4], qlo[PRECISE ? MT : 1][PRECISE ? KS : 1][4];
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+        const int r0 = wrow + m * 16 + g, r1 = r0 + 8;
 #pragma unroll
         for (int s = 0; s < KS; ++s) {
-            float a0 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t] * scale : 0.f;
-            float a1 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t] * scale : 0.f;
-            float a2 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t + 4] * scale : 0.f;
-            float a3 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t + 4] * scale : 0.f;
+            float a0 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t] * qscale : 0.f;
+            float a1 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t] * qscale : 0.f;
+            float a2 = (r0 < S) ? qb[int64_t(r0) * qss + s * 8 + t + 4] * qscale : 0.f;
+            float a3 = (r1 < S) ? qb[int64_t(r1) * qss + s * 8 + t + 4] * qscale : 0.f;
             if (PRECISE) {
-                split_tf32(a0, qhi[s][0], qlo[s][0]); split_tf32(a1, qhi[s][1], qlo[s][1]);
-                split_tf32(a2, qhi[s][2], qlo[s][2]); split_tf32(a3, qhi[s][3], qlo[s][3]);
+                split_tf32(a0, qhi[m][s][0], qlo[m][s][0]); split_tf32(a1, qhi[m][s][1], qlo[m][s][1]);
+                split_tf32(a2, qhi[m][s][2], qlo[m][s][2]); split_tf32(a3, qhi[m][s][3], qlo[m][s][3]);
             } else {
-                qhi[s][0] = f2tf32(a0); qhi[s][1] = f2tf32(a1); qhi[s][2] = f2tf32(a2); qhi[s][3] = f2tf32(a3);
+                qhi[m][s][0] = f2tf32(a0); qhi[m][s][1] = f2tf32(a1); qhi[m][s][2] = f2tf32(a2); qhi[m][s][3] = f2tf32(a3);
             }
         }
     }
 
-    float o[NT][4];
+    float o[MT][NT][4];
+    float mrow[MT][2], lrow[MT][2];
 #pragma unroll
-    for (int n = 0; n < NT; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    for (int m = 0; m < MT; ++m) {
+#pragma unroll
+        for (int n = 0; n < NT; ++n) { o[m][n][0] = o[m][n][1] = o[m][n][2] = o[m][n][3] = 0.f; }
+        mrow[m][0] = mrow[m][1] = -INFINITY;
+        lrow[m][0] = lrow[m][1] = 0.f;
+    }
 
-    // key-tile range: causal upper bound, optional sliding-window lower bound
-    int kt_hi = qt;                                    // last tile index (inclusive)
+    // key-tile range: causal upper bound (last key of the CTA's last row), optional sliding-window lower bound
+    const int last_row = min(q0 + BQ, S) - 1;
+    const int kt_hi = last_row / kAttBK;               // last tile index (inclusive)
     int kt_lo = 0;
     if (window > 0) { int lo = q0 - (window - 1); if (lo > 0) kt_lo = lo / kAttBK; }
 
@@ -116,123 +131,173 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
         const float* tk = sK + buf * kAttBK * LD;
         const float* tv = sV + buf * kAttBK * LD;
         const int key0 = kt * kAttBK;
-
-        // ---- S = (Q*scale) K^T  : 16 x 64 per warp
-        float sc[8][4];
+        // a warp whose rows all precede this key tile has nothing to add (only possible when MT > 1)
+        const bool active = key0 <= wrow + 16 * MT - 1;
+        if (active) {
+            // ---- S = (Q*scale) K^T  : (16*MT) x 64 per warp
+            float sc[MT][8][4];
 #pragma unroll
-        for (int n = 0; n < 8; ++n) {
-            sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+            for (int n = 0; n < 8; ++n) {
 #pragma unroll
-            for (int s = 0; s < KS; ++s) {
-                float k0 = tk[(n * 8 + g) * LD + s * 8 + t];
-                float k1 = tk[(n * 8 + g) * LD + s * 8 + t + 4];
-                if (PRECISE) {
-                    uint32_t bh0, bl0, bh1, bl1;
-                    split_tf32(k0, bh0, bl0); split_tf32(k1, bh1, bl1);
-                    mma_tf32(sc[n], qlo[s], bh0, bh1);
-                    mma_tf32(sc[n], qhi[s], bl0, bl1);
-                    mma_tf32(sc[n], qhi[s], bh0, bh1);
-                } else {
-                    mma_tf32(sc[n], qhi[s], f2tf32(k0), f2tf32(k1));
+                for (int m = 0; m < MT; ++m) sc[m][n][0] = sc[m][n][1] = sc[m][n][2] = sc[m][n][3] = 0.f;
+#pragma unroll
+                for (int s = 0; s < KS; ++s) {
+                    const float k0 = tk[(n * 8 + g) * LD + s * 8 + t];
+                    const float k1 = tk[(n * 8 + g) * LD + s * 8 + t + 4];
+                    if (PRECISE) {
+                        uint32_t bh0, bl0, bh1, bl1;
+                        split_tf32(k0, bh0, bl0); split_tf32(k1, bh1, bl1);
+#pragma unroll
+                        for (int m = 0; m < MT; ++m) {
+                            mma_tf32(sc[m][n], qlo[m][s], bh0, bh1);
+                            mma_tf32(sc[m][n], qhi[m][s], bl0, bl1);
+                            mma_tf32(sc[m][n], qhi[m][s], bh0, bh1);
+                        }
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < MT; ++m) mma_tf32(sc[m][n], qhi[m][s], __float_as_uint(k0), __float_as_uint(k1));
+                    }
                 }
             }
-        }
-        // ---- masks (causal / window / sequence tail) + online softmax
-        const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
-        const bool need_mask = (kt == kt_hi) || (window > 0) || (key0 + kAttBK > S);
-        float mx0 = -INFINITY, mx1 = -INFINITY;
+            // ---- masks (causal / window / sequence tail) + online softmax
+            uint32_t phi[MT][8][4];
 #pragma unroll
-        for (int n = 0; n < 8; ++n) {
-            if (need_mask) {
-                int c0 = key0 + n * 8 + 2 * t, c1 = c0 + 1;
-                bool w00 = c0 <= r0 && c0 < S && (window <= 0 || r0 - c0 < window);
-                bool w01 = c1 <= r0 && c1 < S && (window <= 0 || r0 - c1 < window);
-                bool w10 = c0 <= r1 && c0 < S && (window <= 0 || r1 - c0 < window);
-                bool w11 = c1 <= r1 && c1 < S && (window <= 0 || r1 - c1 < window);
-                if (!w00) sc[n][0] = -INFINITY;
-                if (!w01) sc[n][1] = -INFINITY;
-                if (!w10) sc[n][2] = -INFINITY;
-                if (!w11) sc[n][3] = -INFINITY;
+            for (int m = 0; m < MT; ++m) {
+                const int r0 = wrow + m * 16 + g, r1 = r0 + 8;
+                const bool need_mask = (key0 + kAttBK - 1 > wrow + m * 16) || (window > 0) || (key0 + kAttBK > S);
+                float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+                for (int n = 0; n < 8; ++n) {
+                    if (need_mask) {
+                        int c0 = key0 + n * 8 + 2 * t, c1 = c0 + 1;
+                        bool w00 = c0 <= r0 && c0 < S && (window <= 0 || r0 - c0 < window);
+                        bool w01 = c1 <= r0 && c1 < S && (window <= 0 || r0 - c1 < window);
+                        bool w10 = c0 <= r1 && c0 < S && (window <= 0 || r1 - c0 < window);
+                        bool w11 = c1 <= r1 && c1 < S && (window <= 0 || r1 - c1 < window);
+                        if (!w00) sc[m][n][0] = -INFINITY;
+                        if (!w01) sc[m][n][1] = -INFINITY;
+                        if (!w10) sc[m][n][2] = -INFINITY;
+                        if (!w11) sc[m][n][3] = -INFINITY;
+                    }
+                    mx0 = fmaxf(mx0, fmaxf(sc[m][n][0], sc[m][n][1]));
+                    mx1 = fmaxf(mx1, fmaxf(sc[m][n][2], sc[m][n][3]));
+                }
+                mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+                mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+                const float nm0 = fmaxf(mrow[m][0], mx0), nm1 = fmaxf(mrow[m][1], mx1);
+                const float ref0 = (nm0 == -INFINITY) ? 0.f : nm0, ref1 = (nm1 == -INFINITY) ? 0.f : nm1;
+                // exp(-inf) = 0 on the first tile
+                const float cor0 = PRECISE ? expf(mrow[m][0] - ref0) : exp2f(mrow[m][0] - ref0);
+                const float cor1 = PRECISE ? expf(mrow[m][1] - ref1) : exp2f(mrow[m][1] - ref1);
+                mrow[m][0] = nm0; mrow[m][1] = nm1;
+                float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+                for (int n = 0; n < 8; ++n) {
+                    if (PRECISE) {
+                        sc[m][n][0] = expf(sc[m][n][0] - ref0); sc[m][n][1] = expf(sc[m][n][1] - ref0);
+                        sc[m][n][2] = expf(sc[m][n][2] - ref1); sc[m][n][3] = expf(sc[m][n][3] - ref1);
+                    } else {
+                        sc[m][n][0] = exp2f(sc[m][n][0] - ref0); sc[m][n][1] = exp2f(sc[m][n][1] - ref0);
+                        sc[m][n][2] = exp2f(sc[m][n][2] - ref1); sc[m][n][3] = exp2f(sc[m][n][3] - ref1);
+                    }
+                    rs0 += sc[m][n][0] + sc[m][n][1];
+                    rs1 += sc[m][n][2] + sc[m][n][3];
+                }
+                lrow[m][0] = lrow[m][0] * cor0 + rs0;   // per-thread partial row sums; quad-reduced at the end
+                lrow[m][1] = lrow[m][1] * cor1 + rs1;
+#pragma unroll
+                for (int n = 0; n < NT; ++n) { o[m][n][0] *= cor0; o[m][n][1] *= cor0; o[m][n][2] *= cor1; o[m][n][3] *= cor1; }
+                if (!PRECISE) {
+                    // The C-fragment of S holds columns (2t, 2t+1) where an A-fragment wants (t, t+4): relabel the contraction
+                    // index (key 2t <-> slot t, key 2t+1 <-> slot t+4) and read V rows to match.
+#pragma unroll
+                    for (int n = 0; n < 8; ++n) {
+                        phi[m][n][0] = f2tf32(sc[m][n][0]); phi[m][n][1] = f2tf32(sc[m][n][2]);
+                        phi[m][n][2] = f2tf32(sc[m][n][1]); phi[m][n][3] = f2tf32(sc[m][n][3]);
+                    }
+                }
             }
-            mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
-            mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
-        }
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float nm0 = fmaxf(m0, mx0), nm1 = fmaxf(m1, mx1);
-        const float ref0 = (nm0 == -INFINITY) ? 0.f : nm0, ref1 = (nm1 == -INFINITY) ? 0.f : nm1;
-        const float cor0 = expf(m0 - ref0), cor1 = expf(m1 - ref1);   // exp(-inf) = 0 on the first tile
-        m0 = nm0; m1 = nm1;
-        float rs0 = 0.f, rs1 = 0.f;
-#pragma unroll
-        for (int n = 0; n < 8; ++n) {
-            sc[n][0] = expf(sc[n][0] - ref0); sc[n][1] = expf(sc[n][1] - ref0);
-            sc[n][2] = expf(sc[n][2] - ref1); sc[n][3] = expf(sc[n][3] - ref1);
-            rs0 += sc[n][0] + sc[n][1];
-            rs1 += sc[n][2] + sc[n][3];
-        }
-        l0 = l0 * cor0 + rs0;   // per-thread partial row sums; quad-reduced at the end
-        l1 = l1 * cor1 + rs1;
-#pragma unroll
-        for (int n = 0; n < NT; ++n) { o[n][0] *= cor0; o[n][1] *= cor0; o[n][2] *= cor1; o[n][3] *= cor1; }
 
-        // ---- O += P V. The C-fragment of S holds columns (2t, 2t+1) where an A-fragment wants (t, t+4):
-        // relabel the contraction index (key 2t <-> slot t, key 2t+1 <-> slot t+4) and read V rows to match.
+            // ---- O += P V
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {           // 8 key-slabs of 8 keys
-            uint32_t phi[4], plo[4];
-            if (PRECISE) {
-                split_tf32(sc[s][0], phi[0], plo[0]);   // (row g,   key 2t)   -> a0
-                split_tf32(sc[s][2], phi[1], plo[1]);   // (row g+8, key 2t)   -> a1
-                split_tf32(sc[s][1], phi[2], plo[2]);   // (row g,   key 2t+1) -> a2
-                split_tf32(sc[s][3], phi[3], plo[3]);   // (row g+8, key 2t+1) -> a3
-            } else {
-                phi[0] = f2tf32(sc[s][0]); phi[1] = f2tf32(sc[s][2]); phi[2] = f2tf32(sc[s][1]); phi[3] = f2tf32(sc[s][3]);
-            }
+            for (int s = 0; s < 8; ++s) {           // 8 key-slabs of 8 keys
+                uint32_t ph[MT][4], pl[PRECISE ? MT : 1][4];
 #pragma unroll
-            for (int n = 0; n < NT; ++n) {
-                float v0 = tv[(s * 8 + 2 * t) * LD + n * 8 + g];
-                float v1 = tv[(s * 8 + 2 * t + 1) * LD + n * 8 + g];
-                if (PRECISE) {
-                    uint32_t bh0, bl0, bh1, bl1;
-                    split_tf32(v0, bh0, bl0); split_tf32(v1, bh1, bl1);
-                    mma_tf32(o[n], plo, bh0, bh1);
-                    mma_tf32(o[n], phi, bl0, bl1);
-                    mma_tf32(o[n], phi, bh0, bh1);
-                } else {
-                    mma_tf32(o[n], phi, f2tf32(v0), f2tf32(v1));
+                for (int m = 0; m < MT; ++m) {
+                    if (PRECISE) {
+                        split_tf32(sc[m][s][0], ph[m][0], pl[m][0]);   // (row g,   key 2t)   -> a0
+                        split_tf32(sc[m][s][2], ph[m][1], pl[m][1]);   // (row g+8, key 2t)   -> a1
+                        split_tf32(sc[m][s][1], ph[m][2], pl[m][2]);   // (row g,   key 2t+1) -> a2
+                        split_tf32(sc[m][s][3], ph[m][3], pl[m][3]);   // (row g+8, key 2t+1) -> a3
+                    } else {
+                        ph[m][0] = phi[m][s][0]; ph[m][1] = phi[m][s][1]; ph[m][2] = phi[m][s][2]; ph[m][3] = phi[m][s][3];
+                    }
+                }
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    const float v0 = tv[(s * 8 + 2 * t) * LD + n * 8 + g];
+                    const float v1 = tv[(s * 8 + 2 * t + 1) * LD + n * 8 + g];
+                    if (PRECISE) {
+                        uint32_t bh0, bl0, bh1, bl1;
+                        split_tf32(v0, bh0, bl0); split_tf32(v1, bh1, bl1);
+#pragma unroll
+                        for (int m = 0; m < MT; ++m) {
+                            mma_tf32(o[m][n], pl[m], bh0, bh1);
+                            mma_tf32(o[m][n], ph[m], bl0, bl1);
+                            mma_tf32(o[m][n], ph[m], bh0, bh1);
+                        }
+                    } else {
+#pragma unroll
+                        for (int m = 0; m < MT; ++m) mma_tf32(o[m][n], ph[m], __float_as_uint(v0), __float_as_uint(v1));
+                    }
                 }
             }
         }
         __syncthreads();   // everyone done with this buffer before it is refilled
     }
 
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float inv0 = l0 > 0.f ? 1.0f / l0 : 0.f, inv1 = l1 > 0.f ? 1.0f / l1 : 0.f;
-    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
     float* ob = ctx + b * osb + h * osh;
 #pragma unroll
-    for (int n = 0; n < NT; ++n) {
-        if (r0 < S) *reinterpret_cast<float2*>(ob + int64_t(r0) * oss + n * 8 + 2 * t) = make_float2(o[n][0] * inv0, o[n][1] * inv0);
-        if (r1 < S) *reinterpret_cast<float2*>(ob + int64_t(r1) * oss + n * 8 + 2 * t) = make_float2(o[n][2] * inv1, o[n][3] * inv1);
+    for (int m = 0; m < MT; ++m) {
+        float l0 = lrow[m][0], l1 = lrow[m][1];
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const float inv0 = l0 > 0.f ? 1.0f / l0 : 0.f, inv1 = l1 > 0.f ? 1.0f / l1 : 0.f;
+        const int r0 = wrow + m * 16 + g, r1 = r0 + 8;
+#pragma unroll
+        for (int n = 0; n < NT; ++n) {
+            if (r0 < S) *reinterpret_cast<float2*>(ob + int64_t(r0) * oss + n * 8 + 2 * t) = make_float2(o[m][n][0] * inv0, o[m][n][1] * inv0);
+            if (r1 < S) *reinterpret_cast<float2*>(ob + int64_t(r1) * oss + n * 8 + 2 * t) = make_float2(o[m][n][2] * inv1, o[m][n][3] * inv1);
+        }
     }
+}
+
+template <int HD, bool PRECISE, int MT>
+static int launch_attention_mt(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
+                               int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
+                               int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
+    constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(causal_attention_fwd_kernel<HD, PRECISE, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        attr_set = true;
+    }
+    dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
+    causal_attention_fwd_kernel<HD, PRECISE, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
+                                                                 osh, scale, window);
+    return 0;
 }
 
 template <int HD, bool PRECISE>
 static int launch_attention(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
                             int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                             int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
-    constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(causal_attention_fwd_kernel<HD, PRECISE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        attr_set = true;
-    }
-    dim3 grid(unsigned(ceil_div(S, kAttBQ)), unsigned(B * H));
-    causal_attention_fwd_kernel<HD, PRECISE><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
-                                                             osh, scale, window);
-    return 0;
+    // two 16-row slabs per warp halve the shared-memory reads per MMA; worth it once there are enough 128-row CTAs to
+    // fill the chip, and only where the fragments still fit in registers (fast mode, head_dim <= 64)
+    if (!PRECISE && HD <= 64 && int64_t(ceil_div(S, 128)) * B * H >= 2 * kNumSMs)
+        return launch_attention_mt<HD, PRECISE, (!PRECISE && HD <= 64) ? 2 : 1>(q, k, v, ctx, B, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh,
+                                                                               scale, window, st);
+    return launch_attention_mt<HD, PRECISE, 1>(q, k, v, ctx, B, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale, window, st);
 }
 
 static bool env_attention_precise() {

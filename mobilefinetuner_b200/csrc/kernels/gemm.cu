@@ -36,6 +36,8 @@ static int to_params(const mft_gemm_args* a, GemmParams& p) {
     p.k2 = a->k2; p.a2 = a->a2; p.lda2 = a->lda2; p.b2 = a->b2; p.ldb2 = a->ldb2;
     p.batch = a->batch < 1 ? 1 : a->batch;
     p.stride_a = a->stride_a; p.stride_b = a->stride_b; p.stride_c = a->stride_c;
+    p.addend = a->addend; p.ld_addend = a->ld_addend;
+    p.gelu_grad_x = a->gelu_grad_x; p.ld_gelu_grad_x = a->ld_gelu_grad_x;
     if (p.m == 0 || p.n == 0) return 0;
     if (!p.c || (p.k > 0 && (!p.a || !p.b))) return set_error(1, "mft_gemm: null operand");
     if (p.k2 > 0 && (!p.a2 || !p.b2)) return set_error(1, "mft_gemm: null second-segment operand");

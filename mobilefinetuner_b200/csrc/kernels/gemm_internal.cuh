@@ -14,6 +14,8 @@ struct GemmParams {
     float* gelu_out;
     int k2; const void* a2; int64_t lda2; const void* b2; int64_t ldb2;
     int batch; int64_t stride_a, stride_b, stride_c;
+    const float* addend = nullptr; int64_t ld_addend = 0;
+    const float* gelu_grad_x = nullptr; int64_t ld_gelu_grad_x = 0;
     bool bf16 = false;         // operands are bf16 arrays
     int ksplit = 1;            // SIMT split-K: number of K slices (partials reduced in a fixed order)
     float* partial = nullptr;  // [batch][ksplit][m][n] scratch when ksplit > 1

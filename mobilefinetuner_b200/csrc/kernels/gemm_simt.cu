@@ -137,6 +137,8 @@ gemm_simt_kernel(GemmParams p) {
             if (p.bias) v += p.bias[gn];
             int64_t off = int64_t(gm) * p.ldc + gn;
             if (p.beta != 0.f) v += p.beta * C[off];
+            if (p.addend) v += p.addend[bz * p.stride_c + int64_t(gm) * p.ld_addend + gn];
+            if (p.gelu_grad_x) v *= gelu_tanh_grad_f(p.gelu_grad_x[bz * p.stride_c + int64_t(gm) * p.ld_gelu_grad_x + gn]);
             C[off] = v;
             if (G) G[off] = gelu_tanh_f(v);
         }
@@ -158,6 +160,8 @@ __global__ void gemm_splitk_reduce_kernel(GemmParams p) {
         if (p.bias) v += p.bias[gn];
         const int64_t off = bz * p.stride_c + int64_t(gm) * p.ldc + gn;
         if (p.beta != 0.f) v += p.beta * p.c[off];
+        if (p.addend) v += p.addend[bz * p.stride_c + int64_t(gm) * p.ld_addend + gn];
+        if (p.gelu_grad_x) v *= gelu_tanh_grad_f(p.gelu_grad_x[bz * p.stride_c + int64_t(gm) * p.ld_gelu_grad_x + gn]);
         p.c[off] = v;
         if (p.gelu_out) p.gelu_out[off] = gelu_tanh_f(v);
     }

@@ -158,6 +158,8 @@ struct TcArgs {
     float* c; int64_t ldc, stride_c;
     float* gelu_out;
     const float* bias;
+    const float* addend; int64_t ld_addend;
+    const float* gelu_grad_x; int64_t ld_gelu_grad_x;
     float alpha, beta;
     int tiles_m, tiles_n;
     int debug;                 // MFT_GEMM_DEBUG bits (kernel experiments): 1 = no global stores, 2 = no smem staging either, 4 = no TMEM loads
@@ -166,7 +168,9 @@ struct TcArgs {
 // BF16 = false: fp32 operands in HBM, TF32 MMA (32 elements per 128-byte k-block, K = 8 per instruction).
 // BF16 = true : bf16 operands in HBM, kind::f16 MMA (64 elements per k-block, K = 16 per instruction): same bytes per
 //               k-block, twice the FLOPs per byte staged.
-template <int BN, int CG, bool BF16>
+// FUSED = true adds the residual / GELU-gradient operands to the epilogue; a separate instantiation so that the plain
+// epilogue's instruction schedule (which bounds the kernel on short-K shapes) is not disturbed by code it never runs.
+template <int BN, int CG, bool BF16, bool FUSED>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2, TcArgs p) {
@@ -309,6 +313,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15u) == 0) &&
                             ((p.stride_c & 3) == 0) &&
                             (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0) &&
+                            (!p.addend || (((reinterpret_cast<uintptr_t>(p.addend) & 15u) | (p.ld_addend & 3)) == 0)) &&
+                            (!p.gelu_grad_x || (((reinterpret_cast<uintptr_t>(p.gelu_grad_x) & 15u) | (p.ld_gelu_grad_x & 3)) == 0)) &&
                             (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
         int it = 0;
         for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
@@ -323,6 +329,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const int n0 = nt * BN;
             float* cbase = p.c + int64_t(bz) * p.stride_c;
             float* gbase = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c : nullptr;
+            const float* abase = (FUSED && p.addend) ? p.addend + int64_t(bz) * p.stride_c : nullptr;
+            const float* xbase = (FUSED && p.gelu_grad_x) ? p.gelu_grad_x + int64_t(bz) * p.stride_c : nullptr;
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.n) break;               // warp-uniform
@@ -338,7 +346,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 __syncwarp();
                 const int col = n0 + c0 + c4 * 4;
                 if (p.debug & 1) { __syncwarp(); continue; }
-                if (vec_ok && col + 4 <= p.n) {
+                if (vec_ok && col + 4 <= p.n && (!FUSED || (!abase && !xbase))) {
                     float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (p.bias) bb = __ldg(reinterpret_cast<const float4*>(p.bias + col));
 #pragma unroll
@@ -359,6 +367,53 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                     make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
                         }
                     }
+                } else if (FUSED && vec_ok && col + 4 <= p.n) {   // fused residual / GELU-gradient operands
+                    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (p.bias) bb = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                    // every global operand of the chunk is requested before the first use, the staged accumulators are
+                    // read back in one batch, and only then the math and the eight row stores run
+                    float4 ad[8], gx[8], old[8], acc4[8];
+                    if (abase) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int grow = row_base + q * 4 + r4;
+                            if (grow < p.m) ad[q] = __ldcs(reinterpret_cast<const float4*>(abase + int64_t(grow) * p.ld_addend + col));
+                        }
+                    }
+                    if (xbase) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int grow = row_base + q * 4 + r4;
+                            if (grow < p.m) gx[q] = __ldcs(reinterpret_cast<const float4*>(xbase + int64_t(grow) * p.ld_gelu_grad_x + col));
+                        }
+                    }
+                    if (p.beta != 0.f) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int grow = row_base + q * 4 + r4;
+                            if (grow < p.m) old[q] = *reinterpret_cast<const float4*>(cbase + int64_t(grow) * p.ldc + col);
+                        }
+                    }
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) acc4[q] = *reinterpret_cast<const float4*>(stg + (q * 4 + r4) * kEpiPitch + c4 * 4);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const int grow = row_base + q * 4 + r4;
+                        if (grow < p.m) {
+                            const float4 a = acc4[q];
+                            float4 o = make_float4(a.x * p.alpha + bb.x, a.y * p.alpha + bb.y, a.z * p.alpha + bb.z, a.w * p.alpha + bb.w);
+                            if (p.beta != 0.f) { o.x += p.beta * old[q].x; o.y += p.beta * old[q].y; o.z += p.beta * old[q].z; o.w += p.beta * old[q].w; }
+                            if (abase) { o.x += ad[q].x; o.y += ad[q].y; o.z += ad[q].z; o.w += ad[q].w; }
+                            if (xbase) {
+                                o.x *= gelu_tanh_grad_f(gx[q].x); o.y *= gelu_tanh_grad_f(gx[q].y);
+                                o.z *= gelu_tanh_grad_f(gx[q].z); o.w *= gelu_tanh_grad_f(gx[q].w);
+                            }
+                            *reinterpret_cast<float4*>(cbase + int64_t(grow) * p.ldc + col) = o;
+                            if (gbase)
+                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) =
+                                    make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                        }
+                    }
                 } else {
 #pragma unroll 1
                     for (int q = 0; q < 8; ++q) {
@@ -372,6 +427,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             if (p.bias) o += __ldg(p.bias + cc);
                             float* dst = cbase + int64_t(grow) * p.ldc + cc;
                             if (p.beta != 0.f) o += p.beta * *dst;
+                            if (FUSED && abase) o += abase[int64_t(grow) * p.ld_addend + cc];
+                            if (FUSED && xbase) o *= gelu_tanh_grad_f(xbase[int64_t(grow) * p.ld_gelu_grad_x + cc]);
                             *dst = o;
                             if (gbase) gbase[int64_t(grow) * p.ldc + cc] = gelu_tanh_f(o);
                         }
@@ -518,8 +575,8 @@ void gemm_tc_profile_read(double* flops, double* ms, long long* launches) {
     if (launches) *launches = g_prof.launches;
 }
 
-template <int BN, int CG, bool BF16>
-static int launch_tc(const GemmParams& p, cudaStream_t st) {
+template <int BN, int CG, bool BF16, bool FUSED>
+static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     using Cfg = TcCfg<BN, CG>;
     constexpr int KE = BF16 ? 64 : 32;
     CUtensorMap ma, mb, ma2, mb2;
@@ -536,12 +593,13 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;
     a.alpha = p.alpha; a.beta = p.beta;
+    a.addend = p.addend; a.ld_addend = p.ld_addend; a.gelu_grad_x = p.gelu_grad_x; a.ld_gelu_grad_x = p.ld_gelu_grad_x;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
     static const int dbg = [] { const char* e = getenv("MFT_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     a.debug = dbg;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
         if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
         attr_set = true;
     }
@@ -574,12 +632,18 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16>, ma, mb, ma2, mb2, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED>, ma, mb, ma2, mb2, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): %s", cudaGetErrorString(e));
     return 0;
+}
+
+template <int BN, int CG, bool BF16>
+static int launch_tc(const GemmParams& p, cudaStream_t st) {
+    if (p.addend || p.gelu_grad_x) return launch_tc_impl<BN, CG, BF16, true>(p, st);
+    return launch_tc_impl<BN, CG, BF16, false>(p, st);
 }
 
 static bool env_two_cta() {

@@ -15,7 +15,7 @@ namespace mft {
 // distinct banks. The grid is sized by the launcher (RPW) so that every SM holds several CTAs: one CTA's staging of A
 // overlaps another's streaming.
 template <int RPW, int RMAX, int KC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (RPW <= 2 && RMAX <= 16) ? 2 : 1)
 lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
                  float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha) {
     constexpr int PITCH = RMAX + 4;
@@ -32,33 +32,49 @@ lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restri
 #pragma unroll
         for (int c = 0; c < RMAX; ++c) acc[i][c] = 0.f;
 
+    constexpr int NJ = KC / 32;
     for (int k0 = 0; k0 < K; k0 += KC) {
         const int kc = min(KC, K - k0);
-        __syncthreads();
-        for (int idx = threadIdx.x; idx < KC * RMAX; idx += 256) {
-            int kk, c;
-            if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
-            float v = 0.f;
-            if (kk < kc && c < r) v = a_is_kr ? __ldg(a + int64_t(k0 + kk) * lda + c) : __ldg(a + int64_t(c) * lda + k0 + kk);
-            At[kk * PITCH + c] = v;
+        // this chunk's x values first: their latency overlaps the staging of A below
+        float xv[NJ][RPW];
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) {
+            const int kk = j * 32 + lane;
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) xv[j][i] = (live[i] && kk < kc) ? ld_stream(xr[i] + k0 + kk) : 0.f;
+        }
+        {   // stage the A chunk: all loads of a thread are issued before the first store (fixed trip count, fully unrolled)
+            constexpr int NS = KC * RMAX / 256;
+            float stage[NS];
+#pragma unroll
+            for (int it = 0; it < NS; ++it) {
+                const int idx = it * 256 + threadIdx.x;
+                int kk, c;
+                if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
+                stage[it] = (kk < kc && c < r) ? (a_is_kr ? __ldg(a + int64_t(k0 + kk) * lda + c) : __ldg(a + int64_t(c) * lda + k0 + kk)) : 0.f;
+            }
+            __syncthreads();     // the previous chunk's readers are done with At
+#pragma unroll
+            for (int it = 0; it < NS; ++it) {
+                const int idx = it * 256 + threadIdx.x;
+                int kk, c;
+                if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
+                At[kk * PITCH + c] = stage[it];
+            }
         }
         __syncthreads();
-#pragma unroll 4
-        for (int j = 0; j < KC / 32; ++j) {
-            const int kk = j * 32 + lane;
-            float xv[RPW];
 #pragma unroll
-            for (int i = 0; i < RPW; ++i) xv[i] = (live[i] && kk < kc) ? ld_stream(xr[i] + k0 + kk) : 0.f;
-            const float4* arow = reinterpret_cast<const float4*>(At + kk * PITCH);
+        for (int j = 0; j < NJ; ++j) {
+            const float4* arow = reinterpret_cast<const float4*>(At + (j * 32 + lane) * PITCH);
 #pragma unroll
             for (int c4 = 0; c4 < RMAX / 4; ++c4) {
                 const float4 av = arow[c4];
 #pragma unroll
                 for (int i = 0; i < RPW; ++i) {
-                    acc[i][c4 * 4 + 0] = fmaf(xv[i], av.x, acc[i][c4 * 4 + 0]);
-                    acc[i][c4 * 4 + 1] = fmaf(xv[i], av.y, acc[i][c4 * 4 + 1]);
-                    acc[i][c4 * 4 + 2] = fmaf(xv[i], av.z, acc[i][c4 * 4 + 2]);
-                    acc[i][c4 * 4 + 3] = fmaf(xv[i], av.w, acc[i][c4 * 4 + 3]);
+                    acc[i][c4 * 4 + 0] = fmaf(xv[j][i], av.x, acc[i][c4 * 4 + 0]);
+                    acc[i][c4 * 4 + 1] = fmaf(xv[j][i], av.y, acc[i][c4 * 4 + 1]);
+                    acc[i][c4 * 4 + 2] = fmaf(xv[j][i], av.z, acc[i][c4 * 4 + 2]);
+                    acc[i][c4 * 4 + 3] = fmaf(xv[j][i], av.w, acc[i][c4 * 4 + 3]);
                 }
             }
         }
@@ -77,20 +93,47 @@ lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restri
 // W and RMAX accumulators per column. Row-groups are summed through shared memory in a fixed order, so one partial
 // [r, cols] tile leaves the CTA; the partials over the token splits are summed (fixed order again) by the reduce kernel.
 constexpr int kTnRows = 128, kTnRG = 4, kTnCT = 64;
+// One arrival counter per column block of lora_tn; zero between launches (the reducing CTA resets its counter). Launches
+// are stream-ordered on the library's single stream, so at most one launch uses the table at a time.
+constexpr int kTnMaxTickets = 1024;
+__device__ unsigned g_tn_tickets[kTnMaxTickets];
 
 template <int CPT, int RMAX>
 __global__ void __launch_bounds__(kTnRG * kTnCT)
 lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
-               float* __restrict__ partial, int64_t T, int q, int r) {
+               float* __restrict__ partial, int64_t T, int q, int r, float* __restrict__ out, int64_t ldo, int out_is_rq,
+               float alpha, int use_tickets) {
     extern __shared__ __align__(16) float sm[];
     float* Ss = sm;                                  // [kTnRows][RMAX]
     float* red = sm + kTnRows * RMAX;                // [RMAX][kTnCT * CPT]
     const int ct = threadIdx.x % kTnCT, rg = threadIdx.x / kTnCT;
     const int col = (blockIdx.x * kTnCT + ct) * CPT;
     const int64_t t0 = int64_t(blockIdx.y) * kTnRows;
-    for (int idx = threadIdx.x; idx < kTnRows * RMAX; idx += kTnRG * kTnCT) {
-        const int tt = idx / RMAX, c = idx % RMAX;
-        Ss[idx] = (t0 + tt < T && c < r) ? __ldg(s + (t0 + tt) * lds + c) : 0.f;
+    constexpr int RPG = kTnRows / kTnRG;             // rows per row-group (32): every W load of the thread is issued up front
+    const bool colok = col < q;                      // q % CPT == 0 is guaranteed by the launcher
+    float wv[RPG][CPT];
+#pragma unroll
+    for (int u = 0; u < RPG; ++u) {
+        const int64_t row = t0 + rg * RPG + u;
+        const bool ok = colok && row < T;
+        if (CPT == 2) {
+            const float2 v = ok ? ld_stream(reinterpret_cast<const float2*>(w + row * ldw + col)) : make_float2(0.f, 0.f);
+            wv[u][0] = v.x; wv[u][CPT - 1] = v.y;
+        } else {
+            wv[u][0] = ok ? ld_stream(w + row * ldw + col) : 0.f;
+        }
+    }
+    {
+        constexpr int NS = kTnRows * RMAX / (kTnRG * kTnCT);
+        float stage[NS];
+#pragma unroll
+        for (int it = 0; it < NS; ++it) {
+            const int idx = it * (kTnRG * kTnCT) + threadIdx.x;
+            const int tt = idx / RMAX, c = idx % RMAX;
+            stage[it] = (t0 + tt < T && c < r) ? __ldg(s + (t0 + tt) * lds + c) : 0.f;
+        }
+#pragma unroll
+        for (int it = 0; it < NS; ++it) Ss[it * (kTnRG * kTnCT) + threadIdx.x] = stage[it];
     }
     __syncthreads();
     float acc[CPT][RMAX];
@@ -98,36 +141,18 @@ lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict
     for (int e = 0; e < CPT; ++e)
 #pragma unroll
         for (int c = 0; c < RMAX; ++c) acc[e][c] = 0.f;
-    constexpr int RPG = kTnRows / kTnRG;             // rows per row-group (32)
-    constexpr int U = 8;
-    const bool colok = col < q;                      // q % CPT == 0 is guaranteed by the launcher
-#pragma unroll 1
-    for (int u0 = 0; u0 < RPG; u0 += U) {
-        float wv[U][CPT];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int64_t row = t0 + rg * RPG + u0 + u;
-            const bool ok = colok && row < T;
-            if (CPT == 2) {
-                const float2 v = ok ? ld_stream(reinterpret_cast<const float2*>(w + row * ldw + col)) : make_float2(0.f, 0.f);
-                wv[u][0] = v.x; wv[u][CPT - 1] = v.y;
-            } else {
-                wv[u][0] = ok ? ld_stream(w + row * ldw + col) : 0.f;
-            }
-        }
+    for (int u = 0; u < RPG; ++u) {
+        const float4* srow = reinterpret_cast<const float4*>(Ss + (rg * RPG + u) * RMAX);
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const float4* srow = reinterpret_cast<const float4*>(Ss + (rg * RPG + u0 + u) * RMAX);
+        for (int c4 = 0; c4 < RMAX / 4; ++c4) {
+            const float4 sv = srow[c4];              // same address for the whole warp: broadcast
 #pragma unroll
-            for (int c4 = 0; c4 < RMAX / 4; ++c4) {
-                const float4 sv = srow[c4];          // same address for the whole warp: broadcast
-#pragma unroll
-                for (int e = 0; e < CPT; ++e) {
-                    acc[e][c4 * 4 + 0] = fmaf(wv[u][e], sv.x, acc[e][c4 * 4 + 0]);
-                    acc[e][c4 * 4 + 1] = fmaf(wv[u][e], sv.y, acc[e][c4 * 4 + 1]);
-                    acc[e][c4 * 4 + 2] = fmaf(wv[u][e], sv.z, acc[e][c4 * 4 + 2]);
-                    acc[e][c4 * 4 + 3] = fmaf(wv[u][e], sv.w, acc[e][c4 * 4 + 3]);
-                }
+            for (int e = 0; e < CPT; ++e) {
+                acc[e][c4 * 4 + 0] = fmaf(wv[u][e], sv.x, acc[e][c4 * 4 + 0]);
+                acc[e][c4 * 4 + 1] = fmaf(wv[u][e], sv.y, acc[e][c4 * 4 + 1]);
+                acc[e][c4 * 4 + 2] = fmaf(wv[u][e], sv.z, acc[e][c4 * 4 + 2]);
+                acc[e][c4 * 4 + 3] = fmaf(wv[u][e], sv.w, acc[e][c4 * 4 + 3]);
             }
         }
     }
@@ -144,12 +169,45 @@ lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict
         }
         __syncthreads();
     }
+    constexpr int W = kTnCT * CPT;                   // columns of this CTA
     float* P = partial + size_t(blockIdx.y) * size_t(r) * q;
-    for (int idx = threadIdx.x; idx < r * kTnCT * CPT; idx += kTnRG * kTnCT) {
-        const int c = idx / (kTnCT * CPT), cc = idx % (kTnCT * CPT);
-        const int gcol = blockIdx.x * kTnCT * CPT + cc;
-        if (gcol < q) P[size_t(c) * q + gcol] = red[c * (kTnCT * CPT) + cc];
+    for (int idx = threadIdx.x; idx < r * W; idx += kTnRG * kTnCT) {
+        const int c = idx / W, cc = idx % W;
+        const int gcol = blockIdx.x * W + cc;
+        if (gcol < q) P[size_t(c) * q + gcol] = red[c * W + cc];
     }
+    if (!use_tickets) return;                        // separate reduce kernel follows
+    unsigned* tickets = g_tn_tickets;
+    // The CTA that finishes last for this column block sums the token splits in index order (so the result does not
+    // depend on which CTA that is), applies alpha and writes the output; it leaves the ticket counter at zero again.
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&tickets[blockIdx.x], 1u) == gridDim.y - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int splits = gridDim.y;
+    const size_t n = size_t(r) * q;
+    for (int idx = threadIdx.x; idx < r * W; idx += kTnRG * kTnCT) {
+        const int c = idx / W, cc = idx % W;
+        const int gcol = blockIdx.x * W + cc;
+        if (gcol >= q) continue;
+        const float* src = partial + size_t(c) * q + gcol;
+        float v = 0.f;
+        int sp = 0;
+        for (; sp + 8 <= splits; sp += 8) {
+            float p[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) p[u] = __ldcg(src + size_t(sp + u) * n);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v += p[u];
+        }
+        for (; sp < splits; ++sp) v += __ldcg(src + size_t(sp) * n);
+        v *= alpha;
+        if (out_is_rq) out[int64_t(c) * ldo + gcol] = v; else out[int64_t(gcol) * ldo + c] = v;
+    }
+    if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
 }
 
 // out[c][col] (out_is_rq) or out[col][c] = alpha * sum over splits, fixed order
@@ -159,7 +217,15 @@ __global__ void lora_tn_reduce_kernel(const float* __restrict__ partial, float* 
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         const int c = int(idx / q), col = int(idx % q);
         float v = 0.f;
-        for (int sp = 0; sp < splits; ++sp) v += partial[size_t(sp) * n + idx];
+        int sp = 0;
+        for (; sp + 8 <= splits; sp += 8) {          // eight loads in flight, summed in index order
+            float pv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) pv[u] = __ldcg(partial + size_t(sp + u) * n + idx);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v += pv[u];
+        }
+        for (; sp < splits; ++sp) v += __ldcg(partial + size_t(sp) * n + idx);
         v *= alpha;
         if (out_is_rq) out[int64_t(c) * ldo + col] = v; else out[int64_t(col) * ldo + c] = v;
     }
@@ -189,11 +255,11 @@ extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_
     const int k = int(K);
     if (r <= 16) {
         // rows per warp: as many as still leave >= 2 CTAs per SM
-        if (T >= int64_t(32) * 2 * kNumSMs) launch_down<4, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+        if (T >= int64_t(32) * 2 * kNumSMs) launch_down<4, 16, 128>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
         else if (T >= int64_t(16) * kNumSMs) launch_down<2, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
         else launch_down<1, 16, 256>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
     } else {
-        launch_down<1, 64, 128>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
+        launch_down<1, 64, 64>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
     }
     MFT_CHECK_LAUNCH("mft_lora_down");
     return 0;
@@ -215,17 +281,25 @@ extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t 
     cudaStream_t st = as_stream(stream);
     float* partial = static_cast<float*>(workspace);
     const bool vec = r <= 16 && (q & 1) == 0 && (ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(w) & 7) == 0;
+    const int64_t colblocks = ceil_div(q, vec ? kTnCT * 2 : kTnCT);
+    // the last-arriving CTA sums the splits itself when there are few of them; a long split list is summed faster by a
+    // separate, fully parallel launch
+    const int tk = (colblocks <= kTnMaxTickets && splits <= 8) ? 1 : 0;
     if (vec) {
         const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
-        lora_tn_kernel<2, 16><<<dim3(unsigned(ceil_div(q, kTnCT * 2)), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r);
+        lora_tn_kernel<2, 16><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
+                                                                                                 out_is_rq, alpha, tk);
     } else {
         const size_t smem = (size_t(kTnRows) * 64 + size_t(64) * kTnCT) * sizeof(float);
         static bool attr = false;
         if (!attr) { cudaFuncSetAttribute(lora_tn_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); attr = true; }
-        lora_tn_kernel<1, 64><<<dim3(unsigned(ceil_div(q, kTnCT)), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r);
+        lora_tn_kernel<1, 64><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
+                                                                                                 out_is_rq, alpha, tk);
     }
-    add_launches(1);
-    lora_tn_reduce_kernel<<<stream_grid(int64_t(r) * q, 256), 256, 0, st>>>(partial, out, ldo, out_is_rq, int(splits), int(q), r, alpha);
+    if (!tk) {
+        add_launches(1);
+        lora_tn_reduce_kernel<<<stream_grid(int64_t(r) * q, 256), 256, 0, st>>>(partial, out, ldo, out_is_rq, int(splits), int(q), r, alpha);
+    }
     MFT_CHECK_LAUNCH("mft_lora_tn");
     return 0;
 }

@@ -9,26 +9,70 @@ namespace mft {
 constexpr int kOptCtas = kNumSMs * 4;
 constexpr int kOptThreads = 256;
 
+// Work decomposition shared by the multi-tensor kernels: every tensor is cut into chunks of kOptChunk elements and the CTAs
+// grid-stride over the concatenated chunk list, so 96 small LoRA factors fill the chip as well as one large matrix does
+// (a loop "for each tensor: grid-stride over its elements" leaves most CTAs idle on tensors smaller than the grid).
+constexpr int kOptChunk = kOptThreads * 16;
+constexpr int kOptMaxSlots = 12000;       // (slots + 1) ints of shared memory
+
+// pre[s] = number of chunks before tensor s (tensors without a gradient contribute none when grads_only). Returns the total.
+__device__ int chunk_prefix(const mft_tensor_slot* __restrict__ slots, int num_slots, int* pre, bool grads_only) {
+    for (int s = threadIdx.x; s < num_slots; s += blockDim.x)
+        pre[s + 1] = (grads_only && !slots[s].grad) ? 0 : int((slots[s].n + kOptChunk - 1) / kOptChunk);
+    if (threadIdx.x == 0) pre[0] = 0;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int carry = 0;
+        for (int base = 0; base < num_slots; base += 32) {
+            const int i = base + int(threadIdx.x);
+            int v = i < num_slots ? pre[i + 1] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, v, o);
+                if (int(threadIdx.x) >= o) v += u;
+            }
+            if (i < num_slots) pre[i + 1] = v + carry;
+            carry += __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+    return pre[num_slots];
+}
+__device__ __forceinline__ int chunk_slot(const int* pre, int num_slots, int c) {   // s with pre[s] <= c < pre[s+1]
+    int lo = 0, hi = num_slots - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (pre[mid] <= c) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
 __global__ void __launch_bounds__(kOptThreads)
 grad_sumsq_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, double* __restrict__ partial) {
+    extern __shared__ int pre[];
     __shared__ double dred[32];
+    const int total = chunk_prefix(slots, num_slots, pre, true);
     double acc = 0.0;
-    const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
-    const int64_t stride = int64_t(gridDim.x) * kOptThreads;
-    for (int s = 0; s < num_slots; ++s) {
+    for (int c = blockIdx.x; c < total; c += gridDim.x) {
+        const int s = chunk_slot(pre, num_slots, c);
         const float* g = slots[s].grad;
-        const int64_t n = slots[s].n;
-        if (!g) continue;
+        const int64_t n = slots[s].n, e0 = int64_t(c - pre[s]) * kOptChunk;
         if ((reinterpret_cast<uintptr_t>(g) & 15u) == 0) {
-            const float4* g4 = reinterpret_cast<const float4*>(g);
-            const int64_t n4 = n >> 2;
-            for (int64_t i = tid; i < n4; i += stride) {
-                float4 a = g4[i];
-                acc += double(a.x) * a.x + double(a.y) * a.y + double(a.z) * a.z + double(a.w) * a.w;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t i = e0 + (j * kOptThreads + threadIdx.x) * 4;
+                if (i + 3 < n) {
+                    const float4 a = *reinterpret_cast<const float4*>(g + i);
+                    acc += double(a.x) * a.x + double(a.y) * a.y + double(a.z) * a.z + double(a.w) * a.w;
+                } else {
+                    for (int64_t k = i; k < n; ++k) acc += double(g[k]) * g[k];
+                }
             }
-            for (int64_t i = (n4 << 2) + tid; i < n; i += stride) acc += double(g[i]) * g[i];
         } else {
-            for (int64_t i = tid; i < n; i += stride) acc += double(g[i]) * g[i];
+            for (int j = 0; j < 16; ++j) {
+                const int64_t i = e0 + j * kOptThreads + threadIdx.x;
+                if (i < n) acc += double(g[i]) * g[i];
+            }
         }
     }
     acc = block_sum<double>(acc, dred);
@@ -87,39 +131,53 @@ __global__ void adam_advance_kernel(const mft_tensor_slot* __restrict__ slots, i
 __global__ void __launch_bounds__(kOptThreads)
 adam_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float lr, const float* __restrict__ lr_dev, float b1, float b2,
             float eps, float wd, const float* __restrict__ grad_scale, const int32_t* __restrict__ steps) {
+    extern __shared__ int pre[];
+    const int total = chunk_prefix(slots, num_slots, pre, true);
     const float gs = grad_scale ? grad_scale[0] : 1.0f;
     if (lr_dev) lr = lr_dev[0];
     const float omb1 = 1.0f - b1, omb2 = 1.0f - b2;
-    const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
-    const int64_t stride = int64_t(gridDim.x) * kOptThreads;
-    for (int s = 0; s < num_slots; ++s) {
+    for (int c = blockIdx.x; c < total; c += gridDim.x) {
+        const int s = chunk_slot(pre, num_slots, c);
         mft_tensor_slot sl = slots[s];
-        if (!sl.grad) continue;
         if (steps) {   // device-resident step counters: bias corrections computed here (optim/adam.cpp:222-228)
             sl.bias_corr1 = 1.0f - powf(b1, float(steps[s]));
             sl.bias_corr2 = 1.0f - powf(b2, float(steps[s]));
         }
+        const int64_t e0 = int64_t(c - pre[s]) * kOptChunk;
         const bool vec = ((reinterpret_cast<uintptr_t>(sl.param) | reinterpret_cast<uintptr_t>(sl.grad) |
                            reinterpret_cast<uintptr_t>(sl.m) | reinterpret_cast<uintptr_t>(sl.v)) & 15u) == 0;
         if (vec) {
-            float4* p4 = reinterpret_cast<float4*>(sl.param);
-            const float4* g4 = reinterpret_cast<const float4*>(sl.grad);
-            float4* m4 = reinterpret_cast<float4*>(sl.m);
-            float4* v4 = reinterpret_cast<float4*>(sl.v);
-            const int64_t n4 = sl.n >> 2;
-            for (int64_t i = tid; i < n4; i += stride) {
-                float4 p = p4[i], g = g4[i], m = m4[i], v = v4[i];
-                adam_one(p.x, g.x, m.x, v.x, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
-                adam_one(p.y, g.y, m.y, v.y, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
-                adam_one(p.z, g.z, m.z, v.z, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
-                adam_one(p.w, g.w, m.w, v.w, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
-                p4[i] = p; m4[i] = m; v4[i] = v;
+            float4 p[4], g[4], m[4], v[4];
+            bool full[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {      // all loads of the chunk first
+                const int64_t i = e0 + (j * kOptThreads + threadIdx.x) * 4;
+                full[j] = i + 3 < sl.n;
+                if (full[j]) {
+                    p[j] = *reinterpret_cast<const float4*>(sl.param + i); g[j] = *reinterpret_cast<const float4*>(sl.grad + i);
+                    m[j] = *reinterpret_cast<const float4*>(sl.m + i); v[j] = *reinterpret_cast<const float4*>(sl.v + i);
+                }
             }
-            for (int64_t i = (n4 << 2) + tid; i < sl.n; i += stride)
-                adam_one(sl.param[i], sl.grad[i], sl.m[i], sl.v[i], lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t i = e0 + (j * kOptThreads + threadIdx.x) * 4;
+                if (full[j]) {
+                    adam_one(p[j].x, g[j].x, m[j].x, v[j].x, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+                    adam_one(p[j].y, g[j].y, m[j].y, v[j].y, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+                    adam_one(p[j].z, g[j].z, m[j].z, v[j].z, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+                    adam_one(p[j].w, g[j].w, m[j].w, v[j].w, lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+                    *reinterpret_cast<float4*>(sl.param + i) = p[j]; *reinterpret_cast<float4*>(sl.m + i) = m[j];
+                    *reinterpret_cast<float4*>(sl.v + i) = v[j];
+                } else {
+                    for (int64_t k = i; k < sl.n; ++k)
+                        adam_one(sl.param[k], sl.grad[k], sl.m[k], sl.v[k], lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+                }
+            }
         } else {
-            for (int64_t i = tid; i < sl.n; i += stride)
-                adam_one(sl.param[i], sl.grad[i], sl.m[i], sl.v[i], lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+            for (int j = 0; j < 16; ++j) {
+                const int64_t i = e0 + j * kOptThreads + threadIdx.x;
+                if (i < sl.n) adam_one(sl.param[i], sl.grad[i], sl.m[i], sl.v[i], lr, b1, b2, omb1, omb2, eps, wd, sl.bias_corr1, sl.bias_corr2, gs);
+            }
         }
     }
 }
@@ -132,13 +190,18 @@ namespace mft {
 // bucket[offset + i] = grad[i] (0 where a tensor has no gradient): one launch packs every gradient for the all-reduce
 __global__ void __launch_bounds__(kOptThreads)
 pack_grads_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float* __restrict__ bucket) {
-    const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
-    const int64_t stride = int64_t(gridDim.x) * kOptThreads;
-    for (int s = 0; s < num_slots; ++s) {
+    extern __shared__ int pre[];
+    const int total = chunk_prefix(slots, num_slots, pre, false);
+    for (int c = blockIdx.x; c < total; c += gridDim.x) {
+        const int s = chunk_slot(pre, num_slots, c);
         const float* g = slots[s].grad;
         float* dst = bucket + slots[s].bucket_offset;
-        const int64_t n = slots[s].n;
-        for (int64_t i = tid; i < n; i += stride) dst[i] = g ? g[i] : 0.f;
+        const int64_t n = slots[s].n, e0 = int64_t(c - pre[s]) * kOptChunk;
+#pragma unroll 4
+        for (int j = 0; j < 16; ++j) {
+            const int64_t i = e0 + j * kOptThreads + threadIdx.x;
+            if (i < n) dst[i] = g ? g[i] : 0.f;
+        }
     }
 }
 }  // namespace mft
@@ -146,7 +209,8 @@ pack_grads_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, floa
 extern "C" int mft_pack_grads(const mft_tensor_slot* slots, int32_t num_slots, float* bucket, mft_stream_t stream) {
     if (num_slots == 0) return 0;
     if (!slots || !bucket) return mft::set_error(1, "mft_pack_grads: null pointer");
-    mft::pack_grads_kernel<<<mft::kOptCtas, mft::kOptThreads, 0, mft::as_stream(stream)>>>(slots, num_slots, bucket);
+    if (num_slots > mft::kOptMaxSlots) return mft::set_error(1, "mft_pack_grads: more than %d tensors", mft::kOptMaxSlots);
+    mft::pack_grads_kernel<<<mft::kOptCtas, mft::kOptThreads, size_t(num_slots + 1) * sizeof(int), mft::as_stream(stream)>>>(slots, num_slots, bucket);
     MFT_CHECK_LAUNCH("mft_pack_grads");
     return 0;
 }
@@ -161,7 +225,8 @@ extern "C" int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, d
         return set_error(1, "mft_grad_sumsq: workspace too small");
     cudaStream_t st = as_stream(stream);
     double* partial = static_cast<double*>(workspace);
-    grad_sumsq_kernel<<<kOptCtas, kOptThreads, 0, st>>>(slots, num_slots, partial);
+    if (num_slots > kOptMaxSlots) return set_error(1, "mft_grad_sumsq: more than %d tensors", kOptMaxSlots);
+    grad_sumsq_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), st>>>(slots, num_slots, partial);
     sumsq_final_kernel<<<1, 1024, 0, st>>>(partial, kOptCtas, out);
     add_launches(1);
     MFT_CHECK_LAUNCH("mft_grad_sumsq");
@@ -188,7 +253,8 @@ extern "C" int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, fl
                              float eps, float weight_decay, const float* grad_scale, mft_stream_t stream) {
     if (num_slots == 0) return 0;
     if (!slots) return set_error(1, "mft_adam_step: null slot table");
-    adam_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, lr, nullptr, beta1, beta2, eps, weight_decay, grad_scale, nullptr);
+    if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step: more than %d tensors", kOptMaxSlots);
+    adam_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream)>>>(slots, num_slots, lr, nullptr, beta1, beta2, eps, weight_decay, grad_scale, nullptr);
     MFT_CHECK_LAUNCH("mft_adam_step");
     return 0;
 }
@@ -199,7 +265,8 @@ extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots
     if (!slots || !steps || !lr) return set_error(1, "mft_adam_step_dev: null pointer");
     adam_advance_kernel<<<unsigned(ceil_div(num_slots, 256)), 256, 0, as_stream(stream)>>>(slots, num_slots, steps);
     add_launches(1);
-    adam_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
+    if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step_dev: more than %d tensors", kOptMaxSlots);
+    adam_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream)>>>(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
     MFT_CHECK_LAUNCH("mft_adam_step_dev");
     return 0;
 }

@@ -177,6 +177,46 @@ def test_gemm_tc_epilogue_bias_beta_gelu_and_lora_segment(capi):
     assert rel(g, O.gelu_fwd(c.cpu().numpy())) < 2e-5
 
 
+@pytest.mark.parametrize("m,n,k,path", [(512, 768, 768, "tc"), (300, 200, 100, "tc"), (512, 768, 768, "simt"), (70, 90, 33, "simt"),
+                                          (96, 64, 1024, "splitk")])
+def test_gemm_epilogue_residual_and_gelu_grad(capi, m, n, k, path):
+    """v = acc + bias + addend; v *= gelu'(x)  — equals the separate add / GeluBackward kernels on the same fp32 product."""
+    rng = np.random.default_rng(m + n + k)
+    a = rng.standard_normal((m, k)).astype(np.float32)
+    b = (rng.standard_normal((n, k)) * 0.05).astype(np.float32)
+    bias = rng.standard_normal(n).astype(np.float32)
+    res = rng.standard_normal((m, n)).astype(np.float32)
+    gx = rng.standard_normal((m, n)).astype(np.float32)
+    da, db, dbias, dres, dgx = dev(a), dev(b), dev(bias), dev(res), dev(gx)
+    prev = capi.lib.mft_use_tensor_cores(1 if path == "tc" else 0)
+    try:
+        def run(addend, ggx):
+            c = torch.full((m, n), float("nan"), device="cuda")
+            args = capi.GemmArgs(m, n, k, da.data_ptr(), k, 0, db.data_ptr(), k, 1, c.data_ptr(), n, 1.0, 0.0, dbias.data_ptr(), None,
+                                 0, None, 0, None, 0, 1, 0, 0, 0, addend.data_ptr() if addend is not None else None, n,
+                                 ggx.data_ptr() if ggx is not None else None, n)
+            if path == "splitk":
+                w = ws(capi.lib.mft_gemm_splitk_workspace_bytes(m, n, 1, 4))
+                capi.check(capi.lib.mft_gemm_splitk(C.byref(args), 4, w.data_ptr(), w.numel(), None), "mft_gemm_splitk")
+            else:
+                assert capi.lib.mft_gemm_uses_tensor_cores(C.byref(args)) == (1 if path == "tc" else 0)
+                capi.check(capi.lib.mft_gemm(C.byref(args), None), "mft_gemm")
+            torch.cuda.synchronize()
+            return c
+        plain = run(None, None)
+        fused = run(dres, dgx)
+    finally:
+        capi.lib.mft_use_tensor_cores(prev)
+    # separate kernels on the plain product: add, then GeluBackward
+    s = plain + dres
+    out = torch.empty_like(s)
+    capi.call("mft_gelu_bwd", dgx, s, out, m * n, None)
+    torch.cuda.synchronize()
+    assert torch.equal(fused, out)                      # bit for bit
+    e = (ref_gemm(a, b, 0, 1, bias=bias) + res) * O.gelu_bwd(gx, np.ones_like(gx))
+    assert rel(fused, e) < (TF32_TOL if path == "tc" else FP32_TOL)
+
+
 def test_gemm_tc_batched_and_pitched(capi):
     rng = np.random.default_rng(6)
     a = rng.standard_normal((6, 256, 64)).astype(np.float32)

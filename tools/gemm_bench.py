@@ -13,14 +13,20 @@ SHAPES = [("qkv", 4096, 3072, 1024), ("proj", 4096, 1024, 1024), ("fc_in", 4096,
           ("lm_head", 4096, 50257, 1024), ("lm_head_dx", 4096, 1024, 50264), ("c1_qkv", 512, 2304, 768), ("big", 8192, 8192, 8192)]
 
 
-def bench(name, m, n, k, bf16, iters=20):
+def bench(name, m, n, k, bf16, iters=20, fuse=""):
     dt = torch.bfloat16 if bf16 else torch.float32
     a = torch.randn(m, k, device="cuda").to(dt)
     b = (torch.randn(n, k, device="cuda") * 0.05).to(dt)
     ldc = (n + 31) // 32 * 32
     c = torch.empty(m, ldc, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c.data_ptr(), ldc, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0)
+    bias = torch.randn(n, device="cuda")
+    res = torch.randn(m, ldc, device="cuda") if "res" in fuse else None
+    gx = torch.randn(m, ldc, device="cuda") if "ggrad" in fuse else None
+    gout = torch.empty(m, ldc, device="cuda") if "gelu" in fuse else None
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c.data_ptr(), ldc, 1.0, 0.0, bias.data_ptr() if fuse else None,
+                         gout.data_ptr() if gout is not None else None, 0, None, 0, None, 0, 1, 0, 0, 0,
+                         res.data_ptr() if res is not None else None, ldc, gx.data_ptr() if gx is not None else None, ldc)
     fn = capi.lib.mft_gemm_bf16 if bf16 else capi.lib.mft_gemm
     for _ in range(3):
         capi.check(fn(C.byref(args), None), "gemm")
@@ -36,7 +42,7 @@ def bench(name, m, n, k, bf16, iters=20):
         tot += e0.elapsed_time(e1)
     us = tot / iters * 1e3
     tf = 2.0 * m * n * k / (us * 1e-6) / 1e12
-    print(f"{name:12s} {'bf16' if bf16 else 'tf32'} m={m} n={n} k={k}: {us:8.1f} us  {tf:7.1f} TFLOP/s", flush=True)
+    print(f"{name:12s} {'bf16' if bf16 else 'tf32'} m={m} n={n} k={k} {fuse or 'plain':10s}: {us:8.1f} us  {tf:7.1f} TFLOP/s", flush=True)
 
 
 SKINNY = [("xa   x*A", 4096, 16, 1024, 0, 0), ("dxa gy*B^T", 4096, 16, 1024, 0, 1), ("dB xa^T*gy", 16, 1024, 4096, 1, 0),
@@ -98,6 +104,11 @@ if __name__ == "__main__":
         for sh in SKINNY:
             bench_skinny(*sh)
         bench_lora()
+        sys.exit(0)
+    if sys.argv[1:] == ["fused"]:     # epilogue variants of the c4 shapes
+        for sh, fz in ((SHAPES[1], "bias"), (SHAPES[1], "bias+res"), (SHAPES[3], "bias+res"), (SHAPES[2], "bias"), (SHAPES[2], "bias+gelu"),
+                       (SHAPES[2], "ggrad")):
+            bench(*sh, bf16=False, fuse=fz)
         sys.exit(0)
     which = sys.argv[1:] or ["tf32", "bf16"]
     for mode in which:
