@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmft_b200.so")
+# MFT_B200_LIB: load another build of the same library (kernel-variant experiments, tools/build_variants.sh)
+LIB_PATH = os.environ.get("MFT_B200_LIB") or os.path.join(_HERE, "libmft_b200.so")
 
 
 class MftError(RuntimeError):

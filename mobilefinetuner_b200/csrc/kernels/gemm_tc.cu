@@ -22,9 +22,21 @@ namespace mft {
 constexpr int TBM = 128;          // tile rows  (UMMA M)
 constexpr int TBK = 32;           // fp32 elements per k-block = one 128-byte swizzle span
 constexpr int TUK = 8;            // UMMA K for tf32 (32 bytes)
-constexpr int kTcThreads = 192;
-constexpr int kSmemBudget = 200 * 1024;
-constexpr int kEpiPitch = 36;     // floats per staged row: 16-byte aligned and conflict-free for both access patterns
+#ifndef MFT_TC_EPI_WARPS
+#define MFT_TC_EPI_WARPS 4
+#endif
+#ifndef MFT_TC_EPI_BOXES
+#define MFT_TC_EPI_BOXES 1
+#endif
+constexpr int kEpiWarps = MFT_TC_EPI_WARPS;   // 4 or 8: one or two per TMEM lane group (two: each takes half of the tile's columns)
+constexpr int kEpiBoxes = MFT_TC_EPI_BOXES;   // staging boxes per epilogue warp (2: the next box is filled while the TMA drains one)
+static_assert(kEpiWarps == 4 || kEpiWarps == 8, "epilogue warps");
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;
+constexpr int kEpiPitch = 36;     // floats per staged row (fallback path): 16-byte aligned and conflict-free for both access patterns
+constexpr int kEpiBufBytes = 32 * 128;                  // one 32 x 32 fp32 box in the TMA (128B-swizzled) layout
+constexpr int kEpiStageBytes = (kEpiBoxes * kEpiBufBytes > 32 * kEpiPitch * 4) ? kEpiBoxes * kEpiBufBytes : 5120;   // fallback path needs 4608; keep 1024-byte alignment
+constexpr int kEpiWarpBytes = kEpiStageBytes + 1024;    // boxes + this warp's slice of the bias (<= 256 floats)
+constexpr int kSmemTotal = 227 * 1024;
 
 // CG = CTAs cooperating on one UMMA (cta_group). CG = 2: a cluster of two CTAs computes a 256 x BN tile pair — each CTA
 // stages its own 128 rows of A and HALF of the B tile, the leader issues tcgen05.mma.cta_group::2 (M = 256) which reads
@@ -33,10 +45,13 @@ constexpr int kEpiPitch = 36;     // floats per staged row: 16-byte aligned and 
 template <int BN, int CG = 1> struct TcCfg {
     static constexpr int b_rows = BN / CG;                 // B rows staged by one CTA
     static constexpr int stage_bytes = (TBM + b_rows) * TBK * 4;
-    static constexpr int stages = (kSmemBudget / stage_bytes) > 8 ? 8 : (kSmemBudget / stage_bytes);
+    static constexpr int epi_bytes = kEpiWarps * kEpiWarpBytes;   // per-warp staging for the output boxes
+    static constexpr int budget = kSmemTotal - epi_bytes - 1024 /*align slack*/ - 256 /*barriers*/;
+    static constexpr int stages = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
     static constexpr int tmem_cols = 2 * BN;             // two accumulator buffers
-    static constexpr int epi_bytes = 4 * 32 * kEpiPitch * 4;  // per-warp 32x32 transpose buffers (coalesced stores)
-    static constexpr int smem_bytes = stages * stage_bytes + epi_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int smem_bytes = stages * stage_bytes + epi_bytes + 1024 + 256;
+    static_assert(stages >= 3, "smem ring too shallow");
+    static_assert(stage_bytes % 1024 == 0, "stage size must keep the 1024-byte swizzle alignment");
 };
 
 // ---------------------------------------------------------------- PTX wrappers
@@ -75,6 +90,17 @@ __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMa
         :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// smem box (128B-swizzled, 32 x 32 fp32) -> global, clipped at the tensor edges; completion tracked by bulk groups
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
     asm volatile(
         "{\n\t.reg .b32 ra;\n\t"
@@ -114,6 +140,12 @@ __device__ __forceinline__ void tc_mma_bf16_2sm(uint32_t tmem_d, uint64_t adesc,
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ float gelu_tanh_fast(float x) {     // tanh.approx (one MUFU op, ~2^-11 abs error)
+    const float k0 = 0.7978845608f, k1 = 0.044715f;
+    float th;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(k0 * (x + k1 * x * x * x)));
+    return 0.5f * x * (1.0f + th);
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -162,6 +194,7 @@ struct TcArgs {
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;
     float alpha, beta;
     int tiles_m, tiles_n;
+    int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
     int debug;                 // MFT_GEMM_DEBUG bits (kernel experiments): 1 = no global stores, 2 = no smem staging either, 4 = no TMEM loads
 };
 
@@ -173,7 +206,8 @@ struct TcArgs {
 template <int BN, int CG, bool BF16, bool FUSED>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-               const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2, TcArgs p) {
+               const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
+               const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_g, TcArgs p) {
     using Cfg = TcCfg<BN, CG>;
     constexpr int KE = BF16 ? 64 : 32;                     // elements per k-block (one 128-byte swizzle span)
     const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
@@ -183,7 +217,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     constexpr int NS = Cfg::stages;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    float* epi_stage = reinterpret_cast<float*>(tiles + NS * Cfg::stage_bytes);
+    uint8_t* epi_stage = tiles + NS * Cfg::stage_bytes;      // 1024-byte aligned: stage sizes are multiples of 1024
     uint64_t* bars = reinterpret_cast<uint64_t*>(tiles + NS * Cfg::stage_bytes + Cfg::epi_bytes);
     uint64_t* full = bars;                 // [NS]
     uint64_t* empty = bars + NS;           // [NS]
@@ -201,7 +235,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         for (int i = 0; i < NS; ++i) { mbar_init(&full[i], CG); mbar_init(&empty[i], 1); }      // full: one arrival per CTA, at the leader
-        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4 * CG); }   // tmem_empty: leader only
+        for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], kEpiWarps * CG); }   // tmem_empty: leader only
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -307,8 +341,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         // tcgen05.ld hands each thread one accumulator ROW; storing that directly would hit 32 different 128-byte lines
         // per warp instruction. Each 32x32 chunk is therefore bounced through a per-warp smem buffer so that a warp
         // instruction writes 4 full 128-byte row segments (8 lanes x float4 per row).
-        const int lg = warp & 3;                          // TMEM lane group this warp may touch
-        float* stg = epi_stage + lg * 32 * kEpiPitch;
+        const int lg = warp & 3;                          // TMEM lane group this warp may touch (hardware: warp id % 4)
+        const int half = (warp - 2) >> 2;                 // which part of the tile's columns this warp drains
+        constexpr int HC = BN / (kEpiWarps / 4);          // columns per epilogue warp
+        // all boxes first (each 1024-byte aligned: the 128B swizzle is a function of the absolute smem address), bias slices after
+        uint8_t* wbuf = epi_stage + (warp - 2) * kEpiStageBytes;
+        float* stg = reinterpret_cast<float*>(wbuf);      // fallback path: 32 x kEpiPitch floats (fits in the two boxes)
+        float* sbias = reinterpret_cast<float*>(epi_stage + kEpiWarps * kEpiStageBytes + (warp - 2) * 1024);   // [HC] (HC <= 256)
         const int r4 = lane >> 3, c4 = lane & 7;          // read-back role: row within a group of 4, float4 column
         const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15u) == 0) &&
                             ((p.stride_c & 3) == 0) &&
@@ -316,6 +355,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             (!p.addend || (((reinterpret_cast<uintptr_t>(p.addend) & 15u) | (p.ld_addend & 3)) == 0)) &&
                             (!p.gelu_grad_x || (((reinterpret_cast<uintptr_t>(p.gelu_grad_x) & 15u) | (p.ld_gelu_grad_x & 3)) == 0)) &&
                             (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
+        const bool use_tma = !FUSED && p.tma_c != 0;
+        uint32_t nstore = 0;                              // boxes this warp has handed to the TMA (ring of two buffers)
         int it = 0;
         for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
             const int mt = (tile % tiles_mu) * CG + int(cta_rank);
@@ -331,8 +372,79 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             float* gbase = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c : nullptr;
             const float* abase = (FUSED && p.addend) ? p.addend + int64_t(bz) * p.stride_c : nullptr;
             const float* xbase = (FUSED && p.gelu_grad_x) ? p.gelu_grad_x + int64_t(bz) * p.stride_c : nullptr;
+            if (use_tma) {
+                // ---- TMA path: thread = accumulator row; the row's 32 values of a chunk go to the swizzled box as eight
+                // 16-byte pieces (piece j of row r sits at r*128 + ((j ^ (r & 7)) << 4): conflict-free for a quarter warp),
+                // then one lane hands the box to the TMA, which writes full lines and clips at the matrix edges.
+                const int colw = n0 + half * HC;          // first column of this warp
+                if (p.bias && colw < p.n) {               // this warp's bias slice -> smem (coalesced)
+                    const bool al = (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0 && (colw & 3) == 0;
+                    for (int i = lane * 4; i < HC; i += 128) {
+                        const int c = colw + i;
+                        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (c + 4 <= p.n && al) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + c));
+                        else {
+                            if (c < p.n) b4.x = __ldg(p.bias + c);
+                            if (c + 1 < p.n) b4.y = __ldg(p.bias + c + 1);
+                            if (c + 2 < p.n) b4.z = __ldg(p.bias + c + 2);
+                            if (c + 3 < p.n) b4.w = __ldg(p.bias + c + 3);
+                        }
+                        *reinterpret_cast<float4*>(sbias + i) = b4;
+                    }
+                    __syncwarp();
+                }
+#pragma unroll
+                for (int j = 0; j < HC / 32; ++j) {
+                    const int cc = half * HC + j * 32;    // column offset inside the tile
+                    if (n0 + cc >= p.n) break;            // warp-uniform
+                    float v[32];
+                    tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + cc), v);
+                    if (p.bias) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 b4 = *reinterpret_cast<const float4*>(sbias + j * 32 + q * 4);   // same address for all lanes
+                            v[4 * q] = v[4 * q] * p.alpha + b4.x; v[4 * q + 1] = v[4 * q + 1] * p.alpha + b4.y;
+                            v[4 * q + 2] = v[4 * q + 2] * p.alpha + b4.z; v[4 * q + 3] = v[4 * q + 3] * p.alpha + b4.w;
+                        }
+                    } else if (p.alpha != 1.0f) {
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) v[q] *= p.alpha;
+                    }
+                    {
+                        uint8_t* box = wbuf + (nstore % kEpiBoxes) * kEpiBufBytes;
+                        if (lane == 0) tma_store_wait_read<kEpiBoxes - 1>();      // the store that last used this box has read it
+                        __syncwarp();
+                        uint8_t* rowp = box + lane * 128;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) { tma_store_3d(&map_c, box, n0 + cc, row_base, bz); tma_store_commit(); }
+                        ++nstore;
+                    }
+                    if (gbase) {
+                        uint8_t* box = wbuf + (nstore % kEpiBoxes) * kEpiBufBytes;
+                        if (lane == 0) tma_store_wait_read<kEpiBoxes - 1>();
+                        __syncwarp();
+                        uint8_t* rowp = box + lane * 128;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            float4 gv;
+                            if (p.debug & 8) gv = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                            else if (p.debug & 16) gv = make_float4(gelu_tanh_fast(v[4 * q]), gelu_tanh_fast(v[4 * q + 1]), gelu_tanh_fast(v[4 * q + 2]), gelu_tanh_fast(v[4 * q + 3]));
+                            else gv = make_float4(gelu_tanh_f(v[4 * q]), gelu_tanh_f(v[4 * q + 1]), gelu_tanh_f(v[4 * q + 2]), gelu_tanh_f(v[4 * q + 3]));
+                            *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = gv;
+                        }
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) { tma_store_3d(&map_g, box, n0 + cc, row_base, bz); tma_store_commit(); }
+                        ++nstore;
+                    }
+                }
+            } else {
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
+            for (int c0 = half * HC; c0 < (half + 1) * HC; c0 += 32) {
                 if (n0 + c0 >= p.n) break;               // warp-uniform
                 float v[32];
                 if (p.debug & 4) {
@@ -436,6 +548,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 }
                 __syncwarp();                             // buffer is rewritten by the next chunk
             }
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {                              // one arrival per epilogue warp (of both CTAs when paired), at the leader
@@ -444,6 +557,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     }
 
+    if (warp >= 2 && lane == 0) tma_store_wait_all();     // shared memory stays valid until the TMA has drained every box
     tc_fence_before();
     if (CG == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
@@ -525,6 +639,37 @@ static bool make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, 
     return true;
 }
 
+// Output tensor [batch][rows][cols] fp32 (ld elements between rows): box = {32 cols, 32 rows, 1}, 128B swizzle, used by
+// the epilogue's cp.async.bulk.tensor stores (clipped at the edges, so ragged m / n need no predicates).
+static bool make_store_map(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld, uint64_t stride) {
+    static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+    static std::mutex mu;
+    MapKey key{ptr, cols, rows, batch, ld, stride, 32u, 2u};
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) { *out = it->second; return true; }
+    }
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return false;
+    alignas(64) CUtensorMap m;
+    cuuint64_t dims[3] = {cols, rows, batch};
+    if (batch == 1 || stride == 0) stride = rows * ld;
+    cuuint64_t strides[2] = {ld * 4, stride * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (cache.size() > 4096) cache.clear();
+        cache.emplace(key, m);
+    }
+    *out = m;
+    return true;
+}
+
 bool gemm_tc_eligible(const GemmParams& p) {
     if (p.trans_a != 0 || p.trans_b == 0) return false;                 // both operands must be K-major
     if (p.m < 1 || p.n < 1 || p.k < 1) return false;
@@ -588,7 +733,22 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
             !make_operand_map(&mb2, p.b2, p.k2, p.n, 1, p.ldb2, 0, Cfg::b_rows, BF16))
             return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (segment 2)");
     } else { ma2 = ma; mb2 = mb; }
+    // output boxes: C (and the GELU aux) leave through the TMA when the layout allows it and nothing has to be read back
+    CUtensorMap mc, mg;
+    // (the GELU aux output stays on the register/STG path: with one epilogue warp per scheduler the tanh chains of a whole
+    //  32-value row per thread run with no other warp to hide their latency, measured 125 us vs 81 us on fc_in)
+    static const bool tma_gelu = [] { const char* e = getenv("MFT_GEMM_TMA_GELU"); return e && e[0] == '1'; }();
+    const bool c_ok = !FUSED && p.beta == 0.f && aligned16(p.c) && (p.ldc & 3) == 0 && (p.batch == 1 || (p.stride_c & 3) == 0) &&
+                      (!p.gelu_out || (tma_gelu && aligned16(p.gelu_out)));
+    static const bool tma_store_on = [] { const char* e = getenv("MFT_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
+    bool tma_c = c_ok && tma_store_on;
+    if (tma_c) {
+        tma_c = make_store_map(&mc, p.c, p.n, p.m, p.batch, p.ldc, p.stride_c) &&
+                (!p.gelu_out || make_store_map(&mg, p.gelu_out, p.n, p.m, p.batch, p.ldc, p.stride_c));
+    }
+    if (!tma_c) { mc = ma; mg = ma; } else if (!p.gelu_out) mg = mc;
     TcArgs a;
+    a.tma_c = tma_c ? 1 : 0;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;
@@ -632,7 +792,7 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED>, ma, mb, ma2, mb2, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED>, ma, mb, ma2, mb2, mc, mg, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);
     if (e == cudaSuccess) e = cudaGetLastError();

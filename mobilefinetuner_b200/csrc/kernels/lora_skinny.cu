@@ -33,35 +33,42 @@ lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restri
         for (int c = 0; c < RMAX; ++c) acc[i][c] = 0.f;
 
     constexpr int NJ = KC / 32;
-    for (int k0 = 0; k0 < K; k0 += KC) {
+    constexpr int NS = KC * RMAX / 256;
+    // Software pipeline over the K chunks: the global loads of chunk c+1 (this thread's x values and its share of A) are
+    // in flight while chunk c is multiplied out of shared memory, so only the first chunk's latency is exposed.
+    float xv[NJ][RPW], stage[NS];
+    auto load_chunk = [&](int k0, float (&xo)[NJ][RPW], float (&so)[NS]) {
         const int kc = min(KC, K - k0);
-        // this chunk's x values first: their latency overlaps the staging of A below
-        float xv[NJ][RPW];
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
             const int kk = j * 32 + lane;
 #pragma unroll
-            for (int i = 0; i < RPW; ++i) xv[j][i] = (live[i] && kk < kc) ? ld_stream(xr[i] + k0 + kk) : 0.f;
+            for (int i = 0; i < RPW; ++i) xo[j][i] = (live[i] && kk < kc) ? ld_stream(xr[i] + k0 + kk) : 0.f;
         }
-        {   // stage the A chunk: all loads of a thread are issued before the first store (fixed trip count, fully unrolled)
-            constexpr int NS = KC * RMAX / 256;
-            float stage[NS];
 #pragma unroll
-            for (int it = 0; it < NS; ++it) {
-                const int idx = it * 256 + threadIdx.x;
-                int kk, c;
-                if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
-                stage[it] = (kk < kc && c < r) ? (a_is_kr ? __ldg(a + int64_t(k0 + kk) * lda + c) : __ldg(a + int64_t(c) * lda + k0 + kk)) : 0.f;
-            }
-            __syncthreads();     // the previous chunk's readers are done with At
-#pragma unroll
-            for (int it = 0; it < NS; ++it) {
-                const int idx = it * 256 + threadIdx.x;
-                int kk, c;
-                if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
-                At[kk * PITCH + c] = stage[it];
-            }
+        for (int it = 0; it < NS; ++it) {
+            const int idx = it * 256 + threadIdx.x;
+            int kk, c;
+            if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
+            so[it] = (kk < kc && c < r) ? (a_is_kr ? __ldg(a + int64_t(k0 + kk) * lda + c) : __ldg(a + int64_t(c) * lda + k0 + kk)) : 0.f;
         }
+    };
+    load_chunk(0, xv, stage);
+    for (int k0 = 0; k0 < K; k0 += KC) {
+        float xc[NJ][RPW];
+#pragma unroll
+        for (int j = 0; j < NJ; ++j)
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) xc[j][i] = xv[j][i];
+        __syncthreads();     // the previous chunk's readers are done with At
+#pragma unroll
+        for (int it = 0; it < NS; ++it) {
+            const int idx = it * 256 + threadIdx.x;
+            int kk, c;
+            if (a_is_kr) { c = idx % RMAX; kk = idx / RMAX; } else { kk = idx % KC; c = idx / KC; }
+            At[kk * PITCH + c] = stage[it];
+        }
+        if (k0 + KC < K) load_chunk(k0 + KC, xv, stage);     // next chunk's loads fly during the FMAs below
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < NJ; ++j) {
@@ -71,10 +78,10 @@ lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restri
                 const float4 av = arow[c4];
 #pragma unroll
                 for (int i = 0; i < RPW; ++i) {
-                    acc[i][c4 * 4 + 0] = fmaf(xv[j][i], av.x, acc[i][c4 * 4 + 0]);
-                    acc[i][c4 * 4 + 1] = fmaf(xv[j][i], av.y, acc[i][c4 * 4 + 1]);
-                    acc[i][c4 * 4 + 2] = fmaf(xv[j][i], av.z, acc[i][c4 * 4 + 2]);
-                    acc[i][c4 * 4 + 3] = fmaf(xv[j][i], av.w, acc[i][c4 * 4 + 3]);
+                    acc[i][c4 * 4 + 0] = fmaf(xc[j][i], av.x, acc[i][c4 * 4 + 0]);
+                    acc[i][c4 * 4 + 1] = fmaf(xc[j][i], av.y, acc[i][c4 * 4 + 1]);
+                    acc[i][c4 * 4 + 2] = fmaf(xc[j][i], av.z, acc[i][c4 * 4 + 2]);
+                    acc[i][c4 * 4 + 3] = fmaf(xc[j][i], av.w, acc[i][c4 * 4 + 3]);
                 }
             }
         }
