@@ -15,21 +15,6 @@ constexpr int kAttBQ = 64;   // query rows per CTA
 constexpr int kAttBK = 64;   // keys per tile
 constexpr int kAttPad = 4;   // smem row padding (floats): conflict-free B-fragment reads
 
-__device__ __forceinline__ uint32_t f2tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return r;
-}
-__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-    hi = f2tf32(x);
-    lo = f2tf32(x - __uint_as_float(hi));
-}
-__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
     uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
     int bytes = pred ? 16 : 0;   // src-size 0 => zero fill

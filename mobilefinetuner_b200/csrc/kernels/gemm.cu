@@ -66,6 +66,8 @@ extern "C" int mft_device_check(void) {
     return 0;
 }
 
+namespace mft { bool tensor_cores_enabled() { return g_use_tc; } }
+
 extern "C" int mft_use_tensor_cores(int enable) {
     int prev = g_use_tc ? 1 : 0;
     g_use_tc = enable != 0;

@@ -21,6 +21,7 @@ struct GemmParams {
     float* partial = nullptr;  // [batch][ksplit][m][n] scratch when ksplit > 1
 };
 
+bool tensor_cores_enabled();   // mft_use_tensor_cores state (gemm.cu)
 int launch_gemm_simt(const GemmParams& p, cudaStream_t st);
 bool gemm_tc_eligible(const GemmParams& p);
 int launch_gemm_tc(const GemmParams& p, cudaStream_t st);

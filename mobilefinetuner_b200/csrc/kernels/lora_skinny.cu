@@ -5,7 +5,9 @@
 //   lora_tn   : out     = alpha * S[T,r]^T * W[T,q]      (dB = (xA)^T dY and dA = x^T d(xA): contraction over all tokens)
 // Reference: the matmul/MatmulBackward calls LoRALinear::forward generates for slice.A / slice.B
 // (nn/lora_linear.cpp:66-72, core/backward_functions.cpp:94-138). Algorithmic bytes: 4*T*K (+4*T*r) and 4*T*q (+4*T*r).
+#include <cstdlib>
 #include "common.cuh"
+#include "gemm_internal.cuh"
 
 namespace mft {
 
@@ -93,6 +95,127 @@ lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restri
             const float v = warp_sum(acc[i][c]);
             if (lane == (c & 31) && c < r && live[i]) y[(row0 + i) * ldy + c] = v * alpha;
         }
+    }
+}
+
+// lora_down on the legacy tensor pipe (mma.sync m16n8k8 TF32), the default for r <= 16 and 16-byte aligned x.
+// A CTA owns 16 token rows; its four warps split every 1024-wide K span into quarters. Everything a span needs is
+// requested before anything is used: the span's slice of A goes to shared memory with cp.async ([k][18] floats:
+// conflict-free B-fragment reads), and each lane issues all 32 of its 128-bit x loads (64 KB per CTA in flight), so one
+// memory latency is exposed per span instead of one per tile. A-fragments are built from those registers: lane (g, t)
+// holds x[row g / g+8][k0 + 4t .. 4t+3] per 16-wide k group, with the contraction slots relabelled (slot t <-> k0+4t+{0,2},
+// slot t+4 <-> k0+4t+{1,3} for the two k8 steps). PRECISE = 3xTF32 split (exact mode), else TF32 operands like the
+// large GEMMs. The FMA kernel above stays as the general path (any alignment, r up to 64).
+constexpr int kDmSpan = 1024;         // k per span (4 warps x 256)
+constexpr int kDmPitch = 18;
+constexpr int kDmSmemBytes = kDmSpan * kDmPitch * 4;
+
+__device__ __forceinline__ void cp_async_zfill(void* smem, const void* gmem, int bytes, int src_bytes) {
+    const uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
+    if (bytes == 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" :: "r"(s), "l"(gmem), "r"(src_bytes) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" :: "r"(s), "l"(gmem), "r"(src_bytes) : "memory");
+}
+
+template <bool PRECISE>
+__global__ void __launch_bounds__(128)
+lora_down_mma_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
+                     float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha) {
+    extern __shared__ __align__(16) float As[];                       // [kDmSpan][18]; reused for the cross-warp reduction
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int64_t row0 = int64_t(blockIdx.x) * 16;
+    const bool live0 = row0 + g < T, live1 = row0 + g + 8 < T;
+    const float* x0 = x + (live0 ? row0 + g : 0) * ldx + warp * 256 + t * 4;
+    const float* x1 = x + (live1 ? row0 + g + 8 : 0) * ldx + warp * 256 + t * 4;
+    float acc[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+    const bool pair_ok = a_is_kr && (lda & 1) == 0 && (reinterpret_cast<uintptr_t>(a) & 7u) == 0;
+
+    for (int k0 = 0; k0 < K; k0 += kDmSpan) {
+        if (k0) __syncthreads();                                      // the previous span's readers are done with As
+        // ---- A slice -> shared memory (asynchronous; zero-filled outside K x r)
+        if (pair_ok) {
+            for (int idx = threadIdx.x; idx < kDmSpan * 8; idx += 128) {        // 8-byte pieces: (k, column pair)
+                const int kk = idx >> 3, c = (idx & 7) * 2;
+                const bool in = k0 + kk < K;
+                const int nb = !in ? 0 : (c + 1 < r ? 8 : (c < r ? 4 : 0));
+                cp_async_zfill(As + kk * kDmPitch + c, a + int64_t(in ? k0 + kk : 0) * lda + (c < r ? c : 0), 8, nb);
+            }
+        } else {
+            for (int idx = threadIdx.x; idx < kDmSpan * 16; idx += 128) {
+                int kk, c;
+                if (a_is_kr) { c = idx & 15; kk = idx >> 4; } else { kk = idx % kDmSpan; c = idx / kDmSpan; }
+                const bool in = k0 + kk < K && c < r;
+                const float* src = a_is_kr ? a + int64_t(in ? k0 + kk : 0) * lda + (in ? c : 0) : a + int64_t(in ? c : 0) * lda + (in ? k0 + kk : 0);
+                cp_async_zfill(As + kk * kDmPitch + c, src, 4, in ? 4 : 0);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        // ---- all of this lane's x for the span: 16 groups x 2 row halves
+        float4 xq[2][16];
+#pragma unroll
+        for (int grp = 0; grp < 16; ++grp) {
+            const bool in = k0 + warp * 256 + grp * 16 + t * 4 < K;    // K % 4 == 0: a float4 is inside or outside as a whole
+            xq[0][grp] = (live0 && in) ? ld_stream(reinterpret_cast<const float4*>(x0 + k0 + grp * 16)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            xq[1][grp] = (live1 && in) ? ld_stream(reinterpret_cast<const float4*>(x1 + k0 + grp * 16)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        // The barrier's predicate depends on every loaded value: that keeps all 32 loads in front of it (ptxas would
+        // otherwise sink each read-only load to its first use, one exposed latency per group instead of one per span).
+        uint32_t chk = 0xFFFFFFFFu;
+#pragma unroll
+        for (int grp = 0; grp < 16; ++grp)
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+                chk &= __float_as_uint(xq[h][grp].x) & __float_as_uint(xq[h][grp].y) & __float_as_uint(xq[h][grp].z) & __float_as_uint(xq[h][grp].w);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        (void)__syncthreads_or(chk == 0xFFFFFFFFu);
+#pragma unroll
+        for (int grp = 0; grp < 16; ++grp) {
+            const float* ab = As + (warp * 256 + grp * 16 + t * 4) * kDmPitch + g;
+#pragma unroll
+            for (int step = 0; step < 2; ++step) {                    // k8 step inside the 16-wide group: k = 4t + {0,1} / {2,3}
+                float b[2][2];
+#pragma unroll
+                for (int n = 0; n < 2; ++n) {
+                    b[n][0] = ab[(step * 2) * kDmPitch + n * 8];
+                    b[n][1] = ab[(step * 2 + 1) * kDmPitch + n * 8];
+                }
+                const float a0 = step ? xq[0][grp].z : xq[0][grp].x, a2 = step ? xq[0][grp].w : xq[0][grp].y;
+                const float a1 = step ? xq[1][grp].z : xq[1][grp].x, a3 = step ? xq[1][grp].w : xq[1][grp].y;
+                if (PRECISE) {
+                    uint32_t ah[4], al[4];
+                    split_tf32(a0, ah[0], al[0]); split_tf32(a1, ah[1], al[1]); split_tf32(a2, ah[2], al[2]); split_tf32(a3, ah[3], al[3]);
+#pragma unroll
+                    for (int n = 0; n < 2; ++n) {
+                        uint32_t bh0, bl0, bh1, bl1;
+                        split_tf32(b[n][0], bh0, bl0); split_tf32(b[n][1], bh1, bl1);
+                        mma_tf32(acc[n], al, bh0, bh1);
+                        mma_tf32(acc[n], ah, bl0, bl1);
+                        mma_tf32(acc[n], ah, bh0, bh1);
+                    }
+                } else {
+                    const uint32_t af[4] = {f2tf32(a0), f2tf32(a1), f2tf32(a2), f2tf32(a3)};
+#pragma unroll
+                    for (int n = 0; n < 2; ++n) mma_tf32(acc[n], af, f2tf32(b[n][0]), f2tf32(b[n][1]));
+                }
+            }
+        }
+    }
+    // the four warps hold partial sums over their K quarters: add them in warp order through shared memory
+    __syncthreads();
+    float* red = As;                                                  // [4 warps][16 rows][16 cols]
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+        float* base = red + warp * 256 + n * 8 + 2 * t;
+        base[g * 16] = acc[n][0]; base[g * 16 + 1] = acc[n][1];
+        base[(g + 8) * 16] = acc[n][2]; base[(g + 8) * 16 + 1] = acc[n][3];
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 256; idx += 128) {
+        const int rr = idx >> 4, c = idx & 15;
+        const int64_t row = row0 + rr;
+        if (row < T && c < r) y[row * ldy + c] = (((red[idx] + red[256 + idx]) + red[512 + idx]) + red[768 + idx]) * alpha;
     }
 }
 
@@ -260,6 +383,21 @@ extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_
     if (ceil_div(T, int64_t(8)) > 0x7fffffff) return set_error(1, "mft_lora_down: too many rows");
     cudaStream_t st = as_stream(stream);
     const int k = int(K);
+    static const bool mma_on = [] { const char* e = getenv("MFT_LORA_DOWN_MMA"); return !(e && e[0] == '0'); }();
+    if (mma_on && r <= 16 && (K & 3) == 0 && (ldx & 3) == 0 && aligned16(x)) {
+        const bool precise = !tensor_cores_enabled();          // exact mode: 3xTF32 split, fp32-accurate
+        static bool attr = false;
+        if (!attr) {
+            cudaFuncSetAttribute(lora_down_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDmSmemBytes);
+            cudaFuncSetAttribute(lora_down_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDmSmemBytes);
+            attr = true;
+        }
+        const unsigned grid = unsigned(ceil_div(T, int64_t(16)));
+        if (precise) lora_down_mma_kernel<true><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha);
+        else lora_down_mma_kernel<false><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha);
+        MFT_CHECK_LAUNCH("mft_lora_down");
+        return 0;
+    }
     if (r <= 16) {
         // rows per warp: as many as still leave >= 2 CTAs per SM
         if (T >= int64_t(32) * 2 * kNumSMs) launch_down<4, 16, 128>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);

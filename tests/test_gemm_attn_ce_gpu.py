@@ -118,13 +118,20 @@ def test_gemm_splitk_matches_reference(capi, m, n, k, ta, splits):
 @pytest.mark.parametrize("T,K,r,a_is_kr", [(4096, 1024, 16, 1), (4096, 1024, 16, 0), (100, 768, 8, 1), (33, 64, 4, 0),
                                             (512, 3072, 64, 1), (257, 2048, 32, 0), (10, 24, 4, 1), (37, 101, 5, 1), (2500, 333, 16, 0)])
 def test_lora_down_streaming_kernel(capi, T, K, r, a_is_kr):
+    """Default mode: TF32 operands on the tensor pipe (same class as the large GEMMs); exact mode: 3xTF32 split / fp32 FMA."""
     rng = np.random.default_rng(T + K + r)
     x = rng.standard_normal((T, K)).astype(np.float32)
     A = (rng.standard_normal((K, r) if a_is_kr else (r, K)) * 0.1).astype(np.float32)
-    y = torch.full((T, r), float("nan"), device="cuda")
-    capi.call("mft_lora_down", dev(x), K, dev(A), A.shape[1], a_is_kr, y, r, T, K, r, 2.0, None)
     e = 2.0 * (x.astype(np.float64) @ (A if a_is_kr else A.T).astype(np.float64))
-    assert rel(y, e) < FP32_TOL
+    for exact, tol in ((True, FP32_TOL), (False, TF32_TOL)):
+        prev = capi.lib.mft_use_tensor_cores(0 if exact else 1)
+        try:
+            y = torch.full((T, r), float("nan"), device="cuda")
+            capi.call("mft_lora_down", dev(x), K, dev(A), A.shape[1], a_is_kr, y, r, T, K, r, 2.0, None)
+            torch.cuda.synchronize()
+        finally:
+            capi.lib.mft_use_tensor_cores(prev)
+        assert rel(y, e) < tol, (exact, rel(y, e))
 
 
 @pytest.mark.parametrize("T,q,r,rq", [(4096, 1024, 16, 1), (4096, 1024, 16, 0), (100, 768, 8, 1), (65, 50, 4, 0),
