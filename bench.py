@@ -261,9 +261,17 @@ def main():
     e2e_val = tokens_step * a.steps / (ms_e2e / 1e3)
     achieved_tf = (fl.value / 1e12) / (ms.value / 1e3) if ms.value > 0 else 0.0
     kind = "kind::f16 bf16 operands" if a.precision == "bf16" else "kind::tf32"
+    traffic = None                               # DRAM bytes per GEMM launch from the committed ncu capture of this config
+    tpath = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
+    if a.config == "c4" and a.precision == "tf32" and os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath))["dram_bytes_per_launch"]
+        except Exception:
+            traffic = None
     roofline = {"bound": "tensor", "kernel": f"gemm_tc_kernel (tcgen05.mma cta_group::2 {kind}, TMA-fed, fp32 accumulate in TMEM)",
                 "achieved": round(achieved_tf, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
-                "frac": round(achieved_tf / peaks["tf_sustained"], 4), "traffic": None,
+                "frac": round(achieved_tf / peaks["tf_sustained"], 4), "traffic": traffic,
+                "algorithmic_flop_per_launch": round(fl.value / max(nl.value, 1)),
                 "launches_per_step": nl.value // max(a.profile_steps, 1), "gemm_ms_per_step": round(ms.value / max(a.profile_steps, 1), 3),
                 "step_ms_while_profiled": round(t_prof / max(a.profile_steps, 1), 3),
                 "peak_source": peaks["source"] + ", dense bf16 sustained" + ("" if a.precision == "bf16" else "; the kernel computes in TF32 whose hardware peak is half of bf16")}
