@@ -1,0 +1,107 @@
+"""The reference's own trainer CLIs, end to end.
+
+`mobilefinetuner_b200/bin/<cli>` is the reference's main.cpp compiled from its source and linked against libmft_host (the C++
+mirror over the CUDA kernels); `oracle/_ref/ref_<cli>` is the same source linked against the reference's own CPU library.
+Both read the same synthetic model directory (random-init safetensors, BPE vocabulary, WikiText-style corpus written by
+tools/make_fixtures.py), so tokenisation, batching, LoRA injection, the step itself, the LR schedule and the adapter
+file must all agree. Neither binary nor /root/reference is needed at test time beyond these prebuilt files."""
+import json
+import os
+import re
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "mobilefinetuner_b200", "bin")
+REF = os.path.join(ROOT, "oracle", "_ref")
+pytestmark = pytest.mark.gpu
+
+LINE = re.compile(r"\(global (\d+)/\d+\) \| lr (\S+) \| loss (\S+) \| ppl \S+ \| grad_norm (\S+)")
+
+
+def fixture(tmp_path, **kw):
+    out = str(tmp_path / "fx")
+    args = [sys.executable, os.path.join(ROOT, "tools", "make_fixtures.py"), "--out", out, "--family", "gpt2"]
+    for k, v in kw.items():
+        args += [f"--{k}", str(v)]
+    subprocess.check_call(args, stdout=subprocess.DEVNULL)
+    return out
+
+
+def run_cli(exe, args, env=None, timeout=900):
+    r = subprocess.run([exe] + args, capture_output=True, text=True, timeout=timeout, env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    rows = [(int(m[1]), float(m[2]), float(m[3]), float(m[4])) for m in LINE.finditer(r.stdout)]
+    return rows, r.stdout
+
+
+def read_safetensors(path):
+    with open(path, "rb") as f:
+        n = struct.unpack("<Q", f.read(8))[0]
+        header = json.loads(f.read(n))
+        data = f.read()
+    meta = header.pop("__metadata__", {})
+    return {k: np.frombuffer(data[v["data_offsets"][0]:v["data_offsets"][1]], np.float32).reshape(v["shape"]) for k, v in header.items()}, meta
+
+
+def need(*paths):
+    for p in paths:
+        if not os.path.exists(p):
+            pytest.skip(f"{os.path.relpath(p, ROOT)} not built (needs /root/reference at build time)")
+
+
+def test_gpt2_lora_finetune_cli_matches_reference_build(tmp_path):
+    mine, ref = os.path.join(BIN, "gpt2_lora_finetune"), os.path.join(REF, "ref_gpt2_lora_finetune")
+    need(mine, ref)
+    fx = fixture(tmp_path, n_layer=2, n_embd=64, n_head=4, n_positions=128)
+    common = ["--data_dir", fx + "/data", "--pretrained_dir", fx + "/model", "--steps", "12", "--batch_size", "2", "--seq_len", "32", "--lr", "1e-3",
+              "--seed", "7", "--warmup_steps", "2"]
+    rows_ref, _ = run_cli(ref, common + ["--lora_out", fx + "/ref.safetensors"])
+    env = dict(os.environ, MFT_USE_TENSOR_CORES="0")          # exact fp32 mode: only summation order differs
+    rows, out = run_cli(mine, common + ["--lora_out", fx + "/mine.safetensors"], env=env)
+    assert len(rows) == len(rows_ref) == 12, out[-2000:]
+    for a, b in zip(rows, rows_ref):
+        assert a[0] == b[0] and a[1] == b[1]                                   # same step numbering and LR schedule
+        assert abs(a[2] - b[2]) <= 2e-4 * abs(b[2]), (a, b)                    # loss (printed with 4 decimals)
+        assert abs(a[3] - b[3]) <= 2e-3 * max(b[3], 1e-3) + 1e-3, (a, b)       # grad norm (3 decimals)
+    ta, ma = read_safetensors(fx + "/mine.safetensors")
+    tb, mb = read_safetensors(fx + "/ref.safetensors")
+    assert sorted(ta) == sorted(tb) and ma == mb
+    for k in tb:
+        assert ta[k].shape == tb[k].shape
+        assert np.abs(ta[k] - tb[k]).max() <= 1e-4 * max(np.abs(tb[k]).max(), 1e-6) + 1e-7, k
+    # default (TF32 tensor-core) mode stays within the 1e-3 loss tolerance
+    rows_tc, _ = run_cli(mine, common + ["--lora_out", fx + "/mine_tc.safetensors"])
+    for a, b in zip(rows_tc, rows_ref):
+        assert abs(a[2] - b[2]) <= 1e-3 * abs(b[2]), (a, b)
+
+
+def test_gpt2_lora_cli_resume_from_saved_adapter(tmp_path):
+    mine = os.path.join(BIN, "gpt2_lora_finetune")
+    need(mine)
+    fx = fixture(tmp_path, n_layer=2, n_embd=64, n_head=4, n_positions=128)
+    common = ["--data_dir", fx + "/data", "--pretrained_dir", fx + "/model", "--batch_size", "2", "--seq_len", "32", "--lr", "1e-3", "--seed", "7"]
+    run_cli(mine, common + ["--steps", "4", "--lora_out", fx + "/a.safetensors"])
+    rows, out = run_cli(mine, common + ["--steps", "2", "--resume_from", fx + "/a.safetensors", "--lora_out", fx + "/b.safetensors"])
+    assert len(rows) == 2 and "Loaded" in out
+    ta, _ = read_safetensors(fx + "/a.safetensors")
+    tb, _ = read_safetensors(fx + "/b.safetensors")
+    assert sorted(ta) == sorted(tb)
+    assert any(np.abs(ta[k] - tb[k]).max() > 0 for k in ta)            # training continued from the loaded factors
+
+
+def test_gpt2_full_finetune_cli_matches_reference_build(tmp_path):
+    mine, ref = os.path.join(BIN, "gpt2_full_finetune"), os.path.join(REF, "ref_gpt2_full_finetune")
+    need(mine, ref)
+    fx = fixture(tmp_path, n_layer=2, n_embd=64, n_head=4, n_positions=128)
+    common = ["--data_dir", fx + "/data", "--pretrained_dir", fx + "/model", "--steps", "8", "--batch_size", "2", "--seq_len", "32", "--lr", "1e-4", "--seed", "7"]
+    extra = lambda name: ["--output_path", fx + "/" + name]
+    rows_ref, _ = run_cli(ref, common + extra("ref_full.safetensors"))
+    rows, out = run_cli(mine, common + extra("mine_full.safetensors"), env=dict(os.environ, MFT_USE_TENSOR_CORES="0"))
+    assert len(rows) == len(rows_ref) and rows, out[-2000:]
+    for a, b in zip(rows, rows_ref):
+        assert abs(a[2] - b[2]) <= 2e-4 * abs(b[2]), (a, b)
