@@ -1,3 +1,7 @@
+#include "safetensors_loader.h"
+#include <sstream>
+#include <map>
+#include <cstring>
 #include "gemma_lora_injector.h"
 
 #include <cmath>
@@ -88,7 +92,69 @@ void GemmaLoraInjector::print_info() const {
 }
 void GemmaLoraInjector::merge_all(GemmaModel& model) { model.merge_lora(); }
 void GemmaLoraInjector::unmerge_all(GemmaModel& model) { model.unmerge_lora(); }
-void GemmaLoraInjector::save_lora_safetensors(const std::string&) const { throw std::runtime_error("GemmaLoraInjector::save_lora_safetensors: checkpoint I/O is not part of this build"); }
-void GemmaLoraInjector::load_lora_safetensors(const std::string&) { throw std::runtime_error("GemmaLoraInjector::load_lora_safetensors: checkpoint I/O is not part of this build"); }
+// graph/gemma_lora_injector.cpp:129-212: attention adapters only (q, k, v, o), keys layer.{i}.attn.{q|k|v|proj}[.{slice}].lora_{A|B},
+// tensors in the layout they are held in (PEFT [r,in] / [out,r]); MLP adapters are not written by the reference either.
+void GemmaLoraInjector::save_lora_safetensors(const std::string& path) const {
+    if (!model_) { std::cerr << "[GemmaLoraInjector] save_lora_safetensors: model not set" << std::endl; return; }
+    std::map<std::string, TensorPtr> state;
+    auto add = [&](int layer, const char* target, const LoRALinear* lin) {
+        if (!lin) return;
+        const auto& sl = lin->slices();
+        for (size_t k = 0; k < sl.size(); ++k) {
+            if (!sl[k].A || !sl[k].B) continue;
+            std::string base = "layer." + std::to_string(layer) + "." + target;
+            if (sl.size() > 1) base += "." + std::to_string(k);
+            state[base + ".lora_A"] = sl[k].A;
+            state[base + ".lora_B"] = sl[k].B;
+        }
+    };
+    for (int i = 0; i < model_->config().num_hidden_layers; ++i) {
+        const GemmaBlockWeights& b = model_->get_block(i);
+        add(i, "attn.q", b.q_proj_lora.get());
+        add(i, "attn.k", b.k_proj_lora.get());
+        add(i, "attn.v", b.v_proj_lora.get());
+        add(i, "attn.proj", b.o_proj_lora.get());
+    }
+    std::ostringstream alpha, dropout;
+    alpha << spec_.alpha;
+    dropout << spec_.dropout;
+    write_safetensors(path, state, {{"rank", std::to_string(spec_.rank)}, {"alpha", alpha.str()}, {"dropout", dropout.str()},
+                                    {"targets", "attn.q,attn.k,attn.v,attn.proj"}});
+    std::cout << "[GemmaLoraInjector] Saved " << state.size() << " LoRA tensors to " << path << std::endl;
+}
+
+// Extension (the reference prints "not implemented yet", graph/gemma_lora_injector.cpp:214-216): restores the factors written
+// by save_lora_safetensors into the adapters already injected on the model, so a run can resume.
+void GemmaLoraInjector::load_lora_safetensors(const std::string& path) {
+    if (!model_) throw std::runtime_error("GemmaLoraInjector::load_lora_safetensors: inject() first");
+    SafeTensorsReader reader(path);
+    reader.parse_header();
+    int restored = 0;
+    auto take = [&](int layer, const char* target, LoRALinear* lin) {
+        if (!lin) return;
+        const auto& sl = lin->slices();
+        for (size_t k = 0; k < sl.size(); ++k) {
+            std::string base = "layer." + std::to_string(layer) + "." + target;
+            if (sl.size() > 1) base += "." + std::to_string(k);
+            for (const char* ab : {"A", "B"}) {
+                const std::string key = base + ".lora_" + ab;
+                TensorPtr dst = ab[0] == 'A' ? sl[k].A : sl[k].B;
+                TensorPtr src;
+                try { src = reader.load_tensor(key, false); } catch (const std::exception&) { continue; }
+                if (src->shape() != dst->shape()) throw std::runtime_error("GemmaLoraInjector::load_lora_safetensors: shape mismatch for " + key);
+                std::memcpy(dst->data<float>(), static_cast<const Tensor&>(*src).data<float>(), size_t(dst->numel()) * sizeof(float));
+                ++restored;
+            }
+        }
+    };
+    for (int i = 0; i < model_->config().num_hidden_layers; ++i) {
+        GemmaBlockWeights& b = model_->get_block(i);
+        take(i, "attn.q", b.q_proj_lora.get());
+        take(i, "attn.k", b.k_proj_lora.get());
+        take(i, "attn.v", b.v_proj_lora.get());
+        take(i, "attn.proj", b.o_proj_lora.get());
+    }
+    std::cout << "[GemmaLoraInjector] Restored " << restored << " LoRA tensors from " << path << std::endl;
+}
 
 }  // namespace ops

@@ -84,6 +84,12 @@ void Optimizer::clip_grad_norm(const std::vector<TensorPtr>& parameters, float m
     if (n > max_norm) scale_gradients(parameters, max_norm / n);
 }
 
+float Optimizer::clip_grad_norm_eps(const std::vector<TensorPtr>& parameters, float max_norm, float eps) {
+    const float n = compute_grad_norm(parameters);
+    if (n > max_norm) scale_gradients(parameters, max_norm / (n + eps));
+    return n;
+}
+
 // ---------------------------------------------------------------------------- Adam
 Adam::Adam(const AdamConfig& config) : Optimizer(config), adam_config_(config) {}
 Adam::~Adam() {

@@ -36,6 +36,9 @@ public:
     }
     // Global L2 clip over the non-null gradients, entirely on the device (optim/optimizer.cpp:6-38; scale = max/norm).
     virtual void clip_grad_norm(const std::vector<TensorPtr>& parameters, float max_norm);
+    // B200 extension: the trainers' own clip rule, scale = max/(norm + eps) when norm > max (gpt2_lora_finetune/main.cpp:491-516,
+    // optim/gemma_trainer.cpp:84-102), on the device. Returns the norm.
+    float clip_grad_norm_eps(const std::vector<TensorPtr>& parameters, float max_norm, float eps);
     virtual void save_state(const std::string& path) const = 0;
     virtual void load_state(const std::string& path) = 0;
     virtual float get_learning_rate() const { return config_.learning_rate; }

@@ -105,3 +105,39 @@ def test_gpt2_full_finetune_cli_matches_reference_build(tmp_path):
     assert len(rows) == len(rows_ref) and rows, out[-2000:]
     for a, b in zip(rows, rows_ref):
         assert abs(a[2] - b[2]) <= 2e-4 * abs(b[2]), (a, b)
+
+
+def test_train_lora_gemma_cli_matches_reference_build(tmp_path):
+    """train_lora_gemma.cpp (unchanged, relative includes resolved through a symlink tree) + this library's GemmaLoRATrainer,
+    pretokenised data: loss per step, LR schedule and the saved attention adapters against the reference build."""
+    mine, ref = os.path.join(BIN, "train_lora_gemma"), os.path.join(REF, "ref_train_lora_gemma")
+    need(mine, ref)
+    out = str(tmp_path / "fxg")
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "tools", "make_fixtures.py"), "--out", out, "--family", "gemma", "--n_layer", "4",
+                           "--n_embd", "64", "--n_head", "4", "--head_dim", "32", "--intermediate", "128", "--n_positions", "256"], stdout=subprocess.DEVNULL)
+    step = re.compile(r"\[Step (\d+)\] Loss=(\S+) PPL=\S+ LR=(\S+)")
+
+    def run(exe, outdir, env=None):
+        os.makedirs(outdir, exist_ok=True)
+        r = subprocess.run([exe, "--model_dir", out + "/model", "--pretokenized_path", out + "/data/tokens.bin", "--pretokenized_meta",
+                            out + "/data/meta.json", "--output_dir", outdir, "--seq_len", "32", "--batch", "2", "--epochs", "1", "--max_steps", "10",
+                            "--lr", "1e-3", "--targets", "full"], capture_output=True, text=True, timeout=900, env=env)
+        assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+        return [(int(m[1]), float(m[2]), float(m[3])) for m in step.finditer(r.stdout)], r.stdout
+
+    rows_ref, _ = run(ref, out + "/ref_out")
+    rows, log = run(mine, out + "/mine_out", env=dict(os.environ, MFT_USE_TENSOR_CORES="0"))
+    assert len(rows) == len(rows_ref) == 10, log[-2000:]
+    for a, b in zip(rows, rows_ref):
+        assert a[0] == b[0] and abs(a[2] - b[2]) <= 1e-6 * abs(b[2]) + 1e-12
+        assert abs(a[1] - b[1]) <= 2e-4 * abs(b[1]), (a, b)
+    ta, ma = read_safetensors(out + "/mine_out/gemma_lora.safetensors")
+    tb, mb = read_safetensors(out + "/ref_out/gemma_lora.safetensors")
+    assert sorted(ta) == sorted(tb) and ma == mb and len(tb) == 4 * 4 * 2       # q, k, v, o of 4 layers, A and B
+    for k in tb:
+        # Adam divides by sqrt(v): entries whose gradients are ~1e-8 amplify summation-order noise, so the bound is relative to the
+        # tensor's scale (B starts at zero and is ~2e-3 after ten warm-up steps)
+        assert np.abs(ta[k] - tb[k]).max() <= 2e-3 * max(np.abs(tb[k]).max(), 1e-6) + 1e-7, k
+    rows_tc, _ = run(mine, out + "/mine_tc")
+    for a, b in zip(rows_tc, rows_ref):
+        assert abs(a[1] - b[1]) <= 1e-3 * abs(b[1]), (a, b)
