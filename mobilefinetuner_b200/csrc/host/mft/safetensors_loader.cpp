@@ -194,13 +194,10 @@ TensorPtr SafeTensorsReader::read_tensor_data(const SafeTensorInfo& info, bool t
     std::vector<int64_t> shape = info.shape;
     const bool tr = transpose && shape.size() == 2;
     if (tr) std::swap(shape[0], shape[1]);
-    if (info.dtype == "I32") {
-        auto t = std::make_shared<Tensor>(shape, kInt32, kCPU);
-        std::memcpy(t->data<int32_t>(), raw.data(), bytes);
-        return t;
-    }
-    auto t = std::make_shared<Tensor>(shape, kFloat32, kCPU);
-    float* dst = t->data<float>();
+    // tensors are built from host buffers (copy-from-host constructor): no device memory is touched until a kernel needs them
+    if (info.dtype == "I32") return std::make_shared<Tensor>(shape, static_cast<const void*>(raw.data()), kInt32, kCPU);
+    std::vector<float> buf(static_cast<size_t>(n));
+    float* dst = buf.data();
     auto at = [&](int64_t i) -> float {
         if (info.dtype == "F32") { float f; std::memcpy(&f, raw.data() + i * 4, 4); return f; }
         if (info.dtype == "F16") { uint16_t h; std::memcpy(&h, raw.data() + i * 2, 2); return half_to_float(h); }
@@ -217,7 +214,7 @@ TensorPtr SafeTensorsReader::read_tensor_data(const SafeTensorInfo& info, bool t
         for (int64_t r = 0; r < R; ++r)
             for (int64_t c = 0; c < Ccols; ++c) dst[c * R + r] = at(r * Ccols + c);
     }
-    return t;
+    return std::make_shared<Tensor>(shape, static_cast<const void*>(buf.data()), kFloat32, kCPU);
 }
 
 std::unordered_map<std::string, TensorPtr> SafeTensorsReader::load_tensors_mapped(

@@ -32,7 +32,7 @@ int64_t Tensor::rows() const { return shape_.empty() ? 1 : (shape_.back() == 0 ?
 size_t Tensor::dense_bytes() const { return static_cast<size_t>(numel()) * DTypeUtils::size_of(dtype_); }
 uint64_t Tensor::version() const { return st_ ? st_->version : 0; }
 
-void Tensor::allocate(bool zero) {
+void Tensor::allocate(bool zero, bool defer_device) {
     for (auto d : shape_)
         if (d < 0) throw TensorError("Tensor: negative dimension");
     if (ld_ == 0) ld_ = shape_.empty() ? 1 : shape_.back();
@@ -40,9 +40,21 @@ void Tensor::allocate(bool zero) {
     const size_t es = DTypeUtils::size_of(dtype_);
     st_->dev_bytes = static_cast<size_t>(rows()) * static_cast<size_t>(ld_) * es;
     st_->in_arena = mft_rt::arena_active();
+    if (defer_device) return;          // tensors that start life as host data (from_blob, copy-from-host, file loaders)
     st_->dev = mft_rt::dev_alloc(st_->dev_bytes);
     st_->dev_valid = true;
     if (zero) mft_rt::memset0(st_->dev, st_->dev_bytes);
+}
+
+// Host-initialised tensors get their HBM buffer when a kernel first needs them, so the host-side components (tokenizer,
+// dataset, safetensors reader) work on a machine without a GPU and a batch that is only inspected never costs an upload.
+// The buffer goes where the tensor was created: outside the step arena if it was created outside of it.
+void Tensor::ensure_dev() const {
+    if (st_->dev) return;
+    if (!st_->in_arena && mft_rt::arena_active()) {
+        mft_rt::PersistentScope keep;
+        st_->dev = mft_rt::dev_alloc(st_->dev_bytes);
+    } else st_->dev = mft_rt::dev_alloc(st_->dev_bytes);
 }
 
 // core/tensor.cpp:191-225 — the reference zero-fills every new tensor; the public constructor keeps that.
@@ -54,7 +66,8 @@ Tensor::Tensor(const std::vector<int64_t>& shape, DType dtype, Device device)
 // copy-from-host constructor: host mirror holds the data, uploaded before first device use
 Tensor::Tensor(const std::vector<int64_t>& shape, const void* data, DType dtype, Device device)
     : shape_(shape), dtype_(dtype), device_(device) {
-    allocate(false);
+    const bool from_host = data && prod(shape) > 0;
+    allocate(false, from_host);
     if (data && dense_bytes() > 0) {
         st_->host = std::malloc(dense_bytes());
         std::memcpy(st_->host, data, dense_bytes());
@@ -67,7 +80,7 @@ Tensor::Tensor(const std::vector<int64_t>& shape, const void* data, DType dtype,
 Tensor::Tensor(const std::vector<int64_t>& shape, void* external, DType dtype, Device device, bool wrap)
     : shape_(shape), dtype_(dtype), device_(device) {
     if (!wrap) throw TensorError("Tensor: wrap_external_flag must be true for the wrapping constructor");
-    allocate(false);
+    allocate(false, true);
     st_->host = external;
     st_->host_external = true;
     st_->host_valid = true;
@@ -131,6 +144,7 @@ void* Tensor::host_rw() {
 }
 const void* Tensor::dev() const {
     if (!st_) throw TensorError("Tensor: no storage");
+    ensure_dev();
     if (!st_->dev_valid) {
         const size_t es = DTypeUtils::size_of(dtype_);
         if (numel() > 0) {
@@ -149,6 +163,7 @@ void* Tensor::dev_mut() {
 }
 void* Tensor::dev_out() {
     if (!st_) throw TensorError("Tensor: no storage");
+    ensure_dev();
     st_->dev_valid = true;
     st_->host_valid = false;
     ++st_->version;

@@ -156,7 +156,8 @@ private:
     mutable uint64_t bf16_version_ = ~0ull, bf16_t_version_ = ~0ull;
     mutable int64_t bf16_ld_ = 0, bf16_t_ld_ = 0;
 
-    void allocate(bool zero);
+    void allocate(bool zero, bool defer_device = false);
+    void ensure_dev() const;   // device memory of a host-initialised tensor is allocated at its first device use
     void* host_rw();
     const void* host_ro() const;
     void ensure_host() const;
