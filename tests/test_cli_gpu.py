@@ -141,3 +141,34 @@ def test_train_lora_gemma_cli_matches_reference_build(tmp_path):
     rows_tc, _ = run(mine, out + "/mine_tc")
     for a, b in zip(rows_tc, rows_ref):
         assert abs(a[1] - b[1]) <= 1e-3 * abs(b[1]), (a, b)
+
+
+def test_eval_ppl_cli_matches_reference_build(tmp_path):
+    """Evaluation forward path: eval_ppl.cpp unchanged, on a trained adapter — plain, attached and merged
+    into the base weights (LoRALinear::merge_to_base) — against the reference build on the same files."""
+    mine, ref, trainer = os.path.join(BIN, "eval_ppl"), os.path.join(REF, "ref_eval_ppl"), os.path.join(BIN, "gpt2_lora_finetune")
+    need(mine, ref, trainer)
+    fx = fixture(tmp_path, n_layer=2, n_embd=64, n_head=4, n_positions=128)
+    run_cli(trainer, ["--data_dir", fx + "/data", "--pretrained_dir", fx + "/model", "--steps", "30", "--batch_size", "4", "--seq_len", "32", "--lr", "5e-3",
+                      "--seed", "3", "--lora_out", fx + "/lora.safetensors"])
+    res = re.compile(r"split=(\S+)\s+tokens=(\d+)\s+nll=(\S+)\s+ppl=(\S+)")
+
+    def ppl(exe, extra, env=None):
+        r = subprocess.run([exe, "--data_root", fx + "/data", "--pretrained_dir", fx + "/model", "--split", "valid", "--seq_len", "32", "--batch_size", "4"] + extra,
+                           capture_output=True, text=True, timeout=900, env=env)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        m = res.search(r.stdout)
+        assert m, r.stdout[-1500:]
+        return int(m[2]), float(m[3])
+
+    exact = dict(os.environ, MFT_USE_TENSOR_CORES="0")
+    nlls = []
+    for extra in ([], ["--lora_path", fx + "/lora.safetensors"], ["--lora_path", fx + "/lora.safetensors", "--lora_merge", "1"]):
+        tok_ref, nll_ref = ppl(ref, extra)
+        tok, nll = ppl(mine, extra, env=exact)
+        assert tok == tok_ref and abs(nll - nll_ref) <= 2e-4 * nll_ref, (extra, nll, nll_ref)
+        _, nll_tc = ppl(mine, extra)
+        assert abs(nll_tc - nll_ref) <= 1e-3 * nll_ref
+        nlls.append(nll)
+    assert nlls[1] < nlls[0]                       # the adapter was trained on this distribution
+    assert abs(nlls[1] - nlls[2]) <= 2e-4 * nlls[1]    # merged weights evaluate like attached adapters
