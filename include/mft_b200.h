@@ -148,6 +148,16 @@ size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim);
 int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
                       float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
                       size_t workspace_bytes, mft_stream_t stream);
+/* The residual adds on either side of a LayerNorm folded into it (same fp32 values as the separate ops::add / gradient
+ * accumulation, bit for bit):
+ *   mft_add_layernorm_fwd : sum_out = x + add (ops::add, graph/gpt2_model.cpp block forward) and y = LayerNorm(sum_out)
+ *   mft_layernorm_bwd_add : gx = dX + addend, where addend is the gradient that already reached x through the residual
+ *                           branch (Engine::accumulate_grad, core/autograd_engine.cpp:116-140). */
+int mft_add_layernorm_fwd(const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
+                          int64_t rows, int64_t dim, float eps, mft_stream_t stream);
+int mft_layernorm_bwd_add(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,
+                          float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace, size_t workspace_bytes,
+                          mft_stream_t stream);
 /* LayerNorm backward for callers that cannot allocate device memory. It has no counterpart in the reference.
  * Who needs it: a front end over this ABI (cgo, JNI, ctypes) that merely forwards tensors owned by its host
  * application has no device allocator to take workspace from, and a steady-state loop may ban cudaMalloc because

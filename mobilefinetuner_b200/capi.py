@@ -77,6 +77,8 @@ SIGNATURES = {
     "mft_layernorm_fwd": (C.c_int, [vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_norm_bwd_workspace_bytes": (sz, [i64, i64]),
     "mft_layernorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp, sz, vp]),
+    "mft_add_layernorm_fwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp]),
+    "mft_layernorm_bwd_add": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i64, f32, vp, sz, vp]),
     "mft_layernorm_bwd_static": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_rmsnorm_fwd": (C.c_int, [vp, vp, vp, i64, i64, f32, C.c_int, vp]),
     "mft_rmsnorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, C.c_int, vp, sz, vp]),

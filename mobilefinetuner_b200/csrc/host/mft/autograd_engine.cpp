@@ -123,16 +123,36 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
         if (!node || !node->tensor || !node->backward_fn) continue;
         auto it = pending_.find(node->tensor.get());
         if (it == pending_.end()) continue;                 // nothing flowed into this node
-        TensorPtr g = it->second.grad;
-        std::vector<TensorPtr> in_grads = node->backward_fn->apply(g);
+        Pending* cur = &it->second;                         // element addresses survive the insertions below, iterators may not
+        TensorPtr g = cur->grad;
+        std::vector<TensorPtr> in_grads;
+        std::vector<bool> absorbed;
+        if (node->backward_fn->wants_pending()) {
+            // hand the node the gradients already waiting at its inputs: it may add them while producing its own
+            std::vector<TensorPtr> waiting;
+            for (const auto& e : node->next_edges) {
+                if (!e || !e->input_node || !e->input_node->tensor || e->input_idx < 0) continue;
+                if (size_t(e->input_idx) >= waiting.size()) waiting.resize(size_t(e->input_idx) + 1);
+                auto pit = pending_.find(e->input_node->tensor.get());
+                if (pit != pending_.end()) waiting[size_t(e->input_idx)] = pit->second.grad;
+            }
+            absorbed.assign(waiting.size(), false);
+            in_grads = node->backward_fn->apply_fused(g, waiting, absorbed);
+        } else {
+            in_grads = node->backward_fn->apply(g);
+        }
         for (const auto& e : node->next_edges) {
             if (!e || !e->input_node || !e->input_node->tensor) continue;
             const int idx = e->input_idx;
-            if (idx >= 0 && idx < static_cast<int>(in_grads.size()) && in_grads[idx])
-                add_grad(e->input_node->tensor, in_grads[idx]);
+            if (idx >= 0 && idx < static_cast<int>(in_grads.size()) && in_grads[idx]) {
+                if (size_t(idx) < absorbed.size() && absorbed[size_t(idx)])
+                    pending_[e->input_node->tensor.get()] = Pending{in_grads[idx], true};   // already contains what was waiting
+                else
+                    add_grad(e->input_node->tensor, in_grads[idx]);
+            }
         }
         // interior gradients are dead once consumed (unless retained): release them early
-        if (!node->tensor->retains_grad()) it->second.grad.reset();
+        if (!node->tensor->retains_grad()) cur->grad.reset();
     }
 
     // write-back: leaves (nodes without a backward function) and retain_grad tensors; `.grad` is overwritten

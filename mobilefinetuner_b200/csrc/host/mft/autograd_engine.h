@@ -20,6 +20,15 @@ public:
     virtual ~BackwardFunction() = default;
     // Returns one gradient per registered input (nullptr = no gradient for that input).
     virtual std::vector<TensorPtr> apply(const TensorPtr& grad_output) = 0;
+    // B200 extension (optional): `pending[i]` is the gradient that has already been accumulated for input i, or null. A node
+    // may fold it into the gradient it returns for that input — the add then happens where the new gradient is produced
+    // instead of in a separate accumulation kernel — and reports so in `absorbed[i]`; the engine replaces the pending
+    // gradient by the returned one for those inputs. The default ignores `pending`.
+    virtual std::vector<TensorPtr> apply_fused(const TensorPtr& grad_output, const std::vector<TensorPtr>& pending, std::vector<bool>& absorbed) {
+        (void)pending; (void)absorbed;
+        return apply(grad_output);
+    }
+    virtual bool wants_pending() const { return false; }
 };
 using BackwardFunctionPtr = std::shared_ptr<BackwardFunction>;
 

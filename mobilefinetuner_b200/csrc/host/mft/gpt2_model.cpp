@@ -185,7 +185,10 @@ TensorPtr GPT2Model::run_linear_fused(const TensorPtr& x, const std::unique_ptr<
 // graph/gpt2_model.cpp:530-817. Autograd-visible structure preserved: the attention output carries no history
 // (q/k/v are cut from the graph by the reference's zeros+memcpy split, :616-637), residual adds and
 // LayerNorms are tracked ops.
-TensorPtr GPT2Model::forward_block(const TensorPtr& x, int i) {
+// `carry` (optional): the MLP output of the previous block, not yet added to the residual stream `x_in`. The add then happens
+// inside this block's ln_1 kernel (ops::add_layer_norm). On return *carry_out holds this block's own MLP output when the
+// caller asked for it (carry_out != nullptr), and the returned tensor is the stream WITHOUT it.
+TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr& carry, TensorPtr* carry_out) {
     GPT2BlockWeights& w = blocks_[i];
     if (sharder_) {
         const std::string p = "blocks." + std::to_string(i) + ".";
@@ -194,27 +197,42 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x, int i) {
             sharder_->require(p + k);
     }
     const float eps = config_.layernorm_eps;
-    auto x1 = layer_norm(x, w.ln_1_weight, w.ln_1_bias, eps);
+    // MFT_FUSE_ADD_LN=0 keeps residual adds and LayerNorms as separate kernels (default: fused, bit-identical values)
+    static const bool fuse_ln = [] { const char* e = std::getenv("MFT_FUSE_ADD_LN"); return !(e && e[0] == '0'); }();
+    TensorPtr x = x_in, x1;
+    if (carry && fuse_ln) x1 = add_layer_norm(x_in, carry, w.ln_1_weight, w.ln_1_bias, eps, &x);
+    else {
+        if (carry) x = add(x_in, carry);
+        x1 = layer_norm(x, w.ln_1_weight, w.ln_1_bias, eps);
+    }
     auto qkv = run_linear(x1, w.qkv_lin, w.lora_initialized, w.attn_qkv_weight, w.attn_qkv_bias);
     auto ctx = gpt2_causal_attention(qkv, config_.n_head);
     // MFT_FUSE_EPILOGUE bit 0: residual adds ride in the projections' epilogues; bit 1: GeluBackward rides in the epilogue of
     // fc_out's dX product. Off by default: with four epilogue warps per CTA the extra operand traffic and the tanh cost more
     // inside the GEMM than the separate streaming kernels do (profiles/README.md).
     static const int fuse = [] { const char* e = std::getenv("MFT_FUSE_EPILOGUE"); return e ? std::atoi(e) : 0; }();
-    TensorPtr x2;
+    TensorPtr x2, x3;
     if (fuse & 1) {
         LinearFusion attn_out;
         attn_out.residual = x;
         x2 = run_linear_fused(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias, attn_out);
+        x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
+    } else if (fuse_ln) {
+        x3 = add_layer_norm(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias), w.ln_2_weight, w.ln_2_bias, eps, &x2);
     } else {
         x2 = add(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias));
+        x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
     }
-    auto x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
     TensorPtr h, pre;   // fc_in + tanh-GELU: the activation is written by the GEMM epilogue (graph/gpt2_model.cpp:794-802)
     if (w.lora_initialized && w.fc_in_lin) h = w.fc_in_lin->forward_gelu(x3, &pre);
     else pre = fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, &h);
     // x2 + fc_out(gelu(pre)): residual in the forward epilogue, GeluBackward in the epilogue of the backward dX product
-    if (!fuse) return add(x2, run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias));
+    if (!fuse) {
+        auto m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);
+        if (carry_out) { *carry_out = m; return x2; }      // the next LayerNorm adds it
+        return add(x2, m);
+    }
+    if (carry_out) *carry_out = nullptr;
     LinearFusion mlp_out;
     if (fuse & 1) mlp_out.residual = x2;
     if (fuse & 2) mlp_out.gelu_input_pre = pre;
@@ -230,8 +248,18 @@ TensorPtr GPT2Model::forward(const TensorPtr& input_ids, const TensorPtr& attent
     if (S > config_.n_positions) throw std::runtime_error("seq_len exceeds n_positions");
     if (sharder_) { sharder_->require("wte.weight"); sharder_->require("wpe.weight"); }
     TensorPtr x = embedding_lookup(input_ids, wte_weight_, wpe_weight_);     // not differentiable (:346-381)
-    for (int i = 0; i < config_.n_layer; ++i) x = forward_block(x, i);
-    x = layer_norm(x, ln_f_weight_, ln_f_bias_, config_.layernorm_eps);
+    TensorPtr carry;     // MLP output of the previous block, added inside the next LayerNorm kernel
+    for (int i = 0; i < config_.n_layer; ++i) {
+        TensorPtr next;
+        x = forward_block(x, i, carry, &next);
+        carry = next;
+    }
+    if (carry) {
+        static const bool fuse_ln = [] { const char* e = std::getenv("MFT_FUSE_ADD_LN"); return !(e && e[0] == '0'); }();
+        TensorPtr sum;
+        if (fuse_ln) x = add_layer_norm(x, carry, ln_f_weight_, ln_f_bias_, config_.layernorm_eps, &sum);
+        else x = layer_norm(add(x, carry), ln_f_weight_, ln_f_bias_, config_.layernorm_eps);
+    } else x = layer_norm(x, ln_f_weight_, ln_f_bias_, config_.layernorm_eps);
     return lm_head_tied(x, wte_weight_);                                     // wte only gets a gradient through here
 }
 

@@ -86,7 +86,7 @@ private:
                          const TensorPtr& W, const TensorPtr& b) const;
     TensorPtr run_linear_fused(const TensorPtr& x, const std::unique_ptr<LoRALinear>& lin, bool lora_ready,
                                const TensorPtr& W, const TensorPtr& b, const LinearFusion& fusion) const;
-    TensorPtr forward_block(const TensorPtr& x, int block_idx);
+    TensorPtr forward_block(const TensorPtr& x, int block_idx, const TensorPtr& carry = nullptr, TensorPtr* carry_out = nullptr);
 };
 
 }  // namespace ops

@@ -122,6 +122,8 @@ TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const Tensor
 //                    its autograd input and its dX product returns d pre = (gy W^T + ...) * gelu'(pre) directly
 //                    (GeluBackward, core/backward_functions.cpp:155-177, applied in the epilogue), so the activation's
 //                    gradient is never written to HBM. Only valid when this op is the activation's single consumer.
+// sum = x + a; returns layer_norm(sum) and hands `sum` back (one kernel; same autograd nodes as add + layer_norm).
+TensorPtr add_layer_norm(const TensorPtr& x, const TensorPtr& a, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out);
 struct LinearFusion {
     TensorPtr* gelu_act = nullptr;
     TensorPtr residual;

@@ -93,7 +93,7 @@ namespace {
 class LayerNormBackward : public BackwardFunction {  // core/backward_functions.cpp:425-481
 public:
     LayerNormBackward(TensorPtr x, TensorPtr w, TensorPtr b, float eps) : x_(std::move(x)), w_(std::move(w)), b_(std::move(b)), eps_(eps) {}
-    std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
+    std::vector<TensorPtr> run(const TensorPtr& gy_in, const TensorPtr& waiting) {
         TensorPtr gy = contiguous(gy_in);
         const int64_t dim = x_->shape().back(), rows = x_->numel() / dim;
         auto gx = new_like(x_);
@@ -103,10 +103,24 @@ public:
         TensorPtr gw, gb;
         if (wg) { gw = Tensor::make(w_->shape(), kFloat32); gb = Tensor::make(w_->shape(), kFloat32); }
         size_t wsb = wg ? mft_norm_bwd_workspace_bytes(rows, dim) : 0;
-        mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr,
-                                        wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()),
-                      "mft_layernorm_bwd");
+        if (waiting)
+            mft_rt::check(mft_layernorm_bwd_add(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), waiting->dev_f32(), gx->dev_f32_out(),
+                                                wg ? gw->dev_f32_out() : nullptr, wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_,
+                                                wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_layernorm_bwd_add");
+        else
+            mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr,
+                                            wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()),
+                          "mft_layernorm_bwd");
         return {gx, gw, gb};
+    }
+    std::vector<TensorPtr> apply(const TensorPtr& gy_in) override { return run(gy_in, nullptr); }
+    // the gradient waiting at x (the residual branch's) is added inside the kernel that produces dX
+    bool wants_pending() const override { return true; }
+    std::vector<TensorPtr> apply_fused(const TensorPtr& gy_in, const std::vector<TensorPtr>& pending, std::vector<bool>& absorbed) override {
+        TensorPtr w = !pending.empty() ? pending[0] : nullptr;
+        if (w && (w->numel() != x_->numel() || !w->is_dense())) w = nullptr;
+        if (w && !absorbed.empty()) absorbed[0] = true;
+        return run(gy_in, w);
     }
 private:
     TensorPtr x_, w_, b_;
@@ -142,6 +156,33 @@ TensorPtr layer_norm(const TensorPtr& x_in, const TensorPtr& weight, const Tenso
     auto y = new_like(x);
     mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), y->dev_f32_out(), rows, dim, eps, st()), "mft_layernorm_fwd");
     track(y, {x_in, weight, bias}, std::make_shared<LayerNormBackward>(x, weight, bias, eps));
+    return y;
+}
+
+namespace {
+class ResidualAddBackward : public BackwardFunction {   // AddBackward for equal shapes (core/backward_functions.cpp:36-72)
+public:
+    std::vector<TensorPtr> apply(const TensorPtr& gy) override { return {gy, gy}; }
+};
+}  // namespace
+
+// sum = x + a and y = layer_norm(sum) from one kernel; both results carry the same autograd nodes as ops::add followed by
+// ops::layer_norm (graph/gpt2_model.cpp block forward: residual add, then ln_2 / the next block's ln_1 / ln_f).
+TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out) {
+    require_f32(x_in, "add_layer_norm");
+    require_f32(a_in, "add_layer_norm");
+    if (!weight || !bias || !sum_out) throw TensorError("add_layer_norm: weight, bias and sum_out are required");
+    if (x_in->shape() != a_in->shape()) throw TensorError("add_layer_norm: operands must have the same shape");
+    TensorPtr x = contiguous(x_in), a = contiguous(a_in);
+    const int64_t dim = x->shape().back(), rows = x->numel() / std::max<int64_t>(dim, 1);
+    if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
+    auto sum = new_like(x);
+    auto y = new_like(x);
+    mft_rt::check(mft_add_layernorm_fwd(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), y->dev_f32_out(), rows,
+                                        dim, eps, st()), "mft_add_layernorm_fwd");
+    track(sum, {x_in, a_in}, std::make_shared<ResidualAddBackward>());
+    track(y, {sum, weight, bias}, std::make_shared<LayerNormBackward>(sum, weight, bias, eps));
+    *sum_out = sum;
     return y;
 }
 

@@ -13,7 +13,8 @@ constexpr int kNormMaxCtas = kNumSMs * 2;   // persistent-style grid for the bac
 template <int NV>
 __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
-                     float* __restrict__ y, int64_t rows, int dim, float eps) {
+                     float* __restrict__ y, int64_t rows, int dim, float eps,
+                     const float* __restrict__ add, float* __restrict__ sum_out) {   // add != NULL: normalise x + add, store the sum
     const int lane = threadIdx.x & 31;
     const int dim4 = dim >> 2;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -25,6 +26,11 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
         for (int j = 0; j < NV; ++j) {
             int c = lane + 32 * j;
             v[j] = (c < dim4) ? ld_stream(xr + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (add && c < dim4) {
+                const float4 a = ld_stream(reinterpret_cast<const float4*>(add + r * dim) + c);
+                v[j].x += a.x; v[j].y += a.y; v[j].z += a.z; v[j].w += a.w;
+                st_stream(reinterpret_cast<float4*>(sum_out + r * dim) + c, v[j]);
+            }
             s += v[j].x + v[j].y + v[j].z + v[j].w;
         }
         const float mean = warp_sum(s) / float(dim);
@@ -78,7 +84,8 @@ __global__ void layernorm_fwd_generic(const float* __restrict__ x, const float* 
 template <int NV, bool WG>
 __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ gy,
-                     float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps) {
+                     float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps,
+                     const float* __restrict__ addend) {   // addend != NULL: gx = dx + addend (gradient already waiting at x)
     extern __shared__ float smem[];  // [kNormWarps][2][dim]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int dim4 = dim >> 2;
@@ -143,6 +150,10 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                 o.y = k * (D * (g[j].y * gam[j].y) - s1 - v[j].y * s2);
                 o.z = k * (D * (g[j].z * gam[j].z) - s1 - v[j].z * s2);
                 o.w = k * (D * (g[j].w * gam[j].w) - s1 - v[j].w * s2);
+                if (addend) {
+                    const float4 a = ld_stream(reinterpret_cast<const float4*>(addend + r * dim) + c);
+                    o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+                }
                 st_stream(or_ + c, o);
             }
         }
@@ -344,19 +355,20 @@ static int norm_bwd_ctas(int64_t rows) {
 }
 
 template <int NV>
-static int launch_ln_fwd(const float* x, const float* g, const float* b, float* y, int64_t rows, int dim, float eps, cudaStream_t st) {
+static int launch_ln_fwd(const float* x, const float* g, const float* b, float* y, int64_t rows, int dim, float eps, cudaStream_t st,
+                         const float* add = nullptr, float* sum_out = nullptr) {
     int blocks = int(ceil_div(rows, kNormWarps));
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    layernorm_fwd_kernel<NV><<<blocks, kNormWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps);
+    layernorm_fwd_kernel<NV><<<blocks, kNormWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps, add, sum_out);
     return 0;
 }
 template <int NV>
 static int launch_ln_bwd(const float* x, const float* g, const float* gy, float* gx, float* partial, int64_t rows,
-                         int dim, float eps, int ctas, cudaStream_t st) {
+                         int dim, float eps, int ctas, cudaStream_t st, const float* addend = nullptr) {
     if (!partial) {   // dx only
         int blocks = int(ceil_div(rows, kNormWarps));
         if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-        layernorm_bwd_kernel<NV, false><<<blocks, kNormWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps);
+        layernorm_bwd_kernel<NV, false><<<blocks, kNormWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps, addend);
         return 0;
     }
     size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
@@ -365,7 +377,7 @@ static int launch_ln_bwd(const float* x, const float* g, const float* gy, float*
         cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
-    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps);
+    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps, addend);
     return 0;
 }
 
@@ -373,25 +385,44 @@ static int launch_ln_bwd(const float* x, const float* g, const float* gy, float*
 
 using namespace mft;
 
-extern "C" int mft_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, int64_t rows,
-                                 int64_t dim, float eps, mft_stream_t stream) {
+// add != NULL: y = LayerNorm(x + add) and sum_out = x + add, one pass (the residual add in front of ln_2 / the next block's ln_1)
+static int ln_fwd_impl(const char* who, const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
+                       int64_t rows, int64_t dim, float eps, mft_stream_t stream) {
     if (rows == 0 || dim == 0) return 0;
-    if (!x || !gamma || !beta || !y) return set_error(1, "mft_layernorm_fwd: null pointer");
+    if (!x || !gamma || !beta || !y || (add && !sum_out)) return set_error(1, "%s: null pointer", who);
     cudaStream_t st = as_stream(stream);
-    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta);
+    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) &&
+                     (!add || (aligned16(add) && aligned16(sum_out)));
     if (vec) {
         int nv = int(ceil_div(dim, 128));
-        if (nv <= 1) launch_ln_fwd<1>(x, gamma, beta, y, rows, int(dim), eps, st);
-        else if (nv <= 2) launch_ln_fwd<2>(x, gamma, beta, y, rows, int(dim), eps, st);
-        else if (nv <= 4) launch_ln_fwd<4>(x, gamma, beta, y, rows, int(dim), eps, st);
-        else if (nv <= 6) launch_ln_fwd<6>(x, gamma, beta, y, rows, int(dim), eps, st);
-        else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st);
-        else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st);
+        if (nv <= 1) launch_ln_fwd<1>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        else if (nv <= 2) launch_ln_fwd<2>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        else if (nv <= 4) launch_ln_fwd<4>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        else if (nv <= 6) launch_ln_fwd<6>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
     } else {
-        layernorm_fwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, beta, y, rows, int(dim), eps);
+        const float* src = x;
+        if (add) {   // unaligned / wide rows: separate add, then the generic kernel on the sum
+            int rc = mft_binary(0, x, add, sum_out, 1, 1, rows * dim, 0, 1, stream);
+            if (rc) return rc;
+            src = sum_out;
+        }
+        layernorm_fwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(src, gamma, beta, y, rows, int(dim), eps);
     }
-    MFT_CHECK_LAUNCH("mft_layernorm_fwd");
+    MFT_CHECK_LAUNCH(who);
     return 0;
+}
+
+extern "C" int mft_layernorm_fwd(const float* x, const float* gamma, const float* beta, float* y, int64_t rows,
+                                 int64_t dim, float eps, mft_stream_t stream) {
+    return ln_fwd_impl("mft_layernorm_fwd", x, nullptr, nullptr, gamma, beta, y, rows, dim, eps, stream);
+}
+
+extern "C" int mft_add_layernorm_fwd(const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
+                                     int64_t rows, int64_t dim, float eps, mft_stream_t stream) {
+    if (!add || !sum_out) return set_error(1, "mft_add_layernorm_fwd: null pointer");
+    return ln_fwd_impl("mft_add_layernorm_fwd", x, add, sum_out, gamma, beta, y, rows, dim, eps, stream);
 }
 
 extern "C" size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim) {
@@ -402,9 +433,10 @@ extern "C" size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim) {
     return size_t(parts) * 2 * size_t(dim) * sizeof(float);
 }
 
-extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
-                                 float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
-                                 size_t workspace_bytes, mft_stream_t stream) {
+// addend != NULL: gx = dX + addend — the gradient that already reached x through the residual branch is added while dX is
+// still in registers instead of by a separate accumulation pass.
+static int ln_bwd_impl(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,
+                       float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace, size_t workspace_bytes, mft_stream_t stream) {
     if (dim == 0) return 0;
     if (!x || !gamma || !gy || !gx) return set_error(1, "mft_layernorm_bwd: null pointer");
     if ((dgamma == nullptr) != (dbeta == nullptr)) return set_error(1, "mft_layernorm_bwd: dgamma and dbeta must both be given or both be NULL");
@@ -415,19 +447,21 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
                          mft_norm_bwd_workspace_bytes(rows, dim));
     cudaStream_t st = as_stream(stream);
     float* partial = want_wgrad ? static_cast<float*>(workspace) : nullptr;
-    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(gy) && aligned16(gx) && aligned16(gamma);
+    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(gy) && aligned16(gx) && aligned16(gamma) &&
+                     (!addend || aligned16(addend));
     int parts;
     if (vec) {
         parts = norm_bwd_ctas(rows);
         int nv = int(ceil_div(dim, 128));
-        if (nv <= 1) launch_ln_bwd<1>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
-        else if (nv <= 2) launch_ln_bwd<2>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
-        else if (nv <= 4) launch_ln_bwd<4>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
-        else if (nv <= 6) launch_ln_bwd<6>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
-        else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
-        else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st);
+        if (nv <= 1) launch_ln_bwd<1>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        else if (nv <= 2) launch_ln_bwd<2>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        else if (nv <= 4) launch_ln_bwd<4>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        else if (nv <= 6) launch_ln_bwd<6>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
     } else {
         layernorm_bwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, gy, gx, rows, int(dim), eps);
+        if (addend) { int rc = mft_accumulate(gx, addend, rows * dim, stream); if (rc) return rc; }
         parts = int(ceil_div(rows, 64));
         if (want_wgrad) layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
     }
@@ -437,6 +471,19 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
     }
     MFT_CHECK_LAUNCH("mft_layernorm_bwd");
     return 0;
+}
+
+extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float* gy, float* gx, float* dgamma,
+                                 float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                                 size_t workspace_bytes, mft_stream_t stream) {
+    return ln_bwd_impl(x, gamma, gy, nullptr, gx, dgamma, dbeta, rows, dim, eps, workspace, workspace_bytes, stream);
+}
+
+extern "C" int mft_layernorm_bwd_add(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,
+                                     float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                                     size_t workspace_bytes, mft_stream_t stream) {
+    if (!addend) return set_error(1, "mft_layernorm_bwd_add: null addend");
+    return ln_bwd_impl(x, gamma, gy, addend, gx, dgamma, dbeta, rows, dim, eps, workspace, workspace_bytes, stream);
 }
 
 extern "C" int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t rows, int64_t dim, float eps,

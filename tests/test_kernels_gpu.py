@@ -163,6 +163,38 @@ def test_layernorm_shapes(capi, rows, dim):
     assert rel(y, ey) < FP32_TOL and rel(gx, ex) < 2e-5 and rel(dg, eg) < FP32_TOL and rel(db, eb) < FP32_TOL
 
 
+@pytest.mark.parametrize("rows,dim,wgrad", [(512, 1024, True), (37, 768, False), (64, 100, True), (9, 3000, False), (4096, 1024, False)])
+def test_layernorm_with_residual_operands_equals_separate_kernels(capi, rows, dim, wgrad):
+    """mft_add_layernorm_fwd == add then LayerNorm; mft_layernorm_bwd_add == LayerNorm backward then accumulate — bit for bit."""
+    rng = np.random.default_rng(rows + dim)
+    x, a = (rng.standard_normal((2, rows, dim)) * 1.3).astype(np.float32)
+    w, b = rng.standard_normal((2, dim)).astype(np.float32)
+    gy, wait = rng.standard_normal((2, rows, dim)).astype(np.float32)
+    dx, da, dw, db_, dgy, dwait = dev(x), dev(a), dev(w), dev(b), dev(gy), dev(wait)
+    s_sep = dx + da
+    y_sep = torch.empty_like(dx)
+    capi.call("mft_layernorm_fwd", s_sep, dw, db_, y_sep, rows, dim, 1e-5, None)
+    s_f, y_f = torch.full_like(dx, float("nan")), torch.full_like(dx, float("nan"))
+    capi.call("mft_add_layernorm_fwd", dx, da, s_f, dw, db_, y_f, rows, dim, 1e-5, None)
+    torch.cuda.synchronize()
+    assert torch.equal(s_f, s_sep) and torch.equal(y_f, y_sep)
+    assert rel(y_f, O.layer_norm_fwd(x + a, w, b)) < FP32_TOL
+
+    def bwd(name, extra):
+        gx = torch.full_like(dx, float("nan"))
+        dg = torch.empty(dim, device="cuda") if wgrad else None
+        dbt = torch.empty(dim, device="cuda") if wgrad else None
+        wsp = ws(capi.lib.mft_norm_bwd_workspace_bytes(rows, dim)) if wgrad else None
+        capi.call(name, s_sep, dw, dgy, *extra, gx, dg, dbt, rows, dim, 1e-5, wsp, wsp.numel() if wgrad else 0, None)
+        torch.cuda.synchronize()
+        return gx, dg, dbt
+    gx0, dg0, db0 = bwd("mft_layernorm_bwd", [])
+    gx1, dg1, db1 = bwd("mft_layernorm_bwd_add", [dwait])
+    assert torch.equal(gx1, gx0 + dwait)
+    if wgrad:
+        assert torch.equal(dg0, dg1) and torch.equal(db0, db1)
+
+
 def test_rmsnorm_golden_and_shapes(capi, golden_ops):
     L = golden_ops
     cases = [(L("rms_x"), L("rms_w"), L("rms_gy"), L("rms_y"), L("rms_gx"), L("rms_gw"))]
