@@ -147,7 +147,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-steps", type=int, default=3)
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying the captured CUDA graph")
-    ap.add_argument("--precision", default=os.environ.get("MFT_GEMM_PRECISION", "tf32"), choices=["tf32", "bf16"],
+    ap.add_argument("--precision", default=os.environ.get("MFT_GEMM_PRECISION", "bf16"), choices=["tf32", "bf16"],
                     help="operand precision of the large tensor-core GEMMs (fp32 accumulate either way)")
     a = ap.parse_args()
     if a.impl == "reference":
@@ -263,9 +263,9 @@ def main():
     kind = "kind::f16 bf16 operands" if a.precision == "bf16" else "kind::tf32"
     traffic = None                               # DRAM bytes per GEMM launch from the committed ncu capture of this config
     tpath = os.path.join(ROOT, "profiles", "r1_gemm_traffic.json")
-    if a.config == "c4" and a.precision == "tf32" and os.path.exists(tpath):
+    if a.config == "c4" and os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath))["dram_bytes_per_launch"]
+            traffic = json.load(open(tpath)).get("dram_bytes_per_launch_" + a.precision)
         except Exception:
             traffic = None
     roofline = {"bound": "tensor", "kernel": f"gemm_tc_kernel (tcgen05.mma cta_group::2 {kind}, TMA-fed, fp32 accumulate in TMEM)",

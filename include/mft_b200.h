@@ -63,6 +63,7 @@ typedef struct mft_gemm_args {
     int32_t batch; int64_t stride_a, stride_b, stride_c;
     const float* addend; int64_t ld_addend;            /* [m,n] added after bias/beta (residual stream), or NULL   */
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;  /* [m,n]: result *= d gelu_tanh / dx at this tensor, or NULL */
+    void* gelu_out_bf16; int64_t ld_gelu_out_bf16;     /* bf16 copy of gelu_out (needs gelu_out), or NULL             */
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
 /* bf16-operand form of mft_gemm: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements, multiples of 8),
@@ -88,6 +89,9 @@ int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* workspace, 
  *                  (mft_lora_tn_workspace_bytes) and are reduced in a fixed order (deterministic). */
 int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
                   int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
+/* same, plus a bf16 copy of y (NULL = off; row pitch ld_bf16 elements) for the rank-r segment of the bf16 GEMM */
+int mft_lora_down_ex(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, void* y_bf16,
+                     int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
 size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r);
 int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t ldw, float* out, int64_t ldo, int out_is_rq,
                 int64_t T, int64_t q, int32_t r, float alpha, void* workspace, size_t workspace_bytes, mft_stream_t stream);
@@ -133,6 +137,8 @@ int mft_unary_param(int kind, const float* x, float* y, int64_t n, float p0, flo
 int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t stream);
 int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stream_t stream);
 /* MulBackward for same-shape operands: ga = gy*b, gb = gy*a (core/backward_functions.cpp:74-83). */
+/* mft_gelu_bwd plus a dense bf16 copy of gx (NULL = off) for the bf16 GEMM that consumes it; no reference counterpart. */
+int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream);
 int mft_mul_bwd(const float* a, const float* b, const float* gy, float* ga, float* gb, int64_t n, mft_stream_t stream);
 
 /* ------------------------------------------------------------------ normalisation
@@ -158,6 +164,14 @@ int mft_add_layernorm_fwd(const float* x, const float* add, float* sum_out, cons
 int mft_layernorm_bwd_add(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,
                           float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace, size_t workspace_bytes,
                           mft_stream_t stream);
+/* Supersets for the bf16 GEMM mode (no reference counterpart: the reference is fp32 throughout): `add`/`sum_out`/`addend` may
+ * be NULL; y_bf16 / gx_bf16 (NULL = off) receive a bf16 copy of the fp32 result, row pitch ld_bf16 elements (multiple of 4,
+ * base 8-byte aligned), written by the same kernel so the tensor-core GEMM that consumes the result needs no cast pass. */
+int mft_layernorm_fwd_ex(const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
+                         void* y_bf16, int64_t ld_bf16, int64_t rows, int64_t dim, float eps, mft_stream_t stream);
+int mft_layernorm_bwd_ex(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, void* gx_bf16,
+                         int64_t ld_bf16, float* dgamma, float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                         size_t workspace_bytes, mft_stream_t stream);
 /* LayerNorm backward for callers that cannot allocate device memory. It has no counterpart in the reference.
  * Who needs it: a front end over this ABI (cgo, JNI, ctypes) that merely forwards tensors owned by its host
  * application has no device allocator to take workspace from, and a steady-state loop may ban cudaMalloc because
@@ -201,6 +215,12 @@ int mft_causal_attention_fwd(const float* q, const float* k, const float* v, flo
                              int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
                              int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
                              float scale, int32_t window, mft_stream_t stream);
+/* same, plus a bf16 copy of ctx (NULL = off; same element strides as ctx) for the bf16 GEMM of the output projection */
+int mft_causal_attention_fwd_ex(const float* q, const float* k, const float* v, float* ctx, void* ctx_bf16, int32_t B, int32_t H,
+                                int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                                int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                                float scale, int32_t window, mft_stream_t stream);
 /* Interleaved-pair RoPE on [B,H,S,Hd]: pair (2d,2d+1) rotated by pos*theta^(-2d/Hd)
  * (ops::apply_rope core/ops.cpp:2151-2225). inverse != 0 applies the transpose rotation
  * (ApplyRoPEBackward core/backward_functions.cpp:718-763). */
@@ -233,6 +253,10 @@ int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* labels, int32_
 int mft_lm_ce_bwd(const float* logits, int64_t ld, const int32_t* labels, const float* row_lse,
                   const int32_t* valid, const float* gout, int32_t B, int32_t S, int32_t V, int32_t ignore_index,
                   int32_t reduction, float* dlogits, int64_t ldg, mft_stream_t stream);
+/* same, plus a bf16 copy of dlogits (NULL = off; row pitch ld_bf16 elements) for the bf16 lm_head products */
+int mft_lm_ce_bwd_ex(const float* logits, int64_t ld, const int32_t* labels, const float* row_lse, const int32_t* valid,
+                     const float* gout, int32_t B, int32_t S, int32_t V, int32_t ignore_index, int32_t reduction,
+                     float* dlogits, int64_t ldg, void* dlogits_bf16, int64_t ld_bf16, mft_stream_t stream);
 
 /* ------------------------------------------------------------------ clip + Adam (multi-tensor)
  * A tensor list is an array of mft_tensor_slot in DEVICE memory (param/grad/m/v pointers + length).

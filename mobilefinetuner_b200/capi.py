@@ -34,7 +34,8 @@ class GemmArgs(C.Structure):
                 ("bias", vp), ("gelu_out", vp),
                 ("k2", i32), ("a2", vp), ("lda2", i64), ("b2", vp), ("ldb2", i64),
                 ("batch", i32), ("stride_a", i64), ("stride_b", i64), ("stride_c", i64),
-                ("addend", vp), ("ld_addend", i64), ("gelu_grad_x", vp), ("ld_gelu_grad_x", i64)]
+                ("addend", vp), ("ld_addend", i64), ("gelu_grad_x", vp), ("ld_gelu_grad_x", i64),
+                ("gelu_out_bf16", vp), ("ld_gelu_out_bf16", i64)]
 
 
 class TensorSlot(C.Structure):
@@ -56,6 +57,7 @@ SIGNATURES = {
     "mft_gemm_splitk_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "mft_gemm_splitk": (C.c_int, [C.POINTER(GemmArgs), i32, vp, sz, vp]),
     "mft_lora_down": (C.c_int, [vp, i64, vp, i64, C.c_int, vp, i64, i64, i64, i32, f32, vp]),
+    "mft_lora_down_ex": (C.c_int, [vp, i64, vp, i64, C.c_int, vp, i64, vp, i64, i64, i64, i32, f32, vp]),
     "mft_lora_tn_workspace_bytes": (sz, [i64, i64, i32]),
     "mft_lora_tn": (C.c_int, [vp, i64, vp, i64, vp, i64, C.c_int, i64, i64, i32, f32, vp, sz, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),
@@ -73,12 +75,15 @@ SIGNATURES = {
     "mft_unary_param": (C.c_int, [C.c_int, vp, vp, i64, f32, f32, vp]),
     "mft_gelu_fwd": (C.c_int, [vp, vp, i64, vp]),
     "mft_gelu_bwd": (C.c_int, [vp, vp, vp, i64, vp]),
+    "mft_gelu_bwd_ex": (C.c_int, [vp, vp, vp, vp, i64, vp]),
     "mft_mul_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, vp]),
     "mft_layernorm_fwd": (C.c_int, [vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_norm_bwd_workspace_bytes": (sz, [i64, i64]),
     "mft_layernorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp, sz, vp]),
     "mft_add_layernorm_fwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_layernorm_bwd_add": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i64, f32, vp, sz, vp]),
+    "mft_layernorm_fwd_ex": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i64, i64, f32, vp]),
+    "mft_layernorm_bwd_ex": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, i64, f32, vp, sz, vp]),
     "mft_layernorm_bwd_static": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_rmsnorm_fwd": (C.c_int, [vp, vp, vp, i64, i64, f32, C.c_int, vp]),
     "mft_rmsnorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, C.c_int, vp, sz, vp]),
@@ -87,6 +92,8 @@ SIGNATURES = {
     "mft_attention_precise": (C.c_int, [C.c_int]),
     "mft_causal_attention_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
                                            i64, i64, i64, f32, i32, vp]),
+    "mft_causal_attention_fwd_ex": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
+                                           i64, i64, i64, f32, i32, vp]),
     "mft_rope": (C.c_int, [vp, vp, i64, i64, i64, f32, C.c_int, vp]),
     "mft_repeat_kv_fwd": (C.c_int, [vp, vp, i64, i64, i64, i64, i64, vp]),
     "mft_repeat_kv_bwd": (C.c_int, [vp, vp, i64, i64, i64, i64, i64, vp]),
@@ -94,6 +101,7 @@ SIGNATURES = {
     "mft_lm_ce_workspace_bytes": (sz, [i64]),
     "mft_lm_ce_fwd": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, sz, vp]),
     "mft_lm_ce_bwd": (C.c_int, [vp, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i64, vp]),
+    "mft_lm_ce_bwd_ex": (C.c_int, [vp, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i64, vp, i64, vp]),
     "mft_pack_grads": (C.c_int, [vp, i32, vp, vp]),
     "mft_grad_sumsq_workspace_bytes": (sz, []),
     "mft_grad_sumsq": (C.c_int, [vp, i32, vp, vp, sz, vp]),

@@ -21,9 +21,13 @@ public:
     std::vector<TensorPtr> apply(const TensorPtr& gout) override {
         const auto& s = logits_->shape();
         auto g = Tensor::make(s, kFloat32, false, logits_->ld());
-        mft_rt::check(mft_lm_ce_bwd(logits_->dev_f32(), logits_->ld(), static_cast<const int32_t*>(labels_->dev()), lse_->dev_f32(),
-                                    static_cast<const int32_t*>(valid_->dev()), gout->dev_f32(), int32_t(s[0]), int32_t(s[1]),
-                                    int32_t(s[2]), ignore_, reduction_, g->dev_f32_out(), g->ld(), mft_rt::stream()), "mft_lm_ce_bwd");
+        float* gp = g->dev_f32_out();
+        void* g16 = nullptr;
+        int64_t ld16 = 0;
+        if (internal::emit_bf16_operands()) { auto e = g->bf16_emit(); g16 = e.ptr; ld16 = e.ld; }   // read by the lm_head dX / dW products
+        mft_rt::check(mft_lm_ce_bwd_ex(logits_->dev_f32(), logits_->ld(), static_cast<const int32_t*>(labels_->dev()), lse_->dev_f32(),
+                                       static_cast<const int32_t*>(valid_->dev()), gout->dev_f32(), int32_t(s[0]), int32_t(s[1]),
+                                       int32_t(s[2]), ignore_, reduction_, gp, g->ld(), g16, ld16, mft_rt::stream()), "mft_lm_ce_bwd");
         return {g};
     }
 private:

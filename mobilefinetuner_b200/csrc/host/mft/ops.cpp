@@ -60,7 +60,18 @@ TempBf16 temp_bf16(const float* src, int64_t ld_src, int64_t rows, int64_t cols,
 }  // namespace
 
 int gemm_precision() { return g_precision; }
+bool emit_bf16_operands() {
+    static const bool tc_off = [] { const char* e = std::getenv("MFT_USE_TENSOR_CORES"); return e && e[0] == '0'; }();
+    if (g_precision != 1 || tc_off) return false;
+    const char* e = std::getenv("MFT_BF16_EMIT");      // read per call: tests flip it to compare against the cast-on-demand path
+    return !(e && e[0] == '0');
+}
 void set_gemm_precision(int bf16) { g_precision = bf16 ? 1 : 0; }
+
+bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k) {
+    static const bool tc_off = [] { const char* e = std::getenv("MFT_USE_TENSOR_CORES"); return e && e[0] == '0'; }();
+    return g_precision == 1 && !tc_off && m * n * k >= (int64_t(1) << 24) && m >= 64 && n >= 64 && k >= 32;
+}
 
 // Chooses the execution form of one GEMM. Large products whose operands are not K-major are brought into
 // K-major form by a transpose pass (cached on 2-D weights) so they run on the tcgen05 kernel; everything
@@ -97,13 +108,22 @@ void run_gemm(GemmCall g) {
             else { keep.push_back(temp_bf16(g.b, g.ldb, g.k, g.n, true)); a.b = static_cast<const float*>(keep.back().ptr); a.ldb = keep.back().ld; }
         }
         if (g.k2 > 0) {
-            keep.push_back(temp_bf16(g.a2, g.lda2, g.m, g.k2, false)); a.a2 = static_cast<const float*>(keep.back().ptr); a.lda2 = keep.back().ld;
-            keep.push_back(temp_bf16(g.b2, g.ldb2, g.n, g.k2, false)); a.b2 = static_cast<const float*>(keep.back().ptr); a.ldb2 = keep.back().ld;
+            if (g.a2_tensor && g.a2_tensor->ndim() == 2 && g.a2_tensor->shape()[1] == g.k2 && g.a2_tensor->shape()[0] == g.m) {
+                auto v = g.a2_tensor->bf16_view(); a.a2 = static_cast<const float*>(v.ptr); a.lda2 = v.ld;      // written by lora_down itself
+            } else { keep.push_back(temp_bf16(g.a2, g.lda2, g.m, g.k2, false)); a.a2 = static_cast<const float*>(keep.back().ptr); a.lda2 = keep.back().ld; }
+            if (g.b2_tensor && g.b2_tensor->ndim() == 2) {      // adapter factor: its bf16 K-major shadow is cached per version
+                auto v = g.b2_stored_kn ? g.b2_tensor->bf16_transposed_view() : g.b2_tensor->bf16_view();
+                a.b2 = static_cast<const float*>(v.ptr); a.ldb2 = v.ld;
+            } else { keep.push_back(temp_bf16(g.b2, g.ldb2, g.n, g.k2, false)); a.b2 = static_cast<const float*>(keep.back().ptr); a.ldb2 = keep.back().ld; }
             a.k2 = int32_t(g.k2);
         }
         a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
         a.addend = g.addend; a.ld_addend = g.ld_addend; a.gelu_grad_x = g.gelu_grad_x; a.ld_gelu_grad_x = g.ld_gelu_grad_x;
         a.batch = 1;
+        if (g.gelu_out && g.gelu_tensor && g.gelu_tensor->dev_f32() == g.gelu_out && g.gelu_tensor->ld() == g.ldc) {
+            auto e = g.gelu_tensor->bf16_emit();
+            if (e.ld % 4 == 0) { a.gelu_out_bf16 = e.ptr; a.ld_gelu_out_bf16 = e.ld; }
+        }
         mft_rt::check(mft_gemm_bf16(&a, mft_rt::stream()), "mft_gemm_bf16");
         return;
     }

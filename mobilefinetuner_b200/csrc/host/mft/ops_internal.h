@@ -31,6 +31,10 @@ struct GemmCall {
     int batch = 1; int64_t stride_a = 0, stride_b = 0, stride_c = 0;
     TensorPtr b_weight;   // tensor behind `b` (lets run_gemm reuse its cached K-major / bf16 shadows)
     TensorPtr a_tensor;   // tensor behind `a`, dense view [m or k rows] (bf16 shadow reuse); optional
+    TensorPtr a2_tensor;  // tensor behind `a2` [m, k2] (bf16 shadow reuse); optional
+    TensorPtr b2_tensor;  // tensor behind the rank-r operand: stored [n, k2] (b2_stored_kn = false) or [k2, n] (true); optional
+    bool b2_stored_kn = false;
+    TensorPtr gelu_tensor;   // tensor behind gelu_out: in bf16 mode the epilogue also writes its bf16 shadow
 };
 void run_gemm(GemmCall g);
 
@@ -39,6 +43,10 @@ BackwardFunctionPtr make_gelu_backward(const TensorPtr& x);
 
 // Operand precision of the large (tensor-core) GEMMs: 0 = TF32 (default), 1 = bf16. MFT_GEMM_PRECISION=bf16|tf32.
 int gemm_precision();
+// true when large GEMMs run on bf16 operands: producers of GEMM inputs then also write a bf16 copy (Tensor::bf16_emit)
+bool emit_bf16_operands();
+// true when run_gemm will take the bf16 tensor-core form for an [m,k] x [k,n] product with a K-major A operand
+bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k);
 void set_gemm_precision(int bf16);
 
 }  // namespace internal

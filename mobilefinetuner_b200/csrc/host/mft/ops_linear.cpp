@@ -246,8 +246,15 @@ int skinny_mask() {
 // y[T,r] = alpha * x[T,K] * A   (A [K,r] when a_is_kr, else [r,K])
 void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, bool a_is_kr, int64_t r, float alpha, const TensorPtr& y) {
     if ((skinny_mask() & 1) && r >= 1 && r <= 64) {
-        mft_rt::check(mft_lora_down(x->dev_f32(), x->ld(), A->dev_f32(), A->ld(), a_is_kr ? 1 : 0, y->dev_f32_out(), r, T, K, int32_t(r), alpha,
-                                    mft_rt::stream()), "mft_lora_down");
+        float* yp = y->dev_f32_out();
+        if (emit_bf16_operands()) {      // the rank-r product is the A operand of the bf16 GEMM's second K segment
+            auto e = y->bf16_emit();
+            mft_rt::check(mft_lora_down_ex(x->dev_f32(), x->ld(), A->dev_f32(), A->ld(), a_is_kr ? 1 : 0, yp, r, e.ptr, e.ld, T, K, int32_t(r), alpha,
+                                           mft_rt::stream()), "mft_lora_down_ex");
+        } else {
+            mft_rt::check(mft_lora_down(x->dev_f32(), x->ld(), A->dev_f32(), A->ld(), a_is_kr ? 1 : 0, yp, r, T, K, int32_t(r), alpha,
+                                        mft_rt::stream()), "mft_lora_down");
+        }
         return;
     }
     GemmCall g;
@@ -318,9 +325,13 @@ public:
             std::vector<TensorPtr> keep;
             for (size_t i = 0; i < terms_.size(); ++i) {
                 TermLayout l = classify(terms_[i], in, out);
-                TensorPtr a_in_r = l.a_in_r ? terms_[i].A : small_transpose(terms_[i].A);
+                TensorPtr a_in_r = (l.a_in_r || (i == 0 && gemm_takes_bf16(T, in, out))) ? terms_[i].A : small_transpose(terms_[i].A);
                 keep.push_back(a_in_r);
-                if (i == 0) { g.k2 = l.r; g.a2 = dxa[i]->dev_f32(); g.lda2 = l.r; g.b2 = a_in_r->dev_f32(); g.ldb2 = a_in_r->ld(); }
+                if (i == 0) {
+                    g.k2 = l.r; g.a2 = dxa[i]->dev_f32(); g.lda2 = l.r; g.b2 = a_in_r->dev_f32(); g.ldb2 = a_in_r->ld();
+                    g.a2_tensor = dxa[i];
+                    g.b2_tensor = terms_[i].A; g.b2_stored_kn = !l.a_in_r;      // A [in,r] is K-major as stored; PEFT [r,in] needs the transposed shadow
+                }
             }
             const bool fuse_gelu_bwd = pre_ && terms_.size() <= 1;   // further slices accumulate after the epilogue ran
             if (fuse_gelu_bwd) { g.gelu_grad_x = pre_->dev_f32(); g.ld_gelu_grad_x = pre_->ld(); }
@@ -401,7 +412,8 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
         TermLayout l = classify(terms[i], in, out);
         xa[i] = Tensor::make({T, l.r}, kFloat32);            // s * x A   (kept for dB)
         lora_down(x, T, in, terms[i].A, l.a_in_r, l.r, terms[i].scale, xa[i]);
-        bt[i] = l.b_r_out ? small_transpose(terms[i].B) : terms[i].B;   // [out, r] K-major
+        // [out, r] K-major; the bf16 GEMM form reads the factor's cached bf16 shadow instead (b2_tensor below)
+        bt[i] = (l.b_r_out && !(i == 0 && gemm_takes_bf16(T, out, in))) ? small_transpose(terms[i].B) : terms[i].B;
     }
     GemmCall g;
     g.m = T; g.n = out; g.k = in;
@@ -411,8 +423,12 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     g.bias = bias ? bias->dev_f32() : nullptr;
     TensorPtr act;
     const bool fuse_gelu = gelu_act != nullptr && terms.size() <= 1;   // later slices accumulate after the epilogue ran
-    if (fuse_gelu) { act = Tensor::make(so, kFloat32, false, y->ld()); g.gelu_out = act->dev_f32_out(); }
-    if (!terms.empty()) { g.k2 = xa[0]->shape()[1]; g.a2 = xa[0]->dev_f32(); g.lda2 = g.k2; g.b2 = bt[0]->dev_f32(); g.ldb2 = bt[0]->ld(); }
+    if (fuse_gelu) { act = Tensor::make(so, kFloat32, false, y->ld()); g.gelu_out = act->dev_f32_out(); g.gelu_tensor = act; }
+    if (!terms.empty()) {
+        g.k2 = xa[0]->shape()[1]; g.a2 = xa[0]->dev_f32(); g.lda2 = g.k2; g.b2 = bt[0]->dev_f32(); g.ldb2 = bt[0]->ld();
+        g.a2_tensor = xa[0];
+        g.b2_tensor = terms[0].B; g.b2_stored_kn = classify(terms[0], in, out).b_r_out;   // B [r,out]: transposed shadow; PEFT [out,r]: as stored
+    }
     if (residual) { g.addend = residual->dev_f32(); g.ld_addend = residual->ld(); }   // (x W + b) + residual, then the slices below
     run_gemm(g);
     for (size_t i = 1; i < terms.size(); ++i) {

@@ -197,9 +197,12 @@ TensorPtr gpt2_causal_attention(const TensorPtr& qkv_in, int n_head) {
     const int64_t B = s[0], S = s[1], C = s[2] / 3, Hd = C / n_head;
     auto ctx = Tensor::make({B, S, C}, kFloat32);
     const float* base = qkv->dev_f32();
-    mft_rt::check(mft_causal_attention_fwd(base, base + C, base + 2 * C, ctx->dev_f32_out(), int32_t(B), n_head, int32_t(S), int32_t(Hd),
-                                           S * 3 * C, 3 * C, Hd, S * 3 * C, 3 * C, Hd, S * C, C, Hd,
-                                           1.0f / std::sqrt(float(Hd)), 0, st()), "mft_causal_attention_fwd");
+    float* cp = ctx->dev_f32_out();
+    void* c16 = nullptr;
+    if (internal::emit_bf16_operands() && C % 8 == 0) c16 = ctx->bf16_emit().ptr;     // ctx is the A operand of the output projection
+    mft_rt::check(mft_causal_attention_fwd_ex(base, base + C, base + 2 * C, cp, c16, int32_t(B), n_head, int32_t(S), int32_t(Hd),
+                                              S * 3 * C, 3 * C, Hd, S * 3 * C, 3 * C, Hd, S * C, C, Hd,
+                                              1.0f / std::sqrt(float(Hd)), 0, st()), "mft_causal_attention_fwd");
     return ctx;   // no autograd node: the reference's split severs the graph here
 }
 

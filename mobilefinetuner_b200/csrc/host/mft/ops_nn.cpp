@@ -20,13 +20,29 @@ namespace {
 void* st() { return mft_rt::stream(); }
 
 // ---- unary ops with gradients expressed through other device kernels
+// bf16 GEMM mode: the tensor's bf16 shadow is written by the producing kernel (call after dev_f32_out()). Returns a null
+// pointer when the mode is off or the layout does not allow it (the GEMM then casts on demand as before).
+struct Emit { void* ptr = nullptr; int64_t ld = 0; };
+Emit emit16(const TensorPtr& t, bool need_dense_pitch) {
+    Emit e;
+    if (!emit_bf16_operands() || !t || !t->is_dense() || t->numel() == 0) return e;
+    const int64_t cols = t->shape().empty() ? 1 : t->shape().back();
+    if (need_dense_pitch ? (cols % 8 != 0) : (cols % 4 != 0)) return e;
+    auto v = t->bf16_emit();
+    e.ptr = v.ptr; e.ld = v.ld;
+    return e;
+}
+
 class GeluBackward : public BackwardFunction {       // core/backward_functions.cpp:155-177
 public:
     explicit GeluBackward(TensorPtr x) : x_(std::move(x)) {}
     std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
         TensorPtr gy = contiguous(gy_in);
         auto gx = new_like(x_);
-        mft_rt::check(mft_gelu_bwd(x_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), x_->numel(), st()), "mft_gelu_bwd");
+        float* out = gx->dev_f32_out();
+        const Emit e = emit16(gx, true);      // consumed by fc_in's dX product
+        if (e.ptr) mft_rt::check(mft_gelu_bwd_ex(x_->dev_f32(), gy->dev_f32(), out, e.ptr, x_->numel(), st()), "mft_gelu_bwd_ex");
+        else mft_rt::check(mft_gelu_bwd(x_->dev_f32(), gy->dev_f32(), out, x_->numel(), st()), "mft_gelu_bwd");
         return {gx};
     }
 private:
@@ -103,12 +119,14 @@ public:
         TensorPtr gw, gb;
         if (wg) { gw = Tensor::make(w_->shape(), kFloat32); gb = Tensor::make(w_->shape(), kFloat32); }
         size_t wsb = wg ? mft_norm_bwd_workspace_bytes(rows, dim) : 0;
-        if (waiting)
-            mft_rt::check(mft_layernorm_bwd_add(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), waiting->dev_f32(), gx->dev_f32_out(),
-                                                wg ? gw->dev_f32_out() : nullptr, wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_,
-                                                wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_layernorm_bwd_add");
+        float* gxp = gx->dev_f32_out();
+        const Emit e = emit16(gx, false);     // the stream gradient feeds the dX products of the layer below
+        if (waiting || e.ptr)
+            mft_rt::check(mft_layernorm_bwd_ex(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), waiting ? waiting->dev_f32() : nullptr, gxp, e.ptr, e.ld,
+                                               wg ? gw->dev_f32_out() : nullptr, wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_,
+                                               wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_layernorm_bwd_ex");
         else
-            mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr,
+            mft_rt::check(mft_layernorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gxp, wg ? gw->dev_f32_out() : nullptr,
                                             wg ? gb->dev_f32_out() : nullptr, rows, dim, eps_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()),
                           "mft_layernorm_bwd");
         return {gx, gw, gb};
@@ -154,7 +172,11 @@ TensorPtr layer_norm(const TensorPtr& x_in, const TensorPtr& weight, const Tenso
     const int64_t dim = x->shape().back(), rows = x->numel() / std::max<int64_t>(dim, 1);
     if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
     auto y = new_like(x);
-    mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), y->dev_f32_out(), rows, dim, eps, st()), "mft_layernorm_fwd");
+    float* yp = y->dev_f32_out();
+    const Emit e = emit16(y, false);          // LayerNorm outputs are GEMM inputs (qkv, fc_in, lm_head)
+    if (e.ptr) mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), nullptr, nullptr, weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows, dim, eps, st()),
+                             "mft_layernorm_fwd_ex");
+    else mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), yp, rows, dim, eps, st()), "mft_layernorm_fwd");
     track(y, {x_in, weight, bias}, std::make_shared<LayerNormBackward>(x, weight, bias, eps));
     return y;
 }
@@ -178,8 +200,10 @@ TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const Ten
     if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
     auto sum = new_like(x);
     auto y = new_like(x);
-    mft_rt::check(mft_add_layernorm_fwd(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), y->dev_f32_out(), rows,
-                                        dim, eps, st()), "mft_add_layernorm_fwd");
+    float* yp = y->dev_f32_out();
+    const Emit e = emit16(y, false);
+    mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows,
+                                       dim, eps, st()), "mft_layernorm_fwd_ex");
     track(sum, {x_in, a_in}, std::make_shared<ResidualAddBackward>());
     track(y, {sum, weight, bias}, std::make_shared<LayerNormBackward>(sum, weight, bias, eps));
     *sum_out = sum;

@@ -208,6 +208,16 @@ Tensor::Bf16View Tensor::bf16_view() const {
     return {bf16_->dev, bf16_ld_};
 }
 
+Tensor::Bf16Out Tensor::bf16_emit() {
+    if (dtype_ != kFloat32) throw TensorError("bf16_emit: float32 tensors only");
+    const int64_t cols = shape_.empty() ? 1 : shape_.back(), r = rows();
+    const int64_t ld = (cols + 7) / 8 * 8;
+    if (!bf16_) bf16_ = raw_buffer(size_t(r) * ld * 2, !st_->in_arena);
+    bf16_version_ = version();
+    bf16_ld_ = ld;
+    return {bf16_->dev, ld};
+}
+
 Tensor::Bf16View Tensor::bf16_transposed_view() const {
     if (dtype_ != kFloat32 || shape_.size() != 2) throw TensorError("bf16_transposed_view: 2-D float32 tensors only");
     const int64_t r = shape_[0], c = shape_[1];

@@ -136,6 +136,10 @@ public:
     struct Bf16View { const void* ptr; int64_t ld; };
     Bf16View bf16_view() const;
     Bf16View bf16_transposed_view() const;
+    // For producers that write the bf16 copy themselves: call AFTER dev_*_out(); returns the shadow buffer (allocating it
+    // on first use) and marks it valid for the tensor's current contents, so the next bf16_view() needs no cast kernel.
+    struct Bf16Out { void* ptr; int64_t ld; };
+    Bf16Out bf16_emit();
 
 private:
     std::vector<int64_t> shape_;

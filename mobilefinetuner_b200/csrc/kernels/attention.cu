@@ -34,7 +34,8 @@ __global__ void __launch_bounds__(128)
 causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                             float* __restrict__ ctx, int H, int S,
                             int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
-                            int64_t osb, int64_t oss, int64_t osh, float scale, int window) {
+                            int64_t osb, int64_t oss, int64_t osh, float scale, int window,
+                            __nv_bfloat16* __restrict__ ctx16) {   // ctx16 != NULL: bf16 copy of ctx, same element strides
     constexpr int LD = HD + kAttPad;
     constexpr int KS = HD / 8;    // k-slabs over the head dim (QK^T)
     constexpr int NT = HD / 8;    // n-tiles over the head dim (PV)
@@ -242,6 +243,7 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
     }
 
     float* ob = ctx + b * osb + h * osh;
+    __nv_bfloat16* ob16 = ctx16 ? ctx16 + b * osb + h * osh : nullptr;
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
         float l0 = lrow[m][0], l1 = lrow[m][1];
@@ -253,6 +255,10 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
         for (int n = 0; n < NT; ++n) {
             if (r0 < S) *reinterpret_cast<float2*>(ob + int64_t(r0) * oss + n * 8 + 2 * t) = make_float2(o[m][n][0] * inv0, o[m][n][1] * inv0);
             if (r1 < S) *reinterpret_cast<float2*>(ob + int64_t(r1) * oss + n * 8 + 2 * t) = make_float2(o[m][n][2] * inv1, o[m][n][3] * inv1);
+            if (ob16) {
+                if (r0 < S) *reinterpret_cast<__nv_bfloat162*>(ob16 + int64_t(r0) * oss + n * 8 + 2 * t) = __floats2bfloat162_rn(o[m][n][0] * inv0, o[m][n][1] * inv0);
+                if (r1 < S) *reinterpret_cast<__nv_bfloat162*>(ob16 + int64_t(r1) * oss + n * 8 + 2 * t) = __floats2bfloat162_rn(o[m][n][2] * inv1, o[m][n][3] * inv1);
+            }
         }
     }
 }
@@ -260,7 +266,7 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
 template <int HD, bool PRECISE, int MT>
 static int launch_attention_mt(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
                                int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
-                               int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
+                               int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st, void* ctx16) {
     constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
     static bool attr_set = false;
     if (!attr_set) {
@@ -269,20 +275,20 @@ static int launch_attention_mt(const float* q, const float* k, const float* v, f
     }
     dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
     causal_attention_fwd_kernel<HD, PRECISE, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
-                                                                 osh, scale, window);
+                                                                 osh, scale, window, static_cast<__nv_bfloat16*>(ctx16));
     return 0;
 }
 
 template <int HD, bool PRECISE>
 static int launch_attention(const float* q, const float* k, const float* v, float* ctx, int B, int H, int S,
                             int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
-                            int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st) {
+                            int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st, void* ctx16) {
     // two 16-row slabs per warp halve the shared-memory reads per MMA; worth it once there are enough 128-row CTAs to
     // fill the chip, and only where the fragments still fit in registers (fast mode, head_dim <= 64)
     if (!PRECISE && HD <= 64 && int64_t(ceil_div(S, 128)) * B * H >= 2 * kNumSMs)
         return launch_attention_mt<HD, PRECISE, (!PRECISE && HD <= 64) ? 2 : 1>(q, k, v, ctx, B, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh,
-                                                                               scale, window, st);
-    return launch_attention_mt<HD, PRECISE, 1>(q, k, v, ctx, B, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale, window, st);
+                                                                               scale, window, st, ctx16);
+    return launch_attention_mt<HD, PRECISE, 1>(q, k, v, ctx, B, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale, window, st, ctx16);
 }
 
 static bool env_attention_precise() {
@@ -301,7 +307,7 @@ extern "C" int mft_attention_precise(int enable) {
     return prev;
 }
 
-extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
+static int attention_impl(const float* q, const float* k, const float* v, float* ctx, void* ctx16, int32_t B, int32_t H,
                                         int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
                                         int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
                                         int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
@@ -313,11 +319,13 @@ extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const fl
         return set_error(1, "mft_causal_attention_fwd: k/v must be 16-byte aligned with strides %% 4 == 0");
     if ((reinterpret_cast<uintptr_t>(ctx) & 7u) || (o_stride_b % 2) || (o_stride_s % 2) || (o_stride_h % 2))
         return set_error(1, "mft_causal_attention_fwd: ctx must be 8-byte aligned with even strides");
+    if (ctx16 && ((reinterpret_cast<uintptr_t>(ctx16) & 3u) || (Hd & 1)))
+        return set_error(1, "mft_causal_attention_fwd_ex: the bf16 output must be 4-byte aligned");
     cudaStream_t st = as_stream(stream);
 #define MFT_ATT(HD_) (g_attention_precise ? launch_attention<HD_, true>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
-                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st) \
+                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st, ctx16) \
                                           : launch_attention<HD_, false>(q, k, v, ctx, B, H, S, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, \
-                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st))
+                                            kv_stride_s, kv_stride_h, o_stride_b, o_stride_s, o_stride_h, scale, window, st, ctx16))
     switch (Hd) {
         case 16: MFT_ATT(16); break;
         case 32: MFT_ATT(32); break;
@@ -328,4 +336,23 @@ extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const fl
 #undef MFT_ATT
     MFT_CHECK_LAUNCH("mft_causal_attention_fwd");
     return 0;
+}
+
+extern "C" int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
+                                        int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                        int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                                        int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                                        float scale, int32_t window, mft_stream_t stream) {
+    return attention_impl(q, k, v, ctx, nullptr, B, H, S, Hd, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, kv_stride_s, kv_stride_h,
+                          o_stride_b, o_stride_s, o_stride_h, scale, window, stream);
+}
+
+// same, plus a bf16 copy of ctx (same element strides as ctx) for the bf16 GEMM of the output projection
+extern "C" int mft_causal_attention_fwd_ex(const float* q, const float* k, const float* v, float* ctx, void* ctx_bf16, int32_t B, int32_t H,
+                                           int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                                           int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                                           int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                                           float scale, int32_t window, mft_stream_t stream) {
+    return attention_impl(q, k, v, ctx, ctx_bf16, B, H, S, Hd, q_stride_b, q_stride_s, q_stride_h, kv_stride_b, kv_stride_s, kv_stride_h,
+                          o_stride_b, o_stride_s, o_stride_h, scale, window, stream);
 }

@@ -1,5 +1,6 @@
 // Shared device/host helpers for the mft_b200 kernels (sm_100a only).
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -90,6 +91,16 @@ __device__ __forceinline__ float ld_stream(const float* p) {
 __device__ __forceinline__ void st_stream(float4* p, const float4& v) {
     asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
                  :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Four fp32 values -> four bf16 (round to nearest even), one 8-byte store. Producers of GEMM operands use it to leave a
+// bf16 copy next to their fp32 result, so the bf16 tensor-core GEMM that consumes it needs no separate cast pass.
+__device__ __forceinline__ void st_bf16x4(void* dst, const float4& v) {
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 p;
+    p.x = *reinterpret_cast<const uint32_t*>(&lo);
+    p.y = *reinterpret_cast<const uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(dst) = p;
 }
 
 // ---- legacy-pipe tensor-core helpers (mma.sync m16n8k8 TF32), shared by attention and the LoRA factor kernels

@@ -157,7 +157,8 @@ __global__ void unary_kernel(const float* __restrict__ x, float* __restrict__ y,
 }
 
 // gx = gy * gelu'(x): reads 8 B, writes 4 B per element.
-__global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gy, float* __restrict__ gx, int64_t n) {
+__global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gy, float* __restrict__ gx, int64_t n,
+                                __nv_bfloat16* __restrict__ gx16) {   // gx16 != NULL (dense, 8-byte aligned, n % 4 == 0): bf16 copy of gx
     const int64_t n4 = n >> 2;
     const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gy) | reinterpret_cast<uintptr_t>(gx)) & 15u) == 0;
     int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
@@ -170,6 +171,7 @@ __global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __rest
             r.x = g.x * gelu_tanh_grad_f(v.x); r.y = g.y * gelu_tanh_grad_f(v.y);
             r.z = g.z * gelu_tanh_grad_f(v.z); r.w = g.w * gelu_tanh_grad_f(v.w);
             st_stream(o4 + i, r);
+            if (gx16) st_bf16x4(gx16 + i * 4, r);
         }
         for (int64_t i = n4 * 4 + tid; i < n; i += stride) gx[i] = gy[i] * gelu_tanh_grad_f(x[i]);
     } else {
@@ -276,8 +278,19 @@ extern "C" int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t st
 extern "C" int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stream_t stream) {
     if (n == 0) return 0;
     if (!x || !gy || !gx) return set_error(1, "mft_gelu_bwd: null pointer");
-    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n);
+    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, nullptr);
     MFT_CHECK_LAUNCH("mft_gelu_bwd");
+    return 0;
+}
+
+// same, plus a dense bf16 copy of gx for the bf16 tensor-core GEMM that consumes it (fc_in's dX product)
+extern "C" int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!x || !gy || !gx) return set_error(1, "mft_gelu_bwd_ex: null pointer");
+    const bool ok = gx_bf16 && (n & 3) == 0 && aligned16(x) && aligned16(gy) && aligned16(gx) && (reinterpret_cast<uintptr_t>(gx_bf16) & 7u) == 0;
+    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, ok ? static_cast<__nv_bfloat16*>(gx_bf16) : nullptr);
+    MFT_CHECK_LAUNCH("mft_gelu_bwd_ex");
+    if (gx_bf16 && !ok) return mft_cast_bf16(gx, n, gx_bf16, n, 1, n, stream);
     return 0;
 }
 

@@ -38,6 +38,9 @@ static int to_params(const mft_gemm_args* a, GemmParams& p) {
     p.stride_a = a->stride_a; p.stride_b = a->stride_b; p.stride_c = a->stride_c;
     p.addend = a->addend; p.ld_addend = a->ld_addend;
     p.gelu_grad_x = a->gelu_grad_x; p.ld_gelu_grad_x = a->ld_gelu_grad_x;
+    p.gelu_out_bf16 = a->gelu_out_bf16; p.ld_gelu_out_bf16 = a->ld_gelu_out_bf16;
+    if (p.gelu_out_bf16 && (!p.gelu_out || p.batch > 1 || (p.ld_gelu_out_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.gelu_out_bf16) & 7u)))
+        return set_error(1, "mft_gemm: gelu_out_bf16 needs gelu_out, batch 1, an 8-byte aligned base and a pitch that is a multiple of 4");
     if (p.m == 0 || p.n == 0) return 0;
     if (!p.c || (p.k > 0 && (!p.a || !p.b))) return set_error(1, "mft_gemm: null operand");
     if (p.k2 > 0 && (!p.a2 || !p.b2)) return set_error(1, "mft_gemm: null second-segment operand");
@@ -99,7 +102,9 @@ extern "C" int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* 
         p.ksplit = splits;
         p.partial = static_cast<float*>(workspace);
     }
-    return launch_gemm_simt(p, as_stream(stream));
+    rc = launch_gemm_simt(p, as_stream(stream));
+    if (rc == 0 && p.gelu_out_bf16) rc = mft_cast_bf16(p.gelu_out, p.ldc, p.gelu_out_bf16, p.ld_gelu_out_bf16, p.m, p.n, stream);   // SIMT path: separate cast
+    return rc;
 }
 
 extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
@@ -108,7 +113,9 @@ extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
     if (rc) return rc;
     if (p.m == 0 || p.n == 0) return 0;
     if (g_use_tc && gemm_tc_eligible(p)) return launch_gemm_tc(p, as_stream(stream));
-    return launch_gemm_simt(p, as_stream(stream));
+    rc = launch_gemm_simt(p, as_stream(stream));
+    if (rc == 0 && p.gelu_out_bf16) rc = mft_cast_bf16(p.gelu_out, p.ldc, p.gelu_out_bf16, p.ld_gelu_out_bf16, p.m, p.n, stream);   // SIMT path: separate cast
+    return rc;
 }
 
 extern "C" int mft_gemm_profile(int enable) { gemm_tc_profile_enable(enable != 0); return 0; }

@@ -16,6 +16,7 @@ struct GemmParams {
     int batch; int64_t stride_a, stride_b, stride_c;
     const float* addend = nullptr; int64_t ld_addend = 0;
     const float* gelu_grad_x = nullptr; int64_t ld_gelu_grad_x = 0;
+    void* gelu_out_bf16 = nullptr; int64_t ld_gelu_out_bf16 = 0;
     bool bf16 = false;         // operands are bf16 arrays
     int ksplit = 1;            // SIMT split-K: number of K slices (partials reduced in a fixed order)
     float* partial = nullptr;  // [batch][ksplit][m][n] scratch when ksplit > 1

@@ -192,6 +192,7 @@ struct TcArgs {
     const float* bias;
     const float* addend; int64_t ld_addend;
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;
+    __nv_bfloat16* gelu16; int64_t ld_gelu16;   // bf16 copy of the GELU aux output
     float alpha, beta;
     int tiles_m, tiles_n;
     int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
@@ -474,9 +475,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
                             }
                             *reinterpret_cast<float4*>(dst) = o;
-                            if (gbase)
-                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) =
-                                    make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                            if (gbase) {
+                                const float4 gv = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
+                                if (p.gelu16) st_bf16x4(p.gelu16 + int64_t(grow) * p.ld_gelu16 + col, gv);
+                            }
                         }
                     }
                 } else if (FUSED && vec_ok && col + 4 <= p.n) {   // fused residual / GELU-gradient operands
@@ -521,9 +524,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 o.z *= gelu_tanh_grad_f(gx[q].z); o.w *= gelu_tanh_grad_f(gx[q].w);
                             }
                             *reinterpret_cast<float4*>(cbase + int64_t(grow) * p.ldc + col) = o;
-                            if (gbase)
-                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) =
-                                    make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                            if (gbase) {
+                                const float4 gv = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
+                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
+                                if (p.gelu16) st_bf16x4(p.gelu16 + int64_t(grow) * p.ld_gelu16 + col, gv);
+                            }
                         }
                     }
                 } else {
@@ -542,7 +547,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             if (FUSED && abase) o += abase[int64_t(grow) * p.ld_addend + cc];
                             if (FUSED && xbase) o *= gelu_tanh_grad_f(xbase[int64_t(grow) * p.ld_gelu_grad_x + cc]);
                             *dst = o;
-                            if (gbase) gbase[int64_t(grow) * p.ldc + cc] = gelu_tanh_f(o);
+                            if (gbase) {
+                                const float gv = gelu_tanh_f(o);
+                                gbase[int64_t(grow) * p.ldc + cc] = gv;
+                                if (p.gelu16) p.gelu16[int64_t(grow) * p.ld_gelu16 + cc] = __float2bfloat16_rn(gv);
+                            }
                         }
                     }
                 }
@@ -754,6 +763,7 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;
     a.alpha = p.alpha; a.beta = p.beta;
     a.addend = p.addend; a.ld_addend = p.ld_addend; a.gelu_grad_x = p.gelu_grad_x; a.ld_gelu_grad_x = p.ld_gelu_grad_x;
+    a.gelu16 = static_cast<__nv_bfloat16*>(p.gelu_out_bf16); a.ld_gelu16 = p.ld_gelu_out_bf16;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
     static const int dbg = [] { const char* e = getenv("MFT_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
     a.debug = dbg;

@@ -119,7 +119,8 @@ __device__ __forceinline__ void cp_async_zfill(void* smem, const void* gmem, int
 template <bool PRECISE>
 __global__ void __launch_bounds__(128)
 lora_down_mma_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
-                     float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha) {
+                     float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha,
+                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {   // y16 != NULL: bf16 copy of y
     extern __shared__ __align__(16) float As[];                       // [kDmSpan][18]; reused for the cross-warp reduction
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
@@ -215,7 +216,11 @@ lora_down_mma_kernel(const float* __restrict__ x, int64_t ldx, const float* __re
     for (int idx = threadIdx.x; idx < 256; idx += 128) {
         const int rr = idx >> 4, c = idx & 15;
         const int64_t row = row0 + rr;
-        if (row < T && c < r) y[row * ldy + c] = (((red[idx] + red[256 + idx]) + red[512 + idx]) + red[768 + idx]) * alpha;
+        if (row < T && c < r) {
+            const float v = (((red[idx] + red[256 + idx]) + red[512 + idx]) + red[768 + idx]) * alpha;
+            y[row * ldy + c] = v;
+            if (y16) y16[row * ld16 + c] = __float2bfloat16_rn(v);
+        }
     }
 }
 
@@ -374,8 +379,9 @@ static void launch_down(const float* x, int64_t ldx, const float* a, int64_t lda
     lora_down_kernel<RPW, RMAX, KC><<<unsigned(ceil_div(T, int64_t(8 * RPW))), 256, smem, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha);
 }
 
-extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
-                             int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
+static int lora_down_impl(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
+                          int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream, void* y16v, int64_t ld16) {
+    __nv_bfloat16* y16 = static_cast<__nv_bfloat16*>(y16v);
     if (T == 0 || r == 0) return 0;
     if (!x || !a || !y) return set_error(1, "mft_lora_down: null pointer");
     if (r < 1 || r > 64) return set_error(1, "mft_lora_down: rank %d outside 1..64", r);
@@ -393,8 +399,8 @@ extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_
             attr = true;
         }
         const unsigned grid = unsigned(ceil_div(T, int64_t(16)));
-        if (precise) lora_down_mma_kernel<true><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha);
-        else lora_down_mma_kernel<false><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha);
+        if (precise) lora_down_mma_kernel<true><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
+        else lora_down_mma_kernel<false><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
         MFT_CHECK_LAUNCH("mft_lora_down");
         return 0;
     }
@@ -407,7 +413,19 @@ extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_
         launch_down<1, 64, 64>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, st);
     }
     MFT_CHECK_LAUNCH("mft_lora_down");
+    if (y16) return mft_cast_bf16(y, ldy, y16, ld16, T, r, stream);      // FMA path: separate cast
     return 0;
+}
+
+extern "C" int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
+                             int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
+    return lora_down_impl(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha, stream, nullptr, 0);
+}
+
+// same, plus a bf16 copy of y (row pitch ld_bf16 elements) — the K-major A operand of the rank-r segment of the bf16 GEMM
+extern "C" int mft_lora_down_ex(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, void* y_bf16,
+                                int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
+    return lora_down_impl(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha, stream, y_bf16, ld_bf16);
 }
 
 extern "C" size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r) {

@@ -14,7 +14,8 @@ template <int NV>
 __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                      float* __restrict__ y, int64_t rows, int dim, float eps,
-                     const float* __restrict__ add, float* __restrict__ sum_out) {   // add != NULL: normalise x + add, store the sum
+                     const float* __restrict__ add, float* __restrict__ sum_out,     // add != NULL: normalise x + add, store the sum
+                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {                 // y16 != NULL: bf16 copy of y (pitch ld16)
     const int lane = threadIdx.x & 31;
     const int dim4 = dim >> 2;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -57,6 +58,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                 o.z = (v[j].z - mean) * rstd * g.z + b.z;
                 o.w = (v[j].w - mean) * rstd * g.w + b.w;
                 st_stream(yr + c, o);
+                if (y16) st_bf16x4(y16 + r * ld16 + c * 4, o);
             }
         }
     }
@@ -85,7 +87,8 @@ template <int NV, bool WG>
 __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ gy,
                      float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps,
-                     const float* __restrict__ addend) {   // addend != NULL: gx = dx + addend (gradient already waiting at x)
+                     const float* __restrict__ addend,     // addend != NULL: gx = dx + addend (gradient already waiting at x)
+                     __nv_bfloat16* __restrict__ gx16, int64_t ld16) {   // gx16 != NULL: bf16 copy of gx
     extern __shared__ float smem[];  // [kNormWarps][2][dim]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int dim4 = dim >> 2;
@@ -155,6 +158,7 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                     o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
                 }
                 st_stream(or_ + c, o);
+                if (gx16) st_bf16x4(gx16 + r * ld16 + c * 4, o);
             }
         }
     }
@@ -356,19 +360,20 @@ static int norm_bwd_ctas(int64_t rows) {
 
 template <int NV>
 static int launch_ln_fwd(const float* x, const float* g, const float* b, float* y, int64_t rows, int dim, float eps, cudaStream_t st,
-                         const float* add = nullptr, float* sum_out = nullptr) {
+                         const float* add = nullptr, float* sum_out = nullptr, void* y16 = nullptr, int64_t ld16 = 0) {
     int blocks = int(ceil_div(rows, kNormWarps));
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    layernorm_fwd_kernel<NV><<<blocks, kNormWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps, add, sum_out);
+    layernorm_fwd_kernel<NV><<<blocks, kNormWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps, add, sum_out, static_cast<__nv_bfloat16*>(y16), ld16);
     return 0;
 }
 template <int NV>
 static int launch_ln_bwd(const float* x, const float* g, const float* gy, float* gx, float* partial, int64_t rows,
-                         int dim, float eps, int ctas, cudaStream_t st, const float* addend = nullptr) {
+                         int dim, float eps, int ctas, cudaStream_t st, const float* addend = nullptr, void* gx16v = nullptr, int64_t ld16 = 0) {
+    __nv_bfloat16* gx16 = static_cast<__nv_bfloat16*>(gx16v);
     if (!partial) {   // dx only
         int blocks = int(ceil_div(rows, kNormWarps));
         if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-        layernorm_bwd_kernel<NV, false><<<blocks, kNormWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps, addend);
+        layernorm_bwd_kernel<NV, false><<<blocks, kNormWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps, addend, gx16, ld16);
         return 0;
     }
     size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
@@ -377,7 +382,7 @@ static int launch_ln_bwd(const float* x, const float* g, const float* gy, float*
         cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
-    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps, addend);
+    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps, addend, gx16, ld16);
     return 0;
 }
 
@@ -387,20 +392,21 @@ using namespace mft;
 
 // add != NULL: y = LayerNorm(x + add) and sum_out = x + add, one pass (the residual add in front of ln_2 / the next block's ln_1)
 static int ln_fwd_impl(const char* who, const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
-                       int64_t rows, int64_t dim, float eps, mft_stream_t stream) {
+                       int64_t rows, int64_t dim, float eps, mft_stream_t stream, void* y16 = nullptr, int64_t ld16 = 0) {
     if (rows == 0 || dim == 0) return 0;
     if (!x || !gamma || !beta || !y || (add && !sum_out)) return set_error(1, "%s: null pointer", who);
     cudaStream_t st = as_stream(stream);
     const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) &&
-                     (!add || (aligned16(add) && aligned16(sum_out)));
+                     (!add || (aligned16(add) && aligned16(sum_out))) &&
+                     (!y16 || ((reinterpret_cast<uintptr_t>(y16) & 7u) == 0 && (ld16 & 3) == 0));
     if (vec) {
         int nv = int(ceil_div(dim, 128));
-        if (nv <= 1) launch_ln_fwd<1>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
-        else if (nv <= 2) launch_ln_fwd<2>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
-        else if (nv <= 4) launch_ln_fwd<4>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
-        else if (nv <= 6) launch_ln_fwd<6>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
-        else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
-        else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out);
+        if (nv <= 1) launch_ln_fwd<1>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
+        else if (nv <= 2) launch_ln_fwd<2>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
+        else if (nv <= 4) launch_ln_fwd<4>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
+        else if (nv <= 6) launch_ln_fwd<6>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
+        else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
+        else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
     } else {
         const float* src = x;
         if (add) {   // unaligned / wide rows: separate add, then the generic kernel on the sum
@@ -409,6 +415,7 @@ static int ln_fwd_impl(const char* who, const float* x, const float* add, float*
             src = sum_out;
         }
         layernorm_fwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(src, gamma, beta, y, rows, int(dim), eps);
+        if (y16) { int rc = mft_cast_bf16(y, dim, y16, ld16, rows, dim, stream); if (rc) return rc; }
     }
     MFT_CHECK_LAUNCH(who);
     return 0;
@@ -436,7 +443,8 @@ extern "C" size_t mft_norm_bwd_workspace_bytes(int64_t rows, int64_t dim) {
 // addend != NULL: gx = dX + addend — the gradient that already reached x through the residual branch is added while dX is
 // still in registers instead of by a separate accumulation pass.
 static int ln_bwd_impl(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,
-                       float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace, size_t workspace_bytes, mft_stream_t stream) {
+                       float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace, size_t workspace_bytes, mft_stream_t stream,
+                       void* gx16 = nullptr, int64_t ld16 = 0) {
     if (dim == 0) return 0;
     if (!x || !gamma || !gy || !gx) return set_error(1, "mft_layernorm_bwd: null pointer");
     if ((dgamma == nullptr) != (dbeta == nullptr)) return set_error(1, "mft_layernorm_bwd: dgamma and dbeta must both be given or both be NULL");
@@ -448,20 +456,21 @@ static int ln_bwd_impl(const float* x, const float* gamma, const float* gy, cons
     cudaStream_t st = as_stream(stream);
     float* partial = want_wgrad ? static_cast<float*>(workspace) : nullptr;
     const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(gy) && aligned16(gx) && aligned16(gamma) &&
-                     (!addend || aligned16(addend));
+                     (!addend || aligned16(addend)) && (!gx16 || ((reinterpret_cast<uintptr_t>(gx16) & 7u) == 0 && (ld16 & 3) == 0));
     int parts;
     if (vec) {
         parts = norm_bwd_ctas(rows);
         int nv = int(ceil_div(dim, 128));
-        if (nv <= 1) launch_ln_bwd<1>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
-        else if (nv <= 2) launch_ln_bwd<2>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
-        else if (nv <= 4) launch_ln_bwd<4>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
-        else if (nv <= 6) launch_ln_bwd<6>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
-        else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
-        else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend);
+        if (nv <= 1) launch_ln_bwd<1>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
+        else if (nv <= 2) launch_ln_bwd<2>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
+        else if (nv <= 4) launch_ln_bwd<4>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
+        else if (nv <= 6) launch_ln_bwd<6>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
+        else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
+        else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
     } else {
         layernorm_bwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, gy, gx, rows, int(dim), eps);
         if (addend) { int rc = mft_accumulate(gx, addend, rows * dim, stream); if (rc) return rc; }
+        if (gx16) { int rc = mft_cast_bf16(gx, dim, gx16, ld16, rows, dim, stream); if (rc) return rc; }
         parts = int(ceil_div(rows, 64));
         if (want_wgrad) layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
     }
@@ -477,6 +486,18 @@ extern "C" int mft_layernorm_bwd(const float* x, const float* gamma, const float
                                  float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
                                  size_t workspace_bytes, mft_stream_t stream) {
     return ln_bwd_impl(x, gamma, gy, nullptr, gx, dgamma, dbeta, rows, dim, eps, workspace, workspace_bytes, stream);
+}
+
+// Supersets used by the bf16 GEMM mode: optional residual operands as above plus an optional bf16 copy of the result
+// (y_bf16 / gx_bf16, row pitch ld_bf16 elements, multiple of 4, 8-byte aligned) for the GEMM that consumes it next.
+extern "C" int mft_layernorm_fwd_ex(const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
+                                    void* y_bf16, int64_t ld_bf16, int64_t rows, int64_t dim, float eps, mft_stream_t stream) {
+    return ln_fwd_impl("mft_layernorm_fwd_ex", x, add, sum_out, gamma, beta, y, rows, dim, eps, stream, y_bf16, ld_bf16);
+}
+extern "C" int mft_layernorm_bwd_ex(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, void* gx_bf16,
+                                    int64_t ld_bf16, float* dgamma, float* dbeta, int64_t rows, int64_t dim, float eps, void* workspace,
+                                    size_t workspace_bytes, mft_stream_t stream) {
+    return ln_bwd_impl(x, gamma, gy, addend, gx, dgamma, dbeta, rows, dim, eps, workspace, workspace_bytes, stream, gx_bf16, ld_bf16);
 }
 
 extern "C" int mft_layernorm_bwd_add(const float* x, const float* gamma, const float* gy, const float* addend, float* gx, float* dgamma,

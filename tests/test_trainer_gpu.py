@@ -126,6 +126,51 @@ def test_trainer_bf16_gemm_mode_c1_first_steps():
         hostlib.mft_host_set_gemm_precision(0)
 
 
+@pytest.mark.tf32
+def test_bf16_operands_written_by_producers_equal_cast_on_demand():
+    """bf16 GEMM mode: LayerNorm / attention / GELU / lora_down / CE kernels write the bf16 copy of their result themselves
+    (no cast kernels). The rounding is the same round-to-nearest-even, so losses and parameters must equal the
+    cast-on-demand path bit for bit, with fewer launches."""
+    from mobilefinetuner_b200.trainer import Trainer, hostlib
+    hostlib.mft_host_set_gemm_precision(1)
+    try:
+        out = []
+        for emit in ("0", "1"):
+            os.environ["MFT_BF16_EMIT"] = emit
+            tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096)
+            losses = [tr.step_numpy(tr.next_synthetic_batch()) for _ in range(4)]
+            out.append((losses, [tr.param_checksum(i) for i in range(tr.num_trainable)], tr.kernel_launches))
+            tr.close()
+        assert out[0][0] == out[1][0] and out[0][1] == out[1][1]
+        assert out[1][2] <= out[0][2] - 50, (out[0][2], out[1][2])
+    finally:
+        os.environ.pop("MFT_BF16_EMIT", None)
+        hostlib.mft_host_set_gemm_precision(0)
+
+
+@pytest.mark.tf32
+@pytest.mark.parametrize("bf16", [0, 1])
+def test_trainer_c1_50_steps_tensor_core_modes_within_loss_tolerance(bf16):
+    """Config c1 at full size, 50 steps against the reference build's trajectory (tests/golden/traj/gpt2_small_lora_c1_50.txt):
+    loss within 1e-3 relative at every step in the default TF32 mode and in the bf16-operand mode (north_star tolerance)."""
+    from mobilefinetuner_b200.trainer import Trainer, hostlib
+    hostlib.mft_host_set_gemm_precision(bf16)
+    try:
+        tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096, cuda_graph=True)
+        steps, _ = golden("gpt2_small_lora_c1_50.txt")
+        assert len(steps) == 50
+        worst = 0.0
+        for i, (ref_loss, ref_gnorm, with_grad, total) in enumerate(steps):
+            loss = tr.step_numpy(tr.next_synthetic_batch())
+            worst = max(worst, abs(loss - ref_loss) / ref_loss)
+            assert abs(loss - ref_loss) / ref_loss < 1e-3, (i, loss, ref_loss)
+            assert (tr.num_with_grad, tr.num_trainable) == (with_grad, total)
+        print("worst relative loss error", worst)
+        tr.close()
+    finally:
+        hostlib.mft_host_set_gemm_precision(0)
+
+
 def test_trainer_cuda_graph_replay_matches_reference_50_steps():
     """Steps 0-1 run eagerly, step 2 is captured, steps 3.. are graph replays: the trajectory must not notice."""
     from mobilefinetuner_b200.trainer import Trainer
