@@ -210,6 +210,9 @@ int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64_t rows, in
  * 1 = 3xTF32 split, fp32-accurate (used by the exact-mode parity tests; also selected by MFT_USE_TENSOR_CORES=0).
  * Returns the previous setting. */
 int mft_attention_precise(int enable);
+/* 1: head_dim-64 attention runs on bf16 operands (mma.sync m16n8k16, fp32 accumulate and softmax) — the attention side of the
+ * bf16 GEMM operand mode; ignored while the precise mode is on. Returns the previous setting. No reference counterpart. */
+int mft_attention_bf16(int enable);
 int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
                              int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
                              int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,

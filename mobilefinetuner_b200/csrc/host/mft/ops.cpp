@@ -66,7 +66,10 @@ bool emit_bf16_operands() {
     const char* e = std::getenv("MFT_BF16_EMIT");      // read per call: tests flip it to compare against the cast-on-demand path
     return !(e && e[0] == '0');
 }
-void set_gemm_precision(int bf16) { g_precision = bf16 ? 1 : 0; }
+void set_gemm_precision(int bf16) {
+    g_precision = bf16 ? 1 : 0;
+    mft_attention_bf16(g_precision);      // attention follows the GEMM operand mode
+}
 
 bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k) {
     static const bool tc_off = [] { const char* e = std::getenv("MFT_USE_TENSOR_CORES"); return e && e[0] == '0'; }();

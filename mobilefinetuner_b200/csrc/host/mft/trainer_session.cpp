@@ -384,7 +384,7 @@ extern "C" void mft_trainer_enable_graph(mft_trainer* t, int enable) {
     }
     t->graph_enabled = on;
 }
-extern "C" void mft_host_set_gemm_precision(int bf16) { ops::internal::set_gemm_precision(bf16); }
+extern "C" void mft_host_set_gemm_precision(int bf16) { ops::internal::set_gemm_precision(bf16); }   // also switches attention (ops.cpp)
 extern "C" int mft_host_gemm_precision(void) { return ops::internal::gemm_precision(); }
 extern "C" void mft_trainer_set_lr(mft_trainer* t, float lr) {
     if (!t || !t->opt) return;

@@ -152,6 +152,33 @@ def test_lora_tn_streaming_kernel(capi, T, q, r, rq):
     assert rel(outs[0], e if rq else e.T) < FP32_TOL
 
 
+BF16_TOL = 1e-2   # bf16 inputs (8-bit mantissa), fp32 accumulate (SURVEY §8c)
+
+
+@pytest.mark.parametrize("B,H,S", [(2, 4, 128), (1, 3, 200), (8, 16, 512), (1, 2, 64)])
+def test_attention_bf16_operand_mode(capi, B, H, S):
+    """head_dim 64 on mma.sync m16n8k16 with bf16 operands (fp32 accumulate / softmax), fused-qkv layout, plus its bf16 ctx copy."""
+    Hd, Cc = 64, H * 64
+    rng = np.random.default_rng(B * 100 + S)
+    qkv = rng.standard_normal((B, S, 3 * Cc)).astype(np.float32)
+    d = dev(qkv)
+    ctx = torch.full((B, S, Cc), float("nan"), device="cuda")
+    ctx16 = torch.zeros((B, S, Cc), dtype=torch.bfloat16, device="cuda")
+    prev_p, prev_b = capi.lib.mft_attention_precise(0), capi.lib.mft_attention_bf16(1)
+    try:
+        base = d.data_ptr()
+        capi.check(capi.lib.mft_causal_attention_fwd_ex(base, base + 4 * Cc, base + 8 * Cc, ctx.data_ptr(), ctx16.data_ptr(), B, H, S, Hd,
+                                                       S * 3 * Cc, 3 * Cc, Hd, S * 3 * Cc, 3 * Cc, Hd, S * Cc, Cc, Hd, 1.0 / np.sqrt(Hd), 0, None),
+                   "mft_causal_attention_fwd_ex")
+        torch.cuda.synchronize()
+    finally:
+        capi.lib.mft_attention_precise(prev_p); capi.lib.mft_attention_bf16(prev_b)
+    q, k, v = (qkv[..., i * Cc:(i + 1) * Cc].reshape(B, S, H, Hd).transpose(0, 2, 1, 3) for i in range(3))
+    e = O.causal_attention_fwd(q, k, v, 1.0 / np.sqrt(Hd)).transpose(0, 2, 1, 3).reshape(B, S, Cc)
+    assert rel(ctx, e) < BF16_TOL
+    assert torch.equal(ctx16, ctx.to(torch.bfloat16))
+
+
 # ----------------------------------------------------------------------------- tcgen05 TF32 path
 @pytest.mark.parametrize("m,n,k", [(128, 256, 32), (128, 64, 64), (512, 768, 768), (512, 2304, 768), (300, 200, 100),
                                    (2048, 3072, 768), (129, 257, 36), (4096, 1024, 4096), (64, 64, 4096)])
@@ -242,7 +269,6 @@ def test_gemm_tc_batched_and_pitched(capi):
     assert rel(cc, a_full[:, :k].astype(np.float64) @ bmat.astype(np.float64).T) < TF32_TOL
 
 
-BF16_TOL = 1e-2   # bf16 inputs (8-bit mantissa), fp32 accumulate (SURVEY §8c)
 
 
 @pytest.mark.parametrize("m,n,k,r", [(512, 768, 768, 0), (4096, 1024, 1024, 16), (300, 200, 104, 8), (256, 50257, 768, 0),
