@@ -188,7 +188,8 @@ int mft_layernorm_bwd_static(const float* x, const float* gamma, const float* gy
                              float* dbeta, int64_t rows, int64_t dim, float eps, mft_stream_t stream);
 /* RMSNorm with (1+w) scale, double-precision row statistics: y = x * rsqrt(mean(x^2)+eps) * (1+w)
  * (ops::rms_norm core/ops.cpp:1489-1537, RMSNormBackward core/backward_functions.cpp:483-523).
- * plus_one = 0 gives rms_norm_affine (y = x_hat * w). */
+ * plus_one = 0 gives rms_norm_affine (y = x_hat * w). dw may be NULL in mft_rmsnorm_bwd (frozen weight): only dx is
+ * produced and no workspace is needed. */
 int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t rows, int64_t dim, float eps,
                     int plus_one, mft_stream_t stream);
 int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,

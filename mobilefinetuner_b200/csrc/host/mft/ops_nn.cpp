@@ -151,10 +151,13 @@ public:
         TensorPtr gy = contiguous(gy_in);
         const int64_t dim = x_->shape().back(), rows = x_->numel() / dim;
         auto gx = new_like(x_);
-        auto gw = Tensor::make(w_->shape(), kFloat32);
-        size_t wsb = mft_norm_bwd_workspace_bytes(rows, dim);
-        mft_rt::check(mft_rmsnorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), gw->dev_f32_out(), rows, dim,
-                                      eps_, plus_one_, mft_rt::workspace(wsb), wsb, st()), "mft_rmsnorm_bwd");
+        // the reference always accumulates dW (core/backward_functions.cpp:483-523); with a frozen weight (LoRA runs) nobody reads
+        // it, so the column reduction and its second stage are skipped, like the LayerNorm case above
+        const bool wg = wants_grad(w_);
+        TensorPtr gw = wg ? Tensor::make(w_->shape(), kFloat32) : nullptr;
+        size_t wsb = wg ? mft_norm_bwd_workspace_bytes(rows, dim) : 0;
+        mft_rt::check(mft_rmsnorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr, rows, dim,
+                                      eps_, plus_one_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_rmsnorm_bwd");
         return {gx, gw};
     }
 private:

@@ -1,6 +1,7 @@
 // LayerNorm / RMSNorm(1+w) / softmax: one warp per row, row cached in registers (one HBM read),
 // warp-shuffle reductions, 128-bit accesses. Weight-gradient column sums go through per-CTA partials
 // in caller-provided scratch and a fixed-order second stage (deterministic, no atomics).
+#include <algorithm>
 #include "common.cuh"
 
 namespace mft {
@@ -310,9 +311,10 @@ rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
             double we = plus_one ? 1.0 + double(w[i]) : double(w[i]);
             double g = gr[i], v = xr[i];
             gx[r * dim + i] = float(g * we * inv - v * coeff * dot);
-            my[i] += float(g * v * inv);
+            if (partial) my[i] += float(g * v * inv);
         }
     }
+    if (!partial) return;          // frozen weight: only dx was wanted (uniform over the grid)
     __syncthreads();
     for (int i = threadIdx.x; i < dim; i += blockDim.x) {
         float s = 0.f;
@@ -520,9 +522,9 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
                                int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
                                mft_stream_t stream) {
     if (dim == 0) return 0;
-    if (!x || !w || !gy || !gx || !dw) return set_error(1, "mft_rmsnorm_bwd: null pointer");
-    if (rows == 0) return mft_fill(dw, dim, 0.f, stream);
-    if (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim))
+    if (!x || !w || !gy || !gx) return set_error(1, "mft_rmsnorm_bwd: null pointer");
+    if (rows == 0) return dw ? mft_fill(dw, dim, 0.f, stream) : 0;
+    if (dw && (!workspace || workspace_bytes < mft_norm_bwd_workspace_bytes(rows, dim)))
         return set_error(1, "mft_rmsnorm_bwd: workspace too small");
     if (size_t(kNormWarps) * dim * sizeof(float) > 200 * 1024) return set_error(1, "mft_rmsnorm_bwd: dim %lld too large", (long long)dim);
     cudaStream_t st = as_stream(stream);
@@ -531,12 +533,14 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
         cudaFuncSetAttribute(rmsnorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
-    int parts = norm_bwd_ctas(rows);
-    float* partial = static_cast<float*>(workspace);
+    int parts = dw ? norm_bwd_ctas(rows) : int(std::min<int64_t>(ceil_div(rows, kNormWarps), int64_t(kNumSMs) * 8));
+    float* partial = dw ? static_cast<float*>(workspace) : nullptr;     // dw == NULL (frozen weight): dx only, no second stage
     rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
         x, w, gy, gx, partial, rows, int(dim), eps, plus_one);
-    norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
-    add_launches(1);
+    if (dw) {
+        norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
+        add_launches(1);
+    }
     MFT_CHECK_LAUNCH("mft_rmsnorm_bwd");
     return 0;
 }
