@@ -192,6 +192,9 @@ int mft_layernorm_bwd_static(const float* x, const float* gamma, const float* gy
  * produced and no workspace is needed. */
 int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t rows, int64_t dim, float eps,
                     int plus_one, mft_stream_t stream);
+/* same, plus a bf16 copy of y (NULL = off; row pitch ld_bf16 >= dim) for the bf16 GEMM operand mode; no reference counterpart */
+int mft_rmsnorm_fwd_ex(const float* x, const float* w, float* y, void* y_bf16, int64_t ld_bf16, int64_t rows, int64_t dim,
+                       float eps, int plus_one, mft_stream_t stream);
 int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,
                     int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
                     mft_stream_t stream);

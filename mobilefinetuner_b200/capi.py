@@ -86,6 +86,7 @@ SIGNATURES = {
     "mft_layernorm_bwd_ex": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, vp, vp, i64, i64, f32, vp, sz, vp]),
     "mft_layernorm_bwd_static": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_rmsnorm_fwd": (C.c_int, [vp, vp, vp, i64, i64, f32, C.c_int, vp]),
+    "mft_rmsnorm_fwd_ex": (C.c_int, [vp, vp, vp, vp, i64, i64, i64, f32, C.c_int, vp]),
     "mft_rmsnorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, C.c_int, vp, sz, vp]),
     "mft_softmax_fwd": (C.c_int, [vp, vp, i64, i64, vp]),
     "mft_softmax_bwd": (C.c_int, [vp, vp, vp, i64, i64, vp]),

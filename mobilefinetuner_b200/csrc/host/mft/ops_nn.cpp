@@ -220,7 +220,10 @@ static TensorPtr rms_impl(const TensorPtr& x_in, const TensorPtr& weight, float 
     const int64_t dim = x->shape().back(), rows = x->numel() / std::max<int64_t>(dim, 1);
     if (weight->numel() != dim) throw TensorError("rms_norm: weight size mismatch");
     auto y = new_like(x);
-    mft_rt::check(mft_rmsnorm_fwd(x->dev_f32(), weight->dev_f32(), y->dev_f32_out(), rows, dim, eps, plus_one, st()), "mft_rmsnorm_fwd");
+    float* yp = y->dev_f32_out();
+    const Emit e = emit16(y, false);          // normalised activations feed the q/k/v, gate/up and lm_head products
+    if (e.ptr) mft_rt::check(mft_rmsnorm_fwd_ex(x->dev_f32(), weight->dev_f32(), yp, e.ptr, e.ld, rows, dim, eps, plus_one, st()), "mft_rmsnorm_fwd_ex");
+    else mft_rt::check(mft_rmsnorm_fwd(x->dev_f32(), weight->dev_f32(), yp, rows, dim, eps, plus_one, st()), "mft_rmsnorm_fwd");
     // the reference always registers a node for rms_norm (core/ops.cpp:1521-1524)
     if (autograd::Engine::instance().is_enabled()) {
         y->set_requires_grad(true);

@@ -268,7 +268,8 @@ namespace mft {
 // ---------------------------------------------------------------- RMSNorm (1+w), double statistics
 // One warp per row, generic over dim (row re-read hits L1); Gemma dims are 640 (hidden) and 256 (q/k norm).
 __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, float* __restrict__ y,
-                                   int64_t rows, int dim, float eps, int plus_one) {
+                                   int64_t rows, int dim, float eps, int plus_one,
+                                   __nv_bfloat16* __restrict__ y16, int64_t ld16) {   // y16 != NULL: bf16 copy of y
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -279,7 +280,9 @@ __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __r
         const float rms = float(sqrt(sq / double(dim) + double(eps)));
         for (int i = lane; i < dim; i += 32) {
             float sc = plus_one ? 1.0f + w[i] : w[i];
-            y[r * dim + i] = (xr[i] / rms) * sc;
+            const float o = (xr[i] / rms) * sc;
+            y[r * dim + i] = o;
+            if (y16) y16[r * ld16 + i] = __float2bfloat16_rn(o);
         }
     }
 }
@@ -513,8 +516,20 @@ extern "C" int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t
                                int plus_one, mft_stream_t stream) {
     if (rows == 0 || dim == 0) return 0;
     if (!x || !w || !y) return set_error(1, "mft_rmsnorm_fwd: null pointer");
-    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one);
+    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one, nullptr, 0);
     MFT_CHECK_LAUNCH("mft_rmsnorm_fwd");
+    return 0;
+}
+
+// same, plus a bf16 copy of y (row pitch ld_bf16 >= dim) for the bf16 GEMMs that consume the normalised activations
+extern "C" int mft_rmsnorm_fwd_ex(const float* x, const float* w, float* y, void* y_bf16, int64_t ld_bf16, int64_t rows, int64_t dim,
+                                  float eps, int plus_one, mft_stream_t stream) {
+    if (rows == 0 || dim == 0) return 0;
+    if (!x || !w || !y) return set_error(1, "mft_rmsnorm_fwd_ex: null pointer");
+    if (y_bf16 && ld_bf16 < dim) return set_error(1, "mft_rmsnorm_fwd_ex: bf16 pitch smaller than dim");
+    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one,
+                                                                                   static_cast<__nv_bfloat16*>(y_bf16), ld_bf16);
+    MFT_CHECK_LAUNCH("mft_rmsnorm_fwd_ex");
     return 0;
 }
 
