@@ -108,6 +108,15 @@ int mft_transpose2d(const float* in, int64_t ldi, float* out, int64_t ldo, int64
                     int64_t batch, int64_t stride_in, int64_t stride_out, mft_stream_t stream);
 /* out[b,d2,d1,d3] = in[b,d1,d2,d3]  (ops::permute {0,2,1,3}, core/ops.cpp:886-961; its own inverse). */
 int mft_permute0213(const float* in, float* out, int64_t d0, int64_t d1, int64_t d2, int64_t d3, mft_stream_t stream);
+/* General permute (ops::permute's index loop, core/ops.cpp:886-961) for the layouts without a fast path: out is dense with
+ * shape out_shape[ndim]; src_stride[i] is the INPUT stride (elements) of output axis i. ndim <= 8. */
+int mft_permute_nd(const float* in, float* out, int32_t ndim, const int64_t* out_shape, const int64_t* src_stride, mft_stream_t stream);
+/* Data-preparation helpers that the reference runs as host loops: ops::cast fp32<->int32 (core/tensor.cpp cast,
+ * truncation toward zero), create_causal_mask's lower-triangular ones (core/ops.cpp:1976-1992), and the one-hot rows
+ * behind nll_loss / cross_entropy_loss (core/ops.cpp:1177-1402; targets int32, or float-coded when target_is_i32 = 0). */
+int mft_cast_i32(const void* in, void* out, int64_t n, int to_i32, mft_stream_t stream);
+int mft_tril_ones(float* out, int64_t S, mft_stream_t stream);
+int mft_one_hot(const void* target, int target_is_i32, float* out, int64_t N, int64_t C, mft_stream_t stream);
 
 /* ------------------------------------------------------------------ elementwise (HBM streaming)
  * mft_binary: out = a (op) b with numpy broadcasting of b over a described by (outer, mid, inner):

@@ -65,6 +65,10 @@ SIGNATURES = {
     "mft_gemm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]),
     "mft_transpose2d": (C.c_int, [vp, i64, vp, i64, i64, i64, i64, i64, i64, vp]),
     "mft_permute0213": (C.c_int, [vp, vp, i64, i64, i64, i64, vp]),
+    "mft_permute_nd": (C.c_int, [vp, vp, i32, C.POINTER(i64), C.POINTER(i64), vp]),
+    "mft_cast_i32": (C.c_int, [vp, vp, i64, C.c_int, vp]),
+    "mft_tril_ones": (C.c_int, [vp, i64, vp]),
+    "mft_one_hot": (C.c_int, [vp, C.c_int, vp, i64, i64, vp]),
     "mft_binary": (C.c_int, [C.c_int, vp, vp, vp, i64, i64, i64, C.c_int, i64, vp]),
     "mft_affine": (C.c_int, [vp, vp, i64, f32, f32, vp]),
     "mft_accumulate": (C.c_int, [vp, vp, i64, vp]),

@@ -181,18 +181,13 @@ TensorPtr permute(const TensorPtr& t_in, const std::vector<int>& dims_in) {
         out = Tensor::make(so, kFloat32);
         mft_rt::check(mft_permute0213(t->dev_f32(), out->dev_f32_out(), 1, s[0], s[1], s[2], st), "mft_permute0213");
     } else {
-        // rare general case: staged through the host mirror (not on the training path)
+        // general case: one gather kernel (no host staging)
+        if (nd > 8) throw TensorError("permute: more than 8 dimensions are not supported");
         out = Tensor::make(so, kFloat32);
-        const float* src = t->data<float>();
-        float* dst = out->data<float>();
-        std::vector<int64_t> stride(nd, 1), idx(nd, 0);
+        std::vector<int64_t> stride(nd, 1), src_stride(nd);
         for (int i = nd - 2; i >= 0; --i) stride[i] = stride[i + 1] * s[i + 1];
-        for (int64_t o = 0; o < out->numel(); ++o) {
-            int64_t off = 0;
-            for (int i = 0; i < nd; ++i) off += idx[i] * stride[dims[i]];
-            dst[o] = src[off];
-            for (int i = nd - 1; i >= 0; --i) { if (++idx[i] < so[i]) break; idx[i] = 0; }
-        }
+        for (int i = 0; i < nd; ++i) src_stride[i] = stride[dims[i]];
+        mft_rt::check(mft_permute_nd(t->dev_f32(), out->dev_f32_out(), nd, so.data(), src_stride.data(), st), "mft_permute_nd");
     }
     track(out, {t_in}, std::make_shared<PermuteBackward>(inv));
     return out;

@@ -84,17 +84,17 @@ TensorPtr clamp(const TensorPtr& t_in, float lo, float hi) {
     return out;
 }
 
-// core/tensor.cpp / core/ops.cpp cast: fp32 <-> int32 on the host mirror (data preparation only, never per step);
+// core/tensor.cpp / core/ops.cpp cast: fp32 <-> int32 (truncation), one device kernel;
 // fp16 storage is not used by the fp32 training path and is rejected loudly.
 TensorPtr cast(const TensorPtr& t, DType target) {
     if (!t) throw TensorError("cast: null tensor");
     if (t->dtype() == target) return t->clone();
     if (target == kFloat16 || t->dtype() == kFloat16) throw TensorError("cast: float16 tensors are not supported by the B200 fp32/TF32 path");
-    auto out = std::make_shared<Tensor>(t->shape(), target, t->device());
-    const int64_t n = t->numel();
-    if (t->dtype() == kFloat32 && target == kInt32) { const float* s = t->data<float>(); int32_t* d = out->data<int32_t>(); for (int64_t i = 0; i < n; ++i) d[i] = int32_t(s[i]); }
-    else if (t->dtype() == kInt32 && target == kFloat32) { const int32_t* s = t->data<int32_t>(); float* d = out->data<float>(); for (int64_t i = 0; i < n; ++i) d[i] = float(s[i]); }
-    else throw TensorError("cast: unsupported dtype pair");
+    const bool to_i32 = t->dtype() == kFloat32 && target == kInt32;
+    if (!to_i32 && !(t->dtype() == kInt32 && target == kFloat32)) throw TensorError("cast: unsupported dtype pair");
+    TensorPtr src = t->dtype() == kFloat32 ? contiguous(t) : t;
+    auto out = Tensor::make(t->shape(), target);
+    mft_rt::check(mft_cast_i32(src->dev(), out->dev_out(), t->numel(), to_i32 ? 1 : 0, st()), "mft_cast_i32");
     return out;
 }
 
@@ -108,23 +108,25 @@ TensorPtr uniform(const std::vector<int64_t>& shape, float low, float high, DTyp
 }
 
 // core/ops.cpp dropout: inverted dropout with a host-generated keep mask (LoRA dropout is never applied by
-// LoRALinear::forward in the reference — SURVEY.md Appendix B10 — so this is off the training path).
+// LoRALinear::forward in the reference — SURVEY.md Appendix B10 — so this is off the training path). The uniform draws
+// are initialisation data produced by the host RNG like every other random fill; the thresholding runs on the device.
 TensorPtr dropout(const TensorPtr& t, float p, bool training) {
     if (!training || p <= 0.0f) return t;
     if (p >= 1.0f) return mul(t, 0.0f);
-    auto mask = uniform(t->shape(), 0.f, 1.f);
-    float* m = mask->data<float>();
-    const float keep = 1.0f / (1.0f - p);
-    for (int64_t i = 0; i < mask->numel(); ++i) m[i] = m[i] >= p ? keep : 0.0f;
-    return mul(t, mask);
+    TensorPtr keep_mask;
+    {
+        NoGrad ng;             // the mask is data: u >= p ? 1/(1-p) : 0, thresholded on the device
+        keep_mask = mul(ge(uniform(t->shape(), 0.f, 1.f), full(t->shape(), p)), 1.0f / (1.0f - p));
+    }
+    return mul(t, keep_mask);
 }
 
 // core/ops.cpp:1976-1992 / 1994-2070
 TensorPtr create_causal_mask(int seq_len, DType dtype, Device device) {
-    auto mask = zeros({seq_len, seq_len}, dtype, device);
-    float* d = mask->data<float>();
-    for (int i = 0; i < seq_len; ++i)
-        for (int j = 0; j <= i; ++j) d[int64_t(i) * seq_len + j] = 1.0f;
+    (void)device;
+    if (dtype != kFloat32) throw TensorError("create_causal_mask: float32 only");
+    auto mask = Tensor::make({seq_len, seq_len}, kFloat32);
+    mft_rt::check(mft_tril_ones(mask->dev_f32_out(), seq_len, st()), "mft_tril_ones");
     return mask;
 }
 TensorPtr apply_mask(const TensorPtr& input, const TensorPtr& mask, float mask_value) {
@@ -142,12 +144,8 @@ TensorPtr mse_loss(const TensorPtr& input, const TensorPtr& target, const std::s
     return reduction == "sum" ? sum(sq) : mean(sq);
 }
 static TensorPtr one_hot_from_targets(const TensorPtr& target, int64_t N, int64_t Cn) {
-    auto oh = zeros({N, Cn});
-    float* d = oh->data<float>();
-    for (int64_t i = 0; i < N; ++i) {
-        int64_t c = target->dtype() == kInt32 ? target->data<int32_t>()[i] : int64_t(target->data<float>()[i]);
-        if (c >= 0 && c < Cn) d[i * Cn + c] = 1.0f;
-    }
+    auto oh = Tensor::make({N, Cn}, kFloat32);
+    mft_rt::check(mft_one_hot(target->dev(), target->dtype() == kInt32 ? 1 : 0, oh->dev_f32_out(), N, Cn, st()), "mft_one_hot");
     return oh;
 }
 TensorPtr nll_loss(const TensorPtr& input, const TensorPtr& target, const std::string& reduction) {

@@ -26,6 +26,7 @@ struct Arena {
     char* base = nullptr;
     size_t size = 0, off = 0, high = 0;
     bool enabled = false;
+    int users = 0;             // live trainers sharing the slab
 } g_arena;
 int g_persistent_depth = 0;
 
@@ -128,6 +129,23 @@ void arena_enable(size_t bytes) {
     g_arena.size = bytes;
     g_arena.off = 0;
     g_arena.enabled = true;
+}
+// Trainers share one slab: they all enqueue on the one compute stream and nothing in the arena outlives a step, so a
+// reset by one trainer only recycles memory whose readers are already ordered before the next writer. The slab cannot move
+// while a trainer is alive (its captured graphs and gradients point into it).
+void arena_acquire(size_t bytes) {
+    if (g_arena.users > 0 && g_arena.base && g_arena.size < bytes)
+        fail("mft step arena: a live trainer uses a " + std::to_string(g_arena.size >> 20) + " MiB arena; a second trainer asked for " +
+             std::to_string(bytes >> 20) + " MiB. Destroy the first trainer or create the larger one first.");
+    arena_enable(bytes);
+    ++g_arena.users;
+}
+void arena_release() {
+    if (g_arena.users > 0) --g_arena.users;
+    if (g_arena.users == 0) {              // ops outside a trainer go back to the caching allocator
+        g_arena.enabled = false;
+        g_arena.off = 0;
+    }
 }
 void arena_reset() { g_arena.off = 0; }
 bool arena_active() { return g_arena.enabled && g_persistent_depth == 0; }

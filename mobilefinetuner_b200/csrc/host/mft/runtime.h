@@ -28,6 +28,8 @@ void pinned_free(void* p);
 // arena_reset() rewinds; persistent allocations (parameters, optimizer state, cached weight shadows) are made
 // under a PersistentScope and bypass it.
 void arena_enable(size_t bytes);
+void arena_acquire(size_t bytes);                // ref-counted enable (one per trainer); refuses to move a slab that is in use
+void arena_release();                            // last release switches the arena off
 void arena_reset();
 bool arena_active();
 size_t arena_high_water();

@@ -69,6 +69,8 @@ struct mft_trainer {
     cudaGraphExec_t graph_exec[3] = {nullptr, nullptr, nullptr};
     int eager_runs[3] = {0, 0, 0};
     int64_t phase_launches[3] = {0, 0, 0};
+    cudaEvent_t slots_event[2] = {nullptr, nullptr};   // recorded after each eager upload of the pinned slot table
+    bool capturing = false;
     bool graph_enabled = true;     // runtime switch (mft_trainer_enable_graph); only effective when cfg.use_cuda_graph
     int eager_steps = 0;
 };
@@ -204,6 +206,8 @@ void forward_backward(mft_trainer* t) {
 // per-step host data and can be replayed from a CUDA graph. `packed`: gradients are read from the all-reduced bucket.
 const mft_tensor_slot* upload_slots(mft_trainer* t, bool packed) {
     const size_t n = t->trainable.size();
+    // the previous step's upload may still be reading the pinned table (step_device never synchronises)
+    if (t->slots_event[packed] && !t->capturing) cudaEventSynchronize(t->slots_event[packed]);
     for (size_t i = 0; i < n; ++i) {
         mft_tensor_slot& s = t->slots_host[packed][i];
         std::memset(&s, 0, sizeof(s));
@@ -216,6 +220,10 @@ const mft_tensor_slot* upload_slots(mft_trainer* t, bool packed) {
     }
     // one pinned table per variant: the async upload (or its graph memcpy node) reads the host copy when it executes
     mft_rt::h2d(t->slots_dev[packed], t->slots_host[packed], n * sizeof(mft_tensor_slot));
+    if (!t->capturing) {
+        if (!t->slots_event[packed]) cudaEventCreateWithFlags(&t->slots_event[packed], cudaEventDisableTiming);
+        cudaEventRecord(t->slots_event[packed], static_cast<cudaStream_t>(mft_rt::stream()));
+    }
     return static_cast<const mft_tensor_slot*>(t->slots_dev[packed]);
 }
 
@@ -236,6 +244,16 @@ void update_phase(mft_trainer* t, bool packed) {
     for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
 }
 
+// A replayed update phase (0 = whole step, 2 = update) writes parameters and moments on the device without running the host
+// body that normally records it: note the write here, so host mirrors are re-read and cached shadows are versioned.
+void mark_state_written(mft_trainer* t) {
+    for (size_t i = 0; i < t->trainable.size(); ++i) {
+        (void)t->trainable[i]->dev_f32_mut();
+        (void)t->m[i]->dev_f32_mut();
+        (void)t->v[i]->dev_f32_mut();
+    }
+}
+
 // Runs one phase eagerly, or (cfg.use_cuda_graph) captures it into a CUDA graph after two eager runs and replays it.
 // The step arena makes every intermediate address identical from step to step, which is what makes replay valid.
 template <typename Body>
@@ -244,17 +262,21 @@ void run_phase(mft_trainer* t, int phase, Body body) {
     const bool want_graph = t->cfg.use_cuda_graph && t->graph_enabled;
     if (want_graph && t->graph_exec[phase]) {
         if (cudaGraphLaunch(t->graph_exec[phase], st) != cudaSuccess) mft_rt::fail("cudaGraphLaunch failed");
+        if (phase != 1) mark_state_written(t);
         return;
     }
     const int64_t before = mft_launch_count();
     if (want_graph && t->eager_runs[phase] >= 2) {
         cudaGraph_t graph = nullptr;
         if (cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) != cudaSuccess) mft_rt::fail("cudaStreamBeginCapture failed");
+        t->capturing = true;
         try { body(); } catch (...) {
+            t->capturing = false;
             cudaStreamEndCapture(st, &graph);
             if (graph) cudaGraphDestroy(graph);
             throw;
         }
+        t->capturing = false;
         if (cudaStreamEndCapture(st, &graph) != cudaSuccess || !graph) mft_rt::fail("cudaStreamEndCapture failed (an operation in the step is not capturable)");
         cudaGraphExec_t exec = nullptr;
         cudaError_t e = cudaGraphInstantiate(&exec, graph, 0);
@@ -263,6 +285,7 @@ void run_phase(mft_trainer* t, int phase, Body body) {
         t->graph_exec[phase] = exec;
         t->phase_launches[phase] = mft_launch_count() - before;
         if (cudaGraphLaunch(exec, st) != cudaSuccess) mft_rt::fail("cudaGraphLaunch failed");
+        if (phase != 1) mark_state_written(t);
         return;
     }
     body();
@@ -284,7 +307,7 @@ extern "C" int mft_trainer_create(const mft_trainer_config* cfg, mft_trainer** o
         (void)mft_rt::stream();
         build(t.get());
         const size_t mb = cfg->arena_mb > 0 ? size_t(cfg->arena_mb) : size_t(24) * 1024;
-        mft_rt::arena_enable(mb << 20);
+        mft_rt::arena_acquire(mb << 20);
         t->arena_on = true;
         mft_rt::sync();
         *out = t.release();
@@ -296,9 +319,11 @@ extern "C" void mft_trainer_destroy(mft_trainer* t) {
     if (!t) return;
     try { mft_rt::sync(); } catch (...) {}
     for (auto& g : t->graph_exec) if (g) cudaGraphExecDestroy(g);
-    for (int k = 0; k < 2; ++k) mft_rt::pinned_free(t->slots_host[k]);
+    for (int k = 0; k < 2; ++k) { mft_rt::pinned_free(t->slots_host[k]); if (t->slots_event[k]) cudaEventDestroy(t->slots_event[k]); }
     mft_rt::pinned_free(t->lr_host);
+    const bool had_arena = t->arena_on;
     delete t;
+    if (had_arena) mft_rt::arena_release();
 }
 
 extern "C" int mft_trainer_next_synthetic_batch(mft_trainer* t, int32_t* host_ids) {
@@ -341,6 +366,12 @@ extern "C" int64_t mft_trainer_grad_elems(mft_trainer* t) { return t ? t->grad_e
 extern "C" int mft_trainer_set_grad_bucket(mft_trainer* t, float* dev_bucket, int64_t elems) {
     if (!t || !dev_bucket) return fail("mft_trainer_set_grad_bucket: null argument");
     if (elems < t->grad_elems) return fail("mft_trainer_set_grad_bucket: bucket too small (%lld < %lld)", (long long)elems, (long long)t->grad_elems);
+    if (t->bucket != dev_bucket) {        // phases 1 and 2 bake the bucket address into their graphs: capture them again
+        for (int p = 1; p < 3; ++p) {
+            if (t->graph_exec[p]) { try { mft_rt::sync(); } catch (...) {} cudaGraphExecDestroy(t->graph_exec[p]); t->graph_exec[p] = nullptr; }
+            t->eager_runs[p] = 0;
+        }
+    }
     t->bucket = dev_bucket;
     t->bucket_elems = elems;
     return 0;

@@ -32,6 +32,17 @@ void add_launches(int n);
 
 constexpr int kNumSMs = 148;  // B200
 
+// Function attributes (dynamic shared-memory limit) are per device: `flags` is a per-call-site table indexed by the current
+// device, so a process that drives several GPUs sets the attribute on each of them once.
+constexpr int kMaxDevices = 64;
+inline bool first_use_on_device(bool (&flags)[kMaxDevices]) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return true;   // unknown: set it again, it is cheap
+    if (flags[dev]) return false;
+    flags[dev] = true;
+    return true;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -196,7 +196,6 @@ struct TcArgs {
     float alpha, beta;
     int tiles_m, tiles_n;
     int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
-    int debug;                 // MFT_GEMM_DEBUG bits (kernel experiments): 1 = no global stores, 2 = no smem staging either, 4 = no TMEM loads
 };
 
 // BF16 = false: fp32 operands in HBM, TF32 MMA (32 elements per 128-byte k-block, K = 8 per instruction).
@@ -432,9 +431,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                         for (int q = 0; q < 8; ++q) {
                             float4 gv;
-                            if (p.debug & 8) gv = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
-                            else if (p.debug & 16) gv = make_float4(gelu_tanh_fast(v[4 * q]), gelu_tanh_fast(v[4 * q + 1]), gelu_tanh_fast(v[4 * q + 2]), gelu_tanh_fast(v[4 * q + 3]));
-                            else gv = make_float4(gelu_tanh_f(v[4 * q]), gelu_tanh_f(v[4 * q + 1]), gelu_tanh_f(v[4 * q + 2]), gelu_tanh_f(v[4 * q + 3]));
+                            gv = make_float4(gelu_tanh_f(v[4 * q]), gelu_tanh_f(v[4 * q + 1]), gelu_tanh_f(v[4 * q + 2]), gelu_tanh_f(v[4 * q + 3]));
                             *reinterpret_cast<float4*>(rowp + ((q ^ (lane & 7)) << 4)) = gv;
                         }
                         fence_proxy_async_smem();
@@ -448,17 +445,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             for (int c0 = half * HC; c0 < (half + 1) * HC; c0 += 32) {
                 if (n0 + c0 >= p.n) break;               // warp-uniform
                 float v[32];
-                if (p.debug & 4) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = 0.f;
-                } else tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
-                if (p.debug & 2) continue;
+                tmem_ld32(tmem_base + (uint32_t(lg * 32) << 16) + uint32_t(as * BN + c0), v);
                 float4* srow = reinterpret_cast<float4*>(stg + lane * kEpiPitch);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) srow[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
                 __syncwarp();
                 const int col = n0 + c0 + c4 * 4;
-                if (p.debug & 1) { __syncwarp(); continue; }
                 if (vec_ok && col + 4 <= p.n && (!FUSED || (!abase && !xbase))) {
                     float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (p.bias) bb = __ldg(reinterpret_cast<const float4*>(p.bias + col));
@@ -748,7 +740,7 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     //  32-value row per thread run with no other warp to hide their latency, measured 125 us vs 81 us on fc_in)
     static const bool tma_gelu = [] { const char* e = getenv("MFT_GEMM_TMA_GELU"); return e && e[0] == '1'; }();
     const bool c_ok = !FUSED && p.beta == 0.f && aligned16(p.c) && (p.ldc & 3) == 0 && (p.batch == 1 || (p.stride_c & 3) == 0) &&
-                      (!p.gelu_out || (tma_gelu && aligned16(p.gelu_out)));
+                      (!p.gelu_out || (tma_gelu && !p.gelu_out_bf16 && aligned16(p.gelu_out)));   // the box path writes no bf16 copy
     static const bool tma_store_on = [] { const char* e = getenv("MFT_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
     bool tma_c = c_ok && tma_store_on;
     if (tma_c) {
@@ -765,13 +757,10 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     a.addend = p.addend; a.ld_addend = p.ld_addend; a.gelu_grad_x = p.gelu_grad_x; a.ld_gelu_grad_x = p.ld_gelu_grad_x;
     a.gelu16 = static_cast<__nv_bfloat16*>(p.gelu_out_bf16); a.ld_gelu16 = p.ld_gelu_out_bf16;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
-    static const int dbg = [] { const char* e = getenv("MFT_GEMM_DEBUG"); return e ? atoi(e) : 0; }();
-    a.debug = dbg;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set)) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
         if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
-        attr_set = true;
     }
     const int64_t units = ceil_div(a.tiles_m, CG) * a.tiles_n * a.batch;    // CTAs, or CTA pairs
     const int max_units = kNumSMs / CG;

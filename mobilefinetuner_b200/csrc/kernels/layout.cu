@@ -289,3 +289,70 @@ extern "C" int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, 
     MFT_CHECK_LAUNCH("mft_transpose_cast_bf16");
     return 0;
 }
+
+// ---------------------------------------------------------------- rare layouts / data preparation (device-side, no host loops)
+namespace mft {
+struct PermuteNd { int nd; int64_t out_shape[8]; int64_t src_stride[8]; };   // src_stride[i] = input stride of output axis i
+__global__ void permute_nd_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t n, PermuteNd p) {
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        int64_t rem = idx, off = 0;
+        for (int i = p.nd - 1; i >= 0; --i) { off += (rem % p.out_shape[i]) * p.src_stride[i]; rem /= p.out_shape[i]; }
+        out[idx] = in[off];
+    }
+}
+__global__ void cast_f32_i32_kernel(const float* __restrict__ in, int32_t* __restrict__ out, int64_t n) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = int32_t(in[i]);
+}
+__global__ void cast_i32_f32_kernel(const int32_t* __restrict__ in, float* __restrict__ out, int64_t n) {
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = float(in[i]);
+}
+__global__ void tril_ones_kernel(float* __restrict__ out, int64_t S) {
+    const int64_t n = S * S;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
+        out[i] = (i % S) <= (i / S) ? 1.0f : 0.0f;
+}
+// out[N, C] = 1 at (i, target[i]) when the class is in range, 0 elsewhere; targets int32 or float-coded
+__global__ void one_hot_kernel(const void* __restrict__ target, int target_is_i32, float* __restrict__ out, int64_t N, int64_t C) {
+    const int64_t n = N * C;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = i / C, c = i % C;
+        const int64_t t = target_is_i32 ? int64_t(static_cast<const int32_t*>(target)[r]) : int64_t(static_cast<const float*>(target)[r]);
+        out[i] = t == c ? 1.0f : 0.0f;
+    }
+}
+}  // namespace mft
+
+extern "C" int mft_permute_nd(const float* in, float* out, int32_t ndim, const int64_t* out_shape, const int64_t* src_stride, mft_stream_t stream) {
+    if (ndim < 1 || ndim > 8) return set_error(1, "mft_permute_nd: 1..8 dimensions");
+    if (!in || !out || !out_shape || !src_stride) return set_error(1, "mft_permute_nd: null pointer");
+    mft::PermuteNd p;
+    p.nd = ndim;
+    int64_t n = 1;
+    for (int i = 0; i < ndim; ++i) { p.out_shape[i] = out_shape[i]; p.src_stride[i] = src_stride[i]; n *= out_shape[i]; }
+    if (n == 0) return 0;
+    mft::permute_nd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(in, out, n, p);
+    MFT_CHECK_LAUNCH("mft_permute_nd");
+    return 0;
+}
+extern "C" int mft_cast_i32(const void* in, void* out, int64_t n, int to_i32, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_cast_i32: null pointer");
+    if (to_i32) mft::cast_f32_i32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(static_cast<const float*>(in), static_cast<int32_t*>(out), n);
+    else mft::cast_i32_f32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(static_cast<const int32_t*>(in), static_cast<float*>(out), n);
+    MFT_CHECK_LAUNCH("mft_cast_i32");
+    return 0;
+}
+extern "C" int mft_tril_ones(float* out, int64_t S, mft_stream_t stream) {
+    if (S == 0) return 0;
+    if (!out) return set_error(1, "mft_tril_ones: null pointer");
+    mft::tril_ones_kernel<<<stream_grid(S * S, 256), 256, 0, as_stream(stream)>>>(out, S);
+    MFT_CHECK_LAUNCH("mft_tril_ones");
+    return 0;
+}
+extern "C" int mft_one_hot(const void* target, int target_is_i32, float* out, int64_t N, int64_t C, mft_stream_t stream) {
+    if (N * C == 0) return 0;
+    if (!target || !out) return set_error(1, "mft_one_hot: null pointer");
+    mft::one_hot_kernel<<<stream_grid(N * C, 256), 256, 0, as_stream(stream)>>>(target, target_is_i32, out, N, C);
+    MFT_CHECK_LAUNCH("mft_one_hot");
+    return 0;
+}

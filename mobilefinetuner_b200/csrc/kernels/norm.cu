@@ -382,11 +382,9 @@ static int launch_ln_bwd(const float* x, const float* g, const float* gy, float*
         return 0;
     }
     size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
     layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps, addend, gx16, ld16);
     return 0;
 }
@@ -543,11 +541,9 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
         return set_error(1, "mft_rmsnorm_bwd: workspace too small");
     if (size_t(kNormWarps) * dim * sizeof(float) > 200 * 1024) return set_error(1, "mft_rmsnorm_bwd: dim %lld too large", (long long)dim);
     cudaStream_t st = as_stream(stream);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(rmsnorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
     int parts = dw ? norm_bwd_ctas(rows) : int(std::min<int64_t>(ceil_div(rows, kNormWarps), int64_t(kNumSMs) * 8));
     float* partial = dw ? static_cast<float*>(workspace) : nullptr;     // dw == NULL (frozen weight): dx only, no second stage
     rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
@@ -585,7 +581,6 @@ extern "C" int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64
 static __device__ __align__(256) float g_ln_bwd_static_scratch[MFT_LN_BWD_STATIC_FLOATS];
 
 namespace {
-constexpr int kMaxDevices = 64;
 float* g_ln_bwd_static_ptr[kMaxDevices] = {nullptr};   // device address of the array, resolved once per device
 }  // namespace
 

@@ -263,9 +263,9 @@ extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots
                                  float eps, float weight_decay, const float* grad_scale, int32_t* steps, mft_stream_t stream) {
     if (num_slots == 0) return 0;
     if (!slots || !steps || !lr) return set_error(1, "mft_adam_step_dev: null pointer");
+    if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step_dev: more than %d tensors", kOptMaxSlots);
     adam_advance_kernel<<<unsigned(ceil_div(num_slots, 256)), 256, 0, as_stream(stream)>>>(slots, num_slots, steps);
     add_launches(1);
-    if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step_dev: more than %d tensors", kOptMaxSlots);
     adam_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream)>>>(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
     MFT_CHECK_LAUNCH("mft_adam_step_dev");
     return 0;

@@ -226,3 +226,33 @@ def test_softmax_golden(capi, golden_ops):
     gx = torch.empty_like(x)
     capi.call("mft_softmax_bwd", y, dev(L("softmax_gy")), gx, rows, dim, None)
     assert rel(gx, L("softmax_gx")) < FP32_TOL
+
+
+# ----------------------------------------------------------------------------- rare layouts / data preparation on the device
+def test_permute_nd_cast_tril_one_hot(capi):
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((3, 4, 5, 6)).astype(np.float32)
+    for dims in [(3, 1, 0, 2), (2, 0, 3, 1), (1, 3, 2, 0)]:
+        e = np.ascontiguousarray(x.transpose(dims))
+        stride = [x.strides[d] // 4 for d in dims]
+        out = torch.empty(e.shape, device="cuda")
+        capi.call("mft_permute_nd", dev(x), out, 4, (C.c_int64 * 4)(*e.shape), (C.c_int64 * 4)(*stride), None)
+        assert rel(out, e) == 0
+    f = (rng.standard_normal(1000) * 50).astype(np.float32)
+    oi = torch.empty(1000, dtype=torch.int32, device="cuda")
+    capi.call("mft_cast_i32", dev(f), oi, 1000, 1, None)
+    assert np.array_equal(oi.cpu().numpy(), f.astype(np.int32))
+    of = torch.empty(1000, device="cuda")
+    capi.call("mft_cast_i32", oi, of, 1000, 0, None)
+    assert np.array_equal(of.cpu().numpy(), f.astype(np.int32).astype(np.float32))
+    m = torch.empty(37, 37, device="cuda")
+    capi.call("mft_tril_ones", m, 37, None)
+    assert np.array_equal(m.cpu().numpy(), np.tril(np.ones((37, 37), np.float32)))
+    t = rng.integers(-1, 12, 50).astype(np.int32)       # -1 and 11 are out of range: all-zero rows
+    oh = torch.empty(50, 11, device="cuda")
+    capi.call("mft_one_hot", torch.tensor(t).cuda(), 1, oh, 50, 11, None)
+    e = np.zeros((50, 11), np.float32)
+    for i, c in enumerate(t):
+        if 0 <= c < 11:
+            e[i, c] = 1
+    assert np.array_equal(oh.cpu().numpy(), e)

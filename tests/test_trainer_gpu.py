@@ -179,12 +179,17 @@ def test_trainer_cuda_graph_replay_matches_reference_50_steps():
     tr.close()
     tr = Trainer(2, 16, shape=TINY_GPT2, full_finetune=True, arena_mb=256, cuda_graph=True)
     run(tr, *golden("gpt2_full_tiny.txt"))
-    # the learning rate is read from device memory by the captured update: a schedule takes effect without a new capture
-    tr.set_lr(0.0)
+    # replayed steps keep updating the device copy: a checksum taken earlier must not be served from a stale host mirror
     before = [tr.param_checksum(i) for i in range(tr.num_trainable)]
     for _ in range(2):
         tr.step_numpy(tr.next_synthetic_batch())
-    assert before == [tr.param_checksum(i) for i in range(tr.num_trainable)]
+    moved = [tr.param_checksum(i) for i in range(tr.num_trainable)]
+    assert sum(a != b for a, b in zip(before, moved)) >= tr.num_with_grad
+    # the learning rate is read from device memory by the captured update: a schedule takes effect without a new capture
+    tr.set_lr(0.0)
+    for _ in range(2):
+        tr.step_numpy(tr.next_synthetic_batch())
+    assert moved == [tr.param_checksum(i) for i in range(tr.num_trainable)]
     tr.close()
 
 
@@ -209,6 +214,20 @@ def test_trainer_cuda_graph_gemma_and_split_phases():
     for i in range(a.num_trainable):
         assert a.param_checksum(i) == b.param_checksum(i)
     a.close(); b.close()
+
+
+def test_arena_is_released_with_the_last_trainer_and_cannot_move_under_a_live_one():
+    """The step arena is shared and ref-counted: ops outside a trainer fall back to the caching allocator once the last
+    trainer is gone, and a second trainer may not force a larger slab while the first one's graphs point into the old one."""
+    from mobilefinetuner_b200.trainer import Trainer, TrainerError
+    a = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=64)
+    with pytest.raises(TrainerError, match="arena"):
+        Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=128)
+    a.step_numpy(a.next_synthetic_batch())
+    a.close()
+    b = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=128)     # no live user: the slab may grow
+    b.step_numpy(b.next_synthetic_batch())
+    b.close()
 
 
 def test_data_parallel_two_ranks_equal_single_process():
