@@ -120,3 +120,64 @@ class DataParallelTrainer:
         if self.world > 1:
             dist.all_reduce(v, group=self.group)
         return float(v.item()) / self.world
+
+
+DP_CHECK_SHAPE = dict(model=0, n_layer=2, n_embd=64, n_head=4, vocab_size=503, n_positions=64)
+
+
+def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16):
+    """N ranks stepping their rows (forward/backward -> NCCL all-reduce of the bucket -> update) against ONE process
+    stepping the concatenated batch, on a small GPT-2 LoRA shape in the exact execution mode (fp32 SIMT GEMMs, 3xTF32
+    attention), so the only difference is summation order. Needs an initialised NCCL process group and the current
+    device set. Returns a dict (on every rank; `ok` is rank 0's verdict broadcast to all):
+    loss within 1e-4 relative per step, every trainable tensor within 1e-3 in sum|.|, replicas bit-identical."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from . import capi
+    from .trainer import Trainer
+    world, rank = dist.get_world_size(), dist.get_rank()
+    prev_tc, prev_at = capi.lib.mft_use_tensor_cores(0), capi.lib.mft_attention_precise(1)
+    try:
+        rng = np.random.default_rng(5)
+        batches = rng.integers(0, DP_CHECK_SHAPE["vocab_size"], (steps, per_rank * world, seq)).astype(np.int32)
+        lo, hi = shard_rows(per_rank * world, rank, world)
+        tr = Trainer(per_rank, seq, shape=DP_CHECK_SHAPE, lora_rank=8, lora_alpha=16.0, arena_mb=256, world_size=world, rank=rank,
+                     cuda_graph=graph)
+        dpt = DataParallelTrainer(tr)
+        losses = []
+        for s in range(steps):
+            ids = torch.from_numpy(batches[s, lo:hi].copy()).cuda()
+            dpt.step_device(ids.data_ptr())
+            losses.append(dpt.loss_mean())
+        sums = [tr.param_checksum(i) for i in range(tr.num_trainable)]
+        mine = torch.tensor([[c[1], c[2]] for c in sums], dtype=torch.float64, device="cuda")
+        ref0 = mine.clone()
+        dist.broadcast(ref0, 0)
+        replicas_equal = torch.tensor([1 if torch.equal(mine, ref0) else 0], device="cuda")
+        dist.all_reduce(replicas_equal, op=dist.ReduceOp.MIN)
+        with_grad = tr.num_with_grad
+        tr.close()
+        verdict = torch.zeros(3, dtype=torch.float64, device="cuda")     # ok, worst loss error, worst parameter error
+        if rank == 0:
+            one = Trainer(per_rank * world, seq, shape=DP_CHECK_SHAPE, lora_rank=8, lora_alpha=16.0, arena_mb=256)
+            worst_l = worst_p = 0.0
+            for s in range(steps):
+                l1 = one.step_numpy(batches[s])
+                worst_l = max(worst_l, abs(l1 - losses[s]) / abs(l1))
+            ok = one.num_with_grad == with_grad
+            for i, c in enumerate(sums):
+                n, _, sa1 = one.param_checksum(i)
+                ok = ok and n == c[0]
+                worst_p = max(worst_p, abs(sa1 - c[2]) / max(sa1, 1e-6))
+            one.close()
+            ok = ok and worst_l <= 1e-4 and worst_p <= 1e-3 and bool(replicas_equal.item())
+            verdict = torch.tensor([1.0 if ok else 0.0, worst_l, worst_p], dtype=torch.float64, device="cuda")
+        dist.broadcast(verdict, 0)
+        return {"ok": bool(verdict[0].item() == 1.0), "world": world, "steps": steps, "cuda_graph": bool(graph),
+                "worst_loss_rel_err": float(verdict[1].item()), "worst_param_rel_err": float(verdict[2].item()),
+                "replicas_bit_identical": bool(replicas_equal.item()), "last_loss": losses[-1],
+                "shape": "GPT-2 2 layers x 64, LoRA r8, %d x %d tokens per rank, exact fp32 mode" % (per_rank, seq)}
+    finally:
+        capi.lib.mft_use_tensor_cores(prev_tc)
+        capi.lib.mft_attention_precise(prev_at)

@@ -60,13 +60,7 @@ class TrainerError(RuntimeError):
     pass
 
 
-# BASELINE.json configs: model shapes only; batch/seq are chosen by the caller.
-MODEL_SHAPES = {
-    "gpt2-small": dict(model=0, n_layer=12, n_embd=768, n_head=12, vocab_size=50257, n_positions=1024),
-    "gpt2-medium": dict(model=0, n_layer=24, n_embd=1024, n_head=16, vocab_size=50257, n_positions=1024),
-    "gemma3-270m": dict(model=1, n_layer=18, n_embd=640, n_head=4, vocab_size=262144, n_positions=32768,
-                        intermediate=2048, kv_heads=1, head_dim=256, sliding_window=512),
-}
+from .shapes import MODEL_SHAPES  # noqa: E402,F401  (pure-Python table; re-exported for callers of this module)
 
 
 class Trainer:
