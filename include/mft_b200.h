@@ -237,6 +237,45 @@ int mft_causal_attention_fwd_ex(const float* q, const float* k, const float* v, 
                                 int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
                                 int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
                                 float scale, int32_t window, mft_stream_t stream);
+/* Grouped-query attention with a backward, forward and gradients without the [B,H,S,S] tensor: the whole chain of
+ * graph/gemma_model.cpp:481-505 — repeat_kv_heads (core/ops.cpp:2072-2149: query head h uses kv head h / (H/KV)), Q K^T,
+ * * scale, + causal / sliding mask (finite -1e10, j <= i and, for window > 0, i - j < window: graph/gemma_model.cpp:261-285),
+ * + key_bias[b, j] (the [B,1,1,S] padding mask; NULL = none), softmax (core/ops.cpp:1119-1175), P V — and its backward
+ * (MatmulBackward, SoftmaxBackward core/backward_functions.cpp:297-340, ScaleBackward :970-974, RepeatKVHeadsBackward
+ * :683-716 = sum over the group). q [B,S,H,Hd], k/v [B,S,KV,Hd], ctx [B,S,H,Hd] by (batch, seq, head) strides in elements
+ * (multiples of 4, 16-byte aligned bases); Hd in {16,32,64,128,256}. lse [B,H,S] receives the per-row log-sum-exp the
+ * backward needs (NULL when no backward will run); ctx_bf16 (NULL = off) is a bf16 copy with ctx's strides. With KV == H and
+ * head_dim 64 this is also the true-gradient attention of GPT-2 (core/memory_efficient_attention.cpp:92-162 has no backward).
+ * Precision follows mft_attention_precise. The backward is deterministic (no atomics); its workspace holds rowsum(dO*O) and,
+ * for grouped heads, the per-query-head dK / dV that a last kernel sums in head order. */
+int mft_gqa_attention_fwd(const float* q, const float* k, const float* v, const float* key_bias, float* ctx, float* lse, void* ctx_bf16,
+                          int32_t B, int32_t H, int32_t KV, int32_t S, int32_t Hd,
+                          int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                          int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                          int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                          float scale, int32_t window, mft_stream_t stream);
+size_t mft_gqa_attention_bwd_workspace_bytes(int32_t B, int32_t H, int32_t KV, int32_t S, int32_t Hd);
+/* dctx has ctx's strides; dq / (dk, dv) are written with their own strides (every element of the three is overwritten). */
+int mft_gqa_attention_bwd(const float* q, const float* k, const float* v, const float* key_bias, const float* ctx, const float* lse,
+                          const float* dctx, float* dq, float* dk, float* dv,
+                          int32_t B, int32_t H, int32_t KV, int32_t S, int32_t Hd,
+                          int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
+                          int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
+                          int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
+                          int64_t dq_stride_b, int64_t dq_stride_s, int64_t dq_stride_h,
+                          int64_t dkv_stride_b, int64_t dkv_stride_s, int64_t dkv_stride_h,
+                          float scale, int32_t window, void* workspace, size_t workspace_bytes, mft_stream_t stream);
+/* Per-head RMSNorm (1 + w) then interleaved-pair RoPE for the query AND key projections of a layer in one launch, on the
+ * projections' own [tokens, heads, Hd] layout (position of a row = token index % S): rms_norm core/ops.cpp:1489-1537 +
+ * apply_rope core/ops.cpp:2151-2225 as called by graph/gemma_model.cpp:383-420 (the permutes around them disappear).
+ * Either side may be NULL. do_norm = 0 applies RoPE only (DISABLE_QK_NORM=1). Backward for one tensor: inverse rotation
+ * (ApplyRoPEBackward core/backward_functions.cpp:718-763) then RMSNormBackward (:483-523) for dx; the norm weight's own
+ * gradient is not produced (use mft_rmsnorm_bwd + mft_rope when it trains). */
+int mft_qk_norm_rope_fwd(const float* q, const float* wq, float* yq, int64_t q_tokens, int32_t q_heads,
+                         const float* k, const float* wk, float* yk, int64_t k_tokens, int32_t k_heads,
+                         int32_t S, int32_t Hd, float eps, float theta, int do_norm, mft_stream_t stream);
+int mft_qk_norm_rope_bwd(const float* x, const float* w, const float* gy, float* gx, int64_t tokens, int32_t heads,
+                         int32_t S, int32_t Hd, float eps, float theta, int do_norm, mft_stream_t stream);
 /* Interleaved-pair RoPE on [B,H,S,Hd]: pair (2d,2d+1) rotated by pos*theta^(-2d/Hd)
  * (ops::apply_rope core/ops.cpp:2151-2225). inverse != 0 applies the transpose rotation
  * (ApplyRoPEBackward core/backward_functions.cpp:718-763). */

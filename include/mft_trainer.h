@@ -73,6 +73,18 @@ void mft_trainer_enable_graph(mft_trainer* t, int enable);
 void mft_host_set_gemm_precision(int bf16);
 int mft_host_gemm_precision(void);
 
+/* True-gradient mode (process-wide, off by default; MFT_TRUE_ATTN_GRAD=1 in the environment): GPT-2 attention gets a
+ * backward, so attn.qkv adapters / weights, ln_1 and wpe receive gradients, and `.grad` accumulates over backward calls. The
+ * default mode reproduces the reference, which cuts the graph at the qkv split (graph/gpt2_model.cpp:616-637), ships an
+ * attention without backward (core/memory_efficient_attention.cpp:165-182) and overwrites `.grad` on every backward
+ * (core/autograd_engine.cpp:243); the semantics matched here are pytorch_alignment/gpt2_lora_finetune.py:228-239. */
+void mft_host_set_true_gradients(int enable);
+int mft_host_true_gradients(void);
+/* Gradient accumulation (true-gradient mode only): forward + backward of one micro-batch whose gradients are ADDED to the
+ * sums kept since the last apply; mft_trainer_apply_accumulated() takes their mean, clips, runs Adam and clears them. */
+int mft_trainer_accumulate(mft_trainer* t, const int32_t* dev_ids);
+int mft_trainer_apply_accumulated(mft_trainer* t);
+
 /* Introspection for tests / reports. */
 int32_t mft_trainer_num_trainable(mft_trainer* t);
 int32_t mft_trainer_num_with_grad(mft_trainer* t);       /* tensors that received a gradient in the last step */

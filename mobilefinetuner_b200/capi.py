@@ -100,6 +100,11 @@ SIGNATURES = {
                                            i64, i64, i64, f32, i32, vp]),
     "mft_causal_attention_fwd_ex": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
                                            i64, i64, i64, f32, i32, vp]),
+    "mft_gqa_attention_fwd": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64, i64, i64, i64, f32, i32, vp]),
+    "mft_gqa_attention_bwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
+    "mft_gqa_attention_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 15 + [f32, i32, vp, sz, vp]),
+    "mft_qk_norm_rope_fwd": (C.c_int, [vp, vp, vp, i64, i32, vp, vp, vp, i64, i32, i32, i32, f32, f32, C.c_int, vp]),
+    "mft_qk_norm_rope_bwd": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, i32, f32, f32, C.c_int, vp]),
     "mft_rope": (C.c_int, [vp, vp, i64, i64, i64, f32, C.c_int, vp]),
     "mft_repeat_kv_fwd": (C.c_int, [vp, vp, i64, i64, i64, i64, i64, vp]),
     "mft_repeat_kv_bwd": (C.c_int, [vp, vp, i64, i64, i64, i64, i64, vp]),

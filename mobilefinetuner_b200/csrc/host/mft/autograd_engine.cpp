@@ -164,6 +164,11 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
         const bool leaf = !t->grad_node_ || t->grad_node_->backward_fn == nullptr;
         if (!(leaf || t->retains_grad())) continue;
         TensorPtr g = kv.second.grad;
+        if (accumulate_ && t->grad() && t->grad()->numel() == g->numel() && t->grad()->is_dense()) {   // grad += g
+            TensorPtr gc = contiguous(g);
+            mft_rt::check(mft_accumulate(t->grad()->dev_f32_mut(), gc->dev_f32(), gc->numel(), mft_rt::stream()), "mft_accumulate");
+            continue;
+        }
         // `.grad` may be scaled in place by the caller (host clip), so it must not alias another tensor's gradient
         if (!g->is_dense()) g = contiguous(g);
         else if (!kv.second.owned && g.use_count() > 2) g = g->clone();

@@ -70,6 +70,10 @@ public:
     // True when `t` takes part in the graph being built (has a producer node) or is a leaf that wants a gradient:
     // ops use it to skip gradients nobody will read.
     bool needs_grad(const TensorPtr& t) const;
+    // B200 extension, off by default: `.grad` of a leaf ACCUMULATES over run_backward calls (+=) instead of being
+    // overwritten (core/autograd_engine.cpp:243 overwrites, which breaks gradient accumulation — SURVEY Appendix B2).
+    void set_accumulate(bool on) { accumulate_ = on; }
+    bool accumulates() const { return accumulate_; }
 
 private:
     Engine() = default;
@@ -78,6 +82,7 @@ private:
     std::unordered_map<const Tensor*, TensorPtr> keepalive_;
     std::unordered_map<const Tensor*, Pending> pending_;
     bool enabled_ = true;
+    bool accumulate_ = false;
     void add_grad(const TensorPtr& target, const TensorPtr& g);
     std::vector<NodePtr> order_from(const std::vector<NodePtr>& roots) const;
 };

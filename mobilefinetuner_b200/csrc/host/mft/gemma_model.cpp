@@ -10,6 +10,7 @@
 #include <stdexcept>
 
 #include "ops.h"
+#include "ops_internal.h"
 #include "runtime.h"
 
 namespace ops {
@@ -219,6 +220,22 @@ TensorPtr GemmaModel::attention(const TensorPtr& x, GemmaBlockWeights& b, const 
     auto q = project(x, b.q_proj_lora, b.q_proj_weight);
     auto k = project(x, b.k_proj_lora, b.k_proj_weight);
     auto v = project(x, b.v_proj_lora, b.v_proj_weight);
+    const char* no_norm_env = std::getenv("DISABLE_QK_NORM");
+    const bool do_norm = !(no_norm_env && std::string(no_norm_env) == "1");
+    // Fused path (default): q/k RMSNorm + RoPE in one launch on the projections' own layout, then one grouped-query
+    // attention node with its own backward — no permutes, no repeated K/V, no [B,H,S,S] scores. Same values as the chain
+    // below, which stays for the cases the fused kernels do not cover (trained q/k norm weights, odd head sizes) and as
+    // MFT_GEMMA_FUSED_ATTN=0.
+    static const bool fused_on = [] { const char* e = std::getenv("MFT_GEMMA_FUSED_ATTN"); return !(e && e[0] == '0'); }();
+    if (fused_on && gqa_head_dim_supported(Hd) && H % KV == 0 && !internal::wants_grad(b.q_norm_weight) && !internal::wants_grad(b.k_norm_weight)) {
+        auto qk = qk_norm_rope(q, k, b.q_norm_weight, b.k_norm_weight, int(H), int(KV), int(Hd), config_.rms_norm_eps, theta, do_norm);
+        bool sliding = false;                         // which of the two cached masks the caller passed
+        { auto it = sliding_masks_.find(S); sliding = it != sliding_masks_.end() && it->second == base_mask; }
+        TensorPtr key_bias = pad_mask ? reshape(pad_mask, {B, S}) : nullptr;
+        auto fctx = gqa_attention(qk.first, qk.second, v, key_bias, int(H), int(KV), int(Hd), std::pow(config_.query_pre_attn_scalar, -0.5f),
+                                  sliding ? int(config_.sliding_window) : 0);
+        return project(fctx, b.o_proj_lora, b.o_proj_weight);
+    }
     q = permute(reshape(q, {B, S, H, Hd}), {0, 2, 1, 3});
     k = permute(reshape(k, {B, S, KV, Hd}), {0, 2, 1, 3});
     v = permute(reshape(v, {B, S, KV, Hd}), {0, 2, 1, 3});

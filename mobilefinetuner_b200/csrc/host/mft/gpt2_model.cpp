@@ -9,6 +9,7 @@
 #include <stdexcept>
 
 #include "ops.h"
+#include "ops_internal.h"
 #include "runtime.h"
 
 namespace ops {
@@ -206,7 +207,8 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr
         x1 = layer_norm(x, w.ln_1_weight, w.ln_1_bias, eps);
     }
     auto qkv = run_linear(x1, w.qkv_lin, w.lora_initialized, w.attn_qkv_weight, w.attn_qkv_bias);
-    auto ctx = gpt2_causal_attention(qkv, config_.n_head);
+    // default: the reference's stop-gradient attention; true-gradient mode: the same forward with a backward
+    auto ctx = internal::true_gradients() ? gpt2_causal_attention_with_grad(qkv, config_.n_head) : gpt2_causal_attention(qkv, config_.n_head);
     // MFT_FUSE_EPILOGUE bit 0: residual adds ride in the projections' epilogues; bit 1: GeluBackward rides in the epilogue of
     // fc_out's dX product. Off by default: with four epilogue warps per CTA the extra operand traffic and the tanh cost more
     // inside the GEMM than the separate streaming kernels do (profiles/README.md).

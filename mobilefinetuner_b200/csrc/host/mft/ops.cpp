@@ -71,6 +71,18 @@ void set_gemm_precision(int bf16) {
     mft_attention_bf16(g_precision);      // attention follows the GEMM operand mode
 }
 
+// True-gradient mode (off by default because the parity runs must reproduce the reference's quirks):
+// GPT-2 attention gets a backward (the reference severs the graph at the qkv split, graph/gpt2_model.cpp:616-637, and its
+// memory-efficient attention has no backward, core/memory_efficient_attention.cpp:165-182) and `.grad` accumulates over
+// backward() calls instead of being overwritten (core/autograd_engine.cpp:243) — the semantics
+// pytorch_alignment/gpt2_lora_finetune.py:228-239 trains with. MFT_TRUE_ATTN_GRAD=1 or mft_host_set_true_gradients(1).
+namespace {
+bool env_true_gradients() { const char* e = std::getenv("MFT_TRUE_ATTN_GRAD"); return e && e[0] == '1'; }
+bool g_true_gradients = [] { const bool on = env_true_gradients(); autograd::Engine::instance().set_accumulate(on); return on; }();
+}  // namespace
+bool true_gradients() { return g_true_gradients; }
+void set_true_gradients(bool on) { g_true_gradients = on; autograd::Engine::instance().set_accumulate(on); }
+
 bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k) {
     static const bool tc_off = [] { const char* e = std::getenv("MFT_USE_TENSOR_CORES"); return e && e[0] == '0'; }();
     return g_precision == 1 && !tc_off && m * n * k >= (int64_t(1) << 24) && m >= 64 && n >= 64 && k >= 32;

@@ -2,6 +2,7 @@
 // error behaviour: shape errors throw ops::TensorError / std::runtime_error). Every body enqueues hand-written
 // CUDA kernels through the C ABI (include/mft_b200.h); nothing computes on the host.
 #pragma once
+#include <utility>
 #include <memory>
 #include <string>
 #include <vector>
@@ -137,6 +138,17 @@ TensorPtr lm_head_tied(const TensorPtr& x, const TensorPtr& table);
 // GPT-2 attention over the fused qkv projection [B,S,3C] -> ctx [B,S,C]; forward only, result carries no
 // autograd history exactly like the reference's zeros+memcpy split (graph/gpt2_model.cpp:616-676).
 TensorPtr gpt2_causal_attention(const TensorPtr& qkv, int n_head);
+// Same attention with a backward (true-gradient mode, MFT_TRUE_ATTN_GRAD=1): one node from the fused qkv to ctx.
+TensorPtr gpt2_causal_attention_with_grad(const TensorPtr& qkv, int n_head);
+// Fused Gemma attention pieces (graph/gemma_model.cpp:383-514) on the projections' own [B,S,heads*Hd] layout:
+// per-head RMSNorm (1+w) + RoPE for q and k in one launch (norm weights frozen), and grouped-query attention
+// (causal; window > 0 = sliding; key_bias = additive [B,S] padding mask or null) with a real backward.
+struct GqaLayout { bool fused_qkv = false; int64_t q_off = 0, k_off = 0, v_off = 0; };
+bool gqa_head_dim_supported(int64_t Hd);
+std::pair<TensorPtr, TensorPtr> qk_norm_rope(const TensorPtr& q, const TensorPtr& k, const TensorPtr& wq, const TensorPtr& wk, int H, int KV, int Hd,
+                                             float eps, float theta, bool do_norm);
+TensorPtr gqa_attention(const TensorPtr& q, const TensorPtr& k, const TensorPtr& v, const TensorPtr& key_bias, int H, int KV, int Hd, float scale,
+                        int window);
 // x[b,s,:] = wte[ids[b,s],:] + wpe[s,:]   (wpe == nullptr: Gemma, times `scale`)
 TensorPtr embedding_lookup(const TensorPtr& ids, const TensorPtr& wte, const TensorPtr& wpe, float scale = 1.0f);
 

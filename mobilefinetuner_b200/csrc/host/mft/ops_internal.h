@@ -48,6 +48,9 @@ bool emit_bf16_operands();
 // true when run_gemm will take the bf16 tensor-core form for an [m,k] x [k,n] product with a K-major A operand
 bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k);
 void set_gemm_precision(int bf16);
+// True-gradient mode: GPT-2 attention with a backward + accumulating `.grad` (off by default; MFT_TRUE_ATTN_GRAD=1).
+bool true_gradients();
+void set_true_gradients(bool on);
 
 }  // namespace internal
 }  // namespace ops

@@ -71,6 +71,9 @@ struct mft_trainer {
     int64_t phase_launches[3] = {0, 0, 0};
     cudaEvent_t slots_event[2] = {nullptr, nullptr};   // recorded after each eager upload of the pinned slot table
     bool capturing = false;
+    std::vector<TensorPtr> accum;  // true-gradient mode: persistent gradient sums over micro-batches (mft_trainer_accumulate)
+    int accum_count = 0;
+    float extra_grad_scale = 1.0f; // 1 / micro-batches, folded into the clip factor of the next update
     bool graph_enabled = true;     // runtime switch (mft_trainer_enable_graph); only effective when cfg.use_cuda_graph
     int eager_steps = 0;
 };
@@ -237,7 +240,7 @@ void update_phase(mft_trainer* t, bool packed) {
     const mft_tensor_slot* slots = upload_slots(t, packed);
     const size_t wsb = mft_grad_sumsq_workspace_bytes();
     mft_rt::check(mft_grad_sumsq(slots, n, t->sumsq_dev, mft_rt::workspace(wsb), wsb, mft_rt::stream()), "mft_grad_sumsq");
-    const float pre = packed && t->cfg.world_size > 1 ? 1.0f / float(t->cfg.world_size) : 1.0f;
+    const float pre = (packed && t->cfg.world_size > 1 ? 1.0f / float(t->cfg.world_size) : 1.0f) * t->extra_grad_scale;
     mft_rt::check(mft_clip_scale(t->sumsq_dev, t->cfg.clip_norm, pre, t->scale_dev, t->norm_dev, mft_rt::stream()), "mft_clip_scale");
     mft_rt::check(mft_adam_step_dev(slots, n, t->lr_dev, t->cfg.beta1, t->cfg.beta2, t->cfg.eps, t->cfg.weight_decay,
                                     t->scale_dev, t->steps_dev, mft_rt::stream()), "mft_adam_step_dev");
@@ -397,6 +400,46 @@ extern "C" int mft_trainer_update(mft_trainer* t) {
         return 0;
     } catch (const std::exception& e) { return fail("mft_trainer_update: %s", e.what()); }
 }
+
+// ---- gradient accumulation over micro-batches (true-gradient mode only: the reference overwrites `.grad`)
+extern "C" int mft_trainer_accumulate(mft_trainer* t, const int32_t* dev_ids) {
+    if (!t || !dev_ids) return fail("mft_trainer_accumulate: null argument");
+    if (!ops::internal::true_gradients()) return fail("mft_trainer_accumulate: needs the true-gradient mode (mft_host_set_true_gradients(1) / MFT_TRUE_ATTN_GRAD=1); the default mode reproduces the reference, whose backward overwrites .grad");
+    try {
+        const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
+        mft_rt::d2d(t->ids->dev_out(), dev_ids, bytes);
+        const size_t n = t->trainable.size();
+        if (t->accum.size() != n) t->accum.assign(n, nullptr);
+        for (size_t i = 0; i < n; ++i) t->trainable[i]->set_grad(t->accum[i]);    // the engine adds into these (grad += g)
+        forward_backward(t);
+        for (size_t i = 0; i < n; ++i) {
+            if (!t->grads[i] || t->accum[i]) continue;
+            mft_rt::PersistentScope keep;                  // first micro-batch: move the gradient out of the step arena
+            t->accum[i] = t->grads[i]->clone();
+        }
+        ++t->accum_count;
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_accumulate: %s", e.what()); }
+}
+
+extern "C" int mft_trainer_apply_accumulated(mft_trainer* t) {
+    if (!t) return fail("mft_trainer_apply_accumulated: null argument");
+    if (t->accum_count == 0) return fail("mft_trainer_apply_accumulated: nothing accumulated");
+    try {
+        t->grads = t->accum;
+        t->with_grad = 0;
+        for (auto& g : t->grads) if (g) ++t->with_grad;
+        t->extra_grad_scale = 1.0f / float(t->accum_count);      // mean over micro-batches (the mains scale the loss by 1/accum)
+        update_phase(t, false);
+        t->extra_grad_scale = 1.0f;
+        t->accum.assign(t->trainable.size(), nullptr);
+        t->accum_count = 0;
+        return 0;
+    } catch (const std::exception& e) { t->extra_grad_scale = 1.0f; return fail("mft_trainer_apply_accumulated: %s", e.what()); }
+}
+
+extern "C" void mft_host_set_true_gradients(int enable) { ops::internal::set_true_gradients(enable != 0); }
+extern "C" int mft_host_true_gradients(void) { return ops::internal::true_gradients() ? 1 : 0; }
 
 extern "C" const float* mft_trainer_loss_ptr(mft_trainer* t) { return t ? t->loss_dev : nullptr; }
 extern "C" const float* mft_trainer_grad_norm_ptr(mft_trainer* t) { return t ? t->norm_dev : nullptr; }

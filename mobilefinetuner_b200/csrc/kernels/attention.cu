@@ -520,6 +520,7 @@ static bool env_attention_precise() {
     return e && e[0] == '0';        // exact mode: everything at fp32 accuracy
 }
 static bool g_attention_precise = env_attention_precise();
+bool attention_precise_enabled() { return g_attention_precise; }     // shared with gqa_attention.cu / attention_tc.cu
 
 }  // namespace mft
 

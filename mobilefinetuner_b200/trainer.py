@@ -45,6 +45,10 @@ TRAINER_SIGNATURES = {
     "mft_trainer_enable_graph": (None, [vp, C.c_int]),
     "mft_host_set_gemm_precision": (None, [C.c_int]),
     "mft_host_gemm_precision": (C.c_int, []),
+    "mft_host_set_true_gradients": (None, [C.c_int]),
+    "mft_host_true_gradients": (C.c_int, []),
+    "mft_trainer_accumulate": (C.c_int, [vp, vp]),
+    "mft_trainer_apply_accumulated": (C.c_int, [vp]),
     "mft_trainer_num_trainable": (i32, [vp]),
     "mft_trainer_num_with_grad": (i32, [vp]),
     "mft_trainer_kernel_launches": (i64, [vp]),
@@ -128,6 +132,13 @@ class Trainer:
 
     def update(self):
         self._ck(hostlib.mft_trainer_update(self._h))
+
+    def accumulate(self, dev_ids_ptr):
+        """True-gradient mode: forward + backward of one micro-batch, gradients added to the running sums."""
+        self._ck(hostlib.mft_trainer_accumulate(self._h, dev_ids_ptr))
+
+    def apply_accumulated(self):
+        self._ck(hostlib.mft_trainer_apply_accumulated(self._h))
 
     def make_grad_bucket(self):
         import torch

@@ -197,6 +197,46 @@ def repeat_kv_bwd(gy, rep):
     return gy.reshape(B, H // rep, rep, S, D).sum(axis=2, dtype=F)
 
 
+def gqa_attention_fwd_bwd(q, k, v, rep, scale, window=0, key_bias=None, dctx=None):
+    """The Gemma attention chain as the reference composes it (graph/gemma_model.cpp:481-505) and its backward through the
+    nodes that chain registers: repeat_kv_heads -> Q K^T -> * scale -> + mask [S,S] (0 / -1e10; causal, or causal restricted to
+    i - j < window, :261-285) -> + key_bias [B,1,1,S] -> softmax -> P V; backward = MatmulBackward, SoftmaxBackward (row dot in
+    double), ScaleBackward, RepeatKVHeadsBackward. q [B,H,S,Hd], k/v [B,KV,S,Hd]; returns ctx (and dq, dk, dv when dctx is given)."""
+    q, k, v = np.asarray(q, F), np.asarray(k, F), np.asarray(v, F)
+    S = q.shape[-2]
+    kf, vf = repeat_kv_fwd(k, rep), repeat_kv_fwd(v, rep)
+    s = (np.matmul(q, np.swapaxes(kf, -1, -2)) * F(scale)).astype(F)
+    i, j = np.arange(S)[:, None], np.arange(S)[None, :]
+    forbid = j > i
+    if window > 0:
+        forbid = forbid | (i - j >= window)
+    s = (s + np.where(forbid, F(-1e10), F(0))[None, None]).astype(F)
+    if key_bias is not None:
+        s = (s + np.asarray(key_bias, F)[:, None, None, :]).astype(F)
+    p = softmax_fwd(s)
+    ctx = np.matmul(p, vf).astype(F)
+    if dctx is None:
+        return ctx
+    dctx = np.asarray(dctx, F)
+    dp = np.matmul(dctx, np.swapaxes(vf, -1, -2)).astype(F)
+    dvf = np.matmul(np.swapaxes(p, -1, -2), dctx).astype(F)
+    ds = (softmax_bwd(p, dp) * F(scale)).astype(F)
+    dq = np.matmul(ds, kf).astype(F)
+    dkf = np.matmul(np.swapaxes(ds, -1, -2), q).astype(F)
+    return ctx, dq, repeat_kv_bwd(dkf, rep), repeat_kv_bwd(dvf, rep)
+
+
+def qk_norm_rope_fwd(x, w, theta, eps=1e-6, do_norm=True):
+    """rms_norm (1+w) then apply_rope on [B,H,S,Hd] (graph/gemma_model.cpp:383-420)."""
+    return rope(rms_norm_fwd(x, w, eps) if do_norm else np.asarray(x, F), theta)
+
+
+def qk_norm_rope_bwd(x, w, gy, theta, eps=1e-6, do_norm=True):
+    """ApplyRoPEBackward then RMSNormBackward (dx only)."""
+    dn = rope(gy, theta, inverse=True)
+    return rms_norm_bwd(x, w, dn, eps)[0] if do_norm else dn
+
+
 def embedding_gpt2(ids, wte, wpe):
     """graph/gpt2_model.cpp:346-381,500-528 — wte[id] + wpe[pos]."""
     ids = np.asarray(ids)
