@@ -226,6 +226,8 @@ int mft_attention_precise(int enable);
 /* 1: head_dim-64 attention runs on bf16 operands (mma.sync m16n8k16, fp32 accumulate and softmax) — the attention side of the
  * bf16 GEMM operand mode; ignored while the precise mode is on. Returns the previous setting. No reference counterpart. */
 int mft_attention_bf16(int enable);
+/* Current settings without changing them: bit 0 = precise, bit 1 = bf16 operands. */
+int mft_attention_mode(void);
 int mft_causal_attention_fwd(const float* q, const float* k, const float* v, float* ctx, int32_t B, int32_t H,
                              int32_t S, int32_t Hd, int64_t q_stride_b, int64_t q_stride_s, int64_t q_stride_h,
                              int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
@@ -237,6 +239,12 @@ int mft_causal_attention_fwd_ex(const float* q, const float* k, const float* v, 
                                 int64_t kv_stride_b, int64_t kv_stride_s, int64_t kv_stride_h,
                                 int64_t o_stride_b, int64_t o_stride_s, int64_t o_stride_h,
                                 float scale, int32_t window, mft_stream_t stream);
+/* The same causal attention forward (core/memory_efficient_attention.cpp:92-162) on the tcgen05 tensor cores, for the bf16
+ * operand mode and head_dim 64: q/k/v are the three column blocks of ONE bf16 [B, S, 3C] buffer (the qkv projection's bf16
+ * output; row pitch ld elements, a multiple of 8), loaded by TMA; S = Q K^T and P V run as tcgen05.mma with fp32 accumulators
+ * in TMEM; scores, softmax and the output stay fp32. ctx (fp32) and ctx_bf16 are [B, S, C]; either may be NULL. */
+int mft_causal_attention_tc_fwd(const void* qkv_bf16, int64_t ld, float* ctx, void* ctx_bf16, int32_t B, int32_t H, int32_t S,
+                                int32_t Hd, float scale, mft_stream_t stream);
 /* Grouped-query attention with a backward, forward and gradients without the [B,H,S,S] tensor: the whole chain of
  * graph/gemma_model.cpp:481-505 — repeat_kv_heads (core/ops.cpp:2072-2149: query head h uses kv head h / (H/KV)), Q K^T,
  * * scale, + causal / sliding mask (finite -1e10, j <= i and, for window > 0, i - j < window: graph/gemma_model.cpp:261-285),

@@ -96,10 +96,12 @@ SIGNATURES = {
     "mft_softmax_bwd": (C.c_int, [vp, vp, vp, i64, i64, vp]),
     "mft_attention_precise": (C.c_int, [C.c_int]),
     "mft_attention_bf16": (C.c_int, [C.c_int]),
+    "mft_attention_mode": (C.c_int, []),
     "mft_causal_attention_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
                                            i64, i64, i64, f32, i32, vp]),
     "mft_causal_attention_fwd_ex": (C.c_int, [vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64,
                                            i64, i64, i64, f32, i32, vp]),
+    "mft_causal_attention_tc_fwd": (C.c_int, [vp, i64, vp, vp, i32, i32, i32, i32, f32, vp]),
     "mft_gqa_attention_fwd": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64, i64, i64, i64, i64, f32, i32, vp]),
     "mft_gqa_attention_bwd_workspace_bytes": (sz, [i32, i32, i32, i32, i32]),
     "mft_gqa_attention_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32] + [i64] * 15 + [f32, i32, vp, sz, vp]),

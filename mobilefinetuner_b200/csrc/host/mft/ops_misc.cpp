@@ -2,6 +2,7 @@
 // cast, dropout, batch_norm) plus the model-level device helpers (embedding gather, GPT-2 attention).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <stdexcept>
@@ -194,10 +195,18 @@ TensorPtr gpt2_causal_attention(const TensorPtr& qkv_in, int n_head) {
     if (s.size() != 3 || s[2] % 3) throw TensorError("gpt2_causal_attention: qkv must be [B, S, 3C]");
     const int64_t B = s[0], S = s[1], C = s[2] / 3, Hd = C / n_head;
     auto ctx = Tensor::make({B, S, C}, kFloat32);
-    const float* base = qkv->dev_f32();
     float* cp = ctx->dev_f32_out();
     void* c16 = nullptr;
     if (internal::emit_bf16_operands() && C % 8 == 0) c16 = ctx->bf16_emit().ptr;     // ctx is the A operand of the output projection
+    // bf16 operand mode, head_dim 64: tcgen05 kernel fed by TMA from the projection's bf16 copy (MFT_ATTENTION_TC=0: mma.sync kernel)
+    static const bool tc_on = [] { const char* e = std::getenv("MFT_ATTENTION_TC"); return !(e && e[0] == '0'); }();
+    if (tc_on && Hd == 64 && internal::gemm_precision() == 1 && !(mft_attention_mode() & 1) && (3 * C) % 8 == 0) {
+        auto v16 = qkv->bf16_view();
+        mft_rt::check(mft_causal_attention_tc_fwd(v16.ptr, v16.ld, cp, c16, int32_t(B), n_head, int32_t(S), int32_t(Hd), 1.0f / std::sqrt(float(Hd)), st()),
+                      "mft_causal_attention_tc_fwd");
+        return ctx;
+    }
+    const float* base = qkv->dev_f32();
     mft_rt::check(mft_causal_attention_fwd_ex(base, base + C, base + 2 * C, cp, c16, int32_t(B), n_head, int32_t(S), int32_t(Hd),
                                               S * 3 * C, 3 * C, Hd, S * 3 * C, 3 * C, Hd, S * C, C, Hd,
                                               1.0f / std::sqrt(float(Hd)), 0, st()), "mft_causal_attention_fwd");

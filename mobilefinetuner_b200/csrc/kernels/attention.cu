@@ -532,6 +532,8 @@ extern "C" int mft_attention_bf16(int enable) {
     return prev;
 }
 
+extern "C" int mft_attention_mode(void) { return (g_attention_precise ? 1 : 0) | (g_attention_bf16 ? 2 : 0); }
+
 extern "C" int mft_attention_precise(int enable) {
     int prev = g_attention_precise ? 1 : 0;
     g_attention_precise = enable != 0;

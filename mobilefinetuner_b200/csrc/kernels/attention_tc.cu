@@ -1,0 +1,319 @@
+// Causal self-attention forward on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands by TMA):
+// GPT-2 semantics (core/memory_efficient_attention.cpp:92-162), head_dim 64, bf16 operands, fp32 scores / softmax / output.
+//
+// One CTA = 128 query rows of one (batch, head); keys stream through shared memory in tiles of 64.
+//   warps 0-3 : softmax. Thread t owns query row t == TMEM lane t: it reads its score row with tcgen05.ld, keeps the running
+//               max / sum and the 64 output accumulators in registers, and writes P (bf16) into the 128B-swizzled K-major
+//               shared-memory tile that feeds the second product.
+//   warp 4    : TMA producer (lane 0): Q once, then K / V tiles into a two-stage ring (cp.async.bulk.tensor, SWIZZLE_128B).
+//   warp 5    : TMEM allocator + tcgen05.mma issuer (lane 0):  S = Q K^T  (M 128, N 64, K 64: both operands K-major)  and
+//               O_t = P V (M 128, N 64, K 64: V is read MN-major straight from its [key][head_dim] tile — no transpose).
+// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, so the tensor pipe, the TMA and the softmax
+// of neighbouring tiles overlap; several CTAs are resident per SM (64 KB of shared memory, 128 TMEM columns each).
+// Each tile's O_t is un-normalised with respect to that tile's running max m_t: the owning thread folds it into its
+// registers as acc = acc * 2^(m_{t-1} - m_t) + O_t, so no TMEM read-modify-write is needed.
+// q/k/v come from ONE bf16 [B, S, 3C] buffer (the qkv projection's bf16 output) through one tensor map.
+#include <cuda.h>
+#include <cstdlib>
+#include <cstring>
+#include <unordered_map>
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace mft {
+
+constexpr int kTaBQ = 128, kTaBK = 64, kTaHD = 64;
+constexpr int kTaThreads = 192;
+constexpr int kTaTileBytes = kTaBK * kTaHD * 2;         // 8 KB: one K or V tile
+constexpr int kTaQBytes = kTaBQ * kTaHD * 2;            // 16 KB
+constexpr int kTaPBytes = kTaBQ * kTaBK * 2;            // 16 KB
+constexpr int kTaStages = 2;
+constexpr int kTaSmem = kTaQBytes + kTaStages * 2 * kTaTileBytes + kTaPBytes + 1024 /*align*/ + 128 /*barriers*/;
+constexpr int kTaTmemCols = 128;                        // S: columns [0,64), O_t: [64,128)
+
+struct TaArgs {
+    float* ctx; __nv_bfloat16* ctx16;
+    int H, S;
+    int64_t osb, oss;          // ctx element strides (batch, seq); heads are 64 apart
+    float scale_log2;          // scale * log2(e)
+};
+
+// MN-major, 128B-swizzled B operand: rows = contraction index (keys), 128 bytes (64 bf16 of N) per row, 8-row groups
+// 1024 bytes apart (SBO). One UMMA (K = 16) spans two groups.
+__device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= uint64_t((smem_addr >> 4) & 0x3FFF);
+    d |= uint64_t((1024 >> 4) & 0x3FFF) << 16;         // LBO: stride between 64-element blocks along N (one block here)
+    d |= uint64_t((1024 >> 4) & 0x3FFF) << 32;         // SBO: stride between 8-row groups along K
+    d |= uint64_t(1) << 46;
+    d |= uint64_t(2) << 61;                            // SWIZZLE_128B
+    return d;
+}
+
+__global__ void __launch_bounds__(kTaThreads)
+attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, int C) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = base;
+    uint8_t* sK = sQ + kTaQBytes;                            // [stages][8 KB]
+    uint8_t* sV = sK + kTaStages * kTaTileBytes;             // [stages][8 KB]
+    uint8_t* sP = sV + kTaStages * kTaTileBytes;             // 16 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kTaPBytes);
+    uint64_t* bar_q = bars;                // Q landed
+    uint64_t* bar_full = bars + 1;         // [2] K+V tile landed
+    uint64_t* bar_empty = bars + 3;        // [2] tile consumed by both products
+    uint64_t* bar_s = bars + 5;            // S ready in TMEM
+    uint64_t* bar_sfree = bars + 6;        // every softmax thread has copied S out
+    uint64_t* bar_p = bars + 7;            // P written to shared memory (and O_t copied out)
+    uint64_t* bar_pv = bars + 8;           // O_t ready in TMEM
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qt = gridDim.x - 1 - blockIdx.x;       // heavy query tiles first
+    const int b = blockIdx.y / p.H, h = blockIdx.y % p.H;
+    const int q0 = qt * kTaBQ;
+    const int S = p.S;
+    const int last_row = min(q0 + kTaBQ, S) - 1;
+    const int n_tiles = last_row / kTaBK + 1;        // causal: keys 0 .. last_row
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_q, 1);
+        for (int i = 0; i < kTaStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
+        mbar_init(bar_s, 1); mbar_init(bar_sfree, 4); mbar_init(bar_p, 4); mbar_init(bar_pv, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(tmem_slot)), "r"(uint32_t(kTaTmemCols)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 4) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_qkv)) : "memory");
+            mbar_arrive_expect_tx(bar_q, kTaQBytes);
+            tma_load_3d(sQ, &map_qkv, bar_q, h * kTaHD, q0, b);                       // 64 rows per box: two boxes
+            tma_load_3d(sQ + kTaQBytes / 2, &map_qkv, bar_q, h * kTaHD, q0 + 64, b);
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it & 1;
+                mbar_wait(&bar_empty[st], ((it >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bar_full[st], 2 * kTaTileBytes);
+                tma_load_3d(sK + st * kTaTileBytes, &map_qkv, &bar_full[st], C + h * kTaHD, it * kTaBK, b);
+                tma_load_3d(sV + st * kTaTileBytes, &map_qkv, &bar_full[st], 2 * C + h * kTaHD, it * kTaBK, b);
+            }
+        }
+    } else if (warp == 5) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            // D = f32, A = B = bf16; S: both K-major, N = 64; O_t: A K-major (P), B MN-major (V), N = 64; M = 128
+            constexpr uint32_t idesc_s = (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(kTaBK >> 3) << 17) | (uint32_t(kTaBQ >> 4) << 24);
+            constexpr uint32_t idesc_o = idesc_s | (1u << 16);
+            const uint32_t tS = tmem_base, tO = tmem_base + 64;
+            const uint64_t qdesc = make_kmajor_sw128_desc(smem_u32(sQ));
+            const uint64_t pdesc = make_kmajor_sw128_desc(smem_u32(sP));
+            mbar_wait(bar_q, 0);
+            mbar_wait(&bar_full[0], 0);
+            tc_fence_after();
+            {
+                const uint64_t kdesc = make_kmajor_sw128_desc(smem_u32(sK));
+#pragma unroll
+                for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
+                tc_commit(bar_s);
+            }
+            for (int it = 0; it < n_tiles; ++it) {
+                const int st = it & 1;
+                if (it + 1 < n_tiles) {              // S of the next tile, as soon as S of this one has been copied out
+                    const int sn = (it + 1) & 1;
+                    mbar_wait(&bar_full[sn], ((it + 1) >> 1) & 1);
+                    mbar_wait(bar_sfree, it & 1);
+                    tc_fence_after();
+                    const uint64_t kdesc = make_kmajor_sw128_desc(smem_u32(sK + sn * kTaTileBytes));
+#pragma unroll
+                    for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
+                    tc_commit(bar_s);
+                }
+                mbar_wait(bar_p, it & 1);            // P(it) is in shared memory, O_{it-1} has been copied out
+                tc_fence_after();
+                const uint64_t vdesc = make_mnmajor_sw128_desc(smem_u32(sV + st * kTaTileBytes));
+#pragma unroll
+                for (int k = 0; k < kTaBK / 16; ++k)     // 16 keys per instruction: A advances 32 bytes, B advances 16 rows of 128 bytes
+                    tc_mma_bf16(tO, pdesc + uint64_t(k * 2), vdesc + uint64_t(k * 128), idesc_o, k ? 1u : 0u);
+                tc_commit(&bar_empty[st]);           // K/V stage reusable once both products of this tile retire
+                tc_commit(bar_pv);
+            }
+        }
+    } else {
+        // ===================== softmax warps: thread = query row = TMEM lane =====================
+        const int row = threadIdx.x;                 // 0..127
+        const int qi = q0 + row;
+        const uint32_t lane_addr = tmem_base + (uint32_t(warp * 32) << 16);
+        float acc[kTaHD];
+#pragma unroll
+        for (int i = 0; i < kTaHD; ++i) acc[i] = 0.f;
+        float m_run = -INFINITY, l_run = 0.f;
+        uint8_t* prow = sP + row * 128;
+        for (int it = 0; it < n_tiles; ++it) {
+            const int key0 = it * kTaBK;
+            mbar_wait(bar_s, it & 1);
+            tc_fence_after();
+            float s[kTaBK];
+            {
+                float v[32];
+                tmem_ld32(lane_addr + 0, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s[i] = v[i];
+                tmem_ld32(lane_addr + 32, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) s[32 + i] = v[i];
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_sfree);   // the next S may overwrite TMEM columns [0,64)
+            // scores in the log2 domain; causal mask and sequence tail by index (masked entries contribute exp2(-inf) = 0)
+            const bool need_mask = key0 + kTaBK - 1 > q0 || key0 + kTaBK > S;
+            float mx = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < kTaBK; ++j) {
+                float x = s[j] * p.scale_log2;
+                if (need_mask && (key0 + j > qi || key0 + j >= S)) x = -INFINITY;
+                s[j] = x;
+                mx = fmaxf(mx, x);
+            }
+            const float m_new = fmaxf(m_run, mx);
+            const float m_ref = m_new == -INFINITY ? 0.f : m_new;     // rows past the sequence end see only masked keys
+            const float alpha = exp2f(m_run - m_ref);
+            float sum = 0.f;
+            uint32_t pk[kTaBK / 2];
+#pragma unroll
+            for (int j = 0; j < kTaBK; j += 2) {
+                const float p0 = exp2f(s[j] - m_ref), p1 = exp2f(s[j + 1] - m_ref);
+                sum += p0 + p1;
+                const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
+                pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
+            }
+            l_run = l_run * alpha + sum;
+            m_run = m_new;
+            if (it > 0) {                             // fold in O_{it-1} (relative to the previous max), then rescale
+                mbar_wait(bar_pv, (it - 1) & 1);
+                tc_fence_after();
+                float v[32];
+                tmem_ld32(lane_addr + 64, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = (acc[i] + v[i]) * alpha;
+                tmem_ld32(lane_addr + 96, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[32 + i] = (acc[32 + i] + v[i]) * alpha;
+            }
+            // P row -> 128B-swizzled K-major tile: 16-byte piece c of row r sits at r*128 + ((c ^ (r & 7)) << 4)
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            fence_proxy_async_smem();                 // generic-proxy writes visible to the tensor core's async proxy
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_p);
+        }
+        mbar_wait(bar_pv, (n_tiles - 1) & 1);
+        tc_fence_after();
+        {
+            float v[32];
+            tmem_ld32(lane_addr + 64, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[i] += v[i];
+            tmem_ld32(lane_addr + 96, v);
+#pragma unroll
+            for (int i = 0; i < 32; ++i) acc[32 + i] += v[i];
+        }
+        const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+        // every product has retired: the K/V/P region is free and stages this warp's 32 output rows for coalesced stores
+        float* stage = reinterpret_cast<float*>(sK) + warp * 32 * 68;        // 32 rows x 68 floats per warp (fits K+V+P = 48 KB)
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+            *reinterpret_cast<float4*>(stage + lane * 68 + c * 4) = make_float4(acc[4 * c] * inv, acc[4 * c + 1] * inv, acc[4 * c + 2] * inv, acc[4 * c + 3] * inv);
+        __syncwarp();
+        const int half = lane >> 4, c4 = lane & 15;   // two rows per instruction, 16 lanes x float4 per row
+        float* ob = p.ctx ? p.ctx + int64_t(b) * p.osb + h * kTaHD : nullptr;
+        __nv_bfloat16* ob16 = p.ctx16 ? p.ctx16 + int64_t(b) * p.osb + h * kTaHD : nullptr;
+#pragma unroll 4
+        for (int r = 0; r < 32; r += 2) {
+            const int lr = r + half, gr = q0 + warp * 32 + lr;
+            if (gr >= S) continue;
+            const float4 o4 = *reinterpret_cast<const float4*>(stage + lr * 68 + c4 * 4);
+            if (ob) *reinterpret_cast<float4*>(ob + int64_t(gr) * p.oss + c4 * 4) = o4;
+            if (ob16) st_bf16x4(ob16 + int64_t(gr) * p.oss + c4 * 4, o4);
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(kTaTmemCols)) : "memory");
+    }
+}
+
+// One tensor map over the bf16 [B][S][3C] projection output: box = 64 columns (one head's 128 bytes) x 64 rows, 128B swizzle.
+static bool make_qkv_map(CUtensorMap* out, const void* ptr, uint64_t width, uint64_t S, uint64_t B, uint64_t ld, uint64_t batch_stride) {
+    struct Key { const void* p; uint64_t w, s, b, ld, bs; bool operator==(const Key& o) const { return p == o.p && w == o.w && s == o.s && b == o.b && ld == o.ld && bs == o.bs; } };
+    struct KeyHash { size_t operator()(const Key& k) const { return std::hash<const void*>()(k.p) ^ (k.w * 31 + k.s * 131 + k.b * 1031 + k.ld * 7 + k.bs); } };
+    static std::unordered_map<Key, CUtensorMap, KeyHash> cache;
+    static std::mutex mu;
+    Key key{ptr, width, S, B, ld, batch_stride};
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) { *out = it->second; return true; }
+    }
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return false;
+    alignas(64) CUtensorMap m;
+    cuuint64_t dims[3] = {width, S, B};
+    cuuint64_t strides[2] = {ld * 2, batch_stride * 2};
+    cuuint32_t box[3] = {64, 64, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (cache.size() > 1024) cache.clear();
+        cache.emplace(key, m);
+    }
+    *out = m;
+    return true;
+}
+
+}  // namespace mft
+
+using namespace mft;
+
+/* qkv16: bf16 [B, S, 3C] (row pitch ld elements, batch stride S*ld); ctx / ctx16 [B, S, C] (either may be NULL). */
+extern "C" int mft_causal_attention_tc_fwd(const void* qkv_bf16, int64_t ld, float* ctx, void* ctx_bf16, int32_t B, int32_t H, int32_t S,
+                                           int32_t Hd, float scale, mft_stream_t stream) {
+    if (B == 0 || H == 0 || S == 0) return 0;
+    if (!qkv_bf16 || (!ctx && !ctx_bf16)) return set_error(1, "mft_causal_attention_tc_fwd: null pointer");
+    if (Hd != kTaHD) return set_error(1, "mft_causal_attention_tc_fwd: head_dim must be 64 (got %d)", Hd);
+    const int64_t C = int64_t(H) * Hd;
+    if (ld < 3 * C || (ld & 7) || !aligned16(qkv_bf16)) return set_error(1, "mft_causal_attention_tc_fwd: qkv must be 16-byte aligned with a pitch that is a multiple of 8 and >= 3C");
+    if ((ctx && !aligned16(ctx)) || (ctx_bf16 && (reinterpret_cast<uintptr_t>(ctx_bf16) & 7u))) return set_error(1, "mft_causal_attention_tc_fwd: misaligned output");
+    if (int64_t(B) * H > 65535) return set_error(1, "mft_causal_attention_tc_fwd: B*H too large");
+    CUtensorMap map;
+    if (!make_qkv_map(&map, qkv_bf16, uint64_t(3 * C), uint64_t(S), uint64_t(B), uint64_t(ld), uint64_t(S) * uint64_t(ld)))
+        return set_error(3, "mft_causal_attention_tc_fwd: cuTensorMapEncodeTiled failed");
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set)) {
+        cudaError_t e = cudaFuncSetAttribute(attention_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTaSmem);
+        if (e != cudaSuccess) return set_error(2, "mft_causal_attention_tc_fwd: smem attribute: %s", cudaGetErrorString(e));
+    }
+    TaArgs a;
+    a.ctx = ctx; a.ctx16 = static_cast<__nv_bfloat16*>(ctx_bf16); a.H = H; a.S = S; a.osb = int64_t(S) * C; a.oss = C;
+    a.scale_log2 = scale * 1.4426950408889634f;
+    dim3 grid(unsigned(ceil_div(S, kTaBQ)), unsigned(B * H));
+    attention_tc_fwd_kernel<<<grid, kTaThreads, kTaSmem, as_stream(stream)>>>(map, a, int(C));
+    MFT_CHECK_LAUNCH("mft_causal_attention_tc_fwd");
+    return 0;
+}

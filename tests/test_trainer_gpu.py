@@ -221,11 +221,11 @@ def test_arena_is_released_with_the_last_trainer_and_cannot_move_under_a_live_on
     trainer is gone, and a second trainer may not force a larger slab while the first one's graphs point into the old one."""
     from mobilefinetuner_b200.trainer import Trainer, TrainerError
     a = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=64)
-    with pytest.raises(TrainerError, match="arena"):
-        Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=128)
+    with pytest.raises(TrainerError, match="arena"):                   # larger than any slab an earlier test left behind
+        Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=96 * 1024)
     a.step_numpy(a.next_synthetic_batch())
     a.close()
-    b = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=128)     # no live user: the slab may grow
+    b = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, arena_mb=128)     # no live user: a slab of any size may be taken
     b.step_numpy(b.next_synthetic_batch())
     b.close()
 
