@@ -35,14 +35,18 @@ def test_default_mode_reproduces_the_stop_gradient_and_true_mode_trains_every_ad
     hostlib.mft_host_set_true_gradients(1)
     try:
         b = Trainer(2, 16, shape=TINY, lora_rank=8, lora_alpha=16.0, arena_mb=256)
-        lb = [b.step_numpy(b.next_synthetic_batch()) for _ in range(30)]
-        assert (b.num_with_grad, b.num_trainable) == (8, 8)      # every LoRA tensor receives a gradient
-        assert lb[0] == la[0]                                    # same forward
-        assert lb[1] != la[1]                                    # the qkv adapters now move
-        assert np.mean(lb[-5:]) < np.mean(lb[:5])
-        moved = [b.param_checksum(i) for i in range(8)]
-        assert all(m[2] > 0 for m in moved)                      # B factors (initialised to zero) of qkv and proj all trained
-        b.close()
+        try:
+            lb = [b.step_numpy(b.next_synthetic_batch()) for _ in range(3)]
+            fixed = b.next_synthetic_batch()
+            lb += [b.step_numpy(fixed) for _ in range(40)]           # one batch repeated: the loss on it must fall
+            assert (b.num_with_grad, b.num_trainable) == (8, 8), (b.num_with_grad, b.num_trainable)   # every LoRA tensor receives a gradient
+            assert abs(lb[0] - la[0]) <= 1e-5 * la[0], (lb[0], la[0])            # same forward (another kernel: rounding only)
+            assert lb[2] != la[2]                                    # the qkv adapters now move
+            assert lb[-1] < lb[3], lb
+            moved = [b.param_checksum(i) for i in range(8)]
+            assert all(m[2] > 0 for m in moved), moved               # B factors (initialised to zero) of qkv and proj all trained
+        finally:
+            b.close()
     finally:
         hostlib.mft_host_set_true_gradients(0)
 
@@ -82,7 +86,9 @@ def test_true_gradient_mode_full_size_gpt2_small_all_48_adapters(capi, true_grad
     """GPT-2 small (head_dim 64) LoRA r8 at 4 x 128 on the tensor-core path: 48 / 48 adapter tensors receive gradients."""
     from mobilefinetuner_b200.trainer import Trainer
     t = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096, cuda_graph=True)
-    losses = [t.step_numpy(t.next_synthetic_batch()) for _ in range(6)]
-    assert (t.num_with_grad, t.num_trainable) == (48, 48)
-    assert all(np.isfinite(losses))
-    t.close()
+    try:
+        losses = [t.step_numpy(t.next_synthetic_batch()) for _ in range(6)]
+        assert (t.num_with_grad, t.num_trainable) == (48, 48)
+        assert all(np.isfinite(losses))
+    finally:
+        t.close()
