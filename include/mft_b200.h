@@ -63,7 +63,11 @@ typedef struct mft_gemm_args {
     int32_t batch; int64_t stride_a, stride_b, stride_c;
     const float* addend; int64_t ld_addend;            /* [m,n] added after bias/beta (residual stream), or NULL   */
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;  /* [m,n]: result *= d gelu_tanh / dx at this tensor, or NULL */
-    void* gelu_out_bf16; int64_t ld_gelu_out_bf16;     /* bf16 copy of gelu_out (needs gelu_out), or NULL             */
+    void* gelu_out_bf16; int64_t ld_gelu_out_bf16;     /* bf16 copy of gelu_out, or NULL; on the tensor-core path gelu_out itself
+                                                          may then be NULL (the activation leaves as bf16 only)      */
+    void* c_bf16; int64_t ldc_bf16;                    /* bf16 copy of C (after alpha / bias / beta), or NULL. On the tensor-core path
+                                                          c may then be NULL: the bf16 copy is the only result (its consumers are
+                                                          bf16 GEMM / attention operands), which halves the epilogue's HBM writes */
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
 /* bf16-operand form of mft_gemm: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements, multiples of 8),
@@ -148,6 +152,12 @@ int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stre
 /* MulBackward for same-shape operands: ga = gy*b, gb = gy*a (core/backward_functions.cpp:74-83). */
 /* mft_gelu_bwd plus a dense bf16 copy of gx (NULL = off) for the bf16 GEMM that consumes it; no reference counterpart. */
 int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream);
+/* GeluBackward (core/backward_functions.cpp:155-177) for the bf16 operand mode, with the incoming gradient and the result as
+ * bf16 arrays (they are a bf16-only GEMM result and a bf16 GEMM operand): x is fp32, or bf16 when x_is_bf16; gx (fp32) is
+ * optional. n % 8 == 0, 16-byte aligned pointers. 8 (or 6) bytes per element instead of 14. */
+int mft_gelu_bwd_lowp(const void* x, int x_is_bf16, const void* gy_bf16, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream);
+/* bf16 -> fp32 (row pitches in elements): materialises the fp32 values of a tensor that a kernel produced as bf16 only. */
+int mft_cast_from_bf16(const void* in, int64_t ldi, float* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream);
 int mft_mul_bwd(const float* a, const float* b, const float* gy, float* ga, float* gb, int64_t n, mft_stream_t stream);
 
 /* ------------------------------------------------------------------ normalisation

@@ -35,7 +35,7 @@ class GemmArgs(C.Structure):
                 ("k2", i32), ("a2", vp), ("lda2", i64), ("b2", vp), ("ldb2", i64),
                 ("batch", i32), ("stride_a", i64), ("stride_b", i64), ("stride_c", i64),
                 ("addend", vp), ("ld_addend", i64), ("gelu_grad_x", vp), ("ld_gelu_grad_x", i64),
-                ("gelu_out_bf16", vp), ("ld_gelu_out_bf16", i64)]
+                ("gelu_out_bf16", vp), ("ld_gelu_out_bf16", i64), ("c_bf16", vp), ("ldc_bf16", i64)]
 
 
 class TensorSlot(C.Structure):
@@ -80,6 +80,8 @@ SIGNATURES = {
     "mft_gelu_fwd": (C.c_int, [vp, vp, i64, vp]),
     "mft_gelu_bwd": (C.c_int, [vp, vp, vp, i64, vp]),
     "mft_gelu_bwd_ex": (C.c_int, [vp, vp, vp, vp, i64, vp]),
+    "mft_gelu_bwd_lowp": (C.c_int, [vp, C.c_int, vp, vp, vp, i64, vp]),
+    "mft_cast_from_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
     "mft_mul_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, vp]),
     "mft_layernorm_fwd": (C.c_int, [vp, vp, vp, vp, i64, i64, f32, vp]),
     "mft_norm_bwd_workspace_bytes": (sz, [i64, i64]),

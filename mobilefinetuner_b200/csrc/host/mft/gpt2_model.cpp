@@ -9,6 +9,7 @@
 #include <stdexcept>
 
 #include "ops.h"
+#include "mft_b200.h"
 #include "ops_internal.h"
 #include "runtime.h"
 
@@ -206,7 +207,17 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr
         if (carry) x = add(x_in, carry);
         x1 = layer_norm(x, w.ln_1_weight, w.ln_1_bias, eps);
     }
-    auto qkv = run_linear(x1, w.qkv_lin, w.lora_initialized, w.attn_qkv_weight, w.attn_qkv_bias);
+    // bf16 operand mode: results that are only ever read as bf16 operands skip their fp32 copy (the values stay reachable:
+    // an fp32 reader triggers one upcast). qkv feeds the tcgen05 attention only; the GELU activation feeds fc_out's GEMM
+    // only when fc_out has no adapter and a frozen weight; ln_2's rows feed fc_in's GEMM only under the same condition.
+    const bool lowp = internal::gemm_precision() == 1 && internal::bf16_only_results();
+    const int64_t head_dim = config_.n_embd / config_.n_head;
+    LinearFusion qkv_f;
+    qkv_f.out_bf16_only = lowp && head_dim == 64 && !(mft_attention_mode() & 1) && !internal::true_gradients();
+    auto qkv = run_linear_fused(x1, w.qkv_lin, w.lora_initialized, w.attn_qkv_weight, w.attn_qkv_bias, qkv_f);
+    const bool fc_in_plain = !(w.lora_initialized && w.fc_in_lin && w.fc_in_lin->has_adapter()) && !internal::wants_grad(w.mlp_fc_in_weight) &&
+                             !internal::wants_grad(w.mlp_fc_in_bias);
+    const bool fc_out_plain = !(w.lora_initialized && w.fc_out_lin && w.fc_out_lin->has_adapter()) && !internal::wants_grad(w.mlp_fc_out_weight);
     // default: the reference's stop-gradient attention; true-gradient mode: the same forward with a backward
     auto ctx = internal::true_gradients() ? gpt2_causal_attention_with_grad(qkv, config_.n_head) : gpt2_causal_attention(qkv, config_.n_head);
     // MFT_FUSE_EPILOGUE bit 0: residual adds ride in the projections' epilogues; bit 1: GeluBackward rides in the epilogue of
@@ -220,14 +231,20 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr
         x2 = run_linear_fused(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias, attn_out);
         x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
     } else if (fuse_ln) {
-        x3 = add_layer_norm(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias), w.ln_2_weight, w.ln_2_bias, eps, &x2);
+        x3 = add_layer_norm(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias), w.ln_2_weight, w.ln_2_bias, eps, &x2,
+                            lowp && fc_in_plain);
     } else {
         x2 = add(x, run_linear(ctx, w.proj_lin, w.lora_initialized, w.attn_proj_weight, w.attn_proj_bias));
         x3 = layer_norm(x2, w.ln_2_weight, w.ln_2_bias, eps);
     }
     TensorPtr h, pre;   // fc_in + tanh-GELU: the activation is written by the GEMM epilogue (graph/gpt2_model.cpp:794-802)
-    if (w.lora_initialized && w.fc_in_lin) h = w.fc_in_lin->forward_gelu(x3, &pre);
-    else pre = fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, &h);
+    {
+        LinearFusion f;
+        f.gelu_act = &h;
+        f.gelu_bf16_only = lowp && fc_out_plain && !fuse;
+        if (w.lora_initialized && w.fc_in_lin) pre = w.fc_in_lin->forward_fused(x3, f);
+        else pre = fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, f);
+    }
     // x2 + fc_out(gelu(pre)): residual in the forward epilogue, GeluBackward in the epilogue of the backward dX product
     if (!fuse) {
         auto m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);

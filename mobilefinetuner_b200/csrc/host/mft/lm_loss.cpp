@@ -1,5 +1,7 @@
 #include "lm_loss.h"
 
+#include <cstdlib>
+
 #include <stdexcept>
 
 #include "autograd_engine.h"
@@ -21,10 +23,16 @@ public:
     std::vector<TensorPtr> apply(const TensorPtr& gout) override {
         const auto& s = logits_->shape();
         auto g = Tensor::make(s, kFloat32, false, logits_->ld());
-        float* gp = g->dev_f32_out();
+        float* gp = nullptr;
         void* g16 = nullptr;
         int64_t ld16 = 0;
-        if (internal::emit_bf16_operands()) { auto e = g->bf16_emit(); g16 = e.ptr; ld16 = e.ld; }   // read by the lm_head dX / dW products
+        if (internal::bf16_only_results() && logits_->grad_may_be_bf16() && logits_->ld() % 4 == 0) {
+            auto e = g->bf16_only_out();          // frozen head: dlogits only feeds the bf16 dX product (an fp32 reader gets an upcast)
+            g16 = e.ptr; ld16 = e.ld;
+        } else {
+            gp = g->dev_f32_out();
+            if (internal::emit_bf16_operands()) { auto e = g->bf16_emit(); g16 = e.ptr; ld16 = e.ld; }   // read by the lm_head dX / dW products
+        }
         mft_rt::check(mft_lm_ce_bwd_ex(logits_->dev_f32(), logits_->ld(), static_cast<const int32_t*>(labels_->dev()), lse_->dev_f32(),
                                        static_cast<const int32_t*>(valid_->dev()), gout->dev_f32(), int32_t(s[0]), int32_t(s[1]),
                                        int32_t(s[2]), ignore_, reduction_, gp, g->ld(), g16, ld16, mft_rt::stream()), "mft_lm_ce_bwd");

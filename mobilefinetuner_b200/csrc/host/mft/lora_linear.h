@@ -46,6 +46,8 @@ public:
     const TensorPtr& b() const { return base_b(); }
     const std::vector<LoRASlice>& slices() const { return slices_; }
     bool is_merged() const { return merged_; }
+    // B200 extension: true when the forward adds a rank-r update (adapters attached and not merged into the base weight)
+    bool has_adapter() const { return !merged_ && !slices_.empty(); }
 
 private:
     TensorPtr* W_ref_ = nullptr;

@@ -66,6 +66,12 @@ bool emit_bf16_operands() {
     const char* e = std::getenv("MFT_BF16_EMIT");      // read per call: tests flip it to compare against the cast-on-demand path
     return !(e && e[0] == '0');
 }
+// bf16-only results (MFT_BF16_ONLY=0 keeps every fp32 copy; read per call so tests can compare the two)
+bool bf16_only_results() {
+    if (!emit_bf16_operands()) return false;
+    const char* e = std::getenv("MFT_BF16_ONLY");
+    return !(e && e[0] == '0');
+}
 void set_gemm_precision(int bf16) {
     g_precision = bf16 ? 1 : 0;
     mft_attention_bf16(g_precision);      // attention follows the GEMM operand mode
@@ -110,10 +116,19 @@ void run_gemm(GemmCall g) {
         a.m = int32_t(g.m); a.n = int32_t(g.n); a.k = int32_t(g.k);
         a.trans_a = 0; a.trans_b = 1;
         if (!g.trans_a) {
-            if (g.a_tensor && g.a_tensor->dev_f32() == g.a && g.a_tensor->shape().back() == g.k && g.a_tensor->ld() == g.lda) {
-                auto v = g.a_tensor->bf16_view(); a.a = static_cast<const float*>(v.ptr); a.lda = v.ld;
-            } else { keep.push_back(temp_bf16(g.a, g.lda, g.m, g.k, false)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld; }
-        } else { keep.push_back(temp_bf16(g.a, g.lda, g.k, g.m, true)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld; }
+            // a_tensor with a == null (or a pointing at its fp32 data): its bf16 copy is the operand — written by the producer,
+            // or cast once; a tensor that only exists as bf16 is never materialised as fp32 here
+            const bool a_known = g.a_tensor && g.a_tensor->shape().back() == g.k && g.a_tensor->ld() == g.lda &&
+                                 (g.a == nullptr || (!g.a_tensor->f32_pending() && g.a_tensor->dev_f32() == g.a));
+            if (a_known) { auto v = g.a_tensor->bf16_view(); a.a = static_cast<const float*>(v.ptr); a.lda = v.ld; }
+            else {
+                if (!g.a) g.a = g.a_tensor->dev_f32();
+                keep.push_back(temp_bf16(g.a, g.lda, g.m, g.k, false)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld;
+            }
+        } else {
+            if (!g.a) g.a = g.a_tensor->dev_f32();
+            keep.push_back(temp_bf16(g.a, g.lda, g.k, g.m, true)); a.a = static_cast<const float*>(keep.back().ptr); a.lda = keep.back().ld;
+        }
         const bool b_known = g.b_weight && g.b_weight->ndim() == 2 && g.b_weight->dev_f32() == g.b;
         if (g.trans_b) {
             if (b_known) { auto v = g.b_weight->bf16_view(); a.b = static_cast<const float*>(v.ptr); a.ldb = v.ld; }
@@ -132,16 +147,34 @@ void run_gemm(GemmCall g) {
             } else { keep.push_back(temp_bf16(g.b2, g.ldb2, g.n, g.k2, false)); a.b2 = static_cast<const float*>(keep.back().ptr); a.ldb2 = keep.back().ld; }
             a.k2 = int32_t(g.k2);
         }
-        a.c = g.c; a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias; a.gelu_out = g.gelu_out;
+        a.ldc = g.ldc; a.alpha = g.alpha; a.beta = g.beta; a.bias = g.bias;
         a.addend = g.addend; a.ld_addend = g.ld_addend; a.gelu_grad_x = g.gelu_grad_x; a.ld_gelu_grad_x = g.ld_gelu_grad_x;
         a.batch = 1;
-        if (g.gelu_out && g.gelu_tensor && g.gelu_tensor->dev_f32() == g.gelu_out && g.gelu_tensor->ld() == g.ldc) {
-            auto e = g.gelu_tensor->bf16_emit();
-            if (e.ld % 4 == 0) { a.gelu_out_bf16 = e.ptr; a.ld_gelu_out_bf16 = e.ld; }
+        const bool diet = bf16_only_results();
+        const bool plain_epilogue = g.beta == 0.0f && !g.addend && !g.gelu_grad_x;
+        const bool gelu_here = g.gelu_out != nullptr || (g.gelu_tensor && g.gelu_bf16_only);
+        if (g.c_tensor && !g.c && diet && g.c_bf16_only && plain_epilogue && !gelu_here && g.c_tensor->is_dense() && g.n % 8 == 0 && emit_bf16_operands()) {
+            auto e = g.c_tensor->bf16_only_out();                 // bf16 is the only copy of the result
+            a.c = nullptr; a.c_bf16 = e.ptr; a.ldc_bf16 = e.ld;
+        } else {
+            a.c = g.c ? g.c : g.c_tensor->dev_f32_out();
         }
+        if (g.gelu_tensor && (g.gelu_out || g.gelu_bf16_only) && g.gelu_tensor->ld() == g.ldc) {
+            if (!g.gelu_out && diet && emit_bf16_operands() && g.gelu_tensor->is_dense() && g.n % 8 == 0) {
+                auto e = g.gelu_tensor->bf16_only_out();          // the activation feeds a bf16 GEMM operand only
+                a.gelu_out = nullptr; a.gelu_out_bf16 = e.ptr; a.ld_gelu_out_bf16 = e.ld;
+            } else {
+                a.gelu_out = g.gelu_out ? g.gelu_out : g.gelu_tensor->dev_f32_out();
+                auto e = g.gelu_tensor->bf16_emit();
+                if (e.ld % 4 == 0) { a.gelu_out_bf16 = e.ptr; a.ld_gelu_out_bf16 = e.ld; }
+            }
+        } else a.gelu_out = g.gelu_out;
         mft_rt::check(mft_gemm_bf16(&a, mft_rt::stream()), "mft_gemm_bf16");
         return;
     }
+    if (!g.a && g.a_tensor) g.a = g.a_tensor->dev_f32();
+    if (!g.c && g.c_tensor) g.c = g.c_tensor->dev_f32_out();
+    if (!g.gelu_out && g.gelu_tensor && g.gelu_bf16_only) g.gelu_out = g.gelu_tensor->dev_f32_out();
     if (big && g.batch <= 1) {
         if (g.trans_a) {       // stored [k,m] -> [m,k]
             const int64_t ld = (g.k + 3) / 4 * 4;

@@ -51,6 +51,8 @@ TensorPtr nll_loss(const TensorPtr& input, const TensorPtr& target, const std::s
 
 // normalisation
 TensorPtr layer_norm(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias, float eps = 1e-5f);
+// B200 extension: as layer_norm, result possibly written as bf16 only (bf16 operand mode, consumer is a GEMM operand)
+TensorPtr layer_norm_lowp(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias, float eps, bool y_bf16_only);
 TensorPtr rms_norm(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);         // scale (1 + w)
 TensorPtr rms_norm_affine(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);  // scale w
 TensorPtr batch_norm(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias,
@@ -124,11 +126,15 @@ TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const Tensor
 //                    (GeluBackward, core/backward_functions.cpp:155-177, applied in the epilogue), so the activation's
 //                    gradient is never written to HBM. Only valid when this op is the activation's single consumer.
 // sum = x + a; returns layer_norm(sum) and hands `sum` back (one kernel; same autograd nodes as add + layer_norm).
-TensorPtr add_layer_norm(const TensorPtr& x, const TensorPtr& a, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out);
+TensorPtr add_layer_norm(const TensorPtr& x, const TensorPtr& a, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out,
+                         bool y_bf16_only = false);
 struct LinearFusion {
     TensorPtr* gelu_act = nullptr;
     TensorPtr residual;
     TensorPtr gelu_input_pre;
+    // bf16 operand mode only: the caller knows that y (or the GELU activation) is consumed as a bf16 GEMM / attention operand,
+    // so the epilogue may skip the fp32 copy (Tensor::bf16_only_out — any fp32 reader still gets the values, via an upcast).
+    bool out_bf16_only = false, gelu_bf16_only = false;
 };
 TensorPtr fused_lora_linear(const TensorPtr& x, const TensorPtr& W, const TensorPtr& bias, const std::vector<LoraTerm>& terms,
                             const LinearFusion& fusion);

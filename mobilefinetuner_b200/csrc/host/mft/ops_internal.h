@@ -35,6 +35,14 @@ struct GemmCall {
     TensorPtr b2_tensor;  // tensor behind the rank-r operand: stored [n, k2] (b2_stored_kn = false) or [k2, n] (true); optional
     bool b2_stored_kn = false;
     TensorPtr gelu_tensor;   // tensor behind gelu_out: in bf16 mode the epilogue also writes its bf16 shadow
+    // Result tensor (optional; `c` may then be left null and is resolved by run_gemm). On the bf16 tensor-core form:
+    //   c_bf16_only    : the result leaves as bf16 only (Tensor::bf16_only_out) — for results whose consumers are bf16 GEMM /
+    //                    attention operands; anything else that reads it gets an upcast on demand;
+    //   gelu_bf16_only : same for the GELU aux output.
+    // `a` may also be left null when `a_tensor` is given: the bf16 form then reads the tensor's bf16 copy without touching
+    // (or materialising) its fp32 data.
+    TensorPtr c_tensor;
+    bool c_bf16_only = false, gelu_bf16_only = false;
 };
 void run_gemm(GemmCall g);
 
@@ -48,6 +56,8 @@ bool emit_bf16_operands();
 // true when run_gemm will take the bf16 tensor-core form for an [m,k] x [k,n] product with a K-major A operand
 bool gemm_takes_bf16(int64_t m, int64_t n, int64_t k);
 void set_gemm_precision(int bf16);
+// true when results consumed only as bf16 operands may skip their fp32 copy (bf16 operand mode and MFT_BF16_ONLY != 0)
+bool bf16_only_results();
 // True-gradient mode: GPT-2 attention with a backward + accumulating `.grad` (off by default; MFT_TRUE_ATTN_GRAD=1).
 bool true_gradients();
 void set_true_gradients(bool on);

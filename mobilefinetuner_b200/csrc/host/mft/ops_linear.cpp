@@ -314,9 +314,10 @@ public:
             auto gx = Tensor::make(x_->shape(), kFloat32);
             GemmCall g;
             g.m = T; g.n = in; g.k = out;
-            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
+            g.a = nullptr; g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
             g.b = W_->dev_f32(); g.ldb = W_->ld(); g.trans_b = 1; g.b_weight = W_;   // W stored [in,out]: K-major for this product
-            g.c = gx->dev_f32_out(); g.ldc = in;
+            g.c = nullptr; g.c_tensor = gx; g.ldc = in;
+            g.c_bf16_only = x_->grad_may_be_bf16() && !pre_ && terms_.size() <= 1;     // dX of a GELU activation: read by GeluBackward as bf16
             std::vector<TensorPtr> keep;
             for (size_t i = 0; i < terms_.size(); ++i) {
                 TermLayout l = classify(terms_[i], in, out);
@@ -412,13 +413,19 @@ TensorPtr fused_lora_linear(const TensorPtr& x_in, const TensorPtr& W, const Ten
     }
     GemmCall g;
     g.m = T; g.n = out; g.k = in;
-    g.a = x->dev_f32(); g.lda = in; g.trans_a = 0; g.a_tensor = x;
+    g.a = nullptr; g.lda = in; g.trans_a = 0; g.a_tensor = x;          // resolved by run_gemm (bf16 copy or fp32 data)
     g.b = W->dev_f32(); g.ldb = W->ld(); g.trans_b = 0; g.b_weight = W;
-    g.c = y->dev_f32_out(); g.ldc = y->ld();
+    g.c = nullptr; g.c_tensor = y; g.ldc = y->ld();
+    g.c_bf16_only = fusion.out_bf16_only && terms.size() <= 1 && !residual;
     g.bias = bias ? bias->dev_f32() : nullptr;
     TensorPtr act;
     const bool fuse_gelu = gelu_act != nullptr && terms.size() <= 1;   // later slices accumulate after the epilogue ran
-    if (fuse_gelu) { act = Tensor::make(so, kFloat32, false, y->ld()); g.gelu_out = act->dev_f32_out(); g.gelu_tensor = act; }
+    if (fuse_gelu) {
+        act = Tensor::make(so, kFloat32, false, y->ld());
+        g.gelu_tensor = act;
+        if (fusion.gelu_bf16_only) g.gelu_bf16_only = true; else g.gelu_out = act->dev_f32_out();
+        act->set_grad_may_be_bf16(true);      // its gradient goes to GeluBackward, which reads bf16 directly
+    }
     if (!terms.empty()) {
         g.k2 = xa[0]->shape()[1]; g.a2 = xa[0]->dev_f32(); g.lda2 = g.k2; g.b2 = bt[0]->dev_f32(); g.ldb2 = bt[0]->ld();
         g.a2_tensor = xa[0];
@@ -470,7 +477,7 @@ public:
             gx = Tensor::make(x_->shape(), kFloat32);
             GemmCall g;
             g.m = T; g.n = C; g.k = V;
-            g.a = gy->dev_f32(); g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
+            g.a = nullptr; g.lda = gy->ld(); g.trans_a = 0; g.a_tensor = gy;
             g.b = e_->dev_f32(); g.ldb = e_->ld(); g.trans_b = 0; g.b_weight = e_;   // E stored [k=V, n=C]
             g.c = gx->dev_f32_out(); g.ldc = C;
             run_gemm(g);
@@ -502,10 +509,11 @@ TensorPtr lm_head_tied(const TensorPtr& x_in, const TensorPtr& table) {
     auto y = Tensor::make(so, kFloat32, false, out_ld(V));
     GemmCall g;
     g.m = T; g.n = V; g.k = C;
-    g.a = x->dev_f32(); g.lda = C; g.trans_a = 0; g.a_tensor = x;
+    g.a = nullptr; g.lda = C; g.trans_a = 0; g.a_tensor = x;
     g.b = table->dev_f32(); g.ldb = table->ld(); g.trans_b = 1; g.b_weight = table;     // E [V,C] is K-major for x E^T
     g.c = y->dev_f32_out(); g.ldc = y->ld();
     run_gemm(g);
+    y->set_grad_may_be_bf16(!wants_grad(table));      // frozen table: dlogits only feeds the bf16 dX product
     track(y, {x_in, table}, std::make_shared<LmHeadBackward>(x, table));
     return y;
 }

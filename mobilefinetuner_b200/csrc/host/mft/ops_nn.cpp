@@ -1,6 +1,7 @@
 // Activations, normalisation, softmax, RoPE, GQA repeat, shape ops, reductions and the remaining API surface.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <stdexcept>
@@ -33,12 +34,27 @@ Emit emit16(const TensorPtr& t, bool need_dense_pitch) {
     return e;
 }
 
+// bf16-only result allowed? (bf16 operand mode, vectorisable layout, MFT_BF16_ONLY != 0)
+bool lowp_result_ok(const TensorPtr& y, int64_t dim) {
+    return bf16_only_results() && y->is_dense() && dim % 8 == 0;
+}
+
 class GeluBackward : public BackwardFunction {       // core/backward_functions.cpp:155-177
 public:
     explicit GeluBackward(TensorPtr x) : x_(std::move(x)) {}
     std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
         TensorPtr gy = contiguous(gy_in);
         auto gx = new_like(x_);
+        // the gradient arrived as a bf16-only GEMM result and leaves as a bf16 GEMM operand: stay in bf16 on both sides
+        // (x = the fp32 pre-activation); any fp32 reader of gx (bias / adapter gradients of fc_in) gets an upcast on demand
+        if (gy->f32_pending() && gy->has_bf16() && lowp_result_ok(gx, x_->shape().back()) && x_->numel() % 8 == 0) {
+            auto gv = gy->bf16_view();
+            if (gv.ld == gy->shape().back()) {
+                auto e = gx->bf16_only_out();
+                mft_rt::check(mft_gelu_bwd_lowp(x_->dev_f32(), 0, gv.ptr, nullptr, e.ptr, x_->numel(), st()), "mft_gelu_bwd_lowp");
+                return {gx};
+            }
+        }
         float* out = gx->dev_f32_out();
         const Emit e = emit16(gx, true);      // consumed by fc_in's dX product
         if (e.ptr) mft_rt::check(mft_gelu_bwd_ex(x_->dev_f32(), gy->dev_f32(), out, e.ptr, x_->numel(), st()), "mft_gelu_bwd_ex");
@@ -169,17 +185,27 @@ private:
 
 // core/ops.cpp:1404-1458
 TensorPtr layer_norm(const TensorPtr& x_in, const TensorPtr& weight, const TensorPtr& bias, float eps) {
+    return layer_norm_lowp(x_in, weight, bias, eps, false);
+}
+
+TensorPtr layer_norm_lowp(const TensorPtr& x_in, const TensorPtr& weight, const TensorPtr& bias, float eps, bool y_bf16_only) {
     require_f32(x_in, "layer_norm");
     if (!weight || !bias) throw TensorError("layer_norm: weight and bias are required");
     TensorPtr x = contiguous(x_in);
     const int64_t dim = x->shape().back(), rows = x->numel() / std::max<int64_t>(dim, 1);
     if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
     auto y = new_like(x);
-    float* yp = y->dev_f32_out();
-    const Emit e = emit16(y, false);          // LayerNorm outputs are GEMM inputs (qkv, fc_in, lm_head)
-    if (e.ptr) mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), nullptr, nullptr, weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows, dim, eps, st()),
-                             "mft_layernorm_fwd_ex");
-    else mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), yp, rows, dim, eps, st()), "mft_layernorm_fwd");
+    if (y_bf16_only && dim <= 2048 && lowp_result_ok(y, dim)) {          // the normalised rows are read as a bf16 GEMM operand only
+        auto e = y->bf16_only_out();
+        mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), nullptr, nullptr, weight->dev_f32(), bias->dev_f32(), nullptr, e.ptr, e.ld, rows, dim, eps, st()),
+                      "mft_layernorm_fwd_ex");
+    } else {
+        float* yp = y->dev_f32_out();
+        const Emit e = emit16(y, false);          // LayerNorm outputs are GEMM inputs (qkv, fc_in, lm_head)
+        if (e.ptr) mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), nullptr, nullptr, weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows, dim, eps, st()),
+                                 "mft_layernorm_fwd_ex");
+        else mft_rt::check(mft_layernorm_fwd(x->dev_f32(), weight->dev_f32(), bias->dev_f32(), yp, rows, dim, eps, st()), "mft_layernorm_fwd");
+    }
     track(y, {x_in, weight, bias}, std::make_shared<LayerNormBackward>(x, weight, bias, eps));
     return y;
 }
@@ -193,7 +219,8 @@ public:
 
 // sum = x + a and y = layer_norm(sum) from one kernel; both results carry the same autograd nodes as ops::add followed by
 // ops::layer_norm (graph/gpt2_model.cpp block forward: residual add, then ln_2 / the next block's ln_1 / ln_f).
-TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out) {
+TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const TensorPtr& weight, const TensorPtr& bias, float eps, TensorPtr* sum_out,
+                         bool y_bf16_only) {
     require_f32(x_in, "add_layer_norm");
     require_f32(a_in, "add_layer_norm");
     if (!weight || !bias || !sum_out) throw TensorError("add_layer_norm: weight, bias and sum_out are required");
@@ -203,10 +230,16 @@ TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const Ten
     if (weight->numel() != dim || bias->numel() != dim) throw TensorError("layer_norm: parameter size mismatch");
     auto sum = new_like(x);
     auto y = new_like(x);
-    float* yp = y->dev_f32_out();
-    const Emit e = emit16(y, false);
-    mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows,
-                                       dim, eps, st()), "mft_layernorm_fwd_ex");
+    if (y_bf16_only && dim <= 2048 && lowp_result_ok(y, dim)) {
+        auto e = y->bf16_only_out();
+        mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), nullptr, e.ptr, e.ld, rows,
+                                           dim, eps, st()), "mft_layernorm_fwd_ex");
+    } else {
+        float* yp = y->dev_f32_out();
+        const Emit e = emit16(y, false);
+        mft_rt::check(mft_layernorm_fwd_ex(x->dev_f32(), a->dev_f32(), sum->dev_f32_out(), weight->dev_f32(), bias->dev_f32(), yp, e.ptr, e.ld, rows,
+                                           dim, eps, st()), "mft_layernorm_fwd_ex");
+    }
     track(sum, {x_in, a_in}, std::make_shared<ResidualAddBackward>());
     track(y, {sum, weight, bias}, std::make_shared<LayerNormBackward>(sum, weight, bias, eps));
     *sum_out = sum;

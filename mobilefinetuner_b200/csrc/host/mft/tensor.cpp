@@ -122,6 +122,7 @@ TensorPtr Tensor::make(const std::vector<int64_t>& shape, DType dtype, bool zero
 // ---------------------------------------------------------------- host <-> device coherence
 void Tensor::ensure_host() const {
     if (!st_) throw TensorError("Tensor: no storage");
+    if (st_->f32_pending) (void)dev();          // the data exists as bf16 only: materialise the fp32 buffer first
     if (!st_->host) {
         st_->host = std::malloc(dense_bytes() ? dense_bytes() : 4);
         if (!st_->host) throw TensorError("Tensor: host mirror allocation failed");
@@ -153,6 +154,12 @@ const void* Tensor::dev() const {
         }
         st_->dev_valid = true;
     }
+    if (st_->f32_pending) {                      // produced as bf16 only: fill the fp32 buffer from it, once
+        st_->f32_pending = false;
+        if (numel() > 0)
+            mft_rt::check(mft_cast_from_bf16(st_->lowp->dev, st_->lowp_ld, static_cast<float*>(st_->dev), ld_, rows(), st_->lowp_cols, mft_rt::stream()),
+                          "mft_cast_from_bf16");
+    }
     return st_->dev;
 }
 void* Tensor::dev_mut() {
@@ -166,6 +173,7 @@ void* Tensor::dev_out() {
     ensure_dev();
     st_->dev_valid = true;
     st_->host_valid = false;
+    st_->f32_pending = false;
     ++st_->version;
     return st_->dev;
 }
@@ -199,13 +207,23 @@ Tensor::Bf16View Tensor::bf16_view() const {
     if (dtype_ != kFloat32) throw TensorError("bf16_view: float32 tensors only");
     const int64_t cols = shape_.empty() ? 1 : shape_.back(), r = rows();
     const int64_t ld = (cols + 7) / 8 * 8;
-    if (!bf16_ || bf16_version_ != version()) {
-        if (!bf16_) bf16_ = raw_buffer(size_t(r) * ld * 2, !st_->in_arena);
-        mft_rt::check(mft_cast_bf16(dev_f32(), ld_, bf16_->dev, ld, r, cols, mft_rt::stream()), "mft_cast_bf16");
-        bf16_version_ = version();
-        bf16_ld_ = ld;
+    if (bf16_ && bf16_version_ == version()) return {bf16_->dev, bf16_ld_};
+    if (st_->lowp && st_->lowp_version == version() && st_->lowp_cols == cols) {      // written by the producer (maybe through an alias)
+        bf16_ = st_->lowp; bf16_version_ = version(); bf16_ld_ = st_->lowp_ld;
+        return {bf16_->dev, bf16_ld_};
     }
+    if (!bf16_ || bf16_ == st_->lowp) bf16_ = raw_buffer(size_t(r) * ld * 2, !st_->in_arena);
+    mft_rt::check(mft_cast_bf16(dev_f32(), ld_, bf16_->dev, ld, r, cols, mft_rt::stream()), "mft_cast_bf16");
+    bf16_version_ = version();
+    bf16_ld_ = ld;
     return {bf16_->dev, bf16_ld_};
+}
+
+bool Tensor::has_bf16() const {
+    if (!st_ || dtype_ != kFloat32) return false;
+    if (bf16_ && bf16_version_ == version()) return true;
+    const int64_t cols = shape_.empty() ? 1 : shape_.back();
+    return st_->lowp && st_->lowp_version == version() && st_->lowp_cols == cols;
 }
 
 Tensor::Bf16Out Tensor::bf16_emit() {
@@ -215,7 +233,20 @@ Tensor::Bf16Out Tensor::bf16_emit() {
     if (!bf16_) bf16_ = raw_buffer(size_t(r) * ld * 2, !st_->in_arena);
     bf16_version_ = version();
     bf16_ld_ = ld;
+    st_->lowp = bf16_; st_->lowp_ld = ld; st_->lowp_cols = cols; st_->lowp_version = version();
     return {bf16_->dev, ld};
+}
+
+Tensor::Bf16Out Tensor::bf16_only_out() {
+    if (dtype_ != kFloat32) throw TensorError("bf16_only_out: float32 tensors only");
+    if (!st_) throw TensorError("Tensor: no storage");
+    ensure_dev();
+    st_->dev_valid = true;           // the device side is authoritative (as bf16, until somebody needs fp32)
+    st_->host_valid = false;
+    ++st_->version;
+    Bf16Out o = bf16_emit();
+    st_->f32_pending = true;
+    return o;
 }
 
 Tensor::Bf16View Tensor::bf16_transposed_view() const {

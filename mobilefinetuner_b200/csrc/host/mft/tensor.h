@@ -45,6 +45,13 @@ struct Storage {
     bool host_external = false;      // wrap mode: the caller owns `host`
     bool in_arena = false;           // allocated from the per-step arena (dies at the next arena_reset)
     uint64_t version = 0;            // bumped on every write access (device or host)
+    // bf16 copy written by the kernel that produced this buffer's current contents (version lowp_version). When
+    // f32_pending is set that copy is the ONLY one: the fp32 buffer has not been written and is filled from it (one upcast
+    // kernel) the first time anybody asks for fp32 data. Lives here, not on the Tensor, so reshaped aliases see it too.
+    std::shared_ptr<Storage> lowp;
+    int64_t lowp_ld = 0, lowp_cols = 0;
+    uint64_t lowp_version = ~0ull;
+    bool f32_pending = false;
     ~Storage();
 };
 }  // namespace detail
@@ -140,6 +147,17 @@ public:
     // on first use) and marks it valid for the tensor's current contents, so the next bf16_view() needs no cast kernel.
     struct Bf16Out { void* ptr; int64_t ld; };
     Bf16Out bf16_emit();
+    // For producers whose result is only ever needed as a bf16 GEMM / attention operand: like bf16_emit(), but the fp32
+    // buffer is NOT written (do not call dev_*_out()). Anything that later asks for the fp32 data (dev(), data<T>()) gets it
+    // through one upcast kernel, so correctness never depends on the guess; only the saved HBM traffic does.
+    Bf16Out bf16_only_out();
+    bool f32_pending() const { return st_ && st_->f32_pending; }
+    // true when bf16_view() costs nothing (a valid bf16 copy of the current contents exists)
+    bool has_bf16() const;
+    // hint set by the producer of an activation whose gradient consumer reads bf16 (the GELU backward kernel): the op that
+    // computes that gradient may then write it as bf16 only
+    void set_grad_may_be_bf16(bool v) { grad_may_be_bf16_ = v; }
+    bool grad_may_be_bf16() const { return grad_may_be_bf16_; }
 
 private:
     std::vector<int64_t> shape_;
@@ -152,6 +170,7 @@ private:
     TensorPtr grad_ = nullptr;
     GradFn grad_fn_ = nullptr;
     bool retain_grad_ = false;
+    bool grad_may_be_bf16_ = false;
     autograd::NodePtr grad_node_ = nullptr;
 
     mutable TensorPtr shadow_t_;

@@ -1,5 +1,6 @@
 // HBM-streaming elementwise / layout kernels: 128-bit vectorised, grid-stride, coalesced.
 // Each is bound by HBM bandwidth; algorithmic bytes per element are stated per kernel.
+#include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace mft {
@@ -179,6 +180,65 @@ __global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __rest
     }
 }
 
+// gx = gy * gelu'(x) with gy and gx as bf16 (the gradient arrives from a bf16-only GEMM result and feeds a bf16 GEMM
+// operand): x is read as fp32 (XBF16 = false: 4 B) or as the bf16 pre-activation (XBF16 = true: 2 B), plus 2 B read and 2 B
+// written per element. gx32 != NULL additionally writes the fp32 gradient. n % 8 == 0, 16-byte aligned.
+template <bool XBF16>
+__global__ void gelu_bwd_lowp_kernel(const void* __restrict__ xv, const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx32,
+                                     __nv_bfloat16* __restrict__ gx16, int64_t n) {
+    const int64_t n8 = n >> 3;
+    const uint4* g8 = reinterpret_cast<const uint4*>(gy);
+    uint4* o8 = reinterpret_cast<uint4*>(gx16);
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n8; i += int64_t(gridDim.x) * blockDim.x) {
+        float xs[8];
+        if (XBF16) {
+            const uint4 xr = __ldcs(reinterpret_cast<const uint4*>(xv) + i);
+            const __nv_bfloat162* xp = reinterpret_cast<const __nv_bfloat162*>(&xr);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(xp[e]); xs[2 * e] = f.x; xs[2 * e + 1] = f.y; }
+        } else {
+            const float4 a = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i), b = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i + 1);
+            xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
+        }
+        const uint4 gr = __ldcs(g8 + i);
+        const __nv_bfloat162* gp = reinterpret_cast<const __nv_bfloat162*>(&gr);
+        float r[8];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 g = __bfloat1622float2(gp[e]);
+            r[2 * e] = g.x * gelu_tanh_grad_f(xs[2 * e]);
+            r[2 * e + 1] = g.y * gelu_tanh_grad_f(xs[2 * e + 1]);
+        }
+        uint4 out;
+        __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&out);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) op[e] = __floats2bfloat162_rn(r[2 * e], r[2 * e + 1]);
+        __stcs(o8 + i, out);
+        if (gx32) {
+            st_stream(reinterpret_cast<float4*>(gx32) + 2 * i, make_float4(r[0], r[1], r[2], r[3]));
+            st_stream(reinterpret_cast<float4*>(gx32) + 2 * i + 1, make_float4(r[4], r[5], r[6], r[7]));
+        }
+    }
+}
+
+// bf16 -> fp32, row pitches in elements (fills the fp32 buffer of a tensor that was produced as bf16 only)
+__global__ void cast_from_bf16_kernel(const __nv_bfloat16* __restrict__ in, int64_t ldi, float* __restrict__ out, int64_t ldo, int64_t rows, int64_t cols) {
+    const int64_t c4 = (cols + 3) >> 2, n = rows * c4;
+    const bool vec = ((ldi & 3) == 0) && ((ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 7u) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = idx / c4, c = (idx % c4) << 2;
+        const __nv_bfloat16* src = in + r * ldi + c;
+        float* dst = out + r * ldo + c;
+        if (vec && c + 4 <= cols) {
+            const uint2 v = *reinterpret_cast<const uint2*>(src);
+            const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.x)), b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v.y));
+            *reinterpret_cast<float4*>(dst) = make_float4(a.x, a.y, b.x, b.y);
+        } else {
+            for (int e = 0; e < 4 && c + e < cols; ++e) dst[e] = __bfloat162float(src[e]);
+        }
+    }
+}
+
 // y = pow(x, p0) (kind 0) or clamp(x, p0, p1) (kind 1)
 __global__ void unary_param_kernel(int kind, const float* __restrict__ x, float* __restrict__ y, int64_t n, float p0, float p1) {
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
@@ -291,6 +351,27 @@ extern "C" int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void*
     gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, ok ? static_cast<__nv_bfloat16*>(gx_bf16) : nullptr);
     MFT_CHECK_LAUNCH("mft_gelu_bwd_ex");
     if (gx_bf16 && !ok) return mft_cast_bf16(gx, n, gx_bf16, n, 1, n, stream);
+    return 0;
+}
+
+// gy and gx in bf16 (x fp32, or bf16 when x_is_bf16); gx (fp32) may be NULL
+extern "C" int mft_gelu_bwd_lowp(const void* x, int x_is_bf16, const void* gy_bf16, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!x || !gy_bf16 || !gx_bf16) return set_error(1, "mft_gelu_bwd_lowp: null pointer");
+    if ((n & 7) || !aligned16(x) || !aligned16(gy_bf16) || !aligned16(gx_bf16) || (gx && !aligned16(gx)))
+        return set_error(1, "mft_gelu_bwd_lowp: n must be a multiple of 8 and every pointer 16-byte aligned");
+    const int grid = stream_grid(n, 256, 8);
+    if (x_is_bf16) gelu_bwd_lowp_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(x, static_cast<const __nv_bfloat16*>(gy_bf16), gx, static_cast<__nv_bfloat16*>(gx_bf16), n);
+    else gelu_bwd_lowp_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(x, static_cast<const __nv_bfloat16*>(gy_bf16), gx, static_cast<__nv_bfloat16*>(gx_bf16), n);
+    MFT_CHECK_LAUNCH("mft_gelu_bwd_lowp");
+    return 0;
+}
+
+extern "C" int mft_cast_from_bf16(const void* in, int64_t ldi, float* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream) {
+    if (rows == 0 || cols == 0) return 0;
+    if (!in || !out) return set_error(1, "mft_cast_from_bf16: null pointer");
+    cast_from_bf16_kernel<<<stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(in), ldi, out, ldo, rows, cols);
+    MFT_CHECK_LAUNCH("mft_cast_from_bf16");
     return 0;
 }
 

@@ -39,13 +39,16 @@ static int to_params(const mft_gemm_args* a, GemmParams& p) {
     p.addend = a->addend; p.ld_addend = a->ld_addend;
     p.gelu_grad_x = a->gelu_grad_x; p.ld_gelu_grad_x = a->ld_gelu_grad_x;
     p.gelu_out_bf16 = a->gelu_out_bf16; p.ld_gelu_out_bf16 = a->ld_gelu_out_bf16;
-    if (p.gelu_out_bf16 && (!p.gelu_out || p.batch > 1 || (p.ld_gelu_out_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.gelu_out_bf16) & 7u)))
-        return set_error(1, "mft_gemm: gelu_out_bf16 needs gelu_out, batch 1, an 8-byte aligned base and a pitch that is a multiple of 4");
+    p.c_bf16 = a->c_bf16; p.ldc_bf16 = a->ldc_bf16;
+    if (p.gelu_out_bf16 && (p.batch > 1 || (p.ld_gelu_out_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.gelu_out_bf16) & 7u)))
+        return set_error(1, "mft_gemm: gelu_out_bf16 needs batch 1, an 8-byte aligned base and a pitch that is a multiple of 4");
+    if (p.c_bf16 && (p.batch > 1 || p.ldc_bf16 < p.n || (p.ldc_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.c_bf16) & 7u)))
+        return set_error(1, "mft_gemm: c_bf16 needs batch 1, an 8-byte aligned base and a pitch >= n that is a multiple of 4");
     if (p.m == 0 || p.n == 0) return 0;
-    if (!p.c || (p.k > 0 && (!p.a || !p.b))) return set_error(1, "mft_gemm: null operand");
+    if ((!p.c && !p.c_bf16) || (p.k > 0 && (!p.a || !p.b))) return set_error(1, "mft_gemm: null operand");
     if (p.k2 > 0 && (!p.a2 || !p.b2)) return set_error(1, "mft_gemm: null second-segment operand");
     const int64_t min_lda = p.trans_a ? p.m : p.k, min_ldb = p.trans_b ? p.k : p.n;
-    if (p.lda < min_lda || p.ldb < min_ldb || p.ldc < p.n) return set_error(1, "mft_gemm: leading dimension too small");
+    if (p.lda < min_lda || p.ldb < min_ldb || (p.c && p.ldc < p.n)) return set_error(1, "mft_gemm: leading dimension too small");
     if (p.k2 > 0 && (p.lda2 < p.k2 || p.ldb2 < p.k2)) return set_error(1, "mft_gemm: second-segment ld too small");
     return 0;
 }
@@ -102,8 +105,10 @@ extern "C" int mft_gemm_splitk(const mft_gemm_args* args, int32_t splits, void* 
         p.ksplit = splits;
         p.partial = static_cast<float*>(workspace);
     }
+    if (!p.c || (p.gelu_out_bf16 && !p.gelu_out)) return set_error(1, "mft_gemm_splitk: the SIMT path needs the fp32 result buffers (bf16-only results are a tensor-core feature)");
     rc = launch_gemm_simt(p, as_stream(stream));
     if (rc == 0 && p.gelu_out_bf16) rc = mft_cast_bf16(p.gelu_out, p.ldc, p.gelu_out_bf16, p.ld_gelu_out_bf16, p.m, p.n, stream);   // SIMT path: separate cast
+    if (rc == 0 && p.c_bf16) rc = mft_cast_bf16(p.c, p.ldc, p.c_bf16, p.ldc_bf16, p.m, p.n, stream);
     return rc;
 }
 
@@ -113,8 +118,10 @@ extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
     if (rc) return rc;
     if (p.m == 0 || p.n == 0) return 0;
     if (g_use_tc && gemm_tc_eligible(p)) return launch_gemm_tc(p, as_stream(stream));
+    if (!p.c || (p.gelu_out_bf16 && !p.gelu_out)) return set_error(1, "mft_gemm: the SIMT path needs the fp32 result buffers (bf16-only results are a tensor-core feature)");
     rc = launch_gemm_simt(p, as_stream(stream));
     if (rc == 0 && p.gelu_out_bf16) rc = mft_cast_bf16(p.gelu_out, p.ldc, p.gelu_out_bf16, p.ld_gelu_out_bf16, p.m, p.n, stream);   // SIMT path: separate cast
+    if (rc == 0 && p.c_bf16) rc = mft_cast_bf16(p.c, p.ldc, p.c_bf16, p.ldc_bf16, p.m, p.n, stream);
     return rc;
 }
 

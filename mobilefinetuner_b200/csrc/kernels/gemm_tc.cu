@@ -63,7 +63,9 @@ struct TcArgs {
     const float* bias;
     const float* addend; int64_t ld_addend;
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;
-    __nv_bfloat16* gelu16; int64_t ld_gelu16;   // bf16 copy of the GELU aux output
+    __nv_bfloat16* gelu16; int64_t ld_gelu16;   // bf16 copy of the GELU aux output (gelu_out may be NULL: bf16 only)
+    __nv_bfloat16* c16; int64_t ld_c16;         // bf16 copy of C (c may be NULL on the TMA path: bf16 only)
+    int tma_c16;               // 1: c is NULL and the bf16 result leaves through 64-column TMA boxes (map_g)
     float alpha, beta;
     int tiles_m, tiles_n;
     int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
@@ -225,7 +227,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             (!p.gelu_out || (reinterpret_cast<uintptr_t>(p.gelu_out) & 15u) == 0) &&
                             (!p.addend || (((reinterpret_cast<uintptr_t>(p.addend) & 15u) | (p.ld_addend & 3)) == 0)) &&
                             (!p.gelu_grad_x || (((reinterpret_cast<uintptr_t>(p.gelu_grad_x) & 15u) | (p.ld_gelu_grad_x & 3)) == 0)) &&
-                            (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0);
+                            (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0) &&
+                            (!p.c16 || (((reinterpret_cast<uintptr_t>(p.c16) & 7u) | (p.ld_c16 & 3)) == 0));
         const bool use_tma = !FUSED && p.tma_c != 0;
         uint32_t nstore = 0;                              // boxes this warp has handed to the TMA (ring of two buffers)
         int it = 0;
@@ -281,7 +284,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                         for (int q = 0; q < 32; ++q) v[q] *= p.alpha;
                     }
-                    {
+                    if (p.tma_c16) {
+                        // bf16-only result: two 32-column chunks share one 64-column box (128 bytes of bf16 per row, same
+                        // 128B swizzle); the box leaves after its second half, or after the last chunk inside the matrix
+                        uint8_t* box = wbuf;
+                        if ((j & 1) == 0) {
+                            if (lane == 0) tma_store_wait_read<0>();
+                            __syncwarp();
+                        }
+                        uint8_t* rowp = box + lane * 128;
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * q], v[8 * q + 1]), h1 = __floats2bfloat162_rn(v[8 * q + 2], v[8 * q + 3]);
+                            const __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * q + 4], v[8 * q + 5]), h3 = __floats2bfloat162_rn(v[8 * q + 6], v[8 * q + 7]);
+                            *reinterpret_cast<uint4*>(rowp + ((((j & 1) * 4 + q) ^ (lane & 7)) << 4)) =
+                                make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                                           *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+                        }
+                        const bool last_chunk = (j == HC / 32 - 1) || (n0 + cc + 32 >= p.n);
+                        if ((j & 1) || last_chunk) {
+                            fence_proxy_async_smem();
+                            __syncwarp();
+                            if (lane == 0) { tma_store_3d(&map_g, box, n0 + (cc & ~63), row_base, bz); tma_store_commit(); }
+                        }
+                    } else {
                         uint8_t* box = wbuf + (nstore % kEpiBoxes) * kEpiBufBytes;
                         if (lane == 0) tma_store_wait_read<kEpiBoxes - 1>();      // the store that last used this box has read it
                         __syncwarp();
@@ -293,6 +319,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) { tma_store_3d(&map_c, box, n0 + cc, row_base, bz); tma_store_commit(); }
                         ++nstore;
+                        if (p.c16) {                                  // fp32 through the TMA, bf16 copy straight from registers
+                            const int grow = row_base + lane;
+                            if (grow < p.m) {
+                                __nv_bfloat16* d16 = p.c16 + int64_t(grow) * p.ld_c16 + n0 + cc;
+                                if (n0 + cc + 32 <= p.n) {
+#pragma unroll
+                                    for (int q = 0; q < 4; ++q) {
+                                        const __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * q], v[8 * q + 1]), h1 = __floats2bfloat162_rn(v[8 * q + 2], v[8 * q + 3]);
+                                        const __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * q + 4], v[8 * q + 5]), h3 = __floats2bfloat162_rn(v[8 * q + 6], v[8 * q + 7]);
+                                        *reinterpret_cast<uint4*>(d16 + 8 * q) = make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                                                                                           *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+                                    }
+                                } else {
+                                    for (int e = 0; e < 32 && n0 + cc + e < p.n; ++e) d16[e] = __float2bfloat16_rn(v[e]);
+                                }
+                            }
+                        }
                     }
                     if (gbase) {
                         uint8_t* box = wbuf + (nstore % kEpiBoxes) * kEpiBufBytes;
@@ -338,9 +381,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
                             }
                             *reinterpret_cast<float4*>(dst) = o;
-                            if (gbase) {
+                            if (p.c16) st_bf16x4(p.c16 + int64_t(grow) * p.ld_c16 + col, o);
+                            if (gbase || p.gelu16) {
                                 const float4 gv = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
-                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
+                                if (gbase) *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
                                 if (p.gelu16) st_bf16x4(p.gelu16 + int64_t(grow) * p.ld_gelu16 + col, gv);
                             }
                         }
@@ -387,9 +431,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 o.z *= gelu_tanh_grad_f(gx[q].z); o.w *= gelu_tanh_grad_f(gx[q].w);
                             }
                             *reinterpret_cast<float4*>(cbase + int64_t(grow) * p.ldc + col) = o;
-                            if (gbase) {
+                            if (p.c16) st_bf16x4(p.c16 + int64_t(grow) * p.ld_c16 + col, o);
+                            if (gbase || p.gelu16) {
                                 const float4 gv = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
-                                *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
+                                if (gbase) *reinterpret_cast<float4*>(gbase + int64_t(grow) * p.ldc + col) = gv;
                                 if (p.gelu16) st_bf16x4(p.gelu16 + int64_t(grow) * p.ld_gelu16 + col, gv);
                             }
                         }
@@ -410,9 +455,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             if (FUSED && abase) o += abase[int64_t(grow) * p.ld_addend + cc];
                             if (FUSED && xbase) o *= gelu_tanh_grad_f(xbase[int64_t(grow) * p.ld_gelu_grad_x + cc]);
                             *dst = o;
-                            if (gbase) {
+                            if (p.c16) p.c16[int64_t(grow) * p.ld_c16 + cc] = __float2bfloat16_rn(o);
+                            if (gbase || p.gelu16) {
                                 const float gv = gelu_tanh_f(o);
-                                gbase[int64_t(grow) * p.ldc + cc] = gv;
+                                if (gbase) gbase[int64_t(grow) * p.ldc + cc] = gv;
                                 if (p.gelu16) p.gelu16[int64_t(grow) * p.ld_gelu16 + cc] = __float2bfloat16_rn(gv);
                             }
                         }
@@ -496,10 +542,10 @@ static bool make_operand_map(CUtensorMap* out, const void* ptr, uint64_t inner, 
 
 // Output tensor [batch][rows][cols] fp32 (ld elements between rows): box = {32 cols, 32 rows, 1}, 128B swizzle, used by
 // the epilogue's cp.async.bulk.tensor stores (clipped at the edges, so ragged m / n need no predicates).
-static bool make_store_map(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld, uint64_t stride) {
+static bool make_store_map(CUtensorMap* out, const void* ptr, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld, uint64_t stride, bool bf16 = false) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
     static std::mutex mu;
-    MapKey key{ptr, cols, rows, batch, ld, stride, 32u, 2u};
+    MapKey key{ptr, cols, rows, batch, ld, stride, 32u, bf16 ? 3u : 2u};
     {
         std::lock_guard<std::mutex> lk(mu);
         auto it = cache.find(key);
@@ -510,10 +556,11 @@ static bool make_store_map(CUtensorMap* out, const void* ptr, uint64_t cols, uin
     alignas(64) CUtensorMap m;
     cuuint64_t dims[3] = {cols, rows, batch};
     if (batch == 1 || stride == 0) stride = rows * ld;
-    cuuint64_t strides[2] = {ld * 4, stride * 4};
-    cuuint32_t box[3] = {32, 32, 1};
+    const uint64_t es = bf16 ? 2 : 4;
+    cuuint64_t strides[2] = {ld * es, stride * es};
+    cuuint32_t box[3] = {bf16 ? 64u : 32u, 32, 1};                  // 128 bytes per box row either way
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    CUresult r = enc(&m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return false;
     {
@@ -593,17 +640,29 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     // (the GELU aux output stays on the register/STG path: with one epilogue warp per scheduler the tanh chains of a whole
     //  32-value row per thread run with no other warp to hide their latency, measured 125 us vs 81 us on fc_in)
     static const bool tma_gelu = [] { const char* e = getenv("MFT_GEMM_TMA_GELU"); return e && e[0] == '1'; }();
-    const bool c_ok = !FUSED && p.beta == 0.f && aligned16(p.c) && (p.ldc & 3) == 0 && (p.batch == 1 || (p.stride_c & 3) == 0) &&
-                      (!p.gelu_out || (tma_gelu && !p.gelu_out_bf16 && aligned16(p.gelu_out)));   // the box path writes no bf16 copy
+    const bool bf16_only = p.c == nullptr;                          // the result leaves as bf16 alone (64-column TMA boxes)
+    if (bf16_only) {
+        if (!p.c_bf16 || FUSED || p.beta != 0.f || p.gelu_out || p.gelu_out_bf16 || !aligned16(p.c_bf16) || (p.ldc_bf16 & 7) || p.batch != 1)
+            return set_error(1, "mft_gemm(tc): a bf16-only result needs c_bf16 (16-byte aligned, pitch %% 8 == 0), beta = 0, batch 1 and no GELU / fused operands");
+    }
+    const bool c_ok = !bf16_only && !FUSED && p.beta == 0.f && aligned16(p.c) && (p.ldc & 3) == 0 && (p.batch == 1 || (p.stride_c & 3) == 0) &&
+                      !p.gelu_out_bf16 && (!p.gelu_out || (tma_gelu && aligned16(p.gelu_out))) &&   // the box path writes no bf16 GELU copy
+                      (!p.c_bf16 || (p.batch == 1 && (p.ldc_bf16 & 7) == 0 && aligned16(p.c_bf16)));
     static const bool tma_store_on = [] { const char* e = getenv("MFT_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
     bool tma_c = c_ok && tma_store_on;
     if (tma_c) {
         tma_c = make_store_map(&mc, p.c, p.n, p.m, p.batch, p.ldc, p.stride_c) &&
                 (!p.gelu_out || make_store_map(&mg, p.gelu_out, p.n, p.m, p.batch, p.ldc, p.stride_c));
     }
-    if (!tma_c) { mc = ma; mg = ma; } else if (!p.gelu_out) mg = mc;
+    if (bf16_only) {
+        if (!make_store_map(&mg, p.c_bf16, p.n, p.m, 1, p.ldc_bf16, 0, true)) return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (bf16 result)");
+        mc = mg;
+        tma_c = true;
+    } else if (!tma_c) { mc = ma; mg = ma; } else if (!p.gelu_out) mg = mc;
     TcArgs a;
     a.tma_c = tma_c ? 1 : 0;
+    a.tma_c16 = bf16_only ? 1 : 0;
+    a.c16 = bf16_only ? nullptr : static_cast<__nv_bfloat16*>(p.c_bf16); a.ld_c16 = p.ldc_bf16;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;

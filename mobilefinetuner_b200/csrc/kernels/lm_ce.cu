@@ -91,22 +91,23 @@ lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __
                  const float* __restrict__ row_lse, const int32_t* __restrict__ valid, const float* __restrict__ gout,
                  int64_t rows, int S, int V, int ignore_index, int reduction, float* __restrict__ dlogits, int64_t ldg,
                  __nv_bfloat16* __restrict__ d16, int64_t ld16) {   // d16 != NULL: bf16 copy of dlogits (vectorised path only)
-    const bool vec = ((ld & 3) == 0) && ((ldg & 3) == 0) &&
+    // dlogits == NULL: the bf16 copy is the only result (launcher guarantees the vectorised layout then)
+    const bool vec = ((ld & 3) == 0) && (!dlogits || (ldg & 3) == 0) &&
                      (((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15u) == 0);
     const int cnt = valid[0];
     const float g = gout ? gout[0] : 1.0f;
     const float scale = (reduction == 1) ? g : (cnt > 0 ? g / float(cnt) : 0.0f);
     for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
         const int y = ce_label(labels, row, S, V, ignore_index);
-        float* d = dlogits + row * ldg;
+        float* d = dlogits ? dlogits + row * ldg : nullptr;
         __nv_bfloat16* h = d16 ? d16 + row * ld16 : nullptr;
         if (y < 0) {   // skipped rows get an all-zero gradient (core/lm_loss.cpp:45-52)
             if (vec) {
                 float4* d4 = reinterpret_cast<float4*>(d);
                 const int v4 = V >> 2;
                 const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int i = threadIdx.x; i < v4; i += kCeThreads) { st_stream(d4 + i, z); if (h) st_bf16x4(h + i * 4, z); }
-                for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) { d[i] = 0.f; if (h) h[i] = __float2bfloat16_rn(0.f); }
+                for (int i = threadIdx.x; i < v4; i += kCeThreads) { if (d) st_stream(d4 + i, z); if (h) st_bf16x4(h + i * 4, z); }
+                for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) { if (d) d[i] = 0.f; if (h) h[i] = __float2bfloat16_rn(0.f); }
             } else {
                 for (int i = threadIdx.x; i < V; i += kCeThreads) d[i] = 0.f;
             }
@@ -127,13 +128,13 @@ lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __
                     if (y == base) r.x -= scale; else if (y == base + 1) r.y -= scale;
                     else if (y == base + 2) r.z -= scale; else r.w -= scale;
                 }
-                st_stream(d4 + i, r);
+                if (d) st_stream(d4 + i, r);
                 if (h) st_bf16x4(h + i * 4, r);
             }
             for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) {
                 float r = expf(x[i] - lse) * scale;
                 if (i == y) r -= scale;
-                d[i] = r;
+                if (d) d[i] = r;
                 if (h) h[i] = __float2bfloat16_rn(r);
             }
         } else {
@@ -176,13 +177,14 @@ extern "C" int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* lab
 static int ce_bwd_impl(const float* logits, int64_t ld, const int32_t* labels, const float* row_lse,
                        const int32_t* valid, const float* gout, int32_t B, int32_t S, int32_t V,
                        int32_t ignore_index, int32_t reduction, float* dlogits, int64_t ldg, void* d16, int64_t ld16, mft_stream_t stream) {
-    if (!logits || !labels || !row_lse || !valid || !dlogits) return set_error(1, "mft_lm_ce_bwd: null pointer");
-    if (ld < V || ldg < V || (d16 && ld16 < V)) return set_error(1, "mft_lm_ce_bwd: leading dimension < V");
+    if (!logits || !labels || !row_lse || !valid || (!dlogits && !d16)) return set_error(1, "mft_lm_ce_bwd: null pointer");
+    if (ld < V || (dlogits && ldg < V) || (d16 && ld16 < V)) return set_error(1, "mft_lm_ce_bwd: leading dimension < V");
     const int64_t rows = int64_t(B) * S;
     if (rows == 0 || V == 0) return 0;
     // the bf16 copy is written by the vectorised path; other layouts get a separate cast
-    const bool vec = ((ld & 3) == 0) && ((ldg & 3) == 0) && aligned16(logits) && aligned16(dlogits);
+    const bool vec = ((ld & 3) == 0) && (!dlogits || (ldg & 3) == 0) && aligned16(logits) && (!dlogits || aligned16(dlogits));
     const bool fused16 = d16 && vec && (ld16 & 3) == 0 && (reinterpret_cast<uintptr_t>(d16) & 7u) == 0;
+    if (!dlogits && !fused16) return set_error(1, "mft_lm_ce_bwd_ex: a bf16-only gradient needs 16-byte aligned logits with a pitch %% 4 == 0 and an 8-byte aligned bf16 buffer with a pitch %% 4 == 0");
     int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
     lm_ce_bwd_kernel<<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V,
                                                                 ignore_index, reduction, dlogits, ldg,

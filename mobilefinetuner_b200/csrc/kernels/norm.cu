@@ -58,7 +58,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                 o.y = (v[j].y - mean) * rstd * g.y + b.y;
                 o.z = (v[j].z - mean) * rstd * g.z + b.z;
                 o.w = (v[j].w - mean) * rstd * g.w + b.w;
-                st_stream(yr + c, o);
+                if (y) st_stream(yr + c, o);                 // y == NULL: the bf16 copy is the only result
                 if (y16) st_bf16x4(y16 + r * ld16 + c * 4, o);
             }
         }
@@ -397,9 +397,9 @@ using namespace mft;
 static int ln_fwd_impl(const char* who, const float* x, const float* add, float* sum_out, const float* gamma, const float* beta, float* y,
                        int64_t rows, int64_t dim, float eps, mft_stream_t stream, void* y16 = nullptr, int64_t ld16 = 0) {
     if (rows == 0 || dim == 0) return 0;
-    if (!x || !gamma || !beta || !y || (add && !sum_out)) return set_error(1, "%s: null pointer", who);
+    if (!x || !gamma || !beta || (!y && !y16) || (add && !sum_out)) return set_error(1, "%s: null pointer", who);
     cudaStream_t st = as_stream(stream);
-    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) &&
+    const bool vec = (dim % 4 == 0) && dim <= 2048 && aligned16(x) && (!y || aligned16(y)) && aligned16(gamma) && aligned16(beta) &&
                      (!add || (aligned16(add) && aligned16(sum_out))) &&
                      (!y16 || ((reinterpret_cast<uintptr_t>(y16) & 7u) == 0 && (ld16 & 3) == 0));
     if (vec) {
@@ -411,6 +411,7 @@ static int ln_fwd_impl(const char* who, const float* x, const float* add, float*
         else if (nv <= 8) launch_ln_fwd<8>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
         else launch_ln_fwd<16>(x, gamma, beta, y, rows, int(dim), eps, st, add, sum_out, y16, ld16);
     } else {
+        if (!y) return set_error(1, "%s: a bf16-only result needs dim %% 4 == 0, dim <= 2048 and 16-byte aligned tensors", who);
         const float* src = x;
         if (add) {   // unaligned / wide rows: separate add, then the generic kernel on the sum
             int rc = mft_binary(0, x, add, sum_out, 1, 1, rows * dim, 0, 1, stream);

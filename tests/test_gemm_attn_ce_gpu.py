@@ -472,3 +472,88 @@ def test_clip_and_multitensor_adam(capi):
     g_before = dg[0].clone()
     capi.call("mft_scale_grads", slots, len(P), scale, None)
     assert rel(dg[0], g_before.cpu().numpy() * es) < 1e-7
+
+
+# ----------------------------------------------------------------------------- bf16 results (bf16 operand mode, tcgen05 epilogue)
+@pytest.mark.parametrize("m,n,k", [(512, 768, 256), (300, 1000, 128), (128, 64, 64), (4096, 3072, 1024), (260, 200, 96)])
+def test_gemm_bf16_result_only_and_copy(capi, m, n, k):
+    """c = NULL + c_bf16: the bf16 values are the round-to-nearest of what the fp32 epilogue produces; c + c_bf16: both."""
+    rng = np.random.default_rng(m + n + k)
+    a = torch.tensor(rng.standard_normal((m, k)).astype(np.float32)).cuda().to(torch.bfloat16)
+    b = torch.tensor((rng.standard_normal((n, k)) * 0.1).astype(np.float32)).cuda().to(torch.bfloat16)
+    bias = torch.tensor(rng.standard_normal(n).astype(np.float32)).cuda()
+    ldc = (n + 3) // 4 * 4
+    ld16 = (n + 7) // 8 * 8
+    c32 = torch.zeros(m, ldc, device="cuda")
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c32.data_ptr(), ldc, 0.5, 0.0, bias.data_ptr(), None, 0, None, 0, None, 0, 1, 0, 0, 0)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    expect = c32[:, :n].to(torch.bfloat16)
+    only = torch.zeros(m, ld16, device="cuda", dtype=torch.bfloat16)
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, None, 0, 0.5, 0.0, bias.data_ptr(), None, 0, None, 0, None, 0, 1, 0, 0, 0,
+                         None, 0, None, 0, None, 0, only.data_ptr(), ld16)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    torch.cuda.synchronize()
+    assert torch.equal(only[:, :n], expect)
+    if ld16 > n:
+        assert float(only[:, n:].float().abs().max()) == 0.0          # the TMA clips at the matrix edge: padding untouched
+    both32, both16 = torch.zeros(m, ldc, device="cuda"), torch.zeros(m, ld16, device="cuda", dtype=torch.bfloat16)
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, both32.data_ptr(), ldc, 0.5, 0.0, bias.data_ptr(), None, 0, None, 0, None, 0, 1, 0, 0, 0,
+                         None, 0, None, 0, None, 0, both16.data_ptr(), ld16)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    torch.cuda.synchronize()
+    assert torch.equal(both32, c32) and torch.equal(both16[:, :n], expect)
+
+
+def test_gemm_bf16_gelu_activation_as_bf16_only(capi):
+    rng = np.random.default_rng(3)
+    m, n, k = 512, 1024, 256
+    a = torch.tensor(rng.standard_normal((m, k)).astype(np.float32)).cuda().to(torch.bfloat16)
+    b = torch.tensor((rng.standard_normal((n, k)) * 0.1).astype(np.float32)).cuda().to(torch.bfloat16)
+    pre, act, act16 = torch.zeros(m, n, device="cuda"), torch.zeros(m, n, device="cuda"), torch.zeros(m, n, device="cuda", dtype=torch.bfloat16)
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, pre.data_ptr(), n, 1.0, 0.0, None, act.data_ptr(), 0, None, 0, None, 0, 1, 0, 0, 0)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    pre2 = torch.zeros(m, n, device="cuda")
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, pre2.data_ptr(), n, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0,
+                         None, 0, None, 0, act16.data_ptr(), n)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    torch.cuda.synchronize()
+    assert torch.equal(pre, pre2) and torch.equal(act16, act.to(torch.bfloat16))
+
+
+def test_lowp_elementwise_kernels(capi):
+    """mft_cast_from_bf16, mft_gelu_bwd_lowp (fp32 / bf16 pre-activation), LayerNorm and CE backward with bf16-only results."""
+    rng = np.random.default_rng(11)
+    n = 4096 * 24
+    x = rng.standard_normal(n).astype(np.float32)
+    gy = rng.standard_normal(n).astype(np.float32)
+    dx, dgy16 = dev(x), dev(gy).to(torch.bfloat16)
+    gx16, gx32 = torch.empty(n, device="cuda", dtype=torch.bfloat16), torch.empty(n, device="cuda")
+    capi.call("mft_gelu_bwd_lowp", dx, 0, dgy16, gx32, gx16, n, None)
+    e = O.gelu_bwd(x, dgy16.float().cpu().numpy())
+    assert rel(gx32, e) < FP32_TOL and torch.equal(gx16, gx32.to(torch.bfloat16))
+    x16 = dx.to(torch.bfloat16)
+    capi.call("mft_gelu_bwd_lowp", x16, 1, dgy16, None, gx16, n, None)
+    assert rel(gx16.float(), O.gelu_bwd(x16.float().cpu().numpy(), dgy16.float().cpu().numpy())) < 5e-3
+    src = torch.tensor(rng.standard_normal((37, 104)).astype(np.float32)).cuda().to(torch.bfloat16)       # pitched: 100 of 104 columns
+    out = torch.zeros(37, 100, device="cuda")
+    capi.call("mft_cast_from_bf16", src, 104, out, 100, 37, 100, None)
+    assert torch.equal(out, src[:, :100].float())
+    # LayerNorm with the bf16 copy as the only result
+    rows, dim = 300, 1024
+    xx, g, b = (rng.standard_normal((rows, dim)).astype(np.float32), rng.standard_normal(dim).astype(np.float32), rng.standard_normal(dim).astype(np.float32))
+    y32, y16a, y16b = torch.empty(rows, dim, device="cuda"), torch.empty(rows, dim, device="cuda", dtype=torch.bfloat16), torch.empty(rows, dim, device="cuda", dtype=torch.bfloat16)
+    capi.call("mft_layernorm_fwd_ex", dev(xx), None, None, dev(g), dev(b), y32, y16a, dim, rows, dim, 1e-5, None)
+    capi.call("mft_layernorm_fwd_ex", dev(xx), None, None, dev(g), dev(b), None, y16b, dim, rows, dim, 1e-5, None)
+    assert torch.equal(y16a, y16b) and torch.equal(y16a, y32.to(torch.bfloat16))
+    # CE backward with dlogits as bf16 only
+    B, S, V = 2, 9, 1000
+    logits = rng.standard_normal((B, S, V)).astype(np.float32)
+    labels = rng.integers(0, V, (B, S)).astype(np.int32)
+    dl, dlab = dev(logits), torch.tensor(labels).cuda()
+    loss, valid, lse = torch.zeros(1, device="cuda"), torch.zeros(1, dtype=torch.int32, device="cuda"), torch.empty(B * S, device="cuda")
+    w = ws(capi.lib.mft_lm_ce_workspace_bytes(B * S))
+    capi.call("mft_lm_ce_fwd", dl, V, dlab, B, S, V, -100, 0, loss, valid, lse, w, w.numel(), None)
+    g32, g16a, g16b = torch.empty(B * S, V, device="cuda"), torch.empty(B * S, V, device="cuda", dtype=torch.bfloat16), torch.empty(B * S, V, device="cuda", dtype=torch.bfloat16)
+    capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, g32, V, g16a, V, None)
+    capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, None, 0, g16b, V, None)
+    assert torch.equal(g16a, g16b) and torch.equal(g16a, g32.to(torch.bfloat16))

@@ -135,6 +135,7 @@ def test_bf16_operands_written_by_producers_equal_cast_on_demand():
     hostlib.mft_host_set_gemm_precision(1)
     try:
         out = []
+        os.environ["MFT_BF16_ONLY"] = "0"        # both runs keep every fp32 result: only the way the bf16 copy is made differs
         for emit in ("0", "1"):
             os.environ["MFT_BF16_EMIT"] = emit
             tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096)
@@ -145,6 +146,31 @@ def test_bf16_operands_written_by_producers_equal_cast_on_demand():
         assert out[1][2] <= out[0][2] - 50, (out[0][2], out[1][2])
     finally:
         os.environ.pop("MFT_BF16_EMIT", None)
+        os.environ.pop("MFT_BF16_ONLY", None)
+        hostlib.mft_host_set_gemm_precision(0)
+
+
+@pytest.mark.tf32
+def test_bf16_only_results_stay_within_tolerance_of_keeping_every_fp32_copy():
+    """bf16 operand mode: results that are consumed only as bf16 operands (qkv for the tcgen05 attention, ln_2 rows, the GELU
+    activation and its gradient, dlogits) are written as bf16 alone. Against the same run with every fp32 copy kept
+    (MFT_BF16_ONLY=0) the loss moves by rounding only, with fewer bytes written; GPT-2 small LoRA r8, 4 x 128."""
+    from mobilefinetuner_b200.trainer import Trainer, hostlib
+    hostlib.mft_host_set_gemm_precision(1)
+    try:
+        out = []
+        for only in ("0", "1"):
+            os.environ["MFT_BF16_ONLY"] = only
+            tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096)
+            losses = [tr.step_numpy(tr.next_synthetic_batch()) for _ in range(6)]
+            out.append((losses, tr.grad_norm(), tr.num_with_grad))
+            tr.close()
+        for a, b in zip(out[0][0], out[1][0]):
+            assert abs(a - b) <= 2e-4 * a, (out[0][0], out[1][0])
+        assert abs(out[0][1] - out[1][1]) <= 2e-2 * out[0][1]
+        assert out[0][2] == out[1][2]
+    finally:
+        os.environ.pop("MFT_BF16_ONLY", None)
         hostlib.mft_host_set_gemm_precision(0)
 
 

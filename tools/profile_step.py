@@ -22,11 +22,14 @@ def main():
     ap.add_argument("--config", default="c4", choices=sorted(bench.CONFIGS))
     ap.add_argument("--warm", type=int, default=3)
     ap.add_argument("--steps", type=int, default=1)
-    ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"])
+    ap.add_argument("--precision", default="bf16", choices=["tf32", "bf16"])
+    ap.add_argument("--batch", type=int, default=0, help="sequences per step (default: the config's per-GPU batch)")
     a = ap.parse_args()
     hostlib.mft_host_set_gemm_precision(1 if a.precision == "bf16" else 0)
-    shape, batch, seq, full_ft, r, alpha, _ = bench.CONFIGS[a.config]
-    tr = Trainer(batch, seq, shape=shape, full_finetune=full_ft, lora_rank=r, lora_alpha=alpha, seed=1234, cuda_graph=False)
+    c = bench.CONFIGS[a.config]
+    batch, seq = (a.batch or c["batch"]), c["seq"]
+    tr = Trainer(batch, seq, shape=c["shape"], full_finetune=c["full"], lora_rank=c["rank"], lora_alpha=c["alpha"], seed=1234, cuda_graph=False,
+                 arena_mb=int((bench.ARENA_GIB_PER_SEQ[a.config] * batch + 3) * 1024))
     ids = torch.from_numpy(np.random.default_rng(0).integers(0, tr.cfg.vocab_size, (batch, seq)).astype(np.int32)).cuda()
     for _ in range(a.warm):
         tr.step_device(ids.data_ptr())
