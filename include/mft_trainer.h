@@ -85,6 +85,13 @@ int mft_host_true_gradients(void);
 int mft_trainer_accumulate(mft_trainer* t, const int32_t* dev_ids);
 int mft_trainer_apply_accumulated(mft_trainer* t);
 
+/* Checkpoint for resuming a run: every trainable tensor, both Adam moments and the per-tensor step counters, as one
+ * safetensors file ("param.<i>", "adam.<i>.m", "adam.<i>.v", metadata "adam.<i>.step"). The reference saves adapters
+ * (graph/lora_saver.cpp) but its optimizer state never round-trips (optim/adam.cpp:142-164 reads a header only); a run
+ * resumed from this file continues bit for bit like the uninterrupted one. Both calls synchronise. */
+int mft_trainer_save_state(mft_trainer* t, const char* path);
+int mft_trainer_load_state(mft_trainer* t, const char* path);
+
 /* Introspection for tests / reports. */
 int32_t mft_trainer_num_trainable(mft_trainer* t);
 int32_t mft_trainer_num_with_grad(mft_trainer* t);       /* tensors that received a gradient in the last step */

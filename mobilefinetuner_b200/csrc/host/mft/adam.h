@@ -28,8 +28,14 @@ public:
     ~Adam() override;
 
     void step(const std::vector<TensorPtr>& parameters, const std::vector<TensorPtr>& gradients) override;
+    // Optimizer-state checkpoint. The reference writes an unordered dump and its load_state reads the
+    // header only (optim/adam.cpp:92-164); here the state is a safetensors file keyed by the POSITION of each tensor in
+    // the parameter list of the last step(): "adam.<i>.m", "adam.<i>.v" (F32) and metadata "adam.<i>.step", "num_params",
+    // "lr", "beta1", "beta2", "eps", "weight_decay". load_state() keeps the loaded moments until the next step() (or
+    // bind_state()) sees the parameter list and attaches entry i to parameters[i] (sizes must match).
     void save_state(const std::string& path) const override;
     void load_state(const std::string& path) override;
+    void bind_state(const std::vector<TensorPtr>& parameters);
     void set_learning_rate(float new_lr) override { adam_config_.learning_rate = new_lr; }
     float get_learning_rate() const override { return adam_config_.learning_rate; }
 
@@ -44,6 +50,8 @@ protected:
 private:
     AdamConfig adam_config_;
     std::unordered_map<TensorPtr, AdamState> states_;
+    std::vector<TensorPtr> order_;                 // parameter list of the last step (checkpoint order)
+    std::vector<AdamState> loaded_;                // states read by load_state, not yet attached to tensors
     void* dev_slots_ = nullptr;
     size_t dev_slots_bytes_ = 0;
     void init_state(const TensorPtr& param);

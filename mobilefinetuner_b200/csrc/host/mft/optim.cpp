@@ -3,7 +3,9 @@
 #include <cstring>
 #include <stdexcept>
 
+#include <map>
 #include "adam.h"
+#include "safetensors_loader.h"
 #include "mft_b200.h"
 #include "optimizer.h"
 #include "runtime.h"
@@ -127,6 +129,8 @@ void Adam::step_scaled(const std::vector<TensorPtr>& parameters, const std::vect
 void Adam::step_device(const std::vector<TensorPtr>& parameters, const std::vector<float*>& gradients, const float* dev_grad_scale) {
     if (parameters.size() != gradients.size()) throw std::runtime_error("Parameters and gradients size mismatch");
     if (adam_config_.amsgrad) throw std::runtime_error("Adam: amsgrad is not implemented on the B200 path");
+    if (!loaded_.empty()) bind_state(parameters);
+    order_ = parameters;
     std::vector<TensorPtr> m(parameters.size()), v(parameters.size());
     std::vector<float> bc1(parameters.size(), 1.f), bc2(parameters.size(), 1.f);
     bool any = false;
@@ -149,10 +153,62 @@ void Adam::step_device(const std::vector<TensorPtr>& parameters, const std::vect
 
 void Adam::update_param(TensorPtr param, const TensorPtr& grad, OptimizerState&) { step({param}, {grad}); }
 
-// Optimizer-state checkpointing is outside the hot-path scope (the reference's own
-// load_state only reads a header, optim/adam.cpp:142-164).
-void Adam::save_state(const std::string&) const { throw std::runtime_error("Adam::save_state: not implemented in this build"); }
-void Adam::load_state(const std::string&) { throw std::runtime_error("Adam::load_state: not implemented in this build"); }
+// Optimizer-state checkpoint: see adam.h. Moments are read back through the tensors' host mirrors (one D2H each).
+void Adam::save_state(const std::string& path) const {
+    std::map<std::string, TensorPtr> tensors;
+    std::vector<std::pair<std::string, std::string>> meta;
+    meta.emplace_back("format", "mft_adam_state_v1");
+    meta.emplace_back("num_params", std::to_string(order_.size()));
+    meta.emplace_back("lr", std::to_string(adam_config_.learning_rate));
+    meta.emplace_back("beta1", std::to_string(adam_config_.beta1));
+    meta.emplace_back("beta2", std::to_string(adam_config_.beta2));
+    meta.emplace_back("eps", std::to_string(adam_config_.epsilon));
+    meta.emplace_back("weight_decay", std::to_string(adam_config_.weight_decay));
+    for (size_t i = 0; i < order_.size(); ++i) {
+        auto it = states_.find(order_[i]);
+        if (it == states_.end()) continue;               // never received a gradient: no state, step 0
+        const std::string k = "adam." + std::to_string(i);
+        tensors[k + ".m"] = it->second.m[0];
+        tensors[k + ".v"] = it->second.v[0];
+        meta.emplace_back(k + ".step", std::to_string(it->second.step));
+    }
+    write_safetensors(path, tensors, meta);
+}
+
+void Adam::load_state(const std::string& path) {
+    SafeTensorsReader rd(path);
+    rd.parse_header();
+    const auto& md = rd.metadata();
+    auto fmt = md.find("format");
+    if (fmt == md.end() || fmt->second != "mft_adam_state_v1") throw std::runtime_error("Adam::load_state: " + path + " is not an Adam state file");
+    const size_t n = size_t(std::stoul(md.at("num_params")));
+    loaded_.assign(n, AdamState{});
+    mft_rt::PersistentScope keep;
+    for (size_t i = 0; i < n; ++i) {
+        const std::string k = "adam." + std::to_string(i);
+        auto st = md.find(k + ".step");
+        if (st == md.end()) continue;
+        loaded_[i].step = size_t(std::stoul(st->second));
+        loaded_[i].m.push_back(rd.load_tensor(k + ".m"));
+        loaded_[i].v.push_back(rd.load_tensor(k + ".v"));
+    }
+    states_.clear();
+    if (!order_.empty()) bind_state(order_);
+}
+
+void Adam::bind_state(const std::vector<TensorPtr>& parameters) {
+    if (loaded_.empty()) return;
+    if (loaded_.size() != parameters.size())
+        throw std::runtime_error("Adam: the loaded state holds " + std::to_string(loaded_.size()) + " entries, the parameter list " + std::to_string(parameters.size()));
+    for (size_t i = 0; i < parameters.size(); ++i) {
+        if (loaded_[i].m.empty()) continue;
+        if (loaded_[i].m[0]->numel() != parameters[i]->numel()) throw std::runtime_error("Adam: loaded state " + std::to_string(i) + " does not match its parameter's size");
+        states_[parameters[i]] = std::move(loaded_[i]);
+    }
+    loaded_.clear();
+    order_ = parameters;
+}
+
 void AdamState::to_file(const std::string&) const { throw std::runtime_error("AdamState::to_file: not implemented in this build"); }
 void AdamState::from_file(const std::string&) { throw std::runtime_error("AdamState::from_file: not implemented in this build"); }
 

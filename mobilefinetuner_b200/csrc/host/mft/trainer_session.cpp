@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <random>
 #include <string>
@@ -24,6 +25,7 @@
 #include "ops.h"
 #include "ops_internal.h"
 #include "runtime.h"
+#include "safetensors_loader.h"
 
 using namespace ops;
 
@@ -436,6 +438,61 @@ extern "C" int mft_trainer_apply_accumulated(mft_trainer* t) {
         t->accum_count = 0;
         return 0;
     } catch (const std::exception& e) { t->extra_grad_scale = 1.0f; return fail("mft_trainer_apply_accumulated: %s", e.what()); }
+}
+
+// ---- checkpoint of everything a resumed run needs: trainable tensors, Adam moments and per-tensor step counters
+// (the reference saves adapters, graph/lora_saver.cpp, but no optimizer state: optim/adam.cpp:142-164)
+extern "C" int mft_trainer_save_state(mft_trainer* t, const char* path) {
+    if (!t || !path) return fail("mft_trainer_save_state: null argument");
+    try {
+        mft_rt::sync();
+        const size_t n = t->trainable.size();
+        std::vector<int32_t> steps(n + 4, 0);
+        mft_rt::d2h(steps.data(), t->steps_dev, n * sizeof(int32_t));
+        std::map<std::string, TensorPtr> tensors;
+        std::vector<std::pair<std::string, std::string>> meta;
+        meta.emplace_back("format", "mft_trainer_state_v1");
+        meta.emplace_back("num_params", std::to_string(n));
+        for (size_t i = 0; i < n; ++i) {
+            const std::string k = std::to_string(i);
+            tensors["param." + k] = t->trainable[i];
+            tensors["adam." + k + ".m"] = t->m[i];
+            tensors["adam." + k + ".v"] = t->v[i];
+            meta.emplace_back("adam." + k + ".step", std::to_string(steps[i]));
+        }
+        write_safetensors(path, tensors, meta);
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_save_state: %s", e.what()); }
+}
+
+extern "C" int mft_trainer_load_state(mft_trainer* t, const char* path) {
+    if (!t || !path) return fail("mft_trainer_load_state: null argument");
+    try {
+        mft_rt::sync();
+        SafeTensorsReader rd(path);
+        rd.parse_header();
+        const auto& md = rd.metadata();
+        auto fmt = md.find("format");
+        if (fmt == md.end() || fmt->second != "mft_trainer_state_v1") return fail("mft_trainer_load_state: %s is not a trainer state file", path);
+        const size_t n = t->trainable.size();
+        if (size_t(std::stoul(md.at("num_params"))) != n) return fail("mft_trainer_load_state: the file holds %s tensors, the trainer %zu", md.at("num_params").c_str(), n);
+        std::vector<int32_t> steps(n + 4, 0);
+        auto fill = [](const TensorPtr& dst, const TensorPtr& src, const char* what, size_t i) {
+            if (dst->numel() != src->numel()) throw std::runtime_error(std::string("size mismatch for ") + what + " " + std::to_string(i));
+            std::memcpy(dst->data<float>(), static_cast<const Tensor&>(*src).data<float>(), size_t(dst->numel()) * sizeof(float));
+            (void)dst->dev();        // upload now; the write bumped the version, so cached K-major / bf16 shadows are rebuilt
+        };
+        for (size_t i = 0; i < n; ++i) {
+            const std::string k = std::to_string(i);
+            fill(t->trainable[i], rd.load_tensor("param." + k), "param", i);
+            fill(t->m[i], rd.load_tensor("adam." + k + ".m"), "adam m", i);
+            fill(t->v[i], rd.load_tensor("adam." + k + ".v"), "adam v", i);
+            steps[i] = int32_t(std::stol(md.at("adam." + k + ".step")));
+        }
+        mft_rt::h2d(t->steps_dev, steps.data(), n * sizeof(int32_t));
+        mft_rt::sync();              // `steps` is a stack buffer
+        return 0;
+    } catch (const std::exception& e) { return fail("mft_trainer_load_state: %s", e.what()); }
 }
 
 extern "C" void mft_host_set_true_gradients(int enable) { ops::internal::set_true_gradients(enable != 0); }

@@ -49,6 +49,8 @@ TRAINER_SIGNATURES = {
     "mft_host_true_gradients": (C.c_int, []),
     "mft_trainer_accumulate": (C.c_int, [vp, vp]),
     "mft_trainer_apply_accumulated": (C.c_int, [vp]),
+    "mft_trainer_save_state": (C.c_int, [vp, C.c_char_p]),
+    "mft_trainer_load_state": (C.c_int, [vp, C.c_char_p]),
     "mft_trainer_num_trainable": (i32, [vp]),
     "mft_trainer_num_with_grad": (i32, [vp]),
     "mft_trainer_kernel_launches": (i64, [vp]),
@@ -146,6 +148,13 @@ class Trainer:
         self._bucket = torch.zeros(n, dtype=torch.float32, device="cuda")
         self._ck(hostlib.mft_trainer_set_grad_bucket(self._h, self._bucket.data_ptr(), n))
         return self._bucket
+
+    def save_state(self, path):
+        """Trainable tensors + Adam moments + step counters -> one safetensors file."""
+        self._ck(hostlib.mft_trainer_save_state(self._h, str(path).encode()))
+
+    def load_state(self, path):
+        self._ck(hostlib.mft_trainer_load_state(self._h, str(path).encode()))
 
     def set_lr(self, lr):
         hostlib.mft_trainer_set_lr(self._h, float(lr))

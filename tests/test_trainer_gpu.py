@@ -269,3 +269,34 @@ def test_data_parallel_two_ranks_equal_single_process():
                             "--master-port", "29517", os.path.join(root, "tools", "dp_check.py")], capture_output=True, text=True, timeout=600,
                            env=dict(os.environ, DP_CHECK_GRAPH=graph))
         assert r.returncode == 0 and "DP_CHECK_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("full_ft", [False, True])
+def test_resume_from_saved_state_continues_bit_for_bit(tmp_path, full_ft):
+    """5 steps, save (parameters + Adam moments + step counters), 4 more steps == a fresh trainer that loads the file and runs
+    the same 4 batches: identical losses and parameters (exact mode; CUDA-graph replay on in the resumed trainer)."""
+    from mobilefinetuner_b200.trainer import Trainer
+    rng = np.random.default_rng(17)
+    batches = rng.integers(0, TINY_GPT2["vocab_size"], (9, 2, 16)).astype(np.int32)
+    a = Trainer(2, 16, shape=TINY_GPT2, full_finetune=full_ft, lora_rank=8, lora_alpha=16.0, arena_mb=256)
+    for i in range(5):
+        a.step_numpy(batches[i])
+    path = tmp_path / "state.safetensors"
+    a.save_state(path)
+    la = [a.step_numpy(batches[i]) for i in range(5, 9)]
+    pa = [a.param_checksum(i) for i in range(a.num_trainable)]
+    a.close()
+    b = Trainer(2, 16, shape=TINY_GPT2, full_finetune=full_ft, lora_rank=8, lora_alpha=16.0, arena_mb=256, cuda_graph=True, seed=99)   # other init: all of it must come from the file
+    b.load_state(path)
+    lb = [b.step_numpy(batches[i]) for i in range(5, 9)]
+    if not full_ft:
+        # LoRA run: the frozen base weights come from the seed, so only a trainer with the same seed can resume; check that
+        # a different base really gives different losses, then resume properly
+        assert lb != la
+        b.close()
+        b = Trainer(2, 16, shape=TINY_GPT2, lora_rank=8, lora_alpha=16.0, arena_mb=256, cuda_graph=True)
+        b.load_state(path)
+        lb = [b.step_numpy(batches[i]) for i in range(5, 9)]
+    assert lb == la, (la, lb)
+    assert pa == [b.param_checksum(i) for i in range(b.num_trainable)]
+    b.close()
