@@ -92,6 +92,26 @@ int mft_trainer_apply_accumulated(mft_trainer* t);
 int mft_trainer_save_state(mft_trainer* t, const char* path);
 int mft_trainer_load_state(mft_trainer* t, const char* path);
 
+/* ---- data-parallel exchange without Python: NCCL behind the C ABI (SURVEY §8b last row, §8e). One process per GPU with
+ * its CUDA device already selected. Rank 0 makes the 128-byte unique id (mft_comm_unique_id) and passes it to the other ranks
+ * by any side channel — mft_comm_init_from_file does it through a file that rank 0 writes and the others poll. The
+ * all-reduce is in place, fp32, sum, enqueued on `stream`. libnccl.so.2 is loaded at run time (PyTorch's copy when the
+ * process already carries one, else the system's). Every function returns 0 on success; mft_comm_last_error() explains. */
+typedef struct mft_comm mft_comm;
+const char* mft_comm_last_error(void);
+int mft_comm_nccl_version(void);                               /* e.g. 22703; 0 when libnccl cannot be loaded */
+int mft_comm_unique_id(void* out128);
+int mft_comm_init_rank(mft_comm** out, int world_size, int rank, const void* unique_id_128);
+int mft_comm_init_from_file(mft_comm** out, int world_size, int rank, const char* path, int timeout_s);
+int mft_comm_world_size(mft_comm* c);
+int mft_comm_rank(mft_comm* c);
+int mft_comm_allreduce_sum(mft_comm* c, float* dev_buf, int64_t n, void* stream);
+int mft_comm_destroy(mft_comm* c);
+/* One data-parallel step on this rank's rows (ids in HBM): forward/backward + pack -> all-reduce of the gradient bucket
+ * over `comm` on the trainer's stream -> 1/world, clip, Adam. The trainer must have been created with the communicator's
+ * world_size / rank; it allocates its own bucket on first use unless mft_trainer_set_grad_bucket supplied one. */
+int mft_trainer_step_dp(mft_trainer* t, mft_comm* comm, const int32_t* dev_ids);
+
 /* Introspection for tests / reports. */
 int32_t mft_trainer_num_trainable(mft_trainer* t);
 int32_t mft_trainer_num_with_grad(mft_trainer* t);       /* tensors that received a gradient in the last step */

@@ -73,6 +73,7 @@ struct mft_trainer {
     int64_t phase_launches[3] = {0, 0, 0};
     cudaEvent_t slots_event[2] = {nullptr, nullptr};   // recorded after each eager upload of the pinned slot table
     bool capturing = false;
+    TensorPtr own_bucket;          // gradient bucket allocated by mft_trainer_step_dp when the caller supplied none
     std::vector<TensorPtr> accum;  // true-gradient mode: persistent gradient sums over micro-batches (mft_trainer_accumulate)
     int accum_count = 0;
     float extra_grad_scale = 1.0f; // 1 / micro-batches, folded into the clip factor of the next update
@@ -401,6 +402,21 @@ extern "C" int mft_trainer_update(mft_trainer* t) {
         t->launches = t->phase_launches[1] + t->phase_launches[2];
         return 0;
     } catch (const std::exception& e) { return fail("mft_trainer_update: %s", e.what()); }
+}
+
+extern "C" int mft_trainer_step_dp(mft_trainer* t, mft_comm* comm, const int32_t* dev_ids) {
+    if (!t || !comm || !dev_ids) return fail("mft_trainer_step_dp: null argument");
+    if (mft_comm_world_size(comm) != t->cfg.world_size) return fail("mft_trainer_step_dp: the trainer was built for world_size %d, the communicator has %d", t->cfg.world_size, mft_comm_world_size(comm));
+    try {
+        if (!t->bucket) {                       // the trainer's own bucket (persistent)
+            mft_rt::PersistentScope keep;
+            t->own_bucket = zeros({t->grad_elems > 0 ? t->grad_elems : 4}, kFloat32, kCPU);
+            if (mft_trainer_set_grad_bucket(t, t->own_bucket->dev_f32_mut(), t->grad_elems) != 0) return 1;
+        }
+        if (mft_trainer_forward_backward(t, dev_ids) != 0) return 1;
+        if (mft_comm_allreduce_sum(comm, t->bucket, t->grad_elems, mft_rt::stream()) != 0) return fail("mft_trainer_step_dp: %s", mft_comm_last_error());
+        return mft_trainer_update(t);
+    } catch (const std::exception& e) { return fail("mft_trainer_step_dp: %s", e.what()); }
 }
 
 // ---- gradient accumulation over micro-batches (true-gradient mode only: the reference overwrites `.grad`)

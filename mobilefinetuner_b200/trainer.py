@@ -51,6 +51,16 @@ TRAINER_SIGNATURES = {
     "mft_trainer_apply_accumulated": (C.c_int, [vp]),
     "mft_trainer_save_state": (C.c_int, [vp, C.c_char_p]),
     "mft_trainer_load_state": (C.c_int, [vp, C.c_char_p]),
+    "mft_comm_last_error": (C.c_char_p, []),
+    "mft_comm_nccl_version": (C.c_int, []),
+    "mft_comm_unique_id": (C.c_int, [vp]),
+    "mft_comm_init_rank": (C.c_int, [C.POINTER(vp), C.c_int, C.c_int, vp]),
+    "mft_comm_init_from_file": (C.c_int, [C.POINTER(vp), C.c_int, C.c_int, C.c_char_p, C.c_int]),
+    "mft_comm_world_size": (C.c_int, [vp]),
+    "mft_comm_rank": (C.c_int, [vp]),
+    "mft_comm_allreduce_sum": (C.c_int, [vp, vp, i64, vp]),
+    "mft_comm_destroy": (C.c_int, [vp]),
+    "mft_trainer_step_dp": (C.c_int, [vp, vp, vp]),
     "mft_trainer_num_trainable": (i32, [vp]),
     "mft_trainer_num_with_grad": (i32, [vp]),
     "mft_trainer_kernel_launches": (i64, [vp]),

@@ -300,3 +300,17 @@ def test_resume_from_saved_state_continues_bit_for_bit(tmp_path, full_ft):
     assert lb == la, (la, lb)
     assert pa == [b.param_checksum(i) for i in range(b.num_trainable)]
     b.close()
+
+
+def test_data_parallel_through_the_c_abi_without_python():
+    """mobilefinetuner_b200/bin/dp_two_rank (tools/dp_two_rank.cpp): two processes, one GPU each, mft_comm_* (NCCL loaded by the
+    library) + mft_trainer_step_dp, against one process stepping the concatenated batches; skipped on a single-GPU box."""
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "mobilefinetuner_b200", "bin", "dp_two_rank")
+    assert os.path.exists(exe), "build it with make -C mobilefinetuner_b200/csrc"
+    r = subprocess.run([exe, "2", "8"], capture_output=True, text=True, timeout=600, env=dict(os.environ, MFT_USE_TENSOR_CORES="0"))
+    assert r.returncode == 0 and "DP_C_ABI_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
