@@ -31,6 +31,7 @@ const char* mft_last_error(void);          /* thread-local, valid until the next
 int mft_device_check(void);                /* 0 iff the current device is sm_100 (B200)        */
 int mft_use_tensor_cores(int enable);      /* 1 (default): tcgen05 TF32 GEMM when eligible; 0: SIMT fp32 GEMM
                                               everywhere (bit-faithful fp32, used by parity tests). Returns previous. */
+int mft_tensor_cores_enabled(void);     /* current setting of mft_use_tensor_cores, unchanged */
 
 /* ------------------------------------------------------------------ GEMM
  * C[m,n] = alpha * ( opA(A) * opB(B)  +  A2 * B2^T )  (+ bias[n])  (+ beta * C), optional GELU aux.
@@ -96,6 +97,11 @@ int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int 
 /* same, plus a bf16 copy of y (NULL = off; row pitch ld_bf16 elements) for the rank-r segment of the bf16 GEMM */
 int mft_lora_down_ex(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, void* y_bf16,
                      int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
+/* The same product on bf16 operands (bf16 operand mode): x as the bf16 copy its producer wrote, A as its K-major bf16 shadow
+ * [r][K] (pitch lda) — the array the rank-r segment of mft_gemm_bf16 reads. r <= 16, K a multiple of 128 up to 6144; pitches
+ * multiples of 8, 16-byte aligned bases. y is fp32 [T, r]; y_bf16 (NULL = off) its bf16 copy. */
+int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a_kmajor_bf16, int64_t lda, float* y, int64_t ldy, void* y_bf16,
+                       int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
 size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r);
 int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t ldw, float* out, int64_t ldo, int out_is_rq,
                 int64_t T, int64_t q, int32_t r, float alpha, void* workspace, size_t workspace_bytes, mft_stream_t stream);

@@ -50,6 +50,7 @@ SIGNATURES = {
     "mft_last_error": (C.c_char_p, []),
     "mft_device_check": (C.c_int, []),
     "mft_use_tensor_cores": (C.c_int, [C.c_int]),
+    "mft_tensor_cores_enabled": (C.c_int, []),
     "mft_gemm": (C.c_int, [C.POINTER(GemmArgs), vp]),
     "mft_gemm_bf16": (C.c_int, [C.POINTER(GemmArgs), vp]),
     "mft_cast_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
@@ -58,6 +59,7 @@ SIGNATURES = {
     "mft_gemm_splitk": (C.c_int, [C.POINTER(GemmArgs), i32, vp, sz, vp]),
     "mft_lora_down": (C.c_int, [vp, i64, vp, i64, C.c_int, vp, i64, i64, i64, i32, f32, vp]),
     "mft_lora_down_ex": (C.c_int, [vp, i64, vp, i64, C.c_int, vp, i64, vp, i64, i64, i64, i32, f32, vp]),
+    "mft_lora_down_bf16": (C.c_int, [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32, f32, vp]),
     "mft_lora_tn_workspace_bytes": (sz, [i64, i64, i32]),
     "mft_lora_tn": (C.c_int, [vp, i64, vp, i64, vp, i64, C.c_int, i64, i64, i32, f32, vp, sz, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),

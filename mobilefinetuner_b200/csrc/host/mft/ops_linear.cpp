@@ -240,6 +240,20 @@ int skinny_mask() {
 }
 // y[T,r] = alpha * x[T,K] * A   (A [K,r] when a_is_kr, else [r,K])
 void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, bool a_is_kr, int64_t r, float alpha, const TensorPtr& y) {
+    // bf16 operand mode: x already exists as bf16 (written by its producer) — read that copy (half the bytes) against the
+    // factor's K-major bf16 shadow. MFT_LORA_DOWN_BF16=0 keeps the fp32 kernel.
+    static const bool lowp_on = [] { const char* e = std::getenv("MFT_LORA_DOWN_BF16"); return !(e && e[0] == '0'); }();
+    if (lowp_on && (skinny_mask() & 1) && emit_bf16_operands() && gemm_precision() == 1 && mft_tensor_cores_enabled() && r >= 1 && r <= 16 &&
+        K % 128 == 0 && K <= 6144 && x->has_bf16() && A->ndim() == 2) {
+        auto xv = x->bf16_view();
+        auto av = a_is_kr ? A->bf16_transposed_view() : A->bf16_view();      // [r][K], cached per version of the factor
+        if (xv.ld % 8 == 0 && av.ld % 8 == 0) {
+            float* yp = y->dev_f32_out();
+            auto e = y->bf16_emit();
+            mft_rt::check(mft_lora_down_bf16(xv.ptr, xv.ld, av.ptr, av.ld, yp, r, e.ptr, e.ld, T, K, int32_t(r), alpha, mft_rt::stream()), "mft_lora_down_bf16");
+            return;
+        }
+    }
     if ((skinny_mask() & 1) && r >= 1 && r <= 64) {
         float* yp = y->dev_f32_out();
         if (emit_bf16_operands()) {      // the rank-r product is the A operand of the bf16 GEMM's second K segment

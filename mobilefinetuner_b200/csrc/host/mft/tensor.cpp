@@ -115,7 +115,10 @@ Tensor::~Tensor() = default;
 TensorPtr Tensor::make(const std::vector<int64_t>& shape, DType dtype, bool zero, int64_t ld) {
     auto t = std::shared_ptr<Tensor>(new Tensor());
     t->shape_ = shape; t->dtype_ = dtype; t->ld_ = ld;
-    t->allocate(zero);
+    // Op results take their HBM buffer at first device access: a result that is produced as bf16 only (bf16_only_out) and
+    // never read as fp32 then never occupies its fp32 buffer in the step arena.
+    t->allocate(zero, /*defer_device=*/!zero);
+    if (!zero) t->st_->dev_valid = true;     // nothing on the host to upload
     return t;
 }
 
@@ -129,6 +132,7 @@ void Tensor::ensure_host() const {
     }
     if (!st_->host_valid) {
         const size_t es = DTypeUtils::size_of(dtype_);
+        ensure_dev();
         if (numel() > 0) {
             if (is_dense()) mft_rt::d2h(st_->host, st_->dev, dense_bytes());
             else mft_rt::d2h_2d(st_->host, shape_.back() * es, st_->dev, ld_ * es, shape_.back() * es, rows());
@@ -240,8 +244,7 @@ Tensor::Bf16Out Tensor::bf16_emit() {
 Tensor::Bf16Out Tensor::bf16_only_out() {
     if (dtype_ != kFloat32) throw TensorError("bf16_only_out: float32 tensors only");
     if (!st_) throw TensorError("Tensor: no storage");
-    ensure_dev();
-    st_->dev_valid = true;           // the device side is authoritative (as bf16, until somebody needs fp32)
+    st_->dev_valid = true;           // the device side is authoritative (as bf16, until somebody needs fp32); no fp32 buffer yet
     st_->host_valid = false;
     ++st_->version;
     Bf16Out o = bf16_emit();

@@ -74,6 +74,8 @@ extern "C" int mft_device_check(void) {
 
 namespace mft { bool tensor_cores_enabled() { return g_use_tc; } }
 
+extern "C" int mft_tensor_cores_enabled(void) { return g_use_tc ? 1 : 0; }
+
 extern "C" int mft_use_tensor_cores(int enable) {
     int prev = g_use_tc ? 1 : 0;
     g_use_tc = enable != 0;

@@ -332,7 +332,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                                                                            *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
                                     }
                                 } else {
-                                    for (int e = 0; e < 32 && n0 + cc + e < p.n; ++e) d16[e] = __float2bfloat16_rn(v[e]);
+#pragma unroll
+                                    for (int e = 0; e < 32; ++e)          // compile-time indices: v[] must stay in registers
+                                        if (n0 + cc + e < p.n) d16[e] = __float2bfloat16_rn(v[e]);
                                 }
                             }
                         }

@@ -466,3 +466,121 @@ extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t 
     MFT_CHECK_LAUNCH("mft_lora_tn");
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// lora_down on bf16 operands (bf16 operand mode): y[T,r] = alpha * x[T,K] * A with x given as the bf16 copy its producer
+// wrote (half the bytes of the fp32 rows) and A as its K-major bf16 shadow [r][K] (the same array the rank-r segment of the
+// big GEMM reads). A CTA owns 16 token rows at a time and loops over row blocks; its four warps split K into quarters.
+// The whole shadow goes to shared memory once per CTA as straight 16-byte cp.async copies (no transposition, 32 KB for
+// K = 1024) while the x loads of the first block are already in flight; products run as mma.sync m16n8k16 bf16 with fp32
+// accumulation. Fragments are built straight from 16-byte loads by relabelling the contraction index inside each 32-wide k
+// group (slot 2t,2t+1 <-> k 8t+0,1; slot 2t+8,2t+9 <-> k 8t+2,3 for the first MMA; +4 for the second) — x and A use the same
+// relabelling, so no shuffle is needed. Algorithmic bytes: 2*T*K. HBM-bound.
+namespace mft {
+
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+constexpr int kLbPad = 32;      // bf16 elements of padding per shadow row in shared memory (64 bytes: conflict-free 16-byte reads)
+
+__global__ void __launch_bounds__(128)
+lora_down_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ldx, const __nv_bfloat16* __restrict__ at, int64_t lda,
+                      float* __restrict__ y, int64_t ldy, __nv_bfloat16* __restrict__ y16, int64_t ld16, int64_t T, int K, int r, float alpha) {
+    extern __shared__ __align__(16) uint8_t lb_smem[];
+    const int KP = K + kLbPad;
+    __nv_bfloat16* sA = reinterpret_cast<__nv_bfloat16*>(lb_smem);                 // [16][KP]
+    float* red = reinterpret_cast<float*>(lb_smem + size_t(16) * KP * 2);           // [4 warps][16 rows][16 cols]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int KQ = K >> 2;                                                           // this warp's K quarter (multiple of 32)
+    // shadow -> shared memory (rows >= r are zero)
+    {
+        const int chunks = K >> 3;                                                   // 16-byte pieces per row
+        for (int idx = threadIdx.x; idx < 16 * chunks; idx += 128) {
+            const int c = idx / chunks, pc = idx % chunks;
+            const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(sA + c * KP + pc * 8));
+            const int nb = c < r ? 16 : 0;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(dst), "l"(at + int64_t(c < r ? c : 0) * lda + pc * 8), "r"(nb) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    const int64_t nblk = (T + 15) >> 4;
+    bool first = true;
+    for (int64_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        const int64_t row0 = blk << 4;
+        const bool live0 = row0 + g < T, live1 = row0 + g + 8 < T;
+        const __nv_bfloat16* x0 = x + (live0 ? row0 + g : 0) * ldx + warp * KQ + 8 * t;
+        const __nv_bfloat16* x1 = x + (live1 ? row0 + g + 8 : 0) * ldx + warp * KQ + 8 * t;
+        float acc[2][4];
+#pragma unroll
+        for (int n = 0; n < 2; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+        for (int kc = 0; kc < KQ; kc += 256) {
+            uint4 xa[8], xb[8];
+            const int nit = min(8, (KQ - kc) >> 5);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                xa[i] = (i < nit && live0) ? __ldcs(reinterpret_cast<const uint4*>(x0 + kc + 32 * i)) : make_uint4(0u, 0u, 0u, 0u);
+                xb[i] = (i < nit && live1) ? __ldcs(reinterpret_cast<const uint4*>(x1 + kc + 32 * i)) : make_uint4(0u, 0u, 0u, 0u);
+            }
+            if (first) {                                                             // the shadow must have landed before its first use
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+                __syncthreads();
+                first = false;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (i >= nit) break;
+                const __nv_bfloat16* bp = sA + g * KP + warp * KQ + kc + 32 * i + 8 * t;
+                const uint4 b0 = *reinterpret_cast<const uint4*>(bp);               // output column g
+                const uint4 b1 = *reinterpret_cast<const uint4*>(bp + 8 * KP);      // output column g + 8
+                mma_bf16_16816(acc[0], xa[i].x, xb[i].x, xa[i].y, xb[i].y, b0.x, b0.y);
+                mma_bf16_16816(acc[1], xa[i].x, xb[i].x, xa[i].y, xb[i].y, b1.x, b1.y);
+                mma_bf16_16816(acc[0], xa[i].z, xb[i].z, xa[i].w, xb[i].w, b0.z, b0.w);
+                mma_bf16_16816(acc[1], xa[i].z, xb[i].z, xa[i].w, xb[i].w, b1.z, b1.w);
+            }
+        }
+        // the four warps hold partial sums over their K quarters: add them in warp order through shared memory
+#pragma unroll
+        for (int n = 0; n < 2; ++n) {
+            float* base = red + warp * 256 + n * 8 + 2 * t;
+            base[g * 16] = acc[n][0]; base[g * 16 + 1] = acc[n][1];
+            base[(g + 8) * 16] = acc[n][2]; base[(g + 8) * 16 + 1] = acc[n][3];
+        }
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < 256; idx += 128) {
+            const int rr = idx >> 4, c = idx & 15;
+            const int64_t row = row0 + rr;
+            if (row < T && c < r) {
+                const float v = (((red[idx] + red[256 + idx]) + red[512 + idx]) + red[768 + idx]) * alpha;
+                y[row * ldy + c] = v;
+                if (y16) y16[row * ld16 + c] = __float2bfloat16_rn(v);
+            }
+        }
+        __syncthreads();                                                             // `red` is rewritten by the next block
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");                             // a CTA without any block still drains its copies
+}
+
+}  // namespace mft
+
+extern "C" int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a_kmajor_bf16, int64_t lda, float* y, int64_t ldy, void* y_bf16,
+                                  int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
+    if (T == 0 || r == 0) return 0;
+    if (!x_bf16 || !a_kmajor_bf16 || !y) return set_error(1, "mft_lora_down_bf16: null pointer");
+    if (r < 1 || r > 16) return set_error(1, "mft_lora_down_bf16: rank %d outside 1..16", r);
+    if (K < 128 || (K & 127) || K > 6144) return set_error(1, "mft_lora_down_bf16: K must be a multiple of 128 in 128..6144");
+    if ((ldx & 7) || (lda & 7) || !aligned16(x_bf16) || !aligned16(a_kmajor_bf16)) return set_error(1, "mft_lora_down_bf16: operands must be 16-byte aligned with pitches that are multiples of 8");
+    const size_t smem = size_t(16) * size_t(K + kLbPad) * 2 + 4096;
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set)) cudaFuncSetAttribute(lora_down_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * (6144 + kLbPad) * 2 + 4096);
+    const int64_t nblk = ceil_div(T, int64_t(16));
+    const int64_t cap = int64_t(kNumSMs) * 4;
+    const unsigned grid = unsigned(nblk < cap ? nblk : cap);
+    lora_down_bf16_kernel<<<grid, 128, smem, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(x_bf16), ldx, static_cast<const __nv_bfloat16*>(a_kmajor_bf16), lda,
+                                                                  y, ldy, static_cast<__nv_bfloat16*>(y_bf16), ld_bf16, T, int(K), r, alpha);
+    MFT_CHECK_LAUNCH("mft_lora_down_bf16");
+    return 0;
+}

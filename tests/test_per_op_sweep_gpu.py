@@ -164,3 +164,22 @@ def test_cross_entropy_sweep_tokens_up_to_65536(capi, B, S, V):
         assert rel(g[r, :V], eg[0, s]) < 1e-5
         if s > 3:
             break                                                 # a full-sequence oracle call per row is slow at V = 262144
+
+
+@pytest.mark.parametrize("T,K,r", [(512, 768, 8), (4096, 1024, 16), (1000, 3072, 16), (37, 128, 3), (8192, 4096, 16), (300, 640, 8)])
+def test_lora_down_on_bf16_operands(capi, T, K, r):
+    """mft_lora_down_bf16 (x and the factor's K-major shadow as bf16, mma.sync bf16, fp32 accumulate) against fp64 on the
+    same bf16-rounded inputs (summation order only: 1e-5) and against the fp32 inputs (bf16 operand tolerance 1e-2)."""
+    rng = np.random.default_rng(T + K + r)
+    x = rng.standard_normal((T, K)).astype(np.float32)
+    A = (rng.standard_normal((K, r)) * 0.1).astype(np.float32)
+    x16 = dev(x).to(torch.bfloat16)
+    At16 = dev(np.ascontiguousarray(A.T)).to(torch.bfloat16)             # [r, K]
+    y = torch.full((T, r), float("nan"), device="cuda")
+    y16 = torch.empty(T, r, device="cuda", dtype=torch.bfloat16)
+    capi.call("mft_lora_down_bf16", x16, K, At16, K, y, r, y16, r, T, K, r, 2.0, None)
+    torch.cuda.synchronize()
+    e16 = 2.0 * (x16.float().cpu().numpy().astype(np.float64) @ At16.float().cpu().numpy().astype(np.float64).T)
+    assert rel(y, e16) < 1e-5
+    assert rel(y, 2.0 * (x.astype(np.float64) @ A.astype(np.float64))) < BF16_TOL
+    assert torch.equal(y16, y.to(torch.bfloat16))
