@@ -268,11 +268,9 @@ static int launch_attention_mt(const float* q, const float* k, const float* v, f
                                int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                                int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st, void* ctx16) {
     constexpr size_t smem = size_t(4) * kAttBK * (HD + kAttPad) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(causal_attention_fwd_kernel<HD, PRECISE, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        attr_set = true;
-    }
     dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
     causal_attention_fwd_kernel<HD, PRECISE, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
                                                                  osh, scale, window, static_cast<__nv_bfloat16*>(ctx16));
@@ -498,11 +496,9 @@ static int launch_attention_bf16(const float* q, const float* k, const float* v,
                                  int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                                  int64_t osb, int64_t oss, int64_t osh, float scale, int window, cudaStream_t st, void* ctx16) {
     constexpr size_t smem = size_t(2) * kAttBK * ((HD + 8) + (HD + 4)) * sizeof(float);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[kMaxDevices] = {};
+    if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(causal_attention_bf16_kernel<HD, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        attr_set = true;
-    }
     dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
     causal_attention_bf16_kernel<HD, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale,
                                                             window, static_cast<__nv_bfloat16*>(ctx16));

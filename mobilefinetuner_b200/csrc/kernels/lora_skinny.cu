@@ -374,8 +374,8 @@ template <int RPW, int RMAX, int KC>
 static void launch_down(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, int64_t T, int K,
                         int r, float alpha, cudaStream_t st) {
     constexpr size_t smem = size_t(KC) * (RMAX + 4) * sizeof(float);
-    static bool attr = false;
-    if (!attr) { cudaFuncSetAttribute(lora_down_kernel<RPW, RMAX, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); attr = true; }
+    static bool attr[kMaxDevices] = {};
+    if (first_use_on_device(attr)) cudaFuncSetAttribute(lora_down_kernel<RPW, RMAX, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     lora_down_kernel<RPW, RMAX, KC><<<unsigned(ceil_div(T, int64_t(8 * RPW))), 256, smem, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha);
 }
 
@@ -392,11 +392,10 @@ static int lora_down_impl(const float* x, int64_t ldx, const float* a, int64_t l
     static const bool mma_on = [] { const char* e = getenv("MFT_LORA_DOWN_MMA"); return !(e && e[0] == '0'); }();
     if (mma_on && r <= 16 && (K & 3) == 0 && (ldx & 3) == 0 && aligned16(x)) {
         const bool precise = !tensor_cores_enabled();          // exact mode: 3xTF32 split, fp32-accurate
-        static bool attr = false;
-        if (!attr) {
+        static bool attr[kMaxDevices] = {};
+        if (first_use_on_device(attr)) {
             cudaFuncSetAttribute(lora_down_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDmSmemBytes);
             cudaFuncSetAttribute(lora_down_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDmSmemBytes);
-            attr = true;
         }
         const unsigned grid = unsigned(ceil_div(T, int64_t(16)));
         if (precise) lora_down_mma_kernel<true><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
@@ -447,15 +446,15 @@ extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t 
     const int64_t colblocks = ceil_div(q, vec ? kTnCT * 2 : kTnCT);
     // the last-arriving CTA sums the splits itself when there are few of them; a long split list is summed faster by a
     // separate, fully parallel launch
-    const int tk = (colblocks <= kTnMaxTickets && splits <= 8) ? 1 : 0;
+    const int tk = (colblocks <= kTnMaxTickets && splits <= 64) ? 1 : 0;      // 64 splits x [r x 128] partials = 512 KB from L2 for the last CTA of a column block
     if (vec) {
         const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
         lora_tn_kernel<2, 16><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
                                                                                                  out_is_rq, alpha, tk);
     } else {
         const size_t smem = (size_t(kTnRows) * 64 + size_t(64) * kTnCT) * sizeof(float);
-        static bool attr = false;
-        if (!attr) { cudaFuncSetAttribute(lora_tn_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)); attr = true; }
+        static bool attr[kMaxDevices] = {};
+        if (first_use_on_device(attr)) cudaFuncSetAttribute(lora_tn_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         lora_tn_kernel<1, 64><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
                                                                                                  out_is_rq, alpha, tk);
     }
