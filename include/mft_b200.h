@@ -375,6 +375,16 @@ int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, float lr, flo
 int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots, const float* lr, float beta1, float beta2, float eps,
                       float weight_decay, const float* grad_scale, int32_t* steps, mft_stream_t stream);
 
+/* bf16 shadows of trained matrices after the optimizer step, all tensors in ONE launch (bf16 operand mode): for each slot,
+ * plain[r, c] = bf16(src[r, c]) and / or transposed[c, r] = bf16(src[r, c]) (either pointer may be NULL). The slot table is in
+ * DEVICE memory. max_elems = the largest rows*cols of the table (sizes the grid). No counterpart in the reference (fp32 only). */
+typedef struct mft_shadow_slot {
+    const float* src; int64_t rows, cols, ld_src;
+    void* plain; int64_t ld_plain;
+    void* transposed; int64_t ld_transposed;
+} mft_shadow_slot;
+int mft_refresh_bf16_shadows(const mft_shadow_slot* slots, int32_t num_slots, int64_t max_elems, mft_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,11 @@ class TensorSlot(C.Structure):
                 ("bias_corr1", f32), ("bias_corr2", f32), ("bucket_offset", i64)]
 
 
+class ShadowSlot(C.Structure):
+    _fields_ = [("src", vp), ("rows", i64), ("cols", i64), ("ld_src", i64), ("plain", vp), ("ld_plain", i64), ("transposed", vp),
+                ("ld_transposed", i64)]
+
+
 # name -> (restype, argtypes); must list every symbol declared in include/mft_b200.h
 SIGNATURES = {
     "mft_version": (C.c_int, []),
@@ -119,6 +124,7 @@ SIGNATURES = {
     "mft_lm_ce_fwd": (C.c_int, [vp, i64, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, sz, vp]),
     "mft_lm_ce_bwd": (C.c_int, [vp, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i64, vp]),
     "mft_lm_ce_bwd_ex": (C.c_int, [vp, i64, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, i64, vp, i64, vp]),
+    "mft_refresh_bf16_shadows": (C.c_int, [vp, i32, i64, vp]),
     "mft_pack_grads": (C.c_int, [vp, i32, vp, vp]),
     "mft_grad_sumsq_workspace_bytes": (sz, []),
     "mft_grad_sumsq": (C.c_int, [vp, i32, vp, vp, sz, vp]),

@@ -242,7 +242,8 @@ int skinny_mask() {
 void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, bool a_is_kr, int64_t r, float alpha, const TensorPtr& y) {
     // bf16 operand mode: x already exists as bf16 (written by its producer) — read that copy (half the bytes) against the
     // factor's K-major bf16 shadow. MFT_LORA_DOWN_BF16=0 keeps the fp32 kernel.
-    static const bool lowp_on = [] { const char* e = std::getenv("MFT_LORA_DOWN_BF16"); return !(e && e[0] == '0'); }();
+    const char* lowp_env = std::getenv("MFT_LORA_DOWN_BF16");          // read per call: tests compare the two paths
+    const bool lowp_on = !(lowp_env && lowp_env[0] == '0');
     if (lowp_on && (skinny_mask() & 1) && emit_bf16_operands() && gemm_precision() == 1 && mft_tensor_cores_enabled() && r >= 1 && r <= 16 &&
         K % 128 == 0 && K <= 6144 && x->has_bf16() && A->ndim() == 2) {
         auto xv = x->bf16_view();

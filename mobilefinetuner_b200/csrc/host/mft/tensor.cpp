@@ -223,6 +223,17 @@ Tensor::Bf16View Tensor::bf16_view() const {
     return {bf16_->dev, bf16_ld_};
 }
 
+Tensor::Bf16Shadows Tensor::existing_bf16_shadows() const {
+    Bf16Shadows o{nullptr, 0, nullptr, 0};
+    if (bf16_) { o.plain = bf16_->dev; o.ld_plain = bf16_ld_; }
+    if (bf16_t_) { o.transposed = bf16_t_->dev; o.ld_transposed = bf16_t_ld_; }
+    return o;
+}
+void Tensor::mark_bf16_shadows_current() {
+    if (bf16_) bf16_version_ = version();
+    if (bf16_t_) bf16_t_version_ = version();
+}
+
 bool Tensor::has_bf16() const {
     if (!st_ || dtype_ != kFloat32) return false;
     if (bf16_ && bf16_version_ == version()) return true;

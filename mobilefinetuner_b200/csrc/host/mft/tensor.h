@@ -152,6 +152,11 @@ public:
     // through one upcast kernel, so correctness never depends on the guess; only the saved HBM traffic does.
     Bf16Out bf16_only_out();
     bool f32_pending() const { return st_ && st_->f32_pending; }
+    // For a refresh kernel that rewrites the bf16 shadows of a trained 2-D tensor itself (mft_refresh_bf16_shadows): the
+    // shadow buffers that exist already (null = that shadow has never been asked for), and a way to declare them current.
+    struct Bf16Shadows { void* plain; int64_t ld_plain; void* transposed; int64_t ld_transposed; };
+    Bf16Shadows existing_bf16_shadows() const;
+    void mark_bf16_shadows_current();
     // true when bf16_view() costs nothing (a valid bf16 copy of the current contents exists)
     bool has_bf16() const;
     // hint set by the producer of an activation whose gradient consumer reads bf16 (the GELU backward kernel): the op that

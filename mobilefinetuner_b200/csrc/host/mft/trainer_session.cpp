@@ -3,6 +3,7 @@
 // scale = max/(norm+1e-6), Adam, drop grads); Gemma: optim/gemma_trainer.cpp:104-149.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -73,6 +74,9 @@ struct mft_trainer {
     int64_t phase_launches[3] = {0, 0, 0};
     cudaEvent_t slots_event[2] = {nullptr, nullptr};   // recorded after each eager upload of the pinned slot table
     bool capturing = false;
+    void* shadow_dev = nullptr;    // device table of mft_shadow_slot (bf16 shadows of the trained adapter factors)
+    mft_shadow_slot* shadow_host = nullptr;
+    std::vector<int> shadowed;     // indices into `trainable` whose shadows the refresh kernel rewrote last step
     TensorPtr own_bucket;          // gradient bucket allocated by mft_trainer_step_dp when the caller supplied none
     std::vector<TensorPtr> accum;  // true-gradient mode: persistent gradient sums over micro-batches (mft_trainer_accumulate)
     int accum_count = 0;
@@ -187,6 +191,8 @@ void build(mft_trainer* t) {
         t->slots_dev[k] = mft_rt::dev_alloc(nt * sizeof(mft_tensor_slot) + 16);
         t->slots_host[k] = static_cast<mft_tensor_slot*>(mft_rt::pinned_alloc(nt * sizeof(mft_tensor_slot) + 16));
     }
+    t->shadow_dev = mft_rt::dev_alloc(nt * sizeof(mft_shadow_slot) + 16);
+    t->shadow_host = static_cast<mft_shadow_slot*>(mft_rt::pinned_alloc(nt * sizeof(mft_shadow_slot) + 16));
     t->sumsq_dev = static_cast<double*>(mft_rt::dev_alloc(64));
     t->offsets.resize(t->trainable.size());
     int64_t off = 0;
@@ -233,6 +239,31 @@ const mft_tensor_slot* upload_slots(mft_trainer* t, bool packed) {
     return static_cast<const mft_tensor_slot*>(t->slots_dev[packed]);
 }
 
+// bf16 operand mode: the bf16 copies / K-major transposes of the small trained matrices (adapter factors) that the next
+// forward will read are rewritten by ONE launch right after Adam, instead of one cast launch per factor when first used.
+// Only shadows that already exist are refreshed (after the first step those are exactly the ones the graph reads).
+void refresh_shadows(mft_trainer* t) {
+    t->shadowed.clear();
+    if (!ops::internal::emit_bf16_operands() || ops::internal::gemm_precision() != 1) return;
+    int64_t max_elems = 0;
+    int n = 0;
+    for (size_t i = 0; i < t->trainable.size(); ++i) {
+        const TensorPtr& p = t->trainable[i];
+        if (!t->grads[i] || p->ndim() != 2 || p->numel() > (int64_t(1) << 18) || !p->is_dense()) continue;
+        const auto sh = p->existing_bf16_shadows();
+        if (!sh.plain && !sh.transposed) continue;
+        mft_shadow_slot& s = t->shadow_host[n++];
+        s.src = p->dev_f32(); s.rows = p->shape()[0]; s.cols = p->shape()[1]; s.ld_src = p->ld();
+        s.plain = sh.plain; s.ld_plain = sh.ld_plain; s.transposed = sh.transposed; s.ld_transposed = sh.ld_transposed;
+        max_elems = std::max<int64_t>(max_elems, p->numel());
+        t->shadowed.push_back(int(i));
+    }
+    if (n == 0) return;
+    mft_rt::h2d(t->shadow_dev, t->shadow_host, size_t(n) * sizeof(mft_shadow_slot));
+    mft_rt::check(mft_refresh_bf16_shadows(static_cast<const mft_shadow_slot*>(t->shadow_dev), n, max_elems, mft_rt::stream()), "mft_refresh_bf16_shadows");
+    for (int i : t->shadowed) t->trainable[size_t(i)]->mark_bf16_shadows_current();
+}
+
 void pack_phase(mft_trainer* t) {
     const mft_tensor_slot* slots = upload_slots(t, false);
     mft_rt::check(mft_pack_grads(slots, int32_t(t->trainable.size()), t->bucket, mft_rt::stream()), "mft_pack_grads");
@@ -247,6 +278,7 @@ void update_phase(mft_trainer* t, bool packed) {
     mft_rt::check(mft_clip_scale(t->sumsq_dev, t->cfg.clip_norm, pre, t->scale_dev, t->norm_dev, mft_rt::stream()), "mft_clip_scale");
     mft_rt::check(mft_adam_step_dev(slots, n, t->lr_dev, t->cfg.beta1, t->cfg.beta2, t->cfg.eps, t->cfg.weight_decay,
                                     t->scale_dev, t->steps_dev, mft_rt::stream()), "mft_adam_step_dev");
+    refresh_shadows(t);
     for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
 }
 
@@ -258,6 +290,7 @@ void mark_state_written(mft_trainer* t) {
         (void)t->m[i]->dev_f32_mut();
         (void)t->v[i]->dev_f32_mut();
     }
+    for (int i : t->shadowed) t->trainable[size_t(i)]->mark_bf16_shadows_current();   // the replayed update refreshed them too
 }
 
 // Runs one phase eagerly, or (cfg.use_cuda_graph) captures it into a CUDA graph after two eager runs and replays it.
@@ -326,6 +359,7 @@ extern "C" void mft_trainer_destroy(mft_trainer* t) {
     try { mft_rt::sync(); } catch (...) {}
     for (auto& g : t->graph_exec) if (g) cudaGraphExecDestroy(g);
     for (int k = 0; k < 2; ++k) { mft_rt::pinned_free(t->slots_host[k]); if (t->slots_event[k]) cudaEventDestroy(t->slots_event[k]); }
+    mft_rt::pinned_free(t->shadow_host);
     mft_rt::pinned_free(t->lr_host);
     const bool had_arena = t->arena_on;
     delete t;

@@ -270,3 +270,32 @@ extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots
     MFT_CHECK_LAUNCH("mft_adam_step_dev");
     return 0;
 }
+
+// ---------------------------------------------------------------- bf16 shadows of trained matrices, all in one launch
+// After the optimizer step every trained 2-D tensor that feeds a bf16 GEMM operand needs its bf16 copy (same layout) and /
+// or its K-major bf16 transpose again. One launch over a slot table does all of them (blockIdx.y = tensor), instead of one
+// cast / transpose-cast launch per tensor per step (96 adapter factors = 4 tiny launches each in the Gemma configuration).
+namespace mft {
+__global__ void refresh_shadows_kernel(const mft_shadow_slot* __restrict__ slots) {
+    const mft_shadow_slot s = slots[blockIdx.y];
+    const int64_t n = s.rows * s.cols;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t r = i / s.cols, c = i % s.cols;
+        const __nv_bfloat16 v = __float2bfloat16_rn(s.src[r * s.ld_src + c]);
+        if (s.plain) static_cast<__nv_bfloat16*>(s.plain)[r * s.ld_plain + c] = v;
+        if (s.transposed) static_cast<__nv_bfloat16*>(s.transposed)[c * s.ld_transposed + r] = v;
+    }
+}
+}  // namespace mft
+
+extern "C" int mft_refresh_bf16_shadows(const mft_shadow_slot* slots, int32_t num_slots, int64_t max_elems, mft_stream_t stream) {
+    if (num_slots == 0) return 0;
+    if (!slots) return set_error(1, "mft_refresh_bf16_shadows: null slot table");
+    if (num_slots > 65535) return set_error(1, "mft_refresh_bf16_shadows: more than 65535 tensors");
+    int64_t bx = ceil_div(max_elems > 0 ? max_elems : 1, int64_t(256) * 8);
+    if (bx < 1) bx = 1;
+    if (bx > 64) bx = 64;
+    mft::refresh_shadows_kernel<<<dim3(unsigned(bx), unsigned(num_slots)), 256, 0, as_stream(stream)>>>(slots);
+    MFT_CHECK_LAUNCH("mft_refresh_bf16_shadows");
+    return 0;
+}

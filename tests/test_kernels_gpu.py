@@ -256,3 +256,27 @@ def test_permute_nd_cast_tril_one_hot(capi):
         if 0 <= c < 11:
             e[i, c] = 1
     assert np.array_equal(oh.cpu().numpy(), e)
+
+
+def test_refresh_bf16_shadows_many_tensors_one_launch(capi):
+    """plain[r,c] = bf16(src[r,c]) and transposed[c,r] = bf16(src[r,c]) for a table of small matrices (adapter factors)."""
+    rng = np.random.default_rng(8)
+    shapes = [(1024, 16), (16, 1024), (640, 8), (8, 2048), (3, 5)]
+    srcs = [dev(rng.standard_normal(s).astype(np.float32)) for s in shapes]
+    plains, transposed, slots = [], [], (capi.ShadowSlot * len(shapes))()
+    for i, (s, t) in enumerate(zip(shapes, srcs)):
+        ldp, ldt = (s[1] + 7) // 8 * 8, (s[0] + 7) // 8 * 8
+        p = torch.zeros(s[0], ldp, device="cuda", dtype=torch.bfloat16) if i != 2 else None      # slot 2: transposed only
+        q = torch.zeros(s[1], ldt, device="cuda", dtype=torch.bfloat16) if i != 3 else None      # slot 3: plain only
+        plains.append(p); transposed.append(q)
+        slots[i] = capi.ShadowSlot(t.data_ptr(), s[0], s[1], s[1], p.data_ptr() if p is not None else None, ldp,
+                                   q.data_ptr() if q is not None else None, ldt)
+    table = torch.frombuffer(bytearray(bytes(slots)), dtype=torch.uint8).cuda()
+    capi.call("mft_refresh_bf16_shadows", table, len(shapes), max(a * b for a, b in shapes), None)
+    torch.cuda.synchronize()
+    for s, t, p, q in zip(shapes, srcs, plains, transposed):
+        e = t.to(torch.bfloat16)
+        if p is not None:
+            assert torch.equal(p[:, :s[1]], e)
+        if q is not None:
+            assert torch.equal(q[:, :s[0]], e.t())

@@ -136,6 +136,7 @@ def test_bf16_operands_written_by_producers_equal_cast_on_demand():
     try:
         out = []
         os.environ["MFT_BF16_ONLY"] = "0"        # both runs keep every fp32 result: only the way the bf16 copy is made differs
+        os.environ["MFT_LORA_DOWN_BF16"] = "0"   # ... and the rank-r products read fp32 rows in both
         for emit in ("0", "1"):
             os.environ["MFT_BF16_EMIT"] = emit
             tr = Trainer(4, 128, shape="gpt2-small", lora_rank=8, lora_alpha=16.0, arena_mb=4096)
@@ -147,6 +148,7 @@ def test_bf16_operands_written_by_producers_equal_cast_on_demand():
     finally:
         os.environ.pop("MFT_BF16_EMIT", None)
         os.environ.pop("MFT_BF16_ONLY", None)
+        os.environ.pop("MFT_LORA_DOWN_BF16", None)
         hostlib.mft_host_set_gemm_precision(0)
 
 
