@@ -106,6 +106,22 @@ size_t mft_lora_tn_workspace_bytes(int64_t T, int64_t q, int32_t r);
 int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t ldw, float* out, int64_t ldo, int out_is_rq,
                 int64_t T, int64_t q, int32_t r, float alpha, void* workspace, size_t workspace_bytes, mft_stream_t stream);
 /* 1 if mft_gemm would take the tcgen05 path for these arguments (host-side predicate, no launch). */
+/* Grouped form of mft_lora_tn: many independent products (every adapter's dA / dB of one backward pass, deferred to its end)
+ * in ONE launch. The problem table lives in DEVICE memory. Per problem: the mft_lora_tn arguments, its own `partial` scratch
+ * (mft_lora_tn_workspace_bytes), colblocks = mft_lora_tn_group_colblocks(q), splits = mft_lora_tn_group_splits(T),
+ * use_tickets = 1 when splits <= 64 (the last-arriving CTA of a column block sums the splits in index order) and then a
+ * ticket_base such that [ticket_base, ticket_base + colblocks) ranges of different problems do not overlap and stay below
+ * mft_lora_tn_group_ticket_capacity(). Only problems with mft_lora_tn_group_eligible(...) = 1 may be listed. */
+typedef struct mft_lora_tn_problem {
+    const float* s; int64_t lds; const float* w; int64_t ldw; float* partial; float* out; int64_t ldo;
+    int64_t T, q; int32_t r, out_is_rq; float alpha; int32_t use_tickets, colblocks, splits, ticket_base;
+} mft_lora_tn_problem;
+int mft_lora_tn_group_eligible(int64_t T, int64_t q, int32_t r, const float* w, int64_t ldw);
+int32_t mft_lora_tn_group_colblocks(int64_t q);
+int32_t mft_lora_tn_group_splits(int64_t T);
+int32_t mft_lora_tn_group_ticket_capacity(void);
+int mft_lora_tn_group(const mft_lora_tn_problem* dev_problems, int32_t num_problems, int32_t max_colblocks, int32_t max_splits,
+                      int32_t any_long_split, int64_t max_rq, mft_stream_t stream);
 int mft_gemm_uses_tensor_cores(const mft_gemm_args* args);
 /* Measurement aid (no reference counterpart): while enabled, every tensor-core GEMM launch is bracketed by CUDA events on
  * its stream; read returns the summed algorithmic FLOPs (2*m*n*(k+k2)*batch), summed launch milliseconds and launch count. */

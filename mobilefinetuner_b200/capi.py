@@ -43,6 +43,11 @@ class TensorSlot(C.Structure):
                 ("bias_corr1", f32), ("bias_corr2", f32), ("bucket_offset", i64)]
 
 
+class LoraTnProblem(C.Structure):
+    _fields_ = [("s", vp), ("lds", i64), ("w", vp), ("ldw", i64), ("partial", vp), ("out", vp), ("ldo", i64), ("T", i64), ("q", i64),
+                ("r", i32), ("out_is_rq", i32), ("alpha", f32), ("use_tickets", i32), ("colblocks", i32), ("splits", i32), ("ticket_base", i32)]
+
+
 class ShadowSlot(C.Structure):
     _fields_ = [("src", vp), ("rows", i64), ("cols", i64), ("ld_src", i64), ("plain", vp), ("ld_plain", i64), ("transposed", vp),
                 ("ld_transposed", i64)]
@@ -67,6 +72,11 @@ SIGNATURES = {
     "mft_lora_down_bf16": (C.c_int, [vp, i64, vp, i64, vp, i64, vp, i64, i64, i64, i32, f32, vp]),
     "mft_lora_tn_workspace_bytes": (sz, [i64, i64, i32]),
     "mft_lora_tn": (C.c_int, [vp, i64, vp, i64, vp, i64, C.c_int, i64, i64, i32, f32, vp, sz, vp]),
+    "mft_lora_tn_group_eligible": (C.c_int, [i64, i64, i32, vp, i64]),
+    "mft_lora_tn_group_colblocks": (i32, [i64]),
+    "mft_lora_tn_group_splits": (i32, [i64]),
+    "mft_lora_tn_group_ticket_capacity": (i32, []),
+    "mft_lora_tn_group": (C.c_int, [vp, i32, i32, i32, i32, i64, vp]),
     "mft_gemm_uses_tensor_cores": (C.c_int, [C.POINTER(GemmArgs)]),
     "mft_gemm_profile": (C.c_int, [C.c_int]),
     "mft_gemm_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(i64)]),

@@ -1,4 +1,6 @@
+#include <memory>
 #include "autograd_engine.h"
+#include "ops_internal.h"
 
 #include <algorithm>
 #include <unordered_set>
@@ -119,6 +121,12 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
     }
     if (roots.empty()) { clear_graph(); return; }
 
+    // adapter-gradient products are recorded while the nodes run and launched together afterwards (one grouped kernel)
+    struct DeferGuard {
+        DeferGuard() { internal::begin_deferred_lora_tn(); }
+        ~DeferGuard() { try { internal::flush_deferred_lora_tn(); } catch (...) {} }
+    };
+    auto defer = std::make_unique<DeferGuard>();
     for (const auto& node : order_from(roots)) {
         if (!node || !node->tensor || !node->backward_fn) continue;
         auto it = pending_.find(node->tensor.get());
@@ -154,6 +162,9 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
         // interior gradients are dead once consumed (unless retained): release them early
         if (!node->tensor->retains_grad()) cur->grad.reset();
     }
+
+    internal::flush_deferred_lora_tn();      // every recorded dA / dB product, now (errors propagate; the guard then finds nothing left)
+    defer.reset();
 
     // write-back: leaves (nodes without a backward function) and retain_grad tensors; `.grad` is overwritten
     for (auto& kv : pending_) {

@@ -46,6 +46,10 @@ struct GemmCall {
 };
 void run_gemm(GemmCall g);
 
+// Adapter-gradient products (dA, dB) recorded during a backward pass and launched together at its end (ops_linear.cpp).
+void begin_deferred_lora_tn();
+void flush_deferred_lora_tn();
+
 // Backward node of y = gelu(x) (used by the fused linear+GELU op as well as ops::gelu).
 BackwardFunctionPtr make_gelu_backward(const TensorPtr& x);
 

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstring>
 #include <stdexcept>
+#include <unordered_map>
 
 #include "autograd_engine.h"
 #include "mft_b200.h"
@@ -274,8 +275,41 @@ void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, boo
     g.c = y->dev_f32_out(); g.ldc = r;
     run_gemm(g);
 }
+// ---- adapter gradients of one backward pass, batched: while the engine runs a backward, every eligible dA / dB product is
+// only recorded; flush_deferred_lora_tn() (called by the engine when the last node has run) does all of them in one grouped
+// launch. The operands stay untouched until then: tensors are never modified after they are produced, and the recorded
+// TensorPtrs keep them alive. MFT_LORA_TN_GROUP=0 launches each product on the spot as before.
+struct DeferredTn {
+    bool active = false;
+    std::vector<mft_lora_tn_problem> probs;
+    std::vector<TensorPtr> keep;
+    struct Table { void* host = nullptr; void* dev = nullptr; size_t bytes = 0; };
+    std::unordered_map<uint64_t, std::vector<Table>> tables;      // content hash -> immutable (pinned, device) copies
+} g_tn;
+
+bool tn_group_enabled() {
+    static const bool on = [] { const char* e = std::getenv("MFT_LORA_TN_GROUP"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 // out = S[T,r]^T W[T,q], written as [r,q] (out_is_rq) or [q,r]
 void lora_tn(const TensorPtr& S, const TensorPtr& W, int64_t T, int64_t q, int64_t r, bool out_is_rq, const TensorPtr& out) {
+    if (g_tn.active && (skinny_mask() & 2) && tn_group_enabled()) {
+        const float* wp = W->dev_f32();
+        if (mft_lora_tn_group_eligible(T, q, int32_t(r), wp, W->ld())) {
+            mft_lora_tn_problem p;
+            std::memset(&p, 0, sizeof(p));
+            p.colblocks = mft_lora_tn_group_colblocks(q);
+            p.splits = mft_lora_tn_group_splits(T);
+            auto partial = Tensor::make({int64_t(p.splits) * r * q}, kFloat32);
+            p.s = S->dev_f32(); p.lds = S->ld(); p.w = wp; p.ldw = W->ld(); p.partial = partial->dev_f32_out();
+            p.out = out->dev_f32_out(); p.ldo = out->ld(); p.T = T; p.q = q; p.r = int32_t(r); p.out_is_rq = out_is_rq ? 1 : 0; p.alpha = 1.0f;
+            p.use_tickets = p.splits <= 64 ? 1 : 0;
+            g_tn.probs.push_back(p);
+            g_tn.keep.push_back(S); g_tn.keep.push_back(W); g_tn.keep.push_back(out); g_tn.keep.push_back(partial);
+            return;
+        }
+    }
     if ((skinny_mask() & 2) && r >= 1 && r <= 64) {
         const size_t wsb = mft_lora_tn_workspace_bytes(T, q, int32_t(r));
         mft_rt::check(mft_lora_tn(S->dev_f32(), S->ld(), W->dev_f32(), W->ld(), out->dev_f32_out(), out->ld(), out_is_rq ? 1 : 0, T, q, int32_t(r),
@@ -289,6 +323,54 @@ void lora_tn(const TensorPtr& S, const TensorPtr& W, int64_t T, int64_t q, int64
     g.c = out->dev_f32_out(); g.ldc = out->ld();
     run_gemm(g);
 }
+
+}  // namespace
+
+namespace internal {
+void begin_deferred_lora_tn() { g_tn.active = true; }
+void flush_deferred_lora_tn() {
+    g_tn.active = false;
+    if (g_tn.probs.empty()) return;
+    // ticket ranges; problems that do not fit the ticket table fall back to the separate reduce pass
+    int32_t base = 0, max_cb = 1, max_sp = 1, any_long = 0;
+    int64_t max_rq = 1;
+    const int32_t cap = mft_lora_tn_group_ticket_capacity();
+    for (auto& p : g_tn.probs) {
+        if (p.use_tickets && base + p.colblocks > cap) p.use_tickets = 0;
+        if (p.use_tickets) { p.ticket_base = base; base += p.colblocks; } else any_long = 1;
+        max_cb = std::max(max_cb, p.colblocks); max_sp = std::max(max_sp, p.splits);
+        max_rq = std::max<int64_t>(max_rq, int64_t(p.r) * p.q);
+    }
+    // The table is uploaded from pinned memory; under CUDA-graph replay that copy is re-executed, so a (pinned, device) pair
+    // is written once and never changed: one pair per distinct table content (a step's problems repeat with the same
+    // addresses, thanks to the step arena).
+    const size_t bytes = g_tn.probs.size() * sizeof(mft_lora_tn_problem);
+    uint64_t h = 1469598103934665603ull;
+    const unsigned char* raw = reinterpret_cast<const unsigned char*>(g_tn.probs.data());
+    for (size_t i = 0; i < bytes; ++i) { h ^= raw[i]; h *= 1099511628211ull; }
+    DeferredTn::Table* tab = nullptr;
+    for (auto& c : g_tn.tables[h])
+        if (c.bytes == bytes && std::memcmp(c.host, raw, bytes) == 0) { tab = &c; break; }
+    if (!tab) {
+        DeferredTn::Table c;
+        c.bytes = bytes;
+        c.host = mft_rt::pinned_alloc(bytes);
+        std::memcpy(c.host, raw, bytes);
+        { mft_rt::PersistentScope keep; c.dev = mft_rt::dev_alloc(bytes); }
+        g_tn.tables[h].push_back(c);
+        tab = &g_tn.tables[h].back();
+    }
+    mft_rt::h2d(tab->dev, tab->host, bytes);
+    const int32_t n = int32_t(g_tn.probs.size());
+    g_tn.probs.clear();
+    std::vector<TensorPtr> keep;
+    keep.swap(g_tn.keep);               // released when this function returns: the launch below is already enqueued
+    mft_rt::check(mft_lora_tn_group(static_cast<const mft_lora_tn_problem*>(tab->dev), n, max_cb, max_sp, any_long, max_rq, mft_rt::stream()),
+                  "mft_lora_tn_group");
+}
+}  // namespace internal
+
+namespace {
 
 // One node for  y = x W (+b) + sum_i s_i (x A_i) B_i.
 // Backward (per term, s folded into xa / dxa):   dB = xa^T gy ;  dxa = s gy B^T ;  dA = x^T dxa ;

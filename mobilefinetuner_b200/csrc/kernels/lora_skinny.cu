@@ -234,16 +234,15 @@ constexpr int kTnMaxTickets = 1024;
 __device__ unsigned g_tn_tickets[kTnMaxTickets];
 
 template <int CPT, int RMAX>
-__global__ void __launch_bounds__(kTnRG * kTnCT)
-lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
+__device__ __forceinline__ void lora_tn_body(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
                float* __restrict__ partial, int64_t T, int q, int r, float* __restrict__ out, int64_t ldo, int out_is_rq,
-               float alpha, int use_tickets) {
+               float alpha, int use_tickets, const int bx, const int by, const int nsplits, unsigned* __restrict__ tickets) {
     extern __shared__ __align__(16) float sm[];
     float* Ss = sm;                                  // [kTnRows][RMAX]
     float* red = sm + kTnRows * RMAX;                // [RMAX][kTnCT * CPT]
     const int ct = threadIdx.x % kTnCT, rg = threadIdx.x / kTnCT;
-    const int col = (blockIdx.x * kTnCT + ct) * CPT;
-    const int64_t t0 = int64_t(blockIdx.y) * kTnRows;
+    const int col = (bx * kTnCT + ct) * CPT;
+    const int64_t t0 = int64_t(by) * kTnRows;
     constexpr int RPG = kTnRows / kTnRG;             // rows per row-group (32): every W load of the thread is issued up front
     const bool colok = col < q;                      // q % CPT == 0 is guaranteed by the launcher
     float wv[RPG][CPT];
@@ -305,28 +304,27 @@ lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict
         __syncthreads();
     }
     constexpr int W = kTnCT * CPT;                   // columns of this CTA
-    float* P = partial + size_t(blockIdx.y) * size_t(r) * q;
+    float* P = partial + size_t(by) * size_t(r) * q;
     for (int idx = threadIdx.x; idx < r * W; idx += kTnRG * kTnCT) {
         const int c = idx / W, cc = idx % W;
-        const int gcol = blockIdx.x * W + cc;
+        const int gcol = bx * W + cc;
         if (gcol < q) P[size_t(c) * q + gcol] = red[c * W + cc];
     }
     if (!use_tickets) return;                        // separate reduce kernel follows
-    unsigned* tickets = g_tn_tickets;
     // The CTA that finishes last for this column block sums the token splits in index order (so the result does not
     // depend on which CTA that is), applies alpha and writes the output; it leaves the ticket counter at zero again.
     __shared__ bool last;
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) last = atomicAdd(&tickets[blockIdx.x], 1u) == gridDim.y - 1;
+    if (threadIdx.x == 0) last = atomicAdd(&tickets[bx], 1u) == unsigned(nsplits - 1);
     __syncthreads();
     if (!last) return;
     __threadfence();
-    const int splits = gridDim.y;
+    const int splits = nsplits;
     const size_t n = size_t(r) * q;
     for (int idx = threadIdx.x; idx < r * W; idx += kTnRG * kTnCT) {
         const int c = idx / W, cc = idx % W;
-        const int gcol = blockIdx.x * W + cc;
+        const int gcol = bx * W + cc;
         if (gcol >= q) continue;
         const float* src = partial + size_t(c) * q + gcol;
         float v = 0.f;
@@ -342,7 +340,28 @@ lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict
         v *= alpha;
         if (out_is_rq) out[int64_t(c) * ldo + gcol] = v; else out[int64_t(gcol) * ldo + c] = v;
     }
-    if (threadIdx.x == 0) tickets[blockIdx.x] = 0;
+    if (threadIdx.x == 0) tickets[bx] = 0;
+}
+
+template <int CPT, int RMAX>
+__global__ void __launch_bounds__(kTnRG * kTnCT)
+lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
+               float* __restrict__ partial, int64_t T, int q, int r, float* __restrict__ out, int64_t ldo, int out_is_rq,
+               float alpha, int use_tickets) {
+    lora_tn_body<CPT, RMAX>(s, lds, w, ldw, partial, T, q, r, out, ldo, out_is_rq, alpha, use_tickets, int(blockIdx.x), int(blockIdx.y), int(gridDim.y),
+                            g_tn_tickets);
+}
+
+// Grouped form: blockIdx.z selects one of many independent products (every adapter gradient of a backward pass, deferred
+// to its end), each with its own shapes; CTAs outside a problem's (column blocks x token splits) grid exit at once.
+constexpr int kTnGroupTickets = 32768;
+__device__ unsigned g_tn_group_tickets[kTnGroupTickets];
+__global__ void __launch_bounds__(kTnRG * kTnCT)
+lora_tn_group_kernel(const mft_lora_tn_problem* __restrict__ probs) {
+    const mft_lora_tn_problem p = probs[blockIdx.z];
+    if (int(blockIdx.x) >= p.colblocks || int(blockIdx.y) >= p.splits) return;
+    lora_tn_body<2, 16>(p.s, p.lds, p.w, p.ldw, p.partial, p.T, int(p.q), p.r, p.out, p.ldo, p.out_is_rq, p.alpha, p.use_tickets, int(blockIdx.x),
+                        int(blockIdx.y), p.splits, g_tn_group_tickets + p.ticket_base);
 }
 
 // out[c][col] (out_is_rq) or out[col][c] = alpha * sum over splits, fixed order
@@ -363,6 +382,28 @@ __global__ void lora_tn_reduce_kernel(const float* __restrict__ partial, float* 
         for (; sp < splits; ++sp) v += __ldcg(partial + size_t(sp) * n + idx);
         v *= alpha;
         if (out_is_rq) out[int64_t(c) * ldo + col] = v; else out[int64_t(col) * ldo + c] = v;
+    }
+}
+
+// grouped reduce for the problems whose split list is too long for the last-CTA sum
+__global__ void lora_tn_group_reduce_kernel(const mft_lora_tn_problem* __restrict__ probs) {
+    const mft_lora_tn_problem p = probs[blockIdx.y];
+    if (p.use_tickets) return;
+    const int64_t n = int64_t(p.r) * p.q;
+    for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
+        const int c = int(idx / p.q), col = int(idx % p.q);
+        float v = 0.f;
+        int sp = 0;
+        for (; sp + 8 <= p.splits; sp += 8) {
+            float pv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) pv[u] = __ldcg(p.partial + size_t(sp + u) * n + idx);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v += pv[u];
+        }
+        for (; sp < p.splits; ++sp) v += __ldcg(p.partial + size_t(sp) * n + idx);
+        v *= p.alpha;
+        if (p.out_is_rq) p.out[int64_t(c) * p.ldo + col] = v; else p.out[int64_t(col) * p.ldo + c] = v;
     }
 }
 
@@ -583,3 +624,30 @@ extern "C" int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a
     MFT_CHECK_LAUNCH("mft_lora_down_bf16");
     return 0;
 }
+
+// ---- grouped lora_tn: many independent products in one launch (problem table in device memory)
+extern "C" int mft_lora_tn_group_eligible(int64_t T, int64_t q, int32_t r, const float* w, int64_t ldw) {
+    return (r >= 1 && r <= 16 && T > 0 && q > 0 && (q & 1) == 0 && (ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(w) & 7) == 0 &&
+            ceil_div(T, kTnRows) <= 65535) ? 1 : 0;
+}
+extern "C" int32_t mft_lora_tn_group_colblocks(int64_t q) { return int32_t(ceil_div(q, int64_t(kTnCT) * 2)); }
+extern "C" int32_t mft_lora_tn_group_splits(int64_t T) { return int32_t(ceil_div(T, kTnRows)); }
+
+extern "C" int mft_lora_tn_group(const mft_lora_tn_problem* dev_problems, int32_t num_problems, int32_t max_colblocks, int32_t max_splits,
+                                 int32_t any_long_split, int64_t max_rq, mft_stream_t stream) {
+    if (num_problems == 0) return 0;
+    if (!dev_problems) return set_error(1, "mft_lora_tn_group: null problem table");
+    if (num_problems > 65535 || max_splits > 65535 || max_colblocks < 1 || max_splits < 1) return set_error(1, "mft_lora_tn_group: grid out of range");
+    cudaStream_t st = as_stream(stream);
+    const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
+    lora_tn_group_kernel<<<dim3(unsigned(max_colblocks), unsigned(max_splits), unsigned(num_problems)), kTnRG * kTnCT, smem, st>>>(dev_problems);
+    if (any_long_split) {
+        add_launches(1);
+        int64_t bx = ceil_div(max_rq > 0 ? max_rq : 1, int64_t(256));
+        if (bx > 64) bx = 64;
+        lora_tn_group_reduce_kernel<<<dim3(unsigned(bx), unsigned(num_problems)), 256, 0, st>>>(dev_problems);
+    }
+    MFT_CHECK_LAUNCH("mft_lora_tn_group");
+    return 0;
+}
+extern "C" int32_t mft_lora_tn_group_ticket_capacity(void) { return kTnGroupTickets; }

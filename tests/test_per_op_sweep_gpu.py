@@ -183,3 +183,39 @@ def test_lora_down_on_bf16_operands(capi, T, K, r):
     assert rel(y, e16) < 1e-5
     assert rel(y, 2.0 * (x.astype(np.float64) @ A.astype(np.float64))) < BF16_TOL
     assert torch.equal(y16, y.to(torch.bfloat16))
+
+
+def test_lora_tn_group_equals_individual_launches(capi):
+    """mft_lora_tn_group: several S^T W products of different shapes in one launch == mft_lora_tn one by one (bit for bit: same
+    kernel body, same fixed summation order), including a problem whose split list is too long for the last-CTA sum."""
+    rng = np.random.default_rng(21)
+    cases = [(512, 768, 8, 1), (4096, 1024, 16, 0), (1000, 2304, 16, 1), (128 * 70, 256, 4, 1), (300, 640, 8, 0)]
+    keep, outs, refs = [], [], []
+    probs = (capi.LoraTnProblem * len(cases))()
+    base, max_cb, max_sp, any_long, max_rq = 0, 1, 1, 0, 1
+    for i, (T, q, r, rq) in enumerate(cases):
+        S = dev(rng.standard_normal((T, r)).astype(np.float32))
+        W = dev(rng.standard_normal((T, q)).astype(np.float32))
+        out = torch.full((r, q) if rq else (q, r), float("nan"), device="cuda")
+        ref = torch.empty_like(out)
+        w1 = ws(capi.lib.mft_lora_tn_workspace_bytes(T, q, r))
+        capi.call("mft_lora_tn", S, r, W, q, ref, out.shape[1], rq, T, q, r, 1.0, w1, w1.numel(), None)
+        assert capi.lib.mft_lora_tn_group_eligible(T, q, r, W.data_ptr(), q) == 1
+        part = ws(capi.lib.mft_lora_tn_workspace_bytes(T, q, r))
+        cb, sp = capi.lib.mft_lora_tn_group_colblocks(q), capi.lib.mft_lora_tn_group_splits(T)
+        tk = 1 if sp <= 64 else 0
+        probs[i] = capi.LoraTnProblem(S.data_ptr(), r, W.data_ptr(), q, part.data_ptr(), out.data_ptr(), out.shape[1], T, q, r, rq, 1.0, tk, cb, sp, base)
+        if tk:
+            base += cb
+        else:
+            any_long = 1
+        max_cb, max_sp, max_rq = max(max_cb, cb), max(max_sp, sp), max(max_rq, r * q)
+        keep += [S, W, part]; outs.append(out); refs.append(ref)
+    table = torch.frombuffer(bytearray(bytes(probs)), dtype=torch.uint8).cuda()
+    for _ in range(2):                       # twice: the ticket counters must be back at zero after a launch
+        for o in outs:
+            o.fill_(float("nan"))
+        capi.call("mft_lora_tn_group", table, len(cases), max_cb, max_sp, any_long, max_rq, None)
+        torch.cuda.synchronize()
+        for o, e in zip(outs, refs):
+            assert torch.equal(o, e)
