@@ -98,7 +98,8 @@ int mft_lora_down(const float* x, int64_t ldx, const float* a, int64_t lda, int 
 int mft_lora_down_ex(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy, void* y_bf16,
                      int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);
 /* The same product on bf16 operands (bf16 operand mode): x as the bf16 copy its producer wrote, A as its K-major bf16 shadow
- * [r][K] (pitch lda) — the array the rank-r segment of mft_gemm_bf16 reads. r <= 16, K a multiple of 128 up to 6144; pitches
+ * [r][K] (pitch lda) — the array the rank-r segment of mft_gemm_bf16 reads. r <= 64; K a multiple of 128, up to 6144 (r <= 16),
+ * 3072 (r <= 32) or 1536 (r <= 64): the whole shadow is staged in shared memory; pitches
  * multiples of 8, 16-byte aligned bases. y is fp32 [T, r]; y_bf16 (NULL = off) its bf16 copy. */
 int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a_kmajor_bf16, int64_t lda, float* y, int64_t ldy, void* y_bf16,
                        int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream);

@@ -245,8 +245,8 @@ void lora_down(const TensorPtr& x, int64_t T, int64_t K, const TensorPtr& A, boo
     // factor's K-major bf16 shadow. MFT_LORA_DOWN_BF16=0 keeps the fp32 kernel.
     const char* lowp_env = std::getenv("MFT_LORA_DOWN_BF16");          // read per call: tests compare the two paths
     const bool lowp_on = !(lowp_env && lowp_env[0] == '0');
-    if (lowp_on && (skinny_mask() & 1) && emit_bf16_operands() && gemm_precision() == 1 && mft_tensor_cores_enabled() && r >= 1 && r <= 16 &&
-        K % 128 == 0 && K <= 6144 && x->has_bf16() && A->ndim() == 2) {
+    if (lowp_on && (skinny_mask() & 1) && emit_bf16_operands() && gemm_precision() == 1 && mft_tensor_cores_enabled() && r >= 1 && r <= 64 &&
+        K % 128 == 0 && K <= (r <= 16 ? 6144 : (r <= 32 ? 3072 : 1536)) && x->has_bf16() && A->ndim() == 2) {
         auto xv = x->bf16_view();
         auto av = a_is_kr ? A->bf16_transposed_view() : A->bf16_view();      // [r][K], cached per version of the factor
         if (xv.ld % 8 == 0 && av.ld % 8 == 0) {

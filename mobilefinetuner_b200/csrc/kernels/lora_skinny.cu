@@ -527,19 +527,21 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 
 constexpr int kLbPad = 32;      // bf16 elements of padding per shadow row in shared memory (64 bytes: conflict-free 16-byte reads)
 
+template <int NT>     // output columns in tiles of 8: rank <= 8 * NT
 __global__ void __launch_bounds__(128)
 lora_down_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ldx, const __nv_bfloat16* __restrict__ at, int64_t lda,
                       float* __restrict__ y, int64_t ldy, __nv_bfloat16* __restrict__ y16, int64_t ld16, int64_t T, int K, int r, float alpha) {
     extern __shared__ __align__(16) uint8_t lb_smem[];
     const int KP = K + kLbPad;
-    __nv_bfloat16* sA = reinterpret_cast<__nv_bfloat16*>(lb_smem);                 // [16][KP]
-    float* red = reinterpret_cast<float*>(lb_smem + size_t(16) * KP * 2);           // [4 warps][16 rows][16 cols]
+    constexpr int RC = 8 * NT;                                                       // shadow rows / output columns held
+    __nv_bfloat16* sA = reinterpret_cast<__nv_bfloat16*>(lb_smem);                 // [RC][KP]
+    float* red = reinterpret_cast<float*>(lb_smem + size_t(RC) * KP * 2);           // [4 warps][16 rows][RC cols]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     const int KQ = K >> 2;                                                           // this warp's K quarter (multiple of 32)
     // shadow -> shared memory (rows >= r are zero)
     {
         const int chunks = K >> 3;                                                   // 16-byte pieces per row
-        for (int idx = threadIdx.x; idx < 16 * chunks; idx += 128) {
+        for (int idx = threadIdx.x; idx < RC * chunks; idx += 128) {
             const int c = idx / chunks, pc = idx % chunks;
             const uint32_t dst = static_cast<uint32_t>(__cvta_generic_to_shared(sA + c * KP + pc * 8));
             const int nb = c < r ? 16 : 0;
@@ -554,9 +556,9 @@ lora_down_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ldx, const __
         const bool live0 = row0 + g < T, live1 = row0 + g + 8 < T;
         const __nv_bfloat16* x0 = x + (live0 ? row0 + g : 0) * ldx + warp * KQ + 8 * t;
         const __nv_bfloat16* x1 = x + (live1 ? row0 + g + 8 : 0) * ldx + warp * KQ + 8 * t;
-        float acc[2][4];
+        float acc[NT][4];
 #pragma unroll
-        for (int n = 0; n < 2; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+        for (int n = 0; n < NT; ++n) acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
         for (int kc = 0; kc < KQ; kc += 256) {
             uint4 xa[8], xb[8];
             const int nit = min(8, (KQ - kc) >> 5);
@@ -574,27 +576,27 @@ lora_down_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ldx, const __
             for (int i = 0; i < 8; ++i) {
                 if (i >= nit) break;
                 const __nv_bfloat16* bp = sA + g * KP + warp * KQ + kc + 32 * i + 8 * t;
-                const uint4 b0 = *reinterpret_cast<const uint4*>(bp);               // output column g
-                const uint4 b1 = *reinterpret_cast<const uint4*>(bp + 8 * KP);      // output column g + 8
-                mma_bf16_16816(acc[0], xa[i].x, xb[i].x, xa[i].y, xb[i].y, b0.x, b0.y);
-                mma_bf16_16816(acc[1], xa[i].x, xb[i].x, xa[i].y, xb[i].y, b1.x, b1.y);
-                mma_bf16_16816(acc[0], xa[i].z, xb[i].z, xa[i].w, xb[i].w, b0.z, b0.w);
-                mma_bf16_16816(acc[1], xa[i].z, xb[i].z, xa[i].w, xb[i].w, b1.z, b1.w);
+#pragma unroll
+                for (int n = 0; n < NT; ++n) {
+                    const uint4 b0 = *reinterpret_cast<const uint4*>(bp + n * 8 * KP);   // output column 8n + g
+                    mma_bf16_16816(acc[n], xa[i].x, xb[i].x, xa[i].y, xb[i].y, b0.x, b0.y);
+                    mma_bf16_16816(acc[n], xa[i].z, xb[i].z, xa[i].w, xb[i].w, b0.z, b0.w);
+                }
             }
         }
         // the four warps hold partial sums over their K quarters: add them in warp order through shared memory
 #pragma unroll
-        for (int n = 0; n < 2; ++n) {
-            float* base = red + warp * 256 + n * 8 + 2 * t;
-            base[g * 16] = acc[n][0]; base[g * 16 + 1] = acc[n][1];
-            base[(g + 8) * 16] = acc[n][2]; base[(g + 8) * 16 + 1] = acc[n][3];
+        for (int n = 0; n < NT; ++n) {
+            float* base = red + warp * (16 * RC) + n * 8 + 2 * t;
+            base[g * RC] = acc[n][0]; base[g * RC + 1] = acc[n][1];
+            base[(g + 8) * RC] = acc[n][2]; base[(g + 8) * RC + 1] = acc[n][3];
         }
         __syncthreads();
-        for (int idx = threadIdx.x; idx < 256; idx += 128) {
-            const int rr = idx >> 4, c = idx & 15;
+        for (int idx = threadIdx.x; idx < 16 * RC; idx += 128) {
+            const int rr = idx / RC, c = idx % RC;
             const int64_t row = row0 + rr;
             if (row < T && c < r) {
-                const float v = (((red[idx] + red[256 + idx]) + red[512 + idx]) + red[768 + idx]) * alpha;
+                const float v = (((red[idx] + red[16 * RC + idx]) + red[2 * 16 * RC + idx]) + red[3 * 16 * RC + idx]) * alpha;
                 y[row * ldy + c] = v;
                 if (y16) y16[row * ld16 + c] = __float2bfloat16_rn(v);
             }
@@ -610,17 +612,30 @@ extern "C" int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a
                                   int64_t ld_bf16, int64_t T, int64_t K, int32_t r, float alpha, mft_stream_t stream) {
     if (T == 0 || r == 0) return 0;
     if (!x_bf16 || !a_kmajor_bf16 || !y) return set_error(1, "mft_lora_down_bf16: null pointer");
-    if (r < 1 || r > 16) return set_error(1, "mft_lora_down_bf16: rank %d outside 1..16", r);
-    if (K < 128 || (K & 127) || K > 6144) return set_error(1, "mft_lora_down_bf16: K must be a multiple of 128 in 128..6144");
+    if (r < 1 || r > 64) return set_error(1, "mft_lora_down_bf16: rank %d outside 1..64", r);
+    const int nt = r <= 8 ? 1 : (r <= 16 ? 2 : (r <= 32 ? 4 : 8));
+    const int64_t kmax = nt <= 2 ? 6144 : (nt == 4 ? 3072 : 1536);          // the whole shadow must fit in shared memory
+    if (K < 128 || (K & 127) || K > kmax) return set_error(1, "mft_lora_down_bf16: K must be a multiple of 128 in 128..%lld for rank %d", (long long)kmax, r);
     if ((ldx & 7) || (lda & 7) || !aligned16(x_bf16) || !aligned16(a_kmajor_bf16)) return set_error(1, "mft_lora_down_bf16: operands must be 16-byte aligned with pitches that are multiples of 8");
-    const size_t smem = size_t(16) * size_t(K + kLbPad) * 2 + 4096;
+    const size_t smem = size_t(8 * nt) * size_t(K + kLbPad) * 2 + size_t(4) * 16 * 8 * nt * sizeof(float);
     static bool attr_set[kMaxDevices] = {};
-    if (first_use_on_device(attr_set)) cudaFuncSetAttribute(lora_down_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * (6144 + kLbPad) * 2 + 4096);
+    if (first_use_on_device(attr_set)) {
+        cudaFuncSetAttribute(lora_down_bf16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(lora_down_bf16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(lora_down_bf16_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(lora_down_bf16_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    }
     const int64_t nblk = ceil_div(T, int64_t(16));
     const int64_t cap = int64_t(kNumSMs) * 4;
     const unsigned grid = unsigned(nblk < cap ? nblk : cap);
-    lora_down_bf16_kernel<<<grid, 128, smem, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(x_bf16), ldx, static_cast<const __nv_bfloat16*>(a_kmajor_bf16), lda,
-                                                                  y, ldy, static_cast<__nv_bfloat16*>(y_bf16), ld_bf16, T, int(K), r, alpha);
+    const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x_bf16);
+    const __nv_bfloat16* ap = static_cast<const __nv_bfloat16*>(a_kmajor_bf16);
+    __nv_bfloat16* y16 = static_cast<__nv_bfloat16*>(y_bf16);
+    cudaStream_t st = as_stream(stream);
+    if (nt == 1) lora_down_bf16_kernel<1><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else if (nt == 2) lora_down_bf16_kernel<2><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else if (nt == 4) lora_down_bf16_kernel<4><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else lora_down_bf16_kernel<8><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
     MFT_CHECK_LAUNCH("mft_lora_down_bf16");
     return 0;
 }

@@ -166,7 +166,8 @@ def test_cross_entropy_sweep_tokens_up_to_65536(capi, B, S, V):
             break                                                 # a full-sequence oracle call per row is slow at V = 262144
 
 
-@pytest.mark.parametrize("T,K,r", [(512, 768, 8), (4096, 1024, 16), (1000, 3072, 16), (37, 128, 3), (8192, 4096, 16), (300, 640, 8)])
+@pytest.mark.parametrize("T,K,r", [(512, 768, 8), (4096, 1024, 16), (1000, 3072, 16), (37, 128, 3), (8192, 4096, 16), (300, 640, 8),
+                                   (2048, 1024, 32), (1000, 1536, 64), (512, 3072, 24), (700, 768, 40)])
 def test_lora_down_on_bf16_operands(capi, T, K, r):
     """mft_lora_down_bf16 (x and the factor's K-major shadow as bf16, mma.sync bf16, fp32 accumulate) against fp64 on the
     same bf16-rounded inputs (summation order only: 1e-5) and against the fp32 inputs (bf16 operand tolerance 1e-2)."""

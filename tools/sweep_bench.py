@@ -4,8 +4,8 @@ cross-entropy through the C ABI, timed with CUDA events, L2 flushed between iter
 
     python tools/sweep_bench.py [--json] [--quick] [--out profiles/r2_c5_sweep.txt]
 
-LoRA linear, bf16 operand mode (what bench.py runs): forward = mft_lora_down_ex (x*A, fp32 + bf16 copy) + mft_gemm_bf16 with
-the rank-r second K segment; backward = mft_lora_down_ex (dY*B^T) + mft_gemm_bf16 (dX, second segment dxa*A^T) + two
+LoRA linear, bf16 operand mode (what bench.py runs): forward = mft_lora_down_bf16 (x*A from the bf16 rows) + mft_gemm_bf16 with
+the rank-r second K segment; backward = mft_lora_down_bf16 (dY*B^T) + mft_gemm_bf16 (dX, second segment dxa*A^T) + two
 mft_lora_tn (dA, dB). FLOPs per SURVEY §8d: fwd 2*T*in*out + 2*T*r*(in+out); bwd the same + 2*T*in*r + 2*T*r*out.
 Cross-entropy: mft_lm_ce_fwd + mft_lm_ce_bwd_ex on fp32 logits; bytes = 4*T*V read (forward) + 4*T*V read + 4*T*V written
 (backward) = 12*T*V (the unfused figure of §8d; the second forward pass is served from L2 and not counted).
@@ -72,12 +72,22 @@ def lora_point(T, d_in, d_out, r, iters):
     w1 = torch.empty(max(capi.lib.mft_lora_tn_workspace_bytes(T, d_in, r), 16), dtype=torch.uint8, device="cuda")
     w2 = torch.empty(max(capi.lib.mft_lora_tn_workspace_bytes(T, d_out, r), 16), dtype=torch.uint8, device="cuda")
 
+    At16, B16 = A.t().contiguous().bfloat16(), B.bfloat16()             # K-major shadows of the factors: [r,in], [r,out]
+    kmax = 6144 if r <= 16 else (3072 if r <= 32 else 1536)
+    lowp_f, lowp_b = d_in % 128 == 0 and d_in <= kmax, d_out % 128 == 0 and d_out <= kmax
+
     def fwd():
-        capi.call("mft_lora_down_ex", x, d_in, A, r, 1, xa, r, xa16, r, T, d_in, r, 2.0, None)
+        if lowp_f:
+            capi.call("mft_lora_down_bf16", x16, d_in, At16, d_in, xa, r, xa16, r, T, d_in, r, 2.0, None)
+        else:
+            capi.call("mft_lora_down_ex", x, d_in, A, r, 1, xa, r, xa16, r, T, d_in, r, 2.0, None)
         gemm_bf16(T, d_out, d_in, x16, Wt16, y, r, xa16, Bt16, bias)
 
     def bwd():
-        capi.call("mft_lora_down_ex", gy, d_out, B, d_out, 0, dxa, r, dxa16, r, T, d_out, r, 2.0, None)
+        if lowp_b:
+            capi.call("mft_lora_down_bf16", gy16, d_out, B16, d_out, dxa, r, dxa16, r, T, d_out, r, 2.0, None)
+        else:
+            capi.call("mft_lora_down_ex", gy, d_out, B, d_out, 0, dxa, r, dxa16, r, T, d_out, r, 2.0, None)
         gemm_bf16(T, d_in, d_out, gy16, W16, dx, r, dxa16, A16)
         capi.call("mft_lora_tn", dxa, r, x, d_in, dA, r, 0, T, d_in, r, 1.0, w1, w1.numel(), None)
         capi.call("mft_lora_tn", xa, r, gy, d_out, dB, d_out, 1, T, d_out, r, 1.0, w2, w2.numel(), None)
