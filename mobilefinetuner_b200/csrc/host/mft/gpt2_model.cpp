@@ -242,6 +242,9 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr
         LinearFusion f;
         f.gelu_act = &h;
         f.gelu_bf16_only = lowp && fc_out_plain && !fuse;
+        // the pre-activation is read by GeluBackward only (which takes bf16): MFT_BF16_PREACT=0 keeps it in fp32
+        static const bool preact16 = [] { const char* e = std::getenv("MFT_BF16_PREACT"); return !(e && e[0] == '0'); }();
+        f.out_bf16_only = f.gelu_bf16_only && preact16;
         if (w.lora_initialized && w.fc_in_lin) pre = w.fc_in_lin->forward_fused(x3, f);
         else pre = fused_lora_linear(x3, w.mlp_fc_in_weight, w.mlp_fc_in_bias, {}, f);
     }

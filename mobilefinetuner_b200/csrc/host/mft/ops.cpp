@@ -153,7 +153,8 @@ void run_gemm(GemmCall g) {
         const bool diet = bf16_only_results();
         const bool plain_epilogue = g.beta == 0.0f && !g.addend && !g.gelu_grad_x;
         const bool gelu_here = g.gelu_out != nullptr || (g.gelu_tensor && g.gelu_bf16_only);
-        if (g.c_tensor && !g.c && diet && g.c_bf16_only && plain_epilogue && !gelu_here && g.c_tensor->is_dense() && g.n % 8 == 0 && emit_bf16_operands()) {
+        (void)gelu_here;
+        if (g.c_tensor && !g.c && diet && g.c_bf16_only && plain_epilogue && g.c_tensor->is_dense() && g.n % 8 == 0 && emit_bf16_operands()) {
             auto e = g.c_tensor->bf16_only_out();                 // bf16 is the only copy of the result
             a.c = nullptr; a.c_bf16 = e.ptr; a.ldc_bf16 = e.ld;
         } else {

@@ -51,7 +51,10 @@ public:
             auto gv = gy->bf16_view();
             if (gv.ld == gy->shape().back()) {
                 auto e = gx->bf16_only_out();
-                mft_rt::check(mft_gelu_bwd_lowp(x_->dev_f32(), 0, gv.ptr, nullptr, e.ptr, x_->numel(), st()), "mft_gelu_bwd_lowp");
+                if (x_->f32_pending() && x_->has_bf16() && x_->bf16_view().ld == x_->shape().back())      // the pre-activation itself exists as bf16 only
+                    mft_rt::check(mft_gelu_bwd_lowp(x_->bf16_view().ptr, 1, gv.ptr, nullptr, e.ptr, x_->numel(), st()), "mft_gelu_bwd_lowp");
+                else
+                    mft_rt::check(mft_gelu_bwd_lowp(x_->dev_f32(), 0, gv.ptr, nullptr, e.ptr, x_->numel(), st()), "mft_gelu_bwd_lowp");
                 return {gx};
             }
         }

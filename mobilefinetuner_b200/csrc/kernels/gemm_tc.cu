@@ -382,7 +382,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 float4 old = *reinterpret_cast<const float4*>(dst);
                                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
                             }
-                            *reinterpret_cast<float4*>(dst) = o;
+                            if (p.c) *reinterpret_cast<float4*>(dst) = o;          // c == NULL: pre-activation kept as bf16 only
                             if (p.c16) st_bf16x4(p.c16 + int64_t(grow) * p.ld_c16 + col, o);
                             if (gbase || p.gelu16) {
                                 const float4 gv = make_float4(gelu_tanh_f(o.x), gelu_tanh_f(o.y), gelu_tanh_f(o.z), gelu_tanh_f(o.w));
@@ -456,7 +456,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             if (p.beta != 0.f) o += p.beta * *dst;
                             if (FUSED && abase) o += abase[int64_t(grow) * p.ld_addend + cc];
                             if (FUSED && xbase) o *= gelu_tanh_grad_f(xbase[int64_t(grow) * p.ld_gelu_grad_x + cc]);
-                            *dst = o;
+                            if (p.c) *dst = o;
                             if (p.c16) p.c16[int64_t(grow) * p.ld_c16 + cc] = __float2bfloat16_rn(o);
                             if (gbase || p.gelu16) {
                                 const float gv = gelu_tanh_f(o);
@@ -643,9 +643,10 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     //  32-value row per thread run with no other warp to hide their latency, measured 125 us vs 81 us on fc_in)
     static const bool tma_gelu = [] { const char* e = getenv("MFT_GEMM_TMA_GELU"); return e && e[0] == '1'; }();
     const bool bf16_only = p.c == nullptr;                          // the result leaves as bf16 alone (64-column TMA boxes)
+    const bool gelu_aux = p.gelu_out || p.gelu_out_bf16;
     if (bf16_only) {
-        if (!p.c_bf16 || FUSED || p.beta != 0.f || p.gelu_out || p.gelu_out_bf16 || !aligned16(p.c_bf16) || (p.ldc_bf16 & 7) || p.batch != 1)
-            return set_error(1, "mft_gemm(tc): a bf16-only result needs c_bf16 (16-byte aligned, pitch %% 8 == 0), beta = 0, batch 1 and no GELU / fused operands");
+        if (!p.c_bf16 || FUSED || p.beta != 0.f || !aligned16(p.c_bf16) || (p.ldc_bf16 & 7) || p.batch != 1)
+            return set_error(1, "mft_gemm(tc): a bf16-only result needs c_bf16 (16-byte aligned, pitch %% 8 == 0), beta = 0, batch 1 and no fused operands");
     }
     const bool c_ok = !bf16_only && !FUSED && p.beta == 0.f && aligned16(p.c) && (p.ldc & 3) == 0 && (p.batch == 1 || (p.stride_c & 3) == 0) &&
                       !p.gelu_out_bf16 && (!p.gelu_out || (tma_gelu && aligned16(p.gelu_out))) &&   // the box path writes no bf16 GELU copy
@@ -656,15 +657,16 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
         tma_c = make_store_map(&mc, p.c, p.n, p.m, p.batch, p.ldc, p.stride_c) &&
                 (!p.gelu_out || make_store_map(&mg, p.gelu_out, p.n, p.m, p.batch, p.ldc, p.stride_c));
     }
-    if (bf16_only) {
+    const bool box16 = bf16_only && !gelu_aux;      // with a GELU aux output the register path writes both bf16 arrays
+    if (box16) {
         if (!make_store_map(&mg, p.c_bf16, p.n, p.m, 1, p.ldc_bf16, 0, true)) return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (bf16 result)");
         mc = mg;
         tma_c = true;
     } else if (!tma_c) { mc = ma; mg = ma; } else if (!p.gelu_out) mg = mc;
     TcArgs a;
     a.tma_c = tma_c ? 1 : 0;
-    a.tma_c16 = bf16_only ? 1 : 0;
-    a.c16 = bf16_only ? nullptr : static_cast<__nv_bfloat16*>(p.c_bf16); a.ld_c16 = p.ldc_bf16;
+    a.tma_c16 = box16 ? 1 : 0;
+    a.c16 = box16 ? nullptr : static_cast<__nv_bfloat16*>(p.c_bf16); a.ld_c16 = p.ldc_bf16;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
     a.c = p.c; a.ldc = p.ldc; a.stride_c = p.stride_c; a.gelu_out = p.gelu_out; a.bias = p.bias;

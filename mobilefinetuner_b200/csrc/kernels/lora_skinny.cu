@@ -483,7 +483,19 @@ extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t 
     if (splits > 65535) return set_error(1, "mft_lora_tn: too many tokens");
     cudaStream_t st = as_stream(stream);
     float* partial = static_cast<float*>(workspace);
-    const bool vec = r <= 16 && (q & 1) == 0 && (ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(w) & 7) == 0;
+    const bool vec_layout = (q & 1) == 0 && (ldw & 1) == 0 && (reinterpret_cast<uintptr_t>(w) & 7) == 0;
+    if (r > 16 && vec_layout) {
+        // ranks above 16: slices of 16 columns of S through the 16-wide kernel (W is re-read per slice from L2 / HBM, which is
+        // still several times faster than the one-accumulator-per-rank FMA form: 64 accumulators per thread, one column each)
+        for (int32_t r0 = 0; r0 < r; r0 += 16) {
+            const int32_t rs = r - r0 < 16 ? r - r0 : 16;
+            float* o = out_is_rq ? out + int64_t(r0) * ldo : out + r0;
+            int rc = mft_lora_tn(s + r0, lds, w, ldw, o, ldo, out_is_rq, T, q, rs, alpha, workspace, workspace_bytes, stream);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    const bool vec = r <= 16 && vec_layout;
     const int64_t colblocks = ceil_div(q, vec ? kTnCT * 2 : kTnCT);
     // the last-arriving CTA sums the splits itself when there are few of them; a long split list is summed faster by a
     // separate, fully parallel launch

@@ -518,6 +518,13 @@ def test_gemm_bf16_gelu_activation_as_bf16_only(capi):
     capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
     torch.cuda.synchronize()
     assert torch.equal(pre, pre2) and torch.equal(act16, act.to(torch.bfloat16))
+    # pre-activation AND activation as bf16 only (what fc_in writes when GeluBackward is the pre-activation's only reader)
+    pre16, act16b = torch.zeros(m, n, device="cuda", dtype=torch.bfloat16), torch.zeros(m, n, device="cuda", dtype=torch.bfloat16)
+    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, None, n, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0,
+                         None, 0, None, 0, act16b.data_ptr(), n, pre16.data_ptr(), n)
+    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
+    torch.cuda.synchronize()
+    assert torch.equal(pre16, pre.to(torch.bfloat16)) and torch.equal(act16b, act16)
 
 
 def test_lowp_elementwise_kernels(capi):
