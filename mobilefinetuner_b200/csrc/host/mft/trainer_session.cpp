@@ -76,6 +76,7 @@ struct mft_trainer {
     bool capturing = false;
     void* shadow_dev = nullptr;    // device table of mft_shadow_slot (bf16 shadows of the trained adapter factors)
     mft_shadow_slot* shadow_host = nullptr;
+    std::vector<char> had_grad;    // per trainable tensor: received a gradient in the last eagerly run update
     std::vector<int> shadowed;     // indices into `trainable` whose shadows the refresh kernel rewrote last step
     TensorPtr own_bucket;          // gradient bucket allocated by mft_trainer_step_dp when the caller supplied none
     std::vector<TensorPtr> accum;  // true-gradient mode: persistent gradient sums over micro-batches (mft_trainer_accumulate)
@@ -224,9 +225,12 @@ const mft_tensor_slot* upload_slots(mft_trainer* t, bool packed) {
         mft_tensor_slot& s = t->slots_host[packed][i];
         std::memset(&s, 0, sizeof(s));
         s.n = t->trainable[i]->numel();
-        s.param = t->trainable[i]->dev_f32_mut();          // bumps the version: cached K-major / bf16 shadows get rebuilt
-        s.m = t->m[i]->dev_f32_mut();
-        s.v = t->v[i]->dev_f32_mut();
+        // Adam only writes tensors that have a gradient: only those get their version bumped (cached K-major / bf16 shadows of
+        // the others — e.g. GPT-2's attn.qkv adapters, which the reference never trains — stay valid)
+        const bool written = t->grads[i] != nullptr;
+        s.param = written ? t->trainable[i]->dev_f32_mut() : const_cast<float*>(t->trainable[i]->dev_f32());
+        s.m = written ? t->m[i]->dev_f32_mut() : const_cast<float*>(t->m[i]->dev_f32());
+        s.v = written ? t->v[i]->dev_f32_mut() : const_cast<float*>(t->v[i]->dev_f32());
         s.bucket_offset = t->offsets[i];
         if (t->grads[i]) s.grad = packed ? t->bucket + t->offsets[i] : t->grads[i]->dev_f32_mut();
     }
@@ -279,6 +283,8 @@ void update_phase(mft_trainer* t, bool packed) {
     mft_rt::check(mft_adam_step_dev(slots, n, t->lr_dev, t->cfg.beta1, t->cfg.beta2, t->cfg.eps, t->cfg.weight_decay,
                                     t->scale_dev, t->steps_dev, mft_rt::stream()), "mft_adam_step_dev");
     refresh_shadows(t);
+    t->had_grad.assign(t->trainable.size(), 0);
+    for (size_t i = 0; i < t->trainable.size(); ++i) t->had_grad[i] = t->grads[i] ? 1 : 0;
     for (auto& p : t->trainable) p->set_grad(nullptr);   // gradients live in the step arena; never reused
 }
 
@@ -286,6 +292,7 @@ void update_phase(mft_trainer* t, bool packed) {
 // body that normally records it: note the write here, so host mirrors are re-read and cached shadows are versioned.
 void mark_state_written(mft_trainer* t) {
     for (size_t i = 0; i < t->trainable.size(); ++i) {
+        if (i < t->had_grad.size() && !t->had_grad[i]) continue;     // untouched by the update
         (void)t->trainable[i]->dev_f32_mut();
         (void)t->m[i]->dev_f32_mut();
         (void)t->v[i]->dev_f32_mut();

@@ -735,6 +735,9 @@ static int dispatch_tc(const GemmParams& p, cudaStream_t st) {
     // Paired CTAs (cta_group::2) whenever there are at least two row tiles to pair and the output is wide enough.
     if (two_cta && tiles_m >= 2 && p.n > 64) {
         const int64_t pairs = ceil_div(tiles_m, 2) * p.batch;
+#ifdef MFT_TC_FORCE_BN          /* variant builds only (tools/build_variants.sh): one tile width for every paired launch */
+        return launch_tc<MFT_TC_FORCE_BN, 2, BF16>(p, st);
+#endif
         if (p.n <= 128 || pairs * ceil_div(p.n, 256) < kNumSMs / 4) return launch_tc<128, 2, BF16>(p, st);
         return launch_tc<256, 2, BF16>(p, st);
     }

@@ -157,7 +157,9 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
                 o.y = k * (D * (g[j].y * gam[j].y) - s1 - v[j].y * s2);
                 o.z = k * (D * (g[j].z * gam[j].z) - s1 - v[j].z * s2);
                 o.w = k * (D * (g[j].w * gam[j].w) - s1 - v[j].w * s2);
-                if (!WG) { o.x += ad[j].x; o.y += ad[j].y; o.z += ad[j].z; o.w += ad[j].w; }
+                if (!WG) {       // explicit adds (no contraction into an FMA with the product above): bit-identical to a separate add kernel
+                    o.x = __fadd_rn(o.x, ad[j].x); o.y = __fadd_rn(o.y, ad[j].y); o.z = __fadd_rn(o.z, ad[j].z); o.w = __fadd_rn(o.w, ad[j].w);
+                }
                 else if (addend) {
                     const float4 a = ld_stream(reinterpret_cast<const float4*>(addend + r * dim) + c);
                     o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
