@@ -331,7 +331,8 @@ def main():
         tpath = os.path.join(ROOT, "profiles", name)
         if a.config == "c4" and os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch_" + a.precision)
+                tj = json.load(open(tpath))                  # captures exist for 8 and 64 sequences per GPU
+                traffic = tj.get(f"dram_bytes_per_launch_{a.precision}_b{batch}", tj.get("dram_bytes_per_launch_" + a.precision) if batch == 8 else None)
             except Exception:
                 traffic = None
             break

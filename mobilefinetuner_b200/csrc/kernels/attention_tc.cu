@@ -50,6 +50,12 @@ __device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr) 
     return d;
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {          // one MUFU.EX2; 2^(-inf) = 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 __global__ void __launch_bounds__(kTaThreads)
 attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, int C) {
     extern __shared__ uint8_t smem_raw[];
@@ -173,24 +179,26 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sfree);   // the next S may overwrite TMEM columns [0,64)
-            // scores in the log2 domain; causal mask and sequence tail by index (masked entries contribute exp2(-inf) = 0)
+            // causal mask and sequence tail by index, only on tiles that touch the diagonal or the end of the sequence
             const bool need_mask = key0 + kTaBK - 1 > q0 || key0 + kTaBK > S;
+            if (need_mask) {
+#pragma unroll
+                for (int j = 0; j < kTaBK; ++j)
+                    if (key0 + j > qi || key0 + j >= S) s[j] = -INFINITY;
+            }
+            // the scale is positive, so the row max can be taken on the raw scores; the log2-domain shift then folds into one
+            // FMA per element: p = 2^(s * c - m)
             float mx = -INFINITY;
 #pragma unroll
-            for (int j = 0; j < kTaBK; ++j) {
-                float x = s[j] * p.scale_log2;
-                if (need_mask && (key0 + j > qi || key0 + j >= S)) x = -INFINITY;
-                s[j] = x;
-                mx = fmaxf(mx, x);
-            }
-            const float m_new = fmaxf(m_run, mx);
+            for (int j = 0; j < kTaBK; ++j) mx = fmaxf(mx, s[j]);
+            const float m_new = fmaxf(m_run, mx * p.scale_log2);
             const float m_ref = m_new == -INFINITY ? 0.f : m_new;     // rows past the sequence end see only masked keys
-            const float alpha = exp2f(m_run - m_ref);
+            const float alpha = ex2_approx(m_run - m_ref);
             float sum = 0.f;
             uint32_t pk[kTaBK / 2];
 #pragma unroll
             for (int j = 0; j < kTaBK; j += 2) {
-                const float p0 = exp2f(s[j] - m_ref), p1 = exp2f(s[j + 1] - m_ref);
+                const float p0 = ex2_approx(fmaf(s[j], p.scale_log2, -m_ref)), p1 = ex2_approx(fmaf(s[j + 1], p.scale_log2, -m_ref));
                 sum += p0 + p1;
                 const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
                 pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h2);

@@ -6,20 +6,16 @@ cd "$(dirname "$0")/../mobilefinetuner_b200/csrc"
 make -j8 ../libmft_b200.so > /dev/null
 mkdir -p ../variants build/variants
 OTHERS=$(ls build/*.o | grep -v gemm_tc.o)
-for v in "8 2" "8 1" "4 2" "4 1"; do
+for v in "8 2" "8 1" "4 2"; do
   set -- $v
   name=w$1b$2
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -I../../include -Ikernels \
       --expt-relaxed-constexpr -DMFT_TC_EPI_WARPS=$1 -DMFT_TC_EPI_BOXES=$2 -c kernels/gemm_tc.cu -o build/variants/gemm_tc_$name.o &
 done
 wait
-for v in "8 2" "8 1" "4 2" "4 1"; do
+for v in "8 2" "8 1" "4 2"; do
   set -- $v
   name=w$1b$2
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libmft_b200_$name.so $OTHERS build/variants/gemm_tc_$name.o -lcudart
 done
-# tile-width variant: every paired launch uses 256 x 128 tiles (wave quantisation / epilogue overlap experiments)
-/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -I../../include -Ikernels \
-    --expt-relaxed-constexpr -DMFT_TC_FORCE_BN=128 -c kernels/gemm_tc.cu -o build/variants/gemm_tc_bn128.o
-/usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libmft_b200_bn128.so $OTHERS build/variants/gemm_tc_bn128.o -lcudart
 ls -la ../variants
