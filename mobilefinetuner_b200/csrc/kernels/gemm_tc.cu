@@ -35,7 +35,9 @@ static_assert(kEpiWarpsDefault == 4 || kEpiWarpsDefault == 8, "epilogue warps");
 constexpr int kEpiPitch = 36;     // floats per staged row (fallback path): 16-byte aligned and conflict-free for both access patterns
 constexpr int kEpiBufBytes = 32 * 128;                  // one 32 x 32 fp32 box in the TMA (128B-swizzled) layout
 constexpr int kEpiStageBytes = (kEpiBoxes * kEpiBufBytes > 32 * kEpiPitch * 4) ? kEpiBoxes * kEpiBufBytes : 5120;   // fallback path needs 4608; keep 1024-byte alignment
-constexpr int kEpiWarpBytes = kEpiStageBytes + 1024;    // boxes + this warp's slice of the bias (<= 256 floats)
+// staging per epilogue warp: the eight-warp form (GELU aux output) keeps two boxes, pre-activation and activation
+constexpr int epi_stage_bytes(int ew) { return ew == 8 ? 2 * kEpiBufBytes : kEpiStageBytes; }
+constexpr int epi_warp_bytes(int ew) { return epi_stage_bytes(ew) + 1024; }    // boxes + this warp's slice of the bias (<= 256 floats)
 constexpr int kSmemTotal = 227 * 1024;
 
 // CG = CTAs cooperating on one UMMA (cta_group). CG = 2: a cluster of two CTAs computes a 256 x BN tile pair — each CTA
@@ -45,7 +47,7 @@ constexpr int kSmemTotal = 227 * 1024;
 template <int BN, int CG = 1, int EW = kEpiWarpsDefault> struct TcCfg {
     static constexpr int b_rows = BN / CG;                 // B rows staged by one CTA
     static constexpr int stage_bytes = (TBM + b_rows) * TBK * 4;
-    static constexpr int epi_bytes = EW * kEpiWarpBytes;   // per-warp staging for the output boxes
+    static constexpr int epi_bytes = EW * epi_warp_bytes(EW);   // per-warp staging for the output boxes
     static constexpr int budget = kSmemTotal - epi_bytes - 1024 /*align slack*/ - 256 /*barriers*/;
     static constexpr int stages = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
     static constexpr int tmem_cols = 2 * BN;             // two accumulator buffers
@@ -72,7 +74,8 @@ struct TcArgs {
     const float* gelu_grad_x; int64_t ld_gelu_grad_x;
     __nv_bfloat16* gelu16; int64_t ld_gelu16;   // bf16 copy of the GELU aux output (gelu_out may be NULL: bf16 only)
     __nv_bfloat16* c16; int64_t ld_c16;         // bf16 copy of C (c may be NULL on the TMA path: bf16 only)
-    int tma_c16;               // 1: c is NULL and the bf16 result leaves through 64-column TMA boxes (map_g)
+    int tma_c16;               // 1: c is NULL and the bf16 result leaves through 64-column TMA boxes (map_c)
+    int tma_g16;               // 1: with tma_c16, the GELU aux output (bf16 only) leaves through boxes too (map_g; EW = 8 form)
     float alpha, beta;
     int tiles_m, tiles_n;
     int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
@@ -226,9 +229,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         const int half = (warp - 2) >> 2;                 // which part of the tile's columns this warp drains
         constexpr int HC = BN / (kEpiWarps / 4);          // columns per epilogue warp
         // all boxes first (each 1024-byte aligned: the 128B swizzle is a function of the absolute smem address), bias slices after
-        uint8_t* wbuf = epi_stage + (warp - 2) * kEpiStageBytes;
+        uint8_t* wbuf = epi_stage + (warp - 2) * epi_stage_bytes(EW);
         float* stg = reinterpret_cast<float*>(wbuf);      // fallback path: 32 x kEpiPitch floats (fits in the two boxes)
-        float* sbias = reinterpret_cast<float*>(epi_stage + kEpiWarps * kEpiStageBytes + (warp - 2) * 1024);   // [HC] (HC <= 256)
+        float* sbias = reinterpret_cast<float*>(epi_stage + kEpiWarps * epi_stage_bytes(EW) + (warp - 2) * 1024);   // [HC] (HC <= 256)
         const int r4 = lane >> 3, c4 = lane & 7;          // read-back role: row within a group of 4, float4 column
         const bool vec_ok = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15u) == 0) &&
                             ((p.stride_c & 3) == 0) &&
@@ -309,11 +312,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
                                            *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
                         }
+                        if (EW == 8 && p.tma_g16) {                      // GELU of the same values into the second box
+                            uint8_t* rowg = box + kEpiBufBytes + lane * 128;
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const __nv_bfloat162 h0 = __floats2bfloat162_rn(gelu_tanh_epi(v[8 * q]), gelu_tanh_epi(v[8 * q + 1]));
+                                const __nv_bfloat162 h1 = __floats2bfloat162_rn(gelu_tanh_epi(v[8 * q + 2]), gelu_tanh_epi(v[8 * q + 3]));
+                                const __nv_bfloat162 h2 = __floats2bfloat162_rn(gelu_tanh_epi(v[8 * q + 4]), gelu_tanh_epi(v[8 * q + 5]));
+                                const __nv_bfloat162 h3 = __floats2bfloat162_rn(gelu_tanh_epi(v[8 * q + 6]), gelu_tanh_epi(v[8 * q + 7]));
+                                *reinterpret_cast<uint4*>(rowg + ((((j & 1) * 4 + q) ^ (lane & 7)) << 4)) =
+                                    make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
+                                               *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
+                            }
+                        }
                         const bool last_chunk = (j == HC / 32 - 1) || (n0 + cc + 32 >= p.n);
                         if ((j & 1) || last_chunk) {
                             fence_proxy_async_smem();
                             __syncwarp();
-                            if (lane == 0) { tma_store_3d(&map_g, box, n0 + (cc & ~63), row_base, bz); tma_store_commit(); }
+                            if (lane == 0) {
+                                tma_store_3d(&map_c, box, n0 + (cc & ~63), row_base, bz);
+                                if (EW == 8 && p.tma_g16) tma_store_3d(&map_g, box + kEpiBufBytes, n0 + (cc & ~63), row_base, bz);
+                                tma_store_commit();
+                            }
                         }
                     } else {
                         uint8_t* box = wbuf + (nstore % kEpiBoxes) * kEpiBufBytes;
@@ -665,15 +685,20 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
         tma_c = make_store_map(&mc, p.c, p.n, p.m, p.batch, p.ldc, p.stride_c) &&
                 (!p.gelu_out || make_store_map(&mg, p.gelu_out, p.n, p.m, p.batch, p.ldc, p.stride_c));
     }
-    const bool box16 = bf16_only && !gelu_aux;      // with a GELU aux output the register path writes both bf16 arrays
+    // bf16-only result through boxes: plain, or (eight-warp form) together with a bf16-only GELU aux output
+    const bool box_gelu = bf16_only && EW == 8 && !p.gelu_out && p.gelu_out_bf16 && aligned16(p.gelu_out_bf16) && (p.ld_gelu_out_bf16 & 7) == 0;
+    const bool box16 = bf16_only && (!gelu_aux || box_gelu);      // otherwise the register path writes the bf16 arrays
     if (box16) {
-        if (!make_store_map(&mg, p.c_bf16, p.n, p.m, 1, p.ldc_bf16, 0, true)) return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (bf16 result)");
-        mc = mg;
+        if (!make_store_map(&mc, p.c_bf16, p.n, p.m, 1, p.ldc_bf16, 0, true)) return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (bf16 result)");
+        mg = mc;
+        if (box_gelu && !make_store_map(&mg, p.gelu_out_bf16, p.n, p.m, 1, p.ld_gelu_out_bf16, 0, true))
+            return set_error(3, "mft_gemm(tc): cuTensorMapEncodeTiled failed (bf16 GELU result)");
         tma_c = true;
     } else if (!tma_c) { mc = ma; mg = ma; } else if (!p.gelu_out) mg = mc;
     TcArgs a;
     a.tma_c = tma_c ? 1 : 0;
     a.tma_c16 = box16 ? 1 : 0;
+    a.tma_g16 = (box16 && box_gelu) ? 1 : 0;
     a.c16 = box16 ? nullptr : static_cast<__nv_bfloat16*>(p.c_bf16); a.ld_c16 = p.ldc_bf16;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
