@@ -69,9 +69,6 @@ typedef struct mft_gemm_args {
     void* c_bf16; int64_t ldc_bf16;                    /* bf16 copy of C (after alpha / bias / beta), or NULL. On the tensor-core path
                                                           c may then be NULL: the bf16 copy is the only result (its consumers are
                                                           bf16 GEMM / attention operands), which halves the epilogue's HBM writes */
-    const void* gelu_grad_x_bf16; int64_t ld_gelu_grad_x_bf16;   /* tensor-core path with a bf16-only result (c = NULL): result *=
-                                                          d gelu_tanh / dx at this bf16 [m,n] tensor — GeluBackward folded into
-                                                          the dX product of the layer that consumed the activation; n % 32 == 0 */
 } mft_gemm_args;
 int mft_gemm(const mft_gemm_args* args, mft_stream_t stream);
 /* bf16-operand form of mft_gemm: a, b, a2, b2 point to bf16 arrays (leading dimensions in elements, multiples of 8),

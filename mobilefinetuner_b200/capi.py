@@ -35,8 +35,7 @@ class GemmArgs(C.Structure):
                 ("k2", i32), ("a2", vp), ("lda2", i64), ("b2", vp), ("ldb2", i64),
                 ("batch", i32), ("stride_a", i64), ("stride_b", i64), ("stride_c", i64),
                 ("addend", vp), ("ld_addend", i64), ("gelu_grad_x", vp), ("ld_gelu_grad_x", i64),
-                ("gelu_out_bf16", vp), ("ld_gelu_out_bf16", i64), ("c_bf16", vp), ("ldc_bf16", i64),
-                ("gelu_grad_x_bf16", vp), ("ld_gelu_grad_x_bf16", i64)]
+                ("gelu_out_bf16", vp), ("ld_gelu_out_bf16", i64), ("c_bf16", vp), ("ldc_bf16", i64)]
 
 
 class TensorSlot(C.Structure):

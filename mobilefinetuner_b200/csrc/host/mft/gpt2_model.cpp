@@ -250,15 +250,7 @@ TensorPtr GPT2Model::forward_block(const TensorPtr& x_in, int i, const TensorPtr
     }
     // x2 + fc_out(gelu(pre)): residual in the forward epilogue, GeluBackward in the epilogue of the backward dX product
     if (!fuse) {
-        // bf16-only activations: fc_out takes `pre` as its autograd input, so its dX product applies GeluBackward in its own
-        // epilogue and hands d pre (bf16) straight to fc_in's backward — the activation's gradient never exists in HBM
-        static const bool fold = [] { const char* e = std::getenv("MFT_FOLD_GELU_BWD"); return !(e && e[0] == '0'); }();
-        TensorPtr m;
-        if (fold && pre && pre->f32_pending() && h && h->f32_pending()) {
-            LinearFusion mo;
-            mo.gelu_input_pre = pre;
-            m = run_linear_fused(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias, mo);
-        } else m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);
+        auto m = run_linear(h, w.fc_out_lin, w.lora_initialized, w.mlp_fc_out_weight, w.mlp_fc_out_bias);
         if (carry_out) { *carry_out = m; return x2; }      // the next LayerNorm adds it
         return add(x2, m);
     }

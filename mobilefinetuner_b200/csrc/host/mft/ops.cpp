@@ -157,13 +157,6 @@ void run_gemm(GemmCall g) {
         if (g.c_tensor && !g.c && diet && g.c_bf16_only && plain_epilogue && g.c_tensor->is_dense() && g.n % 8 == 0 && emit_bf16_operands()) {
             auto e = g.c_tensor->bf16_only_out();                 // bf16 is the only copy of the result
             a.c = nullptr; a.c_bf16 = e.ptr; a.ldc_bf16 = e.ld;
-            if (g.gelu_grad16_tensor && !gelu_here && g.n % 32 == 0 && g.gelu_grad16_tensor->has_bf16()) {
-                auto v = g.gelu_grad16_tensor->bf16_view();
-                if (v.ld % 8 == 0) {
-                    a.gelu_grad_x_bf16 = v.ptr; a.ld_gelu_grad_x_bf16 = v.ld;
-                    if (g.gelu_grad16_done) *g.gelu_grad16_done = true;
-                }
-            }
         } else {
             a.c = g.c ? g.c : g.c_tensor->dev_f32_out();
         }

@@ -43,10 +43,6 @@ struct GemmCall {
     // (or materialising) its fp32 data.
     TensorPtr c_tensor;
     bool c_bf16_only = false, gelu_bf16_only = false;
-    // bf16 tensor-core form with a bf16-only result: result *= gelu'(this tensor's bf16 copy) in the epilogue (GeluBackward of
-    // the activation this product's gradient flows to). run_gemm reports through gelu_grad16_done whether it took that form.
-    TensorPtr gelu_grad16_tensor;
-    bool* gelu_grad16_done = nullptr;
 };
 void run_gemm(GemmCall g);
 

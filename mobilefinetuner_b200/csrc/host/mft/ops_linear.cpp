@@ -427,18 +427,8 @@ public:
                 }
             }
             const bool fuse_gelu_bwd = pre_ && terms_.size() <= 1;   // further slices accumulate after the epilogue ran
-            // bf16 operand mode with the pre-activation kept as bf16: GeluBackward rides in the box epilogue of this product and
-            // d pre leaves as bf16 only (it feeds fc_in's dX product). Otherwise the fp32 operand form of the epilogue.
-            bool lowp_done = false;
-            const bool try_lowp = fuse_gelu_bwd && bf16_only_results() && pre_->has_bf16() && pre_->is_dense() && in % 32 == 0 && gemm_takes_bf16(T, in, out);
-            if (try_lowp) { g.gelu_grad16_tensor = pre_; g.gelu_grad16_done = &lowp_done; g.c_bf16_only = true; }
-            else if (fuse_gelu_bwd) { g.gelu_grad_x = pre_->dev_f32(); g.ld_gelu_grad_x = pre_->ld(); }
+            if (fuse_gelu_bwd) { g.gelu_grad_x = pre_->dev_f32(); g.ld_gelu_grad_x = pre_->ld(); }
             run_gemm(g);
-            if (try_lowp && !lowp_done) {             // the product took another form: apply GeluBackward separately
-                TensorPtr pc = contiguous(pre_);
-                float* gxp = gx->dev_f32_mut();
-                mft_rt::check(mft_gelu_bwd(pc->dev_f32(), gxp, gxp, T * in, mft_rt::stream()), "mft_gelu_bwd");
-            }
             for (size_t i = 1; i < terms_.size(); ++i) {     // further slices: accumulate
                 TermLayout l = classify(terms_[i], in, out);
                 GemmCall h;

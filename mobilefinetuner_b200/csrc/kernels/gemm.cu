@@ -40,7 +40,6 @@ static int to_params(const mft_gemm_args* a, GemmParams& p) {
     p.gelu_grad_x = a->gelu_grad_x; p.ld_gelu_grad_x = a->ld_gelu_grad_x;
     p.gelu_out_bf16 = a->gelu_out_bf16; p.ld_gelu_out_bf16 = a->ld_gelu_out_bf16;
     p.c_bf16 = a->c_bf16; p.ldc_bf16 = a->ldc_bf16;
-    p.gelu_grad_x_bf16 = a->gelu_grad_x_bf16; p.ld_gelu_grad_x_bf16 = a->ld_gelu_grad_x_bf16;
     if (p.gelu_out_bf16 && (p.batch > 1 || (p.ld_gelu_out_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.gelu_out_bf16) & 7u)))
         return set_error(1, "mft_gemm: gelu_out_bf16 needs batch 1, an 8-byte aligned base and a pitch that is a multiple of 4");
     if (p.c_bf16 && (p.batch > 1 || p.ldc_bf16 < p.n || (p.ldc_bf16 & 3) || (reinterpret_cast<uintptr_t>(p.c_bf16) & 7u)))
@@ -121,7 +120,6 @@ extern "C" int mft_gemm(const mft_gemm_args* args, mft_stream_t stream) {
     if (rc) return rc;
     if (p.m == 0 || p.n == 0) return 0;
     if (g_use_tc && gemm_tc_eligible(p)) return launch_gemm_tc(p, as_stream(stream));
-    if (p.gelu_grad_x_bf16) return set_error(1, "mft_gemm: gelu_grad_x_bf16 is a tensor-core (bf16-only result) feature");
     if (!p.c || (p.gelu_out_bf16 && !p.gelu_out)) return set_error(1, "mft_gemm: the SIMT path needs the fp32 result buffers (bf16-only results are a tensor-core feature)");
     rc = launch_gemm_simt(p, as_stream(stream));
     if (rc == 0 && p.gelu_out_bf16) rc = mft_cast_bf16(p.gelu_out, p.ldc, p.gelu_out_bf16, p.ld_gelu_out_bf16, p.m, p.n, stream);   // SIMT path: separate cast

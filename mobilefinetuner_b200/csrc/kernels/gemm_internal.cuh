@@ -17,7 +17,6 @@ struct GemmParams {
     const float* addend = nullptr; int64_t ld_addend = 0;
     const float* gelu_grad_x = nullptr; int64_t ld_gelu_grad_x = 0;
     void* gelu_out_bf16 = nullptr; int64_t ld_gelu_out_bf16 = 0;
-    const void* gelu_grad_x_bf16 = nullptr; int64_t ld_gelu_grad_x_bf16 = 0;   // bf16-only result *= gelu'(this bf16 tensor)
     void* c_bf16 = nullptr; int64_t ldc_bf16 = 0;   // bf16 copy of C; with c == nullptr the bf16 copy is the only result (tensor-core path)
     bool bf16 = false;         // operands are bf16 arrays
     int ksplit = 1;            // SIMT split-K: number of K slices (partials reduced in a fixed order)

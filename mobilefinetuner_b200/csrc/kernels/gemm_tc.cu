@@ -64,15 +64,6 @@ __device__ __forceinline__ float gelu_tanh_epi(float x) {
     return __fdividef(x, 1.0f + __expf(-u2));
 }
 
-// d gelu_tanh / dx through the same sigmoid: with s = sigmoid(2u): 0.5 (1 + tanh u) = s and 1 - tanh^2 u = 4 s (1 - s), so
-// gelu'(x) = s + 2 x s (1 - s) * 0.7978845608 (1 + 3 * 0.044715 x^2)          (core/backward_functions.cpp:155-177)
-__device__ __forceinline__ float gelu_tanh_grad_epi(float x) {
-    const float x2 = x * x;
-    const float u2 = 1.5957691216f * (x + 0.044715f * x * x2);
-    const float sg = __fdividef(1.0f, 1.0f + __expf(-u2));
-    return sg + 2.0f * x * sg * (1.0f - sg) * (0.7978845608f * (1.0f + 0.134145f * x2));
-}
-
 struct TcArgs {
     int m, n, batch;
     int kb1, kb2;              // k-blocks of segment 1 / segment 2
@@ -84,7 +75,6 @@ struct TcArgs {
     __nv_bfloat16* gelu16; int64_t ld_gelu16;   // bf16 copy of the GELU aux output (gelu_out may be NULL: bf16 only)
     __nv_bfloat16* c16; int64_t ld_c16;         // bf16 copy of C (c may be NULL on the TMA path: bf16 only)
     int tma_c16;               // 1: c is NULL and the bf16 result leaves through 64-column TMA boxes (map_c)
-    const __nv_bfloat16* ggrad16; int64_t ld_ggrad16;   // box16 form: result *= gelu'(this bf16 pre-activation) (GeluBackward in the epilogue)
     int tma_g16;               // 1: with tma_c16, the GELU aux output (bf16 only) leaves through boxes too (map_g; EW = 8 form)
     float alpha, beta;
     int tiles_m, tiles_n;
@@ -304,26 +294,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     } else if (p.alpha != 1.0f) {
 #pragma unroll
                         for (int q = 0; q < 32; ++q) v[q] *= p.alpha;
-                    }
-                    if (p.tma_c16 && p.ggrad16) {
-                        // GeluBackward folded in: this row's 32 pre-activations of the chunk (64 contiguous bytes of bf16)
-                        const int grow = row_base + lane;
-                        if (grow < p.m) {
-                            const uint4* src = reinterpret_cast<const uint4*>(p.ggrad16 + int64_t(grow) * p.ld_ggrad16 + n0 + cc);
-                            uint4 xr[4];
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) xr[q] = __ldcs(src + q);
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                const __nv_bfloat162* xp = reinterpret_cast<const __nv_bfloat162*>(&xr[q]);
-#pragma unroll
-                                for (int e = 0; e < 4; ++e) {
-                                    const float2 f = __bfloat1622float2(xp[e]);
-                                    v[8 * q + 2 * e] *= gelu_tanh_grad_epi(f.x);
-                                    v[8 * q + 2 * e + 1] *= gelu_tanh_grad_epi(f.y);
-                                }
-                            }
-                        }
                     }
                     if (p.tma_c16) {
                         // bf16-only result: two 32-column chunks share one 64-column box (128 bytes of bf16 per row, same
@@ -729,12 +699,6 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     a.tma_c = tma_c ? 1 : 0;
     a.tma_c16 = box16 ? 1 : 0;
     a.tma_g16 = (box16 && box_gelu) ? 1 : 0;
-    a.ggrad16 = nullptr; a.ld_ggrad16 = 0;
-    if (p.gelu_grad_x_bf16) {
-        if (!box16 || gelu_aux || (p.n & 31) || (p.ld_gelu_grad_x_bf16 & 7) || !aligned16(p.gelu_grad_x_bf16))
-            return set_error(1, "mft_gemm(tc): gelu_grad_x_bf16 needs a bf16-only result (c = NULL, c_bf16 set), n %% 32 == 0, a 16-byte aligned pointer and a pitch %% 8 == 0");
-        a.ggrad16 = static_cast<const __nv_bfloat16*>(p.gelu_grad_x_bf16); a.ld_ggrad16 = p.ld_gelu_grad_x_bf16;
-    }
     a.c16 = box16 ? nullptr : static_cast<__nv_bfloat16*>(p.c_bf16); a.ld_c16 = p.ldc_bf16;
     a.m = p.m; a.n = p.n; a.batch = p.batch;
     a.kb1 = int(ceil_div(p.k, KE)); a.kb2 = p.k2 > 0 ? int(ceil_div(p.k2, KE)) : 0;
@@ -791,7 +755,7 @@ static int launch_tc(const GemmParams& p, cudaStream_t st) {
     // The GELU aux output leaves through registers and st.global (tanh chains, two bf16 arrays): with one epilogue warp per
     // scheduler that epilogue, not the main loop, sets the tile time (fc_in: 82.7 us against 34 us for the plain product);
     // eight epilogue warps, two per TMEM lane group, halve it (57.8 us). The box (TMA) epilogues stay at four.
-    if ((p.gelu_out || p.gelu_out_bf16 || p.gelu_grad_x_bf16) && BN >= 64) return launch_tc_impl<BN, CG, BF16, false, 8>(p, st);
+    if ((p.gelu_out || p.gelu_out_bf16) && BN >= 64) return launch_tc_impl<BN, CG, BF16, false, 8>(p, st);
     return launch_tc_impl<BN, CG, BF16, false, kEpiWarpsDefault>(p, st);
 }
 

@@ -26,7 +26,7 @@ def test_struct_layouts_match_header():
     import ctypes as C
     import mobilefinetuner_b200.capi as capi
     assert C.sizeof(capi.TensorSlot) == 56
-    assert C.sizeof(capi.GemmArgs) == 256      # 224 + c_bf16, ldc_bf16 + gelu_grad_x_bf16, ld_gelu_grad_x_bf16
+    assert C.sizeof(capi.GemmArgs) == 240      # 224 + c_bf16, ldc_bf16
 
 
 def test_no_cpu_fallback_on_missing_device():

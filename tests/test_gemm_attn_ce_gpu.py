@@ -564,22 +564,3 @@ def test_lowp_elementwise_kernels(capi):
     capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, g32, V, g16a, V, None)
     capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, None, 0, g16b, V, None)
     assert torch.equal(g16a, g16b) and torch.equal(g16a, g32.to(torch.bfloat16))
-
-
-def test_gemm_bf16_result_times_gelu_grad_of_bf16_preactivation(capi):
-    """GeluBackward folded into the box epilogue: c_bf16 = bf16((a b^T) * gelu'(pre)) with pre given as bf16."""
-    rng = np.random.default_rng(4)
-    m, n, k = 640, 1024, 256
-    a = torch.tensor(rng.standard_normal((m, k)).astype(np.float32)).cuda().to(torch.bfloat16)
-    b = torch.tensor((rng.standard_normal((n, k)) * 0.1).astype(np.float32)).cuda().to(torch.bfloat16)
-    pre = torch.tensor(rng.standard_normal((m, n)).astype(np.float32) * 2).cuda().to(torch.bfloat16)
-    plain = torch.zeros(m, n, device="cuda")
-    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, plain.data_ptr(), n, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0)
-    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
-    out16 = torch.zeros(m, n, device="cuda", dtype=torch.bfloat16)
-    args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, None, n, 1.0, 0.0, None, None, 0, None, 0, None, 0, 1, 0, 0, 0,
-                         None, 0, None, 0, None, 0, out16.data_ptr(), n, pre.data_ptr(), n)
-    capi.check(capi.lib.mft_gemm_bf16(C.byref(args), None), "mft_gemm_bf16")
-    torch.cuda.synchronize()
-    e = plain.cpu().numpy() * O.gelu_bwd(pre.float().cpu().numpy(), np.ones((m, n), np.float32))
-    assert rel(out16.float(), e) < 6e-3          # bf16 rounding of the result (2^-8 relative to the largest entry)
