@@ -86,7 +86,10 @@ struct TcArgs {
 //               k-block, twice the FLOPs per byte staged.
 // FUSED = true adds the residual / GELU-gradient operands to the epilogue; a separate instantiation so that the plain
 // epilogue's instruction schedule (which bounds the kernel on short-K shapes) is not disturbed by code it never runs.
-template <int BN, int CG, bool BF16, bool FUSED, int EW>
+// FORM specialises the epilogue at compile time (the box epilogues are latency-critical: a runtime flag tested inside their
+// unrolled chunk loop costs several percent of the kernel): 0 = every output form decided at run time; 1 = fp32 result through
+// TMA boxes, nothing else; 2 = bf16-only result through boxes; 3 = bf16-only result and bf16-only GELU aux through boxes (EW = 8).
+template <int BN, int CG, bool BF16, bool FUSED, int EW, int FORM>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
@@ -240,7 +243,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             (!p.gelu_grad_x || (((reinterpret_cast<uintptr_t>(p.gelu_grad_x) & 15u) | (p.ld_gelu_grad_x & 3)) == 0)) &&
                             (!p.bias || (reinterpret_cast<uintptr_t>(p.bias) & 15u) == 0) &&
                             (!p.c16 || (((reinterpret_cast<uintptr_t>(p.c16) & 7u) | (p.ld_c16 & 3)) == 0));
-        const bool use_tma = !FUSED && p.tma_c != 0;
+        const bool use_tma = FORM != 0 ? true : (!FUSED && p.tma_c != 0);
+        const bool f_c16box = FORM != 0 ? (FORM >= 2) : (p.tma_c16 != 0);
+        const bool f_g16box = FORM != 0 ? (FORM == 3) : (EW == 8 && p.tma_g16 != 0);
+        const bool f_c16reg = FORM != 0 ? false : (p.c16 != nullptr);
         uint32_t nstore = 0;                              // boxes this warp has handed to the TMA (ring of two buffers)
         int it = 0;
         for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
@@ -254,7 +260,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const int row_base = mt * TBM + lg * 32;
             const int n0 = nt * BN;
             float* cbase = p.c + int64_t(bz) * p.stride_c;
-            float* gbase = p.gelu_out ? p.gelu_out + int64_t(bz) * p.stride_c : nullptr;
+            float* gbase = (FORM == 0 && p.gelu_out) ? p.gelu_out + int64_t(bz) * p.stride_c : nullptr;
             const float* abase = (FUSED && p.addend) ? p.addend + int64_t(bz) * p.stride_c : nullptr;
             const float* xbase = (FUSED && p.gelu_grad_x) ? p.gelu_grad_x + int64_t(bz) * p.stride_c : nullptr;
             if (use_tma) {
@@ -295,7 +301,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
                         for (int q = 0; q < 32; ++q) v[q] *= p.alpha;
                     }
-                    if (p.tma_c16) {
+                    if (f_c16box) {
                         // bf16-only result: two 32-column chunks share one 64-column box (128 bytes of bf16 per row, same
                         // 128B swizzle); the box leaves after its second half, or after the last chunk inside the matrix
                         uint8_t* box = wbuf;
@@ -312,7 +318,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                                 make_uint4(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1),
                                            *reinterpret_cast<const uint32_t*>(&h2), *reinterpret_cast<const uint32_t*>(&h3));
                         }
-                        if (EW == 8 && p.tma_g16) {                      // GELU of the same values into the second box
+                        if (f_g16box) {                                  // GELU of the same values into the second box
                             uint8_t* rowg = box + kEpiBufBytes + lane * 128;
 #pragma unroll
                             for (int q = 0; q < 4; ++q) {
@@ -331,7 +337,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             __syncwarp();
                             if (lane == 0) {
                                 tma_store_3d(&map_c, box, n0 + (cc & ~63), row_base, bz);
-                                if (EW == 8 && p.tma_g16) tma_store_3d(&map_g, box + kEpiBufBytes, n0 + (cc & ~63), row_base, bz);
+                                if (f_g16box) tma_store_3d(&map_g, box + kEpiBufBytes, n0 + (cc & ~63), row_base, bz);
                                 tma_store_commit();
                             }
                         }
@@ -347,7 +353,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                         __syncwarp();
                         if (lane == 0) { tma_store_3d(&map_c, box, n0 + cc, row_base, bz); tma_store_commit(); }
                         ++nstore;
-                        if (p.c16) {                                  // fp32 through the TMA, bf16 copy straight from registers
+                        if (f_c16reg) {                               // fp32 through the TMA, bf16 copy straight from registers
                             const int grow = row_base + lane;
                             if (grow < p.m) {
                                 __nv_bfloat16* d16 = p.c16 + int64_t(grow) * p.ld_c16 + n0 + cc;
@@ -652,6 +658,10 @@ void gemm_tc_profile_read(double* flops, double* ms, long long* launches) {
     if (launches) *launches = g_prof.launches;
 }
 
+template <int BN, int CG, bool BF16, bool FUSED, int EW, int FORM>
+static int launch_tc_form(const GemmParams& p, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& ma2,
+                          const CUtensorMap& mb2, const CUtensorMap& mc, const CUtensorMap& mg, const TcArgs& a);
+
 template <int BN, int CG, bool BF16, bool FUSED, int EW>
 static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     using Cfg = TcCfg<BN, CG, EW>;
@@ -707,9 +717,22 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     a.addend = p.addend; a.ld_addend = p.ld_addend; a.gelu_grad_x = p.gelu_grad_x; a.ld_gelu_grad_x = p.ld_gelu_grad_x;
     a.gelu16 = static_cast<__nv_bfloat16*>(p.gelu_out_bf16); a.ld_gelu16 = p.ld_gelu_out_bf16;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
+    // compile-time epilogue form (see gemm_tc_kernel): the plain box forms get their own instantiation
+    if (!FUSED) {
+        if (a.tma_c16 && a.tma_g16) { if (EW == 8) return launch_tc_form<BN, CG, BF16, false, EW, (EW == 8 ? 3 : 0)>(p, st, ma, mb, ma2, mb2, mc, mg, a); }
+        else if (a.tma_c16) return launch_tc_form<BN, CG, BF16, false, EW, 2>(p, st, ma, mb, ma2, mb2, mc, mg, a);
+        else if (a.tma_c && !a.c16 && !p.gelu_out && !p.gelu_out_bf16) return launch_tc_form<BN, CG, BF16, false, EW, 1>(p, st, ma, mb, ma2, mb2, mc, mg, a);
+    }
+    return launch_tc_form<BN, CG, BF16, FUSED, EW, 0>(p, st, ma, mb, ma2, mb2, mc, mg, a);
+}
+
+template <int BN, int CG, bool BF16, bool FUSED, int EW, int FORM>
+static int launch_tc_form(const GemmParams& p, cudaStream_t st, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& ma2,
+                          const CUtensorMap& mb2, const CUtensorMap& mc, const CUtensorMap& mg, const TcArgs& a) {
+    using Cfg = TcCfg<BN, CG, EW>;
     static bool attr_set[kMaxDevices] = {};
     if (first_use_on_device(attr_set)) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16, FUSED, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, CG, BF16, FUSED, EW, FORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::smem_bytes);
         if (e != cudaSuccess) return set_error(2, "mft_gemm(tc): smem attribute: %s", cudaGetErrorString(e));
     }
     const int64_t units = ceil_div(a.tiles_m, CG) * a.tiles_n * a.batch;    // CTAs, or CTA pairs
@@ -741,7 +764,7 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED, EW>, ma, mb, ma2, mb2, mc, mg, a);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED, EW, FORM>, ma, mb, ma2, mb2, mc, mg, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);
     if (e == cudaSuccess) e = cudaGetLastError();
