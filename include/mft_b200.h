@@ -175,6 +175,12 @@ int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stre
 /* MulBackward for same-shape operands: ga = gy*b, gb = gy*a (core/backward_functions.cpp:74-83). */
 /* mft_gelu_bwd plus a dense bf16 copy of gx (NULL = off) for the bf16 GEMM that consumes it; no reference counterpart. */
 int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void* gx_bf16, int64_t n, mft_stream_t stream);
+/* GeGLU of the Gemma MLP in one pass: y = gelu_tanh(gate) * up (ops::gelu + ops::mul, graph/gemma_model.cpp:534-551) and its
+ * backward d gate = (gy * up) * gelu'(gate), d up = gy * gelu(gate) (MulBackward + GeluBackward, core/backward_functions.cpp:66-83,
+ * 155-177). The *_bf16 pointers (NULL = off) receive bf16 copies for the GEMMs that consume them. n % 4 == 0, 16-byte aligned. */
+int mft_geglu_fwd(const float* gate, const float* up, float* y, void* y_bf16, int64_t n, mft_stream_t stream);
+int mft_geglu_bwd(const float* gate, const float* up, const float* gy, float* dgate, float* dup, void* dgate_bf16, void* dup_bf16, int64_t n,
+                  mft_stream_t stream);
 /* GeluBackward (core/backward_functions.cpp:155-177) for the bf16 operand mode, with the incoming gradient and the result as
  * bf16 arrays (they are a bf16-only GEMM result and a bf16 GEMM operand): x is fp32, or bf16 when x_is_bf16; gx (fp32) is
  * optional. n % 8 == 0, 16-byte aligned pointers. 8 (or 6) bytes per element instead of 14. */

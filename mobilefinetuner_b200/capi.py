@@ -97,6 +97,8 @@ SIGNATURES = {
     "mft_gelu_fwd": (C.c_int, [vp, vp, i64, vp]),
     "mft_gelu_bwd": (C.c_int, [vp, vp, vp, i64, vp]),
     "mft_gelu_bwd_ex": (C.c_int, [vp, vp, vp, vp, i64, vp]),
+    "mft_geglu_fwd": (C.c_int, [vp, vp, vp, vp, i64, vp]),
+    "mft_geglu_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
     "mft_gelu_bwd_lowp": (C.c_int, [vp, C.c_int, vp, vp, vp, i64, vp]),
     "mft_cast_from_bf16": (C.c_int, [vp, i64, vp, i64, i64, i64, vp]),
     "mft_mul_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, vp]),

@@ -260,9 +260,10 @@ TensorPtr GemmaModel::attention(const TensorPtr& x, GemmaBlockWeights& b, const 
 
 // graph/gemma_model.cpp:522-555 — GeGLU: down( gelu(gate(x)) * up(x) )
 TensorPtr GemmaModel::mlp(const TensorPtr& x, GemmaBlockWeights& b) const {
-    auto gate = gelu(project(x, b.gate_proj_lora, b.gate_proj_weight));
+    auto gate = project(x, b.gate_proj_lora, b.gate_proj_weight);
     auto up = project(x, b.up_proj_lora, b.up_proj_weight);
-    return project(mul(gate, up), b.down_proj_lora, b.down_proj_weight);
+    static const bool fused = [] { const char* e = std::getenv("MFT_GEMMA_FUSED_MLP"); return !(e && e[0] == '0'); }();
+    return project(fused ? geglu(gate, up) : mul(gelu(gate), up), b.down_proj_lora, b.down_proj_weight);
 }
 
 // graph/gemma_model.cpp:579-685

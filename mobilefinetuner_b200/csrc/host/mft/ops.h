@@ -102,6 +102,7 @@ TensorPtr apply_mask(const TensorPtr& input, const TensorPtr& mask, float mask_v
 TensorPtr repeat_kv_heads(const TensorPtr& kv, int repeat_factor);
 TensorPtr apply_rope(const TensorPtr& x, int seq_len, int head_dim, float rope_theta = 10000.0f);
 TensorPtr swiglu(const TensorPtr& gate, const TensorPtr& up);
+TensorPtr geglu(const TensorPtr& gate, const TensorPtr& up);          // B200 extension: gelu(gate) * up as one node / one kernel
 
 bool same_shape(const TensorPtr& a, const TensorPtr& b);
 bool broadcastable(const TensorPtr& a, const TensorPtr& b);

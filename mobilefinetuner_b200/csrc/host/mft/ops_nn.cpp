@@ -121,6 +121,38 @@ TensorPtr exp(const TensorPtr& x) { return unary(5, x, "exp"); }
 TensorPtr log(const TensorPtr& x) { return unary(6, x, "log"); }
 TensorPtr sqrt(const TensorPtr& x) { return unary(7, x, "sqrt"); }
 TensorPtr abs(const TensorPtr& x) { return unary(8, x, "abs"); }
+namespace {
+class GegluBackward : public BackwardFunction {
+public:
+    GegluBackward(TensorPtr gate, TensorPtr up) : gate_(std::move(gate)), up_(std::move(up)) {}
+    std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
+        TensorPtr gy = contiguous(gy_in);
+        auto dg = new_like(gate_), du = new_like(up_);
+        float* dgp = dg->dev_f32_out();
+        float* dup = du->dev_f32_out();
+        const Emit eg = emit16(dg, true), eu = emit16(du, true);      // both feed the dX products of gate / up
+        mft_rt::check(mft_geglu_bwd(gate_->dev_f32(), up_->dev_f32(), gy->dev_f32(), dgp, dup, eg.ptr, eu.ptr, gate_->numel(), st()), "mft_geglu_bwd");
+        return {dg, du};
+    }
+private:
+    TensorPtr gate_, up_;
+};
+}  // namespace
+
+// gelu(gate) * up as one node (B200 extension; the Gemma MLP, graph/gemma_model.cpp:534-551)
+TensorPtr geglu(const TensorPtr& gate_in, const TensorPtr& up_in) {
+    require_f32(gate_in, "geglu");
+    require_f32(up_in, "geglu");
+    if (gate_in->shape() != up_in->shape() || gate_in->numel() % 4) return mul(gelu(gate_in), up_in);
+    TensorPtr gate = contiguous(gate_in), up = contiguous(up_in);
+    auto y = new_like(gate);
+    float* yp = y->dev_f32_out();
+    const Emit e = emit16(y, true);                                   // the down projection's A operand
+    mft_rt::check(mft_geglu_fwd(gate->dev_f32(), up->dev_f32(), yp, e.ptr, gate->numel(), st()), "mft_geglu_fwd");
+    track(y, {gate_in, up_in}, std::make_shared<GegluBackward>(gate, up));
+    return y;
+}
+
 TensorPtr swiglu(const TensorPtr& gate, const TensorPtr& up) { return mul(silu(gate), up); }   // core/ops.cpp:2227-2264
 
 // ---------------------------------------------------------------------------- normalisation

@@ -239,6 +239,35 @@ __global__ void cast_from_bf16_kernel(const __nv_bfloat16* __restrict__ in, int6
     }
 }
 
+// GeGLU: y = gelu_tanh(gate) * up (Gemma MLP, graph/gemma_model.cpp:534-551: ops::gelu then ops::mul) in one pass, with an
+// optional bf16 copy of y for the down projection's GEMM; and its backward: d gate = gy * up * gelu'(gate), d up = gy * gelu(gate)
+// (GeluBackward + MulBackward, core/backward_functions.cpp:155-177, 66-83), each with an optional bf16 copy.
+__global__ void geglu_fwd_kernel(const float* __restrict__ gate, const float* __restrict__ up, float* __restrict__ y, __nv_bfloat16* __restrict__ y16, int64_t n) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        const float4 g = ld_stream(reinterpret_cast<const float4*>(gate) + i), u = ld_stream(reinterpret_cast<const float4*>(up) + i);
+        const float4 r = make_float4(gelu_tanh_f(g.x) * u.x, gelu_tanh_f(g.y) * u.y, gelu_tanh_f(g.z) * u.z, gelu_tanh_f(g.w) * u.w);
+        st_stream(reinterpret_cast<float4*>(y) + i, r);
+        if (y16) st_bf16x4(y16 + i * 4, r);
+    }
+}
+__global__ void geglu_bwd_kernel(const float* __restrict__ gate, const float* __restrict__ up, const float* __restrict__ gy, float* __restrict__ dgate,
+                                 float* __restrict__ dup, __nv_bfloat16* __restrict__ dgate16, __nv_bfloat16* __restrict__ dup16, int64_t n) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
+        const float4 g = ld_stream(reinterpret_cast<const float4*>(gate) + i), u = ld_stream(reinterpret_cast<const float4*>(up) + i);
+        const float4 d = ld_stream(reinterpret_cast<const float4*>(gy) + i);
+        // same association as the two reference nodes: MulBackward gives gy * up, GeluBackward multiplies by gelu'
+        const float4 dg = make_float4((d.x * u.x) * gelu_tanh_grad_f(g.x), (d.y * u.y) * gelu_tanh_grad_f(g.y), (d.z * u.z) * gelu_tanh_grad_f(g.z),
+                                      (d.w * u.w) * gelu_tanh_grad_f(g.w));
+        const float4 du = make_float4(d.x * gelu_tanh_f(g.x), d.y * gelu_tanh_f(g.y), d.z * gelu_tanh_f(g.z), d.w * gelu_tanh_f(g.w));
+        st_stream(reinterpret_cast<float4*>(dgate) + i, dg);
+        st_stream(reinterpret_cast<float4*>(dup) + i, du);
+        if (dgate16) st_bf16x4(dgate16 + i * 4, dg);
+        if (dup16) st_bf16x4(dup16 + i * 4, du);
+    }
+}
+
 // y = pow(x, p0) (kind 0) or clamp(x, p0, p1) (kind 1)
 __global__ void unary_param_kernel(int kind, const float* __restrict__ x, float* __restrict__ y, int64_t n, float p0, float p1) {
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
@@ -351,6 +380,28 @@ extern "C" int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void*
     gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, ok ? static_cast<__nv_bfloat16*>(gx_bf16) : nullptr);
     MFT_CHECK_LAUNCH("mft_gelu_bwd_ex");
     if (gx_bf16 && !ok) return mft_cast_bf16(gx, n, gx_bf16, n, 1, n, stream);
+    return 0;
+}
+
+extern "C" int mft_geglu_fwd(const float* gate, const float* up, float* y, void* y_bf16, int64_t n, mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!gate || !up || !y) return set_error(1, "mft_geglu_fwd: null pointer");
+    if ((n & 3) || !aligned16(gate) || !aligned16(up) || !aligned16(y) || (y_bf16 && (reinterpret_cast<uintptr_t>(y_bf16) & 7u)))
+        return set_error(1, "mft_geglu_fwd: n must be a multiple of 4 and the tensors 16-byte aligned");
+    geglu_fwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(gate, up, y, static_cast<__nv_bfloat16*>(y_bf16), n);
+    MFT_CHECK_LAUNCH("mft_geglu_fwd");
+    return 0;
+}
+extern "C" int mft_geglu_bwd(const float* gate, const float* up, const float* gy, float* dgate, float* dup, void* dgate_bf16, void* dup_bf16, int64_t n,
+                             mft_stream_t stream) {
+    if (n == 0) return 0;
+    if (!gate || !up || !gy || !dgate || !dup) return set_error(1, "mft_geglu_bwd: null pointer");
+    if ((n & 3) || !aligned16(gate) || !aligned16(up) || !aligned16(gy) || !aligned16(dgate) || !aligned16(dup) ||
+        (dgate_bf16 && (reinterpret_cast<uintptr_t>(dgate_bf16) & 7u)) || (dup_bf16 && (reinterpret_cast<uintptr_t>(dup_bf16) & 7u)))
+        return set_error(1, "mft_geglu_bwd: n must be a multiple of 4 and the tensors 16-byte aligned");
+    geglu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(gate, up, gy, dgate, dup, static_cast<__nv_bfloat16*>(dgate_bf16),
+                                                                        static_cast<__nv_bfloat16*>(dup_bf16), n);
+    MFT_CHECK_LAUNCH("mft_geglu_bwd");
     return 0;
 }
 

@@ -280,3 +280,20 @@ def test_refresh_bf16_shadows_many_tensors_one_launch(capi):
             assert torch.equal(p[:, :s[1]], e)
         if q is not None:
             assert torch.equal(q[:, :s[0]], e.t())
+
+
+def test_geglu_fwd_bwd_equals_gelu_then_mul(capi):
+    """mft_geglu_fwd / _bwd against the two reference nodes they replace (ops::gelu then ops::mul): same fp32 values."""
+    rng = np.random.default_rng(12)
+    n = 1024 * 20
+    gate, up, gy = (rng.standard_normal(n).astype(np.float32) for _ in range(3))
+    y, y16 = torch.empty(n, device="cuda"), torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    capi.call("mft_geglu_fwd", dev(gate), dev(up), y, y16, n, None)
+    e = O.gelu_fwd(gate) * up
+    assert rel(y, e) < FP32_TOL and torch.equal(y16, y.to(torch.bfloat16))
+    dg, du = torch.empty(n, device="cuda"), torch.empty(n, device="cuda")
+    dg16, du16 = torch.empty(n, device="cuda", dtype=torch.bfloat16), torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    capi.call("mft_geglu_bwd", dev(gate), dev(up), dev(gy), dg, du, dg16, du16, n, None)
+    assert rel(dg, O.gelu_bwd(gate, gy * up)) < FP32_TOL
+    assert rel(du, gy * O.gelu_fwd(gate)) < FP32_TOL
+    assert torch.equal(dg16, dg.to(torch.bfloat16)) and torch.equal(du16, du.to(torch.bfloat16))
