@@ -246,6 +246,9 @@ int mft_rmsnorm_fwd_ex(const float* x, const float* w, float* y, void* y_bf16, i
 int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,
                     int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
                     mft_stream_t stream);
+/* same, plus a bf16 copy of gx (NULL = off) for the bf16 dX products that read the gradient */
+int mft_rmsnorm_bwd_ex(const float* x, const float* w, const float* gy, float* gx, void* gx_bf16, int64_t ld_bf16, float* dw, int64_t rows,
+                       int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes, mft_stream_t stream);
 
 /* ------------------------------------------------------------------ softmax / attention / rope
  * Softmax over the last dim: core/ops.cpp:1119-1175; backward dx = y*(gy - sum(gy*y)) with the row

@@ -113,6 +113,7 @@ SIGNATURES = {
     "mft_rmsnorm_fwd": (C.c_int, [vp, vp, vp, i64, i64, f32, C.c_int, vp]),
     "mft_rmsnorm_fwd_ex": (C.c_int, [vp, vp, vp, vp, i64, i64, i64, f32, C.c_int, vp]),
     "mft_rmsnorm_bwd": (C.c_int, [vp, vp, vp, vp, vp, i64, i64, f32, C.c_int, vp, sz, vp]),
+    "mft_rmsnorm_bwd_ex": (C.c_int, [vp, vp, vp, vp, vp, i64, vp, i64, i64, f32, C.c_int, vp, sz, vp]),
     "mft_softmax_fwd": (C.c_int, [vp, vp, i64, i64, vp]),
     "mft_softmax_bwd": (C.c_int, [vp, vp, vp, i64, i64, vp]),
     "mft_attention_precise": (C.c_int, [C.c_int]),

@@ -281,10 +281,10 @@ TensorPtr GemmaModel::forward(const TensorPtr& input_ids, const TensorPtr& atten
         const float theta = is_sliding ? config_.rope_local_base_freq : config_.rope_theta;
         auto normed = rms_norm(h, b.input_layernorm_weight, eps);
         auto attn = attention(normed, b, pad, is_sliding ? sliding : causal, theta);
-        attn = rms_norm(attn, b.post_attention_layernorm_weight, eps);
+        attn = rms_norm_post(attn, b.post_attention_layernorm_weight, eps);
         h = add(h, attn);
         auto mlp_in = rms_norm(h, b.pre_feedforward_layernorm_weight, eps);
-        auto m = rms_norm(mlp(mlp_in, b), b.post_feedforward_layernorm_weight, eps);
+        auto m = rms_norm_post(mlp(mlp_in, b), b.post_feedforward_layernorm_weight, eps);
         h = add(h, m);
     }
     h = rms_norm(h, norm_weight_, eps);

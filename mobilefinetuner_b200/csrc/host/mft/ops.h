@@ -54,6 +54,7 @@ TensorPtr layer_norm(const TensorPtr& input, const TensorPtr& weight, const Tens
 // B200 extension: as layer_norm, result possibly written as bf16 only (bf16 operand mode, consumer is a GEMM operand)
 TensorPtr layer_norm_lowp(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias, float eps, bool y_bf16_only);
 TensorPtr rms_norm(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);         // scale (1 + w)
+TensorPtr rms_norm_post(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);    // rms_norm of a projection's output
 TensorPtr rms_norm_affine(const TensorPtr& input, const TensorPtr& weight, float eps = 1e-6f);  // scale w
 TensorPtr batch_norm(const TensorPtr& input, const TensorPtr& weight, const TensorPtr& bias,
                      const TensorPtr& running_mean = nullptr, const TensorPtr& running_var = nullptr,

@@ -197,7 +197,8 @@ private:
 };
 class RmsNormBackward : public BackwardFunction {    // core/backward_functions.cpp:483-523
 public:
-    RmsNormBackward(TensorPtr x, TensorPtr w, float eps, int plus_one) : x_(std::move(x)), w_(std::move(w)), eps_(eps), plus_one_(plus_one) {}
+    RmsNormBackward(TensorPtr x, TensorPtr w, float eps, int plus_one, bool gx_feeds_gemm)
+        : x_(std::move(x)), w_(std::move(w)), eps_(eps), plus_one_(plus_one), gx_feeds_gemm_(gx_feeds_gemm) {}
     std::vector<TensorPtr> apply(const TensorPtr& gy_in) override {
         TensorPtr gy = contiguous(gy_in);
         const int64_t dim = x_->shape().back(), rows = x_->numel() / dim;
@@ -207,14 +208,17 @@ public:
         const bool wg = wants_grad(w_);
         TensorPtr gw = wg ? Tensor::make(w_->shape(), kFloat32) : nullptr;
         size_t wsb = wg ? mft_norm_bwd_workspace_bytes(rows, dim) : 0;
-        mft_rt::check(mft_rmsnorm_bwd(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gx->dev_f32_out(), wg ? gw->dev_f32_out() : nullptr, rows, dim,
-                                      eps_, plus_one_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_rmsnorm_bwd");
+        float* gxp = gx->dev_f32_out();
+        const Emit e = gx_feeds_gemm_ ? emit16(gx, false) : Emit{};      // a post-norm's gradient is the dX operand of the projection behind it
+        mft_rt::check(mft_rmsnorm_bwd_ex(x_->dev_f32(), w_->dev_f32(), gy->dev_f32(), gxp, e.ptr, e.ld, wg ? gw->dev_f32_out() : nullptr, rows, dim,
+                                         eps_, plus_one_, wg ? mft_rt::workspace(wsb) : nullptr, wsb, st()), "mft_rmsnorm_bwd");
         return {gx, gw};
     }
 private:
     TensorPtr x_, w_;
     float eps_;
     int plus_one_;
+    bool gx_feeds_gemm_;
 };
 }  // namespace
 
@@ -281,7 +285,7 @@ TensorPtr add_layer_norm(const TensorPtr& x_in, const TensorPtr& a_in, const Ten
     return y;
 }
 
-static TensorPtr rms_impl(const TensorPtr& x_in, const TensorPtr& weight, float eps, int plus_one) {
+static TensorPtr rms_impl(const TensorPtr& x_in, const TensorPtr& weight, float eps, int plus_one, bool gx_feeds_gemm = false) {
     require_f32(x_in, "rms_norm");
     if (!weight) throw TensorError("rms_norm: weight is required");
     TensorPtr x = contiguous(x_in);
@@ -295,11 +299,14 @@ static TensorPtr rms_impl(const TensorPtr& x_in, const TensorPtr& weight, float 
     // the reference always registers a node for rms_norm (core/ops.cpp:1521-1524)
     if (autograd::Engine::instance().is_enabled()) {
         y->set_requires_grad(true);
-        autograd::Engine::instance().register_node(y, {x_in, weight}, std::make_shared<RmsNormBackward>(x, weight, eps, plus_one));
+        autograd::Engine::instance().register_node(y, {x_in, weight}, std::make_shared<RmsNormBackward>(x, weight, eps, plus_one, gx_feeds_gemm));
     }
     return y;
 }
 TensorPtr rms_norm(const TensorPtr& x, const TensorPtr& w, float eps) { return rms_impl(x, w, eps, 1); }          // core/ops.cpp:1489-1537
+// the same op for a norm applied to a projection's output (Gemma's post-attention / post-feedforward norms): its backward also
+// writes the gradient as the bf16 operand of that projection's dX product
+TensorPtr rms_norm_post(const TensorPtr& x, const TensorPtr& w, float eps) { return rms_impl(x, w, eps, 1, true); }
 TensorPtr rms_norm_affine(const TensorPtr& x, const TensorPtr& w, float eps) { return rms_impl(x, w, eps, 0); }  // core/ops.cpp:1539-1590
 
 // ---------------------------------------------------------------------------- softmax

@@ -296,7 +296,8 @@ __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __r
 // dx per row (double math as the reference) + per-CTA partial dw -> partial[cta][dim].
 __global__ void __launch_bounds__(kNormWarps * 32)
 rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ gy,
-                   float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps, int plus_one) {
+                   float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps, int plus_one,
+                   __nv_bfloat16* __restrict__ gx16, int64_t ld16) {          // gx16 != NULL: bf16 copy of gx
     extern __shared__ float smem[];  // [kNormWarps][dim]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float* my = smem + size_t(warp) * dim;
@@ -319,7 +320,9 @@ rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
         for (int i = lane; i < dim; i += 32) {
             double we = plus_one ? 1.0 + double(w[i]) : double(w[i]);
             double g = gr[i], v = xr[i];
-            gx[r * dim + i] = float(g * we * inv - v * coeff * dot);
+            const float o = float(g * we * inv - v * coeff * dot);
+            gx[r * dim + i] = o;
+            if (gx16) gx16[r * ld16 + i] = __float2bfloat16_rn(o);
             if (partial) my[i] += float(g * v * inv);
         }
     }
@@ -541,9 +544,24 @@ extern "C" int mft_rmsnorm_fwd_ex(const float* x, const float* w, float* y, void
     return 0;
 }
 
+static int rmsnorm_bwd_impl(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows, int64_t dim, float eps,
+                            int plus_one, void* workspace, size_t workspace_bytes, mft_stream_t stream, void* gx16, int64_t ld16);
+
 extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows,
                                int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
                                mft_stream_t stream) {
+    return rmsnorm_bwd_impl(x, w, gy, gx, dw, rows, dim, eps, plus_one, workspace, workspace_bytes, stream, nullptr, 0);
+}
+// same, plus a bf16 copy of gx (row pitch ld_bf16 elements) for the dX products that consume the gradient
+extern "C" int mft_rmsnorm_bwd_ex(const float* x, const float* w, const float* gy, float* gx, void* gx_bf16, int64_t ld_bf16, float* dw,
+                                  int64_t rows, int64_t dim, float eps, int plus_one, void* workspace, size_t workspace_bytes,
+                                  mft_stream_t stream) {
+    if (gx_bf16 && ld_bf16 < dim) return set_error(1, "mft_rmsnorm_bwd_ex: bf16 pitch < dim");
+    return rmsnorm_bwd_impl(x, w, gy, gx, dw, rows, dim, eps, plus_one, workspace, workspace_bytes, stream, gx_bf16, ld_bf16);
+}
+
+static int rmsnorm_bwd_impl(const float* x, const float* w, const float* gy, float* gx, float* dw, int64_t rows, int64_t dim, float eps,
+                            int plus_one, void* workspace, size_t workspace_bytes, mft_stream_t stream, void* gx16, int64_t ld16) {
     if (dim == 0) return 0;
     if (!x || !w || !gy || !gx) return set_error(1, "mft_rmsnorm_bwd: null pointer");
     if (rows == 0) return dw ? mft_fill(dw, dim, 0.f, stream) : 0;
@@ -557,7 +575,7 @@ extern "C" int mft_rmsnorm_bwd(const float* x, const float* w, const float* gy, 
     int parts = dw ? norm_bwd_ctas(rows) : int(std::min<int64_t>(ceil_div(rows, kNormWarps), int64_t(kNumSMs) * 8));
     float* partial = dw ? static_cast<float*>(workspace) : nullptr;     // dw == NULL (frozen weight): dx only, no second stage
     rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
-        x, w, gy, gx, partial, rows, int(dim), eps, plus_one);
+        x, w, gy, gx, partial, rows, int(dim), eps, plus_one, static_cast<__nv_bfloat16*>(gx16), ld16);
     if (dw) {
         norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
         add_launches(1);

@@ -214,6 +214,13 @@ def test_rmsnorm_golden_and_shapes(capi, golden_ops):
         w_ = ws(capi.lib.mft_norm_bwd_workspace_bytes(rows, dim))
         capi.call("mft_rmsnorm_bwd", dx_, dw_, dev(gy), gx, gw, rows, dim, 1e-6, 1, w_, w_.numel(), None)
         assert rel(y, ey) < FP32_TOL and rel(gx, ex) < FP32_TOL and rel(gw, ew) < FP32_TOL
+        # the _ex form: same fp32 result bit for bit, plus its bf16 rounding at a padded pitch
+        gx2, gw2 = torch.empty_like(dx_), torch.empty(dim, device="cuda")
+        ld = dim + 8
+        g16 = torch.zeros(rows, ld, device="cuda", dtype=torch.bfloat16)
+        capi.call("mft_rmsnorm_bwd_ex", dx_, dw_, dev(gy), gx2, g16, ld, gw2, rows, dim, 1e-6, 1, w_, w_.numel(), None)
+        assert torch.equal(gx2, gx) and torch.equal(gw2, gw)
+        assert torch.equal(g16[:, :dim], gx.reshape(rows, dim).to(torch.bfloat16)) and not g16[:, dim:].any()
 
 
 def test_softmax_golden(capi, golden_ops):

@@ -1,0 +1,29 @@
+#!/bin/bash
+# One GPU-box session: tests, bench lines, ncu launch lists. Usage: bash tools/gpu_round.sh <tag> [steps...]
+# steps: tests bench_c4 bench_small ncu_c4 ncu_c4_b64 ncu_c3 gemm_step
+tag=$1; shift
+M="gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active,gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed,sm__throughput.avg.pct_of_peak_sustained_elapsed,lts__t_bytes.sum"
+out=gpurun_out
+for s in "$@"; do
+  case $s in
+    tests) timeout 1500 python -m pytest tests -m gpu -x -q > $out/${tag}_tests.log 2>&1; tail -3 $out/${tag}_tests.log ;;
+    bench_c4)
+      timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_c4_strong.log 2>&1; tail -c 600 $out/${tag}_c4_strong.log
+      timeout 600 python bench.py --scaling weak --steps 20 --warmup 5 > $out/${tag}_c4_weak.log 2>&1; tail -c 300 $out/${tag}_c4_weak.log ;;
+    bench_small)
+      for c in c1 c2 c3; do timeout 600 python bench.py --config $c --steps 20 --warmup 5 > $out/${tag}_$c.log 2>&1; tail -1 $out/${tag}_$c.log | cut -c1-200; done ;;
+    ncu_c4)
+      timeout 300 python tools/profile_step.py --config c4 > $out/${tag}_prof_c4.log 2>&1 &&
+      timeout 900 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c4_metrics.csv python tools/profile_step.py --config c4 > $out/${tag}_ncu_c4.log 2>&1
+      python tools/ncu_summary.py $out/${tag}_c4_metrics.csv > $out/${tag}_c4_kernels.txt 2>&1; head -24 $out/${tag}_c4_kernels.txt ;;
+    ncu_c4_b64)
+      timeout 300 python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_prof_c4_b64.log 2>&1 &&
+      timeout 1200 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c4_b64_metrics.csv python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_ncu_c4_b64.log 2>&1
+      python tools/ncu_summary.py $out/${tag}_c4_b64_metrics.csv > $out/${tag}_c4_b64_kernels.txt 2>&1; head -24 $out/${tag}_c4_b64_kernels.txt ;;
+    ncu_c3)
+      timeout 300 python tools/profile_step.py --config c3 > $out/${tag}_prof_c3.log 2>&1 &&
+      timeout 900 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c3_metrics.csv python tools/profile_step.py --config c3 > $out/${tag}_ncu_c3.log 2>&1
+      python tools/ncu_summary.py $out/${tag}_c3_metrics.csv > $out/${tag}_c3_kernels.txt 2>&1; head -40 $out/${tag}_c3_kernels.txt ;;
+    gemm_step) timeout 300 python tools/gemm_bench.py step > $out/${tag}_gemm_step.log 2>&1; tail -12 $out/${tag}_gemm_step.log ;;
+  esac
+done
