@@ -230,7 +230,7 @@ def main():
     # N > 1: first prove that the data-parallel step equals the single-process step (small shape, exact mode, graph replay)
     dp_check = None
     if world > 1 and not a.no_dp_check:
-        dp_check = dp_equivalence_check(steps=8, graph=not a.no_graph)
+        dp_check = dp_equivalence_check(steps=8, graph=not a.no_graph, full_finetune=CONFIGS[a.config]["full"] if a.config in CONFIGS else False)
     hostlib.mft_host_set_gemm_precision(1 if a.precision == "bf16" else 0)
 
     c, scaling, batch, config = plan(a, world)
@@ -315,6 +315,12 @@ def main():
     capi.lib.mft_gemm_profile(0)
     peaks = load_peaks()
     arena_high = tr.arena_high_water
+    exchange = None
+    if dpt is not None:
+        overlapped = dpt.comm is not None and os.environ.get("MFT_DP_OVERLAP", "1" if c["full"] else "0") != "0"
+        exchange = ("mft_comm (NCCL behind the C ABI, mft_trainer_step_dp)" if dpt.comm else "torch.distributed all_reduce between the phases") + \
+                   (", bucket exchanged in chunks on a side stream while backward runs" if overlapped else ", one all-reduce of the bucket after backward")
+        dpt.close()
 
     if rank != 0:
         if world > 1:
@@ -369,7 +375,7 @@ def main():
             "data": "synthetic", "config": config,
             "run": {"launch": "eager" if a.no_graph else "cuda graph replay of the captured step",
                     "timing": "CUDA events on the compute stream, barrier + synchronize on both sides, max over ranks",
-                    "step_arena_high_water_gib": round(arena_high / 2**30, 2), "loss_last_timed_step": round(loss_now, 5)},
+                    "step_arena_high_water_gib": round(arena_high / 2**30, 2), "loss_last_timed_step": round(loss_now, 5), "exchange": exchange},
             "e2e": {"value": round(e2e_val, 1), "unit": "tokens/s", "h2d_bytes_per_step": tokens_rank * 4 * world,
                     "d2h_bytes_per_step": 4 * world, "ms_per_step": round(ms_e2e / a.steps, 3)},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline, "clocks": clocks}

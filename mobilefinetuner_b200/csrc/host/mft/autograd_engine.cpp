@@ -126,11 +126,32 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
         DeferGuard() { internal::begin_deferred_lora_tn(); }
         ~DeferGuard() { try { internal::flush_deferred_lora_tn(); } catch (...) {} }
     };
-    auto defer = std::make_unique<DeferGuard>();
-    for (const auto& node : order_from(roots)) {
+    std::unique_ptr<DeferGuard> defer;
+    if (!leaf_hook_) defer = std::make_unique<DeferGuard>();
+    const std::vector<NodePtr> order = order_from(roots);
+    // leaf-ready hook: consumers still to run, per leaf that wants a gradient
+    std::unordered_map<const Tensor*, int> consumers_left;
+    auto is_hooked_leaf = [](const EdgePtr& e) {
+        return e && e->input_node && e->input_node->tensor && !e->input_node->backward_fn && e->input_node->tensor->requires_grad();
+    };
+    if (leaf_hook_)
+        for (const auto& node : order)
+            if (node && node->backward_fn)
+                for (const auto& e : node->next_edges) if (is_hooked_leaf(e)) ++consumers_left[e->input_node->tensor.get()];
+    auto consumers_done = [&](const NodePtr& node) {
+        if (!leaf_hook_) return;
+        for (const auto& e : node->next_edges) {
+            if (!is_hooked_leaf(e)) continue;
+            const Tensor* key = e->input_node->tensor.get();
+            if (--consumers_left[key] != 0) continue;
+            auto pit = pending_.find(key);
+            leaf_hook_(e->input_node->tensor, pit != pending_.end() ? pit->second.grad : nullptr);
+        }
+    };
+    for (const auto& node : order) {
         if (!node || !node->tensor || !node->backward_fn) continue;
         auto it = pending_.find(node->tensor.get());
-        if (it == pending_.end()) continue;                 // nothing flowed into this node
+        if (it == pending_.end()) { consumers_done(node); continue; }     // nothing flowed into this node
         Pending* cur = &it->second;                         // element addresses survive the insertions below, iterators may not
         TensorPtr g = cur->grad;
         std::vector<TensorPtr> in_grads;
@@ -161,10 +182,13 @@ void Engine::run_backward(const std::vector<TensorPtr>& outputs, const std::vect
         }
         // interior gradients are dead once consumed (unless retained): release them early
         if (!node->tensor->retains_grad()) cur->grad.reset();
+        consumers_done(node);
     }
 
-    internal::flush_deferred_lora_tn();      // every recorded dA / dB product, now (errors propagate; the guard then finds nothing left)
-    defer.reset();
+    if (defer) {
+        internal::flush_deferred_lora_tn();  // every recorded dA / dB product, now (errors propagate; the guard then finds nothing left)
+        defer.reset();
+    }
 
     // write-back: leaves (nodes without a backward function) and retain_grad tensors; `.grad` is overwritten
     for (auto& kv : pending_) {

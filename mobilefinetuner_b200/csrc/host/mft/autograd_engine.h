@@ -7,6 +7,7 @@
 // arrival (the clone + elementwise += of core/autograd_engine.cpp:116-140 becomes at most one fused
 // out-of-place add), and accumulation runs as a CUDA kernel.
 #pragma once
+#include <functional>
 #include <memory>
 #include <unordered_map>
 #include <vector>
@@ -74,6 +75,12 @@ public:
     // overwritten (core/autograd_engine.cpp:243 overwrites, which breaks gradient accumulation — SURVEY Appendix B2).
     void set_accumulate(bool on) { accumulate_ = on; }
     bool accumulates() const { return accumulate_; }
+    // B200 extension, off by default: called during run_backward as soon as the LAST consumer of a leaf that requires a
+    // gradient has run, with the leaf's final gradient (null if nothing flowed into it). The data-parallel step uses it to
+    // start the exchange of a finished part of the gradient bucket while the rest of backward still runs. While a hook is
+    // set the adapter-gradient products are launched where they occur (no deferred group), so "final" holds for them too.
+    using LeafReadyHook = std::function<void(const TensorPtr& leaf, const TensorPtr& grad)>;
+    void set_leaf_ready_hook(LeafReadyHook h) { leaf_hook_ = std::move(h); }
 
 private:
     Engine() = default;
@@ -83,6 +90,7 @@ private:
     std::unordered_map<const Tensor*, Pending> pending_;
     bool enabled_ = true;
     bool accumulate_ = false;
+    LeafReadyHook leaf_hook_;
     void add_grad(const TensorPtr& target, const TensorPtr& g);
     std::vector<NodePtr> order_from(const std::vector<NodePtr>& roots) const;
 };

@@ -12,6 +12,7 @@
 #include <memory>
 #include <random>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "adam.h"
@@ -84,6 +85,18 @@ struct mft_trainer {
     float extra_grad_scale = 1.0f; // 1 / micro-batches, folded into the clip factor of the next update
     bool graph_enabled = true;     // runtime switch (mft_trainer_enable_graph); only effective when cfg.use_cuda_graph
     int eager_steps = 0;
+    // data-parallel exchange overlapped with backward (mft_trainer_step_dp, large buckets): the bucket is cut into chunks of
+    // consecutive tensors; a chunk is packed and all-reduced on a side stream as soon as the last of its gradients is final
+    struct Chunk { int first = 0, last = 0; int64_t off = 0, elems = 0; int waiting = 0; bool sent = false; cudaEvent_t packed = nullptr; };
+    std::vector<Chunk> chunks;
+    std::vector<int> chunk_of;
+    std::unordered_map<const Tensor*, int> index_of;
+    std::vector<const float*> ready_grad;          // per trainable tensor: device pointer of its final gradient (this step)
+    std::vector<TensorPtr> ready_keep;
+    mft_comm* overlap_comm = nullptr;              // non-null only while such a step runs
+    bool overlap_mode = false;                     // what the phase-1 graph (if any) was captured with
+    cudaStream_t side = nullptr;
+    cudaEvent_t joined = nullptr;
 };
 
 namespace {
@@ -201,12 +214,101 @@ void build(mft_trainer* t) {
     t->grad_elems = off;
 }
 
+// ---- overlapped exchange (see mft_trainer::Chunk)
+void build_chunks(mft_trainer* t) {
+    if (!t->chunks.empty()) return;
+    const char* e = std::getenv("MFT_DP_CHUNK_KB");
+    const int64_t want = std::max<int64_t>(1, e && *e ? std::atoll(e) : 48 * 1024) * 256;      // elements
+    const int n = int(t->trainable.size());
+    t->chunk_of.assign(size_t(n), 0);
+    mft_trainer::Chunk c;
+    for (int i = 0; i < n; ++i) {
+        if (c.last == c.first) c.off = t->offsets[size_t(i)];
+        c.last = i + 1;
+        const int64_t end = i + 1 < n ? t->offsets[size_t(i) + 1] : t->grad_elems;
+        c.elems = end - c.off;
+        t->chunk_of[size_t(i)] = int(t->chunks.size());
+        t->index_of[t->trainable[size_t(i)].get()] = i;
+        if (c.elems >= want || i + 1 == n) {
+            cudaEventCreateWithFlags(&c.packed, cudaEventDisableTiming);
+            t->chunks.push_back(c);
+            c = mft_trainer::Chunk();
+            c.first = c.last = i + 1;
+        }
+    }
+    cudaStreamCreateWithFlags(&t->side, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&t->joined, cudaEventDisableTiming);
+}
+
+void fill_slot(mft_trainer* t, size_t i, bool packed, const float* grad_ptr) {
+    mft_tensor_slot& s = t->slots_host[packed][i];
+    std::memset(&s, 0, sizeof(s));
+    s.n = t->trainable[i]->numel();
+    s.bucket_offset = t->offsets[i];
+    s.param = const_cast<float*>(t->trainable[i]->dev_f32());
+    s.grad = const_cast<float*>(grad_ptr);
+}
+
+// pack one finished chunk into the bucket (compute stream) and start its all-reduce on the side stream
+void send_chunk(mft_trainer* t, mft_trainer::Chunk& c) {
+    cudaStream_t st = static_cast<cudaStream_t>(mft_rt::stream());
+    const size_t n = size_t(c.last - c.first);
+    for (size_t i = size_t(c.first); i < size_t(c.last); ++i) fill_slot(t, i, false, t->ready_grad[i]);
+    char* dev = static_cast<char*>(t->slots_dev[0]) + size_t(c.first) * sizeof(mft_tensor_slot);
+    mft_rt::h2d(dev, t->slots_host[0] + c.first, n * sizeof(mft_tensor_slot));
+    mft_rt::check(mft_pack_grads(reinterpret_cast<const mft_tensor_slot*>(dev), int32_t(n), t->bucket, st), "mft_pack_grads");
+    if (cudaEventRecord(c.packed, st) != cudaSuccess || cudaStreamWaitEvent(t->side, c.packed, 0) != cudaSuccess) mft_rt::fail("overlapped exchange: event fork failed");
+    if (mft_comm_allreduce_sum(t->overlap_comm, t->bucket + c.off, c.elems, t->side) != 0) mft_rt::fail(std::string("overlapped exchange: ") + mft_comm_last_error());
+    c.sent = true;
+}
+
 void forward_backward(mft_trainer* t) {
     if (t->arena_on) mft_rt::arena_reset();
     TensorPtr logits = t->cfg.model == 0 ? t->gpt2->forward(t->ids, nullptr) : t->gemma->forward(t->ids, nullptr);
     TensorPtr loss = lm_cross_entropy(logits, t->ids, -100, "mean");
     mft_rt::d2d(t->loss_dev, loss->dev(), sizeof(float));
-    loss->backward();
+    if (t->overlap_comm) {
+        build_chunks(t);
+        // the previous step's chunk uploads may still be reading the pinned table
+        if (t->slots_event[0] && !t->capturing) cudaEventSynchronize(t->slots_event[0]);
+        t->ready_grad.assign(t->trainable.size(), nullptr);
+        t->ready_keep.clear();
+        for (auto& c : t->chunks) { c.waiting = c.last - c.first; c.sent = false; }
+        struct HookGuard {
+            ~HookGuard() { autograd::Engine::instance().set_leaf_ready_hook(nullptr); }
+        } guard;
+        autograd::Engine::instance().set_leaf_ready_hook([t](const TensorPtr& leaf, const TensorPtr& g) {
+            auto it = t->index_of.find(leaf.get());
+            if (it == t->index_of.end()) return;
+            const size_t i = size_t(it->second);
+            if (g) {
+                TensorPtr d = contiguous(g);
+                if (d != g) t->ready_keep.push_back(d);               // a dense copy made here: keep it until the chunk is packed
+                t->ready_grad[i] = d->dev_f32();                      // g itself is held by the engine until backward ends
+            }
+            mft_trainer::Chunk& c = t->chunks[size_t(t->chunk_of[i])];
+            if (--c.waiting == 0 && !c.sent) send_chunk(t, c);
+        });
+        loss->backward();
+        for (auto& c : t->chunks) {                                    // chunks with tensors the graph never reached (packed as zeros)
+            if (c.sent) continue;
+            for (size_t i = size_t(c.first); i < size_t(c.last); ++i) {   // the engine has written `.grad` by now: read the pointers from there
+                TensorPtr g = t->trainable[i]->grad();
+                if (g && !g->is_dense()) { g = contiguous(g); t->ready_keep.push_back(g); }
+                t->ready_grad[i] = g ? g->dev_f32() : nullptr;
+            }
+            send_chunk(t, c);
+        }
+        t->ready_keep.clear();
+        cudaStream_t st = static_cast<cudaStream_t>(mft_rt::stream());
+        if (cudaEventRecord(t->joined, t->side) != cudaSuccess || cudaStreamWaitEvent(st, t->joined, 0) != cudaSuccess) mft_rt::fail("overlapped exchange: event join failed");
+        if (!t->capturing) {
+            if (!t->slots_event[0]) cudaEventCreateWithFlags(&t->slots_event[0], cudaEventDisableTiming);
+            cudaEventRecord(t->slots_event[0], st);
+        }
+    } else {
+        loss->backward();
+    }
     t->grads.assign(t->trainable.size(), nullptr);
     t->with_grad = 0;
     for (size_t i = 0; i < t->trainable.size(); ++i) {
@@ -366,6 +468,9 @@ extern "C" void mft_trainer_destroy(mft_trainer* t) {
     try { mft_rt::sync(); } catch (...) {}
     for (auto& g : t->graph_exec) if (g) cudaGraphExecDestroy(g);
     for (int k = 0; k < 2; ++k) { mft_rt::pinned_free(t->slots_host[k]); if (t->slots_event[k]) cudaEventDestroy(t->slots_event[k]); }
+    for (auto& c : t->chunks) if (c.packed) cudaEventDestroy(c.packed);
+    if (t->joined) cudaEventDestroy(t->joined);
+    if (t->side) cudaStreamDestroy(t->side);
     mft_rt::pinned_free(t->shadow_host);
     mft_rt::pinned_free(t->lr_host);
     const bool had_arena = t->arena_on;
@@ -424,13 +529,31 @@ extern "C" int mft_trainer_set_grad_bucket(mft_trainer* t, float* dev_bucket, in
     return 0;
 }
 
+// the phase-1 graph is captured with or without the exchange inside: a change of mode captures it again
+static void set_overlap_mode(mft_trainer* t, bool on) {
+    if (t->overlap_mode == on) return;
+    if (t->graph_exec[1]) { try { mft_rt::sync(); } catch (...) {} cudaGraphExecDestroy(t->graph_exec[1]); t->graph_exec[1] = nullptr; }
+    t->eager_runs[1] = 0;
+    t->overlap_mode = on;
+}
+
+// MFT_DP_OVERLAP=0 / 1 forces the choice; by default buckets of 64 MB or more (full fine-tuning) are exchanged in chunks
+// while backward runs, smaller ones (adapters) by one all-reduce after it
+static bool want_overlap(const mft_trainer* t) {
+    if (t->cfg.world_size <= 1) return false;
+    const char* e = std::getenv("MFT_DP_OVERLAP");
+    if (e && *e) return std::atoi(e) != 0;
+    return t->grad_elems >= (int64_t(64) << 18);
+}
+
 extern "C" int mft_trainer_forward_backward(mft_trainer* t, const int32_t* dev_ids) {
     if (!t || !dev_ids) return fail("mft_trainer_forward_backward: null argument");
     if (!t->bucket) return fail("mft_trainer_forward_backward: set a gradient bucket first");
     try {
         const size_t bytes = size_t(t->cfg.batch) * t->cfg.seq_len * sizeof(int32_t);
         mft_rt::d2d(t->ids->dev_out(), dev_ids, bytes);
-        run_phase(t, 1, [t] { forward_backward(t); pack_phase(t); });
+        set_overlap_mode(t, t->overlap_comm != nullptr);
+        run_phase(t, 1, [t] { forward_backward(t); if (!t->overlap_comm) pack_phase(t); });
         t->launches = t->phase_launches[1];
         return 0;
     } catch (const std::exception& e) { return fail("mft_trainer_forward_backward: %s", e.what()); }
@@ -454,8 +577,13 @@ extern "C" int mft_trainer_step_dp(mft_trainer* t, mft_comm* comm, const int32_t
             t->own_bucket = zeros({t->grad_elems > 0 ? t->grad_elems : 4}, kFloat32, kCPU);
             if (mft_trainer_set_grad_bucket(t, t->own_bucket->dev_f32_mut(), t->grad_elems) != 0) return 1;
         }
-        if (mft_trainer_forward_backward(t, dev_ids) != 0) return 1;
-        if (mft_comm_allreduce_sum(comm, t->bucket, t->grad_elems, mft_rt::stream()) != 0) return fail("mft_trainer_step_dp: %s", mft_comm_last_error());
+        const bool overlap = want_overlap(t);
+        t->overlap_comm = overlap ? comm : nullptr;
+        const int rc = mft_trainer_forward_backward(t, dev_ids);
+        t->overlap_comm = nullptr;
+        if (rc != 0) return 1;
+        if (!overlap && mft_comm_allreduce_sum(comm, t->bucket, t->grad_elems, mft_rt::stream()) != 0)
+            return fail("mft_trainer_step_dp: %s", mft_comm_last_error());
         return mft_trainer_update(t);
     } catch (const std::exception& e) { return fail("mft_trainer_step_dp: %s", e.what()); }
 }

@@ -78,8 +78,26 @@ struct TcArgs {
     int tma_g16;               // 1: with tma_c16, the GELU aux output (bf16 only) leaves through boxes too (map_g; EW = 8 form)
     float alpha, beta;
     int tiles_m, tiles_n;
+    int group_m;               // raster: m-units per group (see tile_coords)
     int tma_c;                 // 1: the epilogue writes C (and gelu_out) with TMA box stores through map_c / map_g
 };
+
+// Raster order of the persistent tile loop. Tiles that run at the same time should share operand rows, so that each slab of
+// A and B comes from HBM once and from L2 afterwards: m-units are taken in groups of `gm`; inside a group the index runs over
+// the group's m-units first, then over ALL n-tiles, before the next group starts. gm >= tiles_mu is the plain m-fastest order
+// (fine while A fits in L2); with 32 768 rows the plain order re-read A once per n-tile (twice the algorithmic DRAM bytes on
+// fc_in, four times on the K = 4096 dX product).
+__device__ __forceinline__ void tile_coords(int tile, int tiles_mu, int tiles_n, int gm, int& mu, int& nt, int& bz) {
+    const int per_b = tiles_mu * tiles_n;
+    bz = tile / per_b;
+    int t = tile - bz * per_b;
+    const int grp = t / (gm * tiles_n);
+    const int first = grp * gm;
+    const int rows = min(gm, tiles_mu - first);
+    t -= grp * gm * tiles_n;
+    nt = t / rows;
+    mu = first + (t - nt * rows);
+}
 
 // BF16 = false: fp32 operands in HBM, TF32 MMA (32 elements per 128-byte k-block, K = 8 per instruction).
 // BF16 = true : bf16 operands in HBM, kind::f16 MMA (64 elements per k-block, K = 16 per instruction): same bytes per
@@ -146,9 +164,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int tile = unit; tile < num_tiles; tile += num_units) {
-                const int mt = (tile % tiles_mu) * CG + int(cta_rank);          // this CTA's own 128-row tile
-                const int nt = (tile / tiles_mu) % p.tiles_n;
-                const int bz = tile / (tiles_mu * p.tiles_n);
+                int mu, nt, bz;
+                tile_coords(tile, tiles_mu, p.tiles_n, p.group_m, mu, nt, bz);
+                const int mt = mu * CG + int(cta_rank);                         // this CTA's own 128-row tile
                 const int brow = nt * BN + int(cta_rank) * Cfg::b_rows;         // this CTA's share of the B tile
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
@@ -250,9 +268,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         uint32_t nstore = 0;                              // boxes this warp has handed to the TMA (ring of two buffers)
         int it = 0;
         for (int tile = unit; tile < num_tiles; tile += num_units, ++it) {
-            const int mt = (tile % tiles_mu) * CG + int(cta_rank);
-            const int nt = (tile / tiles_mu) % p.tiles_n;
-            const int bz = tile / (tiles_mu * p.tiles_n);
+            int mu, nt, bz;
+            tile_coords(tile, tiles_mu, p.tiles_n, p.group_m, mu, nt, bz);
+            const int mt = mu * CG + int(cta_rank);
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
             mbar_wait(&tmem_full[as], aphase);
@@ -717,6 +735,14 @@ static int launch_tc_impl(const GemmParams& p, cudaStream_t st) {
     a.addend = p.addend; a.ld_addend = p.ld_addend; a.gelu_grad_x = p.gelu_grad_x; a.ld_gelu_grad_x = p.ld_gelu_grad_x;
     a.gelu16 = static_cast<__nv_bfloat16*>(p.gelu_out_bf16); a.ld_gelu16 = p.ld_gelu_out_bf16;
     a.tiles_m = int(ceil_div(p.m, TBM)); a.tiles_n = int(ceil_div(p.n, BN));
+    {
+        // raster groups (tile_coords): 16 m-units (4096 rows with CTA pairs) keep a group's A slab and one sweep of B inside
+        // L2; a very wide B (the vocabulary) is swept fewer times with 32. MFT_TC_GROUP_M overrides (experiments).
+        static const int forced = [] { const char* e = std::getenv("MFT_TC_GROUP_M"); return e && *e ? std::atoi(e) : 0; }();
+        const int tiles_mu = int(ceil_div(a.tiles_m, CG));
+        const int gm = forced > 0 ? forced : (a.tiles_n >= 64 ? 32 : 16);
+        a.group_m = std::max(1, std::min(gm, tiles_mu));
+    }
     // compile-time epilogue form (see gemm_tc_kernel): the plain box forms get their own instantiation
     if (!FUSED) {
         if (a.tma_c16 && a.tma_g16) { if (EW == 8) return launch_tc_form<BN, CG, BF16, false, EW, (EW == 8 ? 3 : 0)>(p, st, ma, mb, ma2, mb2, mc, mg, a); }

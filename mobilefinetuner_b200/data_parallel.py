@@ -15,6 +15,8 @@ tests/test_data_parallel.py; the device pieces are the C ABI calls named above.
 """
 from __future__ import annotations
 
+import os
+
 BUCKET_ALIGN = 4  # elements; keeps every tensor's slice 16-byte aligned for the vectorised kernels (trainer_session.cpp)
 
 
@@ -89,7 +91,11 @@ class DataParallelTrainer:
     `trainer` must have been created with world_size / rank of the current process group. The all-reduce is issued on
     the trainer's own stream, so it is ordered after the pack and before the update without host synchronisation."""
 
-    def __init__(self, trainer, group=None):
+    def __init__(self, trainer, group=None, exchange=None):
+        """exchange: "mft" = the library's own communicator (mft_comm_*, NCCL loaded by libmft_host; the whole step is then one
+        C-ABI call, mft_trainer_step_dp, and large buckets are exchanged in chunks while backward runs); "torch" = the bucket is
+        all-reduced by torch.distributed between the two phases. Default: "mft" on an NCCL process group (MFT_DP_EXCHANGE
+        overrides)."""
         import torch
         import torch.distributed as dist
         self.trainer = trainer
@@ -99,6 +105,38 @@ class DataParallelTrainer:
             raise ValueError(f"trainer was built for world_size {trainer.cfg.world_size}, process group has {self.world}")
         self.stream = torch.cuda.ExternalStream(trainer.stream)
         self.bucket = trainer.make_grad_bucket() if self.world > 1 else None
+        self.comm = None
+        if exchange is None:
+            exchange = os.environ.get("MFT_DP_EXCHANGE") or ("mft" if self.world > 1 and dist.get_backend(group) == "nccl" else "torch")
+        if exchange not in ("mft", "torch"):
+            raise ValueError(f"exchange must be 'mft' or 'torch', not {exchange!r}")
+        self.exchange = exchange
+        if self.world > 1 and exchange == "mft":
+            self.comm = self._make_comm(dist, torch)
+
+    def _make_comm(self, dist, torch):
+        """rank 0 draws the 128-byte NCCL id, the process group carries it to the others, every rank joins."""
+        import ctypes as C
+        from .trainer import hostlib
+        rank = dist.get_rank(self.group)
+        ident = (C.c_char * 128)()
+        if rank == 0 and hostlib.mft_comm_unique_id(ident) != 0:
+            raise RuntimeError(hostlib.mft_comm_last_error().decode())
+        dev = "cuda" if dist.get_backend(self.group) == "nccl" else "cpu"
+        t = torch.frombuffer(bytearray(ident.raw), dtype=torch.uint8).to(dev)
+        dist.broadcast(t, src=dist.get_global_rank(self.group, 0) if self.group is not None else 0, group=self.group)
+        raw = bytes(t.cpu().numpy().tobytes())
+        comm = C.c_void_p()
+        if hostlib.mft_comm_init_rank(C.byref(comm), self.world, rank, raw) != 0:
+            raise RuntimeError(hostlib.mft_comm_last_error().decode())
+        return comm
+
+    def close(self):
+        if self.comm:
+            from .trainer import hostlib
+            self.trainer.sync()
+            hostlib.mft_comm_destroy(self.comm)
+            self.comm = None
 
     def step_device(self, dev_ids_ptr):
         """One optimiser step on this rank's rows (int32 token ids already in HBM)."""
@@ -106,6 +144,9 @@ class DataParallelTrainer:
         tr = self.trainer
         if self.world == 1:
             tr.step_device(dev_ids_ptr)
+            return
+        if self.comm:
+            tr.step_dp(self.comm, dev_ids_ptr)
             return
         tr.forward_backward(dev_ids_ptr)
         with torch.cuda.stream(self.stream):
@@ -125,12 +166,14 @@ class DataParallelTrainer:
 DP_CHECK_SHAPE = dict(model=0, n_layer=2, n_embd=64, n_head=4, vocab_size=503, n_positions=64)
 
 
-def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16):
+def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16, full_finetune=False):
     """N ranks stepping their rows (forward/backward -> NCCL all-reduce of the bucket -> update) against ONE process
     stepping the concatenated batch, on a small GPT-2 LoRA shape in the exact execution mode (fp32 SIMT GEMMs, 3xTF32
     attention), so the only difference is summation order. Needs an initialised NCCL process group and the current
     device set. Returns a dict (on every rank; `ok` is rank 0's verdict broadcast to all):
-    loss within 1e-4 relative per step, every trainable tensor within 1e-3 in sum|.|, replicas bit-identical."""
+    loss within 1e-4 relative per step, every trainable tensor within 1e-3 in sum|.|, replicas bit-identical.
+    full_finetune: every tensor trains and the exchange is forced into its overlapped form (64 KB chunks all-reduced on a side
+    stream while backward runs), which is what a full fine-tuning bucket uses by default."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -138,12 +181,15 @@ def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16):
     from .trainer import Trainer
     world, rank = dist.get_world_size(), dist.get_rank()
     prev_tc, prev_at = capi.lib.mft_use_tensor_cores(0), capi.lib.mft_attention_precise(1)
+    prev_env = {k: os.environ.get(k) for k in ("MFT_DP_OVERLAP", "MFT_DP_CHUNK_KB")}
+    if full_finetune:
+        os.environ.update(MFT_DP_OVERLAP="1", MFT_DP_CHUNK_KB="64")
     try:
         rng = np.random.default_rng(5)
         batches = rng.integers(0, DP_CHECK_SHAPE["vocab_size"], (steps, per_rank * world, seq)).astype(np.int32)
         lo, hi = shard_rows(per_rank * world, rank, world)
-        tr = Trainer(per_rank, seq, shape=DP_CHECK_SHAPE, lora_rank=8, lora_alpha=16.0, arena_mb=256, world_size=world, rank=rank,
-                     cuda_graph=graph)
+        tr = Trainer(per_rank, seq, shape=DP_CHECK_SHAPE, full_finetune=full_finetune, lora_rank=8, lora_alpha=16.0, arena_mb=256,
+                     world_size=world, rank=rank, cuda_graph=graph)
         dpt = DataParallelTrainer(tr)
         losses = []
         for s in range(steps):
@@ -157,10 +203,12 @@ def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16):
         replicas_equal = torch.tensor([1 if torch.equal(mine, ref0) else 0], device="cuda")
         dist.all_reduce(replicas_equal, op=dist.ReduceOp.MIN)
         with_grad = tr.num_with_grad
+        exchange = dpt.exchange + (" (chunks overlapped with backward)" if full_finetune and dpt.comm else "")
+        dpt.close()
         tr.close()
         verdict = torch.zeros(3, dtype=torch.float64, device="cuda")     # ok, worst loss error, worst parameter error
         if rank == 0:
-            one = Trainer(per_rank * world, seq, shape=DP_CHECK_SHAPE, lora_rank=8, lora_alpha=16.0, arena_mb=256)
+            one = Trainer(per_rank * world, seq, shape=DP_CHECK_SHAPE, full_finetune=full_finetune, lora_rank=8, lora_alpha=16.0, arena_mb=256)
             worst_l = worst_p = 0.0
             for s in range(steps):
                 l1 = one.step_numpy(batches[s])
@@ -177,7 +225,13 @@ def dp_equivalence_check(steps=12, graph=True, per_rank=2, seq=16):
         return {"ok": bool(verdict[0].item() == 1.0), "world": world, "steps": steps, "cuda_graph": bool(graph),
                 "worst_loss_rel_err": float(verdict[1].item()), "worst_param_rel_err": float(verdict[2].item()),
                 "replicas_bit_identical": bool(replicas_equal.item()), "last_loss": losses[-1],
-                "shape": "GPT-2 2 layers x 64, LoRA r8, %d x %d tokens per rank, exact fp32 mode" % (per_rank, seq)}
+                "exchange": exchange,
+                "shape": "GPT-2 2 layers x 64, %s, %d x %d tokens per rank, exact fp32 mode" % ("full fine-tune" if full_finetune else "LoRA r8", per_rank, seq)}
     finally:
+        for k, v in prev_env.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
         capi.lib.mft_use_tensor_cores(prev_tc)
         capi.lib.mft_attention_precise(prev_at)

@@ -145,6 +145,10 @@ class Trainer:
     def update(self):
         self._ck(hostlib.mft_trainer_update(self._h))
 
+    def step_dp(self, comm, dev_ids_ptr):
+        """mft_trainer_step_dp: forward/backward, NCCL exchange through `comm` (an mft_comm handle), update — all behind the C ABI."""
+        self._ck(hostlib.mft_trainer_step_dp(self._h, comm, dev_ids_ptr))
+
     def accumulate(self, dev_ids_ptr):
         """True-gradient mode: forward + backward of one micro-batch, gradients added to the running sums."""
         self._ck(hostlib.mft_trainer_accumulate(self._h, dev_ids_ptr))

@@ -1,5 +1,7 @@
 // Two (or N) data-parallel ranks driven through the C ABI only — no Python, no torch.distributed:
-//   dp_two_rank [world=2] [steps=6]
+//   dp_two_rank [world=2] [steps=6] [full_finetune=0]
+// With full_finetune=1 every tensor trains; MFT_DP_OVERLAP=1 MFT_DP_CHUNK_KB=64 then exercises the exchange that runs in
+// chunks on a side stream while backward is still producing the rest of the gradients.
 // The parent forks one process per rank; rank r selects GPU r, creates a trainer (small GPT-2 LoRA shape) and a communicator
 // (mft_comm_init_from_file), and steps its rows of every global batch with mft_trainer_step_dp. Then the parent steps the SAME
 // global batches in one process (world_size 1) and compares the per-step mean loss and every trainable tensor's checksum.
@@ -18,12 +20,14 @@
 
 #include "mft_trainer.h"
 
+static int g_full = 0;
 static mft_trainer_config make_cfg(int batch, int seq, int world, int rank) {
     mft_trainer_config c;
     std::memset(&c, 0, sizeof(c));
     c.model = 0; c.n_layer = 2; c.n_embd = 64; c.n_head = 4; c.vocab_size = 503; c.n_positions = 64;
     c.lora_rank = 8; c.lora_alpha = 16.0f; c.batch = batch; c.seq_len = seq;
     c.lr = 2e-4f; c.beta1 = 0.9f; c.beta2 = 0.999f; c.eps = 1e-8f; c.weight_decay = 0.0f; c.clip_norm = 1.0f;
+    c.full_finetune = g_full;
     c.seed = 1234; c.world_size = world; c.rank = rank; c.arena_mb = 256; c.use_cuda_graph = 1;
     return c;
 }
@@ -94,6 +98,7 @@ static int run_rank(int world, int rank, int steps, int per, int seq, const std:
 
 int main(int argc, char** argv) {
     const int world = argc > 1 ? std::atoi(argv[1]) : 2, steps = argc > 2 ? std::atoi(argv[2]) : 6;
+    g_full = argc > 3 ? std::atoi(argv[3]) : 0;
     const int per = 2, seq = 16;
     int ngpu = 0;
     // (device count is queried in a child: the parent must not create a CUDA context before fork)
@@ -157,7 +162,7 @@ int main(int argc, char** argv) {
         worst_param = std::fmax(worst_param, std::fabs(rr[0].sumabs[i] - one.sumabs[i]) / std::fmax(one.sumabs[i], 1e-6));
     }
     const bool pass = worst_loss <= 1e-4 && worst_param <= 1e-3;
-    std::printf("%s world %d steps %d worst_loss_rel %.3g worst_param_rel %.3g nccl %d\n", pass ? "DP_C_ABI_OK" : "DP_C_ABI_FAILED", world, steps,
+    std::printf("%s world %d steps %d full %d worst_loss_rel %.3g worst_param_rel %.3g nccl %d\n", pass ? "DP_C_ABI_OK" : "DP_C_ABI_FAILED", world, steps, g_full,
                 worst_loss, worst_param, mft_comm_nccl_version());
     return pass ? 0 : 1;
 }

@@ -99,15 +99,16 @@ def bench_lora(iters=20):
         print(f"{name}: {us:7.1f} us  ({16.8 / us * 1e3:7.1f} GB/s algorithmic)", flush=True)
 
 
-def bench_step_forms(iters=20):
+def bench_step_forms(iters=20, T=4096):
     """The c4 layer's products in the forms the bf16 step launches them: bf16-only qkv, fc_in with the GELU epilogue writing
     pre-activation and activation as bf16, fp32 proj / fc_out, bf16-only dX of fc_out, fp32 dX of fc_in."""
-    T, Cm = 4096, 1024
+    Cm = 1024
     forms = [("qkv->bf16", T, 3 * Cm, Cm, "c16"), ("proj->f32", T, Cm, Cm, "f32"), ("fc_in+gelu->bf16", T, 4 * Cm, Cm, "gelu16"),
              ("fc_out->f32", T, Cm, 4 * Cm, "f32"), ("fc_out dX->bf16", T, 4 * Cm, Cm, "c16"), ("fc_in dX->f32", T, Cm, 4 * Cm, "f32")]
+    once = [("lm_head->f32", T, 50257, Cm, "f32"), ("lm_head dX->f32", T, Cm, 50264, "f32")]       # once per step, not in the layer total
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     total = 0.0
-    for name, m, n, k, form in forms:
+    for name, m, n, k, form in forms + once:
         a = torch.randn(m, k, device="cuda").bfloat16()
         b = (torch.randn(n, k, device="cuda") * 0.05).bfloat16()
         bias = torch.randn(n, device="cuda")
@@ -127,14 +128,16 @@ def bench_step_forms(iters=20):
             e0.record(); capi.lib.mft_gemm_bf16(C.byref(args), None); e1.record(); e1.synchronize()
             tot += e0.elapsed_time(e1)
         us = tot / iters * 1e3
-        total += us
+        if (name, m, n, k, form) in forms:
+            total += us
+        del a, b, c32, c16, g16
         print(f"{name:18s} m={m} n={n} k={k}: {us:8.1f} us  {2.0 * m * n * k / (us * 1e-6) / 1e12:7.1f} TFLOP/s", flush=True)
     print(f"layer total {total:8.1f} us  ({2.0 * T * Cm * Cm * 20 / (total * 1e-6) / 1e12:7.1f} TFLOP/s)", flush=True)
 
 
 if __name__ == "__main__":
-    if sys.argv[1:] == ["step"]:
-        bench_step_forms()
+    if sys.argv[1:2] == ["step"]:
+        bench_step_forms(T=int(sys.argv[2]) if len(sys.argv) > 2 else 4096)
         sys.exit(0)
     if sys.argv[1:] == ["skinny"]:
         for sh in SKINNY:

@@ -24,6 +24,20 @@ for s in "$@"; do
       timeout 300 python tools/profile_step.py --config c3 > $out/${tag}_prof_c3.log 2>&1 &&
       timeout 900 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c3_metrics.csv python tools/profile_step.py --config c3 > $out/${tag}_ncu_c3.log 2>&1
       python tools/ncu_summary.py $out/${tag}_c3_metrics.csv > $out/${tag}_c3_kernels.txt 2>&1; head -40 $out/${tag}_c3_kernels.txt ;;
+    dp)   # on an N-GPU box: NGPU=2 bash tools/gpu_round.sh tag dp
+      n=${NGPU:-2}
+      timeout 900 python -m pytest tests/test_trainer_gpu.py -m gpu -x -q -k "data_parallel" > $out/${tag}_dp_tests.log 2>&1; tail -3 $out/${tag}_dp_tests.log
+      MFT_USE_TENSOR_CORES=0 MFT_DP_OVERLAP=1 MFT_DP_CHUNK_KB=64 timeout 300 mobilefinetuner_b200/bin/dp_two_rank $n 8 1 > $out/${tag}_dp_two_rank_full.log 2>&1; tail -2 $out/${tag}_dp_two_rank_full.log
+      TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511"
+      timeout 600 python bench.py --config c2 --steps 20 --warmup 5 --no-cpu-baseline > $out/${tag}_c2_n1.log 2>&1; tail -1 $out/${tag}_c2_n1.log | cut -c1-160
+      timeout 600 $TR bench.py --config c2 --gpus $n --steps 20 --warmup 5 > $out/${tag}_c2_n$n.log 2>&1; tail -1 $out/${tag}_c2_n$n.log | cut -c1-160
+      MFT_DP_OVERLAP=0 timeout 600 $TR bench.py --config c2 --gpus $n --steps 20 --warmup 5 > $out/${tag}_c2_n${n}_nooverlap.log 2>&1; tail -1 $out/${tag}_c2_n${n}_nooverlap.log | cut -c1-160
+      timeout 600 $TR bench.py --gpus $n --steps 10 --warmup 3 > $out/${tag}_c4_strong_n$n.log 2>&1; tail -1 $out/${tag}_c4_strong_n$n.log | cut -c1-160
+      timeout 600 $TR bench.py --gpus $n --scaling weak --steps 20 --warmup 5 > $out/${tag}_c4_weak_n$n.log 2>&1; tail -1 $out/${tag}_c4_weak_n$n.log | cut -c1-160 ;;
     gemm_step) timeout 300 python tools/gemm_bench.py step > $out/${tag}_gemm_step.log 2>&1; tail -12 $out/${tag}_gemm_step.log ;;
+    gemm_step64)
+      timeout 300 python tools/gemm_bench.py step 32768 > $out/${tag}_gemm_step64.log 2>&1; tail -12 $out/${tag}_gemm_step64.log
+      MFT_TC_GROUP_M=1000 timeout 300 python tools/gemm_bench.py step 32768 > $out/${tag}_gemm_step64_mfast.log 2>&1; tail -12 $out/${tag}_gemm_step64_mfast.log
+      MFT_TC_GROUP_M=8 timeout 300 python tools/gemm_bench.py step 32768 > $out/${tag}_gemm_step64_g8.log 2>&1; tail -12 $out/${tag}_gemm_step64_g8.log ;;
   esac
 done
