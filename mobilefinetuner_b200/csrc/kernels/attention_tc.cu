@@ -2,16 +2,21 @@
 // GPT-2 semantics (core/memory_efficient_attention.cpp:92-162), head_dim 64, bf16 operands, fp32 scores / softmax / output.
 //
 // One CTA = 128 query rows of one (batch, head); keys stream through shared memory in tiles of 64.
-//   warps 0-3 : softmax. Thread t owns query row t == TMEM lane t: it reads its score row with tcgen05.ld, keeps the running
-//               max / sum and the 64 output accumulators in registers, and writes P (bf16) into the 128B-swizzled K-major
-//               shared-memory tile that feeds the second product.
-//   warp 4    : TMA producer (lane 0): Q once, then K / V tiles into a two-stage ring (cp.async.bulk.tensor, SWIZZLE_128B).
-//   warp 5    : TMEM allocator + tcgen05.mma issuer (lane 0):  S = Q K^T  (M 128, N 64, K 64: both operands K-major)  and
+//   warps 0-7 : softmax, TWO threads per query row. Warps w and w + 4 own TMEM lanes 32 (w & 3) .. +31 (a warp reaches the
+//               lane quarter warp_id % 4); the first takes keys / output columns 0-31 of every tile, the second 32-63. Each
+//               thread reads its 32 scores with tcgen05.ld, the pair agrees on the tile's row max through shared memory and
+//               a 64-thread named barrier, and each keeps its own partial row sum and its 32 output accumulators in
+//               registers, writing its half of the P row (bf16) into the 128B-swizzled K-major tile of the second product.
+//               Half the registers and half the dependent chain per thread: twice the warps per scheduler hide the
+//               tcgen05.ld / MUFU / barrier latencies that bounded the one-thread-per-row form (52 % issue-active).
+//   warp 8    : TMA producer (lane 0): Q once, then K / V tiles into a two-stage ring (cp.async.bulk.tensor, SWIZZLE_128B).
+//   warp 9    : TMEM allocator + tcgen05.mma issuer (lane 0):  S = Q K^T  (M 128, N 64, K 64: both operands K-major)  and
 //               O_t = P V (M 128, N 64, K 64: V is read MN-major straight from its [key][head_dim] tile — no transpose).
-// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, so the tensor pipe, the TMA and the softmax
-// of neighbouring tiles overlap; several CTAs are resident per SM (64 KB of shared memory, 128 TMEM columns each).
+// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, and P / O_t are double-buffered (two P tiles in
+// shared memory, two O halves in TMEM), so the softmax of tile t+1 never waits for P(t) V: the chain per tile is
+// S ready -> exp -> P stored, with both products and the TMA off it; two CTAs per SM (82 KB of shared memory, 256 TMEM columns each).
 // Each tile's O_t is un-normalised with respect to that tile's running max m_t: the owning thread folds it into its
-// registers as acc = acc * 2^(m_{t-1} - m_t) + O_t, so no TMEM read-modify-write is needed.
+// registers one tile late as acc = acc * 2^(m_{t-1} - m_t) + O_t, so no TMEM read-modify-write is needed.
 // q/k/v come from ONE bf16 [B, S, 3C] buffer (the qkv projection's bf16 output) through one tensor map.
 #include <cuda.h>
 #include <cstdlib>
@@ -23,13 +28,15 @@
 namespace mft {
 
 constexpr int kTaBQ = 128, kTaBK = 64, kTaHD = 64;
-constexpr int kTaThreads = 192;
+constexpr int kTaThreads = 320;
+constexpr int kTaSoftmaxWarps = 8, kTaProducerWarp = 8, kTaMmaWarp = 9;
 constexpr int kTaTileBytes = kTaBK * kTaHD * 2;         // 8 KB: one K or V tile
 constexpr int kTaQBytes = kTaBQ * kTaHD * 2;            // 16 KB
-constexpr int kTaPBytes = kTaBQ * kTaBK * 2;            // 16 KB
+constexpr int kTaPBytes = kTaBQ * kTaBK * 2;            // 16 KB: one P tile (two of them: tile t+1 is written while P(t) V is read)
 constexpr int kTaStages = 2;
-constexpr int kTaSmem = kTaQBytes + kTaStages * 2 * kTaTileBytes + kTaPBytes + 1024 /*align*/ + 128 /*barriers*/;
-constexpr int kTaTmemCols = 128;                        // S: columns [0,64), O_t: [64,128)
+constexpr int kTaXchBytes = 2 * 2 * kTaBQ * 4;          // row-max exchange between the two threads of a row: [buffer][half][row]
+constexpr int kTaSmem = kTaQBytes + kTaStages * 2 * kTaTileBytes + 2 * kTaPBytes + 1024 /*align*/ + 128 /*barriers*/ + kTaXchBytes;
+constexpr int kTaTmemCols = 256;                        // S: columns [0,64); O_t: [64,128) for even t, [128,192) for odd t
 
 struct TaArgs {
     float* ctx; __nv_bfloat16* ctx16;
@@ -56,23 +63,34 @@ __device__ __forceinline__ float ex2_approx(float x) {          // one MUFU.EX2;
     return y;
 }
 
-__global__ void __launch_bounds__(kTaThreads)
+// named barrier 1 + q for the 64 threads (two warps) that share TMEM lane quarter q
+__device__ __forceinline__ void pair_sync(int q) {
+    switch (q) {
+        case 0: asm volatile("bar.sync 1, 64;" ::: "memory"); break;
+        case 1: asm volatile("bar.sync 2, 64;" ::: "memory"); break;
+        case 2: asm volatile("bar.sync 3, 64;" ::: "memory"); break;
+        default: asm volatile("bar.sync 4, 64;" ::: "memory"); break;
+    }
+}
+
+__global__ void __launch_bounds__(kTaThreads, 2)
 attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, int C) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = base;
     uint8_t* sK = sQ + kTaQBytes;                            // [stages][8 KB]
     uint8_t* sV = sK + kTaStages * kTaTileBytes;             // [stages][8 KB]
-    uint8_t* sP = sV + kTaStages * kTaTileBytes;             // 16 KB
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kTaPBytes);
+    uint8_t* sP = sV + kTaStages * kTaTileBytes;             // [2][16 KB]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kTaPBytes);
     uint64_t* bar_q = bars;                // Q landed
     uint64_t* bar_full = bars + 1;         // [2] K+V tile landed
     uint64_t* bar_empty = bars + 3;        // [2] tile consumed by both products
     uint64_t* bar_s = bars + 5;            // S ready in TMEM
     uint64_t* bar_sfree = bars + 6;        // every softmax thread has copied S out
-    uint64_t* bar_p = bars + 7;            // P written to shared memory (and O_t copied out)
-    uint64_t* bar_pv = bars + 8;           // O_t ready in TMEM
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+    uint64_t* bar_p = bars + 7;            // [2] P(t) written to shared memory buffer t & 1 (and O_{t-2} copied out of TMEM)
+    uint64_t* bar_pv = bars + 9;           // [2] O_t ready in TMEM buffer t & 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 128);      // [2][2][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qt = gridDim.x - 1 - blockIdx.x;       // heavy query tiles first
@@ -85,10 +103,11 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
     if (threadIdx.x == 0) {
         mbar_init(bar_q, 1);
         for (int i = 0; i < kTaStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-        mbar_init(bar_s, 1); mbar_init(bar_sfree, 4); mbar_init(bar_p, 4); mbar_init(bar_pv, 1);
+        mbar_init(bar_s, 1); mbar_init(bar_sfree, kTaSoftmaxWarps);
+        for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], kTaSoftmaxWarps); mbar_init(&bar_pv[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 5) {
+    if (warp == kTaMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(tmem_slot)), "r"(uint32_t(kTaTmemCols)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -97,7 +116,7 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 4) {
+    if (warp == kTaProducerWarp) {
         // ===================== TMA producer =====================
         if (lane == 0) {
             asm volatile("prefetch.tensormap [%0];" :: "l"(reinterpret_cast<uint64_t>(&map_qkv)) : "memory");
@@ -112,15 +131,14 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
                 tma_load_3d(sV + st * kTaTileBytes, &map_qkv, &bar_full[st], 2 * C + h * kTaHD, it * kTaBK, b);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kTaMmaWarp) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             // D = f32, A = B = bf16; S: both K-major, N = 64; O_t: A K-major (P), B MN-major (V), N = 64; M = 128
             constexpr uint32_t idesc_s = (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(kTaBK >> 3) << 17) | (uint32_t(kTaBQ >> 4) << 24);
             constexpr uint32_t idesc_o = idesc_s | (1u << 16);
-            const uint32_t tS = tmem_base, tO = tmem_base + 64;
+            const uint32_t tS = tmem_base;
             const uint64_t qdesc = make_kmajor_sw128_desc(smem_u32(sQ));
-            const uint64_t pdesc = make_kmajor_sw128_desc(smem_u32(sP));
             mbar_wait(bar_q, 0);
             mbar_wait(&bar_full[0], 0);
             tc_fence_after();
@@ -142,115 +160,124 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
                     for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
                     tc_commit(bar_s);
                 }
-                mbar_wait(bar_p, it & 1);            // P(it) is in shared memory, O_{it-1} has been copied out
+                mbar_wait(&bar_p[st], (it >> 1) & 1);   // P(it) is in its buffer, O_{it-2} has been copied out of the same TMEM half
                 tc_fence_after();
+                const uint32_t tO = tmem_base + 64 + uint32_t(st) * 64;
+                const uint64_t pdesc = make_kmajor_sw128_desc(smem_u32(sP + st * kTaPBytes));
                 const uint64_t vdesc = make_mnmajor_sw128_desc(smem_u32(sV + st * kTaTileBytes));
 #pragma unroll
                 for (int k = 0; k < kTaBK / 16; ++k)     // 16 keys per instruction: A advances 32 bytes, B advances 16 rows of 128 bytes
                     tc_mma_bf16(tO, pdesc + uint64_t(k * 2), vdesc + uint64_t(k * 128), idesc_o, k ? 1u : 0u);
                 tc_commit(&bar_empty[st]);           // K/V stage reusable once both products of this tile retire
-                tc_commit(bar_pv);
+                tc_commit(&bar_pv[st]);
             }
         }
     } else {
-        // ===================== softmax warps: thread = query row = TMEM lane =====================
-        const int row = threadIdx.x;                 // 0..127
+        // ===================== softmax warps: two threads per query row (= TMEM lane) =====================
+        const int wq = warp & 3, half = warp >> 2;   // lane quarter; key / output-column half
+        const int row = wq * 32 + lane;              // 0..127
         const int qi = q0 + row;
-        const uint32_t lane_addr = tmem_base + (uint32_t(warp * 32) << 16);
-        float acc[kTaHD];
+        const uint32_t lane_addr = tmem_base + (uint32_t(wq * 32) << 16);
+        float acc[32];
 #pragma unroll
-        for (int i = 0; i < kTaHD; ++i) acc[i] = 0.f;
-        float m_run = -INFINITY, l_run = 0.f;
-        uint8_t* prow = sP + row * 128;
+        for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+        float m_run = -INFINITY, l_run = 0.f;        // l_run: this thread's 32 keys of every tile only
+        float alpha_prev = 0.f;                      // 2^(m_{t-2} - m_{t-1}): applied when O_{t-1} is folded in, one tile late
+        const int lim0 = min(qi, S - 1) - half * 32; // last visible key of this row, relative to this thread's first column
         for (int it = 0; it < n_tiles; ++it) {
             const int key0 = it * kTaBK;
             mbar_wait(bar_s, it & 1);
             tc_fence_after();
-            float s[kTaBK];
-            {
-                float v[32];
-                tmem_ld32(lane_addr + 0, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) s[i] = v[i];
-                tmem_ld32(lane_addr + 32, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) s[32 + i] = v[i];
-            }
+            float s[32];
+            tmem_ld32(lane_addr + uint32_t(half * 32), s);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_sfree);   // the next S may overwrite TMEM columns [0,64)
             // causal mask and sequence tail by index, only on tiles that touch the diagonal or the end of the sequence
-            const bool need_mask = key0 + kTaBK - 1 > q0 || key0 + kTaBK > S;
-            if (need_mask) {
+            if (key0 + kTaBK - 1 > q0 || key0 + kTaBK > S) {
+                const int lim = lim0 - key0;
 #pragma unroll
-                for (int j = 0; j < kTaBK; ++j)
-                    if (key0 + j > qi || key0 + j >= S) s[j] = -INFINITY;
+                for (int j = 0; j < 32; ++j) s[j] = j > lim ? -INFINITY : s[j];
             }
             // the scale is positive, so the row max can be taken on the raw scores; the log2-domain shift then folds into one
             // FMA per element: p = 2^(s * c - m)
-            float mx = -INFINITY;
+            float mx0 = fmaxf(s[0], s[1]), mx1 = fmaxf(s[2], s[3]), mx2 = fmaxf(s[4], s[5]), mx3 = fmaxf(s[6], s[7]);
 #pragma unroll
-            for (int j = 0; j < kTaBK; ++j) mx = fmaxf(mx, s[j]);
+            for (int j = 8; j < 32; j += 8) {
+                mx0 = fmaxf(mx0, fmaxf(s[j], s[j + 1])); mx1 = fmaxf(mx1, fmaxf(s[j + 2], s[j + 3]));
+                mx2 = fmaxf(mx2, fmaxf(s[j + 4], s[j + 5])); mx3 = fmaxf(mx3, fmaxf(s[j + 6], s[j + 7]));
+            }
+            float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            float* xb = xch + (it & 1) * 2 * kTaBQ;  // double-buffered: the partner reads buffer t before it can pass barrier t+1
+            xb[half * kTaBQ + row] = mx;
+            pair_sync(wq);
+            mx = fmaxf(mx, xb[(half ^ 1) * kTaBQ + row]);
             const float m_new = fmaxf(m_run, mx * p.scale_log2);
             const float m_ref = m_new == -INFINITY ? 0.f : m_new;     // rows past the sequence end see only masked keys
             const float alpha = ex2_approx(m_run - m_ref);
-            float sum = 0.f;
-            uint32_t pk[kTaBK / 2];
+            float sum0 = 0.f, sum1 = 0.f;
+            uint32_t pk[16];
 #pragma unroll
-            for (int j = 0; j < kTaBK; j += 2) {
+            for (int j = 0; j < 32; j += 2) {
                 const float p0 = ex2_approx(fmaf(s[j], p.scale_log2, -m_ref)), p1 = ex2_approx(fmaf(s[j + 1], p.scale_log2, -m_ref));
-                sum += p0 + p1;
+                sum0 += p0; sum1 += p1;
                 const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
                 pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
             }
-            l_run = l_run * alpha + sum;
+            l_run = l_run * alpha + (sum0 + sum1);
             m_run = m_new;
-            if (it > 0) {                             // fold in O_{it-1} (relative to the previous max), then rescale
-                mbar_wait(bar_pv, (it - 1) & 1);
-                tc_fence_after();
-                float v[32];
-                tmem_ld32(lane_addr + 64, v);
+            // P row -> 128B-swizzled K-major tile (buffer it & 1: P(it-2) V has retired, see the fold below): 16-byte piece c of
+            // row r sits at r*128 + ((c ^ (r & 7)) << 4); this thread owns pieces 4 half .. 4 half + 3
+            uint8_t* prow = sP + (it & 1) * kTaPBytes + row * 128;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) acc[i] = (acc[i] + v[i]) * alpha;
-                tmem_ld32(lane_addr + 96, v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[32 + i] = (acc[32 + i] + v[i]) * alpha;
-            }
-            // P row -> 128B-swizzled K-major tile: 16-byte piece c of row r sits at r*128 + ((c ^ (r & 7)) << 4)
-#pragma unroll
-            for (int c = 0; c < 8; ++c)
-                *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<uint4*>(prow + (((half * 4 + c) ^ (row & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
             fence_proxy_async_smem();                 // generic-proxy writes visible to the tensor core's async proxy
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_p);
+            if (lane == 0) mbar_arrive(&bar_p[it & 1]);
+            // Off the critical path (P(it) V is already free to start): fold in this thread's 32 columns of O_{it-1}. With
+            // acc_k = sum of O_0..O_k relative to m_k:  acc_{it-1} = acc_{it-2} * 2^(m_{it-2} - m_{it-1}) + O_{it-1}  (one FMA).
+            // Waiting for P(it-1) V here also frees P buffer and TMEM half (it+1) & 1 for the next iteration.
+            if (it > 0) {
+                mbar_wait(&bar_pv[(it - 1) & 1], ((it - 1) >> 1) & 1);
+                tc_fence_after();
+                float v[32];
+                tmem_ld32(lane_addr + 64 + uint32_t(((it - 1) & 1) * 64 + half * 32), v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = fmaf(acc[i], alpha_prev, v[i]);
+                tc_fence_before();
+            }
+            alpha_prev = alpha;
         }
-        mbar_wait(bar_pv, (n_tiles - 1) & 1);
+        mbar_wait(&bar_pv[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1);
         tc_fence_after();
         {
             float v[32];
-            tmem_ld32(lane_addr + 64, v);
+            tmem_ld32(lane_addr + 64 + uint32_t(((n_tiles - 1) & 1) * 64 + half * 32), v);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) acc[i] += v[i];
-            tmem_ld32(lane_addr + 96, v);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) acc[32 + i] += v[i];
+            for (int i = 0; i < 32; ++i) acc[i] = fmaf(acc[i], alpha_prev, v[i]);
         }
-        const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
-        // every product has retired: the K/V/P region is free and stages this warp's 32 output rows for coalesced stores
-        float* stage = reinterpret_cast<float*>(sK) + warp * 32 * 68;        // 32 rows x 68 floats per warp (fits K+V+P = 48 KB)
+        // row sum = the two threads' partial sums (both are relative to the same running max)
+        float* xb = xch + (n_tiles & 1) * 2 * kTaBQ;
+        xb[half * kTaBQ + row] = l_run;
+        pair_sync(wq);
+        const float l_row = l_run + xb[(half ^ 1) * kTaBQ + row];
+        const float inv = l_row > 0.f ? 1.0f / l_row : 0.f;
+        // every product has retired: the K/V/P region is free and stages this warp's 32 rows x 32 columns for coalesced stores
+        float* stage = reinterpret_cast<float*>(sK) + warp * 32 * 36;        // 36 floats per row; 8 warps x 4.5 KB (fits K+V+P = 64 KB)
 #pragma unroll
-        for (int c = 0; c < 16; ++c)
-            *reinterpret_cast<float4*>(stage + lane * 68 + c * 4) = make_float4(acc[4 * c] * inv, acc[4 * c + 1] * inv, acc[4 * c + 2] * inv, acc[4 * c + 3] * inv);
+        for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<float4*>(stage + lane * 36 + c * 4) = make_float4(acc[4 * c] * inv, acc[4 * c + 1] * inv, acc[4 * c + 2] * inv, acc[4 * c + 3] * inv);
         __syncwarp();
-        const int half = lane >> 4, c4 = lane & 15;   // two rows per instruction, 16 lanes x float4 per row
-        float* ob = p.ctx ? p.ctx + int64_t(b) * p.osb + h * kTaHD : nullptr;
-        __nv_bfloat16* ob16 = p.ctx16 ? p.ctx16 + int64_t(b) * p.osb + h * kTaHD : nullptr;
+        const int sub = lane >> 3, c4 = lane & 7;     // four rows per instruction, 8 lanes x float4 per row (128 bytes)
+        float* ob = p.ctx ? p.ctx + int64_t(b) * p.osb + h * kTaHD + half * 32 : nullptr;
+        __nv_bfloat16* ob16 = p.ctx16 ? p.ctx16 + int64_t(b) * p.osb + h * kTaHD + half * 32 : nullptr;
 #pragma unroll 4
-        for (int r = 0; r < 32; r += 2) {
-            const int lr = r + half, gr = q0 + warp * 32 + lr;
+        for (int r = 0; r < 32; r += 4) {
+            const int lr = r + sub, gr = q0 + wq * 32 + lr;
             if (gr >= S) continue;
-            const float4 o4 = *reinterpret_cast<const float4*>(stage + lr * 68 + c4 * 4);
+            const float4 o4 = *reinterpret_cast<const float4*>(stage + lr * 36 + c4 * 4);
             if (ob) *reinterpret_cast<float4*>(ob + int64_t(gr) * p.oss + c4 * 4) = o4;
             if (ob16) st_bf16x4(ob16 + int64_t(gr) * p.oss + c4 * 4, o4);
         }
@@ -258,7 +285,7 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) {
+    if (warp == kTaMmaWarp) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(uint32_t(kTaTmemCols)) : "memory");
     }

@@ -183,41 +183,72 @@ __global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __rest
 // gx = gy * gelu'(x) with gy and gx as bf16 (the gradient arrives from a bf16-only GEMM result and feeds a bf16 GEMM
 // operand): x is read as fp32 (XBF16 = false: 4 B) or as the bf16 pre-activation (XBF16 = true: 2 B), plus 2 B read and 2 B
 // written per element. gx32 != NULL additionally writes the fp32 gradient. n % 8 == 0, 16-byte aligned.
+// gelu'(x) with the hardware tanh (MUFU.TANH, relative error ~2^-11): only where the result is rounded to bf16 anyway
+__device__ __forceinline__ float gelu_tanh_grad_fast(float x) {
+    const float k0 = 0.7978845608f, k1 = 0.044715f;
+    const float x2 = x * x;
+    float t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(k0 * fmaf(k1 * x, x2, x)));
+    const float dinner = k0 * fmaf(3.0f * k1, x2, 1.0f);
+    return fmaf(0.5f * x * fmaf(-t, t, 1.0f), dinner, fmaf(0.5f, t, 0.5f));
+}
+
 template <bool XBF16>
-__global__ void gelu_bwd_lowp_kernel(const void* __restrict__ xv, const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx32,
-                                     __nv_bfloat16* __restrict__ gx16, int64_t n) {
-    const int64_t n8 = n >> 3;
+__device__ __forceinline__ void gelu_bwd_lowp_load(const void* xv, const uint4* g8, int64_t i, float (&xs)[8], uint4& gr) {
+    if (XBF16) {
+        const uint4 xr = __ldcs(reinterpret_cast<const uint4*>(xv) + i);
+        const __nv_bfloat162* xp = reinterpret_cast<const __nv_bfloat162*>(&xr);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(xp[e]); xs[2 * e] = f.x; xs[2 * e + 1] = f.y; }
+    } else {
+        const float4 a = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i), b = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i + 1);
+        xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
+    }
+    gr = __ldcs(g8 + i);
+}
+template <bool FAST>      // FAST: bf16 is the only result (the fp32 copy, when asked for, keeps the exact tanhf)
+__device__ __forceinline__ void gelu_bwd_lowp_store(const float (&xs)[8], const uint4& gr, float* gx32, uint4* o8, int64_t i) {
+    const __nv_bfloat162* gp = reinterpret_cast<const __nv_bfloat162*>(&gr);
+    float r[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const float2 g = __bfloat1622float2(gp[e]);
+        r[2 * e] = g.x * (FAST ? gelu_tanh_grad_fast(xs[2 * e]) : gelu_tanh_grad_f(xs[2 * e]));
+        r[2 * e + 1] = g.y * (FAST ? gelu_tanh_grad_fast(xs[2 * e + 1]) : gelu_tanh_grad_f(xs[2 * e + 1]));
+    }
+    uint4 out;
+    __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&out);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) op[e] = __floats2bfloat162_rn(r[2 * e], r[2 * e + 1]);
+    __stcs(o8 + i, out);
+    if (!FAST && gx32) {
+        st_stream(reinterpret_cast<float4*>(gx32) + 2 * i, make_float4(r[0], r[1], r[2], r[3]));
+        st_stream(reinterpret_cast<float4*>(gx32) + 2 * i + 1, make_float4(r[4], r[5], r[6], r[7]));
+    }
+}
+
+// Two 8-element groups per thread and iteration: both groups' loads are issued before either is used (bytes in flight).
+template <bool XBF16, bool FAST>
+__global__ void __launch_bounds__(256)
+gelu_bwd_lowp_kernel(const void* __restrict__ xv, const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx32,
+                     __nv_bfloat16* __restrict__ gx16, int64_t n) {
+    const int64_t n8 = n >> 3, stride = int64_t(gridDim.x) * blockDim.x;
     const uint4* g8 = reinterpret_cast<const uint4*>(gy);
     uint4* o8 = reinterpret_cast<uint4*>(gx16);
-    for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n8; i += int64_t(gridDim.x) * blockDim.x) {
-        float xs[8];
-        if (XBF16) {
-            const uint4 xr = __ldcs(reinterpret_cast<const uint4*>(xv) + i);
-            const __nv_bfloat162* xp = reinterpret_cast<const __nv_bfloat162*>(&xr);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) { const float2 f = __bfloat1622float2(xp[e]); xs[2 * e] = f.x; xs[2 * e + 1] = f.y; }
-        } else {
-            const float4 a = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i), b = ld_stream(reinterpret_cast<const float4*>(xv) + 2 * i + 1);
-            xs[0] = a.x; xs[1] = a.y; xs[2] = a.z; xs[3] = a.w; xs[4] = b.x; xs[5] = b.y; xs[6] = b.z; xs[7] = b.w;
-        }
-        const uint4 gr = __ldcs(g8 + i);
-        const __nv_bfloat162* gp = reinterpret_cast<const __nv_bfloat162*>(&gr);
-        float r[8];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const float2 g = __bfloat1622float2(gp[e]);
-            r[2 * e] = g.x * gelu_tanh_grad_f(xs[2 * e]);
-            r[2 * e + 1] = g.y * gelu_tanh_grad_f(xs[2 * e + 1]);
-        }
-        uint4 out;
-        __nv_bfloat162* op = reinterpret_cast<__nv_bfloat162*>(&out);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) op[e] = __floats2bfloat162_rn(r[2 * e], r[2 * e + 1]);
-        __stcs(o8 + i, out);
-        if (gx32) {
-            st_stream(reinterpret_cast<float4*>(gx32) + 2 * i, make_float4(r[0], r[1], r[2], r[3]));
-            st_stream(reinterpret_cast<float4*>(gx32) + 2 * i + 1, make_float4(r[4], r[5], r[6], r[7]));
-        }
+    int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+    for (; i + stride < n8; i += 2 * stride) {
+        float xa[8], xb[8];
+        uint4 ga, gb;
+        gelu_bwd_lowp_load<XBF16>(xv, g8, i, xa, ga);
+        gelu_bwd_lowp_load<XBF16>(xv, g8, i + stride, xb, gb);
+        gelu_bwd_lowp_store<FAST>(xa, ga, gx32, o8, i);
+        gelu_bwd_lowp_store<FAST>(xb, gb, gx32, o8, i + stride);
+    }
+    if (i < n8) {
+        float xa[8];
+        uint4 ga;
+        gelu_bwd_lowp_load<XBF16>(xv, g8, i, xa, ga);
+        gelu_bwd_lowp_store<FAST>(xa, ga, gx32, o8, i);
     }
 }
 
@@ -411,9 +442,13 @@ extern "C" int mft_gelu_bwd_lowp(const void* x, int x_is_bf16, const void* gy_bf
     if (!x || !gy_bf16 || !gx_bf16) return set_error(1, "mft_gelu_bwd_lowp: null pointer");
     if ((n & 7) || !aligned16(x) || !aligned16(gy_bf16) || !aligned16(gx_bf16) || (gx && !aligned16(gx)))
         return set_error(1, "mft_gelu_bwd_lowp: n must be a multiple of 8 and every pointer 16-byte aligned");
-    const int grid = stream_grid(n, 256, 8);
-    if (x_is_bf16) gelu_bwd_lowp_kernel<true><<<grid, 256, 0, as_stream(stream)>>>(x, static_cast<const __nv_bfloat16*>(gy_bf16), gx, static_cast<__nv_bfloat16*>(gx_bf16), n);
-    else gelu_bwd_lowp_kernel<false><<<grid, 256, 0, as_stream(stream)>>>(x, static_cast<const __nv_bfloat16*>(gy_bf16), gx, static_cast<__nv_bfloat16*>(gx_bf16), n);
+    const int grid = stream_grid(n, 256, 16);
+    const void* gyp = gy_bf16;
+    auto* g16 = static_cast<const __nv_bfloat16*>(gyp);
+    auto* o16 = static_cast<__nv_bfloat16*>(gx_bf16);
+    cudaStream_t st = as_stream(stream);
+    if (x_is_bf16) { if (gx) gelu_bwd_lowp_kernel<true, false><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); else gelu_bwd_lowp_kernel<true, true><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); }
+    else { if (gx) gelu_bwd_lowp_kernel<false, false><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); else gelu_bwd_lowp_kernel<false, true><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); }
     MFT_CHECK_LAUNCH("mft_gelu_bwd_lowp");
     return 0;
 }

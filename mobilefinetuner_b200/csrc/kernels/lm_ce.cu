@@ -6,6 +6,13 @@
 
 namespace mft {
 
+__device__ __forceinline__ float exp2f_approx(float x) {          // one MUFU.EX2
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+
 constexpr int kCeThreads = 512;
 
 __device__ __forceinline__ int ce_label(const int32_t* labels, int64_t row, int S, int V, int ignore_index) {
@@ -86,6 +93,28 @@ lm_ce_reduce_kernel(const double* __restrict__ row_nll, const int32_t* __restric
     }
 }
 
+// softmax(x) * scale for four logits; FAST (the gradient leaves as bf16 only): one ex2.approx per element
+template <bool FAST>
+__device__ __forceinline__ float4 ce_grad4(float4 a, float lse, float lse_log2, float scale) {
+    float4 r;
+    if (FAST) {
+        const float c = 1.4426950408889634f;
+        r.x = exp2f_approx(fmaf(a.x, c, -lse_log2)) * scale; r.y = exp2f_approx(fmaf(a.y, c, -lse_log2)) * scale;
+        r.z = exp2f_approx(fmaf(a.z, c, -lse_log2)) * scale; r.w = exp2f_approx(fmaf(a.w, c, -lse_log2)) * scale;
+    } else {
+        r.x = expf(a.x - lse) * scale; r.y = expf(a.y - lse) * scale;
+        r.z = expf(a.z - lse) * scale; r.w = expf(a.w - lse) * scale;
+    }
+    return r;
+}
+__device__ __forceinline__ void ce_fix_label(float4& r, int base, int y, float scale) {
+    if (y >= base && y < base + 4) {
+        if (y == base) r.x -= scale; else if (y == base + 1) r.y -= scale;
+        else if (y == base + 2) r.z -= scale; else r.w -= scale;
+    }
+}
+
+template <bool FAST>
 __global__ void __launch_bounds__(kCeThreads)
 lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels,
                  const float* __restrict__ row_lse, const int32_t* __restrict__ valid, const float* __restrict__ gout,
@@ -114,28 +143,36 @@ lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __
             continue;
         }
         const float* x = logits + row * ld;
-        const float lse = row_lse[row];
+        const float lse = row_lse[row], lse_log2 = lse * 1.4426950408889634f;
         if (vec) {
             const float4* x4 = reinterpret_cast<const float4*>(x);
             float4* d4 = reinterpret_cast<float4*>(d);
             const int v4 = V >> 2;
-            for (int i = threadIdx.x; i < v4; i += kCeThreads) {
-                float4 a = ld_stream(x4 + i), r;
-                r.x = expf(a.x - lse) * scale; r.y = expf(a.y - lse) * scale;
-                r.z = expf(a.z - lse) * scale; r.w = expf(a.w - lse) * scale;
-                const int base = i << 2;
-                if (y >= base && y < base + 4) {
-                    if (y == base) r.x -= scale; else if (y == base + 1) r.y -= scale;
-                    else if (y == base + 2) r.z -= scale; else r.w -= scale;
+            int i = threadIdx.x;
+            for (; i + 3 * kCeThreads < v4; i += 4 * kCeThreads) {      // four independent 16-byte loads in flight per thread
+                float4 a[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) a[u] = ld_stream(x4 + i + u * kCeThreads);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int iu = i + u * kCeThreads;
+                    float4 r = ce_grad4<FAST>(a[u], lse, lse_log2, scale);
+                    ce_fix_label(r, iu << 2, y, scale);
+                    if (d) st_stream(d4 + iu, r);
+                    if (h) st_bf16x4(h + iu * 4, r);
                 }
+            }
+            for (; i < v4; i += kCeThreads) {
+                float4 r = ce_grad4<FAST>(ld_stream(x4 + i), lse, lse_log2, scale);
+                ce_fix_label(r, i << 2, y, scale);
                 if (d) st_stream(d4 + i, r);
                 if (h) st_bf16x4(h + i * 4, r);
             }
-            for (int i = (v4 << 2) + threadIdx.x; i < V; i += kCeThreads) {
-                float r = expf(x[i] - lse) * scale;
-                if (i == y) r -= scale;
-                if (d) d[i] = r;
-                if (h) h[i] = __float2bfloat16_rn(r);
+            for (int j = (v4 << 2) + threadIdx.x; j < V; j += kCeThreads) {
+                float r = expf(x[j] - lse) * scale;
+                if (j == y) r -= scale;
+                if (d) d[j] = r;
+                if (h) h[j] = __float2bfloat16_rn(r);
             }
         } else {
             for (int i = threadIdx.x; i < V; i += kCeThreads) {
@@ -186,9 +223,9 @@ static int ce_bwd_impl(const float* logits, int64_t ld, const int32_t* labels, c
     const bool fused16 = d16 && vec && (ld16 & 3) == 0 && (reinterpret_cast<uintptr_t>(d16) & 7u) == 0;
     if (!dlogits && !fused16) return set_error(1, "mft_lm_ce_bwd_ex: a bf16-only gradient needs 16-byte aligned logits with a pitch %% 4 == 0 and an 8-byte aligned bf16 buffer with a pitch %% 4 == 0");
     int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
-    lm_ce_bwd_kernel<<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V,
-                                                                ignore_index, reduction, dlogits, ldg,
-                                                                fused16 ? static_cast<__nv_bfloat16*>(d16) : nullptr, ld16);
+    __nv_bfloat16* h16 = fused16 ? static_cast<__nv_bfloat16*>(d16) : nullptr;
+    if (!dlogits) lm_ce_bwd_kernel<true><<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
+    else lm_ce_bwd_kernel<false><<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
     MFT_CHECK_LAUNCH("mft_lm_ce_bwd");
     if (d16 && !fused16) return mft_cast_bf16(dlogits, ldg, d16, ld16, rows, V, stream);
     return 0;

@@ -563,4 +563,7 @@ def test_lowp_elementwise_kernels(capi):
     g32, g16a, g16b = torch.empty(B * S, V, device="cuda"), torch.empty(B * S, V, device="cuda", dtype=torch.bfloat16), torch.empty(B * S, V, device="cuda", dtype=torch.bfloat16)
     capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, g32, V, g16a, V, None)
     capi.call("mft_lm_ce_bwd_ex", dl, V, dlab, lse, valid, None, B, S, V, -100, 0, None, 0, g16b, V, None)
-    assert torch.equal(g16a, g16b) and torch.equal(g16a, g32.to(torch.bfloat16))
+    assert torch.equal(g16a, g32.to(torch.bfloat16))
+    # the bf16-only form evaluates exp with one ex2.approx (2 ulp in fp32): at most one bf16 step away from the rounded fp32 result
+    a, b = g16a.float(), g16b.float()
+    assert bool(((a - b).abs() <= a.abs() * 2.0 ** -7 + 1e-30).all())

@@ -112,10 +112,11 @@ def bench_step_forms(iters=20, T=4096):
         a = torch.randn(m, k, device="cuda").bfloat16()
         b = (torch.randn(n, k, device="cuda") * 0.05).bfloat16()
         bias = torch.randn(n, device="cuda")
-        c32 = torch.empty(m, n, device="cuda") if form == "f32" else None
+        ldc = n if n % 4 == 0 else (n + 31) // 32 * 32          # the host mirror pads wide odd rows the same way (ops.cpp out_ld)
+        c32 = torch.empty(m, ldc, device="cuda") if form == "f32" else None
         c16 = torch.empty(m, n, device="cuda", dtype=torch.bfloat16) if form != "f32" else None
         g16 = torch.empty(m, n, device="cuda", dtype=torch.bfloat16) if form == "gelu16" else None
-        args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c32.data_ptr() if c32 is not None else None, n, 1.0, 0.0, bias.data_ptr(), None,
+        args = capi.GemmArgs(m, n, k, a.data_ptr(), k, 0, b.data_ptr(), k, 1, c32.data_ptr() if c32 is not None else None, ldc, 1.0, 0.0, bias.data_ptr(), None,
                              0, None, 0, None, 0, 1, 0, 0, 0, None, 0, None, 0, g16.data_ptr() if g16 is not None else None, n,
                              c16.data_ptr() if c16 is not None else None, n)
         for _ in range(3):

@@ -16,10 +16,13 @@ for s in "$@"; do
       timeout 300 python tools/profile_step.py --config c4 > $out/${tag}_prof_c4.log 2>&1 &&
       timeout 900 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c4_metrics.csv python tools/profile_step.py --config c4 > $out/${tag}_ncu_c4.log 2>&1
       python tools/ncu_summary.py $out/${tag}_c4_metrics.csv > $out/${tag}_c4_kernels.txt 2>&1; head -24 $out/${tag}_c4_kernels.txt ;;
-    ncu_c4_b64)
+    ncu_c4_b64)   # 64 x 512 tokens: multi-pass metrics would save / restore ~70 GB per replayed launch, so one pass per run
       timeout 300 python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_prof_c4_b64.log 2>&1 &&
-      timeout 1200 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c4_b64_metrics.csv python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_ncu_c4_b64.log 2>&1
-      python tools/ncu_summary.py $out/${tag}_c4_b64_metrics.csv > $out/${tag}_c4_b64_kernels.txt 2>&1; head -24 $out/${tag}_c4_b64_kernels.txt ;;
+      timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv --log-file $out/${tag}_c4_b64_time.csv python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_ncu_c4_b64.log 2>&1
+      python tools/ncu_summary.py $out/${tag}_c4_b64_time.csv > $out/${tag}_c4_b64_kernels.txt 2>&1; head -24 $out/${tag}_c4_b64_kernels.txt ;;
+    ncu_c4_b64_dram)
+      timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv --log-file $out/${tag}_c4_b64_dram.csv python tools/profile_step.py --config c4 --batch 64 > $out/${tag}_ncu_c4_b64_dram.log 2>&1
+      python tools/ncu_summary.py $out/${tag}_c4_b64_dram.csv > $out/${tag}_c4_b64_dram_kernels.txt 2>&1; head -24 $out/${tag}_c4_b64_dram_kernels.txt ;;
     ncu_c3)
       timeout 300 python tools/profile_step.py --config c3 > $out/${tag}_prof_c3.log 2>&1 &&
       timeout 900 ncu --profile-from-start off --metrics $M --clock-control none --csv --log-file $out/${tag}_c3_metrics.csv python tools/profile_step.py --config c3 > $out/${tag}_ncu_c3.log 2>&1
@@ -34,6 +37,10 @@ for s in "$@"; do
       MFT_DP_OVERLAP=0 timeout 600 $TR bench.py --config c2 --gpus $n --steps 20 --warmup 5 > $out/${tag}_c2_n${n}_nooverlap.log 2>&1; tail -1 $out/${tag}_c2_n${n}_nooverlap.log | cut -c1-160
       timeout 600 $TR bench.py --gpus $n --steps 10 --warmup 3 > $out/${tag}_c4_strong_n$n.log 2>&1; tail -1 $out/${tag}_c4_strong_n$n.log | cut -c1-160
       timeout 600 $TR bench.py --gpus $n --scaling weak --steps 20 --warmup 5 > $out/${tag}_c4_weak_n$n.log 2>&1; tail -1 $out/${tag}_c4_weak_n$n.log | cut -c1-160 ;;
+    ncu_full_gqa)
+      timeout 900 ncu --profile-from-start off --set full --import-source on --clock-control none -k regex:"gqa_fwd|gqa_bwd_dq|gqa_bwd_dkv" -c 3 -o $out/${tag}_gqa_full python tools/profile_step.py --config c3 > $out/${tag}_ncu_full_gqa.log 2>&1; ls -la $out/${tag}_gqa_full.ncu-rep ;;
+    ncu_full_attn)
+      timeout 900 ncu --profile-from-start off --set full --import-source on --clock-control none -k regex:"attention_tc_fwd" -c 2 -o $out/${tag}_attn_full python tools/profile_step.py --config c4 > $out/${tag}_ncu_full_attn.log 2>&1; ls -la $out/${tag}_attn_full.ncu-rep ;;
     gemm_step) timeout 300 python tools/gemm_bench.py step > $out/${tag}_gemm_step.log 2>&1; tail -12 $out/${tag}_gemm_step.log ;;
     gemm_step64)
       timeout 300 python tools/gemm_bench.py step 32768 > $out/${tag}_gemm_step64.log 2>&1; tail -12 $out/${tag}_gemm_step64.log
