@@ -12,11 +12,12 @@
 //   warp 8    : TMA producer (lane 0): Q once, then K / V tiles into a two-stage ring (cp.async.bulk.tensor, SWIZZLE_128B).
 //   warp 9    : TMEM allocator + tcgen05.mma issuer (lane 0):  S = Q K^T  (M 128, N 64, K 64: both operands K-major)  and
 //               O_t = P V (M 128, N 64, K 64: V is read MN-major straight from its [key][head_dim] tile — no transpose).
-// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, and P / O_t are double-buffered (two P tiles in
-// shared memory, two O halves in TMEM), so the softmax of tile t+1 never waits for P(t) V: the chain per tile is
-// S ready -> exp -> P stored, with both products and the TMA off it; two CTAs per SM (82 KB of shared memory, 256 TMEM columns each).
-// Each tile's O_t is un-normalised with respect to that tile's running max m_t: the owning thread folds it into its
-// registers one tile late as acc = acc * 2^(m_{t-1} - m_t) + O_t, so no TMEM read-modify-write is needed.
+// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, and P is double-buffered in shared memory, so the
+// softmax of tile t+1 never waits for P(t) V: the chain per tile is S ready -> exp -> P stored, with both products and the TMA off
+// it; two CTAs per SM (82 KB of shared memory, 128 TMEM columns each).
+// O accumulates in TMEM over all key tiles (the tensor core adds P(t) V to it) and is read once, at the end: TMEM reads run at
+// 64 B/clk per SM, and copying O out every tile doubled them. It is scaled by a max that follows the running row max lazily
+// (see kTaRescaleStep); the rare rescale is a TMEM load / multiply / store by the owning threads between two products.
 // q/k/v come from ONE bf16 [B, S, 3C] buffer (the qkv projection's bf16 output) through one tensor map.
 #include <cuda.h>
 #include <cstdlib>
@@ -36,7 +37,8 @@ constexpr int kTaPBytes = kTaBQ * kTaBK * 2;            // 16 KB: one P tile (tw
 constexpr int kTaStages = 2;
 constexpr int kTaXchBytes = 2 * 2 * kTaBQ * 4;          // row-max exchange between the two threads of a row: [buffer][half][row]
 constexpr int kTaSmem = kTaQBytes + kTaStages * 2 * kTaTileBytes + 2 * kTaPBytes + 1024 /*align*/ + 128 /*barriers*/ + kTaXchBytes;
-constexpr int kTaTmemCols = 256;                        // S: columns [0,64); O_t: [64,128) for even t, [128,192) for odd t
+constexpr int kTaTmemCols = 128;                        // S: columns [0,64); O (accumulated over the key tiles): [64,128)
+constexpr float kTaRescaleStep = 8.0f;                  // log2 units the row max may run ahead of the scaling max before O is rescaled
 
 struct TaArgs {
     float* ctx; __nv_bfloat16* ctx16;
@@ -160,14 +162,14 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
                     for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
                     tc_commit(bar_s);
                 }
-                mbar_wait(&bar_p[st], (it >> 1) & 1);   // P(it) is in its buffer, O_{it-2} has been copied out of the same TMEM half
+                mbar_wait(&bar_p[st], (it >> 1) & 1);   // P(it) is in its buffer (and O has been rescaled if this tile asked for it)
                 tc_fence_after();
-                const uint32_t tO = tmem_base + 64 + uint32_t(st) * 64;
+                const uint32_t tO = tmem_base + 64;
                 const uint64_t pdesc = make_kmajor_sw128_desc(smem_u32(sP + st * kTaPBytes));
                 const uint64_t vdesc = make_mnmajor_sw128_desc(smem_u32(sV + st * kTaTileBytes));
 #pragma unroll
                 for (int k = 0; k < kTaBK / 16; ++k)     // 16 keys per instruction: A advances 32 bytes, B advances 16 rows of 128 bytes
-                    tc_mma_bf16(tO, pdesc + uint64_t(k * 2), vdesc + uint64_t(k * 128), idesc_o, k ? 1u : 0u);
+                    tc_mma_bf16(tO, pdesc + uint64_t(k * 2), vdesc + uint64_t(k * 128), idesc_o, (it | k) ? 1u : 0u);   // O accumulates over the tiles
                 tc_commit(&bar_empty[st]);           // K/V stage reusable once both products of this tile retire
                 tc_commit(&bar_pv[st]);
             }
@@ -178,12 +180,9 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
         const int row = wq * 32 + lane;              // 0..127
         const int qi = q0 + row;
         const uint32_t lane_addr = tmem_base + (uint32_t(wq * 32) << 16);
-        float acc[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc[i] = 0.f;
-        float m_run = -INFINITY, l_run = 0.f;        // l_run: this thread's 32 keys of every tile only
-        float alpha_prev = 0.f;                      // 2^(m_{t-2} - m_{t-1}): applied when O_{t-1} is folded in, one tile late
+        float m_use = 0.f, l_run = 0.f;              // scaling max of this row (log2 domain); l_run: this thread's 32 keys of every tile only
         const int lim0 = min(qi, S - 1) - half * 32; // last visible key of this row, relative to this thread's first column
+        const uint32_t o_addr = lane_addr + 64 + uint32_t(half * 32);    // this thread's 32 columns of O
         for (int it = 0; it < n_tiles; ++it) {
             const int key0 = it * kTaBK;
             mbar_wait(bar_s, it & 1);
@@ -212,22 +211,39 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
             xb[half * kTaBQ + row] = mx;
             pair_sync(wq);
             mx = fmaxf(mx, xb[(half ^ 1) * kTaBQ + row]);
-            const float m_new = fmaxf(m_run, mx * p.scale_log2);
-            const float m_ref = m_new == -INFINITY ? 0.f : m_new;     // rows past the sequence end see only masked keys
-            const float alpha = ex2_approx(m_run - m_ref);
+            const float m_tile = mx * p.scale_log2;  // -inf: every key of this tile is masked for the row (rows past the sequence end)
+            // O accumulates in TMEM over the tiles, scaled by 2^-m_use. m_use follows the running max lazily: P stays below
+            // 2^kTaRescaleStep (exact in bf16 / fp32 at any scale), and O and the row sum are rescaled only when a row's max has
+            // run ahead by more than that step, which after the first tiles is rare. The first tile sets m_use (O is overwritten).
+            if (it == 0) {
+                m_use = m_tile == -INFINITY ? 0.f : m_tile;
+            } else if (__any_sync(0xffffffffu, m_tile > m_use + kTaRescaleStep)) {      // both warps of a row group vote alike
+                const float m_new = fmaxf(m_use, m_tile);
+                const float f = ex2_approx(m_use - m_new);
+                m_use = m_new;
+                l_run *= f;
+                mbar_wait(&bar_pv[(it - 1) & 1], ((it - 1) >> 1) & 1);      // every P V issued so far has retired
+                tc_fence_after();
+                float v[32];
+                tmem_ld32(o_addr, v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] *= f;
+                tmem_st32(o_addr, v);
+                tc_fence_before();
+            }
             float sum0 = 0.f, sum1 = 0.f;
             uint32_t pk[16];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-                const float p0 = ex2_approx(fmaf(s[j], p.scale_log2, -m_ref)), p1 = ex2_approx(fmaf(s[j + 1], p.scale_log2, -m_ref));
+                const float p0 = ex2_approx(fmaf(s[j], p.scale_log2, -m_use)), p1 = ex2_approx(fmaf(s[j + 1], p.scale_log2, -m_use));
                 sum0 += p0; sum1 += p1;
                 const __nv_bfloat162 h2 = __floats2bfloat162_rn(p0, p1);
                 pk[j >> 1] = *reinterpret_cast<const uint32_t*>(&h2);
             }
-            l_run = l_run * alpha + (sum0 + sum1);
-            m_run = m_new;
-            // P row -> 128B-swizzled K-major tile (buffer it & 1: P(it-2) V has retired, see the fold below): 16-byte piece c of
-            // row r sits at r*128 + ((c ^ (r & 7)) << 4); this thread owns pieces 4 half .. 4 half + 3
+            l_run += sum0 + sum1;
+            // P row -> 128B-swizzled K-major tile, buffer it & 1 (free once P(it-2) V has retired): 16-byte piece c of row r sits at
+            // r*128 + ((c ^ (r & 7)) << 4); this thread owns pieces 4 half .. 4 half + 3
+            if (it >= 2) mbar_wait(&bar_pv[it & 1], ((it - 2) >> 1) & 1);
             uint8_t* prow = sP + (it & 1) * kTaPBytes + row * 128;
 #pragma unroll
             for (int c = 0; c < 4; ++c)
@@ -236,28 +252,11 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&bar_p[it & 1]);
-            // Off the critical path (P(it) V is already free to start): fold in this thread's 32 columns of O_{it-1}. With
-            // acc_k = sum of O_0..O_k relative to m_k:  acc_{it-1} = acc_{it-2} * 2^(m_{it-2} - m_{it-1}) + O_{it-1}  (one FMA).
-            // Waiting for P(it-1) V here also frees P buffer and TMEM half (it+1) & 1 for the next iteration.
-            if (it > 0) {
-                mbar_wait(&bar_pv[(it - 1) & 1], ((it - 1) >> 1) & 1);
-                tc_fence_after();
-                float v[32];
-                tmem_ld32(lane_addr + 64 + uint32_t(((it - 1) & 1) * 64 + half * 32), v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) acc[i] = fmaf(acc[i], alpha_prev, v[i]);
-                tc_fence_before();
-            }
-            alpha_prev = alpha;
         }
         mbar_wait(&bar_pv[(n_tiles - 1) & 1], ((n_tiles - 1) >> 1) & 1);
         tc_fence_after();
-        {
-            float v[32];
-            tmem_ld32(lane_addr + 64 + uint32_t(((n_tiles - 1) & 1) * 64 + half * 32), v);
-#pragma unroll
-            for (int i = 0; i < 32; ++i) acc[i] = fmaf(acc[i], alpha_prev, v[i]);
-        }
+        float acc[32];
+        tmem_ld32(o_addr, acc);
         // row sum = the two threads' partial sums (both are relative to the same running max)
         float* xb = xch + (n_tiles & 1) * 2 * kTaBQ;
         xb[half * kTaBQ + row] = l_run;
