@@ -9,12 +9,13 @@
 //               registers, writing its half of the P row (bf16) into the 128B-swizzled K-major tile of the second product.
 //               Half the registers and half the dependent chain per thread: twice the warps per scheduler hide the
 //               tcgen05.ld / MUFU / barrier latencies that bounded the one-thread-per-row form (52 % issue-active).
-//   warp 8    : TMA producer (lane 0): Q once, then K / V tiles into a two-stage ring (cp.async.bulk.tensor, SWIZZLE_128B).
+//   warp 8    : TMA producer (lane 0): Q once, then K and V tiles into their two-stage rings (cp.async.bulk.tensor, SWIZZLE_128B).
 //   warp 9    : TMEM allocator + tcgen05.mma issuer (lane 0):  S = Q K^T  (M 128, N 64, K 64: both operands K-major)  and
 //               O_t = P V (M 128, N 64, K 64: V is read MN-major straight from its [key][head_dim] tile — no transpose).
-// S(t+1) is issued as soon as every softmax thread has copied S(t) out of TMEM, and P is double-buffered in shared memory, so the
-// softmax of tile t+1 never waits for P(t) V: the chain per tile is S ready -> exp -> P stored, with both products and the TMA off
-// it; two CTAs per SM (82 KB of shared memory, 128 TMEM columns each).
+// The score product runs two tiles ahead of the softmax (S is double-buffered in TMEM, K and V have separate two-stage rings so
+// that K(t+2) can be fetched as soon as S(t) has read its stage), and P is double-buffered in shared memory, so the softmax chain
+// per tile is S ready -> exp -> P stored with both products and the TMA off it; two CTAs per SM (84 KB of shared memory, 256
+// TMEM columns each).
 // O accumulates in TMEM over all key tiles (the tensor core adds P(t) V to it) and is read once, at the end: TMEM reads run at
 // 64 B/clk per SM, and copying O out every tile doubled them. It is scaled by a max that follows the running row max lazily
 // (see kTaRescaleStep); the rare rescale is a TMEM load / multiply / store by the owning threads between two products.
@@ -37,7 +38,7 @@ constexpr int kTaPBytes = kTaBQ * kTaBK * 2;            // 16 KB: one P tile (tw
 constexpr int kTaStages = 2;
 constexpr int kTaXchBytes = 2 * 2 * kTaBQ * 4;          // row-max exchange between the two threads of a row: [buffer][half][row]
 constexpr int kTaSmem = kTaQBytes + kTaStages * 2 * kTaTileBytes + 2 * kTaPBytes + 1024 /*align*/ + 128 /*barriers*/ + kTaXchBytes;
-constexpr int kTaTmemCols = 128;                        // S: columns [0,64); O (accumulated over the key tiles): [64,128)
+constexpr int kTaTmemCols = 256;                        // S of even / odd tiles: columns [0,64) / [64,128); O (accumulated over the key tiles): [128,192)
 constexpr float kTaRescaleStep = 8.0f;                  // log2 units the row max may run ahead of the scaling max before O is rescaled
 
 struct TaArgs {
@@ -85,13 +86,14 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
     uint8_t* sP = sV + kTaStages * kTaTileBytes;             // [2][16 KB]
     uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kTaPBytes);
     uint64_t* bar_q = bars;                // Q landed
-    uint64_t* bar_full = bars + 1;         // [2] K+V tile landed
-    uint64_t* bar_empty = bars + 3;        // [2] tile consumed by both products
-    uint64_t* bar_s = bars + 5;            // S ready in TMEM
-    uint64_t* bar_sfree = bars + 6;        // every softmax thread has copied S out
-    uint64_t* bar_p = bars + 7;            // [2] P(t) written to shared memory buffer t & 1 (and O_{t-2} copied out of TMEM)
-    uint64_t* bar_pv = bars + 9;           // [2] O_t ready in TMEM buffer t & 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+    uint64_t* bar_kfull = bars + 1;        // [2] K tile landed          (K and V have their own rings: K(t) is free again after
+    uint64_t* bar_vfull = bars + 3;        // [2] V tile landed           S(t), long before P(t) V releases V(t))
+    uint64_t* bar_kempty = bars + 5;       // [2] S(t) has read K stage t & 1
+    uint64_t* bar_vempty = bars + 7;       // [2] P(t) V has read V stage t & 1
+    uint64_t* bar_s = bars + 9;            // [2] S(t) ready in TMEM buffer t & 1
+    uint64_t* bar_p = bars + 11;           // [2] P(t) written to shared memory buffer t & 1 (S(t) copied out, O rescaled if needed)
+    uint64_t* bar_pv = bars + 13;          // [2] P(t) V retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
     float* xch = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 128);      // [2][2][128]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -104,9 +106,10 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
 
     if (threadIdx.x == 0) {
         mbar_init(bar_q, 1);
-        for (int i = 0; i < kTaStages; ++i) { mbar_init(&bar_full[i], 1); mbar_init(&bar_empty[i], 1); }
-        mbar_init(bar_s, 1); mbar_init(bar_sfree, kTaSoftmaxWarps);
-        for (int i = 0; i < 2; ++i) { mbar_init(&bar_p[i], kTaSoftmaxWarps); mbar_init(&bar_pv[i], 1); }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&bar_kfull[i], 1); mbar_init(&bar_vfull[i], 1); mbar_init(&bar_kempty[i], 1); mbar_init(&bar_vempty[i], 1);
+            mbar_init(&bar_s[i], 1); mbar_init(&bar_p[i], kTaSoftmaxWarps); mbar_init(&bar_pv[i], 1);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kTaMmaWarp) {
@@ -125,12 +128,20 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
             mbar_arrive_expect_tx(bar_q, kTaQBytes);
             tma_load_3d(sQ, &map_qkv, bar_q, h * kTaHD, q0, b);                       // 64 rows per box: two boxes
             tma_load_3d(sQ + kTaQBytes / 2, &map_qkv, bar_q, h * kTaHD, q0 + 64, b);
-            for (int it = 0; it < n_tiles; ++it) {
+            auto load_k = [&](int t) {
+                const int st = t & 1;
+                mbar_wait(&bar_kempty[st], ((t >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bar_kfull[st], kTaTileBytes);
+                tma_load_3d(sK + st * kTaTileBytes, &map_qkv, &bar_kfull[st], C + h * kTaHD, t * kTaBK, b);
+            };
+            load_k(0);
+            if (n_tiles > 1) load_k(1);
+            for (int it = 0; it < n_tiles; ++it) {   // K runs two tiles ahead of V: it is asked for as soon as S(it) has released its stage
                 const int st = it & 1;
-                mbar_wait(&bar_empty[st], ((it >> 1) & 1) ^ 1);
-                mbar_arrive_expect_tx(&bar_full[st], 2 * kTaTileBytes);
-                tma_load_3d(sK + st * kTaTileBytes, &map_qkv, &bar_full[st], C + h * kTaHD, it * kTaBK, b);
-                tma_load_3d(sV + st * kTaTileBytes, &map_qkv, &bar_full[st], 2 * C + h * kTaHD, it * kTaBK, b);
+                mbar_wait(&bar_vempty[st], ((it >> 1) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bar_vfull[st], kTaTileBytes);
+                tma_load_3d(sV + st * kTaTileBytes, &map_qkv, &bar_vfull[st], 2 * C + h * kTaHD, it * kTaBK, b);
+                if (it + 2 < n_tiles) load_k(it + 2);
             }
         }
     } else if (warp == kTaMmaWarp) {
@@ -139,39 +150,35 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
             // D = f32, A = B = bf16; S: both K-major, N = 64; O_t: A K-major (P), B MN-major (V), N = 64; M = 128
             constexpr uint32_t idesc_s = (1u << 4) | (1u << 7) | (1u << 10) | (uint32_t(kTaBK >> 3) << 17) | (uint32_t(kTaBQ >> 4) << 24);
             constexpr uint32_t idesc_o = idesc_s | (1u << 16);
-            const uint32_t tS = tmem_base;
             const uint64_t qdesc = make_kmajor_sw128_desc(smem_u32(sQ));
-            mbar_wait(bar_q, 0);
-            mbar_wait(&bar_full[0], 0);
-            tc_fence_after();
-            {
-                const uint64_t kdesc = make_kmajor_sw128_desc(smem_u32(sK));
+            const uint32_t tO = tmem_base + 128;
+            // S(t) = Q K(t)^T into TMEM buffer t & 1; K stage t & 1 is released by the same commit
+            auto issue_s = [&](int t) {
+                const int sb = t & 1;
+                mbar_wait(&bar_kfull[sb], (t >> 1) & 1);
+                tc_fence_after();
+                const uint64_t kdesc = make_kmajor_sw128_desc(smem_u32(sK + sb * kTaTileBytes));
 #pragma unroll
-                for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
-                tc_commit(bar_s);
-            }
+                for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tmem_base + uint32_t(sb) * 64, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
+                tc_commit(&bar_kempty[sb]);
+                tc_commit(&bar_s[sb]);
+            };
+            mbar_wait(bar_q, 0);
+            issue_s(0);                              // two score tiles ahead of the softmax: its chain never contains a product
+            if (n_tiles > 1) issue_s(1);
             for (int it = 0; it < n_tiles; ++it) {
                 const int st = it & 1;
-                if (it + 1 < n_tiles) {              // S of the next tile, as soon as S of this one has been copied out
-                    const int sn = (it + 1) & 1;
-                    mbar_wait(&bar_full[sn], ((it + 1) >> 1) & 1);
-                    mbar_wait(bar_sfree, it & 1);
-                    tc_fence_after();
-                    const uint64_t kdesc = make_kmajor_sw128_desc(smem_u32(sK + sn * kTaTileBytes));
-#pragma unroll
-                    for (int k = 0; k < kTaHD / 16; ++k) tc_mma_bf16(tS, qdesc + uint64_t(k * 2), kdesc + uint64_t(k * 2), idesc_s, k ? 1u : 0u);
-                    tc_commit(bar_s);
-                }
-                mbar_wait(&bar_p[st], (it >> 1) & 1);   // P(it) is in its buffer (and O has been rescaled if this tile asked for it)
+                mbar_wait(&bar_p[st], (it >> 1) & 1);   // P(it) is in its buffer, S(it) has been copied out, O rescaled if this tile asked for it
+                mbar_wait(&bar_vfull[st], (it >> 1) & 1);
                 tc_fence_after();
-                const uint32_t tO = tmem_base + 64;
                 const uint64_t pdesc = make_kmajor_sw128_desc(smem_u32(sP + st * kTaPBytes));
                 const uint64_t vdesc = make_mnmajor_sw128_desc(smem_u32(sV + st * kTaTileBytes));
 #pragma unroll
                 for (int k = 0; k < kTaBK / 16; ++k)     // 16 keys per instruction: A advances 32 bytes, B advances 16 rows of 128 bytes
                     tc_mma_bf16(tO, pdesc + uint64_t(k * 2), vdesc + uint64_t(k * 128), idesc_o, (it | k) ? 1u : 0u);   // O accumulates over the tiles
-                tc_commit(&bar_empty[st]);           // K/V stage reusable once both products of this tile retire
+                tc_commit(&bar_vempty[st]);
                 tc_commit(&bar_pv[st]);
+                if (it + 2 < n_tiles) issue_s(it + 2);  // its TMEM buffer is free: bar_p(it) means every thread has read S(it)
             }
         }
     } else {
@@ -182,16 +189,13 @@ attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, i
         const uint32_t lane_addr = tmem_base + (uint32_t(wq * 32) << 16);
         float m_use = 0.f, l_run = 0.f;              // scaling max of this row (log2 domain); l_run: this thread's 32 keys of every tile only
         const int lim0 = min(qi, S - 1) - half * 32; // last visible key of this row, relative to this thread's first column
-        const uint32_t o_addr = lane_addr + 64 + uint32_t(half * 32);    // this thread's 32 columns of O
+        const uint32_t o_addr = lane_addr + 128 + uint32_t(half * 32);   // this thread's 32 columns of O
         for (int it = 0; it < n_tiles; ++it) {
             const int key0 = it * kTaBK;
-            mbar_wait(bar_s, it & 1);
+            mbar_wait(&bar_s[it & 1], (it >> 1) & 1);
             tc_fence_after();
             float s[32];
-            tmem_ld32(lane_addr + uint32_t(half * 32), s);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_sfree);   // the next S may overwrite TMEM columns [0,64)
+            tmem_ld32(lane_addr + uint32_t((it & 1) * 64 + half * 32), s);
             // causal mask and sequence tail by index, only on tiles that touch the diagonal or the end of the sequence
             if (key0 + kTaBK - 1 > q0 || key0 + kTaBK > S) {
                 const int lim = lim0 - key0;
