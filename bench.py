@@ -317,7 +317,7 @@ def main():
     arena_high = tr.arena_high_water
     exchange = None
     if dpt is not None:
-        overlapped = dpt.comm is not None and os.environ.get("MFT_DP_OVERLAP", "1" if c["full"] else "0") != "0"
+        overlapped = dpt.comm is not None and os.environ.get("MFT_DP_OVERLAP", "0") not in ("", "0")
         exchange = ("mft_comm (NCCL behind the C ABI, mft_trainer_step_dp)" if dpt.comm else "torch.distributed all_reduce between the phases") + \
                    (", bucket exchanged in chunks on a side stream while backward runs" if overlapped else ", one all-reduce of the bucket after backward")
         dpt.close()

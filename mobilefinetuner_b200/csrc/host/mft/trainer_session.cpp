@@ -537,13 +537,14 @@ static void set_overlap_mode(mft_trainer* t, bool on) {
     t->overlap_mode = on;
 }
 
-// MFT_DP_OVERLAP=0 / 1 forces the choice; by default buckets of 64 MB or more (full fine-tuning) are exchanged in chunks
-// while backward runs, smaller ones (adapters) by one all-reduce after it
+// MFT_DP_OVERLAP=1: the bucket is exchanged in chunks on a side stream while backward still runs (see mft_trainer::Chunk);
+// 2 = the same even with a one-rank communicator (exercises the chunk / side-stream / capture machinery on one GPU).
+// Default 0: one all-reduce after backward.
 static bool want_overlap(const mft_trainer* t) {
-    if (t->cfg.world_size <= 1) return false;
     const char* e = std::getenv("MFT_DP_OVERLAP");
-    if (e && *e) return std::atoi(e) != 0;
-    return t->grad_elems >= (int64_t(64) << 18);
+    const int v = e && *e ? std::atoi(e) : 0;
+    if (v >= 2) return true;
+    return v == 1 && t->cfg.world_size > 1;
 }
 
 extern "C" int mft_trainer_forward_backward(mft_trainer* t, const int32_t* dev_ids) {

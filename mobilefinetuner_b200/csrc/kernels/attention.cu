@@ -35,7 +35,8 @@ causal_attention_fwd_kernel(const float* __restrict__ q, const float* __restrict
                             float* __restrict__ ctx, int H, int S,
                             int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                             int64_t osb, int64_t oss, int64_t osh, float scale, int window,
-                            __nv_bfloat16* __restrict__ ctx16) {   // ctx16 != NULL: bf16 copy of ctx, same element strides
+                            __nv_bfloat16* __restrict__ ctx16) {
+    pdl_sync();   // ctx16 != NULL: bf16 copy of ctx, same element strides
     constexpr int LD = HD + kAttPad;
     constexpr int KS = HD / 8;    // k-slabs over the head dim (QK^T)
     constexpr int NT = HD / 8;    // n-tiles over the head dim (PV)
@@ -272,7 +273,7 @@ static int launch_attention_mt(const float* q, const float* k, const float* v, f
     if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(causal_attention_fwd_kernel<HD, PRECISE, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
-    causal_attention_fwd_kernel<HD, PRECISE, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
+    pdl_launch(causal_attention_fwd_kernel<HD, PRECISE, MT>, grid, 128, smem, st)(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss,
                                                                  osh, scale, window, static_cast<__nv_bfloat16*>(ctx16));
     return 0;
 }
@@ -314,6 +315,7 @@ causal_attention_bf16_kernel(const float* __restrict__ q, const float* __restric
                              int64_t qsb, int64_t qss, int64_t qsh, int64_t ksb, int64_t kss, int64_t ksh,
                              int64_t osb, int64_t oss, int64_t osh, float scale, int window,
                              __nv_bfloat16* __restrict__ ctx16) {
+    pdl_sync();
     constexpr int LDK = HD + 8, LDV = HD + 4;
     constexpr int KS = HD / 16;   // k16 slabs over the head dim (QK^T)
     constexpr int NT = HD / 8;    // n-tiles over the head dim (PV)
@@ -500,7 +502,7 @@ static int launch_attention_bf16(const float* q, const float* k, const float* v,
     if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(causal_attention_bf16_kernel<HD, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     dim3 grid(unsigned(ceil_div(S, 64 * MT)), unsigned(B * H));
-    causal_attention_bf16_kernel<HD, MT><<<grid, 128, smem, st>>>(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale,
+    pdl_launch(causal_attention_bf16_kernel<HD, MT>, grid, 128, smem, st)(q, k, v, ctx, H, S, qsb, qss, qsh, ksb, kss, ksh, osb, oss, osh, scale,
                                                             window, static_cast<__nv_bfloat16*>(ctx16));
     return 0;
 }

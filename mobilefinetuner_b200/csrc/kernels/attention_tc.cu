@@ -78,6 +78,7 @@ __device__ __forceinline__ void pair_sync(int q) {
 
 __global__ void __launch_bounds__(kTaThreads, 2)
 attention_tc_fwd_kernel(const __grid_constant__ CUtensorMap map_qkv, TaArgs p, int C) {
+    pdl_sync();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = base;
@@ -351,7 +352,7 @@ extern "C" int mft_causal_attention_tc_fwd(const void* qkv_bf16, int64_t ld, flo
     a.ctx = ctx; a.ctx16 = static_cast<__nv_bfloat16*>(ctx_bf16); a.H = H; a.S = S; a.osb = int64_t(S) * C; a.oss = C;
     a.scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(unsigned(ceil_div(S, kTaBQ)), unsigned(B * H));
-    attention_tc_fwd_kernel<<<grid, kTaThreads, kTaSmem, as_stream(stream)>>>(map, a, int(C));
+    pdl_launch(attention_tc_fwd_kernel, grid, kTaThreads, kTaSmem, as_stream(stream))(map, a, int(C));
     MFT_CHECK_LAUNCH("mft_causal_attention_tc_fwd");
     return 0;
 }

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 #include "mft_b200.h"
 
 namespace mft {
@@ -145,6 +146,42 @@ __device__ __forceinline__ float gelu_tanh_grad_f(float x) {
     float sech2 = 1.0f - t * t;
     float dinner = k0 * (1.0f + 3.0f * k1 * x2);
     return 0.5f * (1.0f + t) + 0.5f * x * sech2 * dinner;
+}
+
+
+// ---- programmatic dependent launch. Every kernel of the library starts with pdl_sync(): it lets the NEXT kernel of the stream
+// begin launching (its CTAs become resident as this kernel's leave), then waits until the PREVIOUS kernel has completed and its
+// writes are visible. Launched through pdl_launch, a kernel therefore overlaps only its launch latency and prologue with the
+// tail of its predecessor, never its memory accesses; in a chain of short kernels (a 512-token step is ~180 of them) that gap
+// is a large part of the step. Without the launch attribute both instructions are no-ops. MFT_PDL=0 switches the attribute off.
+__device__ __forceinline__ void pdl_sync() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+bool pdl_enabled();      // elementwise.cu (reads MFT_PDL once)
+
+template <typename... KArgs>
+struct PdlLaunch {
+    void (*kernel)(KArgs...);
+    dim3 grid, block;
+    size_t smem;
+    cudaStream_t stream;
+    template <typename... Args>
+    void operator()(Args&&... args) const {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = pdl_enabled() ? 1 : 0;
+        cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);     // errors surface through MFT_CHECK_LAUNCH (cudaGetLastError)
+    }
+};
+template <typename... KArgs>
+inline PdlLaunch<KArgs...> pdl_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+    return PdlLaunch<KArgs...>{kernel, grid, block, smem, stream};
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

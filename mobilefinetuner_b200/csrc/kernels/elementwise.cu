@@ -1,9 +1,16 @@
+#include <stdlib.h>
 // HBM-streaming elementwise / layout kernels: 128-bit vectorised, grid-stride, coalesced.
 // Each is bound by HBM bandwidth; algorithmic bytes per element are stated per kernel.
 #include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace mft {
+
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("MFT_PDL"); return !(e && *e == '0'); }();
+    return on;
+}
+
 
 // ---------------------------------------------------------------- binary with broadcast
 template <int OP>
@@ -24,6 +31,7 @@ __device__ __forceinline__ float bin_apply(float a, float b) {
 template <int OP>
 __global__ void binary_same_vec4(const float4* __restrict__ a, const float4* __restrict__ b,
                                  float4* __restrict__ out, int64_t n4) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
         float4 x = ld_stream(a + i), y = ld_stream(b + i), r;
         r.x = bin_apply<OP>(x.x, y.x); r.y = bin_apply<OP>(x.y, y.y);
@@ -36,6 +44,7 @@ __global__ void binary_same_vec4(const float4* __restrict__ a, const float4* __r
 template <int OP>
 __global__ void binary_bcast(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out,
                              int64_t outer, int64_t mid, int64_t inner, int b_mode, int64_t b_div) {
+    pdl_sync();
     const int64_t n = outer * mid * inner;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         int64_t i = idx % inner;
@@ -54,6 +63,7 @@ __global__ void binary_bcast(const float* __restrict__ a, const float* __restric
 template <int OP>
 __global__ void binary_bias_vec4(const float4* __restrict__ a, const float4* __restrict__ b,
                                  float4* __restrict__ out, int64_t n4, int64_t inner4) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
         float4 x = ld_stream(a + i), y = __ldg(b + (i % inner4)), r;
         r.x = bin_apply<OP>(x.x, y.x); r.y = bin_apply<OP>(x.y, y.y);
@@ -70,21 +80,22 @@ static int launch_binary(const float* a, const float* b, float* out, int64_t out
     const bool al = aligned16(a) && aligned16(b) && aligned16(out);
     if (b_mode == 0 && (n % 4 == 0) && al) {
         int64_t n4 = n / 4;
-        binary_same_vec4<OP><<<stream_grid(n4, 256), 256, 0, st>>>(
+        pdl_launch(binary_same_vec4<OP>, stream_grid(n4, 256), 256, 0, st)(
             reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b), reinterpret_cast<float4*>(out), n4);
     } else if (b_mode == 1 && (inner % 4 == 0) && al) {
         int64_t n4 = n / 4;
-        binary_bias_vec4<OP><<<stream_grid(n4, 256), 256, 0, st>>>(
+        pdl_launch(binary_bias_vec4<OP>, stream_grid(n4, 256), 256, 0, st)(
             reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b), reinterpret_cast<float4*>(out), n4,
             inner / 4);
     } else {
-        binary_bcast<OP><<<stream_grid(n, 256), 256, 0, st>>>(a, b, out, outer, mid, inner, b_mode, b_div < 1 ? 1 : b_div);
+        pdl_launch(binary_bcast<OP>, stream_grid(n, 256), 256, 0, st)(a, b, out, outer, mid, inner, b_mode, b_div < 1 ? 1 : b_div);
     }
     return 0;
 }
 
 // ---------------------------------------------------------------- affine / accumulate / fill
 __global__ void affine_kernel(const float* __restrict__ a, float* __restrict__ out, int64_t n, float alpha, float beta) {
+    pdl_sync();
     const int64_t n4 = n >> 2;
     const bool vec = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0;
     int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
@@ -103,6 +114,7 @@ __global__ void affine_kernel(const float* __restrict__ a, float* __restrict__ o
 }
 
 __global__ void accumulate_kernel(float* __restrict__ acc, const float* __restrict__ g, int64_t n) {
+    pdl_sync();
     const int64_t n4 = n >> 2;
     const bool vec = ((reinterpret_cast<uintptr_t>(acc) | reinterpret_cast<uintptr_t>(g)) & 15u) == 0;
     int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
@@ -121,6 +133,7 @@ __global__ void accumulate_kernel(float* __restrict__ acc, const float* __restri
 }
 
 __global__ void fill_kernel(float* __restrict__ out, int64_t n, float v) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = v;
 }
 
@@ -139,6 +152,7 @@ __device__ __forceinline__ float unary_apply(float x) {
 }
 template <int KIND>
 __global__ void unary_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n) {
+    pdl_sync();
     const int64_t n4 = n >> 2;
     const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) == 0;
     int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
@@ -159,7 +173,8 @@ __global__ void unary_kernel(const float* __restrict__ x, float* __restrict__ y,
 
 // gx = gy * gelu'(x): reads 8 B, writes 4 B per element.
 __global__ void gelu_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gy, float* __restrict__ gx, int64_t n,
-                                __nv_bfloat16* __restrict__ gx16) {   // gx16 != NULL (dense, 8-byte aligned, n % 4 == 0): bf16 copy of gx
+                                __nv_bfloat16* __restrict__ gx16) {
+    pdl_sync();   // gx16 != NULL (dense, 8-byte aligned, n % 4 == 0): bf16 copy of gx
     const int64_t n4 = n >> 2;
     const bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gy) | reinterpret_cast<uintptr_t>(gx)) & 15u) == 0;
     int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, stride = int64_t(gridDim.x) * blockDim.x;
@@ -232,6 +247,7 @@ template <bool XBF16, bool FAST>
 __global__ void __launch_bounds__(256)
 gelu_bwd_lowp_kernel(const void* __restrict__ xv, const __nv_bfloat16* __restrict__ gy, float* __restrict__ gx32,
                      __nv_bfloat16* __restrict__ gx16, int64_t n) {
+    pdl_sync();
     const int64_t n8 = n >> 3, stride = int64_t(gridDim.x) * blockDim.x;
     const uint4* g8 = reinterpret_cast<const uint4*>(gy);
     uint4* o8 = reinterpret_cast<uint4*>(gx16);
@@ -254,6 +270,7 @@ gelu_bwd_lowp_kernel(const void* __restrict__ xv, const __nv_bfloat16* __restric
 
 // bf16 -> fp32, row pitches in elements (fills the fp32 buffer of a tensor that was produced as bf16 only)
 __global__ void cast_from_bf16_kernel(const __nv_bfloat16* __restrict__ in, int64_t ldi, float* __restrict__ out, int64_t ldo, int64_t rows, int64_t cols) {
+    pdl_sync();
     const int64_t c4 = (cols + 3) >> 2, n = rows * c4;
     const bool vec = ((ldi & 3) == 0) && ((ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 7u) == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0);
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
@@ -274,6 +291,7 @@ __global__ void cast_from_bf16_kernel(const __nv_bfloat16* __restrict__ in, int6
 // optional bf16 copy of y for the down projection's GEMM; and its backward: d gate = gy * up * gelu'(gate), d up = gy * gelu(gate)
 // (GeluBackward + MulBackward, core/backward_functions.cpp:155-177, 66-83), each with an optional bf16 copy.
 __global__ void geglu_fwd_kernel(const float* __restrict__ gate, const float* __restrict__ up, float* __restrict__ y, __nv_bfloat16* __restrict__ y16, int64_t n) {
+    pdl_sync();
     const int64_t n4 = n >> 2;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
         const float4 g = ld_stream(reinterpret_cast<const float4*>(gate) + i), u = ld_stream(reinterpret_cast<const float4*>(up) + i);
@@ -284,6 +302,7 @@ __global__ void geglu_fwd_kernel(const float* __restrict__ gate, const float* __
 }
 __global__ void geglu_bwd_kernel(const float* __restrict__ gate, const float* __restrict__ up, const float* __restrict__ gy, float* __restrict__ dgate,
                                  float* __restrict__ dup, __nv_bfloat16* __restrict__ dgate16, __nv_bfloat16* __restrict__ dup16, int64_t n) {
+    pdl_sync();
     const int64_t n4 = n >> 2;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n4; i += int64_t(gridDim.x) * blockDim.x) {
         const float4 g = ld_stream(reinterpret_cast<const float4*>(gate) + i), u = ld_stream(reinterpret_cast<const float4*>(up) + i);
@@ -301,6 +320,7 @@ __global__ void geglu_bwd_kernel(const float* __restrict__ gate, const float* __
 
 // y = pow(x, p0) (kind 0) or clamp(x, p0, p1) (kind 1)
 __global__ void unary_param_kernel(int kind, const float* __restrict__ x, float* __restrict__ y, int64_t n, float p0, float p1) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
         float v = x[i];
         y[i] = kind == 0 ? powf(v, p0) : fminf(fmaxf(v, p0), p1);
@@ -309,6 +329,7 @@ __global__ void unary_param_kernel(int kind, const float* __restrict__ x, float*
 
 __global__ void mul_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b, const float* __restrict__ gy,
                                float* __restrict__ ga, float* __restrict__ gb, int64_t n) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
         float g = gy[i], x = a[i], y = b[i];
         if (ga) ga[i] = g * y;
@@ -345,7 +366,7 @@ extern "C" int mft_binary(int op, const float* a, const float* b, float* out, in
 extern "C" int mft_affine(const float* a, float* out, int64_t n, float alpha, float beta, mft_stream_t stream) {
     if (n == 0) return 0;
     if (!a || !out) return set_error(1, "mft_affine: null pointer");
-    affine_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(a, out, n, alpha, beta);
+    pdl_launch(affine_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(a, out, n, alpha, beta);
     MFT_CHECK_LAUNCH("mft_affine");
     return 0;
 }
@@ -353,7 +374,7 @@ extern "C" int mft_affine(const float* a, float* out, int64_t n, float alpha, fl
 extern "C" int mft_accumulate(float* acc, const float* g, int64_t n, mft_stream_t stream) {
     if (n == 0) return 0;
     if (!acc || !g) return set_error(1, "mft_accumulate: null pointer");
-    accumulate_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(acc, g, n);
+    pdl_launch(accumulate_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(acc, g, n);
     MFT_CHECK_LAUNCH("mft_accumulate");
     return 0;
 }
@@ -365,7 +386,7 @@ extern "C" int mft_fill(float* out, int64_t n, float value, mft_stream_t stream)
         MFT_CUDA_OK(cudaMemsetAsync(out, 0, size_t(n) * 4, as_stream(stream)), "mft_fill");
         return 0;
     }
-    fill_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(out, n, value);
+    pdl_launch(fill_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(out, n, value);
     MFT_CHECK_LAUNCH("mft_fill");
     return 0;
 }
@@ -376,15 +397,15 @@ extern "C" int mft_unary(int kind, const float* x, float* y, int64_t n, mft_stre
     cudaStream_t st = as_stream(stream);
     int g = stream_grid(n, 256, 4);
     switch (kind) {
-        case 0: unary_kernel<0><<<g, 256, 0, st>>>(x, y, n); break;
-        case 1: unary_kernel<1><<<g, 256, 0, st>>>(x, y, n); break;
-        case 2: unary_kernel<2><<<g, 256, 0, st>>>(x, y, n); break;
-        case 3: unary_kernel<3><<<g, 256, 0, st>>>(x, y, n); break;
-        case 4: unary_kernel<4><<<g, 256, 0, st>>>(x, y, n); break;
-        case 5: unary_kernel<5><<<g, 256, 0, st>>>(x, y, n); break;
-        case 6: unary_kernel<6><<<g, 256, 0, st>>>(x, y, n); break;
-        case 7: unary_kernel<7><<<g, 256, 0, st>>>(x, y, n); break;
-        case 8: unary_kernel<8><<<g, 256, 0, st>>>(x, y, n); break;
+        case 0: pdl_launch(unary_kernel<0>, g, 256, 0, st)(x, y, n); break;
+        case 1: pdl_launch(unary_kernel<1>, g, 256, 0, st)(x, y, n); break;
+        case 2: pdl_launch(unary_kernel<2>, g, 256, 0, st)(x, y, n); break;
+        case 3: pdl_launch(unary_kernel<3>, g, 256, 0, st)(x, y, n); break;
+        case 4: pdl_launch(unary_kernel<4>, g, 256, 0, st)(x, y, n); break;
+        case 5: pdl_launch(unary_kernel<5>, g, 256, 0, st)(x, y, n); break;
+        case 6: pdl_launch(unary_kernel<6>, g, 256, 0, st)(x, y, n); break;
+        case 7: pdl_launch(unary_kernel<7>, g, 256, 0, st)(x, y, n); break;
+        case 8: pdl_launch(unary_kernel<8>, g, 256, 0, st)(x, y, n); break;
         default: return set_error(1, "mft_unary: unknown kind %d", kind);
     }
     MFT_CHECK_LAUNCH("mft_unary");
@@ -398,7 +419,7 @@ extern "C" int mft_gelu_fwd(const float* x, float* y, int64_t n, mft_stream_t st
 extern "C" int mft_gelu_bwd(const float* x, const float* gy, float* gx, int64_t n, mft_stream_t stream) {
     if (n == 0) return 0;
     if (!x || !gy || !gx) return set_error(1, "mft_gelu_bwd: null pointer");
-    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, nullptr);
+    pdl_launch(gelu_bwd_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(x, gy, gx, n, nullptr);
     MFT_CHECK_LAUNCH("mft_gelu_bwd");
     return 0;
 }
@@ -408,7 +429,7 @@ extern "C" int mft_gelu_bwd_ex(const float* x, const float* gy, float* gx, void*
     if (n == 0) return 0;
     if (!x || !gy || !gx) return set_error(1, "mft_gelu_bwd_ex: null pointer");
     const bool ok = gx_bf16 && (n & 3) == 0 && aligned16(x) && aligned16(gy) && aligned16(gx) && (reinterpret_cast<uintptr_t>(gx_bf16) & 7u) == 0;
-    gelu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(x, gy, gx, n, ok ? static_cast<__nv_bfloat16*>(gx_bf16) : nullptr);
+    pdl_launch(gelu_bwd_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(x, gy, gx, n, ok ? static_cast<__nv_bfloat16*>(gx_bf16) : nullptr);
     MFT_CHECK_LAUNCH("mft_gelu_bwd_ex");
     if (gx_bf16 && !ok) return mft_cast_bf16(gx, n, gx_bf16, n, 1, n, stream);
     return 0;
@@ -419,7 +440,7 @@ extern "C" int mft_geglu_fwd(const float* gate, const float* up, float* y, void*
     if (!gate || !up || !y) return set_error(1, "mft_geglu_fwd: null pointer");
     if ((n & 3) || !aligned16(gate) || !aligned16(up) || !aligned16(y) || (y_bf16 && (reinterpret_cast<uintptr_t>(y_bf16) & 7u)))
         return set_error(1, "mft_geglu_fwd: n must be a multiple of 4 and the tensors 16-byte aligned");
-    geglu_fwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(gate, up, y, static_cast<__nv_bfloat16*>(y_bf16), n);
+    pdl_launch(geglu_fwd_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(gate, up, y, static_cast<__nv_bfloat16*>(y_bf16), n);
     MFT_CHECK_LAUNCH("mft_geglu_fwd");
     return 0;
 }
@@ -430,7 +451,7 @@ extern "C" int mft_geglu_bwd(const float* gate, const float* up, const float* gy
     if ((n & 3) || !aligned16(gate) || !aligned16(up) || !aligned16(gy) || !aligned16(dgate) || !aligned16(dup) ||
         (dgate_bf16 && (reinterpret_cast<uintptr_t>(dgate_bf16) & 7u)) || (dup_bf16 && (reinterpret_cast<uintptr_t>(dup_bf16) & 7u)))
         return set_error(1, "mft_geglu_bwd: n must be a multiple of 4 and the tensors 16-byte aligned");
-    geglu_bwd_kernel<<<stream_grid(n, 256, 4), 256, 0, as_stream(stream)>>>(gate, up, gy, dgate, dup, static_cast<__nv_bfloat16*>(dgate_bf16),
+    pdl_launch(geglu_bwd_kernel, stream_grid(n, 256, 4), 256, 0, as_stream(stream))(gate, up, gy, dgate, dup, static_cast<__nv_bfloat16*>(dgate_bf16),
                                                                         static_cast<__nv_bfloat16*>(dup_bf16), n);
     MFT_CHECK_LAUNCH("mft_geglu_bwd");
     return 0;
@@ -447,8 +468,8 @@ extern "C" int mft_gelu_bwd_lowp(const void* x, int x_is_bf16, const void* gy_bf
     auto* g16 = static_cast<const __nv_bfloat16*>(gyp);
     auto* o16 = static_cast<__nv_bfloat16*>(gx_bf16);
     cudaStream_t st = as_stream(stream);
-    if (x_is_bf16) { if (gx) gelu_bwd_lowp_kernel<true, false><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); else gelu_bwd_lowp_kernel<true, true><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); }
-    else { if (gx) gelu_bwd_lowp_kernel<false, false><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); else gelu_bwd_lowp_kernel<false, true><<<grid, 256, 0, st>>>(x, g16, gx, o16, n); }
+    if (x_is_bf16) { if (gx) pdl_launch(gelu_bwd_lowp_kernel<true, false>, grid, 256, 0, st)(x, g16, gx, o16, n); else pdl_launch(gelu_bwd_lowp_kernel<true, true>, grid, 256, 0, st)(x, g16, gx, o16, n); }
+    else { if (gx) pdl_launch(gelu_bwd_lowp_kernel<false, false>, grid, 256, 0, st)(x, g16, gx, o16, n); else pdl_launch(gelu_bwd_lowp_kernel<false, true>, grid, 256, 0, st)(x, g16, gx, o16, n); }
     MFT_CHECK_LAUNCH("mft_gelu_bwd_lowp");
     return 0;
 }
@@ -456,7 +477,7 @@ extern "C" int mft_gelu_bwd_lowp(const void* x, int x_is_bf16, const void* gy_bf
 extern "C" int mft_cast_from_bf16(const void* in, int64_t ldi, float* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream) {
     if (rows == 0 || cols == 0) return 0;
     if (!in || !out) return set_error(1, "mft_cast_from_bf16: null pointer");
-    cast_from_bf16_kernel<<<stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream)>>>(static_cast<const __nv_bfloat16*>(in), ldi, out, ldo, rows, cols);
+    pdl_launch(cast_from_bf16_kernel, stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream))(static_cast<const __nv_bfloat16*>(in), ldi, out, ldo, rows, cols);
     MFT_CHECK_LAUNCH("mft_cast_from_bf16");
     return 0;
 }
@@ -465,7 +486,7 @@ extern "C" int mft_mul_bwd(const float* a, const float* b, const float* gy, floa
                            mft_stream_t stream) {
     if (n == 0) return 0;
     if (!a || !b || !gy) return set_error(1, "mft_mul_bwd: null pointer");
-    mul_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(a, b, gy, ga, gb, n);
+    pdl_launch(mul_bwd_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(a, b, gy, ga, gb, n);
     MFT_CHECK_LAUNCH("mft_mul_bwd");
     return 0;
 }
@@ -474,7 +495,7 @@ extern "C" int mft_unary_param(int kind, const float* x, float* y, int64_t n, fl
     if (n == 0) return 0;
     if (!x || !y) return set_error(1, "mft_unary_param: null pointer");
     if (kind < 0 || kind > 1) return set_error(1, "mft_unary_param: unknown kind %d", kind);
-    unary_param_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(kind, x, y, n, p0, p1);
+    pdl_launch(unary_param_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(kind, x, y, n, p0, p1);
     MFT_CHECK_LAUNCH("mft_unary_param");
     return 0;
 }

@@ -46,6 +46,7 @@ __device__ __forceinline__ void stash_tile(float (*s)[EXT + 4], const TileRegs<E
 template <int MI, int NJ>
 __global__ void __launch_bounds__(256)
 gemm_simt_kernel(GemmParams p) {
+    pdl_sync();
     constexpr int BM = 16 * MI, BN = 16 * NJ;
     __shared__ __align__(16) float As[SBK][BM + 4];
     __shared__ __align__(16) float Bs[SBK][BN + 4];
@@ -147,6 +148,7 @@ gemm_simt_kernel(GemmParams p) {
 
 // Fixed-order reduction of the split-K partials + epilogue (deterministic, unlike atomics).
 __global__ void gemm_splitk_reduce_kernel(GemmParams p) {
+    pdl_sync();
     const int64_t total = int64_t(p.batch) * p.m * p.n;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < total; idx += int64_t(gridDim.x) * blockDim.x) {
         const int gn = int(idx % p.n);
@@ -171,13 +173,13 @@ int launch_gemm_simt(const GemmParams& p, cudaStream_t st) {
     const int bm = p.m <= 16 ? 16 : SBM, bn = p.n <= 16 ? 16 : SBN;
     dim3 grid(unsigned(ceil_div(p.n, bn)), unsigned(ceil_div(p.m, bm)), unsigned(p.batch * p.ksplit));
     if (grid.y > 65535 || grid.z > 65535) return set_error(1, "mft_gemm(simt): grid too large");
-    if (bm == 16 && bn == 16) gemm_simt_kernel<1, 1><<<grid, 256, 0, st>>>(p);
-    else if (bm == 16) gemm_simt_kernel<1, 4><<<grid, 256, 0, st>>>(p);
-    else if (bn == 16) gemm_simt_kernel<4, 1><<<grid, 256, 0, st>>>(p);
-    else gemm_simt_kernel<4, 4><<<grid, 256, 0, st>>>(p);
+    if (bm == 16 && bn == 16) pdl_launch(gemm_simt_kernel<1, 1>, grid, 256, 0, st)(p);
+    else if (bm == 16) pdl_launch(gemm_simt_kernel<1, 4>, grid, 256, 0, st)(p);
+    else if (bn == 16) pdl_launch(gemm_simt_kernel<4, 1>, grid, 256, 0, st)(p);
+    else pdl_launch(gemm_simt_kernel<4, 4>, grid, 256, 0, st)(p);
     add_launches(1);
     if (p.ksplit > 1) {
-        gemm_splitk_reduce_kernel<<<stream_grid(int64_t(p.batch) * p.m * p.n, 256), 256, 0, st>>>(p);
+        pdl_launch(gemm_splitk_reduce_kernel, stream_grid(int64_t(p.batch) * p.m * p.n, 256), 256, 0, st)(p);
         add_launches(1);
     }
     cudaError_t e = cudaGetLastError();

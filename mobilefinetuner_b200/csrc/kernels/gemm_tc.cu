@@ -112,6 +112,7 @@ __global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const __grid_constant__ CUtensorMap map_a2, const __grid_constant__ CUtensorMap map_b2,
                const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_g, TcArgs p) {
+    pdl_sync();
     using Cfg = TcCfg<BN, CG, EW>;
     constexpr int kEpiWarps = EW;
     constexpr int KE = BF16 ? 64 : 32;                     // elements per k-block (one 128-byte swizzle span)
@@ -785,11 +786,13 @@ static int launch_tc_form(const GemmParams& p, cudaStream_t st, const CUtensorMa
     cfg.blockDim = dim3(64 + 32 * EW);
     cfg.dynamicSmemBytes = Cfg::smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;      // the kernel starts with pdl_sync() (common.cuh)
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, CG, BF16, FUSED, EW, FORM>, ma, mb, ma2, mb2, mc, mg, a);
     if (g_prof.on) cudaEventRecord(g_prof.pool[slot].second, st);
     add_launches(1);

@@ -103,6 +103,7 @@ __device__ __forceinline__ float masked_score(float dot, float scale, int i, int
 template <int HD, int BQ, int NW, bool PRECISE>
 __global__ void __launch_bounds__(NW * 32)
 gqa_fwd_kernel(GqaArgs p) {
+    pdl_sync();
     constexpr int LD = HD + 4, LDP = kGBK + 4;
     constexpr int RG = BQ / 16, CG = NW / RG, NT_S = (kGBK / 8) / CG, NT_O = HD / (8 * CG);
     constexpr int THREADS = NW * 32, TPR = THREADS / BQ, EPT = kGBK / TPR;
@@ -212,6 +213,7 @@ gqa_fwd_kernel(GqaArgs p) {
 template <int HD, int NW, bool PRECISE>
 __global__ void __launch_bounds__(NW * 32)
 gqa_bwd_dq_kernel(GqaArgs p) {
+    pdl_sync();
     constexpr int BQ = kGBK, LD = HD + 4, LDP = kGBK + 4;
     constexpr int RG = BQ / 16, CG = NW / RG, NT_S = (kGBK / 8) / CG, NT_O = HD / (8 * CG);
     constexpr int THREADS = NW * 32, TPR = THREADS / BQ;
@@ -305,6 +307,7 @@ gqa_bwd_dq_kernel(GqaArgs p) {
 template <int HD, int NW, bool PRECISE>
 __global__ void __launch_bounds__(NW * 32)
 gqa_bwd_dkv_kernel(GqaArgs p) {
+    pdl_sync();
     constexpr int LD = HD + 4, LDP = kGBK + 4;
     constexpr int RG = kGBK / 16, CG = NW / RG, NT_S = (kGBK / 8) / CG, NT_O = HD / (8 * CG);
     constexpr int THREADS = NW * 32;
@@ -400,6 +403,7 @@ gqa_bwd_dkv_kernel(GqaArgs p) {
 // (RepeatKVHeadsBackward, core/backward_functions.cpp:683-716)
 __global__ void gqa_group_sum_kernel(const float* __restrict__ pk, const float* __restrict__ pv, float* __restrict__ dk, float* __restrict__ dv,
                                      int B, int H, int KV, int S, int HD, int64_t dksb, int64_t dkss, int64_t dksh) {
+    pdl_sync();
     const int rep = H / KV, c4 = HD / 4;
     const int64_t n = int64_t(B) * KV * S * c4;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
@@ -430,7 +434,7 @@ static int launch_gqa_fwd(const GqaArgs& a, cudaStream_t st) {
     if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(gqa_fwd_kernel<HD, BQ, NW, PRECISE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     dim3 grid(unsigned(ceil_div(a.S, BQ)), unsigned(a.B * a.H));
-    gqa_fwd_kernel<HD, BQ, NW, PRECISE><<<grid, NW * 32, smem, st>>>(a);
+    pdl_launch(gqa_fwd_kernel<HD, BQ, NW, PRECISE>, grid, NW * 32, smem, st)(a);
     return 0;
 }
 template <int HD, bool PRECISE>
@@ -444,15 +448,15 @@ static int launch_gqa_bwd(GqaArgs a, float* part_k, float* part_v, cudaStream_t 
         cudaFuncSetAttribute(gqa_bwd_dkv_kernel<HD, NW, PRECISE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_kv));
     }
     dim3 grid(unsigned(ceil_div(a.S, kGBK)), unsigned(a.B * a.H));
-    gqa_bwd_dq_kernel<HD, NW, PRECISE><<<grid, NW * 32, smem_dq, st>>>(a);
+    pdl_launch(gqa_bwd_dq_kernel<HD, NW, PRECISE>, grid, NW * 32, smem_dq, st)(a);
     float* dk_final = a.dk;
     float* dv_final = a.dv;
     if (a.H != a.KV) { a.partial = 1; a.dk = part_k; a.dv = part_v; }
-    gqa_bwd_dkv_kernel<HD, NW, PRECISE><<<grid, NW * 32, smem_kv, st>>>(a);
+    pdl_launch(gqa_bwd_dkv_kernel<HD, NW, PRECISE>, grid, NW * 32, smem_kv, st)(a);
     add_launches(1);
     if (a.H != a.KV) {
         const int64_t n = int64_t(a.B) * a.KV * a.S * (HD / 4);
-        gqa_group_sum_kernel<<<stream_grid(n, 256), 256, 0, st>>>(part_k, part_v, dk_final, dv_final, a.B, a.H, a.KV, a.S, HD, a.dksb, a.dkss, a.dksh);
+        pdl_launch(gqa_group_sum_kernel, stream_grid(n, 256), 256, 0, st)(part_k, part_v, dk_final, dv_final, a.B, a.H, a.KV, a.S, HD, a.dksb, a.dkss, a.dksh);
         add_launches(1);
     }
     return 0;

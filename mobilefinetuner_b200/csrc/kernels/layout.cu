@@ -7,6 +7,7 @@ namespace mft {
 // 32x32 shared-memory tile transpose (coalesced on both sides, padded against bank conflicts).
 __global__ void transpose2d_kernel(const float* __restrict__ in, int64_t ldi, float* __restrict__ out, int64_t ldo,
                                    int64_t rows, int64_t cols, int64_t stride_in, int64_t stride_out) {
+    pdl_sync();
     __shared__ float tile[32][33];
     in += blockIdx.z * stride_in;
     out += blockIdx.z * stride_out;
@@ -25,6 +26,7 @@ __global__ void transpose2d_kernel(const float* __restrict__ in, int64_t ldi, fl
 // fp32 -> bf16 (round to nearest even), row pitches in elements; 4 elements per thread
 __global__ void cast_bf16_kernel(const float* __restrict__ in, int64_t ldi, __nv_bfloat16* __restrict__ out, int64_t ldo,
                                  int64_t rows, int64_t cols) {
+    pdl_sync();
     const int64_t c4 = (cols + 3) >> 2;
     const int64_t n = rows * c4;
     const bool vec = ((ldi & 3) == 0) && ((ldo & 3) == 0) && ((reinterpret_cast<uintptr_t>(in) & 15u) == 0) &&
@@ -49,6 +51,7 @@ __global__ void cast_bf16_kernel(const float* __restrict__ in, int64_t ldi, __nv
 // out[c, r] (bf16, ldo) = in[r, c] (fp32, ldi): K-major bf16 shadow of a weight in one pass
 __global__ void transpose_cast_bf16_kernel(const float* __restrict__ in, int64_t ldi, __nv_bfloat16* __restrict__ out, int64_t ldo,
                                            int64_t rows, int64_t cols) {
+    pdl_sync();
     __shared__ float tile[32][33];
     const int64_t c0 = int64_t(blockIdx.x) * 32, r0 = int64_t(blockIdx.y) * 32;
     for (int j = threadIdx.y; j < 32; j += blockDim.y) {
@@ -65,6 +68,7 @@ __global__ void transpose_cast_bf16_kernel(const float* __restrict__ in, int64_t
 // out[b, j, i, :] = in[b, i, j, :]  — rows of d3 floats are moved whole (coalesced both sides).
 __global__ void permute0213_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t d0, int64_t d1,
                                    int64_t d2, int64_t d3) {
+    pdl_sync();
     const int64_t n = d0 * d1 * d2 * d3;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         int64_t d = idx % d3;
@@ -81,6 +85,7 @@ __global__ void permute0213_kernel(const float* __restrict__ in, float* __restri
 constexpr int kColsumRowsPerCta = 256;
 __global__ void colsum_partial_kernel(const float* __restrict__ g, int64_t ldg, float* __restrict__ partial,
                                       int64_t rows, int64_t n) {
+    pdl_sync();
     __shared__ float red[8][33];
     const int64_t c = int64_t(blockIdx.x) * 32 + threadIdx.x;
     const int64_t r0 = int64_t(blockIdx.y) * kColsumRowsPerCta;
@@ -100,6 +105,7 @@ __global__ void colsum_partial_kernel(const float* __restrict__ g, int64_t ldg, 
 }
 // stage 2: fixed-order sum of the slabs (deterministic).
 __global__ void colsum_final_kernel(const float* __restrict__ partial, float* __restrict__ out, int64_t slabs, int64_t n) {
+    pdl_sync();
     int64_t c = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
     if (c >= n) return;
     float s = 0.f;
@@ -111,6 +117,7 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, float* __
 __global__ void embedding_kernel(const int32_t* __restrict__ ids, const float* __restrict__ wte,
                                  const float* __restrict__ wpe, float* __restrict__ x, int64_t tokens, int64_t S,
                                  int64_t C, int64_t vocab, float scale, int32_t* status) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int64_t warps_per_grid = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t t = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; t < tokens; t += warps_per_grid) {
@@ -142,6 +149,7 @@ __global__ void embedding_kernel(const int32_t* __restrict__ ids, const float* _
 // RoPE on interleaved pairs. One thread per pair; float2 accesses.
 __global__ void rope_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t BH, int64_t S, int64_t Hd,
                             float theta, int inverse) {
+    pdl_sync();
     const int64_t half = Hd >> 1;
     const int64_t n = BH * S * half;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
@@ -162,6 +170,7 @@ __global__ void rope_kernel(const float* __restrict__ x, float* __restrict__ y, 
 
 __global__ void repeat_kv_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t B, int64_t KV,
                                      int64_t rep, int64_t SHd) {
+    pdl_sync();
     const int64_t n = B * KV * rep * SHd;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         int64_t e = idx % SHd;
@@ -172,6 +181,7 @@ __global__ void repeat_kv_fwd_kernel(const float* __restrict__ x, float* __restr
 }
 __global__ void repeat_kv_bwd_kernel(const float* __restrict__ gy, float* __restrict__ gx, int64_t B, int64_t KV,
                                      int64_t rep, int64_t SHd) {
+    pdl_sync();
     const int64_t n = B * KV * SHd;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         int64_t e = idx % SHd;
@@ -194,7 +204,7 @@ extern "C" int mft_transpose2d(const float* in, int64_t ldi, float* out, int64_t
     if (batch > 65535) return set_error(1, "mft_transpose2d: batch %lld too large", (long long)batch);
     dim3 grid(unsigned(ceil_div(cols, 32)), unsigned(ceil_div(rows, 32)), unsigned(batch));
     if (grid.y > 65535) return set_error(1, "mft_transpose2d: too many rows");
-    transpose2d_kernel<<<grid, dim3(32, 8), 0, as_stream(stream)>>>(in, ldi, out, ldo, rows, cols, stride_in, stride_out);
+    pdl_launch(transpose2d_kernel, grid, dim3(32, 8), 0, as_stream(stream))(in, ldi, out, ldo, rows, cols, stride_in, stride_out);
     MFT_CHECK_LAUNCH("mft_transpose2d");
     return 0;
 }
@@ -204,7 +214,7 @@ extern "C" int mft_permute0213(const float* in, float* out, int64_t d0, int64_t 
     int64_t n = d0 * d1 * d2 * d3;
     if (n == 0) return 0;
     if (!in || !out) return set_error(1, "mft_permute0213: null pointer");
-    permute0213_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(in, out, d0, d1, d2, d3);
+    pdl_launch(permute0213_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(in, out, d0, d1, d2, d3);
     MFT_CHECK_LAUNCH("mft_permute0213");
     return 0;
 }
@@ -223,8 +233,8 @@ extern "C" int mft_colsum(const float* g, int64_t ldg, float* out, int64_t rows,
         return set_error(1, "mft_colsum: workspace too small (%zu < %zu)", workspace_bytes, mft_colsum_workspace_bytes(rows, n));
     if (slabs > 65535) return set_error(1, "mft_colsum: too many rows");
     float* partial = static_cast<float*>(workspace);
-    colsum_partial_kernel<<<dim3(unsigned(ceil_div(n, 32)), unsigned(slabs)), dim3(32, 8), 0, as_stream(stream)>>>(g, ldg, partial, rows, n);
-    colsum_final_kernel<<<unsigned(ceil_div(n, 256)), 256, 0, as_stream(stream)>>>(partial, out, slabs, n);
+    pdl_launch(colsum_partial_kernel, dim3(unsigned(ceil_div(n, 32)), unsigned(slabs)), dim3(32, 8), 0, as_stream(stream))(g, ldg, partial, rows, n);
+    pdl_launch(colsum_final_kernel, unsigned(ceil_div(n, 256)), 256, 0, as_stream(stream))(partial, out, slabs, n);
     add_launches(1);
     MFT_CHECK_LAUNCH("mft_colsum");
     return 0;
@@ -237,7 +247,7 @@ extern "C" int mft_embedding_fwd(const int32_t* ids, const float* wte, const flo
     if ((C & 3) == 0 && !(aligned16(wte) && aligned16(x) && (!wpe || aligned16(wpe))))
         return set_error(1, "mft_embedding_fwd: tables must be 16-byte aligned");
     int blocks = stream_grid(tokens * 32, 256);
-    embedding_kernel<<<blocks, 256, 0, as_stream(stream)>>>(ids, wte, wpe, x, tokens, S, C, vocab, scale, status);
+    pdl_launch(embedding_kernel, blocks, 256, 0, as_stream(stream))(ids, wte, wpe, x, tokens, S, C, vocab, scale, status);
     MFT_CHECK_LAUNCH("mft_embedding_fwd");
     return 0;
 }
@@ -247,7 +257,7 @@ extern "C" int mft_rope(const float* x, float* y, int64_t BH, int64_t S, int64_t
     if (BH * S * Hd == 0) return 0;
     if (!x || !y) return set_error(1, "mft_rope: null pointer");
     if (Hd & 1) return set_error(1, "mft_rope: head_dim must be even");
-    rope_kernel<<<stream_grid(BH * S * (Hd / 2), 256), 256, 0, as_stream(stream)>>>(x, y, BH, S, Hd, theta, inverse);
+    pdl_launch(rope_kernel, stream_grid(BH * S * (Hd / 2), 256), 256, 0, as_stream(stream))(x, y, BH, S, Hd, theta, inverse);
     MFT_CHECK_LAUNCH("mft_rope");
     return 0;
 }
@@ -257,7 +267,7 @@ extern "C" int mft_repeat_kv_fwd(const float* x, float* y, int64_t B, int64_t KV
     int64_t n = B * KV * rep * S * Hd;
     if (n == 0) return 0;
     if (!x || !y) return set_error(1, "mft_repeat_kv_fwd: null pointer");
-    repeat_kv_fwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(x, y, B, KV, rep, S * Hd);
+    pdl_launch(repeat_kv_fwd_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(x, y, B, KV, rep, S * Hd);
     MFT_CHECK_LAUNCH("mft_repeat_kv_fwd");
     return 0;
 }
@@ -267,7 +277,7 @@ extern "C" int mft_repeat_kv_bwd(const float* gy, float* gx, int64_t B, int64_t 
     int64_t n = B * KV * S * Hd;
     if (n == 0) return 0;
     if (!gy || !gx) return set_error(1, "mft_repeat_kv_bwd: null pointer");
-    repeat_kv_bwd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(gy, gx, B, KV, rep, S * Hd);
+    pdl_launch(repeat_kv_bwd_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(gy, gx, B, KV, rep, S * Hd);
     MFT_CHECK_LAUNCH("mft_repeat_kv_bwd");
     return 0;
 }
@@ -275,7 +285,7 @@ extern "C" int mft_repeat_kv_bwd(const float* gy, float* gx, int64_t B, int64_t 
 extern "C" int mft_cast_bf16(const float* in, int64_t ldi, void* out, int64_t ldo, int64_t rows, int64_t cols, mft_stream_t stream) {
     if (rows == 0 || cols == 0) return 0;
     if (!in || !out) return set_error(1, "mft_cast_bf16: null pointer");
-    cast_bf16_kernel<<<stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream)>>>(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
+    pdl_launch(cast_bf16_kernel, stream_grid(rows * ((cols + 3) / 4), 256), 256, 0, as_stream(stream))(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
     MFT_CHECK_LAUNCH("mft_cast_bf16");
     return 0;
 }
@@ -285,7 +295,7 @@ extern "C" int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, 
     if (!in || !out) return set_error(1, "mft_transpose_cast_bf16: null pointer");
     dim3 grid(unsigned(ceil_div(cols, 32)), unsigned(ceil_div(rows, 32)));
     if (grid.y > 65535) return set_error(1, "mft_transpose_cast_bf16: too many rows");
-    transpose_cast_bf16_kernel<<<grid, dim3(32, 8), 0, as_stream(stream)>>>(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
+    pdl_launch(transpose_cast_bf16_kernel, grid, dim3(32, 8), 0, as_stream(stream))(in, ldi, static_cast<__nv_bfloat16*>(out), ldo, rows, cols);
     MFT_CHECK_LAUNCH("mft_transpose_cast_bf16");
     return 0;
 }
@@ -294,6 +304,7 @@ extern "C" int mft_transpose_cast_bf16(const float* in, int64_t ldi, void* out, 
 namespace mft {
 struct PermuteNd { int nd; int64_t out_shape[8]; int64_t src_stride[8]; };   // src_stride[i] = input stride of output axis i
 __global__ void permute_nd_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t n, PermuteNd p) {
+    pdl_sync();
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         int64_t rem = idx, off = 0;
         for (int i = p.nd - 1; i >= 0; --i) { off += (rem % p.out_shape[i]) * p.src_stride[i]; rem /= p.out_shape[i]; }
@@ -301,18 +312,22 @@ __global__ void permute_nd_kernel(const float* __restrict__ in, float* __restric
     }
 }
 __global__ void cast_f32_i32_kernel(const float* __restrict__ in, int32_t* __restrict__ out, int64_t n) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = int32_t(in[i]);
 }
 __global__ void cast_i32_f32_kernel(const int32_t* __restrict__ in, float* __restrict__ out, int64_t n) {
+    pdl_sync();
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) out[i] = float(in[i]);
 }
 __global__ void tril_ones_kernel(float* __restrict__ out, int64_t S) {
+    pdl_sync();
     const int64_t n = S * S;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x)
         out[i] = (i % S) <= (i / S) ? 1.0f : 0.0f;
 }
 // out[N, C] = 1 at (i, target[i]) when the class is in range, 0 elsewhere; targets int32 or float-coded
 __global__ void one_hot_kernel(const void* __restrict__ target, int target_is_i32, float* __restrict__ out, int64_t N, int64_t C) {
+    pdl_sync();
     const int64_t n = N * C;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
         const int64_t r = i / C, c = i % C;
@@ -330,29 +345,29 @@ extern "C" int mft_permute_nd(const float* in, float* out, int32_t ndim, const i
     int64_t n = 1;
     for (int i = 0; i < ndim; ++i) { p.out_shape[i] = out_shape[i]; p.src_stride[i] = src_stride[i]; n *= out_shape[i]; }
     if (n == 0) return 0;
-    mft::permute_nd_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(in, out, n, p);
+    pdl_launch(mft::permute_nd_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(in, out, n, p);
     MFT_CHECK_LAUNCH("mft_permute_nd");
     return 0;
 }
 extern "C" int mft_cast_i32(const void* in, void* out, int64_t n, int to_i32, mft_stream_t stream) {
     if (n == 0) return 0;
     if (!in || !out) return set_error(1, "mft_cast_i32: null pointer");
-    if (to_i32) mft::cast_f32_i32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(static_cast<const float*>(in), static_cast<int32_t*>(out), n);
-    else mft::cast_i32_f32_kernel<<<stream_grid(n, 256), 256, 0, as_stream(stream)>>>(static_cast<const int32_t*>(in), static_cast<float*>(out), n);
+    if (to_i32) pdl_launch(mft::cast_f32_i32_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(static_cast<const float*>(in), static_cast<int32_t*>(out), n);
+    else pdl_launch(mft::cast_i32_f32_kernel, stream_grid(n, 256), 256, 0, as_stream(stream))(static_cast<const int32_t*>(in), static_cast<float*>(out), n);
     MFT_CHECK_LAUNCH("mft_cast_i32");
     return 0;
 }
 extern "C" int mft_tril_ones(float* out, int64_t S, mft_stream_t stream) {
     if (S == 0) return 0;
     if (!out) return set_error(1, "mft_tril_ones: null pointer");
-    mft::tril_ones_kernel<<<stream_grid(S * S, 256), 256, 0, as_stream(stream)>>>(out, S);
+    pdl_launch(mft::tril_ones_kernel, stream_grid(S * S, 256), 256, 0, as_stream(stream))(out, S);
     MFT_CHECK_LAUNCH("mft_tril_ones");
     return 0;
 }
 extern "C" int mft_one_hot(const void* target, int target_is_i32, float* out, int64_t N, int64_t C, mft_stream_t stream) {
     if (N * C == 0) return 0;
     if (!target || !out) return set_error(1, "mft_one_hot: null pointer");
-    mft::one_hot_kernel<<<stream_grid(N * C, 256), 256, 0, as_stream(stream)>>>(target, target_is_i32, out, N, C);
+    pdl_launch(mft::one_hot_kernel, stream_grid(N * C, 256), 256, 0, as_stream(stream))(target, target_is_i32, out, N, C);
     MFT_CHECK_LAUNCH("mft_one_hot");
     return 0;
 }

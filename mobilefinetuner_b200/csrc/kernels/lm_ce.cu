@@ -27,6 +27,7 @@ __device__ __forceinline__ int ce_label(const int32_t* labels, int64_t row, int 
 __global__ void __launch_bounds__(kCeThreads)
 lm_ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels, int64_t rows, int S,
                  int V, int ignore_index, float* __restrict__ row_lse, double* __restrict__ row_nll) {
+    pdl_sync();
     __shared__ float sred[32];
     __shared__ double dred[32];
     const bool vec = ((ld & 3) == 0) && ((reinterpret_cast<uintptr_t>(logits) & 15u) == 0);
@@ -75,6 +76,7 @@ lm_ce_fwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __
 __global__ void __launch_bounds__(1024)
 lm_ce_reduce_kernel(const double* __restrict__ row_nll, const int32_t* __restrict__ labels, int64_t rows, int S, int V,
                     int ignore_index, int reduction, float* __restrict__ loss_out, int32_t* __restrict__ valid_out) {
+    pdl_sync();
     __shared__ double dred[32];
     __shared__ double cred[32];
     double s = 0.0, c = 0.0;
@@ -119,7 +121,8 @@ __global__ void __launch_bounds__(kCeThreads)
 lm_ce_bwd_kernel(const float* __restrict__ logits, int64_t ld, const int32_t* __restrict__ labels,
                  const float* __restrict__ row_lse, const int32_t* __restrict__ valid, const float* __restrict__ gout,
                  int64_t rows, int S, int V, int ignore_index, int reduction, float* __restrict__ dlogits, int64_t ldg,
-                 __nv_bfloat16* __restrict__ d16, int64_t ld16) {   // d16 != NULL: bf16 copy of dlogits (vectorised path only)
+                 __nv_bfloat16* __restrict__ d16, int64_t ld16) {
+    pdl_sync();   // d16 != NULL: bf16 copy of dlogits (vectorised path only)
     // dlogits == NULL: the bf16 copy is the only result (launcher guarantees the vectorised layout then)
     const bool vec = ((ld & 3) == 0) && (!dlogits || (ldg & 3) == 0) &&
                      (((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(dlogits)) & 15u) == 0);
@@ -203,9 +206,9 @@ extern "C" int mft_lm_ce_fwd(const float* logits, int64_t ld, const int32_t* lab
     double* row_nll = static_cast<double*>(workspace);
     if (rows > 0 && V > 0) {
         int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
-        lm_ce_fwd_kernel<<<grid, kCeThreads, 0, st>>>(logits, ld, labels, rows, S, V, ignore_index, row_lse, row_nll);
+        pdl_launch(lm_ce_fwd_kernel, grid, kCeThreads, 0, st)(logits, ld, labels, rows, S, V, ignore_index, row_lse, row_nll);
     }
-    lm_ce_reduce_kernel<<<1, 1024, 0, st>>>(row_nll, labels, rows, S, V, ignore_index, reduction, loss_out, valid_out);
+    pdl_launch(lm_ce_reduce_kernel, 1, 1024, 0, st)(row_nll, labels, rows, S, V, ignore_index, reduction, loss_out, valid_out);
     add_launches(1);
     MFT_CHECK_LAUNCH("mft_lm_ce_fwd");
     return 0;
@@ -224,8 +227,8 @@ static int ce_bwd_impl(const float* logits, int64_t ld, const int32_t* labels, c
     if (!dlogits && !fused16) return set_error(1, "mft_lm_ce_bwd_ex: a bf16-only gradient needs 16-byte aligned logits with a pitch %% 4 == 0 and an 8-byte aligned bf16 buffer with a pitch %% 4 == 0");
     int grid = int(rows < int64_t(kNumSMs) * 4 ? rows : int64_t(kNumSMs) * 4);
     __nv_bfloat16* h16 = fused16 ? static_cast<__nv_bfloat16*>(d16) : nullptr;
-    if (!dlogits) lm_ce_bwd_kernel<true><<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
-    else lm_ce_bwd_kernel<false><<<grid, kCeThreads, 0, as_stream(stream)>>>(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
+    if (!dlogits) pdl_launch(lm_ce_bwd_kernel<true>, grid, kCeThreads, 0, as_stream(stream))(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
+    else pdl_launch(lm_ce_bwd_kernel<false>, grid, kCeThreads, 0, as_stream(stream))(logits, ld, labels, row_lse, valid, gout, rows, S, V, ignore_index, reduction, dlogits, ldg, h16, ld16);
     MFT_CHECK_LAUNCH("mft_lm_ce_bwd");
     if (d16 && !fused16) return mft_cast_bf16(dlogits, ldg, d16, ld16, rows, V, stream);
     return 0;

@@ -20,6 +20,7 @@ template <int RPW, int RMAX, int KC>
 __global__ void __launch_bounds__(256, (RPW <= 2 && RMAX <= 16) ? 2 : 1)
 lora_down_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
                  float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha) {
+    pdl_sync();
     constexpr int PITCH = RMAX + 4;
     extern __shared__ __align__(16) float At[];     // [KC][PITCH]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -120,7 +121,8 @@ template <bool PRECISE>
 __global__ void __launch_bounds__(128)
 lora_down_mma_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ a, int64_t lda, int a_is_kr,
                      float* __restrict__ y, int64_t ldy, int64_t T, int K, int r, float alpha,
-                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {   // y16 != NULL: bf16 copy of y
+                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {
+    pdl_sync();   // y16 != NULL: bf16 copy of y
     extern __shared__ __align__(16) float As[];                       // [kDmSpan][18]; reused for the cross-warp reduction
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
@@ -348,6 +350,7 @@ __global__ void __launch_bounds__(kTnRG * kTnCT)
 lora_tn_kernel(const float* __restrict__ s, int64_t lds, const float* __restrict__ w, int64_t ldw,
                float* __restrict__ partial, int64_t T, int q, int r, float* __restrict__ out, int64_t ldo, int out_is_rq,
                float alpha, int use_tickets) {
+    pdl_sync();
     lora_tn_body<CPT, RMAX>(s, lds, w, ldw, partial, T, q, r, out, ldo, out_is_rq, alpha, use_tickets, int(blockIdx.x), int(blockIdx.y), int(gridDim.y),
                             g_tn_tickets);
 }
@@ -358,6 +361,7 @@ constexpr int kTnGroupTickets = 32768;
 __device__ unsigned g_tn_group_tickets[kTnGroupTickets];
 __global__ void __launch_bounds__(kTnRG * kTnCT)
 lora_tn_group_kernel(const mft_lora_tn_problem* __restrict__ probs) {
+    pdl_sync();
     const mft_lora_tn_problem p = probs[blockIdx.z];
     if (int(blockIdx.x) >= p.colblocks || int(blockIdx.y) >= p.splits) return;
     lora_tn_body<2, 16>(p.s, p.lds, p.w, p.ldw, p.partial, p.T, int(p.q), p.r, p.out, p.ldo, p.out_is_rq, p.alpha, p.use_tickets, int(blockIdx.x),
@@ -367,6 +371,7 @@ lora_tn_group_kernel(const mft_lora_tn_problem* __restrict__ probs) {
 // out[c][col] (out_is_rq) or out[col][c] = alpha * sum over splits, fixed order
 __global__ void lora_tn_reduce_kernel(const float* __restrict__ partial, float* __restrict__ out, int64_t ldo, int out_is_rq,
                                       int splits, int q, int r, float alpha) {
+    pdl_sync();
     const int64_t n = int64_t(r) * q;
     for (int64_t idx = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; idx < n; idx += int64_t(gridDim.x) * blockDim.x) {
         const int c = int(idx / q), col = int(idx % q);
@@ -387,6 +392,7 @@ __global__ void lora_tn_reduce_kernel(const float* __restrict__ partial, float* 
 
 // grouped reduce for the problems whose split list is too long for the last-CTA sum
 __global__ void lora_tn_group_reduce_kernel(const mft_lora_tn_problem* __restrict__ probs) {
+    pdl_sync();
     const mft_lora_tn_problem p = probs[blockIdx.y];
     if (p.use_tickets) return;
     const int64_t n = int64_t(p.r) * p.q;
@@ -417,7 +423,7 @@ static void launch_down(const float* x, int64_t ldx, const float* a, int64_t lda
     constexpr size_t smem = size_t(KC) * (RMAX + 4) * sizeof(float);
     static bool attr[kMaxDevices] = {};
     if (first_use_on_device(attr)) cudaFuncSetAttribute(lora_down_kernel<RPW, RMAX, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    lora_down_kernel<RPW, RMAX, KC><<<unsigned(ceil_div(T, int64_t(8 * RPW))), 256, smem, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha);
+    pdl_launch(lora_down_kernel<RPW, RMAX, KC>, unsigned(ceil_div(T, int64_t(8 * RPW))), 256, smem, st)(x, ldx, a, lda, a_is_kr, y, ldy, T, K, r, alpha);
 }
 
 static int lora_down_impl(const float* x, int64_t ldx, const float* a, int64_t lda, int a_is_kr, float* y, int64_t ldy,
@@ -439,8 +445,8 @@ static int lora_down_impl(const float* x, int64_t ldx, const float* a, int64_t l
             cudaFuncSetAttribute(lora_down_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDmSmemBytes);
         }
         const unsigned grid = unsigned(ceil_div(T, int64_t(16)));
-        if (precise) lora_down_mma_kernel<true><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
-        else lora_down_mma_kernel<false><<<grid, 128, kDmSmemBytes, st>>>(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
+        if (precise) pdl_launch(lora_down_mma_kernel<true>, grid, 128, kDmSmemBytes, st)(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
+        else pdl_launch(lora_down_mma_kernel<false>, grid, 128, kDmSmemBytes, st)(x, ldx, a, lda, a_is_kr, y, ldy, T, k, r, alpha, y16, ld16);
         MFT_CHECK_LAUNCH("mft_lora_down");
         return 0;
     }
@@ -502,18 +508,18 @@ extern "C" int mft_lora_tn(const float* s, int64_t lds, const float* w, int64_t 
     const int tk = (colblocks <= kTnMaxTickets && splits <= 64) ? 1 : 0;      // 64 splits x [r x 128] partials = 512 KB from L2 for the last CTA of a column block
     if (vec) {
         const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
-        lora_tn_kernel<2, 16><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
+        pdl_launch(lora_tn_kernel<2, 16>, dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st)(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
                                                                                                  out_is_rq, alpha, tk);
     } else {
         const size_t smem = (size_t(kTnRows) * 64 + size_t(64) * kTnCT) * sizeof(float);
         static bool attr[kMaxDevices] = {};
         if (first_use_on_device(attr)) cudaFuncSetAttribute(lora_tn_kernel<1, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        lora_tn_kernel<1, 64><<<dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st>>>(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
+        pdl_launch(lora_tn_kernel<1, 64>, dim3(unsigned(colblocks), unsigned(splits)), kTnRG * kTnCT, smem, st)(s, lds, w, ldw, partial, T, int(q), r, out, ldo,
                                                                                                  out_is_rq, alpha, tk);
     }
     if (!tk) {
         add_launches(1);
-        lora_tn_reduce_kernel<<<stream_grid(int64_t(r) * q, 256), 256, 0, st>>>(partial, out, ldo, out_is_rq, int(splits), int(q), r, alpha);
+        pdl_launch(lora_tn_reduce_kernel, stream_grid(int64_t(r) * q, 256), 256, 0, st)(partial, out, ldo, out_is_rq, int(splits), int(q), r, alpha);
     }
     MFT_CHECK_LAUNCH("mft_lora_tn");
     return 0;
@@ -543,6 +549,7 @@ template <int NT>     // output columns in tiles of 8: rank <= 8 * NT
 __global__ void __launch_bounds__(128)
 lora_down_bf16_kernel(const __nv_bfloat16* __restrict__ x, int64_t ldx, const __nv_bfloat16* __restrict__ at, int64_t lda,
                       float* __restrict__ y, int64_t ldy, __nv_bfloat16* __restrict__ y16, int64_t ld16, int64_t T, int K, int r, float alpha) {
+    pdl_sync();
     extern __shared__ __align__(16) uint8_t lb_smem[];
     const int KP = K + kLbPad;
     constexpr int RC = 8 * NT;                                                       // shadow rows / output columns held
@@ -644,10 +651,10 @@ extern "C" int mft_lora_down_bf16(const void* x_bf16, int64_t ldx, const void* a
     const __nv_bfloat16* ap = static_cast<const __nv_bfloat16*>(a_kmajor_bf16);
     __nv_bfloat16* y16 = static_cast<__nv_bfloat16*>(y_bf16);
     cudaStream_t st = as_stream(stream);
-    if (nt == 1) lora_down_bf16_kernel<1><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
-    else if (nt == 2) lora_down_bf16_kernel<2><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
-    else if (nt == 4) lora_down_bf16_kernel<4><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
-    else lora_down_bf16_kernel<8><<<grid, 128, smem, st>>>(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    if (nt == 1) pdl_launch(lora_down_bf16_kernel<1>, grid, 128, smem, st)(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else if (nt == 2) pdl_launch(lora_down_bf16_kernel<2>, grid, 128, smem, st)(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else if (nt == 4) pdl_launch(lora_down_bf16_kernel<4>, grid, 128, smem, st)(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
+    else pdl_launch(lora_down_bf16_kernel<8>, grid, 128, smem, st)(xp, ldx, ap, lda, y, ldy, y16, ld_bf16, T, int(K), r, alpha);
     MFT_CHECK_LAUNCH("mft_lora_down_bf16");
     return 0;
 }
@@ -667,12 +674,12 @@ extern "C" int mft_lora_tn_group(const mft_lora_tn_problem* dev_problems, int32_
     if (num_problems > 65535 || max_splits > 65535 || max_colblocks < 1 || max_splits < 1) return set_error(1, "mft_lora_tn_group: grid out of range");
     cudaStream_t st = as_stream(stream);
     const size_t smem = (size_t(kTnRows) * 16 + size_t(16) * kTnCT * 2) * sizeof(float);
-    lora_tn_group_kernel<<<dim3(unsigned(max_colblocks), unsigned(max_splits), unsigned(num_problems)), kTnRG * kTnCT, smem, st>>>(dev_problems);
+    pdl_launch(lora_tn_group_kernel, dim3(unsigned(max_colblocks), unsigned(max_splits), unsigned(num_problems)), kTnRG * kTnCT, smem, st)(dev_problems);
     if (any_long_split) {
         add_launches(1);
         int64_t bx = ceil_div(max_rq > 0 ? max_rq : 1, int64_t(256));
         if (bx > 64) bx = 64;
-        lora_tn_group_reduce_kernel<<<dim3(unsigned(bx), unsigned(num_problems)), 256, 0, st>>>(dev_problems);
+        pdl_launch(lora_tn_group_reduce_kernel, dim3(unsigned(bx), unsigned(num_problems)), 256, 0, st)(dev_problems);
     }
     MFT_CHECK_LAUNCH("mft_lora_tn_group");
     return 0;

@@ -16,7 +16,8 @@ __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                      float* __restrict__ y, int64_t rows, int dim, float eps,
                      const float* __restrict__ add, float* __restrict__ sum_out,     // add != NULL: normalise x + add, store the sum
-                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {                 // y16 != NULL: bf16 copy of y (pitch ld16)
+                     __nv_bfloat16* __restrict__ y16, int64_t ld16) {
+    pdl_sync();                 // y16 != NULL: bf16 copy of y (pitch ld16)
     const int lane = threadIdx.x & 31;
     const int dim4 = dim >> 2;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -68,6 +69,7 @@ layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
 // Generic fallback (any dim / alignment): one warp per row, three passes through L1/L2.
 __global__ void layernorm_fwd_generic(const float* __restrict__ x, const float* __restrict__ gamma,
                                       const float* __restrict__ beta, float* __restrict__ y, int64_t rows, int dim, float eps) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -89,7 +91,8 @@ __global__ void __launch_bounds__(kNormWarps * 32)
 layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ gy,
                      float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps,
                      const float* __restrict__ addend,     // addend != NULL: gx = dx + addend (gradient already waiting at x)
-                     __nv_bfloat16* __restrict__ gx16, int64_t ld16) {   // gx16 != NULL: bf16 copy of gx
+                     __nv_bfloat16* __restrict__ gx16, int64_t ld16) {
+    pdl_sync();   // gx16 != NULL: bf16 copy of gx
     extern __shared__ float smem[];  // [kNormWarps][2][dim]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int dim4 = dim >> 2;
@@ -189,6 +192,7 @@ layernorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ gamm
 
 __global__ void layernorm_bwd_generic(const float* __restrict__ x, const float* __restrict__ gamma,
                                       const float* __restrict__ gy, float* __restrict__ gx, int64_t rows, int dim, float eps) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -215,6 +219,7 @@ __global__ void layernorm_bwd_generic(const float* __restrict__ x, const float* 
 // generic weight-grad partials: CTA b handles rows [b*chunk, (b+1)*chunk), thread per column.
 __global__ void layernorm_wgrad_generic(const float* __restrict__ x, const float* __restrict__ gy,
                                         float* __restrict__ partial, int64_t rows, int dim, float eps, int64_t chunk) {
+    pdl_sync();
     extern __shared__ float stats[];  // [chunk][2] mean, rstd
     const int64_t r0 = int64_t(blockIdx.x) * chunk;
     int64_t r1 = r0 + chunk; if (r1 > rows) r1 = rows;
@@ -247,6 +252,7 @@ __global__ void layernorm_wgrad_generic(const float* __restrict__ x, const float
 __global__ void __launch_bounds__(256)
 norm_wgrad_final(const float* __restrict__ partial, float* __restrict__ out0, float* __restrict__ out1,
                  int parts, int dim, int per_part) {
+    pdl_sync();
     __shared__ float ra[8][33], rb[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + tx;
@@ -275,7 +281,8 @@ namespace mft {
 // One warp per row, generic over dim (row re-read hits L1); Gemma dims are 640 (hidden) and 256 (q/k norm).
 __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, float* __restrict__ y,
                                    int64_t rows, int dim, float eps, int plus_one,
-                                   __nv_bfloat16* __restrict__ y16, int64_t ld16) {   // y16 != NULL: bf16 copy of y
+                                   __nv_bfloat16* __restrict__ y16, int64_t ld16) {
+    pdl_sync();   // y16 != NULL: bf16 copy of y
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -297,7 +304,8 @@ __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __r
 __global__ void __launch_bounds__(kNormWarps * 32)
 rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ gy,
                    float* __restrict__ gx, float* __restrict__ partial, int64_t rows, int dim, float eps, int plus_one,
-                   __nv_bfloat16* __restrict__ gx16, int64_t ld16) {          // gx16 != NULL: bf16 copy of gx
+                   __nv_bfloat16* __restrict__ gx16, int64_t ld16) {
+    pdl_sync();          // gx16 != NULL: bf16 copy of gx
     extern __shared__ float smem[];  // [kNormWarps][dim]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float* my = smem + size_t(warp) * dim;
@@ -338,6 +346,7 @@ rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 
 // ---------------------------------------------------------------- softmax over the last dim
 __global__ void softmax_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t rows, int dim) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -353,6 +362,7 @@ __global__ void softmax_fwd_kernel(const float* __restrict__ x, float* __restric
 }
 __global__ void softmax_bwd_kernel(const float* __restrict__ y, const float* __restrict__ gy, float* __restrict__ gx,
                                    int64_t rows, int dim) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
     for (int64_t r = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5; r < rows; r += warps) {
@@ -379,7 +389,7 @@ static int launch_ln_fwd(const float* x, const float* g, const float* b, float* 
     constexpr int kFwdWarps = 4;
     int blocks = int(ceil_div(rows, kFwdWarps));
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-    layernorm_fwd_kernel<NV><<<blocks, kFwdWarps * 32, 0, st>>>(x, g, b, y, rows, dim, eps, add, sum_out, static_cast<__nv_bfloat16*>(y16), ld16);
+    pdl_launch(layernorm_fwd_kernel<NV>, blocks, kFwdWarps * 32, 0, st)(x, g, b, y, rows, dim, eps, add, sum_out, static_cast<__nv_bfloat16*>(y16), ld16);
     return 0;
 }
 template <int NV>
@@ -390,14 +400,14 @@ static int launch_ln_bwd(const float* x, const float* g, const float* gy, float*
         constexpr int kDxWarps = 4;
         int blocks = int(ceil_div(rows, kDxWarps));
         if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-        layernorm_bwd_kernel<NV, false><<<blocks, kDxWarps * 32, 0, st>>>(x, g, gy, gx, nullptr, rows, dim, eps, addend, gx16, ld16);
+        pdl_launch(layernorm_bwd_kernel<NV, false>, blocks, kDxWarps * 32, 0, st)(x, g, gy, gx, nullptr, rows, dim, eps, addend, gx16, ld16);
         return 0;
     }
     size_t smem = size_t(kNormWarps) * 2 * dim * sizeof(float);
     static bool attr_set[kMaxDevices] = {};
     if (first_use_on_device(attr_set))
         cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    layernorm_bwd_kernel<NV, true><<<ctas, kNormWarps * 32, smem, st>>>(x, g, gy, gx, partial, rows, dim, eps, addend, gx16, ld16);
+    pdl_launch(layernorm_bwd_kernel<NV, true>, ctas, kNormWarps * 32, smem, st)(x, g, gy, gx, partial, rows, dim, eps, addend, gx16, ld16);
     return 0;
 }
 
@@ -430,7 +440,7 @@ static int ln_fwd_impl(const char* who, const float* x, const float* add, float*
             if (rc) return rc;
             src = sum_out;
         }
-        layernorm_fwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(src, gamma, beta, y, rows, int(dim), eps);
+        pdl_launch(layernorm_fwd_generic, stream_grid(rows * 32, 256), 256, 0, st)(src, gamma, beta, y, rows, int(dim), eps);
         if (y16) { int rc = mft_cast_bf16(y, dim, y16, ld16, rows, dim, stream); if (rc) return rc; }
     }
     MFT_CHECK_LAUNCH(who);
@@ -484,14 +494,14 @@ static int ln_bwd_impl(const float* x, const float* gamma, const float* gy, cons
         else if (nv <= 8) launch_ln_bwd<8>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
         else launch_ln_bwd<16>(x, gamma, gy, gx, partial, rows, int(dim), eps, parts, st, addend, gx16, ld16);
     } else {
-        layernorm_bwd_generic<<<stream_grid(rows * 32, 256), 256, 0, st>>>(x, gamma, gy, gx, rows, int(dim), eps);
+        pdl_launch(layernorm_bwd_generic, stream_grid(rows * 32, 256), 256, 0, st)(x, gamma, gy, gx, rows, int(dim), eps);
         if (addend) { int rc = mft_accumulate(gx, addend, rows * dim, stream); if (rc) return rc; }
         if (gx16) { int rc = mft_cast_bf16(gx, dim, gx16, ld16, rows, dim, stream); if (rc) return rc; }
         parts = int(ceil_div(rows, 64));
-        if (want_wgrad) layernorm_wgrad_generic<<<parts, 256, 64 * 2 * sizeof(float), st>>>(x, gy, partial, rows, int(dim), eps, 64);
+        if (want_wgrad) pdl_launch(layernorm_wgrad_generic, parts, 256, 64 * 2 * sizeof(float), st)(x, gy, partial, rows, int(dim), eps, 64);
     }
     if (want_wgrad) {
-        norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dgamma, dbeta, parts, int(dim), 2);
+        pdl_launch(norm_wgrad_final, unsigned(ceil_div(dim, 32)), 256, 0, st)(partial, dgamma, dbeta, parts, int(dim), 2);
         add_launches(1);
     }
     MFT_CHECK_LAUNCH("mft_layernorm_bwd");
@@ -527,7 +537,7 @@ extern "C" int mft_rmsnorm_fwd(const float* x, const float* w, float* y, int64_t
                                int plus_one, mft_stream_t stream) {
     if (rows == 0 || dim == 0) return 0;
     if (!x || !w || !y) return set_error(1, "mft_rmsnorm_fwd: null pointer");
-    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one, nullptr, 0);
+    pdl_launch(rmsnorm_fwd_kernel, stream_grid(rows * 32, 256), 256, 0, as_stream(stream))(x, w, y, rows, int(dim), eps, plus_one, nullptr, 0);
     MFT_CHECK_LAUNCH("mft_rmsnorm_fwd");
     return 0;
 }
@@ -538,7 +548,7 @@ extern "C" int mft_rmsnorm_fwd_ex(const float* x, const float* w, float* y, void
     if (rows == 0 || dim == 0) return 0;
     if (!x || !w || !y) return set_error(1, "mft_rmsnorm_fwd_ex: null pointer");
     if (y_bf16 && ld_bf16 < dim) return set_error(1, "mft_rmsnorm_fwd_ex: bf16 pitch smaller than dim");
-    rmsnorm_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, w, y, rows, int(dim), eps, plus_one,
+    pdl_launch(rmsnorm_fwd_kernel, stream_grid(rows * 32, 256), 256, 0, as_stream(stream))(x, w, y, rows, int(dim), eps, plus_one,
                                                                                    static_cast<__nv_bfloat16*>(y_bf16), ld_bf16);
     MFT_CHECK_LAUNCH("mft_rmsnorm_fwd_ex");
     return 0;
@@ -574,10 +584,10 @@ static int rmsnorm_bwd_impl(const float* x, const float* w, const float* gy, flo
         cudaFuncSetAttribute(rmsnorm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     int parts = dw ? norm_bwd_ctas(rows) : int(std::min<int64_t>(ceil_div(rows, kNormWarps), int64_t(kNumSMs) * 8));
     float* partial = dw ? static_cast<float*>(workspace) : nullptr;     // dw == NULL (frozen weight): dx only, no second stage
-    rmsnorm_bwd_kernel<<<parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st>>>(
+    pdl_launch(rmsnorm_bwd_kernel, parts, kNormWarps * 32, size_t(kNormWarps) * dim * sizeof(float), st)(
         x, w, gy, gx, partial, rows, int(dim), eps, plus_one, static_cast<__nv_bfloat16*>(gx16), ld16);
     if (dw) {
-        norm_wgrad_final<<<unsigned(ceil_div(dim, 32)), 256, 0, st>>>(partial, dw, nullptr, parts, int(dim), 1);
+        pdl_launch(norm_wgrad_final, unsigned(ceil_div(dim, 32)), 256, 0, st)(partial, dw, nullptr, parts, int(dim), 1);
         add_launches(1);
     }
     MFT_CHECK_LAUNCH("mft_rmsnorm_bwd");
@@ -587,7 +597,7 @@ static int rmsnorm_bwd_impl(const float* x, const float* w, const float* gy, flo
 extern "C" int mft_softmax_fwd(const float* x, float* y, int64_t rows, int64_t dim, mft_stream_t stream) {
     if (rows == 0 || dim == 0) return 0;
     if (!x || !y) return set_error(1, "mft_softmax_fwd: null pointer");
-    softmax_fwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(x, y, rows, int(dim));
+    pdl_launch(softmax_fwd_kernel, stream_grid(rows * 32, 256), 256, 0, as_stream(stream))(x, y, rows, int(dim));
     MFT_CHECK_LAUNCH("mft_softmax_fwd");
     return 0;
 }
@@ -595,7 +605,7 @@ extern "C" int mft_softmax_fwd(const float* x, float* y, int64_t rows, int64_t d
 extern "C" int mft_softmax_bwd(const float* y, const float* gy, float* gx, int64_t rows, int64_t dim, mft_stream_t stream) {
     if (rows == 0 || dim == 0) return 0;
     if (!y || !gy || !gx) return set_error(1, "mft_softmax_bwd: null pointer");
-    softmax_bwd_kernel<<<stream_grid(rows * 32, 256), 256, 0, as_stream(stream)>>>(y, gy, gx, rows, int(dim));
+    pdl_launch(softmax_bwd_kernel, stream_grid(rows * 32, 256), 256, 0, as_stream(stream))(y, gy, gx, rows, int(dim));
     MFT_CHECK_LAUNCH("mft_softmax_bwd");
     return 0;
 }

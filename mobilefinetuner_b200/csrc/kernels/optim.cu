@@ -49,6 +49,7 @@ __device__ __forceinline__ int chunk_slot(const int* pre, int num_slots, int c) 
 
 __global__ void __launch_bounds__(kOptThreads)
 grad_sumsq_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, double* __restrict__ partial) {
+    pdl_sync();
     extern __shared__ int pre[];
     __shared__ double dred[32];
     const int total = chunk_prefix(slots, num_slots, pre, true);
@@ -80,6 +81,7 @@ grad_sumsq_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, doub
 }
 
 __global__ void __launch_bounds__(1024) sumsq_final_kernel(const double* __restrict__ partial, int parts, double* __restrict__ out) {
+    pdl_sync();
     __shared__ double dred[32];
     double s = 0.0;
     for (int i = threadIdx.x; i < parts; i += blockDim.x) s += partial[i];
@@ -89,6 +91,7 @@ __global__ void __launch_bounds__(1024) sumsq_final_kernel(const double* __restr
 
 __global__ void clip_scale_kernel(const double* __restrict__ sumsq, float max_norm, float pre_scale,
                                   float* __restrict__ scale_out, float* __restrict__ norm_out) {
+    pdl_sync();
     // gpt2_lora_finetune/main.cpp:491-516: norm = sqrt(sum g^2) (double); if norm > max: scale = max/(norm+1e-6)
     double norm = sqrt(sumsq[0]) * double(pre_scale);
     float sc = 1.0f;
@@ -99,6 +102,7 @@ __global__ void clip_scale_kernel(const double* __restrict__ sumsq, float max_no
 
 __global__ void __launch_bounds__(kOptThreads)
 scale_grads_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, const float* __restrict__ scale) {
+    pdl_sync();
     const float sc = scale[0];
     if (sc == 1.0f) return;
     const int64_t tid = blockIdx.x * int64_t(kOptThreads) + threadIdx.x;
@@ -124,6 +128,7 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 
 // steps[s] += 1 for every slot that has a gradient (optim/adam.cpp:35-43: the per-tensor step only advances then)
 __global__ void adam_advance_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, int32_t* __restrict__ steps) {
+    pdl_sync();
     for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < num_slots; s += gridDim.x * blockDim.x)
         if (slots[s].grad) steps[s] += 1;
 }
@@ -131,6 +136,7 @@ __global__ void adam_advance_kernel(const mft_tensor_slot* __restrict__ slots, i
 __global__ void __launch_bounds__(kOptThreads)
 adam_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float lr, const float* __restrict__ lr_dev, float b1, float b2,
             float eps, float wd, const float* __restrict__ grad_scale, const int32_t* __restrict__ steps) {
+    pdl_sync();
     extern __shared__ int pre[];
     const int total = chunk_prefix(slots, num_slots, pre, true);
     const float gs = grad_scale ? grad_scale[0] : 1.0f;
@@ -190,6 +196,7 @@ namespace mft {
 // bucket[offset + i] = grad[i] (0 where a tensor has no gradient): one launch packs every gradient for the all-reduce
 __global__ void __launch_bounds__(kOptThreads)
 pack_grads_kernel(const mft_tensor_slot* __restrict__ slots, int num_slots, float* __restrict__ bucket) {
+    pdl_sync();
     extern __shared__ int pre[];
     const int total = chunk_prefix(slots, num_slots, pre, false);
     for (int c = blockIdx.x; c < total; c += gridDim.x) {
@@ -210,7 +217,7 @@ extern "C" int mft_pack_grads(const mft_tensor_slot* slots, int32_t num_slots, f
     if (num_slots == 0) return 0;
     if (!slots || !bucket) return mft::set_error(1, "mft_pack_grads: null pointer");
     if (num_slots > mft::kOptMaxSlots) return mft::set_error(1, "mft_pack_grads: more than %d tensors", mft::kOptMaxSlots);
-    mft::pack_grads_kernel<<<mft::kOptCtas, mft::kOptThreads, size_t(num_slots + 1) * sizeof(int), mft::as_stream(stream)>>>(slots, num_slots, bucket);
+    pdl_launch(mft::pack_grads_kernel, mft::kOptCtas, mft::kOptThreads, size_t(num_slots + 1) * sizeof(int), mft::as_stream(stream))(slots, num_slots, bucket);
     MFT_CHECK_LAUNCH("mft_pack_grads");
     return 0;
 }
@@ -226,8 +233,8 @@ extern "C" int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, d
     cudaStream_t st = as_stream(stream);
     double* partial = static_cast<double*>(workspace);
     if (num_slots > kOptMaxSlots) return set_error(1, "mft_grad_sumsq: more than %d tensors", kOptMaxSlots);
-    grad_sumsq_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), st>>>(slots, num_slots, partial);
-    sumsq_final_kernel<<<1, 1024, 0, st>>>(partial, kOptCtas, out);
+    pdl_launch(grad_sumsq_kernel, kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), st)(slots, num_slots, partial);
+    pdl_launch(sumsq_final_kernel, 1, 1024, 0, st)(partial, kOptCtas, out);
     add_launches(1);
     MFT_CHECK_LAUNCH("mft_grad_sumsq");
     return 0;
@@ -236,7 +243,7 @@ extern "C" int mft_grad_sumsq(const mft_tensor_slot* slots, int32_t num_slots, d
 extern "C" int mft_clip_scale(const double* sumsq, float max_norm, float pre_scale, float* scale_out, float* norm_out,
                               mft_stream_t stream) {
     if (!sumsq) return set_error(1, "mft_clip_scale: null pointer");
-    clip_scale_kernel<<<1, 1, 0, as_stream(stream)>>>(sumsq, max_norm, pre_scale, scale_out, norm_out);
+    pdl_launch(clip_scale_kernel, 1, 1, 0, as_stream(stream))(sumsq, max_norm, pre_scale, scale_out, norm_out);
     MFT_CHECK_LAUNCH("mft_clip_scale");
     return 0;
 }
@@ -244,7 +251,7 @@ extern "C" int mft_clip_scale(const double* sumsq, float max_norm, float pre_sca
 extern "C" int mft_scale_grads(const mft_tensor_slot* slots, int32_t num_slots, const float* scale, mft_stream_t stream) {
     if (num_slots == 0) return 0;
     if (!slots || !scale) return set_error(1, "mft_scale_grads: null pointer");
-    scale_grads_kernel<<<kOptCtas, kOptThreads, 0, as_stream(stream)>>>(slots, num_slots, scale);
+    pdl_launch(scale_grads_kernel, kOptCtas, kOptThreads, 0, as_stream(stream))(slots, num_slots, scale);
     MFT_CHECK_LAUNCH("mft_scale_grads");
     return 0;
 }
@@ -254,7 +261,7 @@ extern "C" int mft_adam_step(const mft_tensor_slot* slots, int32_t num_slots, fl
     if (num_slots == 0) return 0;
     if (!slots) return set_error(1, "mft_adam_step: null slot table");
     if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step: more than %d tensors", kOptMaxSlots);
-    adam_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream)>>>(slots, num_slots, lr, nullptr, beta1, beta2, eps, weight_decay, grad_scale, nullptr);
+    pdl_launch(adam_kernel, kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream))(slots, num_slots, lr, nullptr, beta1, beta2, eps, weight_decay, grad_scale, nullptr);
     MFT_CHECK_LAUNCH("mft_adam_step");
     return 0;
 }
@@ -264,9 +271,9 @@ extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots
     if (num_slots == 0) return 0;
     if (!slots || !steps || !lr) return set_error(1, "mft_adam_step_dev: null pointer");
     if (num_slots > kOptMaxSlots) return set_error(1, "mft_adam_step_dev: more than %d tensors", kOptMaxSlots);
-    adam_advance_kernel<<<unsigned(ceil_div(num_slots, 256)), 256, 0, as_stream(stream)>>>(slots, num_slots, steps);
+    pdl_launch(adam_advance_kernel, unsigned(ceil_div(num_slots, 256)), 256, 0, as_stream(stream))(slots, num_slots, steps);
     add_launches(1);
-    adam_kernel<<<kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream)>>>(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
+    pdl_launch(adam_kernel, kOptCtas, kOptThreads, size_t(num_slots + 1) * sizeof(int), as_stream(stream))(slots, num_slots, 0.0f, lr, beta1, beta2, eps, weight_decay, grad_scale, steps);
     MFT_CHECK_LAUNCH("mft_adam_step_dev");
     return 0;
 }
@@ -277,6 +284,7 @@ extern "C" int mft_adam_step_dev(const mft_tensor_slot* slots, int32_t num_slots
 // cast / transpose-cast launch per tensor per step (96 adapter factors = 4 tiny launches each in the Gemma configuration).
 namespace mft {
 __global__ void refresh_shadows_kernel(const mft_shadow_slot* __restrict__ slots) {
+    pdl_sync();
     const mft_shadow_slot s = slots[blockIdx.y];
     const int64_t n = s.rows * s.cols;
     for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
@@ -295,7 +303,7 @@ extern "C" int mft_refresh_bf16_shadows(const mft_shadow_slot* slots, int32_t nu
     int64_t bx = ceil_div(max_elems > 0 ? max_elems : 1, int64_t(256) * 8);
     if (bx < 1) bx = 1;
     if (bx > 64) bx = 64;
-    mft::refresh_shadows_kernel<<<dim3(unsigned(bx), unsigned(num_slots)), 256, 0, as_stream(stream)>>>(slots);
+    pdl_launch(mft::refresh_shadows_kernel, dim3(unsigned(bx), unsigned(num_slots)), 256, 0, as_stream(stream))(slots);
     MFT_CHECK_LAUNCH("mft_refresh_bf16_shadows");
     return 0;
 }

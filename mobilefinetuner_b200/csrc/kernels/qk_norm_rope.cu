@@ -16,6 +16,7 @@ struct NormRopeSide {
 template <int MAXP>   // pairs per lane: Hd <= 64 * MAXP
 __global__ void __launch_bounds__(256)
 qk_norm_rope_fwd_kernel(NormRopeSide a, NormRopeSide b, int S, int Hd, float eps, float theta, int do_norm) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int half = Hd >> 1;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5, total = a.rows + b.rows;
@@ -57,6 +58,7 @@ qk_norm_rope_fwd_kernel(NormRopeSide a, NormRopeSide b, int S, int Hd, float eps
 template <int MAXP>
 __global__ void __launch_bounds__(256)
 qk_norm_rope_bwd_kernel(NormRopeSide a, int S, int Hd, float eps, float theta, int do_norm) {
+    pdl_sync();
     const int lane = threadIdx.x & 31;
     const int half = Hd >> 1;
     const int64_t warps = (int64_t(gridDim.x) * blockDim.x) >> 5;
@@ -117,8 +119,8 @@ extern "C" int mft_qk_norm_rope_fwd(const float* q, const float* wq, float* yq, 
     if (S < 1) return set_error(1, "mft_qk_norm_rope_fwd: S must be positive");
     NormRopeSide a{q, wq, nullptr, yq, rq, q_heads > 0 ? q_heads : 1}, b{k, wk, nullptr, yk, rk, k_heads > 0 ? k_heads : 1};
     const int grid = stream_grid((rq + rk) * 32, 256);
-    if (Hd <= 128) qk_norm_rope_fwd_kernel<2><<<grid, 256, 0, as_stream(stream)>>>(a, b, S, Hd, eps, theta, do_norm);
-    else qk_norm_rope_fwd_kernel<8><<<grid, 256, 0, as_stream(stream)>>>(a, b, S, Hd, eps, theta, do_norm);
+    if (Hd <= 128) pdl_launch(qk_norm_rope_fwd_kernel<2>, grid, 256, 0, as_stream(stream))(a, b, S, Hd, eps, theta, do_norm);
+    else pdl_launch(qk_norm_rope_fwd_kernel<8>, grid, 256, 0, as_stream(stream))(a, b, S, Hd, eps, theta, do_norm);
     MFT_CHECK_LAUNCH("mft_qk_norm_rope_fwd");
     return 0;
 }
@@ -132,8 +134,8 @@ extern "C" int mft_qk_norm_rope_bwd(const float* x, const float* w, const float*
     if (S < 1 || heads < 1) return set_error(1, "mft_qk_norm_rope_bwd: S and heads must be positive");
     NormRopeSide a{x, w, gy, gx, rows, heads};
     const int grid = stream_grid(rows * 32, 256);
-    if (Hd <= 128) qk_norm_rope_bwd_kernel<2><<<grid, 256, 0, as_stream(stream)>>>(a, S, Hd, eps, theta, do_norm);
-    else qk_norm_rope_bwd_kernel<8><<<grid, 256, 0, as_stream(stream)>>>(a, S, Hd, eps, theta, do_norm);
+    if (Hd <= 128) pdl_launch(qk_norm_rope_bwd_kernel<2>, grid, 256, 0, as_stream(stream))(a, S, Hd, eps, theta, do_norm);
+    else pdl_launch(qk_norm_rope_bwd_kernel<8>, grid, 256, 0, as_stream(stream))(a, S, Hd, eps, theta, do_norm);
     MFT_CHECK_LAUNCH("mft_qk_norm_rope_bwd");
     return 0;
 }

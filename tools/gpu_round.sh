@@ -6,7 +6,7 @@ M="gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_te
 out=gpurun_out
 for s in "$@"; do
   case $s in
-    tests) timeout 1500 python -m pytest tests -m gpu -x -q > $out/${tag}_tests.log 2>&1; tail -3 $out/${tag}_tests.log ;;
+    tests) timeout 600 python -m pytest tests -m gpu -x -q > $out/${tag}_tests.log 2>&1; tail -3 $out/${tag}_tests.log ;;
     bench_c4)
       timeout 600 python bench.py --steps 10 --warmup 3 > $out/${tag}_c4_strong.log 2>&1; tail -c 600 $out/${tag}_c4_strong.log
       timeout 600 python bench.py --scaling weak --steps 20 --warmup 5 > $out/${tag}_c4_weak.log 2>&1; tail -c 300 $out/${tag}_c4_weak.log ;;
@@ -41,6 +41,11 @@ for s in "$@"; do
       timeout 900 ncu --profile-from-start off --set full --import-source on --clock-control none -k regex:"gqa_fwd|gqa_bwd_dq|gqa_bwd_dkv" -c 3 -o $out/${tag}_gqa_full python tools/profile_step.py --config c3 > $out/${tag}_ncu_full_gqa.log 2>&1; ls -la $out/${tag}_gqa_full.ncu-rep ;;
     ncu_full_attn)
       timeout 900 ncu --profile-from-start off --set full --import-source on --clock-control none -k regex:"attention_tc_fwd" -c 2 -o $out/${tag}_attn_full python tools/profile_step.py --config c4 > $out/${tag}_ncu_full_attn.log 2>&1; ls -la $out/${tag}_attn_full.ncu-rep ;;
+    overlap1)   # the overlapped exchange with a one-rank communicator (one GPU): chunks, side stream, NCCL nodes inside the captured phase
+      MFT_USE_TENSOR_CORES=0 MFT_DP_OVERLAP=2 MFT_DP_CHUNK_KB=64 timeout 90 mobilefinetuner_b200/bin/dp_two_rank 1 8 1 > $out/${tag}_overlap1.log 2>&1; echo "overlap1 rc=$?"; tail -2 $out/${tag}_overlap1.log ;;
+    bench_nopdl)
+      for c in c1 c3; do MFT_PDL=0 timeout 300 python bench.py --config $c --steps 20 --warmup 5 --no-cpu-baseline > $out/${tag}_${c}_nopdl.log 2>&1; tail -1 $out/${tag}_${c}_nopdl.log | cut -c1-200; done
+      MFT_PDL=0 timeout 300 python bench.py --scaling weak --steps 20 --warmup 5 --no-cpu-baseline > $out/${tag}_c4_weak_nopdl.log 2>&1; tail -1 $out/${tag}_c4_weak_nopdl.log | cut -c1-200 ;;
     gemm_step) timeout 300 python tools/gemm_bench.py step > $out/${tag}_gemm_step.log 2>&1; tail -12 $out/${tag}_gemm_step.log ;;
     gemm_step64)
       timeout 300 python tools/gemm_bench.py step 32768 > $out/${tag}_gemm_step64.log 2>&1; tail -12 $out/${tag}_gemm_step64.log
