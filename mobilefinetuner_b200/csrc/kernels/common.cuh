@@ -149,11 +149,13 @@ __device__ __forceinline__ float gelu_tanh_grad_f(float x) {
 }
 
 
-// ---- programmatic dependent launch. Every kernel of the library starts with pdl_sync(): it lets the NEXT kernel of the stream
-// begin launching (its CTAs become resident as this kernel's leave), then waits until the PREVIOUS kernel has completed and its
-// writes are visible. Launched through pdl_launch, a kernel therefore overlaps only its launch latency and prologue with the
-// tail of its predecessor, never its memory accesses; in a chain of short kernels (a 512-token step is ~180 of them) that gap
-// is a large part of the step. Without the launch attribute both instructions are no-ops. MFT_PDL=0 switches the attribute off.
+// ---- programmatic dependent launch (opt-in: MFT_PDL=1). Every kernel of the library starts with pdl_sync(): it lets the NEXT
+// kernel of the stream begin launching (its CTAs become resident as this kernel's leave), then waits until the PREVIOUS kernel
+// has completed and its writes are visible. Launched through pdl_launch with the attribute, a kernel overlaps only its launch
+// latency with the tail of its predecessor, never its memory accesses. Without the attribute both instructions are no-ops.
+// Measured on B200 with the captured steps (profiles/r2_pdl_on_off.txt): c1 285 k vs 304 k tokens/s, c3 80.5 k vs 83.4 k with
+// the attribute on vs off — early-resident CTAs spinning in griddepcontrol.wait cost more than the launch gap they hide, so
+// the attribute stays off; all 222 GPU tests pass either way.
 __device__ __forceinline__ void pdl_sync() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");

@@ -7,7 +7,7 @@
 namespace mft {
 
 bool pdl_enabled() {
-    static const bool on = [] { const char* e = getenv("MFT_PDL"); return !(e && *e == '0'); }();
+    static const bool on = [] { const char* e = getenv("MFT_PDL"); return e && *e == '1'; }();      // off by default, see common.cuh
     return on;
 }
 
