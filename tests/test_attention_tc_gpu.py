@@ -32,6 +32,32 @@ def test_attention_tc_forward_matches_reference_attention(capi, B, H, S):
     assert rel(ctx16.float(), ctx.cpu().numpy()) < 5e-3
 
 
+@pytest.mark.parametrize("kind", ["peaky", "ramp"])
+def test_attention_tc_rescales_when_the_row_max_runs_ahead(capi, kind):
+    """O accumulates in TMEM under a scaling max that follows the running row max lazily (rescaled by a TMEM load / store only
+    when a later tile's max is more than 2^8 above it). Scores with a large spread ("peaky": std 9) and keys whose magnitude
+    grows with the position ("ramp") make that happen at most tiles; unit-variance inputs never do."""
+    B, H, S, Hd = 2, 2, 512, 64
+    C = H * Hd
+    rng = np.random.default_rng(77)
+    qkv = rng.standard_normal((B, S, 3 * C)).astype(np.float32)
+    if kind == "peaky":
+        qkv[:, :, :2 * C] *= 3.0
+    else:
+        qkv[:, :, C:2 * C] *= (1.0 + np.arange(S, dtype=np.float32) / 16.0)[None, :, None]
+    q16 = torch.tensor(qkv).cuda().to(torch.bfloat16).contiguous()
+    ctx = torch.full((B, S, C), float("nan"), device="cuda")
+    scale = 0.125
+    capi.call("mft_causal_attention_tc_fwd", q16, 3 * C, ctx, None, B, H, S, Hd, scale, None)
+    torch.cuda.synchronize()
+    heads = lambda a: np.ascontiguousarray(a.reshape(B, S, H, Hd).transpose(0, 2, 1, 3))
+    qr = q16.float().cpu().numpy()
+    e = O.causal_attention_fwd(heads(qr[:, :, :C]), heads(qr[:, :, C:2 * C]), heads(qr[:, :, 2 * C:]), scale)
+    e = e.transpose(0, 2, 1, 3).reshape(B, S, C)
+    assert bool(torch.isfinite(ctx).all())
+    assert rel(ctx, e) < 4e-3, (kind, rel(ctx, e))
+
+
 def test_attention_tc_rejects_other_head_sizes(capi):
     x = torch.zeros(1, 8, 3 * 32, device="cuda", dtype=torch.bfloat16)
     out = torch.empty(1, 8, 32, device="cuda")
