@@ -181,7 +181,8 @@ def test_attention_bf16_operand_mode(capi, B, H, S):
 
 # ----------------------------------------------------------------------------- tcgen05 TF32 path
 @pytest.mark.parametrize("m,n,k", [(128, 256, 32), (128, 64, 64), (512, 768, 768), (512, 2304, 768), (300, 200, 100),
-                                   (2048, 3072, 768), (129, 257, 36), (4096, 1024, 4096), (64, 64, 4096)])
+                                   (2048, 3072, 768), (129, 257, 36), (4096, 1024, 4096), (64, 64, 4096),
+                                   (4500, 300, 64)])       # 18 m-units: one raster group of 16 and a short one of 2
 def test_gemm_tc_shapes(capi, m, n, k):
     rng = np.random.default_rng(m + n + k)
     a = rng.standard_normal((m, k)).astype(np.float32)
@@ -272,7 +273,7 @@ def test_gemm_tc_batched_and_pitched(capi):
 
 
 @pytest.mark.parametrize("m,n,k,r", [(512, 768, 768, 0), (4096, 1024, 1024, 16), (300, 200, 104, 8), (256, 50257, 768, 0),
-                                     (2048, 3072, 768, 0)])
+                                     (2048, 3072, 768, 0), (5000, 520, 128, 0)])      # 20 m-units: raster groups of 16 + 4
 def test_gemm_bf16_tensor_core_path(capi, m, n, k, r):
     """mft_cast_bf16 / mft_transpose_cast_bf16 + mft_gemm_bf16 (kind::f16 tcgen05) against the fp64 product."""
     rng = np.random.default_rng(m + n + k)
