@@ -539,6 +539,10 @@ def test_lowp_elementwise_kernels(capi):
     capi.call("mft_gelu_bwd_lowp", dx, 0, dgy16, gx32, gx16, n, None)
     e = O.gelu_bwd(x, dgy16.float().cpu().numpy())
     assert rel(gx32, e) < FP32_TOL and torch.equal(gx16, gx32.to(torch.bfloat16))
+    gx16f = torch.empty(n, device="cuda", dtype=torch.bfloat16)      # bf16 as the only result: hardware tanh, at most one bf16 step away
+    capi.call("mft_gelu_bwd_lowp", dx, 0, dgy16, None, gx16f, n, None)
+    assert rel(gx16f.float(), e) < 5e-3
+    assert bool(((gx16f.float() - gx16.float()).abs() <= gx16.float().abs() * 2.0 ** -6 + 1e-3).all())
     x16 = dx.to(torch.bfloat16)
     capi.call("mft_gelu_bwd_lowp", x16, 1, dgy16, None, gx16, n, None)
     assert rel(gx16.float(), O.gelu_bwd(x16.float().cpu().numpy(), dgy16.float().cpu().numpy())) < 5e-3
